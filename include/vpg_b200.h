@@ -1,0 +1,200 @@
+/*
+ * vpg_b200.h — C ABI of libvpg_b200.so: the B200-native (sm_100a) per-token policy-gradient hot path of verl.
+ *
+ * The reference (rfahrn/verl) is pure Python and has no FFI; its boundary for this path is a set of Python
+ * functions.  Each entry point below names the reference function it replaces (file:line under
+ * /root/reference).  The Python mirror in verl_b200/ binds these with ctypes and re-exposes the reference names.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller (PyTorch's allocator); the library never allocates
+ *    or frees device memory, never synchronises, and enqueues all work on `stream` (a cudaStream_t);
+ *  - return value 0 = success, negative = error (vpg_last_error() gives the message); no exceptions, no exit;
+ *  - "f32" buffers are float, "bf16" are __nv_bfloat16 bit patterns, "i64" int64_t, "i32" int32_t;
+ *  - masks are int64 / int32 / uint8(bool) / float32 selected by `mask_dtype` (VPG_MASK_*): the reference passes
+ *    int64 attention/response masks (verl/protocol.py), bool and float also occur in its tests.
+ */
+#ifndef VPG_B200_H_
+#define VPG_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VPG_OK 0
+#define VPG_ERR_INVALID (-1)
+#define VPG_ERR_CUDA (-2)
+#define VPG_ERR_WORKSPACE (-3)
+#define VPG_ERR_UNSUPPORTED (-4)
+
+/* mask / value element types */
+#define VPG_MASK_I64 0
+#define VPG_MASK_I32 1
+#define VPG_MASK_U8 2
+#define VPG_MASK_F32 3
+
+/* agg_loss modes — verl/trainer/ppo/core_algos.py:686-719 */
+#define VPG_AGG_TOKEN_MEAN 0
+#define VPG_AGG_SEQ_MEAN_TOKEN_SUM 1
+#define VPG_AGG_SEQ_MEAN_TOKEN_MEAN 2
+#define VPG_AGG_SEQ_MEAN_TOKEN_SUM_NORM 3
+
+/* kl_penalty kinds — verl/trainer/ppo/core_algos.py:1034-1069 */
+#define VPG_KL_K1 0      /* "kl" / "k1"          */
+#define VPG_KL_ABS 1     /* "abs"                */
+#define VPG_KL_MSE 2     /* "mse" / "k2"         */
+#define VPG_KL_LOW_VAR 3 /* "low_var_kl" / "k3"  */
+#define VPG_KL_NONE (-1)
+
+const char* vpg_version(void);
+/* last error message of the calling thread ("" if none) */
+const char* vpg_last_error(void);
+/* number of kernels this library has launched in the calling process (monotonic; for bench.py's gpu_launches) */
+int64_t vpg_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Fused lm-head -> per-token log-prob + entropy.
+ * Replaces verl/utils/kernel/kernels.py:474-663 (efficient_entropy_forward: Triton mainloop :120-254 + epilogue
+ * :257-346) behind verl/utils/kernel/linear_cross_entropy.py:42-87.
+ *
+ * Stage 1 (vpg_lce_fwd_partials): tcgen05/TMEM GEMM hidden[T,H] x weight[V,H]^T fed by TMA with the online
+ *   softmax statistics fused in the epilogue; the [T,V] logits are never written.  Per token and per vocab split
+ *   s it writes 4 floats into `partials` laid out [4][num_splits][T]:
+ *     plane 0: m  = max_v  (x_v * log2(e)/temperature)           (log2 domain)
+ *     plane 1: s  = sum_v  2^(x_v*log2e/temp - m)
+ *     plane 2: b  = sum_v  x_v * 2^(x_v*log2e/temp - m)           (x = raw dot product)
+ *     plane 3: t  = x_{label}  if the label falls in this split (after subtracting label_offset) else 0
+ * Stage 2 (vpg_lce_finalize): merges `num_parts` partial sets (splits, and for vocab-parallel runs the gathered
+ *   partials of all ranks) into logprobs[T], entropy[T] and the two per-token scalars the backward needs:
+ *   lse[T] (natural-log log-sum-exp of logits/temperature) and eb[T] (= sum_v p_v * logit_v).
+ *
+ * hidden: bf16 [T,H] row-major, weight: bf16 [V,H] row-major (nn.Linear layout), labels: i64 [T].
+ * H % 64 == 0 is required (the reference requires H % 128 == 0, kernels.py:504).
+ * label_offset = rank * V_local for vocab-parallel shards (kernels.py:232), 0 otherwise.
+ * ------------------------------------------------------------------------------------------------------------ */
+int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm_count);
+int vpg_lce_fwd_partials(const void* hidden_bf16, const void* weight_bf16, const int64_t* labels, int64_t T,
+                         int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                         float* partials /* [4][num_splits][T] */, void* stream);
+int vpg_lce_finalize(const float* partials /* [4][num_parts][T] */, int num_parts, int64_t T, float temperature,
+                     float* logprobs, float* entropy, float* lse, float* eb, void* stream);
+
+/* Backward.  Replaces verl/utils/kernel/kernels.py:1345-1553 (efficient_entropy_backward; default strategy
+ * _Split_Dlogits_N :1230-1342 + two cuBLAS GEMMs :1538-1548).
+ *   dlogits[t,v] = ( g_lp[t]*(1[v==label_t] - p) - g_ent[t]*p*(logit - eb[t]) ) / temperature
+ *   d_hidden = dlogits . W        d_weight = dlogits^T . hidden
+ * The vocab range is processed in chunks of `chunk_v` columns (multiple of 256): recompute tile -> dlogits chunk
+ * (bf16 workspace, never the logits) -> two tcgen05 GEMMs.  d_hidden is accumulated in fp32 across chunks.
+ * Workspace size: vpg_lce_bwd_workspace_bytes().  g_lp / g_ent may be NULL (treated as zeros).
+ * d_hidden: bf16 [T,H]; d_weight: bf16 [V,H].  For vocab-parallel shards the caller all-reduces d_hidden. */
+size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v);
+int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V);
+int vpg_lce_bwd(const void* hidden_bf16, const void* weight_bf16, const int64_t* labels, const float* lse,
+                const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
+                float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden_bf16, void* d_weight_bf16,
+                void* workspace, size_t workspace_bytes, void* stream);
+
+/* Plain bf16 GEMM on the same tcgen05 mainloop (used by the backward; exported for tests):
+ *   C[M,N] (bf16 or f32) = A . B with
+ *   a_kmajor=1: A is [M,K] row-major, else A is [K,M] row-major (i.e. A^T stored);
+ *   b_kmajor=1: B is [N,K] row-major, else B is [K,N] row-major.
+ *   out_mode 0: store bf16, 1: store f32, 2: f32 += , 3: bf16 = f32_accum_in + acc (accum_in given separately) */
+int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                  int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
+                  int64_t ld_accum, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Materialised-logits variants — verl/utils/torch_functional.py:64-133 (logprobs_from_logits*) and :145-160
+ * (entropy_from_logits*).  logits: [T,V] f32 or bf16 (logits_bf16 != 0), row stride ld (elements).
+ * One pass over each row: online log-sum-exp, label gather and sum p*logit.  Either output may be NULL.
+ * ------------------------------------------------------------------------------------------------------------ */
+int vpg_logits_stats(const void* logits, int logits_bf16, int64_t T, int64_t V, int64_t ld, const int64_t* labels,
+                     float* logprobs, float* entropy, float* lse, void* stream);
+/* backward of the above: dlogits = g_lp*(onehot - p) - g_ent*p*(logit - eb), with eb = lse - entropy */
+int vpg_logits_stats_bwd(const void* logits, int logits_bf16, int64_t T, int64_t V, int64_t ld,
+                         const int64_t* labels, const float* lse, const float* entropy, const float* g_lp,
+                         const float* g_ent, void* dlogits, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * rmpad index plumbing — flash_attn.bert_padding (unpad_input / index_first_axis / pad_input), third-party file
+ * used at verl/workers/actor/dp_actor.py:110-125,221-232, and verl/utils/torch_functional.py:629-638
+ * (get_unpad_data).  Integer outputs are bit-exact.
+ *   mask [B,S] -> indices i64 [nnz] (ascending flat positions of non-zero mask), seqlens i32 [B],
+ *   cu_seqlens i32 [B+1], totals i32 [2] = {nnz, max_seqlen}.  workspace: vpg_unpad_workspace_bytes(B*S).
+ * ------------------------------------------------------------------------------------------------------------ */
+size_t vpg_unpad_workspace_bytes(int64_t n);
+int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,
+                      int32_t* cu_seqlens, int32_t* totals, void* workspace, size_t workspace_bytes, void* stream);
+/* out[i, :] = src[indices[i], :]  rows of row_bytes bytes (index_first_axis) */
+int vpg_gather_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
+                    void* stream);
+/* out[indices[i], :] = src[i, :]; `out` has n_out rows and is zero-filled first when zero_fill != 0 (pad_input);
+ * accumulate_f32 != 0 does out += (float rows; backward of index_first_axis with repeated indices not needed). */
+int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
+                     int64_t n_out, int zero_fill, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Token ops — verl/trainer/ppo/core_algos.py and verl/utils/torch_functional.py.
+ * All value tensors are f32 [B,L] contiguous; mask as described above.
+ * ------------------------------------------------------------------------------------------------------------ */
+
+/* masked_sum/masked_mean building block (torch_functional.py:163-185): out[0] = sum(where(m,v,0)*m),
+ * out[1] = sum(m).  `out` (2 doubles) is zeroed by the call.  axis=None only. */
+int vpg_masked_sum(const float* values, const void* mask, int mask_dtype, int64_t n, double* out, void* stream);
+/* per-row variant: out_sum[b], out_cnt[b] (float) — used for axis=-1 and the seq-mean agg modes */
+int vpg_masked_row_sum(const float* values, const void* mask, int mask_dtype, int64_t B, int64_t L, float* out_sum,
+                       float* out_cnt, void* stream);
+
+/* kl_penalty elementwise forward (core_algos.py:1034-1069); grad_out (may be NULL) receives d kl / d logprob */
+int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int64_t n, float* out, float* grad_out,
+                   void* stream);
+
+/* Fused actor loss, forward + closed-form gradient in one pass:
+ *   compute_policy_loss (core_algos.py:722-794) + entropy bonus + KL loss + agg_loss as composed in
+ *   verl/workers/actor/dp_actor.py:422-469:
+ *     policy_loss = agg(pg) - entropy_coeff*agg(entropy) + kl_coef*agg(kl_penalty(lp, ref))   , times loss_scale
+ *   entropy / ref_log_prob may be NULL (coeffs ignored).
+ *   metrics[8] (f32, device): {policy_loss, pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower, entropy_agg, kl_agg,
+ *                             mask_sum}
+ *   d_log_prob / d_entropy (may be NULL): gradient of policy_loss (incl. loss_scale) wrt log_prob / entropy.
+ *   workspace: vpg_ppo_loss_workspace_bytes(B, L). */
+size_t vpg_ppo_loss_workspace_bytes(int64_t B, int64_t L);
+int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
+                 int mask_dtype, const float* entropy, const float* ref_log_prob, int64_t B, int64_t L,
+                 float clip_low, float clip_high, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
+                 int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy, void* workspace,
+                 size_t workspace_bytes, void* stream);
+
+/* agg_loss forward for an arbitrary loss matrix (core_algos.py:686-719); out[0] = loss; d_loss_mat (may be NULL)
+ * receives d loss / d loss_mat.  workspace as vpg_ppo_loss_workspace_bytes. */
+int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_t B, int64_t L, int agg_mode,
+                 float* out, float* d_loss_mat, void* workspace, size_t workspace_bytes, void* stream);
+
+/* compute_grpo_outcome_advantage (core_algos.py:245-308): scores = row-sum(rewards); per group (group_ids i32 [B],
+ * values in [0,num_groups), built on the host from the uid strings in first-seen order) mean and unbiased std,
+ * singleton -> (0,1); adv = (score-mean)/(std+eps) (or score-mean) broadcast * mask.
+ * workspace: vpg_grpo_workspace_bytes(B, num_groups). */
+size_t vpg_grpo_workspace_bytes(int64_t B, int64_t num_groups);
+int vpg_grpo_advantage(const float* token_level_rewards, const void* mask, int mask_dtype, const int32_t* group_ids,
+                       int64_t B, int64_t L, int64_t num_groups, float epsilon, int norm_by_std, float* advantages,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* compute_gae_advantage_return (core_algos.py:193-241): reverse recurrence per row with masked carry-through,
+ * returns = adv + values, then masked_whiten (torch_functional.py:206-223) over the whole batch.
+ * status[0] (i32, device) = 0 ok, 1 mask sum == 0, 2 mask sum == 1 (the reference raises ValueError there).
+ * workspace: vpg_gae_workspace_bytes(B, L). */
+size_t vpg_gae_workspace_bytes(int64_t B, int64_t L);
+int vpg_gae(const float* token_level_rewards, const float* values, const void* mask, int mask_dtype, int64_t B,
+            int64_t L, float gamma, float lam, float* advantages, float* returns, int32_t* status, void* workspace,
+            size_t workspace_bytes, void* stream);
+
+/* masked_whiten (torch_functional.py:206-223) over all elements. status as above. */
+int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
+                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VPG_B200_H_ */

@@ -1,0 +1,169 @@
+"""ctypes binding of libvpg_b200.so (see include/vpg_b200.h).
+
+There is no CPU fallback: importing this module without the built library, or calling an op on a non-CUDA tensor,
+raises.  Build the library with ``python -m verl_b200.csrc.build`` (or ``__graft_entry__.build()``).
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libvpg_b200.so"
+
+c_void_p, c_int, c_int64, c_float, c_size_t = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol declared in include/vpg_b200.h
+SIGNATURES: dict[str, tuple] = {
+    "vpg_version": (C.c_char_p, []),
+    "vpg_last_error": (C.c_char_p, []),
+    "vpg_launch_count": (c_int64, []),
+    "vpg_lce_num_splits": (c_int, [c_int64, c_int64, c_int64, c_int]),
+    "vpg_lce_fwd_partials": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_void_p],
+    ),
+    "vpg_lce_finalize": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "vpg_lce_bwd_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64]),
+    "vpg_lce_bwd_default_chunk": (c_int64, [c_int64, c_int64, c_int64]),
+    "vpg_lce_bwd": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float,
+         c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_gemm_bf16": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_int,
+         c_void_p, c_int64, c_void_p],
+    ),
+    "vpg_logits_stats": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "vpg_logits_stats_bwd": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p],
+    ),
+    "vpg_unpad_workspace_bytes": (c_size_t, [c_int64]),
+    "vpg_unpad_indices": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_gather_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "vpg_scatter_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int, c_void_p]),
+    "vpg_masked_sum": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_void_p, c_void_p]),
+    "vpg_masked_row_sum": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "vpg_kl_penalty": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p]),
+    "vpg_ppo_loss_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "vpg_ppo_loss": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float,
+         c_float, c_int, c_float, c_float, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+         c_void_p],
+    ),
+    "vpg_agg_loss": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_grpo_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "vpg_grpo_advantage": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p,
+         c_size_t, c_void_p],
+    ),
+    "vpg_gae_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "vpg_gae": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_masked_whiten": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+}
+
+MASK_I64, MASK_I32, MASK_U8, MASK_F32 = 0, 1, 2, 3
+AGG_MODES = {
+    "token-mean": 0,
+    "seq-mean-token-sum": 1,
+    "seq-mean-token-mean": 2,
+    "seq-mean-token-sum-norm": 3,
+}
+KL_KINDS = {"kl": 0, "k1": 0, "abs": 1, "mse": 2, "k2": 2, "low_var_kl": 3, "k3": 3}
+
+_lib = None
+
+
+def lib_path() -> Path:
+    return Path(os.environ.get("VPG_B200_LIB", str(_LIB_PATH)))
+
+
+def load() -> C.CDLL:
+    """Load the shared library and bind every declared symbol (raises if the library or a symbol is missing)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not path.exists():
+        raise RuntimeError(
+            f"{path} is missing: build it with `python -m verl_b200.csrc.build`. "
+            "verl_b200 has no CPU / PyTorch fallback for its CUDA ops."
+        )
+    lib = C.CDLL(str(path))
+    for name, (restype, argtypes) in SIGNATURES.items():
+        if os.environ.get("VPG_B200_PARTIAL") == "1" and not hasattr(lib, name):
+            continue  # developer probe of a partially built library only
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().vpg_last_error().decode()
+        kind = {-1: ValueError, -3: RuntimeError, -4: NotImplementedError}.get(rc, RuntimeError)
+        raise kind(f"libvpg_b200 error {rc}: {msg}")
+
+
+def ptr(t: torch.Tensor | None):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("verl_b200 ops require CUDA tensors (there is no CPU fallback)")
+    if not t.is_contiguous():
+        raise ValueError("verl_b200 ops require contiguous tensors")
+    return t.data_ptr()
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def mask_arg(mask: torch.Tensor):
+    """(tensor, dtype enum) for a mask; bool is reinterpreted as uint8 without a copy."""
+    if mask.dtype == torch.int64:
+        return mask, MASK_I64
+    if mask.dtype == torch.int32:
+        return mask, MASK_I32
+    if mask.dtype == torch.bool:
+        return mask.view(torch.uint8), MASK_U8
+    if mask.dtype == torch.uint8:
+        return mask, MASK_U8
+    if mask.dtype == torch.float32:
+        return mask, MASK_F32
+    return mask.to(torch.float32), MASK_F32
+
+
+def launch_count() -> int:
+    return int(load().vpg_launch_count())

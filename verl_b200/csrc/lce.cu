@@ -1,0 +1,354 @@
+// Fused lm-head -> log-prob / entropy (forward partials, finalize, backward) and the plain tcgen05 GEMM entry.
+// Replaces verl/utils/kernel/kernels.py:474-663 (forward) and :1345-1553 (backward) of the reference.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <mutex>
+
+#include "common.h"
+#include "tc_gemm.cuh"
+
+namespace vpg {
+
+// --------------------------------------------------------------------------------------- tensor maps (host)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    });
+    return fn;
+}
+
+// bf16 2-D tensor map over a row-major [outer][inner] matrix with row stride ld (elements), 128B swizzle.
+static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
+                     int box_outer) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld * 2) % 16 != 0)
+        return set_error(VPG_ERR_INVALID, "TMA operand must be 16-byte aligned with a 16-byte-multiple row stride");
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return VPG_OK;
+}
+
+// K-major operand stored [rows][K]; MN-major operand stored [K][rows]
+static int make_operand_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int64_t ld, bool mn_major,
+                             int tile_rows) {
+    if (!mn_major) return make_tmap(tm, base, K, rows, ld, kBlockK, tile_rows);
+    return make_tmap(tm, base, rows, K, ld, 64, kBlockK);
+}
+
+template <int kMode, bool kAMn, bool kBMn>
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn>;
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    // per-device attribute: set every call (cheap) so multi-device processes are handled
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    (void)once;
+    if (attr_err != cudaSuccess)
+        return set_error(VPG_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", kSmemBytes,
+                         cudaGetErrorString(attr_err));
+    const int64_t units = static_cast<int64_t>(p.num_m_tiles) * p.num_splits;
+    if (units <= 0) return VPG_OK;
+    const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
+    kern<<<grid, kNumThreads, kSmemBytes, stream>>>(ta, tb, p);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+// balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
+static int choose_splits(int num_m_tiles, int num_n_tiles, int grid) {
+    int best_s = 1;
+    double best_cost = 1e30;
+    const int max_s = num_n_tiles < 64 ? num_n_tiles : 64;
+    for (int s = 1; s <= max_s; ++s) {
+        const int tps = (num_n_tiles + s - 1) / s;
+        const int s_eff = (num_n_tiles + tps - 1) / tps;  // non-empty splits
+        if (s_eff != s) continue;
+        const int64_t units = static_cast<int64_t>(num_m_tiles) * s;
+        const int last = num_n_tiles - (s - 1) * tps;
+        // worst CTA load under u = blockIdx + i*grid
+        int64_t worst = 0;
+        const int g = static_cast<int>(units < grid ? units : grid);
+        for (int cta = 0; cta < g; ++cta) {
+            int64_t load = 0;
+            for (int64_t u = cta; u < units; u += g) load += ((u % s) == s - 1) ? last : tps;
+            if (load > worst) worst = load;
+        }
+        // mild preference for >= 4 concurrent vocab streams (L2 reuse of the token tile) and fewer partials
+        double cost = static_cast<double>(worst) * (1.0 + 0.002 * s) * (s < 4 && num_m_tiles * s >= grid ? 1.03 : 1.0);
+        if (cost < best_cost) {
+            best_cost = cost;
+            best_s = s;
+        }
+    }
+    return best_s;
+}
+
+// --------------------------------------------------------------------------------------- finalize kernel
+// partials [4][P][T] -> logprobs, entropy, lse, eb.  One thread per token; reads are coalesced along T.
+__global__ void lce_finalize_kernel(const float* __restrict__ part, int P, long long T, float inv_temp,
+                                    float* __restrict__ logprobs, float* __restrict__ entropy,
+                                    float* __restrict__ lse_out, float* __restrict__ eb_out) {
+    const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    const long long plane = static_cast<long long>(P) * T;
+    float m = -INFINITY;
+    for (int i = 0; i < P; ++i) m = fmaxf(m, part[i * T + t]);
+    float s = 0.f, b = 0.f, tg = 0.f;
+    for (int i = 0; i < P; ++i) {
+        const float mi = part[i * T + t];
+        const float f = (mi == -INFINITY) ? 0.f : exp2f(mi - m);
+        s = fmaf(part[plane + i * T + t], f, s);
+        b = fmaf(part[2 * plane + i * T + t], f, b);
+        tg += part[3 * plane + i * T + t];
+    }
+    const float ln2 = 0.6931471805599453f;
+    const float lse = (m + log2f(s)) * ln2;
+    const float eb = (b / s) * inv_temp;
+    if (logprobs) logprobs[t] = tg * inv_temp - lse;
+    if (entropy) entropy[t] = lse - eb;
+    if (lse_out) lse_out[t] = lse;
+    if (eb_out) eb_out[t] = eb;
+}
+
+static int check_lce_shapes(int64_t T, int64_t H, int64_t V) {
+    VPG_CHECK_ARG(T >= 0 && H > 0 && V > 0, "invalid shape T=%lld H=%lld V=%lld", (long long)T, (long long)H,
+                  (long long)V);
+    VPG_CHECK_ARG(H % 64 == 0, "hidden size must be a multiple of 64 (got %lld)", (long long)H);
+    VPG_CHECK_ARG(T < (1LL << 31) - 256 && V < (1LL << 31) - 256, "T and V must fit in int32");
+    return VPG_OK;
+}
+
+}  // namespace vpg
+
+using namespace vpg;
+
+extern "C" {
+
+int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
+    (void)H;
+    if (T <= 0 || V <= 0) return 1;
+    if (sm <= 0) sm = sm_count();
+    return choose_splits(static_cast<int>(ceil_div(T, kBlockM)), static_cast<int>(ceil_div(V, kBlockN)), sm);
+}
+
+int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
+                         int64_t V, float temperature, int64_t label_offset, int num_splits, float* partials,
+                         void* stream) {
+    int rc = check_lce_shapes(T, H, V);
+    if (rc) return rc;
+    VPG_CHECK_ARG(hidden && weight && labels && partials, "null pointer argument");
+    VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0 (got %f)", temperature);
+    if (T == 0) return VPG_OK;
+    TcParams p{};
+    p.num_m_tiles = static_cast<int>(ceil_div(T, kBlockM));
+    p.num_n_tiles = static_cast<int>(ceil_div(V, kBlockN));
+    p.num_k_blocks = static_cast<int>(H / kBlockK);
+    VPG_CHECK_ARG(num_splits >= 1 && num_splits <= p.num_n_tiles, "num_splits %d out of range [1,%d]", num_splits,
+                  p.num_n_tiles);
+    p.num_splits = num_splits;
+    p.tiles_per_split = static_cast<int>(ceil_div(p.num_n_tiles, num_splits));
+    p.M = static_cast<int>(T);
+    p.N = static_cast<int>(V);
+    p.scale_log2 = 1.4426950408889634f / temperature;
+    p.inv_temp = 1.0f / temperature;
+    p.labels = reinterpret_cast<const long long*>(labels);
+    p.label_offset = label_offset;
+    p.partials = partials;
+    CUtensorMap ta, tb;
+    if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
+    if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, kBlockN))) return rc;
+    return launch_tc<MODE_FWD, false, false>(ta, tb, p, static_cast<cudaStream_t>(stream));
+}
+
+int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temperature, float* logprobs,
+                     float* entropy, float* lse, float* eb, void* stream) {
+    VPG_CHECK_ARG(partials && num_parts >= 1 && T >= 0, "invalid finalize arguments");
+    VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
+    if (T == 0) return VPG_OK;
+    const int threads = 256;
+    lce_finalize_kernel<<<static_cast<unsigned>(ceil_div(T, threads)), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        partials, num_parts, T, 1.0f / temperature, logprobs, entropy, lse, eb);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
+    (void)H;
+    const int64_t t_pad = round_up(T > 0 ? T : 1, kBlockM);
+    const int64_t v_pad = round_up(V, kBlockN);
+    const int64_t budget = 3LL << 30;  // bytes of bf16 dlogits workspace
+    int64_t c = budget / (t_pad * 2) / kBlockN * kBlockN;
+    if (c < kBlockN) c = kBlockN;
+    if (c > v_pad) c = v_pad;
+    // even out the chunks
+    const int64_t n_chunks = ceil_div(v_pad, c);
+    c = round_up(ceil_div(v_pad, n_chunks), kBlockN);
+    return c;
+}
+
+size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v) {
+    if (T <= 0) return 0;
+    if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
+    const int64_t t_pad = round_up(T, kBlockM);
+    const int64_t v_pad = round_up(V, kBlockN);
+    if (chunk_v > v_pad) chunk_v = v_pad;
+    size_t bytes = static_cast<size_t>(t_pad) * chunk_v * 2;
+    bytes = round_up(bytes, 256);
+    if (chunk_v < v_pad) bytes += static_cast<size_t>(T) * H * 4;  // fp32 d_hidden accumulator
+    return bytes + 256;
+}
+
+int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, const float* lse, const float* eb,
+                const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V, float temperature,
+                int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight, void* workspace,
+                size_t workspace_bytes, void* stream_) {
+    int rc = check_lce_shapes(T, H, V);
+    if (rc) return rc;
+    VPG_CHECK_ARG(hidden && weight && labels && lse && eb && d_hidden && d_weight, "null pointer argument");
+    VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (T == 0) {
+        VPG_CUDA(cudaMemsetAsync(d_weight, 0, static_cast<size_t>(V) * H * 2, stream));
+        return VPG_OK;
+    }
+    if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
+    VPG_CHECK_ARG(chunk_v % kBlockN == 0, "chunk_v must be a multiple of %d", kBlockN);
+    const int64_t t_pad = round_up(T, kBlockM);
+    const int64_t v_pad = round_up(V, kBlockN);
+    if (chunk_v > v_pad) chunk_v = v_pad;
+    const size_t need = vpg_lce_bwd_workspace_bytes(T, H, V, chunk_v);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "lce_bwd workspace too small: need %zu bytes, got %zu", need,
+                         workspace_bytes);
+    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-byte aligned");
+    __nv_bfloat16* ds = reinterpret_cast<__nv_bfloat16*>(workspace);
+    const int64_t ldds = chunk_v;
+    float* dh_acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) +
+                                             round_up(static_cast<int64_t>(t_pad) * chunk_v * 2, 256));
+    const int num_chunks = static_cast<int>(ceil_div(v_pad, chunk_v));
+    const int m_tiles_t = static_cast<int>(t_pad / kBlockM);
+
+    for (int ci = 0; ci < num_chunks; ++ci) {
+        const int64_t v0 = static_cast<int64_t>(ci) * chunk_v;
+        const int64_t vc = (V - v0) < chunk_v ? (V - v0) : chunk_v;
+        const __nv_bfloat16* w_chunk = reinterpret_cast<const __nv_bfloat16*>(weight) + v0 * H;
+        const int n_tiles_c = static_cast<int>(ceil_div(vc, kBlockN));
+        CUtensorMap ta, tb;
+        {  // 1. recompute logits tile -> dlogits chunk (bf16)
+            TcParams p{};
+            p.num_m_tiles = m_tiles_t;
+            p.num_n_tiles = n_tiles_c;
+            p.num_k_blocks = static_cast<int>(H / kBlockK);
+            p.num_splits = choose_splits(m_tiles_t, n_tiles_c, sm_count());
+            p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
+            p.M = static_cast<int>(T);
+            p.N = static_cast<int>(vc);
+            p.scale_log2 = 1.4426950408889634f / temperature;
+            p.inv_temp = 1.0f / temperature;
+            p.labels = reinterpret_cast<const long long*>(labels);
+            p.label_offset = label_offset + v0;
+            p.lse = lse;
+            p.eb = eb;
+            p.g_lp = g_lp;
+            p.g_ent = g_ent;
+            p.ds = ds;
+            p.ldds = ldds;
+            if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
+            if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, kBlockN))) return rc;
+            if ((rc = launch_tc<MODE_DS, false, false>(ta, tb, p, stream))) return rc;
+        }
+        const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
+        {  // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
+            TcParams p{};
+            p.num_m_tiles = static_cast<int>(ceil_div(vc, kBlockM));
+            p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
+            p.num_k_blocks = static_cast<int>(t_pad / kBlockK);
+            p.num_splits = p.num_n_tiles;
+            p.tiles_per_split = 1;
+            p.M = static_cast<int>(vc);
+            p.N = static_cast<int>(H);
+            p.out = reinterpret_cast<__nv_bfloat16*>(d_weight) + v0 * H;
+            p.ldc = H;
+            p.out_mode = OUT_BF16;
+            if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM))) return rc;
+            if ((rc = make_operand_tmap(&tb, hidden, H, T, H, true, kBlockN))) return rc;
+            if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream))) return rc;
+        }
+        {  // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
+            TcParams p{};
+            p.num_m_tiles = m_tiles_t;
+            p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
+            p.num_k_blocks = static_cast<int>(ceil_div(vc, kBlockK));
+            p.num_splits = p.num_n_tiles;
+            p.tiles_per_split = 1;
+            p.M = static_cast<int>(T);
+            p.N = static_cast<int>(H);
+            if (num_chunks == 1) {
+                p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16;
+            } else if (ci == 0) {
+                p.out = dh_acc, p.ldc = H, p.out_mode = OUT_F32;
+            } else if (ci < num_chunks - 1) {
+                p.out = dh_acc, p.ldc = H, p.out_mode = OUT_F32_ACC;
+            } else {
+                p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16_FROM_ACC;
+                p.accum = dh_acc, p.ld_accum = H;
+            }
+            if ((rc = make_operand_tmap(&ta, ds, t_pad, vc_cols, ldds, false, kBlockM))) return rc;
+            if ((rc = make_operand_tmap(&tb, w_chunk, H, vc, H, true, kBlockN))) return rc;
+            if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream))) return rc;
+        }
+    }
+    return VPG_OK;
+}
+
+int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                  int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
+                  int64_t ld_accum, void* stream_) {
+    VPG_CHECK_ARG(A && B && C, "null pointer argument");
+    VPG_CHECK_ARG(M > 0 && N > 0 && K > 0, "invalid GEMM shape");
+    VPG_CHECK_ARG(out_mode >= 0 && out_mode <= 3, "invalid out_mode %d", out_mode);
+    VPG_CHECK_ARG(ldc % 8 == 0, "ldc must be a multiple of 8");
+    VPG_CHECK_ARG(out_mode != OUT_BF16_FROM_ACC || (accum_f32 && ld_accum % 4 == 0), "accum buffer required");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    TcParams p{};
+    p.num_m_tiles = static_cast<int>(ceil_div(M, kBlockM));
+    p.num_n_tiles = static_cast<int>(ceil_div(N, kBlockN));
+    p.num_k_blocks = static_cast<int>(ceil_div(K, kBlockK));
+    p.num_splits = p.num_n_tiles;
+    p.tiles_per_split = 1;
+    p.M = static_cast<int>(M);
+    p.N = static_cast<int>(N);
+    p.out = C;
+    p.ldc = ldc;
+    p.out_mode = out_mode;
+    p.accum = accum_f32;
+    p.ld_accum = ld_accum;
+    CUtensorMap ta, tb;
+    int rc;
+    if ((rc = make_operand_tmap(&ta, A, M, K, lda, !a_kmajor, kBlockM))) return rc;
+    if ((rc = make_operand_tmap(&tb, B, N, K, ldb, !b_kmajor, kBlockN))) return rc;
+    if (a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, false, false>(ta, tb, p, stream);
+    if (a_kmajor && !b_kmajor) return launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream);
+    if (!a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, true, false>(ta, tb, p, stream);
+    return launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream);
+}
+
+}  // extern "C"

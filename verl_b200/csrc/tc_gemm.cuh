@@ -1,0 +1,513 @@
+// Persistent warp-specialised tcgen05 GEMM mainloop for sm_100a with pluggable epilogues.
+//
+//   D[128 x 256] (fp32, TMEM) = A[128 x K] * B[256 x K]^T,  bf16 operands staged by TMA into 128B-swizzled smem.
+//
+// Roles (384 threads, 1 CTA / SM):
+//   warp 0      TMA producer (lane 0 issues cp.async.bulk.tensor)
+//   warp 1      MMA issuer   (lane 0 issues tcgen05.mma / tcgen05.commit)
+//   warp 2      TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
+//   warp 3      idle
+//   warps 4-11  epilogue: warp w reads TMEM lanes 32*(w%4).., columns 128*((w-4)/4)..  via tcgen05.ld
+//
+// Pipelines: smem ring (full/empty mbarriers, kStages deep) between TMA and MMA; TMEM ring (tmem_full /
+// tmem_empty, 2 deep) between MMA and epilogue, so the epilogue of tile i overlaps the MMAs of tile i+1.
+//
+// Work is split into "units" = (m_tile, [n_begin, n_end) range of 256-wide n tiles).  The fused lm-head kernels
+// keep per-row softmax state in registers across the n tiles of a unit; the plain GEMM uses 1 tile per unit.
+#pragma once
+#include <cuda.h>
+
+#include "ptx.cuh"
+
+namespace vpg {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockN = 256;
+constexpr int kBlockK = 64;   // 64 bf16 = 128 B = one swizzle atom row
+constexpr int kUmmaK = 16;
+constexpr int kStages = 4;
+constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KB
+constexpr int kBBytes = kBlockN * kBlockK * 2;  // 32 KB
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kNumThreads = 384;
+constexpr int kEpiWarp0 = 4;
+constexpr int kNumEpiWarps = 8;
+constexpr int kTmemCols = 512;
+constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + 8192 /*barriers + scratch*/;
+
+enum : int { MODE_FWD = 0, MODE_DS = 1, MODE_GEMM = 2 };
+enum : int { OUT_BF16 = 0, OUT_F32 = 1, OUT_F32_ACC = 2, OUT_BF16_FROM_ACC = 3 };
+
+struct TcParams {
+    // tiling
+    int num_m_tiles;
+    int num_n_tiles;
+    int num_k_blocks;
+    int num_splits;       // units per m tile
+    int tiles_per_split;  // n tiles per unit
+    // logical bounds for masking
+    int M;  // valid rows
+    int N;  // valid columns
+    // ---- lm-head (MODE_FWD / MODE_DS)
+    float scale_log2;  // log2(e) / temperature
+    float inv_temp;
+    const long long* labels;  // [M]
+    long long label_offset;   // subtracted from labels to get a local column
+    float* partials;          // MODE_FWD: [4][num_splits][M]
+    const float* lse;         // MODE_DS: [M]
+    const float* eb;          // MODE_DS: [M]
+    const float* g_lp;        // MODE_DS: [M] or null
+    const float* g_ent;       // MODE_DS: [M] or null
+    __nv_bfloat16* ds;        // MODE_DS: [num_m_tiles*128][ldds]
+    long long ldds;
+    // ---- plain GEMM epilogue
+    void* out;
+    long long ldc;
+    int out_mode;
+    float* accum;  // OUT_F32_ACC: same as out; OUT_BF16_FROM_ACC: fp32 partial to add
+    long long ld_accum;
+};
+
+struct SmemLayout {
+    uint8_t* stages;
+    uint64_t* full;        // [kStages]
+    uint64_t* empty;       // [kStages]
+    uint64_t* tmem_full;   // [2]
+    uint64_t* tmem_empty;  // [2]
+    uint32_t* tmem_ptr;
+    float4* scratch;  // [2][128]
+};
+
+__device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw) {
+    SmemLayout L;
+    uintptr_t base = (reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023);
+    L.stages = reinterpret_cast<uint8_t*>(base);
+    uint8_t* aux = L.stages + kStages * kStageBytes;
+    L.full = reinterpret_cast<uint64_t*>(aux);
+    L.empty = L.full + kStages;
+    L.tmem_full = L.empty + kStages;
+    L.tmem_empty = L.tmem_full + 2;
+    L.tmem_ptr = reinterpret_cast<uint32_t*>(L.tmem_empty + 2);
+    L.scratch = reinterpret_cast<float4*>(aux + 256);
+    return L;
+}
+
+__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[32]) {
+    // tcgen05.wait::ld with the destination registers as in/out operands so that the compiler cannot hoist
+    // their consumers above the wait.
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]),
+                   "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]),
+                   "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]),
+                   "+r"(r[29]), "+r"(r[30]), "+r"(r[31])::"memory");
+}
+
+// ------------------------------------------------------------------------------------------------ epilogues
+struct FwdState {
+    float m2;
+    float s[4];
+    float b[4];
+    float tgt;
+};
+
+template <bool kMasked>
+__device__ __forceinline__ void fwd_chunk(FwdState& st, const uint32_t (&r)[32], float c, int lab_rel, int n_valid) {
+    // n_valid: number of valid columns in this chunk (only read when kMasked)
+    float x[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(r[j]);
+    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float v = x[j];
+        if (kMasked) v = (j < n_valid) ? v : -INFINITY;
+        mx[j & 3] = fmaxf(mx[j & 3], v);
+    }
+    float cmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+    float new_m = fmaxf(st.m2, cmax * c);
+    float f = ex2f(st.m2 - new_m);  // st.m2 = -inf on the first chunk -> 0
+    st.m2 = new_m;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        st.s[i] *= f;
+        st.b[i] *= f;
+    }
+    float neg_m = -new_m;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float e = ex2f(fmaf(x[j], c, neg_m));
+        if (kMasked) e = (j < n_valid) ? e : 0.f;
+        st.s[j & 3] += e;
+        st.b[j & 3] = fmaf(x[j], e, st.b[j & 3]);  // masked columns hold x = 0 (TMA zero fill), e = 0
+    }
+    if (static_cast<unsigned>(lab_rel) < 32u) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j == lab_rel) st.tgt = x[j];
+    }
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+struct DsRow {
+    float lse2;  // lse * log2(e)
+    float a;     // inv_temp * (g_lp - g_ent*eb)
+    float b;     // g_ent * inv_temp^2
+    float glp;   // g_lp * inv_temp
+};
+
+// dlogits chunk: d = -p*(a + b*x) (+ glp at the label column), zero for columns >= n_valid
+__device__ __forceinline__ void ds_chunk(const DsRow& rw, const uint32_t (&r)[32], float c, int lab_rel, int n_valid,
+                                         __nv_bfloat16* dst) {
+    float d[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float x = __uint_as_float(r[j]);
+        float e = ex2f(fmaf(x, c, -rw.lse2));
+        float q = fmaf(rw.b, x, rw.a);
+        d[j] = -e * q;
+    }
+    if (static_cast<unsigned>(lab_rel) < 32u) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j == lab_rel) d[j] += rw.glp;
+    }
+    if (n_valid < 32) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j >= n_valid) d[j] = 0.f;
+    }
+    uint4* o = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+    for (int q4 = 0; q4 < 4; ++q4) {
+        uint4 v;
+        v.x = pack_bf16x2(d[q4 * 8 + 0], d[q4 * 8 + 1]);
+        v.y = pack_bf16x2(d[q4 * 8 + 2], d[q4 * 8 + 3]);
+        v.z = pack_bf16x2(d[q4 * 8 + 4], d[q4 * 8 + 5]);
+        v.w = pack_bf16x2(d[q4 * 8 + 6], d[q4 * 8 + 7]);
+        o[q4] = v;
+    }
+}
+
+__device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r)[32], long long row, int col,
+                                           int n_valid) {
+    if (n_valid <= 0) return;
+    if (p.out_mode == OUT_BF16 || p.out_mode == OUT_BF16_FROM_ACC) {
+        float d[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) d[j] = __uint_as_float(r[j]);
+        if (p.out_mode == OUT_BF16_FROM_ACC) {
+            const float* acc = p.accum + row * p.ld_accum + col;
+            if (n_valid == 32) {
+#pragma unroll
+                for (int q4 = 0; q4 < 8; ++q4) {
+                    float4 a = reinterpret_cast<const float4*>(acc)[q4];
+                    d[q4 * 4 + 0] += a.x;
+                    d[q4 * 4 + 1] += a.y;
+                    d[q4 * 4 + 2] += a.z;
+                    d[q4 * 4 + 3] += a.w;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < n_valid) d[j] += acc[j];
+            }
+        }
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ldc + col;
+        if (n_valid == 32) {
+            uint4* o4 = reinterpret_cast<uint4*>(o);
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+                uint4 v;
+                v.x = pack_bf16x2(d[q4 * 8 + 0], d[q4 * 8 + 1]);
+                v.y = pack_bf16x2(d[q4 * 8 + 2], d[q4 * 8 + 3]);
+                v.z = pack_bf16x2(d[q4 * 8 + 4], d[q4 * 8 + 5]);
+                v.w = pack_bf16x2(d[q4 * 8 + 6], d[q4 * 8 + 7]);
+                o4[q4] = v;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < n_valid) o[j] = __float2bfloat16_rn(d[j]);
+        }
+    } else {
+        float* o = reinterpret_cast<float*>(p.out) + row * p.ldc + col;
+        const bool acc = (p.out_mode == OUT_F32_ACC);
+        if (n_valid == 32) {
+            float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4) {
+                float4 v = make_float4(__uint_as_float(r[q4 * 4 + 0]), __uint_as_float(r[q4 * 4 + 1]),
+                                       __uint_as_float(r[q4 * 4 + 2]), __uint_as_float(r[q4 * 4 + 3]));
+                if (acc) {
+                    float4 a = o4[q4];
+                    v.x += a.x;
+                    v.y += a.y;
+                    v.z += a.z;
+                    v.w += a.w;
+                }
+                o4[q4] = v;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < n_valid) o[j] = __uint_as_float(r[j]) + (acc ? o[j] : 0.f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ kernel
+// kAMn / kBMn: operand is MN-major in global memory (stored [K][MN]); otherwise K-major (stored [MN][K]).
+//   K-major operand : one TMA box {64 (k), rows}            -> rows x 128 B, SBO = 1024 B, K step = +32 B
+//   MN-major operand: rows/64 TMA boxes {64 (mn), 64 (k)}   -> blocks of 64 k-rows x 128 B (8 KB),
+//                     LBO = 8192 B (next 64 mn), SBO = 1024 B (next 8 k), K step (16 rows) = +2048 B
+template <int kMode, bool kAMn, bool kBMn>
+__global__ void __launch_bounds__(kNumThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    SmemLayout L = carve_smem(smem_raw);
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&L.full[i], 1);
+            mbar_init(&L.empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&L.tmem_full[i], 1);
+            mbar_init(&L.tmem_empty[i], kNumEpiWarps);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc<1>(L.tmem_ptr, kTmemCols);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *L.tmem_ptr;
+
+    const int num_units = p.num_m_tiles * p.num_splits;
+
+    if (warp == 0) {
+        // ===================================================================== TMA producer
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+            const int m_tile = u / p.num_splits;
+            const int sp = u - m_tile * p.num_splits;
+            const int nb = sp * p.tiles_per_split;
+            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
+            for (int n = nb; n < ne; ++n) {
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&L.empty[stage], phase ^ 1);
+                    if (lane == 0) {
+                        uint8_t* sa = L.stages + stage * kStageBytes;
+                        uint8_t* sb = sa + kABytes;
+                        mbar_arrive_expect_tx(&L.full[stage], kStageBytes);
+                        if (!kAMn) {
+                            tma_load_2d(&tmap_a, &L.full[stage], sa, kb * kBlockK, m_tile * kBlockM);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < kBlockM / 64; ++j)
+                                tma_load_2d(&tmap_a, &L.full[stage], sa + j * 8192, m_tile * kBlockM + j * 64,
+                                            kb * kBlockK);
+                        }
+                        if (!kBMn) {
+                            tma_load_2d(&tmap_b, &L.full[stage], sb, kb * kBlockK, n * kBlockN);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < kBlockN / 64; ++j)
+                                tma_load_2d(&tmap_b, &L.full[stage], sb + j * 8192, n * kBlockN + j * 64,
+                                            kb * kBlockK);
+                        }
+                    }
+                    __syncwarp();
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================================== MMA issuer
+        constexpr uint32_t idesc = make_idesc_bf16(kBlockM, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u);
+        int stage = 0;
+        uint32_t phase = 0;
+        uint32_t acc_iter = 0;
+        for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+            const int m_tile = u / p.num_splits;
+            const int sp = u - m_tile * p.num_splits;
+            const int nb = sp * p.tiles_per_split;
+            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
+            for (int n = nb; n < ne; ++n, ++acc_iter) {
+                const uint32_t buf = acc_iter & 1u;
+                const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+                mbar_wait(&L.tmem_empty[buf], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * kBlockN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&L.full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = smem_u32(L.stages + stage * kStageBytes);
+                        const uint32_t sb = sa + kABytes;
+                        const uint64_t adesc = kAMn ? make_smem_desc(sa, 8192, 1024) : make_smem_desc(sa, 16, 1024);
+                        const uint64_t bdesc = kBMn ? make_smem_desc(sb, 8192, 1024) : make_smem_desc(sb, 16, 1024);
+#pragma unroll
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            // advance the 14-bit start-address field (units of 16 B)
+                            const uint64_t a_adv = kAMn ? (k * 2048) >> 4 : (k * 32) >> 4;
+                            const uint64_t b_adv = kBMn ? (k * 2048) >> 4 : (k * 32) >> 4;
+                            umma_bf16<1>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(&L.empty[stage]);  // frees the smem slot once these MMAs retire
+                        if (kb == p.num_k_blocks - 1) umma_commit(&L.tmem_full[buf]);
+                    }
+                    __syncwarp();
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===================================================================== epilogue
+        const int ew = warp - kEpiWarp0;  // 0..7
+        const int quarter = warp & 3;     // TMEM lane quarter this warp may access
+        const int half = ew >> 2;         // column half: 0 -> [0,128), 1 -> [128,256)
+        const int row_in_tile = quarter * 32 + lane;
+        const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
+        const float c = p.scale_log2;
+        uint32_t acc_iter = 0;
+        uint32_t unit_iter = 0;
+        for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++unit_iter) {
+            const int m_tile = u / p.num_splits;
+            const int sp = u - m_tile * p.num_splits;
+            const int nb = sp * p.tiles_per_split;
+            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
+            const long long row = static_cast<long long>(m_tile) * kBlockM + row_in_tile;
+            const bool row_ok = row < p.M;
+
+            FwdState st;
+            DsRow rw;
+            int lab = -1;
+            if (kMode == MODE_FWD) {
+                st.m2 = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) st.s[i] = 0.f, st.b[i] = 0.f;
+                st.tgt = 0.f;
+            }
+            if (kMode == MODE_FWD || kMode == MODE_DS) {
+                if (row_ok) {
+                    long long l = p.labels[row] - p.label_offset;
+                    lab = (l >= 0 && l < p.N) ? static_cast<int>(l) : -1;
+                }
+            }
+            if (kMode == MODE_DS) {
+                rw.lse2 = 0.f, rw.a = 0.f, rw.b = 0.f, rw.glp = 0.f;
+                if (row_ok) {
+                    const float glp = p.g_lp ? p.g_lp[row] : 0.f;
+                    const float gent = p.g_ent ? p.g_ent[row] : 0.f;
+                    rw.lse2 = p.lse[row] * 1.4426950408889634f;
+                    rw.a = p.inv_temp * (glp - gent * p.eb[row]);
+                    rw.b = gent * p.inv_temp * p.inv_temp;
+                    rw.glp = glp * p.inv_temp;
+                }
+            }
+
+            for (int n = nb; n < ne; ++n, ++acc_iter) {
+                const uint32_t buf = acc_iter & 1u;
+                const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+                mbar_wait(&L.tmem_full[buf], acc_phase);
+                tc_fence_after();
+                const int col0 = n * kBlockN + half * 128;
+                const uint32_t taddr = tmem_base + t_lane + buf * kBlockN + half * 128;
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32(taddr, ra);
+#pragma unroll
+                for (int cc = 0; cc < 4; cc += 2) {
+                    tmem_ld_wait_dep(ra);
+                    tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
+                    {
+                        const int cb = col0 + cc * 32;
+                        const int n_valid = p.N - cb;
+                        if (kMode == MODE_FWD) {
+                            if (n_valid >= 32) fwd_chunk<false>(st, ra, c, lab - cb, 32);
+                            else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
+                        } else if (kMode == MODE_DS) {
+                            ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                        } else {
+                            if (row_ok) gemm_chunk(p, ra, row, cb, min(n_valid, 32));
+                        }
+                    }
+                    tmem_ld_wait_dep(rb);
+                    if (cc + 2 < 4) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
+                    {
+                        const int cb = col0 + (cc + 1) * 32;
+                        const int n_valid = p.N - cb;
+                        if (kMode == MODE_FWD) {
+                            if (n_valid >= 32) fwd_chunk<false>(st, rb, c, lab - cb, 32);
+                            else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
+                        } else if (kMode == MODE_DS) {
+                            ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                        } else {
+                            if (row_ok) gemm_chunk(p, rb, row, cb, min(n_valid, 32));
+                        }
+                    }
+                }
+                // all TMEM reads of this accumulator are complete (wait::ld above): hand it back to the MMA warp
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&L.tmem_empty[buf]);
+            }
+
+            if (kMode == MODE_FWD) {
+                // merge the two column halves of each row, then write this unit's partials
+                float s = (st.s[0] + st.s[1]) + (st.s[2] + st.s[3]);
+                float b = (st.b[0] + st.b[1]) + (st.b[2] + st.b[3]);
+                float4* scr = L.scratch + (unit_iter & 1u) * 128;
+                if (half == 1) scr[row_in_tile] = make_float4(st.m2, s, b, st.tgt);
+                named_bar_sync(1, kNumEpiWarps * 32);
+                if (half == 0) {
+                    const float4 o = scr[row_in_tile];
+                    const float m = fmaxf(st.m2, o.x);
+                    const float f0 = (st.m2 == -INFINITY) ? 0.f : ex2f(st.m2 - m);
+                    const float f1 = (o.x == -INFINITY) ? 0.f : ex2f(o.x - m);
+                    s = s * f0 + o.y * f1;
+                    b = b * f0 + o.z * f1;
+                    const float t = st.tgt + o.w;
+                    if (row_ok) {
+                        const long long plane = static_cast<long long>(p.num_splits) * p.M;
+                        float* dst = p.partials + static_cast<long long>(sp) * p.M + row;
+                        dst[0] = m;
+                        dst[plane] = s;
+                        dst[2 * plane] = b;
+                        dst[3 * plane] = t;
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem_base, kTmemCols);
+    }
+}
+
+}  // namespace vpg
