@@ -155,6 +155,8 @@ int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int
  *   compute_policy_loss (core_algos.py:722-794) + entropy bonus + KL loss + agg_loss as composed in
  *   verl/workers/actor/dp_actor.py:422-469:
  *     policy_loss = agg(pg) - entropy_coeff*agg(entropy) + kl_coef*agg(kl_penalty(lp, ref))   , times loss_scale
+ *   ratio_lo = (float)(1 - cliprange_low), ratio_hi = (float)(1 + cliprange_high): the clamp bounds, rounded to
+ *   fp32 by the caller exactly as torch.clamp rounds its Python-float bounds.
  *   entropy / ref_log_prob may be NULL (coeffs ignored).
  *   metrics[8] (f32, device): {policy_loss, pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower, entropy_agg, kl_agg,
  *                             mask_sum}
@@ -163,7 +165,7 @@ int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int
 size_t vpg_ppo_loss_workspace_bytes(int64_t B, int64_t L);
 int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
                  int mask_dtype, const float* entropy, const float* ref_log_prob, int64_t B, int64_t L,
-                 float clip_low, float clip_high, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
+                 float ratio_lo, float ratio_hi, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
                  int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy, void* workspace,
                  size_t workspace_bytes, void* stream);
 

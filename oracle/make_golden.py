@@ -1,0 +1,257 @@
+"""TEST INFRASTRUCTURE — generate tests/golden/*.npz by running the UNMODIFIED reference functions
+(/root/reference, loaded through oracle.ref_import) on seeded inputs.  Run in the build container:
+
+    python -m oracle.make_golden
+
+The fixtures travel to the GPU box; the reference does not.  Every array is fp32 / int64 / int32 (bf16 inputs are
+stored as their exact fp32 values).
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def _np(t):
+    if isinstance(t, torch.Tensor):
+        t = t.detach()
+        if t.dtype == torch.bfloat16:
+            t = t.float()
+        return t.cpu().numpy()
+    return np.asarray(t)
+
+
+def _bf16(shape, gen, lo=-0.5, hi=0.5):
+    return (torch.rand(*shape, generator=gen) * (hi - lo) + lo).bfloat16()
+
+
+def gen_lce(ref):
+    """FusedLinearForPPO fed fp32 copies of bf16 data (the recipe of tests/utils/test_linear_cross_entropy.py:82-96)."""
+    out = {}
+    cases = {"a": (37, 128, 1000, 1.5), "b": (130, 256, 777, 0.7), "c": (64, 128, 1536, 1.0)}
+    for name, (T, H, V, temp) in cases.items():
+        g = torch.Generator().manual_seed(233376 + len(name) + T)
+        hidden = _bf16((T, H), g)
+        weight = _bf16((V, H), g)
+        labels = torch.randint(0, V, (T,), generator=g)
+        g_lp = torch.rand(T, generator=g) * 2 - 1
+        g_ent = torch.rand(T, generator=g) - 0.5
+        h32 = hidden.float().requires_grad_(True)
+        w32 = weight.float().requires_grad_(True)
+        lp, ent = ref.fused_torch.FusedLinearForPPO()(h32, w32, labels, temperature=temp)
+        (lp * g_lp + ent * g_ent).sum().backward()
+        out.update({
+            f"{name}_shape": np.array([T, H, V]), f"{name}_temperature": np.array(temp),
+            f"{name}_hidden": _np(hidden), f"{name}_weight": _np(weight), f"{name}_labels": _np(labels),
+            f"{name}_g_lp": _np(g_lp), f"{name}_g_ent": _np(g_ent),
+            f"{name}_logprobs": _np(lp), f"{name}_entropy": _np(ent),
+            f"{name}_d_hidden": _np(h32.grad), f"{name}_d_weight": _np(w32.grad),
+        })
+    np.savez_compressed(os.path.join(OUT, "lce.npz"), **out)
+
+
+def gen_logits(ref):
+    g = torch.Generator().manual_seed(7)
+    F_ = ref.torch_functional
+    out = {}
+    logits = torch.randn(5, 7, 333, generator=g) * 3
+    labels = torch.randint(0, 333, (5, 7), generator=g)
+    out["f32_logits"], out["labels"] = _np(logits), _np(labels)
+    out["f32_logprobs_v2"] = _np(F_.logprobs_from_logits_v2(logits, labels))
+    out["f32_logprobs_naive"] = _np(F_.logprobs_from_logits_naive(logits, labels))
+    out["f32_entropy"] = _np(F_.entropy_from_logits(logits))
+    out["f32_entropy_chunked"] = _np(F_.entropy_from_logits_with_chunking(logits.reshape(-1, 333), chunk_size=8))
+    lb = logits.bfloat16()
+    out["bf16_logits"] = _np(lb)
+    out["bf16_logprobs_v2"] = _np(F_.logprobs_from_logits_v2(lb.reshape(-1, 333), labels.reshape(-1)))
+    out["bf16_entropy"] = _np(F_.entropy_from_logits(lb))
+    np.savez_compressed(os.path.join(OUT, "logits.npz"), **out)
+
+
+def gen_masked(ref):
+    g = torch.Generator().manual_seed(11)
+    F_ = ref.torch_functional
+    out = {}
+    v = torch.randn(6, 40, generator=g)
+    lens = torch.randint(3, 41, (6,), generator=g)
+    m = (torch.arange(40)[None, :] < lens[:, None]).long()
+    out["values"], out["mask"] = _np(v), _np(m)
+    out["masked_sum"] = _np(F_.masked_sum(v, m))
+    out["masked_mean"] = _np(F_.masked_mean(v, m))
+    out["masked_mean_axis"] = _np(F_.masked_mean(v, m, axis=-1))
+    out["masked_sum_axis"] = _np(F_.masked_sum(v, m, axis=-1))
+    out["masked_var"] = _np(F_.masked_var(v, m))
+    out["masked_var_biased"] = _np(F_.masked_var(v, m, unbiased=False))
+    out["masked_whiten"] = _np(F_.masked_whiten(v, m))
+    out["masked_whiten_noshift"] = _np(F_.masked_whiten(v, m, shift_mean=False))
+    # known answers of tests/utils/test_torch_functional.py:55-66
+    out["ka_values"] = np.array([1.0, 2.0, 3.0, 4.0], dtype=np.float32)
+    out["ka_mask"] = np.array([1, 0, 0, 1], dtype=np.int64)
+    out["ka_mean"] = _np(F_.masked_mean(torch.tensor([1.0, 2.0, 3.0, 4.0]), torch.tensor([1, 0, 0, 1])))
+    out["ka_nan_outside"] = _np(F_.masked_mean(torch.tensor([1.0, float("nan"), 3.0, 4.0]),
+                                               torch.tensor([True, False, False, True])))
+    np.savez_compressed(os.path.join(OUT, "masked.npz"), **out)
+
+
+def _response_mask(B, L, g, min_frac=0.25):
+    lens = torch.randint(int(L * min_frac), L + 1, (B,), generator=g)
+    return (torch.arange(L)[None, :] < lens[:, None]).long(), lens
+
+
+def gen_grpo(ref):
+    g = torch.Generator().manual_seed(13)
+    ca = ref.core_algos
+    out = {}
+    B, L = 14, 24
+    mask, lens = _response_mask(B, L, g)
+    rewards = torch.zeros(B, L)
+    rewards[torch.arange(B), lens - 1] = torch.rand(B, generator=g)  # one scalar at the last valid token
+    uids = np.array([f"uid-{i // 3:02d}-é" for i in range(B)], dtype=object)  # 4 groups of 3 + a group of 2
+    uids[-1] = "solo"                                                          # + one singleton
+    perm = torch.randperm(B, generator=g).numpy()
+    uids = uids[perm]
+    # two rows of one group get identical scores (std 0 path needs eps)
+    out["rewards"], out["mask"], out["uids"] = _np(rewards), _np(mask), np.array([str(u) for u in uids])
+    for norm in (True, False):
+        adv, ret = ca.compute_grpo_outcome_advantage(rewards.clone(), mask, uids, norm_adv_by_std_in_grpo=norm)
+        out[f"adv_norm{int(norm)}"] = _np(adv)
+    dense = torch.randn(B, L, generator=g) * mask
+    out["dense_rewards"] = _np(dense)
+    out["dense_adv"] = _np(ca.compute_grpo_outcome_advantage(dense.clone(), mask, uids)[0])
+    eq = rewards.clone()
+    eq[:] = 0
+    eq[:, 0] = 0.5  # every score equal -> advantages exactly 0 for groups, (0.5-0)/(1+eps) for the singleton
+    out["equal_adv"] = _np(ca.compute_grpo_outcome_advantage(eq.clone(), mask, uids)[0])
+    np.savez_compressed(os.path.join(OUT, "grpo.npz"), **out)
+
+
+def gen_gae(ref):
+    g = torch.Generator().manual_seed(17)
+    ca = ref.core_algos
+    out = {}
+    B, L = 5, 67
+    # multi-turn style mask: response tokens interleaved with observation (0) spans, trailing padding
+    mask = (torch.rand(B, L, generator=g) > 0.3).long()
+    lens = torch.randint(20, L + 1, (B,), generator=g)
+    mask = mask * (torch.arange(L)[None, :] < lens[:, None]).long()
+    rewards = torch.randn(B, L, generator=g) * 0.1
+    values = torch.randn(B, L, generator=g)
+    out["rewards"], out["values"], out["mask"] = _np(rewards), _np(values), _np(mask)
+    for i, (gamma, lam) in enumerate([(1.0, 1.0), (0.97, 0.9)]):
+        adv, ret = ca.compute_gae_advantage_return(rewards, values, mask, gamma, lam)
+        out[f"gamma{i}"], out[f"lam{i}"] = np.array(gamma), np.array(lam)
+        out[f"adv{i}"], out[f"ret{i}"] = _np(adv), _np(ret)
+    np.savez_compressed(os.path.join(OUT, "gae.npz"), **out)
+
+
+def gen_loss(ref):
+    g = torch.Generator().manual_seed(19)
+    ca = ref.core_algos
+    out = {}
+    B, L = 8, 64
+    mask, _ = _response_mask(B, L, g)
+    old = -torch.rand(B, L, generator=g) * 3
+    lp = old + 0.3 * torch.randn(B, L, generator=g)  # wide enough to hit clip and dual-clip regions
+    lp[0, 0] = old[0, 0] + 25.0                      # beyond the +-20 clamp
+    lp[0, 1] = old[0, 1] - 25.0
+    ref_lp = old + 0.2 * torch.randn(B, L, generator=g)
+    ref_lp[1, 0] = lp[1, 0] + 3.0                    # low_var_kl above its clamp of 10
+    adv = torch.randn(B, L, generator=g)
+    ent = torch.rand(B, L, generator=g) * 2
+    out.update(mask=_np(mask), old=_np(old), lp=_np(lp), ref=_np(ref_lp), adv=_np(adv), ent=_np(ent))
+    cfgs = {
+        "vanilla": dict(lo=0.2, hi=0.2, c=3.0, ent_coeff=0.0, kl_coef=0.0, kl="low_var_kl", scale=1.0),
+        "dapo": dict(lo=0.2, hi=0.28, c=10.0, ent_coeff=1e-3, kl_coef=0.0, kl="low_var_kl", scale=0.25),
+        "grpo_kl": dict(lo=0.2, hi=0.2, c=3.0, ent_coeff=0.0, kl_coef=0.01, kl="low_var_kl", scale=0.5),
+        "all": dict(lo=0.1, hi=0.3, c=2.0, ent_coeff=0.01, kl_coef=0.05, kl="mse", scale=1.0),
+    }
+    modes = ["token-mean", "seq-mean-token-sum", "seq-mean-token-mean", "seq-mean-token-sum-norm"]
+    for cname, c in cfgs.items():
+        for mode in modes:
+            lpg = lp.clone().requires_grad_(True)
+            eg = ent.clone().requires_grad_(True)
+            pg_loss, clipfrac, ppo_kl, clipfrac_lower = ca.compute_policy_loss(
+                old_log_prob=old, log_prob=lpg, advantages=adv, response_mask=mask, cliprange=c["lo"],
+                cliprange_low=c["lo"], cliprange_high=c["hi"], clip_ratio_c=c["c"], loss_agg_mode=mode)
+            # composition of verl/workers/actor/dp_actor.py:445-469
+            policy_loss = pg_loss
+            ent_loss = torch.zeros(())
+            kl_loss = torch.zeros(())
+            if c["ent_coeff"] != 0:
+                ent_loss = ca.agg_loss(loss_mat=eg, loss_mask=mask, loss_agg_mode=mode)
+                policy_loss = pg_loss - ent_loss * c["ent_coeff"]
+            if c["kl_coef"] != 0:
+                kld = ca.kl_penalty(logprob=lpg, ref_logprob=ref_lp, kl_penalty=c["kl"])
+                kl_loss = ca.agg_loss(loss_mat=kld, loss_mask=mask, loss_agg_mode=mode)
+                policy_loss = policy_loss + kl_loss * c["kl_coef"]
+            loss = policy_loss * c["scale"]
+            loss.backward()
+            key = f"{cname}|{mode}"
+            out[key + "|scalars"] = np.array([_np(loss), _np(pg_loss), _np(clipfrac), _np(ppo_kl), _np(clipfrac_lower),
+                                              _np(ent_loss), _np(kl_loss)], dtype=np.float32)
+            out[key + "|d_lp"] = _np(lpg.grad)
+            out[key + "|d_ent"] = _np(eg.grad) if eg.grad is not None else np.zeros((B, L), np.float32)
+        out[cname + "|cfg"] = np.array([c["lo"], c["hi"], c["c"], c["ent_coeff"], c["kl_coef"], c["scale"]])
+        out[cname + "|kl"] = np.array(c["kl"])
+    for kind in ["kl", "abs", "mse", "low_var_kl"]:
+        out["kl_penalty|" + kind] = _np(ca.kl_penalty(lp, ref_lp, kind))
+    for mode in modes:
+        out["agg|" + mode] = _np(ca.agg_loss(ent, mask, mode))
+    np.savez_compressed(os.path.join(OUT, "loss.npz"), **out)
+
+
+def gen_rmpad(ref):
+    import flash_attn.bert_padding as bp  # third-party pure-torch file, v2.8.3 in this image
+
+    out = {}
+    torch.manual_seed(23)
+    B, S = 8, 64
+    if ref.model is not None:
+        mask = ref.model.create_random_mask(torch.zeros(B, S, dtype=torch.long), max_ratio_of_valid_token=0.8,
+                                            max_ratio_of_left_padding=0.1, min_ratio_of_valid_token=0.5)
+    else:
+        mask = (torch.rand(B, S) > 0.3).long()
+    ids = torch.randint(0, 50000, (B, S))
+    x_rmpad, indices, cu, max_s, seqused = bp.unpad_input(ids.unsqueeze(-1), mask)
+    idx2, cu2, max2 = ref.torch_functional.get_unpad_data(mask)
+    assert torch.equal(indices, idx2) and torch.equal(cu, cu2) and max_s == max2
+    vals = torch.randn(indices.numel(), 1)
+    padded = bp.pad_input(vals, indices, B, S)
+    hs = torch.randn(B, S, 6)
+    hs_rmpad = bp.index_first_axis(hs.reshape(B * S, 6), indices)
+    out.update(mask=_np(mask), ids=_np(ids), ids_rmpad=_np(x_rmpad.squeeze(-1)), indices=_np(indices),
+               cu_seqlens=_np(cu), max_seqlen=np.array(max_s), seqused=_np(seqused), vals=_np(vals),
+               padded=_np(padded), hs=_np(hs), hs_rmpad=_np(hs_rmpad))
+    # edge cases: an empty row, a full row, all-empty
+    edge = torch.zeros(4, 9, dtype=torch.long)
+    edge[1] = 1
+    edge[2, 3:7] = 1
+    _, e_idx, e_cu, e_max, e_used = bp.unpad_input(torch.zeros(4, 9, 1), edge)
+    out.update(edge_mask=_np(edge), edge_indices=_np(e_idx), edge_cu=_np(e_cu), edge_max=np.array(e_max))
+    np.savez_compressed(os.path.join(OUT, "rmpad.npz"), **out)
+
+
+def main():
+    from oracle import ref_import
+
+    if not ref_import.available():
+        sys.exit("reference tree not available; golden vectors can only be regenerated in the build container")
+    ref = ref_import.load()
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(min(8, os.cpu_count() or 1))
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_rmpad):
+        fn(ref)
+        print("wrote", fn.__name__)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,314 @@
+"""TEST INFRASTRUCTURE ONLY — CPU restatement (PyTorch-CPU / numpy) of the reference algorithms on the hot path.
+
+Each function cites the reference lines it restates (paths relative to /root/reference).  The restatement is
+validated against the unmodified reference (oracle/make_golden.py -> tests/golden/*.npz, tests/test_oracle_cpu.py).
+Parity status: pinned (see oracle/__init__.py).  Never imported by verl_b200.
+"""
+
+from __future__ import annotations
+
+from collections import OrderedDict
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+# ------------------------------------------------------------------------------------------------ lm-head
+def lce_forward(hidden, weight, labels, temperature=1.0, chunk=512, compute_dtype=torch.float32):
+    """Per-token log-prob and entropy of softmax(hidden @ weight.T / temperature).
+
+    Restates verl/utils/experimental/torch_functional.py:20-37 (chunked, :109-117) and the fp32 recipe of
+    tests/utils/test_linear_cross_entropy.py:48-61: logits in fp32, log_softmax gather, entropy = lse - sum p*logit.
+    compute_dtype=float32 upcasts bf16 inputs first (the kernel tests' reference); bf16 keeps the matmul in bf16 like
+    the reference's production torch backend.
+    """
+    T = hidden.shape[0]
+    w = weight.to(compute_dtype)
+    lp = torch.empty(T, dtype=torch.float32)
+    ent = torch.empty(T, dtype=torch.float32)
+    for s in range(0, T, chunk):
+        e = min(s + chunk, T)
+        logits = (hidden[s:e].to(compute_dtype) @ w.t()) / temperature
+        logits = logits.float()
+        lse = torch.logsumexp(logits, dim=-1)
+        p = torch.softmax(logits, dim=-1)
+        lp[s:e] = logits.gather(-1, labels[s:e, None]).squeeze(-1) - lse
+        ent[s:e] = lse - (p * logits).sum(-1)
+    return lp, ent
+
+
+def lce_backward(hidden, weight, labels, g_lp, g_ent, temperature=1.0, chunk=512):
+    """d_hidden, d_weight (fp32) of lce_forward for upstream grads g_lp, g_ent (either may be None).
+
+    Restates verl/utils/experimental/torch_functional.py:40-72:
+      dlogits = g_lp*(onehot - p) + p*(log p + entropy)*(-g_ent), / temperature; dH = dlogits@W; dW = dlogits.T@H
+    (same expression as the Triton kernel's, verl/utils/kernel/kernels.py:1327-1334).
+    """
+    T = hidden.shape[0]
+    h32, w32 = hidden.float(), weight.float()
+    dh = torch.zeros_like(h32)
+    dw = torch.zeros_like(w32)
+    for s in range(0, T, chunk):
+        e = min(s + chunk, T)
+        logits = (h32[s:e] @ w32.t()) / temperature
+        p = torch.softmax(logits, dim=-1)
+        d = torch.zeros_like(logits)
+        if g_lp is not None:
+            onehot = torch.zeros_like(logits).scatter_(-1, labels[s:e, None], 1.0)
+            d += g_lp[s:e, None].float() * (onehot - p)
+        if g_ent is not None:
+            logp = torch.log_softmax(logits, dim=-1)
+            entropy = torch.logsumexp(logits, dim=-1) - (p * logits).sum(-1)
+            d += p * (logp + entropy[:, None]) * (-g_ent[s:e, None].float())
+        d = d / temperature
+        dh[s:e] = d @ w32
+        dw += d.t() @ h32[s:e]
+    return dh, dw
+
+
+def lce_forward_vocab_parallel(hidden, weight_shards, labels, temperature=1.0):
+    """Vocab-parallel combine, as verl/utils/kernel/kernels.py:609-661 does with 3 all-reduces: every shard r gives
+    {m_r, s_r = sum exp(l - m_r), b_r = sum l*exp(l - m_r), t_r = l[label] if the label is local}; merge with the
+    log-sum-exp rule.  Equal shards, label offset rank*V_local (kernels.py:232)."""
+    ms, ss, bs, ts = [], [], [], []
+    for r, w in enumerate(weight_shards):
+        logits = (hidden.float() @ w.float().t()) / temperature
+        m = logits.max(-1).values
+        ex = torch.exp(logits - m[:, None])
+        ms.append(m), ss.append(ex.sum(-1)), bs.append((logits * ex).sum(-1))
+        local = labels - r * w.shape[0]
+        ok = (local >= 0) & (local < w.shape[0])
+        t = torch.zeros_like(m)
+        t[ok] = logits[ok, local[ok]]
+        ts.append(t)
+    M = torch.stack(ms).max(0).values
+    s = sum(si * torch.exp(mi - M) for si, mi in zip(ss, ms))
+    b = sum(bi * torch.exp(mi - M) for bi, mi in zip(bs, ms))
+    lse = M + torch.log(s)
+    return sum(ts) - lse, lse - b / s
+
+
+def logprobs_from_logits(logits, labels):
+    """verl/utils/torch_functional.py:116-133 (fp32 branch: gather - logsumexp; bf16 branch: log_softmax then gather).
+    Output in logits' dtype."""
+    if logits.dtype in (torch.float32, torch.float64):
+        picked = torch.gather(logits, -1, labels.unsqueeze(-1)).squeeze(-1)
+        return picked - torch.logsumexp(logits, dim=-1)
+    return F.log_softmax(logits, dim=-1).gather(-1, labels.unsqueeze(-1)).squeeze(-1)
+
+
+def entropy_from_logits(logits):
+    """verl/utils/torch_functional.py:145-149"""
+    p = torch.softmax(logits, dim=-1)
+    return torch.logsumexp(logits, dim=-1) - (p * logits).sum(-1)
+
+
+# ------------------------------------------------------------------------------------------------ masked ops
+def masked_sum(values, mask, axis=None):
+    """verl/utils/torch_functional.py:163-168"""
+    kept = torch.where(mask.bool(), values, torch.zeros((), dtype=values.dtype))
+    return (kept * mask).sum(axis)
+
+
+def masked_mean(values, mask, axis=None):
+    """verl/utils/torch_functional.py:171-185"""
+    return masked_sum(values, mask, axis) / (mask.sum(axis) + 1e-8)
+
+
+def masked_var(values, mask, unbiased=True):
+    """verl/utils/torch_functional.py:188-203"""
+    mu = masked_mean(values, mask)
+    var = masked_mean((values - mu) ** 2, mask)
+    if unbiased:
+        n = mask.sum()
+        if n == 0:
+            raise ValueError("At least one element in the mask has to be 1.")
+        if n == 1:
+            raise ValueError("The sum of the mask is one, which can cause a division by zero.")
+        var = var * (n / (n - 1))
+    return var
+
+
+def masked_whiten(values, mask, shift_mean=True):
+    """verl/utils/torch_functional.py:206-223"""
+    mu, var = masked_mean(values, mask), masked_var(values, mask)
+    out = (values - mu) * torch.rsqrt(var + 1e-8)
+    return out if shift_mean else out + mu
+
+
+# ------------------------------------------------------------------------------------------------ rmpad
+def unpad_indices(attention_mask):
+    """flash_attn.bert_padding.unpad_input's index part (third-party, v2.8.3; call sites
+    verl/workers/actor/dp_actor.py:110-125) == verl/utils/torch_functional.py:629-638 (get_unpad_data):
+    -> indices int64 [nnz] ascending, seqlens int32 [B], cu_seqlens int32 [B+1], max_seqlen int."""
+    m = np.asarray(attention_mask.cpu())
+    seqlens = m.sum(axis=-1).astype(np.int32)
+    indices = np.flatnonzero(m.reshape(-1)).astype(np.int64)
+    cu = np.zeros(m.shape[0] + 1, dtype=np.int32)
+    cu[1:] = np.cumsum(seqlens, dtype=np.int32)
+    return (torch.from_numpy(indices), torch.from_numpy(seqlens), torch.from_numpy(cu),
+            int(seqlens.max()) if seqlens.size else 0)
+
+
+def gather_rows(x, indices):
+    """index_first_axis (flash_attn.bert_padding)"""
+    return x[indices]
+
+
+def pad_rows(x, indices, n_rows):
+    """pad_input / index_put_first_axis (flash_attn.bert_padding): zeros everywhere else"""
+    out = torch.zeros((n_rows, *x.shape[1:]), dtype=x.dtype)
+    out[indices] = x
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ advantages
+def group_ids(index):
+    """First-seen integer id per uid — the grouping verl/trainer/ppo/core_algos.py:286-291 performs with a dict."""
+    table = OrderedDict()
+    out = np.empty(len(index), dtype=np.int32)
+    for i, k in enumerate(index):
+        k = k.item() if isinstance(k, np.generic) else k
+        out[i] = table.setdefault(k, len(table))
+    return out, len(table)
+
+
+def grpo_outcome_advantage(token_level_rewards, response_mask, index, epsilon=1e-6, norm_adv_by_std_in_grpo=True):
+    """verl/trainer/ppo/core_algos.py:245-308: score = row sum; group mean and UNBIASED std (torch.std); a group
+    of one uses mean 0 / std 1; adv = (score-mean)/(std+eps) or score-mean; broadcast * mask."""
+    scores = token_level_rewards.sum(dim=-1)
+    gid, n = group_ids(index)
+    out = scores.clone()
+    for g in range(n):
+        rows = np.flatnonzero(gid == g)
+        vals = scores[rows]
+        if len(rows) == 1:
+            mean, std = torch.tensor(0.0), torch.tensor(1.0)
+        else:
+            mean, std = vals.mean(), vals.std()  # unbiased
+        out[rows] = (vals - mean) / (std + epsilon) if norm_adv_by_std_in_grpo else vals - mean
+    return out.unsqueeze(-1) * response_mask
+
+
+def gae_advantage_return(token_level_rewards, values, response_mask, gamma, lam):
+    """verl/trainer/ppo/core_algos.py:193-241: reverse recurrence with masked carry-through, returns = adv + values,
+    then masked_whiten(adv)."""
+    B, L = token_level_rewards.shape
+    next_v = torch.zeros(B)
+    carry = torch.zeros(B)
+    adv = torch.empty(B, L)
+    for t in range(L - 1, -1, -1):
+        m = response_mask[:, t]
+        delta = token_level_rewards[:, t] + gamma * next_v - values[:, t]
+        cand = delta + gamma * lam * carry
+        next_v = values[:, t] * m + (1 - m) * next_v
+        carry = cand * m + (1 - m) * carry
+        adv[:, t] = carry
+    returns = adv + values
+    return masked_whiten(adv, response_mask), returns
+
+
+# ------------------------------------------------------------------------------------------------ losses
+def agg_loss(loss_mat, loss_mask, loss_agg_mode):
+    """verl/trainer/ppo/core_algos.py:686-719"""
+    if loss_agg_mode == "token-mean":
+        return masked_mean(loss_mat, loss_mask)
+    per_seq = (loss_mat * loss_mask).sum(-1)
+    if loss_agg_mode == "seq-mean-token-sum":
+        return per_seq.mean()
+    if loss_agg_mode == "seq-mean-token-mean":
+        return (per_seq / loss_mask.sum(-1)).mean()
+    if loss_agg_mode == "seq-mean-token-sum-norm":
+        return per_seq.sum() / loss_mask.shape[-1]
+    raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+
+
+def policy_loss(old_log_prob, log_prob, advantages, response_mask, cliprange=None, cliprange_low=None,
+                cliprange_high=None, clip_ratio_c=3.0, loss_agg_mode="token-mean"):
+    """verl/trainer/ppo/core_algos.py:722-794 -> (pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower)"""
+    assert clip_ratio_c > 1.0
+    lo = cliprange if cliprange_low is None else cliprange_low
+    hi = cliprange if cliprange_high is None else cliprange_high
+    log_ratio = torch.clamp(log_prob - old_log_prob, min=-20.0, max=20.0)
+    ratio = torch.exp(log_ratio)
+    ppo_kl = masked_mean(-log_ratio, response_mask)
+    unclipped = -advantages * ratio
+    clipped = -advantages * torch.clamp(ratio, 1 - lo, 1 + hi)
+    worst = torch.maximum(unclipped, clipped)
+    pg_clipfrac = masked_mean(torch.gt(clipped, unclipped).float(), response_mask)
+    dual = -advantages * clip_ratio_c
+    capped = torch.min(dual, worst)
+    pg_clipfrac_lower = masked_mean(torch.gt(worst, dual) * (advantages < 0).float(), response_mask)
+    per_token = torch.where(advantages < 0, capped, worst)
+    return agg_loss(per_token, response_mask, loss_agg_mode), pg_clipfrac, ppo_kl, pg_clipfrac_lower
+
+
+def kl_penalty(logprob, ref_logprob, kind):
+    """verl/trainer/ppo/core_algos.py:1034-1069"""
+    if kind in ("kl", "k1"):
+        return logprob - ref_logprob
+    if kind == "abs":
+        return (logprob - ref_logprob).abs()
+    if kind in ("mse", "k2"):
+        return 0.5 * (logprob - ref_logprob).square()
+    if kind in ("low_var_kl", "k3"):
+        k = torch.clamp(ref_logprob - logprob, min=-20, max=20)
+        return torch.clamp(torch.exp(k) - k - 1, min=-10, max=10)
+    raise NotImplementedError
+
+
+def actor_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low, cliprange_high, clip_ratio_c=3.0,
+               loss_agg_mode="token-mean", entropy=None, entropy_coeff=0.0, ref_log_prob=None, kl_loss_coef=0.0,
+               kl_loss_type="low_var_kl", loss_scale=1.0):
+    """Loss composition of verl/workers/actor/dp_actor.py:422-469 -> (loss, dict of the logged scalars)."""
+    pg, clipfrac, ppo_kl, clipfrac_lower = policy_loss(
+        old_log_prob, log_prob, advantages, response_mask, cliprange_low=cliprange_low, cliprange_high=cliprange_high,
+        clip_ratio_c=clip_ratio_c, loss_agg_mode=loss_agg_mode)
+    total = pg
+    ent_loss = torch.zeros(())
+    kl_loss = torch.zeros(())
+    if entropy is not None and entropy_coeff != 0:
+        ent_loss = agg_loss(entropy, response_mask, loss_agg_mode)
+        total = pg - ent_loss * entropy_coeff
+    if ref_log_prob is not None:
+        kl_loss = agg_loss(kl_penalty(log_prob, ref_log_prob, kl_loss_type), response_mask, loss_agg_mode)
+        total = total + kl_loss * kl_loss_coef
+    return total * loss_scale, dict(pg_loss=pg, pg_clipfrac=clipfrac, ppo_kl=ppo_kl, pg_clipfrac_lower=clipfrac_lower,
+                                    entropy_loss=ent_loss, kl_loss=kl_loss)
+
+
+# ------------------------------------------------------------------------------------------------ partial format
+def lce_partials(hidden, weight, labels, temperature, label_offset=0, num_splits=1):
+    """CPU restatement of the PARTIAL format the CUDA forward emits (include/vpg_b200.h, vpg_lce_fwd_partials):
+    [4][S][T] = {m (log2 domain), s, b (raw-dot weighted), t}.  Used to test the vocab-parallel exchange on CPU
+    (gloo); the statistics themselves are the reference's (verl/utils/kernel/kernels.py:226-254)."""
+    T, V = hidden.shape[0], weight.shape[0]
+    x = hidden.float() @ weight.float().t()
+    c = 1.4426950408889634 / temperature
+    n_tiles = -(-V // 256)
+    tps = -(-n_tiles // num_splits)
+    out = torch.zeros(4, num_splits, T)
+    out[0].fill_(float("-inf"))
+    local = labels - label_offset
+    for sp in range(num_splits):
+        lo, hi = sp * tps * 256, min((sp + 1) * tps * 256, V)
+        if lo >= hi:
+            continue
+        xs = x[:, lo:hi]
+        m = (xs * c).max(-1).values
+        e = torch.exp2(xs * c - m[:, None])
+        out[0, sp], out[1, sp], out[2, sp] = m, e.sum(-1), (xs * e).sum(-1)
+        ok = (local >= lo) & (local < hi)
+        out[3, sp][ok] = x[ok, local[ok]]
+    return out
+
+
+def lce_finalize(partials, temperature):
+    """CPU restatement of vpg_lce_finalize: merge [4][P][T] partials -> (logprobs, entropy)."""
+    m, s, b, t = partials[0], partials[1], partials[2], partials[3]
+    M = m.max(0).values
+    f = torch.where(torch.isinf(m), torch.zeros_like(m), torch.exp2(m - M[None]))
+    S, Bv = (s * f).sum(0), (b * f).sum(0)
+    lse = (M + torch.log2(S)) * 0.6931471805599453
+    return t.sum(0) / temperature - lse, lse - (Bv / S) / temperature

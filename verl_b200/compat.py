@@ -1,0 +1,88 @@
+"""Install verl_b200 behind the reference's own import paths.
+
+``install()`` makes the hot-path names of an (importable or absent) ``verl`` resolve to this package:
+
+  verl.utils.kernel.linear_cross_entropy.linear_cross_entropy   (used by verl/models/transformers/dense_common.py:
+      179-185, qwen2_vl.py:544, qwen2_5_vl.py:273-279, verl/models/mcore/model_forward_fused.py:302-309)
+  verl.utils.kernel.kernels.{set_backward_method, BackwardEnum, EntropyReductionEnum, ...}
+  verl.utils.torch_functional.{logprobs_from_logits, entropy_from_logits, masked_mean, ...}
+  verl.trainer.ppo.core_algos.{compute_policy_loss, agg_loss, kl_penalty, compute_grpo_outcome_advantage,
+      compute_gae_advantage_return} (+ registry entries "gae" and "grpo")
+  flash_attn.bert_padding.{unpad_input, pad_input, index_first_axis}   (only with patch_flash_attn=True)
+
+If the real ``verl`` package is importable its modules are patched attribute by attribute (everything outside the
+hot path keeps working); otherwise light namespace modules are registered so that
+``from verl.utils.kernel.linear_cross_entropy import linear_cross_entropy`` works stand-alone.
+"""
+
+from __future__ import annotations
+
+import importlib
+import sys
+import types
+
+from . import bert_padding as _bp
+from .trainer.ppo import core_algos as _ca
+from .utils import torch_functional as _tf
+from .utils.kernel import kernels as _k
+from .utils.kernel import linear_cross_entropy as _lce
+
+_TF_NAMES = [
+    "logprobs_from_logits", "logprobs_from_logits_v2", "logprobs_from_logits_naive", "logprobs_from_logits_flash_attn",
+    "entropy_from_logits", "entropy_from_logits_with_chunking", "masked_sum", "masked_mean", "masked_var",
+    "masked_whiten", "get_unpad_data", "log_probs_from_logits_response_rmpad", "log_probs_from_logits_all_rmpad",
+    "gather_from_labels",
+]
+_CA_NAMES = ["compute_policy_loss", "agg_loss", "kl_penalty", "compute_grpo_outcome_advantage",
+             "compute_gae_advantage_return", "compute_rewards"]
+
+
+def _try_import(name):
+    try:
+        return importlib.import_module(name)
+    except Exception:
+        return None
+
+
+def _namespace(name):
+    mod = sys.modules.get(name)
+    if mod is None:
+        mod = types.ModuleType(name)
+        mod.__path__ = []  # namespace-like
+        sys.modules[name] = mod
+        parent, _, leaf = name.rpartition(".")
+        if parent:
+            setattr(_namespace(parent), leaf, mod)
+    return mod
+
+
+def install(patch_flash_attn: bool = False) -> dict:
+    """Route the reference's hot-path imports to verl_b200.  Returns {module name: 'patched' | 'shadowed'}."""
+    report = {}
+    targets = {
+        "verl.utils.kernel.linear_cross_entropy": (_lce, ["LinearCrossEntropy", "linear_cross_entropy"]),
+        "verl.utils.kernel.kernels": (_k, [n for n in dir(_k) if not n.startswith("__")]),
+        "verl.utils.torch_functional": (_tf, _TF_NAMES),
+        "verl.trainer.ppo.core_algos": (_ca, _CA_NAMES),
+    }
+    for name, (src, names) in targets.items():
+        real = _try_import(name)
+        if real is not None and real is not src:
+            for n in names:
+                setattr(real, n, getattr(src, n))
+            if name.endswith("core_algos"):
+                for key in ("gae", "grpo"):
+                    real.ADV_ESTIMATOR_REGISTRY[key] = _ca.ADV_ESTIMATOR_REGISTRY[key]
+            report[name] = "patched"
+        else:
+            parent, _, leaf = name.rpartition(".")
+            sys.modules[name] = src
+            setattr(_namespace(parent), leaf, src)
+            report[name] = "shadowed"
+    if patch_flash_attn:
+        fa = _try_import("flash_attn.bert_padding")
+        if fa is not None:
+            for n in ("unpad_input", "pad_input", "index_first_axis", "index_put_first_axis"):
+                setattr(fa, n, getattr(_bp, n))
+            report["flash_attn.bert_padding"] = "patched"
+    return report

@@ -1,0 +1,298 @@
+// Remove-padding (rmpad) index plumbing: mask -> (indices, seqlens, cu_seqlens, max_seqlen), row gather / scatter.
+// Reference: flash_attn.bert_padding (unpad_input / index_first_axis / pad_input; third-party file, called from
+// verl/workers/actor/dp_actor.py:110-125,221-232) and verl/utils/torch_functional.py:629-638 (get_unpad_data).
+//   indices  = nonzero(mask.flatten())            (int64, ascending)
+//   seqlens  = mask.sum(-1, dtype=int32)          (sum of mask VALUES, as the reference computes it)
+//   cu_seqlens = pad(cumsum(seqlens, int32), (1,0)),  max_seqlen = seqlens.max()
+// Integer outputs are bit-exact.  Stream compaction: tile counts -> single-block scan -> ordered tile write with
+// ballot/popc ranks, so the index list is produced in ascending order without a sort.
+#include <cuda_runtime.h>
+
+#include "common.h"
+#include "reduce.cuh"
+
+namespace vpg {
+
+constexpr int kTileThreads = 256;
+constexpr int kItems = 16;                          // mask elements per thread
+constexpr int kTile = kTileThreads * kItems;        // 4096 elements per block
+
+template <typename MT>
+__device__ __forceinline__ bool mask_nonzero(MT m) {
+    return m != MT(0);
+}
+
+// nonzero count of every tile
+template <typename MT>
+__global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, int* __restrict__ tile_counts) {
+    __shared__ int red[32];
+    const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        // warp-contiguous layout: element = tile0 + j*256 + tid  (coalesced)
+        const long long i = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
+        c += (i < n && mask_nonzero(mask[i])) ? 1 : 0;
+    }
+    const int tot = block_sum<int>(c, red);
+    if (threadIdx.x == 0) tile_counts[blockIdx.x] = tot;
+}
+
+// per-row integer sums (seqlens); one block per row
+template <typename MT>
+__global__ void row_len_kernel(const MT* __restrict__ mask, long long S, int* __restrict__ seqlens) {
+    __shared__ long long red[32];
+    const long long base = static_cast<long long>(blockIdx.x) * S;
+    long long c = 0;
+    for (long long t = threadIdx.x; t < S; t += blockDim.x) c += static_cast<long long>(mask[base + t]);
+    const long long tot = block_sum<long long>(c, red);
+    if (threadIdx.x == 0) seqlens[blockIdx.x] = static_cast<int>(tot);
+}
+
+// single block: exclusive scan of tile counts -> tile_offsets (long long), inclusive scan of seqlens -> cu_seqlens,
+// totals = {nnz, max_seqlen}
+__global__ void scan_kernel(const int* __restrict__ tile_counts, int num_tiles, long long* __restrict__ tile_offsets,
+                            const int* __restrict__ seqlens, int B, int* __restrict__ cu_seqlens,
+                            int* __restrict__ totals) {
+    __shared__ long long warp_tot[32];
+    __shared__ long long carry_s;
+    __shared__ int max_s[32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    // ---- tiles
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < num_tiles; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        const long long v = (i < num_tiles) ? tile_counts[i] : 0;
+        long long inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) warp_tot[w] = inc;
+        __syncthreads();
+        long long pre = 0;
+        for (int ww = 0; ww < w; ++ww) pre += warp_tot[ww];
+        const long long carry = carry_s;
+        if (i < num_tiles) tile_offsets[i] = carry + pre + inc - v;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry_s = carry + pre + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        tile_offsets[num_tiles] = carry_s;
+        totals[0] = static_cast<int>(carry_s);
+    }
+    __syncthreads();
+    // ---- rows: int32 cumsum (wraps like torch's int32 cumsum would)
+    if (threadIdx.x == 0) {
+        carry_s = 0;
+        cu_seqlens[0] = 0;
+    }
+    int mx = 0;
+    __syncthreads();
+    for (int base = 0; base < B; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        const int v = (i < B) ? seqlens[i] : 0;
+        if (i < B) mx = max(mx, v);
+        long long inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) warp_tot[w] = inc;
+        __syncthreads();
+        long long pre = 0;
+        for (int ww = 0; ww < w; ++ww) pre += warp_tot[ww];
+        const long long carry = carry_s;
+        if (i < B) cu_seqlens[i + 1] = static_cast<int>(carry + pre + inc);
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry_s = carry + pre + inc;
+        __syncthreads();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) max_s[w] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int m = 0;
+        for (int ww = 0; ww < nw; ++ww) m = max(m, max_s[ww]);
+        totals[1] = (B > 0) ? m : 0;
+    }
+}
+
+// ordered write of the nonzero positions of each tile
+template <typename MT>
+__global__ void tile_write_kernel(const MT* __restrict__ mask, long long n, const long long* __restrict__ tile_offsets,
+                                  long long* __restrict__ indices) {
+    __shared__ int warp_cnt[kItems][kTileThreads / 32];
+    const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    bool f[kItems];
+    unsigned bal[kItems];
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        const long long i = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
+        f[j] = (i < n) && mask_nonzero(mask[i]);
+        bal[j] = __ballot_sync(0xffffffffu, f[j]);
+        if (lane == 0) warp_cnt[j][w] = __popc(bal[j]);
+    }
+    __syncthreads();
+    // element order inside the tile is (j, warp, lane): rank = sum of counts of all earlier (j', w') + lane prefix
+    long long off = tile_offsets[blockIdx.x];
+    int run = 0;
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        int before = 0, total_j = 0;
+#pragma unroll
+        for (int ww = 0; ww < kTileThreads / 32; ++ww) {
+            const int c = warp_cnt[j][ww];
+            before += (ww < w) ? c : 0;
+            total_j += c;
+        }
+        if (f[j]) {
+            const int r = run + before + __popc(bal[j] & ((1u << lane) - 1u));
+            indices[off + r] = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
+        }
+        run += total_j;
+    }
+}
+
+// out[i*upr + c] = src[idx[i]*upr + c]  (units of U bytes)
+template <typename U>
+__global__ void gather_units_kernel(const U* __restrict__ src, const long long* __restrict__ idx, long long n_idx,
+                                    long long upr, U* __restrict__ out) {
+    const long long total = n_idx * upr;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < total; u += stride) {
+        const long long r = u / upr, c = u - r * upr;
+        out[u] = src[idx[r] * upr + c];
+    }
+}
+template <typename U>
+__global__ void scatter_units_kernel(const U* __restrict__ src, const long long* __restrict__ idx, long long n_idx,
+                                     long long upr, U* __restrict__ out) {
+    const long long total = n_idx * upr;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < total; u += stride) {
+        const long long r = u / upr, c = u - r * upr;
+        out[idx[r] * upr + c] = src[u];
+    }
+}
+
+static inline int unit_bytes(const void* a, const void* b, int64_t row_bytes) {
+    const uintptr_t x = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
+                        static_cast<uintptr_t>(row_bytes);
+    if ((x & 15) == 0) return 16;
+    if ((x & 7) == 0) return 8;
+    if ((x & 3) == 0) return 4;
+    if ((x & 1) == 0) return 2;
+    return 1;
+}
+
+static inline unsigned copy_grid(int64_t total_units) {
+    int64_t g = ceil_div(total_units, 256);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
+    if (g > cap) g = cap;
+    return static_cast<unsigned>(g < 1 ? 1 : g);
+}
+
+}  // namespace vpg
+
+using namespace vpg;
+
+extern "C" {
+
+size_t vpg_unpad_workspace_bytes(int64_t n) {
+    const int64_t tiles = ceil_div(n > 0 ? n : 1, kTile);
+    return static_cast<size_t>(tiles) * sizeof(int) + 16 + static_cast<size_t>(tiles + 1) * sizeof(long long) + 16;
+}
+
+int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,
+                      int32_t* cu_seqlens, int32_t* totals, void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(mask && indices && seqlens && cu_seqlens && totals, "null pointer argument");
+    VPG_CHECK_ARG(B >= 0 && S >= 0 && B * S < (1LL << 31), "mask too large (B*S must fit int32)");
+    VPG_CHECK_ARG(mask_dtype != VPG_MASK_F32, "float masks are not supported by unpad_indices");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int64_t n = B * S;
+    const size_t need = vpg_unpad_workspace_bytes(n);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "unpad workspace too small: need %zu, got %zu", need, workspace_bytes);
+    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 7) == 0, "workspace must be 8-byte aligned");
+    const int tiles = static_cast<int>(n > 0 ? ceil_div(n, kTile) : 0);
+    long long* tile_offsets = static_cast<long long*>(workspace);
+    int* tile_counts = reinterpret_cast<int*>(tile_offsets + (ceil_div(n > 0 ? n : 1, kTile) + 1));
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (tiles > 0) {
+            tile_count_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(mk, n, tile_counts);
+            count_launch();
+        }
+        if (B > 0 && S > 0) {
+            row_len_kernel<MT><<<static_cast<unsigned>(B), 256, 0, stream>>>(mk, S, seqlens);
+            count_launch();
+        } else if (B > 0) {
+            VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
+        }
+        scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, tiles, tile_offsets, seqlens, static_cast<int>(B), cu_seqlens,
+                                            totals);
+        count_launch();
+        if (tiles > 0) {
+            tile_write_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(mk, n, tile_offsets,
+                                                                      reinterpret_cast<long long*>(indices));
+            count_launch();
+        }
+    });
+    VPG_CUDA(cudaPeekAtLastError());
+    return VPG_OK;
+}
+
+int vpg_gather_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
+                    void* stream_) {
+    VPG_CHECK_ARG(n_idx >= 0 && row_bytes > 0, "invalid gather_rows arguments");
+    if (n_idx == 0) return VPG_OK;
+    VPG_CHECK_ARG(src && indices && out, "null pointer argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const long long* idx = reinterpret_cast<const long long*>(indices);
+    const int u = unit_bytes(src, out, row_bytes);
+    const int64_t upr = row_bytes / u;
+    const unsigned g = copy_grid(n_idx * upr);
+    switch (u) {
+        case 16: gather_units_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, n_idx, upr, (uint4*)out); break;
+        case 8: gather_units_kernel<uint2><<<g, 256, 0, stream>>>((const uint2*)src, idx, n_idx, upr, (uint2*)out); break;
+        case 4: gather_units_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, idx, n_idx, upr, (uint32_t*)out); break;
+        case 2: gather_units_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, n_idx, upr, (uint16_t*)out); break;
+        default: gather_units_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, n_idx, upr, (uint8_t*)out); break;
+    }
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
+                     int64_t n_out, int zero_fill, void* stream_) {
+    VPG_CHECK_ARG(n_idx >= 0 && row_bytes > 0 && n_out >= 0, "invalid scatter_rows arguments");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (zero_fill && n_out > 0) {
+        VPG_CHECK_ARG(out, "null output");
+        VPG_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(n_out) * row_bytes, stream));
+    }
+    if (n_idx == 0) return VPG_OK;
+    VPG_CHECK_ARG(src && indices && out, "null pointer argument");
+    const long long* idx = reinterpret_cast<const long long*>(indices);
+    const int u = unit_bytes(src, out, row_bytes);
+    const int64_t upr = row_bytes / u;
+    const unsigned g = copy_grid(n_idx * upr);
+    switch (u) {
+        case 16: scatter_units_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, n_idx, upr, (uint4*)out); break;
+        case 8: scatter_units_kernel<uint2><<<g, 256, 0, stream>>>((const uint2*)src, idx, n_idx, upr, (uint2*)out); break;
+        case 4: scatter_units_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, idx, n_idx, upr, (uint32_t*)out); break;
+        case 2: scatter_units_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, n_idx, upr, (uint16_t*)out); break;
+        default: scatter_units_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, n_idx, upr, (uint8_t*)out); break;
+    }
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+}  // extern "C"

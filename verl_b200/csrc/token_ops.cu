@@ -1,0 +1,919 @@
+// Memory-bound token kernels: masked reductions, agg_loss, fused PPO actor loss (+ closed-form gradient),
+// KL penalty, GRPO group advantage, GAE (+ masked whiten).
+// Reference semantics: verl/trainer/ppo/core_algos.py and verl/utils/torch_functional.py (lines cited per kernel).
+//
+// Design: every [B,L] pass is one coalesced sweep with 128-bit loads (4 tokens / thread / iteration; scalar path for
+// unaligned or L % 4 != 0 inputs), per-thread fp32 partials -> warp shuffle -> one double atomic per block and
+// quantity.  Scalars that depend on a global sum (token-mean normaliser) are produced by a first, mask-only pass;
+// the "last block done" pattern folds the tiny finalisation into the same launch.  Compiled with --fmad=false so
+// that elementwise results follow the reference's separately rounded fp32 operations.
+#include <cuda_runtime.h>
+
+#include "common.h"
+#include "reduce.cuh"
+
+namespace vpg {
+
+constexpr int kThreads = 256;
+
+template <int VEC>
+struct Pack {
+    float v[VEC];
+};
+
+template <int VEC>
+__device__ __forceinline__ Pack<VEC> ldv(const float* __restrict__ p, long long i) {
+    Pack<VEC> r;
+    if constexpr (VEC == 4) {
+        const float4 a = load_f4(p, i);
+        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
+    } else {
+        r.v[0] = p[i];
+    }
+    return r;
+}
+template <int VEC, typename MT>
+__device__ __forceinline__ Pack<VEC> ldm(const MT* __restrict__ p, long long i) {
+    Pack<VEC> r;
+    if constexpr (VEC == 4) {
+        const float4 a = load_mask4<MT>(p, i);
+        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
+    } else {
+        r.v[0] = mask_to_float(p[i]);
+    }
+    return r;
+}
+template <int VEC>
+__device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pack<VEC>& r) {
+    if constexpr (VEC == 4) {
+        store_f4(p, i, make_float4(r.v[0], r.v[1], r.v[2], r.v[3]));
+    } else {
+        p[i] = r.v[0];
+    }
+}
+
+// blocks per row so that the grid has >= ~4 waves when the problem is large enough, never more than needed
+static inline int blocks_per_row(int64_t B, int64_t L, int vec) {
+    const int64_t per_block = static_cast<int64_t>(kThreads) * vec * 2;
+    int64_t need = ceil_div(L, per_block);
+    int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * 8, B > 0 ? B : 1);
+    int64_t g = need < want ? need : want;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+
+// "last block done": returns true in every thread of the block that arrives last
+__device__ __forceinline__ bool last_block_done(unsigned int* counter, unsigned int total) {
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(counter, 1u);
+        is_last = (prev == total - 1);
+    }
+    __syncthreads();
+    if (is_last) __threadfence();
+    return is_last;
+}
+
+// =====================================================================================================
+// masked_sum (verl/utils/torch_functional.py:163-168): out[0] = sum(where(m!=0, v, 0) * m), out[1] = sum(m)
+// =====================================================================================================
+template <int VEC, typename MT>
+__global__ void masked_sum_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
+                                  double* __restrict__ out) {
+    __shared__ double red[32];
+    float s = 0.f, c = 0.f;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
+        const Pack<VEC> v = ldv<VEC>(values, i);
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            s += (m.v[j] != 0.f ? v.v[j] : 0.f) * m.v[j];
+            c += m.v[j];
+        }
+    }
+    const double bs = block_sum<double>(static_cast<double>(s), red);
+    const double bc = block_sum<double>(static_cast<double>(c), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&out[0], bs);
+        atomicAdd(&out[1], bc);
+    }
+}
+
+// per-row (axis=-1): out_sum[b] = sum_t where(m,v,0)*m, out_cnt[b] = sum_t m.  One block per row, no atomics.
+template <int VEC, typename MT>
+__global__ void masked_row_sum_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long L,
+                                      float* __restrict__ row_sum, float* __restrict__ row_cnt) {
+    __shared__ double red[32];
+    const long long base = static_cast<long long>(blockIdx.x) * L;
+    float s = 0.f, c = 0.f;
+    for (long long t = static_cast<long long>(threadIdx.x) * VEC; t < L; t += static_cast<long long>(blockDim.x) * VEC) {
+        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+        Pack<VEC> v;
+        if (values) v = ldv<VEC>(values, base + t);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            if (values) s += (m.v[j] != 0.f ? v.v[j] : 0.f) * m.v[j];
+            c += m.v[j];
+        }
+    }
+    const double bs = block_sum<double>(static_cast<double>(s), red);
+    const double bc = block_sum<double>(static_cast<double>(c), red);
+    if (threadIdx.x == 0) {
+        if (row_sum) row_sum[blockIdx.x] = static_cast<float>(bs);
+        if (row_cnt) row_cnt[blockIdx.x] = static_cast<float>(bc);
+    }
+}
+
+// =====================================================================================================
+// kl_penalty (verl/trainer/ppo/core_algos.py:1034-1069), elementwise; optional d out / d logprob
+// =====================================================================================================
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+__device__ __forceinline__ void kl_term(int kind, float lp, float ref, float& out, float& grad) {
+    if (kind == VPG_KL_K1) {
+        out = lp - ref;
+        grad = 1.f;
+    } else if (kind == VPG_KL_ABS) {
+        const float d = lp - ref;
+        out = fabsf(d);
+        grad = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+    } else if (kind == VPG_KL_MSE) {
+        const float d = lp - ref;
+        out = 0.5f * (d * d);
+        grad = d;
+    } else {  // low_var_kl
+        const float kr = ref - lp;
+        const float k = clampf(kr, -20.f, 20.f);
+        const float r = expf(k);
+        const float raw = r - k - 1.f;
+        out = clampf(raw, -10.f, 10.f);
+        const bool in_k = (kr >= -20.f) && (kr <= 20.f);
+        const bool in_c = (raw >= -10.f) && (raw <= 10.f);
+        grad = (in_k && in_c) ? -(r - 1.f) : 0.f;
+    }
+}
+
+template <int VEC>
+__global__ void kl_penalty_kernel(const float* __restrict__ lp, const float* __restrict__ ref, int kind, long long n,
+                                  float* __restrict__ out, float* __restrict__ grad) {
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
+        const Pack<VEC> a = ldv<VEC>(lp, i);
+        const Pack<VEC> b = ldv<VEC>(ref, i);
+        Pack<VEC> o, g;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) kl_term(kind, a.v[j], b.v[j], o.v[j], g.v[j]);
+        stv<VEC>(out, i, o);
+        if (grad) stv<VEC>(grad, i, g);
+    }
+}
+
+// =====================================================================================================
+// Fused PPO actor loss.  compute_policy_loss (core_algos.py:722-794) + agg_loss (:686-719) + kl_penalty (:1034-1069)
+// composed as in verl/workers/actor/dp_actor.py:422-469, forward and closed-form gradient.
+//
+// workspace (doubles): [0] two uint32 counters | [1] N = sum(mask) | [2..10) global sums G[8] |
+//                      [10, 10+B) row mask sums | [10+B, 10+4B) row sums of {pg, entropy, kl} * mask
+//   G: 0 pg 1 -log_ratio 2 clip 3 clip_lower 4 entropy 5 kl   (all weighted where(m,v,0)*m as masked_mean does)
+// =====================================================================================================
+struct PpoParams {
+    const float* old_lp;
+    const float* lp;
+    const float* adv;
+    const float* entropy;  // may be null
+    const float* ref_lp;   // may be null
+    long long B, L;
+    int gx;
+    float ratio_lo, ratio_hi, clip_c;
+    int agg_mode;
+    float entropy_coeff, kl_coef;
+    int kl_kind;
+    float loss_scale;
+    float* metrics;
+    float* d_lp;
+    float* d_ent;
+    double* ws;
+};
+
+constexpr int kWsHeader = 10;
+
+// pass 1: row mask counts; last block sums them into ws[1]
+template <int VEC, typename MT>
+__global__ void mask_count_kernel(const MT* __restrict__ mask, long long B, long long L, int gx, double* ws) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    float c = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) c += m.v[j];
+    }
+    const double bc = block_sum<double>(static_cast<double>(c), red);
+    if (threadIdx.x == 0) atomicAdd(&ws[kWsHeader + b], bc);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
+    if (last_block_done(&counters[0], gridDim.x)) {
+        double s = 0.0;
+        for (long long i = threadIdx.x; i < B; i += blockDim.x) s += __ldcg(&ws[kWsHeader + i]);
+        s = block_sum<double>(s, red);
+        if (threadIdx.x == 0) ws[1] = s;
+    }
+}
+
+// gradient weight of one token for the chosen aggregation mode (d agg / d loss_mat[b,t])
+__device__ __forceinline__ float agg_coef(int mode, double n_total, double row_cnt, long long B, long long L) {
+    if (mode == VPG_AGG_TOKEN_MEAN) return static_cast<float>(1.0 / (n_total + 1e-8));
+    if (mode == VPG_AGG_SEQ_MEAN_TOKEN_SUM) return static_cast<float>(1.0 / static_cast<double>(B));
+    if (mode == VPG_AGG_SEQ_MEAN_TOKEN_MEAN) return static_cast<float>(1.0 / (static_cast<double>(B) * row_cnt));
+    return static_cast<float>(1.0 / static_cast<double>(L));
+}
+
+__device__ __forceinline__ double agg_finalize(int mode, const double* row_sum, const double* row_cnt, double g_where,
+                                               double n_total, long long B, long long L, double* red) {
+    // returns the aggregated loss in thread 0
+    if (mode == VPG_AGG_TOKEN_MEAN) return g_where / (n_total + 1e-8);
+    double s = 0.0;
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const double rs = __ldcg(&row_sum[i]);
+        s += (mode == VPG_AGG_SEQ_MEAN_TOKEN_MEAN) ? rs / __ldcg(&row_cnt[i]) : rs;
+    }
+    s = block_sum<double>(s, red);
+    if (mode == VPG_AGG_SEQ_MEAN_TOKEN_SUM_NORM) return s / static_cast<double>(L);
+    return s / static_cast<double>(B);
+}
+
+template <int VEC, typename MT>
+__global__ void ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / p.gx;
+    const int cx = blockIdx.x % p.gx;
+    const long long base = b * p.L;
+    double* ws = p.ws;
+    const double n_total = ws[1];
+    const double row_cnt = ws[kWsHeader + b];
+    const float coef = agg_coef(p.agg_mode, n_total, row_cnt, p.B, p.L) * p.loss_scale;
+    const bool where_w = (p.agg_mode == VPG_AGG_TOKEN_MEAN);
+    const bool has_ent = p.entropy != nullptr;
+    const bool has_kl = p.ref_lp != nullptr && p.kl_kind >= 0;
+
+    float a_pg = 0.f, a_lr = 0.f, a_clip = 0.f, a_low = 0.f, a_ent = 0.f, a_kl = 0.f;  // where-weighted
+    float r_pg = 0.f, r_ent = 0.f, r_kl = 0.f;                                           // plain v*m
+    const long long stride = static_cast<long long>(p.gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < p.L; t += stride) {
+        const long long i = base + t;
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> old = ldv<VEC>(p.old_lp, i);
+        const Pack<VEC> lp = ldv<VEC>(p.lp, i);
+        const Pack<VEC> adv = ldv<VEC>(p.adv, i);
+        Pack<VEC> ent, ref, dlp, dent;
+        if (has_ent) ent = ldv<VEC>(p.entropy, i);
+        if (has_kl) ref = ldv<VEC>(p.ref_lp, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const float mj = m.v[j];
+            const bool on = mj != 0.f;
+            const float A = adv.v[j];
+            const float lr_raw = lp.v[j] - old.v[j];
+            const float lr = clampf(lr_raw, -20.f, 20.f);
+            const float ratio = expf(lr);
+            const float l1 = -A * ratio;
+            const float rc = clampf(ratio, p.ratio_lo, p.ratio_hi);
+            const float l2 = -A * rc;
+            const float c1 = fmaxf(l1, l2);
+            const float l3 = -A * p.clip_c;
+            const float c2 = fminf(l3, c1);
+            const float pg = (A < 0.f) ? c2 : c1;
+            const float f_clip = (l2 > l1) ? 1.f : 0.f;
+            const float f_low = ((c1 > l3) ? 1.f : 0.f) * ((A < 0.f) ? 1.f : 0.f);
+            a_pg += (on ? pg : 0.f) * mj;
+            a_lr += (on ? -lr : 0.f) * mj;
+            a_clip += (on ? f_clip : 0.f) * mj;
+            a_low += (on ? f_low : 0.f) * mj;
+            r_pg += pg * mj;
+            // ---- gradient of pg wrt log_prob (ties of maximum/min split 1/2, as torch autograd does)
+            const bool in_lr = (lr_raw >= -20.f) && (lr_raw <= 20.f);
+            const float dl1 = in_lr ? -A * ratio : 0.f;
+            const bool in_clip = (ratio >= p.ratio_lo) && (ratio <= p.ratio_hi);
+            const float dl2 = (in_lr && in_clip) ? -A * ratio : 0.f;
+            const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
+            const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
+            float g = (A < 0.f) ? g_c2 : g_c1;
+            if (has_kl) {
+                float kv, kg;
+                kl_term(p.kl_kind, lp.v[j], ref.v[j], kv, kg);
+                a_kl += (on ? kv : 0.f) * mj;
+                r_kl += kv * mj;
+                g += p.kl_coef * kg;
+            }
+            const float w = where_w ? (on ? mj : 0.f) : mj;
+            dlp.v[j] = coef * w * g;
+            if (has_ent) {
+                a_ent += (on ? ent.v[j] : 0.f) * mj;
+                r_ent += ent.v[j] * mj;
+                dent.v[j] = -(coef * w) * p.entropy_coeff;
+            }
+        }
+        if (p.d_lp) stv<VEC>(p.d_lp, i, dlp);
+        if (p.d_ent && has_ent) stv<VEC>(p.d_ent, i, dent);
+    }
+    float acc[9] = {a_pg, a_lr, a_clip, a_low, a_ent, a_kl, r_pg, r_ent, r_kl};
+    double tot[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) tot[k] = block_sum<double>(static_cast<double>(acc[k]), red);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) atomicAdd(&ws[2 + k], tot[k]);
+        double* rows = ws + kWsHeader + p.B;
+        atomicAdd(&rows[b], tot[6]);
+        atomicAdd(&rows[p.B + b], tot[7]);
+        atomicAdd(&rows[2 * p.B + b], tot[8]);
+    }
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
+    if (last_block_done(&counters[1], gridDim.x)) {
+        const double* rcnt = ws + kWsHeader;
+        const double* rows = ws + kWsHeader + p.B;
+        const double G0 = __ldcg(&ws[2]), G1 = __ldcg(&ws[3]), G2 = __ldcg(&ws[4]), G3 = __ldcg(&ws[5]);
+        const double G4 = __ldcg(&ws[6]), G5 = __ldcg(&ws[7]);
+        const double pg_loss = agg_finalize(p.agg_mode, rows, rcnt, G0, n_total, p.B, p.L, red);
+        const double ent_loss = has_ent ? agg_finalize(p.agg_mode, rows + p.B, rcnt, G4, n_total, p.B, p.L, red) : 0.0;
+        const double kl_loss = has_kl ? agg_finalize(p.agg_mode, rows + 2 * p.B, rcnt, G5, n_total, p.B, p.L, red) : 0.0;
+        if (threadIdx.x == 0) {
+            // fp32 composition as in dp_actor.py:445-469
+            const float pgf = static_cast<float>(pg_loss), entf = static_cast<float>(ent_loss);
+            const float klf = static_cast<float>(kl_loss);
+            float policy = pgf;
+            if (has_ent && p.entropy_coeff != 0.f) policy = policy - entf * p.entropy_coeff;
+            if (has_kl) policy = policy + klf * p.kl_coef;
+            const double den = n_total + 1e-8;
+            p.metrics[0] = policy * p.loss_scale;
+            p.metrics[1] = pgf;
+            p.metrics[2] = static_cast<float>(G2 / den);
+            p.metrics[3] = static_cast<float>(G1 / den);
+            p.metrics[4] = static_cast<float>(G3 / den);
+            p.metrics[5] = entf;
+            p.metrics[6] = klf;
+            p.metrics[7] = static_cast<float>(n_total);
+        }
+    }
+}
+
+// agg_loss for an arbitrary loss matrix: forward sums + gradient d loss / d loss_mat
+template <int VEC, typename MT>
+__global__ void agg_loss_kernel(const float* __restrict__ loss_mat, const MT* __restrict__ mask, long long B,
+                                long long L, int gx, int mode, float* __restrict__ out, float* __restrict__ d_mat,
+                                double* ws) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    const double n_total = ws[1];
+    const double row_cnt = ws[kWsHeader + b];
+    const float coef = agg_coef(mode, n_total, row_cnt, B, L);
+    const bool where_w = (mode == VPG_AGG_TOKEN_MEAN);
+    float a = 0.f, r = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const long long i = base + t;
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> v = ldv<VEC>(loss_mat, i);
+        Pack<VEC> d;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const bool on = m.v[j] != 0.f;
+            a += (on ? v.v[j] : 0.f) * m.v[j];
+            r += v.v[j] * m.v[j];
+            d.v[j] = coef * (where_w ? (on ? m.v[j] : 0.f) : m.v[j]);
+        }
+        if (d_mat) stv<VEC>(d_mat, i, d);
+    }
+    const double ta = block_sum<double>(static_cast<double>(a), red);
+    const double tr = block_sum<double>(static_cast<double>(r), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&ws[2], ta);
+        atomicAdd(&ws[kWsHeader + B + b], tr);
+    }
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
+    if (last_block_done(&counters[1], gridDim.x)) {
+        const double v = agg_finalize(mode, ws + kWsHeader + B, ws + kWsHeader, __ldcg(&ws[2]), n_total, B, L, red);
+        if (threadIdx.x == 0) out[0] = static_cast<float>(v);
+    }
+}
+
+// =====================================================================================================
+// GRPO outcome advantage (core_algos.py:245-308)
+// workspace (doubles): [0,B) scores | [B, B+3G) per group {count, sum, sum of squared deviations}
+// =====================================================================================================
+template <int VEC, typename MT>
+__global__ void row_score_kernel(const float* __restrict__ rewards, long long L, int gx, double* __restrict__ scores) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    float s = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const Pack<VEC> v = ldv<VEC>(rewards, base + t);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) s += v.v[j];
+    }
+    const double bs = block_sum<double>(static_cast<double>(s), red);
+    if (threadIdx.x == 0) atomicAdd(&scores[b], bs);
+}
+
+// single block: group statistics and the per-row scalar advantage (written as float into adv_row[B])
+__global__ void grpo_group_kernel(const double* __restrict__ scores, const int* __restrict__ gid, long long B,
+                                  long long G, float eps, int norm_by_std, double* __restrict__ gstat,
+                                  float* __restrict__ adv_row) {
+    // pass 1: count and sum (scores are rounded to fp32 first: the reference holds them in an fp32 tensor)
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const double s = static_cast<double>(static_cast<float>(scores[i]));
+        atomicAdd(&gstat[3 * g + 0], 1.0);
+        atomicAdd(&gstat[3 * g + 1], s);
+    }
+    __syncthreads();
+    // pass 2: squared deviations from the group mean
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const double n = gstat[3 * g + 0];
+        const double mean = gstat[3 * g + 1] / n;
+        const double d = static_cast<double>(static_cast<float>(scores[i])) - mean;
+        atomicAdd(&gstat[3 * g + 2], d * d);
+    }
+    __syncthreads();
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const double n = gstat[3 * g + 0];
+        float mean, stdv;
+        if (n <= 1.0) {  // singleton group: mean 0, std 1 (core_algos.py:293-295)
+            mean = 0.f;
+            stdv = 1.f;
+        } else {
+            mean = static_cast<float>(gstat[3 * g + 1] / n);
+            stdv = static_cast<float>(sqrt(gstat[3 * g + 2] / (n - 1.0)));  // unbiased, torch.std
+        }
+        const float sc = static_cast<float>(scores[i]);
+        adv_row[i] = norm_by_std ? (sc - mean) / (stdv + eps) : (sc - mean);
+    }
+}
+
+template <int VEC, typename MT>
+__global__ void broadcast_mask_kernel(const float* __restrict__ row_val, const MT* __restrict__ mask, long long L,
+                                      int gx, float* __restrict__ out) {
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    const float a = row_val[b];
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+        Pack<VEC> o;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) o.v[j] = a * m.v[j];
+        stv<VEC>(out, base + t, o);
+    }
+}
+
+// =====================================================================================================
+// GAE (core_algos.py:193-241).  One block per row; each thread owns a contiguous segment of kSeg tokens held in
+// registers.  The reverse recurrence over (nextvalues, lastgaelam) is an affine map per token:
+//     nv' = (1-m) nv + m v          lg' = m*gamma*nv + (m*gamma*lam + (1-m)) lg + m (r - v)
+// Phase 1 composes each segment's map, phase 2 does a block-wide right-to-left exclusive scan of the segment maps,
+// phase 3 replays the segment with its true incoming state using the reference's exact operation order.
+// Rows longer than blockDim*kSeg are processed in super-chunks from the right, carrying the state.
+// Also accumulates sum(adv*m), sum(adv^2*m), sum(m) (doubles) for the whitening pass.
+// =====================================================================================================
+constexpr int kSeg = 8;
+
+struct Affine {  // (nv, lg) -> (an*nv + cn, p*nv + q*lg + r)
+    float an, cn, p, q, r;
+};
+__device__ __forceinline__ Affine affine_identity() { return Affine{1.f, 0.f, 0.f, 1.f, 0.f}; }
+// h = g after f  (apply f first, then g)
+__device__ __forceinline__ Affine affine_compose(const Affine& g, const Affine& f) {
+    Affine h;
+    h.an = g.an * f.an;
+    h.cn = g.an * f.cn + g.cn;
+    h.p = g.p * f.an + g.q * f.p;
+    h.q = g.q * f.q;
+    h.r = g.p * f.cn + g.q * f.r + g.r;
+    return h;
+}
+__device__ __forceinline__ Affine affine_shfl_down(const Affine& a, int delta) {
+    Affine o;
+    o.an = __shfl_down_sync(0xffffffffu, a.an, delta);
+    o.cn = __shfl_down_sync(0xffffffffu, a.cn, delta);
+    o.p = __shfl_down_sync(0xffffffffu, a.p, delta);
+    o.q = __shfl_down_sync(0xffffffffu, a.q, delta);
+    o.r = __shfl_down_sync(0xffffffffu, a.r, delta);
+    return o;
+}
+
+template <typename MT>
+__global__ void gae_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                           const MT* __restrict__ mask, long long L, float gamma, float lam,
+                           float* __restrict__ adv_out, float* __restrict__ ret_out, double* __restrict__ sums) {
+    __shared__ Affine warp_maps[32];
+    __shared__ float carry[2];
+    __shared__ double red[32];
+    const long long base = static_cast<long long>(blockIdx.x) * L;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const float gl = gamma * lam;
+    const long long span = static_cast<long long>(blockDim.x) * kSeg;
+    if (threadIdx.x == 0) carry[0] = 0.f, carry[1] = 0.f;
+    float s1 = 0.f, s2 = 0.f, sc = 0.f;
+    // super-chunks from the right end; chunk k covers [start, start+span)
+    const long long n_chunks = (L + span - 1) / span;
+    for (long long ck = n_chunks - 1; ck >= 0; --ck) {
+        __syncthreads();
+        const long long t0 = ck * span + static_cast<long long>(threadIdx.x) * kSeg;
+        float r[kSeg], v[kSeg], m[kSeg];
+#pragma unroll
+        for (int j = 0; j < kSeg; ++j) {
+            const long long t = t0 + j;
+            const bool ok = t < L;
+            r[j] = ok ? rewards[base + t] : 0.f;
+            v[j] = ok ? values[base + t] : 0.f;
+            m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps
+        }
+        // phase 1: compose this segment right-to-left
+        Affine seg = affine_identity();
+#pragma unroll
+        for (int j = kSeg - 1; j >= 0; --j) {
+            Affine st;
+            st.an = 1.f - m[j];
+            st.cn = m[j] * v[j];
+            st.p = m[j] * gamma;
+            st.q = m[j] * gl + (1.f - m[j]);
+            st.r = m[j] * (r[j] - v[j]);
+            seg = affine_compose(st, seg);
+        }
+        // phase 2: exclusive suffix scan over threads (thread i needs the composition of segments i+1.. end)
+        Affine inc = seg;  // inclusive suffix: seg_i after (segments to the right)
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const Affine o = affine_shfl_down(inc, d);
+            if (lane + d < 32) inc = affine_compose(inc, o);
+        }
+        if (lane == 0) warp_maps[w] = inc;  // whole-warp map
+        __syncthreads();
+        // map of everything to the right of this warp
+        Affine right = affine_identity();
+        for (int ww = nw - 1; ww > w; --ww) right = affine_compose(warp_maps[ww], right);
+        // exclusive within the warp: composition of lanes > lane
+        Affine excl = affine_shfl_down(inc, 1);
+        if (lane == 31) excl = affine_identity();
+        excl = affine_compose(excl, right);
+        // incoming state for this segment
+        const float nv_in = carry[0], lg_in = carry[1];
+        float nv = excl.an * nv_in + excl.cn;
+        float lg = excl.p * nv_in + excl.q * lg_in + excl.r;
+        // phase 3: replay with the reference's operation order
+        float a[kSeg];
+#pragma unroll
+        for (int j = kSeg - 1; j >= 0; --j) {
+            const float delta = r[j] + gamma * nv - v[j];
+            const float lg_ = delta + gl * lg;
+            nv = v[j] * m[j] + (1.f - m[j]) * nv;
+            lg = lg_ * m[j] + (1.f - m[j]) * lg;
+            a[j] = lg;
+        }
+#pragma unroll
+        for (int j = 0; j < kSeg; ++j) {
+            const long long t = t0 + j;
+            if (t < L) {
+                adv_out[base + t] = a[j];
+                ret_out[base + t] = a[j] + v[j];
+                s1 += (m[j] != 0.f ? a[j] : 0.f) * m[j];
+                s2 += (m[j] != 0.f ? a[j] * a[j] : 0.f) * m[j];
+                sc += m[j];
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {  // state after the leftmost token of this chunk
+            carry[0] = nv;
+            carry[1] = lg;
+        }
+    }
+    const double d1 = block_sum<double>(static_cast<double>(s1), red);
+    const double d2 = block_sum<double>(static_cast<double>(s2), red);
+    const double dc = block_sum<double>(static_cast<double>(sc), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&sums[0], d1);
+        atomicAdd(&sums[1], d2);
+        atomicAdd(&sums[2], dc);
+    }
+}
+
+// sums of v*m, v^2*m, m for masked_whiten
+template <int VEC, typename MT>
+__global__ void whiten_stats_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
+                                    double* __restrict__ sums) {
+    __shared__ double red[32];
+    float s1 = 0.f, s2 = 0.f, sc = 0.f;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
+        const Pack<VEC> v = ldv<VEC>(values, i);
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const bool on = m.v[j] != 0.f;
+            s1 += (on ? v.v[j] : 0.f) * m.v[j];
+            s2 += (on ? v.v[j] * v.v[j] : 0.f) * m.v[j];
+            sc += m.v[j];
+        }
+    }
+    const double d1 = block_sum<double>(static_cast<double>(s1), red);
+    const double d2 = block_sum<double>(static_cast<double>(s2), red);
+    const double dc = block_sum<double>(static_cast<double>(sc), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&sums[0], d1);
+        atomicAdd(&sums[1], d2);
+        atomicAdd(&sums[2], dc);
+    }
+}
+
+// masked_whiten (torch_functional.py:206-223): mean = S1/(N+1e-8); var = E[(x-mean)^2] * N/(N-1);
+// out = (x - mean) * rsqrt(var + 1e-8) (+ mean if !shift_mean).  In place allowed (values == out).
+template <int VEC>
+__global__ void whiten_apply_kernel(const float* values, long long n, const double* __restrict__ sums,
+                                    int shift_mean, float* out, int* __restrict__ status) {
+    const double N = sums[2];
+    if (N == 0.0 || N == 1.0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = (N == 0.0) ? 1 : 2;
+        return;  // the reference raises ValueError (torch_functional.py:195-200); outputs are left untouched
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = 0;
+    const double den = N + 1e-8;
+    const double mean_d = sums[0] / den;
+    // sum((x-mean)^2 m) = S2 - 2 mean S1 + mean^2 N
+    double var_d = (sums[1] - 2.0 * mean_d * sums[0] + mean_d * mean_d * N) / den;
+    var_d = var_d * (N / (N - 1.0));
+    const float mean = static_cast<float>(mean_d);
+    const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-8f);
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
+        Pack<VEC> v = ldv<VEC>(values, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            float wv = (v.v[j] - mean) * rstd;
+            if (!shift_mean) wv += mean;
+            v.v[j] = wv;
+        }
+        stv<VEC>(out, i, v);
+    }
+}
+
+static inline int flat_grid(int64_t n, int vec) {
+    int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    if (g > cap) g = cap;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+
+}  // namespace vpg
+
+
+using namespace vpg;
+
+// vector path requires 16-byte aligned rows
+static inline bool rows_vec_ok(int64_t L, const void* mask, int mask_dtype, std::initializer_list<const void*> ptrs) {
+    if (L % 4 != 0) return false;
+    if (mask && !mask_aligned(mask, mask_dtype)) return false;
+    for (const void* p : ptrs)
+        if (p && !aligned16(p)) return false;
+    return true;
+}
+
+extern "C" {
+
+int vpg_masked_sum(const float* values, const void* mask, int mask_dtype, int64_t n, double* out, void* stream_) {
+    VPG_CHECK_ARG(values && mask && out && n >= 0, "invalid masked_sum arguments");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), stream));
+    if (n == 0) return VPG_OK;
+    const bool vec = rows_vec_ok(n, mask, mask_dtype, {values});
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            masked_sum_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, mk, n, out);
+        else
+            masked_sum_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, mk, n, out);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_masked_row_sum(const float* values, const void* mask, int mask_dtype, int64_t B, int64_t L, float* out_sum,
+                       float* out_cnt, void* stream_) {
+    VPG_CHECK_ARG(mask && B >= 0 && L >= 0 && (out_sum || out_cnt), "invalid masked_row_sum arguments");
+    VPG_CHECK_ARG(!out_sum || values, "values required when out_sum is requested");
+    if (B == 0) return VPG_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {values});
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            masked_row_sum_kernel<4, MT><<<static_cast<unsigned>(B), kThreads, 0, stream>>>(values, mk, L, out_sum, out_cnt);
+        else
+            masked_row_sum_kernel<1, MT><<<static_cast<unsigned>(B), kThreads, 0, stream>>>(values, mk, L, out_sum, out_cnt);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int64_t n, float* out, float* grad_out,
+                   void* stream_) {
+    VPG_CHECK_ARG(logprob && ref_logprob && out && n >= 0, "invalid kl_penalty arguments");
+    if (kind < 0 || kind > 3) return set_error(VPG_ERR_UNSUPPORTED, "kl_penalty kind %d is not implemented", kind);
+    if (n == 0) return VPG_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (rows_vec_ok(n, nullptr, 0, {logprob, ref_logprob, out, grad_out}))
+        kl_penalty_kernel<4><<<flat_grid(n, 4), kThreads, 0, stream>>>(logprob, ref_logprob, kind, n, out, grad_out);
+    else
+        kl_penalty_kernel<1><<<flat_grid(n, 1), kThreads, 0, stream>>>(logprob, ref_logprob, kind, n, out, grad_out);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+size_t vpg_ppo_loss_workspace_bytes(int64_t B, int64_t L) {
+    (void)L;
+    return static_cast<size_t>(kWsHeader + 4 * (B > 0 ? B : 0)) * sizeof(double);
+}
+
+int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
+                 int mask_dtype, const float* entropy, const float* ref_log_prob, int64_t B, int64_t L,
+                 float ratio_lo, float ratio_hi, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
+                 int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy, void* workspace,
+                 size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(old_log_prob && log_prob && advantages && mask && metrics, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    VPG_CHECK_ARG(agg_mode >= 0 && agg_mode <= 3, "invalid loss_agg_mode %d", agg_mode);
+    VPG_CHECK_ARG(clip_c > 1.0f, "clip_ratio_c must be > 1.0 (got %f)", clip_c);  // core_algos.py:761
+    if (ref_log_prob && (kl_kind < 0 || kl_kind > 3))
+        return set_error(VPG_ERR_UNSUPPORTED, "kl_penalty kind %d is not implemented", kl_kind);
+    const size_t need = vpg_ppo_loss_workspace_bytes(B, L);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "ppo_loss workspace too small: need %zu, got %zu", need, workspace_bytes);
+    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 7) == 0, "workspace must be 8-byte aligned");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+    const bool vec = rows_vec_ok(L, mask, mask_dtype,
+                                 {old_log_prob, log_prob, advantages, entropy, ref_log_prob, d_log_prob, d_entropy});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    PpoParams p{};
+    p.old_lp = old_log_prob, p.lp = log_prob, p.adv = advantages, p.entropy = entropy, p.ref_lp = ref_log_prob;
+    p.B = B, p.L = L, p.gx = gx;
+    p.ratio_lo = ratio_lo, p.ratio_hi = ratio_hi, p.clip_c = clip_c;
+    p.agg_mode = agg_mode, p.entropy_coeff = entropy_coeff, p.kl_coef = kl_coef, p.kl_kind = kl_kind;
+    p.loss_scale = loss_scale;
+    p.metrics = metrics, p.d_lp = d_log_prob, p.d_ent = d_entropy;
+    p.ws = static_cast<double*>(workspace);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec) {
+            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws);
+            count_launch();
+            ppo_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(p, mk);
+        } else {
+            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws);
+            count_launch();
+            ppo_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(p, mk);
+        }
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_t B, int64_t L, int agg_mode,
+                 float* out, float* d_loss_mat, void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(loss_mat && mask && out, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    if (agg_mode < 0 || agg_mode > 3) return set_error(VPG_ERR_INVALID, "Invalid loss_agg_mode: %d", agg_mode);
+    const size_t need = vpg_ppo_loss_workspace_bytes(B, L);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "agg_loss workspace too small: need %zu, got %zu", need, workspace_bytes);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+    double* ws = static_cast<double*>(workspace);
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {loss_mat, d_loss_mat});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec) {
+            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws);
+            count_launch();
+            agg_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws);
+        } else {
+            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws);
+            count_launch();
+            agg_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws);
+        }
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+size_t vpg_grpo_workspace_bytes(int64_t B, int64_t G) {
+    return static_cast<size_t>((B > 0 ? B : 0) + 3 * (G > 0 ? G : 0)) * sizeof(double) +
+           static_cast<size_t>(B > 0 ? B : 0) * sizeof(float) + 16;
+}
+
+int vpg_grpo_advantage(const float* rewards, const void* mask, int mask_dtype, const int32_t* group_ids, int64_t B,
+                       int64_t L, int64_t G, float epsilon, int norm_by_std, float* advantages, void* workspace,
+                       size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(rewards && mask && group_ids && advantages, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0 && G > 0 && G <= B, "invalid GRPO shape B=%lld L=%lld groups=%lld", (long long)B,
+                  (long long)L, (long long)G);
+    const size_t need = vpg_grpo_workspace_bytes(B, G);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "grpo workspace too small: need %zu, got %zu", need, workspace_bytes);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* scores = static_cast<double*>(workspace);
+    double* gstat = scores + B;
+    float* adv_row = reinterpret_cast<float*>(gstat + 3 * G);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, static_cast<size_t>(B + 3 * G) * sizeof(double), stream));
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {rewards, advantages});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    if (vec)
+        row_score_kernel<4, float><<<grid, kThreads, 0, stream>>>(rewards, L, gx, scores);
+    else
+        row_score_kernel<1, float><<<grid, kThreads, 0, stream>>>(rewards, L, gx, scores);
+    count_launch();
+    grpo_group_kernel<<<1, 1024, 0, stream>>>(scores, group_ids, B, G, epsilon, norm_by_std, gstat, adv_row);
+    count_launch();
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            broadcast_mask_kernel<4, MT><<<grid, kThreads, 0, stream>>>(adv_row, mk, L, gx, advantages);
+        else
+            broadcast_mask_kernel<1, MT><<<grid, kThreads, 0, stream>>>(adv_row, mk, L, gx, advantages);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+size_t vpg_gae_workspace_bytes(int64_t B, int64_t L) {
+    (void)B;
+    (void)L;
+    return 4 * sizeof(double);
+}
+
+static int whiten_apply(const float* values, int64_t n, const double* sums, int shift_mean, float* out,
+                        int32_t* status, cudaStream_t stream) {
+    if (n % 4 == 0 && aligned16(values) && aligned16(out))
+        whiten_apply_kernel<4><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, n, sums, shift_mean, out, status);
+    else
+        whiten_apply_kernel<1><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, n, sums, shift_mean, out, status);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_gae(const float* rewards, const float* values, const void* mask, int mask_dtype, int64_t B, int64_t L,
+            float gamma, float lam, float* advantages, float* returns, int32_t* status, void* workspace,
+            size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(rewards && values && mask && advantages && returns && status, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    if (!workspace || workspace_bytes < vpg_gae_workspace_bytes(B, L))
+        return set_error(VPG_ERR_WORKSPACE, "gae workspace too small");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* sums = static_cast<double*>(workspace);
+    VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
+    int64_t threads = round_up(ceil_div(L, kSeg), 32);
+    if (threads > 1024) threads = 1024;
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        gae_kernel<MT><<<static_cast<unsigned>(B), static_cast<unsigned>(threads), 0, stream>>>(
+            rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums);
+    });
+    VPG_LAUNCH_CHECK();
+    return whiten_apply(advantages, B * L, sums, 1, advantages, status, stream);
+}
+
+int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
+                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(values && mask && out && status && n > 0, "invalid masked_whiten arguments");
+    if (!workspace || workspace_bytes < 4 * sizeof(double))
+        return set_error(VPG_ERR_WORKSPACE, "masked_whiten workspace too small");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* sums = static_cast<double*>(workspace);
+    VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
+    const bool vec = rows_vec_ok(n, mask, mask_dtype, {values});
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            whiten_stats_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, mk, n, sums);
+        else
+            whiten_stats_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, mk, n, sums);
+    });
+    VPG_LAUNCH_CHECK();
+    return whiten_apply(values, n, sums, shift_mean, out, status, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,340 @@
+"""Thin tensor-level wrappers over the C ABI (include/vpg_b200.h).
+
+Everything here takes/returns torch CUDA tensors, allocates outputs and workspaces with torch's caching allocator
+and enqueues on the current stream.  No op has a CPU or PyTorch fallback: a non-CUDA input raises.
+The reference-named Python API (verl_b200.utils.*, verl_b200.trainer.*) is built on these.
+"""
+
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _lib
+from ._lib import AGG_MODES, KL_KINDS, check, mask_arg, ptr, stream_ptr
+
+_F32 = torch.float32
+
+
+def _lib_():
+    return _lib.load()
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("verl_b200 ops require CUDA tensors (there is no CPU fallback)")
+
+
+def _f32c(t: torch.Tensor | None) -> torch.Tensor | None:
+    if t is None:
+        return None
+    if t.dtype != _F32:
+        t = t.to(_F32)
+    return t.contiguous()
+
+
+def _ws(nbytes: int, device) -> torch.Tensor:
+    # float64 storage keeps the 8-byte alignment the kernels ask for (torch allocations are 512-byte aligned)
+    return torch.empty((max(int(nbytes), 8) + 7) // 8, dtype=torch.float64, device=device)
+
+
+# --------------------------------------------------------------------------------------------------- lm-head
+def lce_num_splits(T: int, H: int, V: int) -> int:
+    return int(_lib_().vpg_lce_num_splits(T, H, V, 0))
+
+
+def lce_forward_partials(hidden, weight, labels, temperature: float, label_offset: int = 0, num_splits: int = 0):
+    """-> partials [4, S, T] fp32 (see vpg_lce_fwd_partials)."""
+    _require_cuda(hidden, weight, labels)
+    T, H = hidden.shape
+    V = weight.shape[0]
+    S = num_splits or lce_num_splits(T, H, V)
+    part = torch.empty((4, S, T), dtype=_F32, device=hidden.device)
+    with torch.cuda.device(hidden.device):
+        check(_lib_().vpg_lce_fwd_partials(ptr(hidden), ptr(weight), ptr(labels), T, H, V, float(temperature),
+                                           int(label_offset), S, ptr(part), stream_ptr(hidden.device)))
+    return part
+
+
+def lce_finalize(partials, temperature: float):
+    """partials [4, P, T] -> (logprobs, entropy, lse, eb), each fp32 [T]."""
+    _require_cuda(partials)
+    _, P, T = partials.shape
+    out = torch.empty((4, T), dtype=_F32, device=partials.device)
+    with torch.cuda.device(partials.device):
+        check(_lib_().vpg_lce_finalize(ptr(partials), P, T, float(temperature), ptr(out[0]), ptr(out[1]), ptr(out[2]),
+                                       ptr(out[3]), stream_ptr(partials.device)))
+    return out[0], out[1], out[2], out[3]
+
+
+def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int = 0,
+                 chunk_v: int = 0):
+    """-> (d_hidden bf16 [T,H], d_weight bf16 [V,H])."""
+    _require_cuda(hidden, weight, labels, lse, eb)
+    T, H = hidden.shape
+    V = weight.shape[0]
+    lib = _lib_()
+    nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
+    ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
+    d_hidden = torch.empty_like(hidden)
+    d_weight = torch.empty_like(weight)
+    with torch.cuda.device(hidden.device):
+        check(lib.vpg_lce_bwd(ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb), ptr(g_lp), ptr(g_ent), T, H, V,
+                              float(temperature), int(label_offset), int(chunk_v), ptr(d_hidden), ptr(d_weight),
+                              ptr(ws), nbytes, stream_ptr(hidden.device)))
+    return d_hidden, d_weight
+
+
+def gemm_bf16(A, B, a_kmajor=True, b_kmajor=True, out_dtype=torch.bfloat16):
+    """C = op(A) @ op(B)^T on the tcgen05 mainloop.  A: [M,K] (k-major) or [K,M]; B: [N,K] (k-major) or [K,N]."""
+    _require_cuda(A, B)
+    M, K = (A.shape if a_kmajor else A.shape[::-1])
+    N, K2 = (B.shape if b_kmajor else B.shape[::-1])
+    assert K == K2
+    C = torch.empty((M, N), dtype=out_dtype, device=A.device)
+    mode = 0 if out_dtype == torch.bfloat16 else 1
+    with torch.cuda.device(A.device):
+        check(_lib_().vpg_gemm_bf16(ptr(A), ptr(B), M, N, K, A.stride(0), B.stride(0), int(a_kmajor), int(b_kmajor),
+                                    ptr(C), C.stride(0), mode, None, 0, stream_ptr(A.device)))
+    return C
+
+
+# --------------------------------------------------------------------------------------------------- logits
+def logits_stats(logits2d, labels=None, want_logprobs=True, want_entropy=True):
+    """logits [T,V] (fp32 or bf16, last dim contiguous) -> (logprobs|None, entropy|None, lse), fp32 [T]."""
+    _require_cuda(logits2d, labels)
+    if logits2d.dtype not in (torch.float32, torch.bfloat16):
+        logits2d = logits2d.float()
+    if logits2d.stride(-1) != 1:
+        logits2d = logits2d.contiguous()
+    T, V = logits2d.shape
+    dev = logits2d.device
+    lp = torch.empty(T, dtype=_F32, device=dev) if (want_logprobs and labels is not None) else None
+    ent = torch.empty(T, dtype=_F32, device=dev) if want_entropy else None
+    lse = torch.empty(T, dtype=_F32, device=dev)
+    ld = logits2d.stride(0) if T > 1 else V
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_logits_stats(logits2d.data_ptr(), int(logits2d.dtype == torch.bfloat16), T, V, ld,
+                                       ptr(labels) if lp is not None else None, ptr(lp), ptr(ent), ptr(lse),
+                                       stream_ptr(dev)))
+    return lp, ent, lse
+
+
+def logits_stats_backward(logits2d, labels, lse, entropy, g_lp, g_ent):
+    _require_cuda(logits2d)
+    T, V = logits2d.shape
+    assert logits2d.is_contiguous()
+    d = torch.empty_like(logits2d)
+    with torch.cuda.device(logits2d.device):
+        check(_lib_().vpg_logits_stats_bwd(ptr(logits2d), int(logits2d.dtype == torch.bfloat16), T, V, V, ptr(labels),
+                                           ptr(lse), ptr(entropy), ptr(g_lp), ptr(g_ent), ptr(d),
+                                           stream_ptr(logits2d.device)))
+    return d
+
+
+# --------------------------------------------------------------------------------------------------- rmpad
+def unpad_indices(mask2d):
+    """mask [B,S] -> (indices i64 [nnz], seqlens i32 [B], cu_seqlens i32 [B+1], max_seqlen int).
+
+    One device->host read of {nnz, max_seqlen} (the reference syncs here too: nonzero() and .item()).
+    """
+    _require_cuda(mask2d)
+    if mask2d.dtype.is_floating_point:
+        raise TypeError("attention masks must be integer or bool")
+    if mask2d.dtype not in (torch.int64, torch.int32, torch.bool, torch.uint8):
+        mask2d = mask2d.to(torch.int64)
+    mask2d = mask2d.contiguous()
+    m, mdt = mask_arg(mask2d)
+    B, S = mask2d.shape
+    dev = mask2d.device
+    lib = _lib_()
+    n = B * S
+    indices_full = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    seqlens = torch.empty(B, dtype=torch.int32, device=dev)
+    cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    totals = torch.empty(2, dtype=torch.int32, device=dev)
+    nbytes = int(lib.vpg_unpad_workspace_bytes(n))
+    ws = _ws(nbytes, dev)
+    with torch.cuda.device(dev):
+        check(lib.vpg_unpad_indices(ptr(m), mdt, B, S, ptr(indices_full), ptr(seqlens), ptr(cu), ptr(totals), ptr(ws),
+                                    ws.numel() * 8, stream_ptr(dev)))
+    nnz, max_seqlen = totals.tolist()
+    return indices_full[:nnz], seqlens, cu, int(max_seqlen)
+
+
+def gather_rows(src, indices):
+    """src [N, ...] contiguous, indices i64 [n] -> [n, ...]  (index_first_axis)."""
+    _require_cuda(src, indices)
+    src = src.contiguous()
+    row_shape = src.shape[1:]
+    row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
+    out = torch.empty((indices.numel(), *row_shape), dtype=src.dtype, device=src.device)
+    if indices.numel() and row_bytes:
+        with torch.cuda.device(src.device):
+            check(_lib_().vpg_gather_rows(ptr(src), ptr(indices.contiguous()), indices.numel(), row_bytes, ptr(out),
+                                          stream_ptr(src.device)))
+    return out
+
+
+def scatter_rows(src, indices, n_out: int):
+    """zeros [n_out, ...] with out[indices[i]] = src[i]  (pad_input / index_put_first_axis)."""
+    _require_cuda(src, indices)
+    src = src.contiguous()
+    row_shape = src.shape[1:]
+    row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
+    out = torch.empty((n_out, *row_shape), dtype=src.dtype, device=src.device)
+    if n_out and row_bytes:
+        with torch.cuda.device(src.device):
+            check(_lib_().vpg_scatter_rows(ptr(src), ptr(indices.contiguous()), indices.numel(), row_bytes, ptr(out),
+                                           n_out, 1, stream_ptr(src.device)))
+    return out
+
+
+# --------------------------------------------------------------------------------------------------- token ops
+def masked_sums(values, mask):
+    """-> float64 [2] = {sum(where(m,v,0)*m), sum(m)} over all elements."""
+    _require_cuda(values, mask)
+    v = _f32c(values)
+    m, mdt = mask_arg(mask.contiguous())
+    out = torch.empty(2, dtype=torch.float64, device=v.device)
+    with torch.cuda.device(v.device):
+        check(_lib_().vpg_masked_sum(ptr(v), ptr(m), mdt, v.numel(), ptr(out), stream_ptr(v.device)))
+    return out
+
+
+def masked_row_sums(values, mask):
+    """last-axis sums: -> (sum fp32 [rows], count fp32 [rows])."""
+    _require_cuda(values, mask)
+    v = _f32c(values)
+    m, mdt = mask_arg(mask.contiguous())
+    L = v.shape[-1]
+    rows = v.numel() // max(L, 1)
+    s = torch.empty(rows, dtype=_F32, device=v.device)
+    c = torch.empty(rows, dtype=_F32, device=v.device)
+    with torch.cuda.device(v.device):
+        check(_lib_().vpg_masked_row_sum(ptr(v), ptr(m), mdt, rows, L, ptr(s), ptr(c), stream_ptr(v.device)))
+    return s, c
+
+
+def kl_penalty_fwd(logprob, ref_logprob, kind: str, want_grad: bool):
+    if kind == "full" or kind not in KL_KINDS:
+        raise NotImplementedError  # verl/trainer/ppo/core_algos.py:1065-1069
+    _require_cuda(logprob, ref_logprob)
+    a, b = _f32c(logprob), _f32c(ref_logprob)
+    out = torch.empty_like(a)
+    g = torch.empty_like(a) if want_grad else None
+    with torch.cuda.device(a.device):
+        check(_lib_().vpg_kl_penalty(ptr(a), ptr(b), KL_KINDS[kind], a.numel(), ptr(out), ptr(g), stream_ptr(a.device)))
+    return out, g
+
+
+def _as_2d(t):
+    return t.reshape(-1, t.shape[-1]) if t.dim() != 2 else t
+
+
+def ppo_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low, cliprange_high, clip_ratio_c=3.0,
+             loss_agg_mode="token-mean", entropy=None, entropy_coeff=0.0, ref_log_prob=None, kl_loss_coef=0.0,
+             kl_loss_type="low_var_kl", loss_scale=1.0, want_grad=True):
+    """Fused actor loss forward + closed-form gradient (vpg_ppo_loss).
+
+    -> (metrics fp32 [8], d_log_prob | None, d_entropy | None)
+    metrics = [loss*scale, pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower, entropy_agg, kl_agg, mask_sum]
+    """
+    _require_cuda(old_log_prob, log_prob, advantages, response_mask)
+    if loss_agg_mode not in AGG_MODES:
+        raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+    assert clip_ratio_c > 1.0, (
+        "The lower bound of the clip_ratio_c for dual-clip PPO should be greater than 1.0,"
+        + f" but get the value: {clip_ratio_c}."
+    )
+    if ref_log_prob is not None and (kl_loss_type == "full" or kl_loss_type not in KL_KINDS):
+        raise NotImplementedError
+    old, lp, adv = _f32c(_as_2d(old_log_prob)), _f32c(_as_2d(log_prob)), _f32c(_as_2d(advantages))
+    m, mdt = mask_arg(_as_2d(response_mask).contiguous())
+    ent = _f32c(_as_2d(entropy)) if entropy is not None else None
+    ref = _f32c(_as_2d(ref_log_prob)) if ref_log_prob is not None else None
+    B, L = lp.shape
+    dev = lp.device
+    lib = _lib_()
+    metrics = torch.empty(8, dtype=_F32, device=dev)
+    d_lp = torch.empty_like(lp) if want_grad else None
+    d_ent = torch.empty_like(lp) if (want_grad and ent is not None) else None
+    ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), dev)
+    with torch.cuda.device(dev):
+        check(lib.vpg_ppo_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, ptr(ent), ptr(ref), B, L,
+                               float(1 - cliprange_low), float(1 + cliprange_high), float(clip_ratio_c),
+                               AGG_MODES[loss_agg_mode], float(entropy_coeff), float(kl_loss_coef),
+                               KL_KINDS.get(kl_loss_type, -1) if ref is not None else -1, float(loss_scale),
+                               ptr(metrics), ptr(d_lp), ptr(d_ent), ptr(ws), ws.numel() * 8, stream_ptr(dev)))
+    return metrics, d_lp, d_ent
+
+
+def agg_loss_fwd(loss_mat, loss_mask, loss_agg_mode: str, want_grad: bool):
+    if loss_agg_mode not in AGG_MODES:
+        raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+    _require_cuda(loss_mat, loss_mask)
+    v = _f32c(_as_2d(loss_mat))
+    m, mdt = mask_arg(_as_2d(loss_mask).contiguous())
+    B, L = v.shape
+    lib = _lib_()
+    out = torch.empty(1, dtype=_F32, device=v.device)
+    d = torch.empty_like(v) if want_grad else None
+    ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), v.device)
+    with torch.cuda.device(v.device):
+        check(lib.vpg_agg_loss(ptr(v), ptr(m), mdt, B, L, AGG_MODES[loss_agg_mode], ptr(out), ptr(d), ptr(ws),
+                               ws.numel() * 8, stream_ptr(v.device)))
+    return out[0], d
+
+
+def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: int, epsilon: float, norm_by_std: bool):
+    _require_cuda(token_level_rewards, response_mask, group_ids)
+    r = _f32c(token_level_rewards)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = r.shape
+    lib = _lib_()
+    adv = torch.empty_like(r)
+    ws = _ws(int(lib.vpg_grpo_workspace_bytes(B, num_groups)), r.device)
+    with torch.cuda.device(r.device):
+        check(lib.vpg_grpo_advantage(ptr(r), ptr(m), mdt, ptr(group_ids), B, L, int(num_groups), float(epsilon),
+                                     int(bool(norm_by_std)), ptr(adv), ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
+    return adv
+
+
+def _raise_whiten_status(status: torch.Tensor):
+    code = int(status.item())
+    if code == 1:
+        raise ValueError("At least one element in the mask has to be 1.")
+    if code == 2:
+        raise ValueError("The sum of the mask is one, which can cause a division by zero.")
+
+
+def gae(token_level_rewards, values, response_mask, gamma: float, lam: float):
+    _require_cuda(token_level_rewards, values, response_mask)
+    r, v = _f32c(token_level_rewards), _f32c(values)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = r.shape
+    lib = _lib_()
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    status = torch.zeros(1, dtype=torch.int32, device=r.device)
+    ws = _ws(int(lib.vpg_gae_workspace_bytes(B, L)), r.device)
+    with torch.cuda.device(r.device):
+        check(lib.vpg_gae(ptr(r), ptr(v), ptr(m), mdt, B, L, float(gamma), float(lam), ptr(adv), ptr(ret), ptr(status),
+                          ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
+    _raise_whiten_status(status)
+    return adv, ret
+
+
+def masked_whiten(values, mask, shift_mean=True):
+    _require_cuda(values, mask)
+    v = _f32c(values)
+    m, mdt = mask_arg(mask.contiguous())
+    out = torch.empty_like(v)
+    status = torch.zeros(1, dtype=torch.int32, device=v.device)
+    ws = _ws(32, v.device)
+    with torch.cuda.device(v.device):
+        check(_lib_().vpg_masked_whiten(ptr(v), ptr(m), mdt, v.numel(), int(bool(shift_mean)), ptr(out), ptr(status),
+                                        ptr(ws), ws.numel() * 8, stream_ptr(v.device)))
+    _raise_whiten_status(status)
+    return out

@@ -1,0 +1,363 @@
+"""Token-level RL math of verl/trainer/ppo/core_algos.py on libvpg_b200, same names and signatures.
+
+Hot-path functions (CUDA kernels, no torch fallback):
+  compute_gae_advantage_return   core_algos.py:193-241
+  compute_grpo_outcome_advantage core_algos.py:245-308
+  agg_loss                       core_algos.py:686-719
+  compute_policy_loss            core_algos.py:722-794
+  kl_penalty                     core_algos.py:1034-1069
+  compute_rewards                core_algos.py:~670-684 (elementwise, built on kl_penalty's k1 kernel)
+plus fused_actor_loss(): compute_policy_loss + entropy bonus + KL loss + agg_loss + loss scale in one launch pair,
+the composition verl/workers/actor/dp_actor.py:422-469 performs with ~60 torch kernels.
+
+Host-side API kept for drop-in use: the policy-loss / advantage-estimator registries (:33-108), the
+AdvantageEstimator enum (:111-128) and the KL controllers (:131-190).
+"""
+
+from __future__ import annotations
+
+from enum import Enum
+from typing import Any, Optional
+
+import numpy as np
+import torch
+
+from ... import ops
+
+__all__ = [
+    "register_policy_loss",
+    "get_policy_loss_fn",
+    "register_adv_est",
+    "get_adv_estimator_fn",
+    "AdvantageEstimator",
+    "AdaptiveKLController",
+    "FixedKLController",
+    "get_kl_controller",
+    "compute_gae_advantage_return",
+    "compute_grpo_outcome_advantage",
+    "compute_rewards",
+    "agg_loss",
+    "compute_policy_loss",
+    "kl_penalty",
+    "fused_actor_loss",
+    "group_ids_from_index",
+]
+
+# ------------------------------------------------------------------------------------------------ registries
+POLICY_LOSS_REGISTRY: dict[str, Any] = {}
+ADV_ESTIMATOR_REGISTRY: dict[str, Any] = {}
+
+
+def register_policy_loss(name):
+    """Decorator: make ``fn`` retrievable as policy loss ``name`` (core_algos.py:36-50)."""
+
+    def _wrap(fn):
+        POLICY_LOSS_REGISTRY[name] = fn
+        return fn
+
+    return _wrap
+
+
+def get_policy_loss_fn(name):
+    """Look a registered policy loss up by name (core_algos.py:53-68)."""
+    if name not in POLICY_LOSS_REGISTRY:
+        raise ValueError(f"Unsupported loss mode: {name}. Supported modes are: {list(POLICY_LOSS_REGISTRY.keys())}")
+    return POLICY_LOSS_REGISTRY[name]
+
+
+def _est_key(name_or_enum):
+    return name_or_enum.value if isinstance(name_or_enum, Enum) else name_or_enum
+
+
+def register_adv_est(name_or_enum):
+    """Decorator registering an advantage estimator; re-registering a different fn under a taken name is an error
+    (core_algos.py:74-91)."""
+
+    def _wrap(fn):
+        key = _est_key(name_or_enum)
+        prev = ADV_ESTIMATOR_REGISTRY.get(key)
+        if prev is not None and prev != fn:
+            raise ValueError(f"Adv estimator {key} has already been registered: {prev} vs {fn}")
+        ADV_ESTIMATOR_REGISTRY[key] = fn
+        return fn
+
+    return _wrap
+
+
+def get_adv_estimator_fn(name_or_enum):
+    """core_algos.py:94-108"""
+    key = _est_key(name_or_enum)
+    if key not in ADV_ESTIMATOR_REGISTRY:
+        raise ValueError(f"Unknown advantage estimator simply: {key}")
+    return ADV_ESTIMATOR_REGISTRY[key]
+
+
+class AdvantageEstimator(str, Enum):
+    """Names of the reference's estimators (core_algos.py:111-128); only GAE and GRPO have kernels in this build."""
+
+    GAE = "gae"
+    GRPO = "grpo"
+    REINFORCE_PLUS_PLUS = "reinforce_plus_plus"
+    REINFORCE_PLUS_PLUS_BASELINE = "reinforce_plus_plus_baseline"
+    REMAX = "remax"
+    RLOO = "rloo"
+    OPO = "opo"
+    GRPO_PASSK = "grpo_passk"
+    GPG = "gpg"
+
+
+# ------------------------------------------------------------------------------------------------ KL controllers
+class AdaptiveKLController:
+    """Adaptive KL coefficient, https://arxiv.org/pdf/1909.08593.pdf (core_algos.py:131-152)."""
+
+    def __init__(self, init_kl_coef, target_kl, horizon):
+        self.value = init_kl_coef
+        self.target = target_kl
+        self.horizon = horizon
+
+    def update(self, current_kl, n_steps):
+        err = np.clip(current_kl / self.target - 1, -0.2, 0.2)
+        self.value *= 1 + err * n_steps / self.horizon
+
+
+class FixedKLController:
+    """Constant KL coefficient (core_algos.py:155-168)."""
+
+    def __init__(self, kl_coef):
+        self.value = kl_coef
+
+    def update(self, current_kl, n_steps):
+        pass
+
+
+def get_kl_controller(kl_ctrl):
+    """core_algos.py:171-190"""
+    if kl_ctrl.type == "fixed":
+        return FixedKLController(kl_coef=kl_ctrl.kl_coef)
+    if kl_ctrl.type == "adaptive":
+        assert kl_ctrl.horizon > 0, f"horizon must be larger than 0. Got {kl_ctrl.horizon}"
+        return AdaptiveKLController(init_kl_coef=kl_ctrl.kl_coef, target_kl=kl_ctrl.target_kl, horizon=kl_ctrl.horizon)
+    raise NotImplementedError
+
+
+# ------------------------------------------------------------------------------------------------ advantages
+def group_ids_from_index(index) -> tuple[np.ndarray, int]:
+    """uid array (numpy object array of strings, list, or tensor) -> (int32 ids in first-seen order, num_groups).
+
+    This is the host half of GRPO's "group assignment": the reference groups by dictionary key
+    (``id2score[index[i]]``, core_algos.py:286-291); insertion order of that dict is first-seen order.
+    """
+    if isinstance(index, torch.Tensor):
+        index = index.detach().cpu().numpy()
+    table: dict[Any, int] = {}
+    out = np.empty(len(index), dtype=np.int32)
+    for i, key in enumerate(index):
+        if isinstance(key, np.generic):
+            key = key.item()
+        gid = table.get(key)
+        if gid is None:
+            gid = len(table)
+            table[key] = gid
+        out[i] = gid
+    return out, len(table)
+
+
+@register_adv_est(AdvantageEstimator.GAE)
+def compute_gae_advantage_return(
+    token_level_rewards: torch.Tensor,
+    values: torch.Tensor,
+    response_mask: torch.Tensor,
+    gamma: torch.Tensor,
+    lam: torch.Tensor,
+):
+    """GAE advantages and returns, then masked whitening of the advantages (core_algos.py:193-241).
+
+    One kernel evaluates the reverse recurrence of every row as a block-parallel scan of affine maps, a second one
+    normalises.  Returns (advantages, returns), both (bs, response_length) fp32.
+    """
+    with torch.no_grad():
+        advantages, returns = ops.gae(token_level_rewards, values, response_mask, float(gamma), float(lam))
+    return advantages, returns
+
+
+@register_adv_est(AdvantageEstimator.GRPO)
+def compute_grpo_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: np.ndarray,
+    epsilon: float = 1e-6,
+    norm_adv_by_std_in_grpo: bool = True,
+    config: Optional[Any] = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """GRPO outcome advantage (core_algos.py:245-308): per-uid group mean / unbiased std of the sequence scores,
+    singleton groups use (0, 1); the SAME tensor is returned twice, as the reference does (:308)."""
+    gids, n_groups = group_ids_from_index(index)
+    with torch.no_grad():
+        gid_dev = torch.from_numpy(gids).to(token_level_rewards.device, non_blocking=True)
+        scores = ops.grpo_advantage(
+            token_level_rewards, response_mask, gid_dev, n_groups, float(epsilon), bool(norm_adv_by_std_in_grpo)
+        )
+    return scores, scores
+
+
+def compute_rewards(token_level_scores, old_log_prob, ref_log_prob, kl_ratio):
+    """token_level_scores - (old_log_prob - ref_log_prob) * kl_ratio (core_algos.py:670-684)."""
+    kl, _ = ops.kl_penalty_fwd(old_log_prob, ref_log_prob, "kl", want_grad=False)
+    return token_level_scores - kl * kl_ratio
+
+
+# ------------------------------------------------------------------------------------------------ losses
+class _AggLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, loss_mat, loss_mask, mode):
+        out, d = ops.agg_loss_fwd(loss_mat, loss_mask, mode, want_grad=loss_mat.requires_grad)
+        ctx.shape, ctx.in_dtype = loss_mat.shape, loss_mat.dtype
+        if d is not None:
+            ctx.save_for_backward(d)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        return (d * g).view(ctx.shape).to(ctx.in_dtype), None, None
+
+
+def agg_loss(loss_mat: torch.Tensor, loss_mask: torch.Tensor, loss_agg_mode: str):
+    """Aggregate a (bs, response_length) loss matrix into a scalar (core_algos.py:686-719).
+
+    Modes: token-mean, seq-mean-token-sum, seq-mean-token-mean, seq-mean-token-sum-norm; anything else raises
+    ValueError like the reference.
+    """
+    if loss_agg_mode not in ops.AGG_MODES:
+        raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+    return _AggLoss.apply(loss_mat, loss_mask, loss_agg_mode)
+
+
+class _KlPenalty(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logprob, ref_logprob, kind):
+        need = logprob.requires_grad or ref_logprob.requires_grad
+        out, g = ops.kl_penalty_fwd(logprob, ref_logprob, kind, want_grad=need)
+        ctx.dt = (logprob.dtype, ref_logprob.dtype)
+        ctx.need = (logprob.requires_grad, ref_logprob.requires_grad)
+        if need:
+            ctx.save_for_backward(g)
+        return out.view(logprob.shape)
+
+    @staticmethod
+    def backward(ctx, go):
+        (g,) = ctx.saved_tensors
+        d = go.reshape(g.shape) * g  # d out / d logprob; every kind is antisymmetric in (logprob, ref_logprob)
+        d_lp = d.view(go.shape).to(ctx.dt[0]) if ctx.need[0] else None
+        d_ref = (-d).view(go.shape).to(ctx.dt[1]) if ctx.need[1] else None
+        return d_lp, d_ref, None
+
+
+def kl_penalty(logprob: torch.FloatTensor, ref_logprob: torch.FloatTensor, kl_penalty) -> torch.FloatTensor:
+    """kl / k1, abs, mse / k2, low_var_kl / k3 (core_algos.py:1034-1069); "full" and unknown kinds raise
+    NotImplementedError like the reference."""
+    if kl_penalty == "full" or kl_penalty not in ops.KL_KINDS:
+        raise NotImplementedError
+    return _KlPenalty.apply(logprob, ref_logprob, kl_penalty)
+
+
+class _PolicyLoss(torch.autograd.Function):
+    """Forward = fused kernel, backward = the closed-form d loss / d log_prob the same launch produced."""
+
+    @staticmethod
+    def forward(ctx, log_prob, old_log_prob, advantages, response_mask, entropy, ref_log_prob, cfg):
+        need = log_prob.requires_grad or (entropy is not None and entropy.requires_grad)
+        metrics, d_lp, d_ent = ops.ppo_loss(
+            old_log_prob, log_prob, advantages, response_mask, entropy=entropy, ref_log_prob=ref_log_prob,
+            want_grad=need, **cfg,
+        )
+        ctx.lp_meta = (log_prob.shape, log_prob.dtype, log_prob.requires_grad)
+        ctx.ent_meta = None if entropy is None else (entropy.shape, entropy.dtype, entropy.requires_grad)
+        saved = [t for t in (d_lp, d_ent) if t is not None]
+        ctx.has = (d_lp is not None, d_ent is not None)
+        ctx.save_for_backward(*saved)
+        loss = metrics[0].clone()
+        stats = metrics
+        ctx.mark_non_differentiable(stats)
+        return loss, stats
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_stats):
+        saved = list(ctx.saved_tensors)
+        d_lp = saved.pop(0) if ctx.has[0] else None
+        d_ent = saved.pop(0) if ctx.has[1] else None
+        g_lp = None
+        if d_lp is not None and ctx.lp_meta[2]:
+            g_lp = (d_lp * g_loss).view(ctx.lp_meta[0]).to(ctx.lp_meta[1])
+        g_ent = None
+        if d_ent is not None and ctx.ent_meta is not None and ctx.ent_meta[2]:
+            g_ent = (d_ent * g_loss).view(ctx.ent_meta[0]).to(ctx.ent_meta[1])
+        return g_lp, None, None, None, g_ent, None, None
+
+
+def compute_policy_loss(
+    old_log_prob,
+    log_prob,
+    advantages,
+    response_mask,
+    cliprange=None,
+    cliprange_low=None,
+    cliprange_high=None,
+    clip_ratio_c=3.0,
+    loss_agg_mode: str = "token-mean",
+):
+    """Clipped PPO objective with dual-clip (core_algos.py:722-794).
+
+    Returns (pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower) as 0-dim fp32 tensors; pg_loss carries the gradient
+    wrt log_prob (the three statistics are detached — nothing in verl differentiates them).
+    """
+    assert clip_ratio_c > 1.0, (
+        "The lower bound of the clip_ratio_c for dual-clip PPO should be greater than 1.0,"
+        + f" but get the value: {clip_ratio_c}."
+    )
+    if cliprange_low is None:
+        cliprange_low = cliprange
+    if cliprange_high is None:
+        cliprange_high = cliprange
+    cfg = dict(cliprange_low=cliprange_low, cliprange_high=cliprange_high, clip_ratio_c=clip_ratio_c,
+               loss_agg_mode=loss_agg_mode)
+    loss, stats = _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, None, None, cfg)
+    return loss, stats[2], stats[3], stats[4]
+
+
+def fused_actor_loss(
+    old_log_prob,
+    log_prob,
+    advantages,
+    response_mask,
+    *,
+    cliprange=0.2,
+    cliprange_low=None,
+    cliprange_high=None,
+    clip_ratio_c=3.0,
+    loss_agg_mode: str = "token-mean",
+    entropy=None,
+    entropy_coeff: float = 0.0,
+    ref_log_prob=None,
+    kl_loss_coef: float = 0.0,
+    kl_loss_type: str = "low_var_kl",
+    loss_scale: float = 1.0,
+):
+    """Whole actor-loss composition of dp_actor.py:422-469 in one fused pass:
+
+        loss = loss_scale * ( pg_loss - entropy_coeff * agg(entropy) + kl_loss_coef * agg(kl_penalty(lp, ref)) )
+
+    Returns (loss, metrics) where ``loss`` is differentiable wrt log_prob and entropy and ``metrics`` is ONE detached
+    fp32[8] device tensor [loss, pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower, entropy_loss, kl_loss, mask_sum]
+    (a single .tolist() replaces the reference's four .item() syncs, dp_actor.py:472-479).
+    """
+    if cliprange_low is None:
+        cliprange_low = cliprange
+    if cliprange_high is None:
+        cliprange_high = cliprange
+    use_ent = entropy is not None and entropy_coeff != 0
+    cfg = dict(cliprange_low=cliprange_low, cliprange_high=cliprange_high, clip_ratio_c=clip_ratio_c,
+               loss_agg_mode=loss_agg_mode, entropy_coeff=entropy_coeff if use_ent else 0.0,
+               kl_loss_coef=kl_loss_coef, kl_loss_type=kl_loss_type, loss_scale=loss_scale)
+    return _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, entropy if use_ent else None,
+                             ref_log_prob, cfg)

@@ -1,0 +1,186 @@
+"""Host side of the fused lm-head op — mirror of verl/utils/kernel/kernels.py (enums :46-117, host functions
+efficient_entropy_forward :474-663 and efficient_entropy_backward :1345-1553), backed by libvpg_b200's tcgen05
+kernels instead of Triton.
+
+Differences a maintainer should know (all outputs match the reference within its own test tolerances):
+* the three saved per-token tensors are (lse, 1, eb) in the reference's (maximum, accumulate, entropy_b) slots:
+  the reference identity ``logprob = target - maximum - log(accumulate)`` holds with maximum=lse, accumulate=1;
+* vocab-parallel runs exchange ONE all-gather of the packed [4,S,T] partials instead of the reference's three
+  dependent all-reduces (kernels.py:612,617,644);
+* ``BackwardEnum`` values are accepted by ``set_backward_method`` for API compatibility; the backward always uses
+  the split-along-vocab strategy (the reference default, ``_Split_Dlogits_N``) on tcgen05 GEMMs.
+"""
+
+from __future__ import annotations
+
+import typing
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+from ... import ops
+
+
+@dataclass
+class EntropyReductionEnum:
+    """Enum for the reduction method of cross entropy (verl/utils/kernel/kernels.py:46-54)."""
+
+    _None = 0
+    _Sum = 1
+    _Mean = 2
+
+
+def get_entropy_reduction_enum_number(reduction: str) -> int:
+    """verl/utils/kernel/kernels.py:57-70"""
+    if reduction == "none":
+        return EntropyReductionEnum._None
+    if reduction == "sum":
+        return EntropyReductionEnum._Sum
+    if reduction == "mean":
+        return EntropyReductionEnum._Mean
+    raise ValueError(f"Invalid reduction: {reduction}")
+
+
+def get_entropy_reduction_enum(ce_reduction: int) -> int:
+    """verl/utils/kernel/kernels.py:73-87"""
+    if ce_reduction in (0, 1, 2):
+        return ce_reduction
+    raise ValueError(f"Invalid ce_reduction: {ce_reduction}")
+
+
+@dataclass
+class BackwardEnum:
+    """verl/utils/kernel/kernels.py:90-101"""
+
+    _Total_Fuse_MN = 0
+    _Total_Separate = 1
+    _Split_Dlogits_N = 2
+    _Split_Dlogits_M = 3
+
+
+@dataclass
+class Config:
+    _backward: int = BackwardEnum._Split_Dlogits_N
+    _use_triton: bool = False  # there is no Triton in this build
+    _chunk_v: int = 0  # 0 = library default (vpg_lce_bwd_default_chunk)
+
+
+_config = Config()
+
+
+def set_backward_method(backward_method: int):
+    """verl/utils/kernel/kernels.py:112-117.  Recorded only; see the module docstring."""
+    global _config
+    _config._backward = backward_method
+
+
+def set_backward_chunk(chunk_v: int):
+    """Vocab columns of dlogits materialised at a time in the backward (multiple of 256; 0 = default)."""
+    global _config
+    _config._chunk_v = int(chunk_v)
+
+
+def _check_inputs(hidden, weight, labels):
+    # same preconditions as verl/utils/kernel/kernels.py:485-490,504
+    assert hidden.is_cuda and weight.is_cuda and labels.is_cuda
+    assert weight.device == hidden.device and labels.device == hidden.device
+    assert hidden.dim() == 2 and weight.dim() == 2 and labels.dim() == 1
+    assert hidden.is_contiguous() and weight.is_contiguous() and labels.is_contiguous()
+    assert hidden.shape[0] == labels.shape[0] and hidden.shape[1] == weight.shape[1]
+    assert hidden.shape[1] % 128 == 0
+    assert hidden.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16, "the sm_100a kernels take bf16 operands"
+    assert labels.dtype == torch.int64
+
+
+def exchange_partials(partials: torch.Tensor, group) -> torch.Tensor:
+    """Vocab-parallel exchange: ONE all-gather of the packed per-token partials {m, s, b, t} ([4,S,T] per rank)
+    -> [4, world*S, T].  The merge done by vpg_lce_finalize is associative and commutative, so rank order is free.
+    Replaces the reference's all_reduce(MAX) + all_reduce(SUM) + all_reduce(SUM) (kernels.py:612,617,644)."""
+    world = dist.get_world_size(group)
+    four, S, T = partials.shape
+    gathered = torch.empty((world * four, S, T), dtype=partials.dtype, device=partials.device)
+    dist.all_gather_into_tensor(gathered, partials.contiguous(), group=group)
+    return gathered.view(world, four, S, T).permute(1, 0, 2, 3).reshape(four, world * S, T).contiguous()
+
+
+def efficient_entropy_forward(
+    hidden: torch.Tensor,
+    weight: torch.Tensor,
+    labels: torch.Tensor,
+    reduction: typing.Optional[int] = 2,
+    temperature: typing.Optional[float] = 1.0,
+    dist_process_group: typing.Optional[dist.ProcessGroup] = None,
+) -> list[torch.Tensor]:
+    """forward host function — verl/utils/kernel/kernels.py:474-663.
+
+    Returns (logprobs, entropy, maximum, accumulate, entropy_b) like the reference.
+    """
+    _check_inputs(hidden, weight, labels)
+    REDUCTION = get_entropy_reduction_enum(reduction)
+    rank = 0 if dist_process_group is None else dist.get_rank(dist_process_group)
+    world = 1 if dist_process_group is None else dist.get_world_size(dist_process_group)
+    vocab_local = weight.shape[0]
+
+    partials = ops.lce_forward_partials(hidden, weight, labels, temperature, label_offset=rank * vocab_local)
+    if world > 1:
+        partials = exchange_partials(partials, dist_process_group)
+    logprobs, entropy, lse, eb = ops.lce_finalize(partials, temperature)
+
+    if REDUCTION == EntropyReductionEnum._Sum:
+        logprobs = logprobs.sum()
+    elif REDUCTION == EntropyReductionEnum._Mean:
+        logprobs = logprobs.sum() / logprobs.numel()
+    accumulate = torch.ones_like(lse)
+    return (logprobs, entropy, lse, accumulate, eb)
+
+
+def efficient_entropy_backward(
+    dlogprobs: torch.Tensor,
+    dentropy: torch.Tensor,
+    hidden: torch.Tensor,
+    weight: torch.Tensor,
+    labels: torch.Tensor,
+    maximum: torch.Tensor,
+    acc: torch.Tensor,
+    entropy_b: torch.Tensor,
+    reduction: typing.Optional[int] = 2,
+    should_return_fp32_grad: bool = False,
+    temperature: typing.Optional[float] = 1.0,
+    dist_process_group: typing.Optional[dist.ProcessGroup] = None,
+) -> list[torch.Tensor]:
+    """backward host function — verl/utils/kernel/kernels.py:1345-1553.
+
+    d_hidden is NOT all-reduced across a vocab-parallel group, exactly like the reference (its callers do it:
+    tests/utils/test_linear_cross_entropy_tp.py:313-314).
+    """
+    _check_inputs(hidden, weight, labels)
+    REDUCTION = get_entropy_reduction_enum(reduction)
+    num_tokens = hidden.shape[0]
+    rank = 0 if dist_process_group is None else dist.get_rank(dist_process_group)
+
+    g_lp = None
+    if dlogprobs is not None:
+        if REDUCTION == EntropyReductionEnum._None:
+            assert dlogprobs.shape == (num_tokens,)
+            g_lp = dlogprobs.to(torch.float32).contiguous()
+        else:
+            assert dlogprobs.dim() == 0
+            g = dlogprobs.to(torch.float32)
+            if REDUCTION == EntropyReductionEnum._Mean:
+                g = g / num_tokens
+            g_lp = g.expand(num_tokens).contiguous()
+    g_ent = None
+    if dentropy is not None:
+        assert dentropy.shape == (num_tokens,)
+        g_ent = dentropy.to(torch.float32).contiguous()
+
+    # maximum + log(acc) is the log-sum-exp for both this module's and the reference's saved triple
+    lse = maximum if acc is None else maximum + torch.log(acc)
+    d_hidden, d_weight = ops.lce_backward(
+        hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
+        label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v,
+    )
+    if should_return_fp32_grad:
+        d_hidden, d_weight = d_hidden.float(), d_weight.float()
+    return d_hidden, d_weight
