@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""Benchmark of the per-token policy-gradient hot path (BASELINE.json metric: fused lm-head logprob+entropy tokens/s
+at Qwen2.5-7B shape, 1-8 B200).
+
+One "step" = one pass of the hot path over one rmpad micro-batch of synthetic hidden states:
+    fused lm-head forward (log-prob + entropy, logits never materialised)
+    -> fused PPO actor loss (clip / dual-clip, entropy bonus, low-var KL, token-mean) forward + closed-form gradient
+    -> fused lm-head backward (recompute tiles -> d_hidden, d_weight)
+through the public API (linear_cross_entropy autograd op + core_algos.fused_actor_loss).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--tokens T]
+
+N = 1: BASELINE configs[1] (H=3584, V=152064, T=65536 rmpad tokens).  N > 1 (torchrun): the same micro-batch with the
+lm-head weight vocab-parallel over N ranks (V/N rows each), one all-gather of the packed per-token partials in the
+forward and one all-reduce of d_hidden in the backward -> strong scaling.
+--impl reference: the reference algorithm's CPU path (oracle port, all host threads) on a bounded token sample.
+Prints ONE JSON line on rank 0.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HIDDEN, VOCAB, TOKENS = 3584, 152064, 65536  # Qwen2.5-7B lm-head, rmpad 64k tokens (BASELINE.json configs[1])
+METRIC = "fused lm-head logprob+entropy fwd+bwd tokens/s (Qwen2.5-7B shape)"
+LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0, loss_agg_mode="token-mean",
+                entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(burst=float(p["bf16_tflops"]), sustained=float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                    hbm=float(p["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+    except Exception:
+        return dict(burst=1590.0, sustained=1400.0, hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs"""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower() == "active"})
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+# ----------------------------------------------------------------------------------------------- CPU reference arm
+def cpu_reference_sample(sample_tokens: int, threads: int, repeats: int = 1):
+    """The reference algorithm on the host cores: chunked (512) lm-head log-prob/entropy forward + hand-written
+    backward (verl/utils/experimental/torch_functional.py:20-72) and the actor loss composition
+    (verl/trainer/ppo/core_algos.py + dp_actor.py:422-469), via the oracle port.  Returns tokens/s."""
+    import torch
+
+    from oracle import port
+
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(233376)
+    hidden = (torch.rand(sample_tokens, HIDDEN, generator=g) - 0.5).bfloat16()
+    weight = (torch.rand(VOCAB, HIDDEN, generator=g) - 0.5).bfloat16()
+    labels = torch.randint(0, VOCAB, (sample_tokens,), generator=g)
+    old = -torch.rand(1, sample_tokens, generator=g) * 3
+    adv = torch.randn(1, sample_tokens, generator=g)
+    mask = torch.ones(1, sample_tokens, dtype=torch.long)
+    best = float("inf")
+    w32 = weight.float()  # the parameter cast is not part of a step
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        lp, ent = port.lce_forward(hidden, w32, labels, 1.0)
+        lp_ = lp.view(1, -1).clone().requires_grad_(True)
+        ent_ = ent.view(1, -1).clone().requires_grad_(True)
+        loss, _ = port.actor_loss(old, lp_, adv, mask, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0,
+                                  entropy=ent_, entropy_coeff=1e-3, ref_log_prob=old, kl_loss_coef=0.01)
+        loss.backward()
+        port.lce_backward(hidden, w32, labels, lp_.grad.view(-1), ent_.grad.view(-1), 1.0)
+        best = min(best, time.perf_counter() - t0)
+    return sample_tokens / best, best
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = args.cpu_tokens
+    times = []
+    for i in range(args.warmup + args.steps):
+        tps, dt = cpu_reference_sample(sample, threads)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    value = sample / (ms * 1e-3)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32 (bf16 inputs upcast, CPU)", "data": "synthetic",
+        "config": {"workload": f"Qwen2.5-7B lm-head H={HIDDEN} V={VOCAB}, fused logprob+entropy fwd+bwd + PPO loss; "
+                               f"reference CPU path on a {sample}-token sample per step"},
+        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": "port",
+                         "sample": f"{sample} tokens per step at full H and V (tokens/s is linear in T)"},
+        "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from verl_b200 import _lib
+    from verl_b200.trainer.ppo import core_algos
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: verl_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    group = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    _lib.load()
+
+    T, H, V = args.tokens, HIDDEN, VOCAB
+    assert V % world == 0
+    v_local = V // world
+    gen = torch.Generator(device=dev).manual_seed(233376)  # same on all ranks: hidden / labels are replicated
+    # ---- synthetic inputs: pinned host copies for the end-to-end leg, device copies for `value`
+    hidden_d = (torch.rand(T, H, device=dev, generator=gen) - 0.5).bfloat16()
+    labels_d = torch.randint(0, V, (T,), device=dev, generator=gen)
+    old_d = -torch.rand(1, T, device=dev, generator=gen) * 3
+    ref_d = old_d + 0.05 * torch.randn(1, T, device=dev, generator=gen)
+    adv_d = torch.randn(1, T, device=dev, generator=gen)
+    mask_d = (torch.rand(1, T, device=dev, generator=gen) < 0.9).long()
+    wgen = torch.Generator(device=dev).manual_seed(1000 + rank)
+    weight = (torch.rand(v_local, H, device=dev, generator=wgen) - 0.5).bfloat16().requires_grad_(True)
+    host = {k: v.cpu().pin_memory() for k, v in dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d,
+                                                     mask=mask_d).items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+    staging = {k: torch.empty_like(v, device=dev) for k, v in host.items()}
+    metrics_host = torch.empty(8, dtype=torch.float32).pin_memory()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    seg = {"fwd": [], "loss": [], "bwd": []}
+
+    def step(e2e: bool, record: bool):
+        if e2e:
+            for k in host:
+                staging[k].copy_(host[k], non_blocking=True)
+            src = staging
+        else:
+            src = dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d, mask=mask_d)
+        hidden = src["hidden"].detach().requires_grad_(True)
+        weight.grad = None
+        marks = [ev() for _ in range(4)] if record else None
+        if record:
+            marks[0].record()
+        lp, ent = linear_cross_entropy(hidden, weight, src["labels"], 1.0, "none", group)
+        if record:
+            marks[1].record()
+        loss, metrics = core_algos.fused_actor_loss(src["old"], lp.view(1, -1), src["adv"], src["mask"],
+                                                    entropy=ent.view(1, -1), ref_log_prob=src["ref"], **LOSS_CFG)
+        if record:
+            marks[2].record()
+        loss.backward()
+        if world > 1:  # caller-side reduction of d_hidden, as in the reference (test_linear_cross_entropy_tp.py:313)
+            dist.all_reduce(hidden.grad, group=group)
+        if record:
+            marks[3].record()
+            seg["_marks"].append(marks)
+        if e2e:
+            metrics_host.copy_(metrics, non_blocking=True)
+            torch.cuda.current_stream().synchronize()  # the host reads the step's loss / metrics
+        return metrics
+
+    def timed(e2e: bool, steps: int, record: bool):
+        seg["_marks"] = []
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = ev(), ev()
+        e0.record()
+        for _ in range(steps):
+            step(e2e, record)
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step(False, False)
+    step(True, False)
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    ms_dev = timed(False, args.steps, True)
+    launches = _lib.launch_count() - launches0
+    marks = seg["_marks"]
+    ms_e2e = timed(True, args.steps, False)
+    clocks = sampler.stop() if rank == 0 else None
+
+    fwd_ms = sum(m[0].elapsed_time(m[1]) for m in marks) / len(marks)
+    loss_ms = sum(m[1].elapsed_time(m[2]) for m in marks) / len(marks)
+    bwd_ms = sum(m[2].elapsed_time(m[3]) for m in marks) / len(marks)
+
+    if rank == 0:
+        peaks = _peaks()
+        flops_fwd = 2.0 * T * H * v_local  # per GPU
+        fwd_tf = flops_fwd / (fwd_ms * 1e-3) / 1e12
+        step_useful_tf = 3 * flops_fwd / (ms_dev * 1e-3) / 1e12
+        step_exec_tf = 4 * flops_fwd / (ms_dev * 1e-3) / 1e12
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            tps, dt = cpu_reference_sample(args.cpu_tokens, threads)
+            cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port",
+                   "sample": f"{args.cpu_tokens} tokens at full H and V, fp32 math on bf16 inputs, {dt:.1f} s"}
+        line = {
+            "metric": METRIC, "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {
+                "workload": f"Qwen2.5-7B lm-head (H={H}, V={V}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
+                            "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
+                "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), "
+                               "all-gather of [4,S,T] partials + all-reduce of d_hidden",
+                "l2": "inputs exceed L2 (hidden 470 MB + weight shard >= 136 MB per step)",
+                "loss": LOSS_CFG,
+            },
+            "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {
+                "kernel": "tc_gemm_kernel<MODE_FWD> (tcgen05 lm-head forward with fused online-softmax epilogue)",
+                "bound": "tensor", "achieved": fwd_tf, "peak": peaks["sustained"], "unit": "TFLOP/s",
+                "frac": fwd_tf / peaks["sustained"], "traffic": None,
+                "peak_source": peaks["source"] + ", sustained bf16 figure (kernel timed inside a long step)",
+                "frac_of_burst_peak": fwd_tf / peaks["burst"],
+                "algorithmic_flops_per_launch": flops_fwd, "launch_ms": fwd_ms,
+            },
+            "roofline_step": {
+                "useful_tflops": step_useful_tf, "executed_tflops": step_exec_tf,
+                "useful_frac_of_sustained": step_useful_tf / peaks["sustained"],
+                "useful_frac_of_burst": step_useful_tf / peaks["burst"],
+                "executed_frac_of_sustained": step_exec_tf / peaks["sustained"],
+                "segments_ms": {"lm_head_fwd": fwd_ms, "ppo_loss": loss_ms, "lm_head_bwd(+allreduce)": bwd_ms},
+                "note": "useful = 6*T*H*V/N per GPU (fwd + dH + dW), executed = 8*T*H*V/N (tile recompute in the backward)",
+            },
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--tokens", type=int, default=TOKENS)
+    ap.add_argument("--cpu-tokens", type=int, default=512, help="token sample of the CPU reference arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

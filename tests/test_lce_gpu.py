@@ -1,0 +1,229 @@
+"""GPU parity of the fused lm-head op (tcgen05 kernels through the C ABI) against the oracle and the reference's
+golden vectors.  Tolerances: north_star's 2e-3 abs on fp32 log-probs / entropy for bf16 inputs (the reference's own
+kernel test allows logprobs atol 1e-3 rtol 2e-4, entropy atol 5e-3 rtol 5e-4, grads atol 2e-2 rtol 4e-2:
+tests/utils/test_linear_cross_entropy.py:218-223,270-275)."""
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+LP_ATOL = 2e-3
+GRAD_ATOL, GRAD_RTOL = 2e-2, 4e-2
+
+
+def T(a, dev):
+    return torch.from_numpy(np.asarray(a)).to(dev)
+
+
+def _inputs(Tn, H, V, seed, dev):
+    """distributions of the reference test (tests/utils/test_linear_cross_entropy.py:145-162)"""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    hidden = (torch.rand(Tn, H, generator=g) - 0.5).bfloat16().to(dev)
+    weight = (torch.rand(V, H, generator=g) - 0.5).bfloat16().to(dev)
+    labels = torch.randint(0, V, (Tn,), generator=g).to(dev)
+    g_lp = (torch.rand(Tn, generator=g) * 2 - 1).to(dev)
+    g_ent = (torch.rand(Tn, generator=g) - 0.5).to(dev)
+    return hidden, weight, labels, g_lp, g_ent
+
+
+def _gpu_fp32_reference(hidden, weight, labels, temperature, g_lp=None, g_ent=None):
+    """plain PyTorch fp32 reference of the same op (run_torch_entropy recipe,
+    tests/utils/test_linear_cross_entropy.py:48-61), chunked so that [T,V] fp32 stays small"""
+    h = hidden.float().requires_grad_(g_lp is not None)
+    w = weight.float().requires_grad_(g_lp is not None)
+    lps, ents = [], []
+    for s in range(0, h.shape[0], 1024):
+        logits = (h[s:s + 1024] @ w.t()) / temperature
+        lse = torch.logsumexp(logits, -1)
+        p = torch.softmax(logits, -1)
+        ents.append(lse - (p * logits).sum(-1))
+        lps.append(logits.gather(-1, labels[s:s + 1024, None]).squeeze(-1) - lse)
+    lp, ent = torch.cat(lps), torch.cat(ents)
+    if g_lp is None:
+        return lp, ent, None, None
+    (lp * g_lp + ent * g_ent).sum().backward()
+    return lp.detach(), ent.detach(), h.grad, w.grad
+
+
+@pytest.mark.parametrize("case", ["a", "b", "c"])
+def test_forward_backward_vs_reference_golden(case, dev):
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    g = load_golden("lce")
+    hidden = T(g[f"{case}_hidden"], dev).bfloat16().requires_grad_(True)
+    weight = T(g[f"{case}_weight"], dev).bfloat16().requires_grad_(True)
+    labels = T(g[f"{case}_labels"], dev)
+    temp = float(g[f"{case}_temperature"])
+    lp, ent = linear_cross_entropy(hidden, weight, labels, temp, "none")
+    assert lp.dtype == torch.float32 and lp.shape == (hidden.shape[0],)
+    torch.testing.assert_close(lp, T(g[f"{case}_logprobs"], dev), atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent, T(g[f"{case}_entropy"], dev), atol=LP_ATOL, rtol=0)
+    (lp * T(g[f"{case}_g_lp"], dev) + ent * T(g[f"{case}_g_ent"], dev)).sum().backward()
+    assert hidden.grad.dtype == torch.bfloat16 and weight.grad.dtype == torch.bfloat16
+    torch.testing.assert_close(hidden.grad.float(), T(g[f"{case}_d_hidden"], dev), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(weight.grad.float(), T(g[f"{case}_d_weight"], dev), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+
+
+# the reference's five test shapes (tests/utils/test_linear_cross_entropy.py:116-140); V of the first two scaled by
+# 1/8 and 1/4 to keep the fp32 torch reference's [T,V] buffers small, the tile-tail structure (V % 256 != 0) is kept
+SHAPES = [
+    (1937, 3584, 152064 // 8),
+    (2169, 896, 151936 // 4),
+    (1530, 2048, 32256),
+    (1388, 4096, 102400 // 4),
+    (300, 128, 1000),
+    (128, 64, 256),
+    (1, 128, 7),
+]
+
+
+@pytest.mark.parametrize("Tn,H,V", SHAPES)
+def test_forward_backward_vs_oracle_shapes(Tn, H, V, dev):
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    temp = 1.5
+    hidden, weight, labels, g_lp, g_ent = _inputs(Tn, H, V, 233376, dev)
+    hidden.requires_grad_(True), weight.requires_grad_(True)
+    lp, ent = linear_cross_entropy(hidden, weight, labels, temp, "none")
+    (lp * g_lp + ent * g_ent).sum().backward()
+    lp_r, ent_r, dh_r, dw_r = _gpu_fp32_reference(hidden.detach(), weight.detach(), labels, temp, g_lp, g_ent)
+    torch.testing.assert_close(lp, lp_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent, ent_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(hidden.grad.float(), dh_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(weight.grad.float(), dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    if Tn <= 300:  # the CPU oracle itself at sizes it finishes in seconds
+        lp_o, ent_o = port.lce_forward(hidden.detach().cpu(), weight.detach().cpu(), labels.cpu(), temp)
+        torch.testing.assert_close(lp.cpu(), lp_o, atol=LP_ATOL, rtol=0)
+        torch.testing.assert_close(ent.cpu(), ent_o, atol=LP_ATOL, rtol=0)
+
+
+def test_reductions_and_3d_shapes(dev):
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    hidden, weight, labels, g_lp, g_ent = _inputs(4 * 96, 256, 1500, 1, dev)
+    lp, ent = linear_cross_entropy(hidden, weight, labels, 1.0, "none")
+    lp_sum, _ = linear_cross_entropy(hidden, weight, labels, 1.0, "sum")
+    lp_mean, _ = linear_cross_entropy(hidden, weight, labels, 1.0, "mean")
+    assert lp_sum.dim() == 0 and lp_mean.dim() == 0
+    torch.testing.assert_close(lp_sum, lp.sum(), rtol=1e-5, atol=1e-3)
+    torch.testing.assert_close(lp_mean, lp.mean(), rtol=1e-5, atol=1e-5)
+    # [B,S,H] with B>1 -> [B,S]; [1,T,H] -> flat [T] like the reference's Triton op
+    lp3, ent3 = linear_cross_entropy(hidden.view(4, 96, 256), weight, labels.view(4, 96), 1.0, "none")
+    assert lp3.shape == (4, 96) and torch.equal(lp3.reshape(-1), lp) and torch.equal(ent3.reshape(-1), ent)
+    lp1, _ = linear_cross_entropy(hidden.view(1, -1, 256), weight, labels.view(1, -1), 1.0, "none")
+    assert lp1.shape == (4 * 96,)
+    # backward through the mean reduction and without an entropy gradient
+    h = hidden.clone().requires_grad_(True)
+    w = weight.clone().requires_grad_(True)
+    lp_mean, _ = linear_cross_entropy(h, w, labels, 1.0, "mean")
+    lp_mean.backward()
+    ones = torch.full_like(g_lp, 1.0 / h.shape[0])
+    _, _, dh_r, dw_r = _gpu_fp32_reference(hidden, weight, labels, 1.0, ones, torch.zeros_like(g_ent))
+    torch.testing.assert_close(h.grad.float(), dh_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(w.grad.float(), dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+
+
+@pytest.mark.parametrize("chunk", [256, 512, 1024])
+def test_backward_chunking_is_consistent(chunk, dev):
+    """d_hidden accumulated in fp32 over vocab chunks must agree with the single-chunk result"""
+    from verl_b200 import ops
+
+    hidden, weight, labels, g_lp, g_ent = _inputs(500, 256, 2000, 3, dev)
+    part = ops.lce_forward_partials(hidden, weight, labels, 1.3)
+    _, _, lse, eb = ops.lce_finalize(part, 1.3)
+    dh0, dw0 = ops.lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, 1.3, chunk_v=2048)
+    dh1, dw1 = ops.lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, 1.3, chunk_v=chunk)
+    torch.testing.assert_close(dw0.float(), dw1.float(), atol=0, rtol=0)  # d_weight rows do not depend on chunking
+    torch.testing.assert_close(dh0.float(), dh1.float(), atol=4e-3, rtol=2e-2)
+
+
+@pytest.mark.parametrize("splits", [1, 2, 5, 8])
+def test_split_invariance(splits, dev):
+    from verl_b200 import ops
+
+    hidden, weight, labels, _, _ = _inputs(257, 128, 2100, 4, dev)
+    base = ops.lce_finalize(ops.lce_forward_partials(hidden, weight, labels, 1.0, num_splits=1), 1.0)
+    out = ops.lce_finalize(ops.lce_forward_partials(hidden, weight, labels, 1.0, num_splits=splits), 1.0)
+    for a, b in zip(base, out):
+        torch.testing.assert_close(a, b, atol=2e-5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_vocab_parallel_emulated_on_one_gpu(world, dev):
+    """vocab-parallel path with the ranks emulated serially: shard r runs the real kernel with label_offset =
+    r*V_local (verl/utils/kernel/kernels.py:232), partials are concatenated as exchange_partials would, finalize
+    merges.  Must equal the single-shard result; d_hidden partials must sum to the full d_hidden
+    (tests/utils/test_linear_cross_entropy_tp.py:313-314)."""
+    from verl_b200 import ops
+
+    Tn, H, V = 700, 512, 8 * 2004
+    hidden, weight, labels, g_lp, g_ent = _inputs(Tn, H, V, 5, dev)
+    full = ops.lce_finalize(ops.lce_forward_partials(hidden, weight, labels, 1.5), 1.5)
+    v_local = V // world
+    parts = [ops.lce_forward_partials(hidden, weight[r * v_local:(r + 1) * v_local].contiguous(), labels, 1.5,
+                                      label_offset=r * v_local, num_splits=2) for r in range(world)]
+    merged = torch.cat(parts, dim=1)
+    lp, ent, lse, eb = ops.lce_finalize(merged, 1.5)
+    torch.testing.assert_close(lp, full[0], atol=2e-5, rtol=1e-5)
+    torch.testing.assert_close(ent, full[1], atol=2e-5, rtol=1e-5)
+    dh_full, dw_full = ops.lce_backward(hidden, weight, labels, full[2], full[3], g_lp, g_ent, 1.5)
+    dh_sum = torch.zeros(Tn, H, device=dev)
+    for r in range(world):
+        w_r = weight[r * v_local:(r + 1) * v_local].contiguous()
+        dh_r, dw_r = ops.lce_backward(hidden, w_r, labels, lse, eb, g_lp, g_ent, 1.5, label_offset=r * v_local)
+        dh_sum += dh_r.float()
+        torch.testing.assert_close(dw_r.float(), dw_full[r * v_local:(r + 1) * v_local].float(), atol=1e-2, rtol=2e-2)
+    torch.testing.assert_close(dh_sum, dh_full.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+
+
+def test_full_size_properties(dev):
+    """BASELINE configs[1] at full size (T=65536, H=3584, V=152064): size-independent properties —
+    (1) probabilities: logprob <= 0, 0 <= entropy <= ln V;  (2) a random subset of rows equals the fp32 reference;
+    (3) linearity of the backward in (g_lp, g_ent) checked on d_hidden rows."""
+    from verl_b200 import ops
+
+    Tn, H, V = 65536, 3584, 152064
+    g = torch.Generator(device=dev).manual_seed(9)
+    hidden = (torch.rand(Tn, H, device=dev, generator=g) - 0.5).bfloat16()
+    weight = (torch.rand(V, H, device=dev, generator=g) - 0.5).bfloat16()
+    labels = torch.randint(0, V, (Tn,), device=dev, generator=g)
+    lp, ent, lse, eb = ops.lce_finalize(ops.lce_forward_partials(hidden, weight, labels, 1.0), 1.0)
+    assert torch.isfinite(lp).all() and torch.isfinite(ent).all()
+    assert (lp <= 1e-4).all() and (ent >= -1e-3).all() and (ent <= np.log(V) + 1e-3).all()
+    rows = torch.randperm(Tn, device=dev, generator=g)[:512]
+    lp_r, ent_r, _, _ = _gpu_fp32_reference(hidden[rows], weight, labels[rows], 1.0)
+    torch.testing.assert_close(lp[rows], lp_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent[rows], ent_r, atol=LP_ATOL, rtol=0)
+    del lp_r, ent_r
+    # backward on a 4096-token slice at full H and V: linearity d(a*g1 + g2) == a*d(g1) + d(g2)
+    sl = slice(0, 4096)
+    h, lab = hidden[sl].contiguous(), labels[sl].contiguous()
+    g1 = torch.rand(4096, device=dev, generator=g) * 2 - 1
+    g2 = torch.rand(4096, device=dev, generator=g) - 0.5
+    dh_a, _ = ops.lce_backward(h, weight, lab, lse[sl].contiguous(), eb[sl].contiguous(), g1, None, 1.0)
+    dh_b, _ = ops.lce_backward(h, weight, lab, lse[sl].contiguous(), eb[sl].contiguous(), None, g2, 1.0)
+    dh_c, _ = ops.lce_backward(h, weight, lab, lse[sl].contiguous(), eb[sl].contiguous(), 2 * g1, g2, 1.0)
+    torch.testing.assert_close(dh_c.float(), 2 * dh_a.float() + dh_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+
+
+def test_gemm_all_majors(dev):
+    from verl_b200 import ops
+
+    torch.manual_seed(0)
+    for (M, N, K) in [(128, 256, 64), (304, 520, 192), (1000, 1024, 1024)]:
+        A = (torch.rand(M, K, device=dev) - 0.5).bfloat16()
+        B = (torch.rand(N, K, device=dev) - 0.5).bfloat16()
+        ref = A.float() @ B.float().t()
+        for a_k in (True, False):
+            for b_k in (True, False):
+                Ain = A if a_k else A.t().contiguous()
+                Bin = B if b_k else B.t().contiguous()
+                C = ops.gemm_bf16(Ain, Bin, a_k, b_k, out_dtype=torch.float32)
+                torch.testing.assert_close(C, ref, atol=1e-3, rtol=1e-4)
+                Cb = ops.gemm_bf16(Ain, Bin, a_k, b_k, out_dtype=torch.bfloat16)
+                torch.testing.assert_close(Cb.float(), ref, atol=5e-2, rtol=2e-2)

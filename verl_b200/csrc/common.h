@@ -27,11 +27,11 @@ int sm_count();  // SMs of the current device (cached per device)
                                     __FILE__, __LINE__);                                                 \
     } while (0)
 
-// call after a <<<>>> launch
+// call after a <<<>>> launch (cudaGetLastError also clears a non-sticky launch error so that it is reported once)
 #define VPG_LAUNCH_CHECK()                  \
     do {                                    \
         ::vpg::count_launch();              \
-        VPG_CUDA(cudaPeekAtLastError());    \
+        VPG_CUDA(cudaGetLastError());       \
     } while (0)
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

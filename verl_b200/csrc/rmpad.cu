@@ -245,7 +245,7 @@ int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, in
             count_launch();
         }
     });
-    VPG_CUDA(cudaPeekAtLastError());
+    VPG_CUDA(cudaGetLastError());
     return VPG_OK;
 }
 

@@ -514,7 +514,7 @@ __device__ __forceinline__ Affine affine_shfl_down(const Affine& a, int delta) {
 }
 
 template <typename MT>
-__global__ void gae_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+__global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
                            const MT* __restrict__ mask, long long L, float gamma, float lam,
                            float* __restrict__ adv_out, float* __restrict__ ret_out, double* __restrict__ sums) {
     __shared__ Affine warp_maps[32];
@@ -887,7 +887,7 @@ int vpg_gae(const float* rewards, const float* values, const void* mask, int mas
     double* sums = static_cast<double*>(workspace);
     VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
     int64_t threads = round_up(ceil_div(L, kSeg), 32);
-    if (threads > 1024) threads = 1024;
+    if (threads > 512) threads = 512;
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         gae_kernel<MT><<<static_cast<unsigned>(B), static_cast<unsigned>(threads), 0, stream>>>(
             rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums);

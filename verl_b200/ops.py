@@ -151,6 +151,9 @@ def unpad_indices(mask2d):
     dev = mask2d.device
     lib = _lib_()
     n = B * S
+    if n == 0:  # nothing to scan: no launch
+        return (torch.empty(0, dtype=torch.int64, device=dev), torch.zeros(B, dtype=torch.int32, device=dev),
+                torch.zeros(B + 1, dtype=torch.int32, device=dev), 0)
     indices_full = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     seqlens = torch.empty(B, dtype=torch.int32, device=dev)
     cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
