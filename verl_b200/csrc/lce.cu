@@ -3,6 +3,8 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common.h"
@@ -53,23 +55,54 @@ static int make_operand_tmap(CUtensorMap* tm, const void* base, int64_t rows, in
     return make_tmap(tm, base, rows, K, ld, 64, kBlockK);
 }
 
-template <int kMode, bool kAMn, bool kBMn>
-static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
-    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn>;
-    static std::once_flag once;
-    static cudaError_t attr_err = cudaSuccess;
+// cta_group used by every tcgen05 launch: 2 (CTA pairs, 256x256 tiles) unless VPG_CTA_GROUP=1 is set
+static int cta_group() {
+    static int cg = [] {
+        const char* e = getenv("VPG_CTA_GROUP");
+        return (e && e[0] == '1') ? 1 : 2;
+    }();
+    return cg;
+}
+static int tile_m() { return kBlockM * cta_group(); }
+static int num_workers() { return cta_group() == 2 ? sm_count() / 2 : sm_count(); }
+static int b_tile_rows() { return kBlockN / cta_group(); }
+
+template <int kMode, bool kAMn, bool kBMn, int kCG>
+static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG>;
+    constexpr int smem = TileCfg<kCG>::kSmemBytes;
     // per-device attribute: set every call (cheap) so multi-device processes are handled
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    (void)once;
+    cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (attr_err != cudaSuccess)
-        return set_error(VPG_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", kSmemBytes,
-                         cudaGetErrorString(attr_err));
+        return set_error(VPG_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(attr_err));
     const int64_t units = static_cast<int64_t>(p.num_m_tiles) * p.num_splits;
     if (units <= 0) return VPG_OK;
-    const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
-    kern<<<grid, kNumThreads, kSmemBytes, stream>>>(ta, tb, p);
-    VPG_LAUNCH_CHECK();
+    const int workers = static_cast<int>(units < num_workers() ? units : num_workers());
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(static_cast<unsigned>(workers * kCG));
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCG;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+    count_launch();
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return set_error(VPG_ERR_CUDA, "tc_gemm_kernel launch failed: %s", cudaGetErrorString(e));
+    }
     return VPG_OK;
+}
+
+template <int kMode, bool kAMn, bool kBMn>
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+    if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream);
+    return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream);
 }
 
 // balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
@@ -146,7 +179,8 @@ int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
     (void)H;
     if (T <= 0 || V <= 0) return 1;
     if (sm <= 0) sm = sm_count();
-    return choose_splits(static_cast<int>(ceil_div(T, kBlockM)), static_cast<int>(ceil_div(V, kBlockN)), sm);
+    const int workers = cta_group() == 2 ? sm / 2 : sm;
+    return choose_splits(static_cast<int>(ceil_div(T, tile_m())), static_cast<int>(ceil_div(V, kBlockN)), workers);
 }
 
 int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
@@ -158,7 +192,7 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
     VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0 (got %f)", temperature);
     if (T == 0) return VPG_OK;
     TcParams p{};
-    p.num_m_tiles = static_cast<int>(ceil_div(T, kBlockM));
+    p.num_m_tiles = static_cast<int>(ceil_div(T, tile_m()));
     p.num_n_tiles = static_cast<int>(ceil_div(V, kBlockN));
     p.num_k_blocks = static_cast<int>(H / kBlockK);
     VPG_CHECK_ARG(num_splits >= 1 && num_splits <= p.num_n_tiles, "num_splits %d out of range [1,%d]", num_splits,
@@ -174,7 +208,7 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
     p.partials = partials;
     CUtensorMap ta, tb;
     if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
-    if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, kBlockN))) return rc;
+    if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, b_tile_rows()))) return rc;
     return launch_tc<MODE_FWD, false, false>(ta, tb, p, static_cast<cudaStream_t>(stream));
 }
 
@@ -192,7 +226,7 @@ int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temp
 
 int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
     (void)H;
-    const int64_t t_pad = round_up(T > 0 ? T : 1, kBlockM);
+    const int64_t t_pad = round_up(T > 0 ? T : 1, 2 * kBlockM);
     const int64_t v_pad = round_up(V, kBlockN);
     const int64_t budget = 3LL << 30;  // bytes of bf16 dlogits workspace
     int64_t c = budget / (t_pad * 2) / kBlockN * kBlockN;
@@ -207,7 +241,7 @@ int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
 size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v) {
     if (T <= 0) return 0;
     if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
-    const int64_t t_pad = round_up(T, kBlockM);
+    const int64_t t_pad = round_up(T, 2 * kBlockM);
     const int64_t v_pad = round_up(V, kBlockN);
     if (chunk_v > v_pad) chunk_v = v_pad;
     size_t bytes = static_cast<size_t>(t_pad) * chunk_v * 2;
@@ -231,7 +265,7 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
     }
     if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
     VPG_CHECK_ARG(chunk_v % kBlockN == 0, "chunk_v must be a multiple of %d", kBlockN);
-    const int64_t t_pad = round_up(T, kBlockM);
+    const int64_t t_pad = round_up(T, 2 * kBlockM);  // dlogits rows: multiple of the largest m tile (256)
     const int64_t v_pad = round_up(V, kBlockN);
     if (chunk_v > v_pad) chunk_v = v_pad;
     const size_t need = vpg_lce_bwd_workspace_bytes(T, H, V, chunk_v);
@@ -244,7 +278,7 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
     float* dh_acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) +
                                              round_up(static_cast<int64_t>(t_pad) * chunk_v * 2, 256));
     const int num_chunks = static_cast<int>(ceil_div(v_pad, chunk_v));
-    const int m_tiles_t = static_cast<int>(t_pad / kBlockM);
+    const int m_tiles_t = static_cast<int>(t_pad / tile_m());
 
     for (int ci = 0; ci < num_chunks; ++ci) {
         const int64_t v0 = static_cast<int64_t>(ci) * chunk_v;
@@ -257,7 +291,7 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
             p.num_m_tiles = m_tiles_t;
             p.num_n_tiles = n_tiles_c;
             p.num_k_blocks = static_cast<int>(H / kBlockK);
-            p.num_splits = choose_splits(m_tiles_t, n_tiles_c, sm_count());
+            p.num_splits = choose_splits(m_tiles_t, n_tiles_c, num_workers());
             p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
             p.M = static_cast<int>(T);
             p.N = static_cast<int>(vc);
@@ -272,13 +306,13 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
             p.ds = ds;
             p.ldds = ldds;
             if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
-            if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, kBlockN))) return rc;
+            if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, b_tile_rows()))) return rc;
             if ((rc = launch_tc<MODE_DS, false, false>(ta, tb, p, stream))) return rc;
         }
         const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
         {  // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
             TcParams p{};
-            p.num_m_tiles = static_cast<int>(ceil_div(vc, kBlockM));
+            p.num_m_tiles = static_cast<int>(ceil_div(vc, tile_m()));
             p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
             p.num_k_blocks = static_cast<int>(t_pad / kBlockK);
             p.num_splits = p.num_n_tiles;
@@ -329,7 +363,7 @@ int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K,
     VPG_CHECK_ARG(out_mode != OUT_BF16_FROM_ACC || (accum_f32 && ld_accum % 4 == 0), "accum buffer required");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     TcParams p{};
-    p.num_m_tiles = static_cast<int>(ceil_div(M, kBlockM));
+    p.num_m_tiles = static_cast<int>(ceil_div(M, tile_m()));
     p.num_n_tiles = static_cast<int>(ceil_div(N, kBlockN));
     p.num_k_blocks = static_cast<int>(ceil_div(K, kBlockK));
     p.num_splits = p.num_n_tiles;
@@ -344,7 +378,7 @@ int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K,
     CUtensorMap ta, tb;
     int rc;
     if ((rc = make_operand_tmap(&ta, A, M, K, lda, !a_kmajor, kBlockM))) return rc;
-    if ((rc = make_operand_tmap(&tb, B, N, K, ldb, !b_kmajor, kBlockN))) return rc;
+    if ((rc = make_operand_tmap(&tb, B, N, K, ldb, !b_kmajor, b_tile_rows()))) return rc;
     if (a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, false, false>(ta, tb, p, stream);
     if (a_kmajor && !b_kmajor) return launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream);
     if (!a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, true, false>(ta, tb, p, stream);

@@ -8,6 +8,8 @@
 //   warp 2      TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
 //   warp 3      idle
 //   warps 4-11  epilogue: warp w reads TMEM lanes 32*(w%4).., columns 128*((w-4)/4)..  via tcgen05.ld
+// With kCG = 2 the same roles run in both CTAs of a pair except the MMA issuer (leader CTA only); TMA transaction
+// bytes of both CTAs are signalled on the leader's full barrier, tcgen05.commit multicasts to both CTAs.
 //
 // Pipelines: smem ring (full/empty mbarriers, kStages deep) between TMA and MMA; TMEM ring (tmem_full /
 // tmem_empty, 2 deep) between MMA and epilogue, so the epilogue of tile i overlaps the MMAs of tile i+1.
@@ -25,15 +27,25 @@ constexpr int kBlockM = 128;
 constexpr int kBlockN = 256;
 constexpr int kBlockK = 64;   // 64 bf16 = 128 B = one swizzle atom row
 constexpr int kUmmaK = 16;
-constexpr int kStages = 4;
-constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KB
-constexpr int kBBytes = kBlockN * kBlockK * 2;  // 32 KB
-constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KB: every CTA stages its own 128 rows of A
+constexpr int kMaxStages = 8;
 constexpr int kNumThreads = 384;
+
+// kCG = 1: one CTA computes a 128x256 tile.  kCG = 2 (tcgen05 cta_group::2, cluster of 2 CTAs on one TPC): the pair
+// computes a 256x256 tile; each CTA stages its 128 rows of A and HALF of B (128 rows), the tensor cores of both SMs
+// read B from both halves, so shared-memory and L2->SM traffic per flop drop by a third.
+template <int kCG>
+struct TileCfg {
+    static constexpr int kTileM = kBlockM * kCG;          // rows per unit
+    static constexpr int kBRows = kBlockN / kCG;          // B rows staged by one CTA
+    static constexpr int kBBytes = kBRows * kBlockK * 2;  // 32 KB / 16 KB
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (kCG == 1) ? 4 : 6;
+    static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + 8192 /*barriers + scratch*/;
+};
 constexpr int kEpiWarp0 = 4;
 constexpr int kNumEpiWarps = 8;
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + 8192 /*barriers + scratch*/;
 
 enum : int { MODE_FWD = 0, MODE_DS = 1, MODE_GEMM = 2 };
 enum : int { OUT_BF16 = 0, OUT_F32 = 1, OUT_F32_ACC = 2, OUT_BF16_FROM_ACC = 3 };
@@ -70,22 +82,22 @@ struct TcParams {
 
 struct SmemLayout {
     uint8_t* stages;
-    uint64_t* full;        // [kStages]
-    uint64_t* empty;       // [kStages]
+    uint64_t* full;        // [kMaxStages]
+    uint64_t* empty;       // [kMaxStages]
     uint64_t* tmem_full;   // [2]
     uint64_t* tmem_empty;  // [2]
     uint32_t* tmem_ptr;
     float4* scratch;  // [2][128]
 };
 
-__device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw) {
+__device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw, int stage_bytes_total) {
     SmemLayout L;
     uintptr_t base = (reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023);
     L.stages = reinterpret_cast<uint8_t*>(base);
-    uint8_t* aux = L.stages + kStages * kStageBytes;
+    uint8_t* aux = L.stages + stage_bytes_total;
     L.full = reinterpret_cast<uint64_t*>(aux);
-    L.empty = L.full + kStages;
-    L.tmem_full = L.empty + kStages;
+    L.empty = L.full + kMaxStages;
+    L.tmem_full = L.empty + kMaxStages;
     L.tmem_empty = L.tmem_full + 2;
     L.tmem_ptr = reinterpret_cast<uint32_t*>(L.tmem_empty + 2);
     L.scratch = reinterpret_cast<float4*>(aux + 256);
@@ -265,14 +277,21 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
 //   K-major operand : one TMA box {64 (k), rows}            -> rows x 128 B, SBO = 1024 B, K step = +32 B
 //   MN-major operand: rows/64 TMA boxes {64 (mn), 64 (k)}   -> blocks of 64 k-rows x 128 B (8 KB),
 //                     LBO = 8192 B (next 64 mn), SBO = 1024 B (next 8 k), K step (16 rows) = +2048 B
-template <int kMode, bool kAMn, bool kBMn>
+template <int kMode, bool kAMn, bool kBMn, int kCG>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const TcParams p) {
+    using Cfg = TileCfg<kCG>;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int kStageBytes = Cfg::kStageBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    SmemLayout L = carve_smem(smem_raw);
+    SmemLayout L = carve_smem(smem_raw, kStages * kStageBytes);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = (kCG == 2) ? cluster_ctarank() : 0u;
+    const bool is_leader = (cta_rank == 0);
+    const int worker = (kCG == 2) ? (blockIdx.x >> 1) : blockIdx.x;          // CTA (pair) index
+    const int num_workers = (kCG == 2) ? (gridDim.x >> 1) : gridDim.x;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
@@ -280,56 +299,75 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) {
-            mbar_init(&L.full[i], 1);
-            mbar_init(&L.empty[i], 1);
+            mbar_init(&L.full[i], 1);   // leader's barrier collects the transaction bytes of both CTAs
+            mbar_init(&L.empty[i], 1);  // one tcgen05.commit (multicast to both CTAs when kCG == 2)
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&L.tmem_full[i], 1);
-            mbar_init(&L.tmem_empty[i], kNumEpiWarps);
+            mbar_init(&L.tmem_empty[i], kNumEpiWarps * kCG);  // epilogue warps of both CTAs arrive on the leader
         }
         fence_barrier_init();
     }
     if (warp == 2) {
-        tmem_alloc<1>(L.tmem_ptr, kTmemCols);
+        tmem_alloc<kCG>(L.tmem_ptr, kTmemCols);
     }
     tc_fence_before();
-    __syncthreads();
+    if (kCG == 2) cluster_sync(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *L.tmem_ptr;
 
     const int num_units = p.num_m_tiles * p.num_splits;
 
     if (warp == 0) {
-        // ===================================================================== TMA producer
+        // ===================================================================== TMA producer (every CTA)
         int stage = 0;
         uint32_t phase = 0;
-        for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        for (int u = worker; u < num_units; u += num_workers) {
             const int m_tile = u / p.num_splits;
             const int sp = u - m_tile * p.num_splits;
             const int nb = sp * p.tiles_per_split;
             const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
+            const int m0 = m_tile * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
             for (int n = nb; n < ne; ++n) {
+                const int n0 = n * kBlockN + static_cast<int>(cta_rank) * Cfg::kBRows;
                 for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                     mbar_wait(&L.empty[stage], phase ^ 1);
                     if (lane == 0) {
                         uint8_t* sa = L.stages + stage * kStageBytes;
                         uint8_t* sb = sa + kABytes;
-                        mbar_arrive_expect_tx(&L.full[stage], kStageBytes);
-                        if (!kAMn) {
-                            tma_load_2d(&tmap_a, &L.full[stage], sa, kb * kBlockK, m_tile * kBlockM);
-                        } else {
+                        if (kCG == 1) {
+                            mbar_arrive_expect_tx(&L.full[stage], kStageBytes);
+                            if (!kAMn) {
+                                tma_load_2d(&tmap_a, &L.full[stage], sa, kb * kBlockK, m0);
+                            } else {
 #pragma unroll
-                            for (int j = 0; j < kBlockM / 64; ++j)
-                                tma_load_2d(&tmap_a, &L.full[stage], sa + j * 8192, m_tile * kBlockM + j * 64,
-                                            kb * kBlockK);
-                        }
-                        if (!kBMn) {
-                            tma_load_2d(&tmap_b, &L.full[stage], sb, kb * kBlockK, n * kBlockN);
-                        } else {
+                                for (int j = 0; j < kBlockM / 64; ++j)
+                                    tma_load_2d(&tmap_a, &L.full[stage], sa + j * 8192, m0 + j * 64, kb * kBlockK);
+                            }
+                            if (!kBMn) {
+                                tma_load_2d(&tmap_b, &L.full[stage], sb, kb * kBlockK, n0);
+                            } else {
 #pragma unroll
-                            for (int j = 0; j < kBlockN / 64; ++j)
-                                tma_load_2d(&tmap_b, &L.full[stage], sb + j * 8192, n * kBlockN + j * 64,
-                                            kb * kBlockK);
+                                for (int j = 0; j < Cfg::kBRows / 64; ++j)
+                                    tma_load_2d(&tmap_b, &L.full[stage], sb + j * 8192, n0 + j * 64, kb * kBlockK);
+                            }
+                        } else {
+                            const uint32_t full_leader = mapa(smem_u32(&L.full[stage]), 0);
+                            if (is_leader) mbar_arrive_expect_tx(&L.full[stage], 2 * kStageBytes);
+                            if (!kAMn) {
+                                tma_load_2d_2sm(&tmap_a, full_leader, sa, kb * kBlockK, m0);
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < kBlockM / 64; ++j)
+                                    tma_load_2d_2sm(&tmap_a, full_leader, sa + j * 8192, m0 + j * 64, kb * kBlockK);
+                            }
+                            if (!kBMn) {
+                                tma_load_2d_2sm(&tmap_b, full_leader, sb, kb * kBlockK, n0);
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < Cfg::kBRows / 64; ++j)
+                                    tma_load_2d_2sm(&tmap_b, full_leader, sb + j * 8192, n0 + j * 64, kb * kBlockK);
+                            }
                         }
                     }
                     __syncwarp();
@@ -340,13 +378,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===================================================================== MMA issuer
-        constexpr uint32_t idesc = make_idesc_bf16(kBlockM, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u);
+    } else if (warp == 1 && is_leader) {
+        // ===================================================================== MMA issuer (leader CTA)
+        constexpr uint32_t idesc = make_idesc_bf16(kBlockM * kCG, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u);
         int stage = 0;
         uint32_t phase = 0;
         uint32_t acc_iter = 0;
-        for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        for (int u = worker; u < num_units; u += num_workers) {
             const int m_tile = u / p.num_splits;
             const int sp = u - m_tile * p.num_splits;
             const int nb = sp * p.tiles_per_split;
@@ -370,10 +408,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             // advance the 14-bit start-address field (units of 16 B)
                             const uint64_t a_adv = kAMn ? (k * 2048) >> 4 : (k * 32) >> 4;
                             const uint64_t b_adv = kBMn ? (k * 2048) >> 4 : (k * 32) >> 4;
-                            umma_bf16<1>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                            umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
                         }
-                        umma_commit(&L.empty[stage]);  // frees the smem slot once these MMAs retire
-                        if (kb == p.num_k_blocks - 1) umma_commit(&L.tmem_full[buf]);
+                        // frees the smem slot (in both CTAs) once these MMAs retire
+                        if (kCG == 1) umma_commit(&L.empty[stage]); else umma_commit_2sm(&L.empty[stage], 3);
+                        if (kb == p.num_k_blocks - 1) {
+                            if (kCG == 1) umma_commit(&L.tmem_full[buf]); else umma_commit_2sm(&L.tmem_full[buf], 3);
+                        }
                     }
                     __syncwarp();
                     if (++stage == kStages) {
@@ -384,7 +425,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
         }
     } else if (warp >= kEpiWarp0) {
-        // ===================================================================== epilogue
+        // ===================================================================== epilogue (every CTA, own 128 rows)
         const int ew = warp - kEpiWarp0;  // 0..7
         const int quarter = warp & 3;     // TMEM lane quarter this warp may access
         const int half = ew >> 2;         // column half: 0 -> [0,128), 1 -> [128,256)
@@ -393,12 +434,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const float c = p.scale_log2;
         uint32_t acc_iter = 0;
         uint32_t unit_iter = 0;
-        for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++unit_iter) {
+        for (int u = worker; u < num_units; u += num_workers, ++unit_iter) {
             const int m_tile = u / p.num_splits;
             const int sp = u - m_tile * p.num_splits;
             const int nb = sp * p.tiles_per_split;
             const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
-            const long long row = static_cast<long long>(m_tile) * kBlockM + row_in_tile;
+            const long long row = static_cast<long long>(m_tile) * Cfg::kTileM + cta_rank * kBlockM + row_in_tile;
             const bool row_ok = row < p.M;
 
             FwdState st;
@@ -471,7 +512,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // all TMEM reads of this accumulator are complete (wait::ld above): hand it back to the MMA warp
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&L.tmem_empty[buf]);
+                if (lane == 0) {
+                    if (kCG == 1) mbar_arrive(&L.tmem_empty[buf]); else mbar_arrive_cluster(&L.tmem_empty[buf], 0);
+                }
             }
 
             if (kMode == MODE_FWD) {
@@ -503,10 +546,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (kCG == 2) cluster_sync(); else __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc<1>(tmem_base, kTmemCols);
+        tmem_dealloc<kCG>(tmem_base, kTmemCols);
     }
 }
 
