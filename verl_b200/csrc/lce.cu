@@ -5,6 +5,7 @@
 
 #include <stdlib.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.h"
@@ -55,6 +56,16 @@ static int make_operand_tmap(CUtensorMap* tm, const void* base, int64_t rows, in
     return make_tmap(tm, base, rows, K, ld, 64, kBlockK);
 }
 
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+static unsigned int next_epoch() {  // one counter for all tc_gemm_kernel instantiations
+    static std::atomic<unsigned int> epoch_counter{1};
+    return epoch_counter.fetch_add(1) & 0x7FFu;
+}
+
 // cta_group used by every tcgen05 launch: 2 (CTA pairs, 256x256 tiles) unless VPG_CTA_GROUP=1 is set
 static int cta_group() {
     static int cg = [] {
@@ -68,8 +79,13 @@ static int num_workers() { return cta_group() == 2 ? sm_count() / 2 : sm_count()
 static int b_tile_rows() { return kBlockN / cta_group(); }
 
 template <int kMode, bool kAMn, bool kBMn, int kCG>
-static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
     auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG>;
+    TcParams p = p_in;
+    p.sync_slack = env_int("VPG_SYNC_SLACK", 1);
+    p.sync_epoch = next_epoch();
+    if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
+    if (env_int("VPG_HINT_B", -1) >= 0) p.hint_b = env_int("VPG_HINT_B", 0);
     constexpr int smem = TileCfg<kCG>::kSmemBytes;
     // per-device attribute: set every call (cheap) so multi-device processes are handled
     cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -85,7 +101,7 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kCG;
+    attr[0].val.clusterDim.x = (kCG == 1 && env_int("VPG_CLUSTER1", 1) == 2 && (workers % 2) == 0) ? 2 : kCG;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -206,6 +222,8 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
     p.labels = reinterpret_cast<const long long*>(labels);
     p.label_offset = label_offset;
     p.partials = partials;
+    p.worker_perm = env_int("VPG_WORKER_PERM", 0) ? num_splits : 0;
+    if (const char* e = getenv("VPG_DEBUG_TRACE_PTR")) p.debug_trace = reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0));
     CUtensorMap ta, tb;
     if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
     if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, b_tile_rows()))) return rc;
@@ -372,7 +390,7 @@ int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K,
     p.N = static_cast<int>(N);
     p.out = C;
     p.ldc = ldc;
-    p.out_mode = out_mode;
+    p.out_mode = env_int("VPG_DEBUG_SKIP_EPI", 0) ? OUT_DEBUG_SKIP : out_mode;
     p.accum = accum_f32;
     p.ld_accum = ld_accum;
     CUtensorMap ta, tb;

@@ -114,6 +114,30 @@ __device__ __forceinline__ void tma_load_2d_2sm(const void* tmap, uint32_t bar_c
         : "memory");
 }
 
+// L2 eviction-priority hints for TMA loads (the fixed createpolicy encodings CUTLASS calls TMA::CacheHintSm90)
+constexpr uint64_t kHintEvictNormal = 0x1000000000000000ull;
+constexpr uint64_t kHintEvictFirst = 0x12F0000000000000ull;
+constexpr uint64_t kHintEvictLast = 0x14F0000000000000ull;
+__host__ __device__ constexpr uint64_t l2_hint(int kind) {
+    return kind == 1 ? kHintEvictFirst : kind == 2 ? kHintEvictLast : kHintEvictNormal;
+}
+__device__ __forceinline__ void tma_load_2d_hint(const void* tmap, uint64_t* bar, void* dst, int c0, int c1,
+                                                 uint64_t hint) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, "
+        "%4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(hint)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm_hint(const void* tmap, uint32_t bar_cluster_addr, void* dst, int c0,
+                                                     int c1, uint64_t hint) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], "
+        "[%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "l"(hint)
+        : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 __device__ __forceinline__ void tc_fence_before() {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
