@@ -82,7 +82,7 @@ template <int kMode, bool kAMn, bool kBMn, int kCG>
 static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
     auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG>;
     TcParams p = p_in;
-    p.sync_slack = env_int("VPG_SYNC_SLACK", 1);
+    p.sync_slack = env_int("VPG_SYNC_SLACK", 2);
     p.sync_epoch = next_epoch();
     if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
     if (env_int("VPG_HINT_B", -1) >= 0) p.hint_b = env_int("VPG_HINT_B", 0);

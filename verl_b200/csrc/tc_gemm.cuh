@@ -289,9 +289,10 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
 // cta_group::2 the CTA pairs run at slightly different rates (a few % depending on where the pair sits on the die)
 // and drift apart by many tiles, after which every pair pulls its own copy of the weight stream from DRAM (measured:
 // 60-165 GB instead of 15 GB for the configs[1] forward).  Each leader-CTA producer publishes its tile counter and
-// waits (bounded) until the slowest worker is at most `slack` tiles behind.  This only shapes timing: a timeout
+// waits (bounded) until the slowest worker is at most `slack` checkpoints (of kPaceKBlocks k-blocks) behind.  This only shapes timing: a timeout
 // (non-resident workers, concurrent launches sharing the counters) disables it for the rest of the launch.
 constexpr int kMaxWorkers = 96;
+constexpr uint32_t kPaceKBlocks = 32;  // checkpoint period in 64-wide k-blocks (~16k clocks of MMA work)
 __device__ unsigned int g_progress[kMaxWorkers];
 
 __device__ __forceinline__ void st_relaxed_u32(unsigned int* p, unsigned int v) {
@@ -399,7 +400,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint32_t phase = 0;
         // Soft lock-step (see g_progress): keep every worker within `sync_slack` tiles of the slowest one.
         bool pace = (p.sync_slack > 0) && is_leader && num_workers <= kMaxWorkers;
-        uint32_t tile_iter = 0;
+        uint32_t kb_total = 0;  // k-blocks issued so far; pacing checkpoints every kPaceKBlocks of them
         const uint32_t epoch = p.sync_epoch << 20;
         for (int u = worker; u < num_units; u += num_workers) {
             const int m_tile = u / p.num_splits;
@@ -407,10 +408,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int nb = sp * p.tiles_per_split;
             const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
             const int m0 = m_tile * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
-            for (int n = nb; n < ne; ++n, ++tile_iter) {
-                if (pace) pace = pace_wait(worker, num_workers, epoch, tile_iter, p.sync_slack, lane);
+            for (int n = nb; n < ne; ++n) {
                 const int n0 = n * kBlockN + static_cast<int>(cta_rank) * Cfg::kBRows;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++kb_total) {
+                    if (pace && (kb_total % kPaceKBlocks) == 0)
+                        pace = pace_wait(worker, num_workers, epoch, kb_total / kPaceKBlocks, p.sync_slack, lane);
                     mbar_wait(&L.empty[stage], phase ^ 1);
                     if (elect_one()) {
                         uint8_t* sa = L.stages + stage * kStageBytes;
