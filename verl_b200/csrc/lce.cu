@@ -243,17 +243,35 @@ int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temp
 }
 
 int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
-    (void)H;
+    // Largest chunk whose bf16 dlogits buffer fits the budget, then the chunk count (up to +8) that wastes the fewest
+    // waves of the persistent grid in the three kernels of a chunk (cost in units of tile x k-block).
     const int64_t t_pad = round_up(T > 0 ? T : 1, 2 * kBlockM);
-    const int64_t v_pad = round_up(V, kBlockN);
-    const int64_t budget = 3LL << 30;  // bytes of bf16 dlogits workspace
-    int64_t c = budget / (t_pad * 2) / kBlockN * kBlockN;
-    if (c < kBlockN) c = kBlockN;
-    if (c > v_pad) c = v_pad;
-    // even out the chunks
-    const int64_t n_chunks = ceil_div(v_pad, c);
-    c = round_up(ceil_div(v_pad, n_chunks), kBlockN);
-    return c;
+    const int64_t v_tiles = ceil_div(V, kBlockN);
+    const int64_t budget = static_cast<int64_t>(env_int("VPG_BWD_WS_MB", 4096)) << 20;  // bf16 dlogits workspace
+    int64_t max_tiles = budget / (t_pad * 2) / kBlockN;
+    if (max_tiles < 1) max_tiles = 1;
+    if (max_tiles > v_tiles) max_tiles = v_tiles;
+    const int64_t W = num_workers(), tm = tile_m();
+    const int64_t m_t = ceil_div(t_pad, tm), n_h = ceil_div(H, kBlockN);
+    const int64_t min_chunks = ceil_div(v_tiles, max_tiles);
+    int64_t best_c = max_tiles;
+    double best_cost = 1e300;
+    for (int64_t nc = min_chunks; nc <= min_chunks + 8 && nc <= v_tiles; ++nc) {
+        const int64_t c = ceil_div(v_tiles, nc);
+        double cost = 0;
+        for (int64_t done = 0; done < v_tiles; done += c) {
+            const int64_t ct = (v_tiles - done) < c ? (v_tiles - done) : c;  // tiles in this chunk
+            cost += static_cast<double>(ceil_div(m_t * ct, W)) * (H / kBlockK);                       // dlogits
+            cost += static_cast<double>(ceil_div(ceil_div(ct * kBlockN, tm) * n_h, W)) * (t_pad / kBlockK);  // d_weight
+            cost += static_cast<double>(ceil_div(m_t * n_h, W)) * (ct * kBlockN / kBlockK);            // d_hidden
+            cost += 0.02 * (t_pad / kBlockK);                                                           // launches, fp32 RMW
+        }
+        if (cost < best_cost) {
+            best_cost = cost;
+            best_c = c;
+        }
+    }
+    return best_c * kBlockN;
 }
 
 size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v) {
