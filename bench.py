@@ -36,6 +36,18 @@ LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_rati
                 entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
 
 
+def _traffic(T, H, V):
+    """DRAM bytes per forward launch from the committed `ncu --set full` capture (None if the shape differs)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            t = json.load(f)["tc_gemm_fwd"]
+        if (t["T"], t["H"], t["V"]) == (T, H, V):
+            return t["dram_read_bytes"] + t["dram_write_bytes"]
+    except Exception:
+        pass
+    return None
+
+
 def _peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -286,7 +298,9 @@ def run_ours(args):
             "roofline": {
                 "kernel": "tc_gemm_kernel<MODE_FWD> (tcgen05 lm-head forward with fused online-softmax epilogue)",
                 "bound": "tensor", "achieved": fwd_tf, "peak": peaks["sustained"], "unit": "TFLOP/s",
-                "frac": fwd_tf / peaks["sustained"], "traffic": None,
+                "frac": fwd_tf / peaks["sustained"], "traffic": _traffic(T, H, v_local),
+                "traffic_unit": "bytes of DRAM read+write per launch (ncu --set full, profiles/roofline_traffic.json); "
+                                "algorithmic operand bytes = 2*(T*H + V*H) + 16*S*T",
                 "peak_source": peaks["source"] + ", sustained bf16 figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": fwd_tf / peaks["burst"],
                 "algorithmic_flops_per_launch": flops_fwd, "launch_ms": fwd_ms,
