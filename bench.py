@@ -36,6 +36,18 @@ LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_rati
                 entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
 
 
+def workload_config(T, world):
+    """`config` of the JSON line — identical for both arms (the reference arm times a bounded sample of it)."""
+    return {
+        "workload": f"Qwen2.5-7B lm-head (H={HIDDEN}, V={VOCAB}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
+                    "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
+        "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), "
+                       "all-gather of [4,S,T] partials + all-reduce of d_hidden",
+        "l2": "inputs exceed L2 (hidden 470 MB + weight shard >= 136 MB per step)",
+        "loss": LOSS_CFG,
+    }
+
+
 def _traffic(T, H, V):
     """DRAM bytes per forward launch from the committed `ncu --set full` capture (None if the shape differs)."""
     try:
@@ -95,6 +107,9 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------- CPU reference arm
+_CPU_INPUTS: dict = {}
+
+
 def cpu_reference_sample(sample_tokens: int, threads: int, repeats: int = 1):
     """The reference algorithm on the host cores: chunked (512) lm-head log-prob/entropy forward + hand-written
     backward (verl/utils/experimental/torch_functional.py:20-72) and the actor loss composition
@@ -104,15 +119,20 @@ def cpu_reference_sample(sample_tokens: int, threads: int, repeats: int = 1):
     from oracle import port
 
     torch.set_num_threads(threads)
-    g = torch.Generator().manual_seed(233376)
-    hidden = (torch.rand(sample_tokens, HIDDEN, generator=g) - 0.5).bfloat16()
-    weight = (torch.rand(VOCAB, HIDDEN, generator=g) - 0.5).bfloat16()
-    labels = torch.randint(0, VOCAB, (sample_tokens,), generator=g)
-    old = -torch.rand(1, sample_tokens, generator=g) * 3
-    adv = torch.randn(1, sample_tokens, generator=g)
-    mask = torch.ones(1, sample_tokens, dtype=torch.long)
+    if _CPU_INPUTS.get("n") != sample_tokens:  # synthetic inputs are built once, outside every timed region
+        g = torch.Generator().manual_seed(233376)
+        _CPU_INPUTS.update(
+            n=sample_tokens,
+            hidden=(torch.rand(sample_tokens, HIDDEN, generator=g) - 0.5).bfloat16(),
+            w32=(torch.rand(VOCAB, HIDDEN, generator=g) - 0.5).bfloat16().float(),  # parameter cast: not part of a step
+            labels=torch.randint(0, VOCAB, (sample_tokens,), generator=g),
+            old=-torch.rand(1, sample_tokens, generator=g) * 3,
+            adv=torch.randn(1, sample_tokens, generator=g),
+            mask=(torch.rand(1, sample_tokens, generator=g) < 0.9).long(),
+        )
+    hidden, w32, labels = _CPU_INPUTS["hidden"], _CPU_INPUTS["w32"], _CPU_INPUTS["labels"]
+    old, adv, mask = _CPU_INPUTS["old"], _CPU_INPUTS["adv"], _CPU_INPUTS["mask"]
     best = float("inf")
-    w32 = weight.float()  # the parameter cast is not part of a step
     for _ in range(repeats):
         t0 = time.perf_counter()
         lp, ent = port.lce_forward(hidden, w32, labels, 1.0)
@@ -131,7 +151,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample = args.cpu_tokens
+    sample = args.cpu_tokens or 2048
     times = []
     for i in range(args.warmup + args.steps):
         tps, dt = cpu_reference_sample(sample, threads)
@@ -143,10 +163,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32 (bf16 inputs upcast, CPU)", "data": "synthetic",
-        "config": {"workload": f"Qwen2.5-7B lm-head H={HIDDEN} V={VOCAB}, fused logprob+entropy fwd+bwd + PPO loss; "
-                               f"reference CPU path on a {sample}-token sample per step"},
+        "config": workload_config(args.tokens, max(args.gpus, 1)),
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": "port",
-                         "sample": f"{sample} tokens per step at full H and V (tokens/s is linear in T)"},
+                         "sample": f"{sample}-token sample of the workload per step at full H and V, oracle port of the reference's "
+                                   "chunk-512 CPU path (tokens/s is linear in T)"},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -191,18 +211,42 @@ def run_ours(args):
     weight = (torch.rand(v_local, H, device=dev, generator=wgen) - 0.5).bfloat16().requires_grad_(True)
     host = {k: v.cpu().pin_memory() for k, v in dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d,
                                                      mask=mask_d).items()}
-    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
-    staging = {k: torch.empty_like(v, device=dev) for k, v in host.items()}
+    # end-to-end leg: two staging slots filled by a copy stream, so the H2D copy of step i+1 runs under the compute of
+    # step i (every step's copy is inside the timed region).  With N ranks `hidden` is replicated: each rank copies
+    # only its T/N rows over PCIe and the ranks all-gather the rest over NVLink.
+    assert T % world == 0
+    rows = T // world
+    staging = [{k: torch.empty_like(v, device=dev) for k, v in host.items()} for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    small_bytes = sum(v.numel() * v.element_size() for k, v in host.items() if k != "hidden")
+    h2d_bytes = host["hidden"].numel() * host["hidden"].element_size() + world * small_bytes  # whole job, per step
     metrics_host = torch.empty(8, dtype=torch.float32).pin_memory()
+
+    def enqueue_h2d(slot: int):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])
+            for k in host:
+                if k == "hidden" and world > 1:
+                    sl = slice(rank * rows, (rank + 1) * rows)
+                    staging[slot][k][sl].copy_(host[k][sl], non_blocking=True)
+                else:
+                    staging[slot][k].copy_(host[k], non_blocking=True)
+            ready[slot].record(copy_stream)
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     seg = {"fwd": [], "loss": [], "bwd": []}
 
-    def step(e2e: bool, record: bool):
+    def step(e2e: bool, record: bool, slot: int = 0, prefetch: bool = False):
         if e2e:
-            for k in host:
-                staging[k].copy_(host[k], non_blocking=True)
-            src = staging
+            cur = torch.cuda.current_stream()
+            cur.wait_event(ready[slot])
+            if prefetch:
+                enqueue_h2d(slot ^ 1)
+            src = staging[slot]
+            if world > 1:
+                dist.all_gather_into_tensor(src["hidden"], src["hidden"][rank * rows:(rank + 1) * rows], group=group)
         else:
             src = dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d, mask=mask_d)
         hidden = src["hidden"].detach().requires_grad_(True)
@@ -224,6 +268,7 @@ def run_ours(args):
             marks[3].record()
             seg["_marks"].append(marks)
         if e2e:
+            consumed[slot].record()
             metrics_host.copy_(metrics, non_blocking=True)
             torch.cuda.current_stream().synchronize()  # the host reads the step's loss / metrics
         return metrics
@@ -235,8 +280,10 @@ def run_ours(args):
         torch.cuda.synchronize()
         e0, e1 = ev(), ev()
         e0.record()
-        for _ in range(steps):
-            step(e2e, record)
+        if e2e:
+            enqueue_h2d(0)  # step 0's inputs: inside the timed region, not hidden behind anything
+        for i in range(steps):
+            step(e2e, record, slot=i & 1, prefetch=i + 1 < steps)
         e1.record()
         if world > 1:
             dist.barrier()
@@ -250,6 +297,7 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step(False, False)
+    enqueue_h2d(0)
     step(True, False)
     torch.cuda.synchronize()
 
@@ -276,23 +324,21 @@ def run_ours(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            tps, dt = cpu_reference_sample(args.cpu_tokens, threads)
+            n_cpu = args.cpu_tokens or 4096
+            tps, dt = cpu_reference_sample(n_cpu, threads)
             cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port",
-                   "sample": f"{args.cpu_tokens} tokens at full H and V, fp32 math on bf16 inputs, {dt:.1f} s"}
+                   "sample": f"{n_cpu} tokens at full H and V, fp32 math on bf16 inputs, {dt:.1f} s"}
         line = {
             "metric": METRIC, "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {
-                "workload": f"Qwen2.5-7B lm-head (H={H}, V={V}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
-                            "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
-                "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), "
-                               "all-gather of [4,S,T] partials + all-reduce of d_hidden",
-                "l2": "inputs exceed L2 (hidden 470 MB + weight shard >= 136 MB per step)",
-                "loss": LOSS_CFG,
-            },
+            "config": workload_config(T, world),
             "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32},
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32 * world,
+                    "how": "pinned host -> device on a copy stream, double-buffered (step i+1's inputs copy under step "
+                           "i's compute; every copy is inside the timed region)"
+                           + ("" if world == 1 else f"; each rank copies T/{world} rows of hidden and the ranks "
+                              "all-gather the replicated tensor over NVLink") + "; metrics[8] read back every step"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
@@ -327,7 +373,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--tokens", type=int, default=TOKENS)
-    ap.add_argument("--cpu-tokens", type=int, default=512, help="token sample of the CPU reference arm")
+    ap.add_argument("--cpu-tokens", type=int, default=0,
+                    help="token sample of the CPU legs (0 = 4096 for cpu_baseline, 2048 per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -48,6 +48,18 @@ extern "C" {
 #define VPG_KL_LOW_VAR 3 /* "low_var_kl" / "k3"  */
 #define VPG_KL_NONE (-1)
 
+/* policy-gradient term of vpg_ppo_loss */
+#define VPG_PG_CLIP 0 /* compute_policy_loss, core_algos.py:722-794 (clip + dual-clip) */
+#define VPG_PG_GPG 1  /* compute_policy_loss_gpg, core_algos.py:797-815: -log_prob * advantages */
+
+/* outcome-reward advantage estimators sharing GRPO's skeleton — verl/trainer/ppo/core_algos.py */
+#define VPG_ADV_GRPO 0          /* :245-308 */
+#define VPG_ADV_RLOO 1          /* :425-476 */
+#define VPG_ADV_OPO 2           /* :479-530 */
+#define VPG_ADV_GPG 3           /* :608-667 */
+#define VPG_ADV_RFPP_BASELINE 4 /* :372-422 */
+#define VPG_ADV_GRPO_PASSK 5    /* :309-369 */
+
 const char* vpg_version(void);
 /* last error message of the calling thread ("" if none) */
 const char* vpg_last_error(void);
@@ -161,18 +173,26 @@ int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int
  *   metrics[8] (f32, device): {policy_loss, pg_loss, pg_clipfrac, ppo_kl, pg_clipfrac_lower, entropy_agg, kl_agg,
  *                             mask_sum}
  *   d_log_prob / d_entropy (may be NULL): gradient of policy_loss (incl. loss_scale) wrt log_prob / entropy.
+ *   pg_kind = VPG_PG_GPG replaces the clipped term by -log_prob*advantages (compute_policy_loss_gpg,
+ *   core_algos.py:797-815; the three clip statistics are 0 then, as in the reference).
  *   workspace: vpg_ppo_loss_workspace_bytes(B, L). */
 size_t vpg_ppo_loss_workspace_bytes(int64_t B, int64_t L);
 int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
                  int mask_dtype, const float* entropy, const float* ref_log_prob, int64_t B, int64_t L,
-                 float ratio_lo, float ratio_hi, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
-                 int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy, void* workspace,
-                 size_t workspace_bytes, void* stream);
+                 float ratio_lo, float ratio_hi, float clip_c, int pg_kind, int agg_mode, float entropy_coeff,
+                 float kl_coef, int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy,
+                 void* workspace, size_t workspace_bytes, void* stream);
 
 /* agg_loss forward for an arbitrary loss matrix (core_algos.py:686-719); out[0] = loss; d_loss_mat (may be NULL)
  * receives d loss / d loss_mat.  workspace as vpg_ppo_loss_workspace_bytes. */
 int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_t B, int64_t L, int agg_mode,
                  float* out, float* d_loss_mat, void* workspace, size_t workspace_bytes, void* stream);
+
+/* compute_value_loss (core_algos.py:992-1031): out[0] = vf_loss = 0.5*agg(max((vp-ret)^2, (clip(vp)-ret)^2)),
+ * out[1] = vf_clipfrac; d_vpreds (may be NULL) receives d vf_loss / d vpreds.  workspace as vpg_ppo_loss. */
+int vpg_value_loss(const float* vpreds, const float* returns, const float* values, const void* mask, int mask_dtype,
+                   int64_t B, int64_t L, float cliprange_value, int agg_mode, float* out, float* d_vpreds,
+                   void* workspace, size_t workspace_bytes, void* stream);
 
 /* compute_grpo_outcome_advantage (core_algos.py:245-308): scores = row-sum(rewards); per group (group_ids i32 [B],
  * values in [0,num_groups), built on the host from the uid strings in first-seen order) mean and unbiased std,
@@ -182,6 +202,28 @@ size_t vpg_grpo_workspace_bytes(int64_t B, int64_t num_groups);
 int vpg_grpo_advantage(const float* token_level_rewards, const void* mask, int mask_dtype, const int32_t* group_ids,
                        int64_t B, int64_t L, int64_t num_groups, float epsilon, int norm_by_std, float* advantages,
                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* The other outcome-reward estimators with GRPO's skeleton (kind = VPG_ADV_*): RLOO, OPO, GPG,
+ * REINFORCE++-baseline (followed by masked_whiten over the broadcast matrix, binary masks), GRPO-pass@k.
+ * f_norm is GPG's normaliser.  status[0] (i32, device): 0 ok, 1 / 2 = mask sum 0 / 1 (REINFORCE++-baseline's
+ * masked_whiten raises ValueError), 3 = a pass@k group with fewer than 2 samples (ValueError in the reference).
+ * workspace: vpg_outcome_advantage_workspace_bytes(B, num_groups). */
+size_t vpg_outcome_advantage_workspace_bytes(int64_t B, int64_t num_groups);
+int vpg_outcome_advantage(int kind, const float* token_level_rewards, const void* mask, int mask_dtype,
+                          const int32_t* group_ids, int64_t B, int64_t L, int64_t num_groups, float epsilon,
+                          int norm_by_std, float f_norm, float* advantages, int32_t* status, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
+/* compute_reinforce_plus_plus_outcome_advantage (core_algos.py:533-569): discounted reverse return with reset after
+ * masked-out tokens, advantages = masked_whiten(returns) * mask.  status as vpg_gae.
+ * compute_remax_outcome_advantage (core_algos.py:572-605): returns = reverse cumsum of rewards*mask,
+ * advantages = returns - reward_baselines[b] * mask. */
+size_t vpg_reverse_scan_workspace_bytes(int64_t B, int64_t L);
+int vpg_reinforce_plus_plus(const float* token_level_rewards, const void* mask, int mask_dtype, int64_t B, int64_t L,
+                            float gamma, float* advantages, float* returns, int32_t* status, void* workspace,
+                            size_t workspace_bytes, void* stream);
+int vpg_remax(const float* token_level_rewards, const float* reward_baselines, const void* mask, int mask_dtype,
+              int64_t B, int64_t L, float* advantages, float* returns, void* stream);
 
 /* compute_gae_advantage_return (core_algos.py:193-241): reverse recurrence per row with masked carry-through,
  * returns = adv + values, then masked_whiten (torch_functional.py:206-223) over the whole batch.

@@ -207,6 +207,66 @@ def gen_loss(ref):
     np.savez_compressed(os.path.join(OUT, "loss.npz"), **out)
 
 
+def gen_estimators(ref):
+    """The other registered advantage estimators + value loss + GPG loss."""
+    g = torch.Generator().manual_seed(29)
+    ca = ref.core_algos
+    out = {}
+    B, L = 14, 24
+    mask, lens = _response_mask(B, L, g)
+    rewards = torch.zeros(B, L)
+    rewards[torch.arange(B), lens - 1] = torch.rand(B, generator=g)
+    rewards[3] = 0  # a zero score (GPG's alpha counts non-zero scores)
+    uids = np.array([f"uid-{i // 3:02d}" for i in range(B)], dtype=object)  # groups of 3 + one of 2
+    uids_solo = uids.copy()
+    uids_solo[-1] = "solo"
+    perm = torch.randperm(B, generator=g).numpy()
+    uids, uids_solo = uids[perm], uids_solo[perm]
+    dense = torch.randn(B, L, generator=g) * mask
+    baselines = torch.rand(B, generator=g)
+    out.update(rewards=_np(rewards), mask=_np(mask), uids=np.array([str(u) for u in uids]),
+               uids_solo=np.array([str(u) for u in uids_solo]), dense=_np(dense), baselines=_np(baselines))
+    cfg = {"norm_adv_by_std_in_grpo": True}
+    for tag, rw in (("outcome", rewards), ("dense", dense)):
+        for utag, u in (("", uids), ("_solo", uids_solo)):
+            out[f"rloo_{tag}{utag}"] = _np(ca.compute_rloo_outcome_advantage(rw.clone(), mask, u)[0])
+            out[f"opo_{tag}{utag}"] = _np(ca.compute_opo_outcome_advantage(rw.clone(), mask, u)[0])
+            out[f"gpg_{tag}{utag}"] = _np(ca.compute_gpg_outcome_advantage(rw.clone(), mask, u, f_norm=1.5)[0])
+            out[f"rfppb_{tag}{utag}"] = _np(
+                ca.compute_reinforce_plus_plus_baseline_outcome_advantage(rw.clone(), mask, u)[0])
+        out[f"passk_{tag}_norm1"] = _np(ca.compute_grpo_passk_outcome_advantage(rw.clone(), mask, uids, config=cfg)[0])
+        out[f"passk_{tag}_norm0"] = _np(ca.compute_grpo_passk_outcome_advantage(
+            rw.clone(), mask, uids, config={"norm_adv_by_std_in_grpo": False})[0])
+    # reverse scans on a multi-turn style mask (holes inside the response)
+    holes = (torch.rand(B, L, generator=g) > 0.25).long() * mask
+    out["holes"] = _np(holes)
+    for i, gamma in enumerate((1.0, 0.95)):
+        cfgobj = type("Cfg", (), {"gamma": gamma})()
+        adv, ret = ca.compute_reinforce_plus_plus_outcome_advantage(dense.clone(), holes, config=cfgobj)
+        out[f"rfpp_gamma{i}"], out[f"rfpp_adv{i}"], out[f"rfpp_ret{i}"] = np.array(gamma), _np(adv), _np(ret)
+    adv, ret = ca.compute_remax_outcome_advantage(dense.clone(), baselines, holes)
+    out["remax_adv"], out["remax_ret"] = _np(adv), _np(ret)
+    # value loss and GPG policy loss, every aggregation mode, with gradients
+    vpreds = torch.randn(B, L, generator=g)
+    values = vpreds + 0.3 * torch.randn(B, L, generator=g)
+    rets = values + 0.5 * torch.randn(B, L, generator=g)
+    lp = -torch.rand(B, L, generator=g) * 3
+    adv = torch.randn(B, L, generator=g)
+    out.update(vpreds=_np(vpreds), values=_np(values), rets=_np(rets), lp=_np(lp), adv=_np(adv))
+    for mode in ["token-mean", "seq-mean-token-sum", "seq-mean-token-mean", "seq-mean-token-sum-norm"]:
+        vp = vpreds.clone().requires_grad_(True)
+        vf, frac = ca.compute_value_loss(vp, rets, values, mask, cliprange_value=0.2, loss_agg_mode=mode)
+        vf.backward()
+        out[f"vf|{mode}"] = np.array([_np(vf), _np(frac)], dtype=np.float32)
+        out[f"vf_grad|{mode}"] = _np(vp.grad)
+        lpg = lp.clone().requires_grad_(True)
+        loss = ca.compute_policy_loss_gpg(None, lpg, adv, mask, loss_agg_mode=mode)[0]
+        loss.backward()
+        out[f"gpg_loss|{mode}"] = _np(loss)
+        out[f"gpg_loss_grad|{mode}"] = _np(lpg.grad)
+    np.savez_compressed(os.path.join(OUT, "estimators.npz"), **out)
+
+
 def gen_rmpad(ref):
     import flash_attn.bert_padding as bp  # third-party pure-torch file, v2.8.3 in this image
 
@@ -246,7 +306,10 @@ def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_rmpad):
+    only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_rmpad):
+        if only and fn.__name__[4:] not in only:
+            continue
         fn(ref)
         print("wrote", fn.__name__)
     for f in sorted(os.listdir(OUT)):

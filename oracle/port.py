@@ -191,6 +191,95 @@ def grpo_outcome_advantage(token_level_rewards, response_mask, index, epsilon=1e
     return out.unsqueeze(-1) * response_mask
 
 
+def _group_rows(index):
+    gid, n = group_ids(index)
+    return [np.flatnonzero(gid == g) for g in range(n)]
+
+
+def rloo_outcome_advantage(token_level_rewards, response_mask, index):
+    """verl/trainer/ppo/core_algos.py:425-476: leave-one-out baseline, written as score*n/(n-1) - mean*n/(n-1)."""
+    scores = token_level_rewards.sum(dim=-1)
+    out = scores.clone()
+    for rows in _group_rows(index):
+        n = len(rows)
+        if n > 1:
+            vals = scores[rows]
+            out[rows] = vals * n / (n - 1) - vals.mean() * n / (n - 1)
+    return out.unsqueeze(-1) * response_mask
+
+
+def opo_outcome_advantage(token_level_rewards, response_mask, index):
+    """verl/trainer/ppo/core_algos.py:479-530: baseline = sum(len*score)/sum(len) of the uid group (0 for singletons)."""
+    scores = token_level_rewards.sum(dim=-1)
+    lens = response_mask.sum(dim=-1)
+    out = scores.clone()
+    for rows in _group_rows(index):
+        if len(rows) > 1:
+            ln = lens[rows]
+            out[rows] = scores[rows] - (ln * scores[rows]).sum() / ln.sum()
+    return out.unsqueeze(-1) * response_mask
+
+
+def gpg_outcome_advantage(token_level_rewards, response_mask, index, f_norm=1.0):
+    """verl/trainer/ppo/core_algos.py:608-667: alpha*(score - group mean)/f_norm, alpha = B / max(#nonzero scores, 1)."""
+    scores = token_level_rewards.sum(dim=-1)
+    alpha = scores.shape[0] / torch.count_nonzero(scores).clamp(min=1)
+    out = scores.clone()
+    for rows in _group_rows(index):
+        mean = scores[rows].mean() if len(rows) > 1 else torch.tensor(0.0)
+        out[rows] = alpha * (scores[rows] - mean) / f_norm
+    return out.unsqueeze(-1) * response_mask
+
+
+def reinforce_plus_plus_baseline_outcome_advantage(token_level_rewards, response_mask, index):
+    """verl/trainer/ppo/core_algos.py:372-422: score - group mean, tiled * mask, masked_whiten, * mask."""
+    L = token_level_rewards.shape[-1]
+    scores = token_level_rewards.sum(dim=-1)
+    out = scores.clone()
+    for rows in _group_rows(index):
+        if len(rows) > 1:
+            out[rows] = scores[rows] - scores[rows].mean()
+    tiled = out.unsqueeze(-1).tile([1, L]) * response_mask
+    return masked_whiten(tiled, response_mask) * response_mask
+
+
+def grpo_passk_outcome_advantage(token_level_rewards, response_mask, index, epsilon=1e-6, norm_adv_by_std_in_grpo=True):
+    """verl/trainer/ppo/core_algos.py:309-369: the best response of each group gets r_max - r_second_max
+    (/ (std + eps) when normalised), every other response 0; a group of fewer than 2 raises ValueError."""
+    scores = token_level_rewards.sum(dim=-1)
+    out = torch.zeros_like(scores)
+    for rows in _group_rows(index):
+        if len(rows) < 2:
+            raise ValueError("Pass@k requires at least 2 samples per group.")
+        vals = scores[rows]
+        order = torch.argsort(vals, descending=True, stable=True)
+        a = vals[order[0]] - vals[order[1]]
+        if norm_adv_by_std_in_grpo:
+            a = a / (vals.std() + epsilon)
+        out[rows[order[0]]] = a
+    return out.unsqueeze(-1) * response_mask
+
+
+def reinforce_plus_plus_outcome_advantage(token_level_rewards, response_mask, gamma):
+    """verl/trainer/ppo/core_algos.py:533-569: R_t = r_t + gamma * run; run = R_t * m_t (reset after EOS);
+    advantages = masked_whiten(returns) * mask."""
+    B, L = token_level_rewards.shape
+    returns = torch.zeros_like(token_level_rewards)
+    run = torch.zeros(B)
+    for t in range(L - 1, -1, -1):
+        run = token_level_rewards[:, t] + gamma * run
+        returns[:, t] = run
+        run = run * response_mask[:, t]
+    return masked_whiten(returns, response_mask) * response_mask, returns
+
+
+def remax_outcome_advantage(token_level_rewards, reward_baselines, response_mask):
+    """verl/trainer/ppo/core_algos.py:572-605: suffix sums of the masked rewards minus the per-row baseline."""
+    masked = (token_level_rewards * response_mask).numpy()
+    returns = torch.from_numpy(np.ascontiguousarray(np.cumsum(masked[:, ::-1], axis=-1, dtype=np.float32)[:, ::-1]))
+    return returns - reward_baselines.unsqueeze(-1) * response_mask, returns
+
+
 def gae_advantage_return(token_level_rewards, values, response_mask, gamma, lam):
     """verl/trainer/ppo/core_algos.py:193-241: reverse recurrence with masked carry-through, returns = adv + values,
     then masked_whiten(adv)."""
@@ -242,6 +331,20 @@ def policy_loss(old_log_prob, log_prob, advantages, response_mask, cliprange=Non
     pg_clipfrac_lower = masked_mean(torch.gt(worst, dual) * (advantages < 0).float(), response_mask)
     per_token = torch.where(advantages < 0, capped, worst)
     return agg_loss(per_token, response_mask, loss_agg_mode), pg_clipfrac, ppo_kl, pg_clipfrac_lower
+
+
+def policy_loss_gpg(log_prob, advantages, response_mask, loss_agg_mode="token-mean"):
+    """verl/trainer/ppo/core_algos.py:797-815"""
+    return agg_loss(-log_prob * advantages, response_mask, loss_agg_mode)
+
+
+def value_loss(vpreds, returns, values, response_mask, cliprange_value, loss_agg_mode="token-mean"):
+    """verl/trainer/ppo/core_algos.py:992-1031 (clip_by_value: verl/utils/torch_functional.py:136-142)"""
+    clipped = torch.max(torch.min(vpreds, values + cliprange_value), values - cliprange_value)
+    plain_err = (vpreds - returns) ** 2
+    clipped_err = (clipped - returns) ** 2
+    vf_loss = 0.5 * agg_loss(torch.max(plain_err, clipped_err), response_mask, loss_agg_mode)
+    return vf_loss, masked_mean(torch.gt(clipped_err, plain_err).float(), response_mask)
 
 
 def kl_penalty(logprob, ref_logprob, kind):

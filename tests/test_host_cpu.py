@@ -46,7 +46,7 @@ def test_host_only_entry_points():
     # argument validation happens before any CUDA call
     rc = lib.vpg_lce_fwd_partials(None, None, None, 128, 100, 1000, 1.0, 0, 1, None, None)
     assert rc == -1 and b"multiple of 64" in lib.vpg_last_error()
-    rc = lib.vpg_ppo_loss(None, None, None, None, 0, None, None, 4, 4, 0.8, 1.2, 3.0, 0, 0.0, 0.0, -1, 1.0, None, None,
+    rc = lib.vpg_ppo_loss(None, None, None, None, 0, None, None, 4, 4, 0.8, 1.2, 3.0, 0, 0, 0.0, 0.0, -1, 1.0, None, None,
                           None, None, 0, None)
     assert rc == -1
 

@@ -65,9 +65,27 @@ SIGNATURES: dict[str, tuple] = {
     "vpg_ppo_loss": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float,
-         c_float, c_int, c_float, c_float, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+         c_float, c_int, c_int, c_float, c_float, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
          c_void_p],
     ),
+    "vpg_value_loss": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p,
+         c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_outcome_advantage_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "vpg_outcome_advantage": (
+        c_int,
+        [c_int, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64, c_int64, c_float, c_int, c_float, c_void_p,
+         c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_reverse_scan_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "vpg_reinforce_plus_plus": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+         c_void_p],
+    ),
+    "vpg_remax": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "vpg_agg_loss": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
@@ -97,6 +115,8 @@ AGG_MODES = {
     "seq-mean-token-mean": 2,
     "seq-mean-token-sum-norm": 3,
 }
+PG_KINDS = {"clip": 0, "gpg": 1}
+ADV_KINDS = {"grpo": 0, "rloo": 1, "opo": 2, "gpg": 3, "reinforce_plus_plus_baseline": 4, "grpo_passk": 5}
 KL_KINDS = {"kl": 0, "k1": 0, "abs": 1, "mse": 2, "k2": 2, "low_var_kl": 3, "k3": 3}
 
 _lib = None

@@ -1,0 +1,442 @@
+// Outcome-reward advantage estimators that share GRPO's skeleton (row score -> per-uid group statistics -> per-row
+// scalar -> broadcast * mask) and the two reverse-scan estimators (REINFORCE++, ReMax).
+// Reference: verl/trainer/ppo/core_algos.py
+//   GRPO :245-308, GRPO-PassK :309-369, REINFORCE++-baseline :372-422, RLOO :425-476, OPO :479-530,
+//   REINFORCE++ :533-569, ReMax :572-605, GPG :608-667.
+// The reference evaluates all of these with Python loops over the batch (and over time steps for REINFORCE++) on
+// the driver CPU.  Here: one coalesced sweep for the row statistics (128-bit loads), one single-block kernel for the
+// group statistics (B <= a few thousand rows: latency-bound, fp64 atomics in shared/global memory), one coalesced
+// sweep that writes the [B,L] advantage.  Compiled with --fmad=false like token_ops.cu.
+#include <cuda_runtime.h>
+
+#include "token_common.cuh"
+
+namespace vpg {
+
+// -------------------------------------------------------------------------------------------------------------
+// row statistics: score[b] = sum_t rewards[b,t] (NOT masked, core_algos.py:281), len[b] = sum_t mask[b,t]
+// -------------------------------------------------------------------------------------------------------------
+template <int VEC, typename MT>
+__global__ void row_score_len_kernel(const float* __restrict__ rewards, const MT* __restrict__ mask, long long L, int gx,
+                                     double* __restrict__ scores, double* __restrict__ lens) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    float s = 0.f, c = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const Pack<VEC> v = ldv<VEC>(rewards, base + t);
+        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            s += v.v[j];
+            c += m.v[j];
+        }
+    }
+    const double bs = block_sum<double>(static_cast<double>(s), red);
+    const double bc = block_sum<double>(static_cast<double>(c), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&scores[b], bs);
+        atomicAdd(&lens[b], bc);
+    }
+}
+
+// order-preserving map float -> uint32 (larger float <=> larger key)
+__device__ __forceinline__ unsigned int float_key(float f) {
+    const unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(unsigned int k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+constexpr int kGStat = 5;  // per group: count, sum, M2 (squared deviations), sum(len), sum(len*score)
+
+// single block.  gstat [kGStat*G] doubles and top [2*G] u64 are zeroed by the caller.
+__global__ void __launch_bounds__(1024)
+outcome_group_kernel(int kind, const double* __restrict__ scores, const double* __restrict__ lens,
+                     const int* __restrict__ gid, long long B, long long G, float eps, int norm_by_std, float f_norm,
+                     double* __restrict__ gstat, unsigned long long* __restrict__ top, float* __restrict__ adv_row,
+                     int* __restrict__ status) {
+    __shared__ double red[32];
+    __shared__ double bc[4];
+    // pass 1: count / sum (+ length-weighted sums, + group arg-max).  Scores are rounded to fp32 first: the reference
+    // holds them in an fp32 tensor.
+    double nnz_local = 0.0;
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const float sf = static_cast<float>(scores[i]);
+        const double s = static_cast<double>(sf);
+        atomicAdd(&gstat[kGStat * g + 0], 1.0);
+        atomicAdd(&gstat[kGStat * g + 1], s);
+        if (kind == VPG_ADV_OPO) {
+            const double len = lens[i];
+            atomicAdd(&gstat[kGStat * g + 3], len);
+            // fp32 product as in (len_tensor * score_tensor), core_algos.py:522
+            atomicAdd(&gstat[kGStat * g + 4], static_cast<double>(static_cast<float>(len) * sf));
+        }
+        if (kind == VPG_ADV_GRPO_PASSK) {
+            const unsigned long long key = (static_cast<unsigned long long>(float_key(sf)) << 32) |
+                                           static_cast<unsigned long long>(0xffffffffu - static_cast<unsigned int>(i));
+            atomicMax(&top[g], key);
+        }
+        if (sf != 0.f) nnz_local += 1.0;
+    }
+    __syncthreads();
+    const double nnz = block_sum<double>(nnz_local, red);
+    if (threadIdx.x == 0) bc[0] = nnz;
+    // pass 2: squared deviations from the group mean (+ runner-up for pass@k)
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const double n = gstat[kGStat * g + 0];
+        const double mean = gstat[kGStat * g + 1] / n;
+        const float sf = static_cast<float>(scores[i]);
+        const double d = static_cast<double>(sf) - mean;
+        atomicAdd(&gstat[kGStat * g + 2], d * d);
+        if (kind == VPG_ADV_GRPO_PASSK) {
+            const unsigned int arg = 0xffffffffu - static_cast<unsigned int>(top[g] & 0xffffffffull);
+            if (static_cast<unsigned int>(i) != arg) {
+                const unsigned long long key = (static_cast<unsigned long long>(float_key(sf)) << 32) |
+                                               static_cast<unsigned long long>(0xffffffffu - static_cast<unsigned int>(i));
+                atomicMax(&top[G + g], key);
+            }
+            if (n < 2.0) status[0] = 3;  // "Pass@k requires at least 2 samples per group" (core_algos.py:355-358)
+        }
+    }
+    __syncthreads();
+    // pass 3: per-row scalar
+    double w1 = 0.0, wn = 0.0;  // REINFORCE++-baseline: sum len*s, sum len
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const int g = gid[i];
+        const double n = gstat[kGStat * g + 0];
+        const float sc = static_cast<float>(scores[i]);
+        const bool single = n <= 1.0;
+        const float mean = single ? 0.f : static_cast<float>(gstat[kGStat * g + 1] / n);
+        const float stdv = single ? 1.f : static_cast<float>(sqrt(gstat[kGStat * g + 2] / (n - 1.0)));  // torch.std
+        float a;
+        if (kind == VPG_ADV_GRPO) {
+            a = norm_by_std ? (sc - mean) / (stdv + eps) : (sc - mean);
+        } else if (kind == VPG_ADV_RLOO) {
+            // scores[i] * n / (n - 1) - mean * n / (n - 1)  for n > 1, unchanged otherwise (core_algos.py:467-471)
+            const float nf = static_cast<float>(n), n1 = static_cast<float>(n - 1.0);
+            a = single ? sc : (sc * nf / n1 - mean * nf / n1);
+        } else if (kind == VPG_ADV_OPO) {
+            const float bsl = single ? 0.f
+                                     : static_cast<float>(gstat[kGStat * g + 4]) / static_cast<float>(gstat[kGStat * g + 3]);
+            a = sc - bsl;
+        } else if (kind == VPG_ADV_GPG) {
+            // alpha = bsz / count_nonzero(scores).clamp(min=1)  (core_algos.py:646-647)
+            const float alpha = static_cast<float>(B) / static_cast<float>(fmax(bc[0], 1.0));
+            a = alpha * (sc - mean) / f_norm;
+        } else if (kind == VPG_ADV_RFPP_BASELINE) {
+            a = sc - mean;
+            w1 += lens[i] * static_cast<double>(a);
+            wn += lens[i];
+        } else {  // pass@k: only the best response of a group gets r_max - r_second_max (core_algos.py:359-366)
+            const unsigned long long k1 = top[g], k2 = top[G + g];
+            const unsigned int arg = 0xffffffffu - static_cast<unsigned int>(k1 & 0xffffffffull);
+            a = 0.f;
+            if (static_cast<unsigned int>(i) == arg && n >= 2.0) {
+                a = key_float(static_cast<unsigned int>(k1 >> 32)) - key_float(static_cast<unsigned int>(k2 >> 32));
+                if (norm_by_std) a = a / (stdv + eps);
+            }
+        }
+        adv_row[i] = a;
+    }
+    if (kind != VPG_ADV_RFPP_BASELINE) return;
+    // masked_whiten of the broadcast matrix in closed form (binary masks): every valid token of row i holds s_i
+    //   mean = sum_i len_i s_i / (N + 1e-8);  var = sum_i len_i (s_i - mean)^2 / (N + 1e-8) * N / (N - 1)
+    const double S1 = block_sum<double>(w1, red);
+    const double N = block_sum<double>(wn, red);
+    if (threadIdx.x == 0) bc[1] = S1, bc[2] = N;
+    __syncthreads();
+    const double Nn = bc[2];
+    if (Nn == 0.0 || Nn == 1.0) {
+        if (threadIdx.x == 0) status[0] = (Nn == 0.0) ? 1 : 2;  // masked_var raises (torch_functional.py:195-200)
+        return;
+    }
+    const double mean_w = bc[1] / (Nn + 1e-8);
+    double v = 0.0;
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+        const double d = static_cast<double>(adv_row[i]) - mean_w;
+        v += lens[i] * d * d;
+    }
+    __syncthreads();
+    const double V = block_sum<double>(v, red);
+    if (threadIdx.x == 0) bc[3] = V;
+    __syncthreads();
+    const double var = bc[3] / (Nn + 1e-8) * (Nn / (Nn - 1.0));
+    const float meanf = static_cast<float>(mean_w);
+    const float rstd = rsqrtf(static_cast<float>(var) + 1e-8f);
+    for (long long i = threadIdx.x; i < B; i += blockDim.x) adv_row[i] = (adv_row[i] - meanf) * rstd;
+}
+
+// out[b,t] = row_val[b] * mask[b,t] (- is never needed); optional second output gets the same values
+template <int VEC, typename MT>
+__global__ void row_broadcast_kernel(const float* __restrict__ row_val, const MT* __restrict__ mask, long long L, int gx,
+                                     float* __restrict__ out) {
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    const float a = row_val[b];
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+        Pack<VEC> o;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) o.v[j] = a * m.v[j];
+        stv<VEC>(out, base + t, o);
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// Reverse scans.  One block per row, each thread owns kScanSeg contiguous tokens in registers; the recurrence on the
+// running value is affine per token (run' = a*run + b), so segments compose, a block-wide right-to-left exclusive
+// scan gives each segment its incoming value, and the segment is replayed in the reference's operation order.
+//   MODE 0  REINFORCE++ (core_algos.py:557-563): R_t = r_t + gamma*run ; run = R_t * m_t          (a = m*gamma, b = m*r)
+//   MODE 1  ReMax       (core_algos.py:601):      run = run + r_t*m_t ; R_t = run                   (a = 1,       b = r*m)
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kScanSeg = 8;
+
+struct Lin {
+    float a, b;
+};
+// h = g after f
+__device__ __forceinline__ Lin lin_compose(const Lin& g, const Lin& f) { return Lin{g.a * f.a, g.a * f.b + g.b}; }
+__device__ __forceinline__ Lin lin_shfl_down(const Lin& x, int d) {
+    return Lin{__shfl_down_sync(0xffffffffu, x.a, d), __shfl_down_sync(0xffffffffu, x.b, d)};
+}
+
+template <typename MT, int MODE>
+__global__ void __launch_bounds__(512)
+reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ mask, const float* __restrict__ baselines,
+                    long long L, float gamma, float* __restrict__ adv_out, float* __restrict__ ret_out,
+                    double* __restrict__ sums) {
+    __shared__ Lin warp_maps[32];
+    __shared__ float carry;
+    __shared__ double red[32];
+    const long long base = static_cast<long long>(blockIdx.x) * L;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const long long span = static_cast<long long>(blockDim.x) * kScanSeg;
+    const float bsl = (MODE == 1) ? baselines[blockIdx.x] : 0.f;
+    if (threadIdx.x == 0) carry = 0.f;
+    float s1 = 0.f, s2 = 0.f, sc = 0.f;
+    const long long n_chunks = (L + span - 1) / span;
+    for (long long ck = n_chunks - 1; ck >= 0; --ck) {
+        __syncthreads();
+        const long long t0 = ck * span + static_cast<long long>(threadIdx.x) * kScanSeg;
+        float r[kScanSeg], m[kScanSeg];
+#pragma unroll
+        for (int j = 0; j < kScanSeg; ++j) {
+            const long long t = t0 + j;
+            const bool ok = t < L;
+            r[j] = ok ? rewards[base + t] : 0.f;
+            m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps (see below)
+        }
+        Lin seg{1.f, 0.f};
+#pragma unroll
+        for (int j = kScanSeg - 1; j >= 0; --j) {
+            const bool ok = (t0 + j) < L;
+            Lin st;
+            if (MODE == 0) {
+                st.a = ok ? m[j] * gamma : 1.f;
+                st.b = ok ? m[j] * r[j] : 0.f;
+            } else {
+                st.a = 1.f;
+                st.b = r[j] * m[j];
+            }
+            seg = lin_compose(st, seg);
+        }
+        Lin inc = seg;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const Lin o = lin_shfl_down(inc, d);
+            if (lane + d < 32) inc = lin_compose(inc, o);
+        }
+        if (lane == 0) warp_maps[w] = inc;
+        __syncthreads();
+        Lin right{1.f, 0.f};
+        for (int ww = nw - 1; ww > w; --ww) right = lin_compose(warp_maps[ww], right);
+        Lin excl = lin_shfl_down(inc, 1);
+        if (lane == 31) excl = Lin{1.f, 0.f};
+        excl = lin_compose(excl, right);
+        float run = excl.a * carry + excl.b;
+        float R[kScanSeg];
+#pragma unroll
+        for (int j = kScanSeg - 1; j >= 0; --j) {
+            if ((t0 + j) < L) {
+                if (MODE == 0) {
+                    R[j] = r[j] + gamma * run;
+                    run = R[j] * m[j];
+                } else {
+                    run = run + r[j] * m[j];
+                    R[j] = run;
+                }
+            } else {
+                R[j] = 0.f;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kScanSeg; ++j) {
+            const long long t = t0 + j;
+            if (t < L) {
+                ret_out[base + t] = R[j];
+                if (MODE == 0) {
+                    const bool on = m[j] != 0.f;
+                    s1 += (on ? R[j] : 0.f) * m[j];
+                    s2 += (on ? R[j] * R[j] : 0.f) * m[j];
+                    sc += m[j];
+                } else {
+                    adv_out[base + t] = R[j] - bsl * m[j];
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) carry = run;
+    }
+    if (MODE == 0) {
+        const double d1 = block_sum<double>(static_cast<double>(s1), red);
+        const double d2 = block_sum<double>(static_cast<double>(s2), red);
+        const double dc = block_sum<double>(static_cast<double>(sc), red);
+        if (threadIdx.x == 0) {
+            atomicAdd(&sums[0], d1);
+            atomicAdd(&sums[1], d2);
+            atomicAdd(&sums[2], dc);
+        }
+    }
+}
+
+// advantages = masked_whiten(returns, mask) * mask  (core_algos.py:565-566; torch_functional.py:206-223)
+template <int VEC, typename MT>
+__global__ void whiten_mask_apply_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
+                                         const double* __restrict__ sums, float* __restrict__ out,
+                                         int* __restrict__ status) {
+    const double N = sums[2];
+    if (N == 0.0 || N == 1.0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = (N == 0.0) ? 1 : 2;
+        return;
+    }
+    const double den = N + 1e-8;
+    const double mean_d = sums[0] / den;
+    double var_d = (sums[1] - 2.0 * mean_d * sums[0] + mean_d * mean_d * N) / den;
+    var_d = var_d * (N / (N - 1.0));
+    const float mean = static_cast<float>(mean_d);
+    const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-8f);
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
+        Pack<VEC> v = ldv<VEC>(values, i);
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) v.v[j] = ((v.v[j] - mean) * rstd) * m.v[j];
+        stv<VEC>(out, i, v);
+    }
+}
+
+}  // namespace vpg
+
+using namespace vpg;
+
+extern "C" {
+
+size_t vpg_outcome_advantage_workspace_bytes(int64_t B, int64_t G) {
+    const size_t b = static_cast<size_t>(B > 0 ? B : 0), g = static_cast<size_t>(G > 0 ? G : 0);
+    return (2 * b + kGStat * g + 2 * g) * sizeof(double) + b * sizeof(float) + 16;
+}
+
+int vpg_outcome_advantage(int kind, const float* rewards, const void* mask, int mask_dtype, const int32_t* group_ids,
+                          int64_t B, int64_t L, int64_t G, float epsilon, int norm_by_std, float f_norm,
+                          float* advantages, int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(rewards && mask && group_ids && advantages && status, "null pointer argument");
+    VPG_CHECK_ARG(kind >= VPG_ADV_GRPO && kind <= VPG_ADV_GRPO_PASSK, "unknown outcome advantage kind %d", kind);
+    VPG_CHECK_ARG(B > 0 && L > 0 && G > 0 && G <= B, "invalid shape B=%lld L=%lld groups=%lld", (long long)B,
+                  (long long)L, (long long)G);
+    VPG_CHECK_ARG(B < (1ll << 31), "batch too large");
+    const size_t need = vpg_outcome_advantage_workspace_bytes(B, G);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "outcome advantage workspace too small: need %zu, got %zu", need,
+                         workspace_bytes);
+    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 7) == 0, "workspace must be 8-byte aligned");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* scores = static_cast<double*>(workspace);
+    double* lens = scores + B;
+    double* gstat = lens + B;
+    unsigned long long* top = reinterpret_cast<unsigned long long*>(gstat + kGStat * G);
+    float* adv_row = reinterpret_cast<float*>(top + 2 * G);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, static_cast<size_t>(2 * B + (kGStat + 2) * G) * sizeof(double), stream));
+    VPG_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {rewards, advantages});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            row_score_len_kernel<4, MT><<<grid, kThreads, 0, stream>>>(rewards, mk, L, gx, scores, lens);
+        else
+            row_score_len_kernel<1, MT><<<grid, kThreads, 0, stream>>>(rewards, mk, L, gx, scores, lens);
+        count_launch();
+        outcome_group_kernel<<<1, 1024, 0, stream>>>(kind, scores, lens, group_ids, B, G, epsilon, norm_by_std, f_norm,
+                                                     gstat, top, adv_row, status);
+        count_launch();
+        if (vec)
+            row_broadcast_kernel<4, MT><<<grid, kThreads, 0, stream>>>(adv_row, mk, L, gx, advantages);
+        else
+            row_broadcast_kernel<1, MT><<<grid, kThreads, 0, stream>>>(adv_row, mk, L, gx, advantages);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+size_t vpg_reverse_scan_workspace_bytes(int64_t B, int64_t L) {
+    (void)B;
+    (void)L;
+    return 4 * sizeof(double);
+}
+
+static inline unsigned scan_threads(int64_t L) {
+    int64_t threads = round_up(ceil_div(L, kScanSeg), 32);
+    if (threads > 512) threads = 512;
+    return static_cast<unsigned>(threads);
+}
+
+int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dtype, int64_t B, int64_t L, float gamma,
+                            float* advantages, float* returns, int32_t* status, void* workspace,
+                            size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(rewards && mask && advantages && returns && status, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    if (!workspace || workspace_bytes < vpg_reverse_scan_workspace_bytes(B, L))
+        return set_error(VPG_ERR_WORKSPACE, "reinforce++ workspace too small");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* sums = static_cast<double*>(workspace);
+    VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
+    VPG_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
+    const int64_t n = B * L;
+    const bool vec = rows_vec_ok(n, mask, mask_dtype, {returns, advantages});
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        reverse_scan_kernel<MT, 0><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
+            rewards, mk, nullptr, L, gamma, advantages, returns, sums);
+        count_launch();
+        if (vec)
+            whiten_mask_apply_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(returns, mk, n, sums, advantages, status);
+        else
+            whiten_mask_apply_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(returns, mk, n, sums, advantages, status);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_remax(const float* rewards, const float* reward_baselines, const void* mask, int mask_dtype, int64_t B,
+              int64_t L, float* advantages, float* returns, void* stream_) {
+    VPG_CHECK_ARG(rewards && reward_baselines && mask && advantages && returns, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        reverse_scan_kernel<MT, 1><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
+            rewards, static_cast<const MT*>(mask), reward_baselines, L, 1.f, advantages, returns, nullptr);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+}  // extern "C"

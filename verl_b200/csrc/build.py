@@ -20,8 +20,8 @@ LIB_DIR = PKG / "lib"
 BUILD_DIR = CSRC / "build"
 LIB_PATH = LIB_DIR / "libvpg_b200.so"
 
-SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "rmpad.cu", "logits_ops.cu"]
-HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "../../include/vpg_b200.h"]
+SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu"]
+HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "token_common.cuh", "../../include/vpg_b200.h"]
 
 NVCC_FLAGS = [
     "-gencode",
@@ -58,10 +58,10 @@ def _fingerprint(flags_per_src: dict[str, list[str]]) -> str:
 
 def _flags_for(src: str) -> list[str]:
     flags = list(NVCC_FLAGS)
-    if src in ("token_ops.cu", "rmpad.cu", "logits_ops.cu"):
+    if src in ("token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu"):
         # bit-faithful fp32 arithmetic for the parity-critical memory-bound ops
         flags.remove("--use_fast_math")
-        flags += ["--fmad=false"] if src == "token_ops.cu" else []
+        flags += ["--fmad=false"] if src in ("token_ops.cu", "adv_ops.cu") else []
     return flags
 
 

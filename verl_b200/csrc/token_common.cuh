@@ -1,0 +1,94 @@
+// Shared device / host helpers of the memory-bound token kernels (token_ops.cu, adv_ops.cu): 128-bit packs, grid
+// sizing, the "last block done" finalisation pattern.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <initializer_list>
+
+#include "common.h"
+#include "reduce.cuh"
+
+namespace vpg {
+
+constexpr int kThreads = 256;
+
+template <int VEC>
+struct Pack {
+    float v[VEC];
+};
+
+template <int VEC>
+__device__ __forceinline__ Pack<VEC> ldv(const float* __restrict__ p, long long i) {
+    Pack<VEC> r;
+    if constexpr (VEC == 4) {
+        const float4 a = load_f4(p, i);
+        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
+    } else {
+        r.v[0] = p[i];
+    }
+    return r;
+}
+template <int VEC, typename MT>
+__device__ __forceinline__ Pack<VEC> ldm(const MT* __restrict__ p, long long i) {
+    Pack<VEC> r;
+    if constexpr (VEC == 4) {
+        const float4 a = load_mask4<MT>(p, i);
+        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
+    } else {
+        r.v[0] = mask_to_float(p[i]);
+    }
+    return r;
+}
+template <int VEC>
+__device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pack<VEC>& r) {
+    if constexpr (VEC == 4) {
+        store_f4(p, i, make_float4(r.v[0], r.v[1], r.v[2], r.v[3]));
+    } else {
+        p[i] = r.v[0];
+    }
+}
+
+// blocks per row so that the grid has >= ~4 waves when the problem is large enough, never more than needed
+static inline int blocks_per_row(int64_t B, int64_t L, int vec) {
+    const int64_t per_block = static_cast<int64_t>(kThreads) * vec * 2;
+    int64_t need = ceil_div(L, per_block);
+    int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * 8, B > 0 ? B : 1);
+    int64_t g = need < want ? need : want;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+
+// "last block done": returns true in every thread of the block that arrives last
+__device__ __forceinline__ bool last_block_done(unsigned int* counter, unsigned int total) {
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(counter, 1u);
+        is_last = (prev == total - 1);
+    }
+    __syncthreads();
+    if (is_last) __threadfence();
+    return is_last;
+}
+
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+static inline int flat_grid(int64_t n, int vec) {
+    int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    if (g > cap) g = cap;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+
+
+// vector path requires 16-byte aligned rows
+static inline bool rows_vec_ok(int64_t L, const void* mask, int mask_dtype, std::initializer_list<const void*> ptrs) {
+    if (L % 4 != 0) return false;
+    if (mask && !mask_aligned(mask, mask_dtype)) return false;
+    for (const void* p : ptrs)
+        if (p && !aligned16(p)) return false;
+    return true;
+}
+
+
+}  // namespace vpg

@@ -9,71 +9,9 @@
 // that elementwise results follow the reference's separately rounded fp32 operations.
 #include <cuda_runtime.h>
 
-#include "common.h"
-#include "reduce.cuh"
+#include "token_common.cuh"
 
 namespace vpg {
-
-constexpr int kThreads = 256;
-
-template <int VEC>
-struct Pack {
-    float v[VEC];
-};
-
-template <int VEC>
-__device__ __forceinline__ Pack<VEC> ldv(const float* __restrict__ p, long long i) {
-    Pack<VEC> r;
-    if constexpr (VEC == 4) {
-        const float4 a = load_f4(p, i);
-        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
-    } else {
-        r.v[0] = p[i];
-    }
-    return r;
-}
-template <int VEC, typename MT>
-__device__ __forceinline__ Pack<VEC> ldm(const MT* __restrict__ p, long long i) {
-    Pack<VEC> r;
-    if constexpr (VEC == 4) {
-        const float4 a = load_mask4<MT>(p, i);
-        r.v[0] = a.x, r.v[1] = a.y, r.v[2] = a.z, r.v[3] = a.w;
-    } else {
-        r.v[0] = mask_to_float(p[i]);
-    }
-    return r;
-}
-template <int VEC>
-__device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pack<VEC>& r) {
-    if constexpr (VEC == 4) {
-        store_f4(p, i, make_float4(r.v[0], r.v[1], r.v[2], r.v[3]));
-    } else {
-        p[i] = r.v[0];
-    }
-}
-
-// blocks per row so that the grid has >= ~4 waves when the problem is large enough, never more than needed
-static inline int blocks_per_row(int64_t B, int64_t L, int vec) {
-    const int64_t per_block = static_cast<int64_t>(kThreads) * vec * 2;
-    int64_t need = ceil_div(L, per_block);
-    int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * 8, B > 0 ? B : 1);
-    int64_t g = need < want ? need : want;
-    return static_cast<int>(g < 1 ? 1 : g);
-}
-
-// "last block done": returns true in every thread of the block that arrives last
-__device__ __forceinline__ bool last_block_done(unsigned int* counter, unsigned int total) {
-    __shared__ bool is_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int prev = atomicAdd(counter, 1u);
-        is_last = (prev == total - 1);
-    }
-    __syncthreads();
-    if (is_last) __threadfence();
-    return is_last;
-}
 
 // =====================================================================================================
 // masked_sum (verl/utils/torch_functional.py:163-168): out[0] = sum(where(m!=0, v, 0) * m), out[1] = sum(m)
@@ -129,7 +67,6 @@ __global__ void masked_row_sum_kernel(const float* __restrict__ values, const MT
 // =====================================================================================================
 // kl_penalty (verl/trainer/ppo/core_algos.py:1034-1069), elementwise; optional d out / d logprob
 // =====================================================================================================
-__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
 
 __device__ __forceinline__ void kl_term(int kind, float lp, float ref, float& out, float& grad) {
     if (kind == VPG_KL_K1) {
@@ -187,6 +124,7 @@ struct PpoParams {
     long long B, L;
     int gx;
     float ratio_lo, ratio_hi, clip_c;
+    int pg_kind;  // VPG_PG_CLIP: compute_policy_loss; VPG_PG_GPG: -log_prob * advantages (core_algos.py:797-815)
     int agg_mode;
     float entropy_coeff, kl_coef;
     int kl_kind;
@@ -286,11 +224,12 @@ __global__ void ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) 
             const float c1 = fmaxf(l1, l2);
             const float l3 = -A * p.clip_c;
             const float c2 = fminf(l3, c1);
-            const float pg = (A < 0.f) ? c2 : c1;
-            const float f_clip = (l2 > l1) ? 1.f : 0.f;
-            const float f_low = ((c1 > l3) ? 1.f : 0.f) * ((A < 0.f) ? 1.f : 0.f);
+            const bool gpg = p.pg_kind == VPG_PG_GPG;
+            const float pg = gpg ? (-lp.v[j] * A) : ((A < 0.f) ? c2 : c1);
+            const float f_clip = (!gpg && l2 > l1) ? 1.f : 0.f;
+            const float f_low = gpg ? 0.f : ((c1 > l3) ? 1.f : 0.f) * ((A < 0.f) ? 1.f : 0.f);
             a_pg += (on ? pg : 0.f) * mj;
-            a_lr += (on ? -lr : 0.f) * mj;
+            a_lr += (on && !gpg ? -lr : 0.f) * mj;
             a_clip += (on ? f_clip : 0.f) * mj;
             a_low += (on ? f_low : 0.f) * mj;
             r_pg += pg * mj;
@@ -302,6 +241,7 @@ __global__ void ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) 
             const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
             const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
             float g = (A < 0.f) ? g_c2 : g_c1;
+            if (p.pg_kind == VPG_PG_GPG) g = -A;
             if (has_kl) {
                 float kv, kg;
                 kl_term(p.kl_kind, lp.v[j], ref.v[j], kv, kg);
@@ -400,6 +340,74 @@ __global__ void agg_loss_kernel(const float* __restrict__ loss_mat, const MT* __
     if (last_block_done(&counters[1], gridDim.x)) {
         const double v = agg_finalize(mode, ws + kWsHeader + B, ws + kWsHeader, __ldcg(&ws[2]), n_total, B, L, red);
         if (threadIdx.x == 0) out[0] = static_cast<float>(v);
+    }
+}
+
+// =====================================================================================================
+// compute_value_loss (core_algos.py:992-1031): clipped value loss, forward + closed-form gradient wrt vpreds.
+//   vpc = max(min(vp, v + c), v - c); l1 = (vp - ret)^2; l2 = (vpc - ret)^2
+//   vf_loss = 0.5 * agg(max(l1, l2)); vf_clipfrac = masked_mean(l2 > l1)
+// workspace as ppo_loss (mask_count_kernel runs first): G[0] = where-weighted loss sum, G[1] = clip count,
+// rows[b] = plain row sums.  out[0] = vf_loss, out[1] = vf_clipfrac.
+// =====================================================================================================
+template <int VEC, typename MT>
+__global__ void value_loss_kernel(const float* __restrict__ vpreds, const float* __restrict__ returns,
+                                  const float* __restrict__ values, const MT* __restrict__ mask, long long B,
+                                  long long L, int gx, float cliprange, int mode, float* __restrict__ out,
+                                  float* __restrict__ d_vpreds, double* ws) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    const double n_total = ws[1];
+    const double row_cnt = ws[kWsHeader + b];
+    const float coef = agg_coef(mode, n_total, row_cnt, B, L);
+    const bool where_w = (mode == VPG_AGG_TOKEN_MEAN);
+    float a = 0.f, r = 0.f, cf = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const long long i = base + t;
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> vp = ldv<VEC>(vpreds, i);
+        const Pack<VEC> rt = ldv<VEC>(returns, i);
+        const Pack<VEC> vo = ldv<VEC>(values, i);
+        Pack<VEC> d;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const bool on = m.v[j] != 0.f;
+            const float hi = vo.v[j] + cliprange, lo = vo.v[j] - cliprange;
+            const float y = fminf(vp.v[j], hi);
+            const float vpc = fmaxf(y, lo);
+            const float e1 = vp.v[j] - rt.v[j], e2 = vpc - rt.v[j];
+            const float l1 = e1 * e1, l2 = e2 * e2;
+            const float lmax = fmaxf(l1, l2);
+            a += (on ? lmax : 0.f) * m.v[j];
+            r += lmax * m.v[j];
+            cf += (on ? ((l2 > l1) ? 1.f : 0.f) : 0.f) * m.v[j];
+            // d vpc / d vp through torch.min / torch.max (ties split 1/2 like torch autograd)
+            const float dmin = (vp.v[j] < hi) ? 1.f : ((vp.v[j] == hi) ? 0.5f : 0.f);
+            const float dmax = (y > lo) ? 1.f : ((y == lo) ? 0.5f : 0.f);
+            const float g1 = 2.f * e1, g2 = 2.f * e2 * (dmin * dmax);
+            const float g = (l1 > l2) ? g1 : ((l1 < l2) ? g2 : 0.5f * (g1 + g2));
+            d.v[j] = 0.5f * (coef * (where_w ? (on ? m.v[j] : 0.f) : m.v[j])) * g;
+        }
+        if (d_vpreds) stv<VEC>(d_vpreds, i, d);
+    }
+    const double ta = block_sum<double>(static_cast<double>(a), red);
+    const double tr = block_sum<double>(static_cast<double>(r), red);
+    const double tc = block_sum<double>(static_cast<double>(cf), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&ws[2], ta);
+        atomicAdd(&ws[3], tc);
+        atomicAdd(&ws[kWsHeader + B + b], tr);
+    }
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
+    if (last_block_done(&counters[1], gridDim.x)) {
+        const double v = agg_finalize(mode, ws + kWsHeader + B, ws + kWsHeader, __ldcg(&ws[2]), n_total, B, L, red);
+        if (threadIdx.x == 0) {
+            out[0] = 0.5f * static_cast<float>(v);
+            out[1] = static_cast<float>(__ldcg(&ws[3]) / (n_total + 1e-8));
+        }
     }
 }
 
@@ -668,26 +676,10 @@ __global__ void whiten_apply_kernel(const float* values, long long n, const doub
     }
 }
 
-static inline int flat_grid(int64_t n, int vec) {
-    int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    if (g > cap) g = cap;
-    return static_cast<int>(g < 1 ? 1 : g);
-}
-
 }  // namespace vpg
 
 
 using namespace vpg;
-
-// vector path requires 16-byte aligned rows
-static inline bool rows_vec_ok(int64_t L, const void* mask, int mask_dtype, std::initializer_list<const void*> ptrs) {
-    if (L % 4 != 0) return false;
-    if (mask && !mask_aligned(mask, mask_dtype)) return false;
-    for (const void* p : ptrs)
-        if (p && !aligned16(p)) return false;
-    return true;
-}
 
 extern "C" {
 
@@ -747,10 +739,11 @@ size_t vpg_ppo_loss_workspace_bytes(int64_t B, int64_t L) {
 
 int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
                  int mask_dtype, const float* entropy, const float* ref_log_prob, int64_t B, int64_t L,
-                 float ratio_lo, float ratio_hi, float clip_c, int agg_mode, float entropy_coeff, float kl_coef,
-                 int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy, void* workspace,
-                 size_t workspace_bytes, void* stream_) {
+                 float ratio_lo, float ratio_hi, float clip_c, int pg_kind, int agg_mode, float entropy_coeff,
+                 float kl_coef, int kl_kind, float loss_scale, float* metrics, float* d_log_prob, float* d_entropy,
+                 void* workspace, size_t workspace_bytes, void* stream_) {
     VPG_CHECK_ARG(old_log_prob && log_prob && advantages && mask && metrics, "null pointer argument");
+    VPG_CHECK_ARG(pg_kind == VPG_PG_CLIP || pg_kind == VPG_PG_GPG, "unknown policy-loss kind %d", pg_kind);
     VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
     VPG_CHECK_ARG(agg_mode >= 0 && agg_mode <= 3, "invalid loss_agg_mode %d", agg_mode);
     VPG_CHECK_ARG(clip_c > 1.0f, "clip_ratio_c must be > 1.0 (got %f)", clip_c);  // core_algos.py:761
@@ -769,7 +762,7 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
     PpoParams p{};
     p.old_lp = old_log_prob, p.lp = log_prob, p.adv = advantages, p.entropy = entropy, p.ref_lp = ref_log_prob;
     p.B = B, p.L = L, p.gx = gx;
-    p.ratio_lo = ratio_lo, p.ratio_hi = ratio_hi, p.clip_c = clip_c;
+    p.ratio_lo = ratio_lo, p.ratio_hi = ratio_hi, p.clip_c = clip_c, p.pg_kind = pg_kind;
     p.agg_mode = agg_mode, p.entropy_coeff = entropy_coeff, p.kl_coef = kl_coef, p.kl_kind = kl_kind;
     p.loss_scale = loss_scale;
     p.metrics = metrics, p.d_lp = d_log_prob, p.d_ent = d_entropy;
@@ -814,6 +807,39 @@ int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_
             mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws);
             count_launch();
             agg_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws);
+        }
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_value_loss(const float* vpreds, const float* returns, const float* values, const void* mask, int mask_dtype,
+                   int64_t B, int64_t L, float cliprange_value, int agg_mode, float* out, float* d_vpreds,
+                   void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(vpreds && returns && values && mask && out, "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    if (agg_mode < 0 || agg_mode > 3) return set_error(VPG_ERR_INVALID, "Invalid loss_agg_mode: %d", agg_mode);
+    const size_t need = vpg_ppo_loss_workspace_bytes(B, L);
+    if (!workspace || workspace_bytes < need)
+        return set_error(VPG_ERR_WORKSPACE, "value_loss workspace too small: need %zu, got %zu", need, workspace_bytes);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+    double* ws = static_cast<double*>(workspace);
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {vpreds, returns, values, d_vpreds});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec) {
+            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws);
+            count_launch();
+            value_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(vpreds, returns, values, mk, B, L, gx,
+                                                                    cliprange_value, agg_mode, out, d_vpreds, ws);
+        } else {
+            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws);
+            count_launch();
+            value_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(vpreds, returns, values, mk, B, L, gx,
+                                                                    cliprange_value, agg_mode, out, d_vpreds, ws);
         }
     });
     VPG_LAUNCH_CHECK();

@@ -12,7 +12,7 @@ import math
 import torch
 
 from . import _lib
-from ._lib import AGG_MODES, KL_KINDS, check, mask_arg, ptr, stream_ptr
+from ._lib import ADV_KINDS, AGG_MODES, KL_KINDS, PG_KINDS, check, mask_arg, ptr, stream_ptr
 
 _F32 = torch.float32
 
@@ -239,7 +239,7 @@ def _as_2d(t):
 
 def ppo_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low, cliprange_high, clip_ratio_c=3.0,
              loss_agg_mode="token-mean", entropy=None, entropy_coeff=0.0, ref_log_prob=None, kl_loss_coef=0.0,
-             kl_loss_type="low_var_kl", loss_scale=1.0, want_grad=True):
+             kl_loss_type="low_var_kl", loss_scale=1.0, want_grad=True, pg_kind="clip"):
     """Fused actor loss forward + closed-form gradient (vpg_ppo_loss).
 
     -> (metrics fp32 [8], d_log_prob | None, d_entropy | None)
@@ -268,7 +268,7 @@ def ppo_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low
     with torch.cuda.device(dev):
         check(lib.vpg_ppo_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, ptr(ent), ptr(ref), B, L,
                                float(1 - cliprange_low), float(1 + cliprange_high), float(clip_ratio_c),
-                               AGG_MODES[loss_agg_mode], float(entropy_coeff), float(kl_loss_coef),
+                               PG_KINDS[pg_kind], AGG_MODES[loss_agg_mode], float(entropy_coeff), float(kl_loss_coef),
                                KL_KINDS.get(kl_loss_type, -1) if ref is not None else -1, float(loss_scale),
                                ptr(metrics), ptr(d_lp), ptr(d_ent), ptr(ws), ws.numel() * 8, stream_ptr(dev)))
     return metrics, d_lp, d_ent
@@ -291,6 +291,76 @@ def agg_loss_fwd(loss_mat, loss_mask, loss_agg_mode: str, want_grad: bool):
     return out[0], d
 
 
+def value_loss(vpreds, returns, values, response_mask, cliprange_value: float, loss_agg_mode: str, want_grad: bool):
+    """compute_value_loss forward + closed-form gradient -> (out fp32 [2] = {vf_loss, vf_clipfrac}, d_vpreds | None)."""
+    if loss_agg_mode not in AGG_MODES:
+        raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+    _require_cuda(vpreds, returns, values, response_mask)
+    vp, rt, vo = _f32c(_as_2d(vpreds)), _f32c(_as_2d(returns)), _f32c(_as_2d(values))
+    m, mdt = mask_arg(_as_2d(response_mask).contiguous())
+    B, L = vp.shape
+    lib = _lib_()
+    out = torch.empty(2, dtype=_F32, device=vp.device)
+    d = torch.empty_like(vp) if want_grad else None
+    ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), vp.device)
+    with torch.cuda.device(vp.device):
+        check(lib.vpg_value_loss(ptr(vp), ptr(rt), ptr(vo), ptr(m), mdt, B, L, float(cliprange_value),
+                                 AGG_MODES[loss_agg_mode], ptr(out), ptr(d), ptr(ws), ws.numel() * 8,
+                                 stream_ptr(vp.device)))
+    return out, d
+
+
+def outcome_advantage(kind: str, token_level_rewards, response_mask, group_ids, num_groups: int, epsilon: float = 1e-6,
+                      norm_by_std: bool = True, f_norm: float = 1.0):
+    """RLOO / OPO / GPG / REINFORCE++-baseline / GRPO-pass@k (and GRPO) outcome advantages -> fp32 [B, L]."""
+    _require_cuda(token_level_rewards, response_mask, group_ids)
+    r = _f32c(token_level_rewards)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = r.shape
+    lib = _lib_()
+    adv = torch.empty_like(r)
+    status = torch.empty(1, dtype=torch.int32, device=r.device)
+    ws = _ws(int(lib.vpg_outcome_advantage_workspace_bytes(B, num_groups)), r.device)
+    with torch.cuda.device(r.device):
+        check(lib.vpg_outcome_advantage(ADV_KINDS[kind], ptr(r), ptr(m), mdt, ptr(group_ids), B, L, int(num_groups),
+                                        float(epsilon), int(bool(norm_by_std)), float(f_norm), ptr(adv), ptr(status),
+                                        ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
+    if kind in ("reinforce_plus_plus_baseline", "grpo_passk"):  # the two kinds whose reference can raise
+        code = int(status.item())
+        if code == 3:
+            raise ValueError("Pass@k requires at least 2 samples per group.")
+        _raise_whiten_code(code)
+    return adv
+
+
+def reinforce_plus_plus(token_level_rewards, response_mask, gamma: float):
+    _require_cuda(token_level_rewards, response_mask)
+    r = _f32c(token_level_rewards)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = r.shape
+    lib = _lib_()
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    status = torch.empty(1, dtype=torch.int32, device=r.device)
+    ws = _ws(int(lib.vpg_reverse_scan_workspace_bytes(B, L)), r.device)
+    with torch.cuda.device(r.device):
+        check(lib.vpg_reinforce_plus_plus(ptr(r), ptr(m), mdt, B, L, float(gamma), ptr(adv), ptr(ret), ptr(status),
+                                          ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
+    _raise_whiten_status(status)
+    return adv, ret
+
+
+def remax(token_level_rewards, reward_baselines, response_mask):
+    _require_cuda(token_level_rewards, reward_baselines, response_mask)
+    r, bsl = _f32c(token_level_rewards), _f32c(reward_baselines)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = r.shape
+    assert bsl.shape == (B,)
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    with torch.cuda.device(r.device):
+        check(_lib_().vpg_remax(ptr(r), ptr(bsl), ptr(m), mdt, B, L, ptr(adv), ptr(ret), stream_ptr(r.device)))
+    return adv, ret
+
+
 def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: int, epsilon: float, norm_by_std: bool):
     _require_cuda(token_level_rewards, response_mask, group_ids)
     r = _f32c(token_level_rewards)
@@ -306,7 +376,10 @@ def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: in
 
 
 def _raise_whiten_status(status: torch.Tensor):
-    code = int(status.item())
+    _raise_whiten_code(int(status.item()))
+
+
+def _raise_whiten_code(code: int):
     if code == 1:
         raise ValueError("At least one element in the mask has to be 1.")
     if code == 2:

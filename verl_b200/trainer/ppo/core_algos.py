@@ -3,6 +3,10 @@
 Hot-path functions (CUDA kernels, no torch fallback):
   compute_gae_advantage_return   core_algos.py:193-241
   compute_grpo_outcome_advantage core_algos.py:245-308
+  the other registered estimators: grpo_passk :309-369, reinforce_plus_plus_baseline :372-422,
+  rloo :425-476, opo :479-530, reinforce_plus_plus :533-569, remax :572-605, gpg :608-667
+  compute_policy_loss_gpg        core_algos.py:797-815
+  compute_value_loss             core_algos.py:992-1031
   agg_loss                       core_algos.py:686-719
   compute_policy_loss            core_algos.py:722-794
   kl_penalty                     core_algos.py:1034-1069
@@ -35,6 +39,15 @@ __all__ = [
     "get_kl_controller",
     "compute_gae_advantage_return",
     "compute_grpo_outcome_advantage",
+    "compute_grpo_passk_outcome_advantage",
+    "compute_reinforce_plus_plus_baseline_outcome_advantage",
+    "compute_rloo_outcome_advantage",
+    "compute_opo_outcome_advantage",
+    "compute_reinforce_plus_plus_outcome_advantage",
+    "compute_remax_outcome_advantage",
+    "compute_gpg_outcome_advantage",
+    "compute_policy_loss_gpg",
+    "compute_value_loss",
     "compute_rewards",
     "agg_loss",
     "compute_policy_loss",
@@ -93,7 +106,7 @@ def get_adv_estimator_fn(name_or_enum):
 
 
 class AdvantageEstimator(str, Enum):
-    """Names of the reference's estimators (core_algos.py:111-128); only GAE and GRPO have kernels in this build."""
+    """Names of the reference's estimators (core_algos.py:111-128); every one of them has kernels in this build."""
 
     GAE = "gae"
     GRPO = "grpo"
@@ -198,6 +211,125 @@ def compute_grpo_outcome_advantage(
             token_level_rewards, response_mask, gid_dev, n_groups, float(epsilon), bool(norm_adv_by_std_in_grpo)
         )
     return scores, scores
+
+
+def _outcome(kind, token_level_rewards, response_mask, index, **kw):
+    gids, n_groups = group_ids_from_index(index)
+    with torch.no_grad():
+        gid_dev = torch.from_numpy(gids).to(token_level_rewards.device, non_blocking=True)
+        adv = ops.outcome_advantage(kind, token_level_rewards, response_mask, gid_dev, n_groups, **kw)
+    return adv, adv
+
+
+def _cfg_get(config, key, default):
+    """``config.get(key, default)`` for dict-like / dataclass-like algorithm configs (AlgoConfig.get, base_config.py:26-91)."""
+    if config is None:
+        return default
+    if hasattr(config, "get"):
+        return config.get(key, default)
+    return getattr(config, key, default)
+
+
+@register_adv_est(AdvantageEstimator.GRPO_PASSK)
+def compute_grpo_passk_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: np.ndarray,
+    epsilon: float = 1e-6,
+    norm_adv_by_std_in_grpo: bool = True,
+    config: Optional[Any] = None,
+    **kwargs,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """Pass@k advantage (core_algos.py:309-369): only the best response of each uid group gets r_max - r_second_max
+    (optionally / (std + eps)); groups with fewer than two samples raise ValueError."""
+    assert config is not None
+    norm = _cfg_get(config, "norm_adv_by_std_in_grpo", True)
+    return _outcome("grpo_passk", token_level_rewards, response_mask, index, epsilon=float(epsilon), norm_by_std=bool(norm))
+
+
+@register_adv_est(AdvantageEstimator.REINFORCE_PLUS_PLUS_BASELINE)
+def compute_reinforce_plus_plus_baseline_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: torch.Tensor,
+    epsilon: float = 1e-6,
+    config: Optional[Any] = None,
+    **kwargs,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """RF++-baseline (core_algos.py:372-422): score minus the uid-group mean, broadcast over the response, then
+    masked_whiten over the batch and * mask.  The whitening of the broadcast matrix is evaluated in closed form from
+    the row lengths (response masks are 0/1)."""
+    return _outcome("reinforce_plus_plus_baseline", token_level_rewards, response_mask, index, epsilon=float(epsilon))
+
+
+@register_adv_est(AdvantageEstimator.RLOO)
+def compute_rloo_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: np.ndarray,
+    epsilon: float = 1e-6,
+    config: Optional[Any] = None,
+    **kwargs,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """RLOO (core_algos.py:425-476): score * n/(n-1) - group_mean * n/(n-1) for groups of n > 1."""
+    return _outcome("rloo", token_level_rewards, response_mask, index, epsilon=float(epsilon))
+
+
+@register_adv_est(AdvantageEstimator.OPO)
+def compute_opo_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: np.ndarray,
+    epsilon: float = 1e-6,
+    config: Optional[Any] = None,
+    **kwargs,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """OPO (core_algos.py:479-530): baseline = length-weighted mean score of the uid group."""
+    return _outcome("opo", token_level_rewards, response_mask, index, epsilon=float(epsilon))
+
+
+@register_adv_est(AdvantageEstimator.REINFORCE_PLUS_PLUS)
+def compute_reinforce_plus_plus_outcome_advantage(
+    token_level_rewards: torch.Tensor, response_mask: torch.Tensor, config: Optional[Any] = None, **kwargs
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """REINFORCE++ (core_algos.py:533-569): discounted reverse return that resets after masked-out tokens (one
+    block-parallel scan per row instead of a Python loop over time steps), advantages = masked_whiten(returns) * mask."""
+    assert config is not None
+    gamma = config.gamma if hasattr(config, "gamma") else config["gamma"]
+    with torch.no_grad():
+        advantages, returns = ops.reinforce_plus_plus(token_level_rewards, response_mask, float(gamma))
+    return advantages, returns
+
+
+@register_adv_est(AdvantageEstimator.REMAX)
+def compute_remax_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    reward_baselines: torch.Tensor,
+    response_mask: torch.Tensor,
+    config: Optional[Any] = None,
+    **kwargs,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """ReMax (core_algos.py:572-605): returns = reverse cumulative sum of the masked rewards, advantages = returns -
+    reward_baselines[:, None] * mask."""
+    with torch.no_grad():
+        advantages, returns = ops.remax(token_level_rewards, reward_baselines, response_mask)
+    return advantages, returns
+
+
+@register_adv_est(AdvantageEstimator.GPG)
+def compute_gpg_outcome_advantage(
+    token_level_rewards: torch.Tensor,
+    response_mask: torch.Tensor,
+    index: np.ndarray,
+    epsilon: float = 1e-6,
+    f_norm: float = 1.0,
+    alpha: float = 1.0,
+    config=None,
+    **kwargs,
+):
+    """GPG (core_algos.py:608-667): alpha * (score - group_mean) / f_norm with alpha = bsz / count_nonzero(scores)
+    (the ``alpha`` argument is overwritten by the reference too, :647)."""
+    return _outcome("gpg", token_level_rewards, response_mask, index, epsilon=float(epsilon), f_norm=float(f_norm))
 
 
 def compute_rewards(token_level_scores, old_log_prob, ref_log_prob, kl_ratio):
@@ -323,6 +455,47 @@ def compute_policy_loss(
                loss_agg_mode=loss_agg_mode)
     loss, stats = _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, None, None, cfg)
     return loss, stats[2], stats[3], stats[4]
+
+
+@register_policy_loss("gpg")
+def compute_policy_loss_gpg(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean", config=None):
+    """GPG policy loss (core_algos.py:797-815): agg_loss(-log_prob * advantages); the three statistics are 0."""
+    cfg = dict(cliprange_low=0.2, cliprange_high=0.2, clip_ratio_c=3.0, loss_agg_mode=loss_agg_mode, pg_kind="gpg")
+    loss, _ = _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, None, None, cfg)
+    zero = torch.tensor(0.0)
+    return loss, zero, zero.clone(), zero.clone()
+
+
+class _ValueLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vpreds, returns, values, response_mask, cliprange_value, mode):
+        out, d = ops.value_loss(vpreds, returns, values, response_mask, cliprange_value, mode,
+                                want_grad=vpreds.requires_grad)
+        ctx.meta = (vpreds.shape, vpreds.dtype)
+        if d is not None:
+            ctx.save_for_backward(d)
+        clipfrac = out[1]
+        ctx.mark_non_differentiable(clipfrac)
+        return out[0], clipfrac
+
+    @staticmethod
+    def backward(ctx, g, _g_clip):
+        (d,) = ctx.saved_tensors
+        return (d * g).view(ctx.meta[0]).to(ctx.meta[1]), None, None, None, None, None
+
+
+def compute_value_loss(
+    vpreds: torch.Tensor,
+    returns: torch.Tensor,
+    values: torch.Tensor,
+    response_mask: torch.Tensor,
+    cliprange_value: float,
+    loss_agg_mode: str = "token-mean",
+):
+    """Clipped value loss (core_algos.py:992-1031) -> (vf_loss, vf_clipfrac); one fused forward + gradient pass."""
+    if loss_agg_mode not in ops.AGG_MODES:
+        raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")
+    return _ValueLoss.apply(vpreds, returns, values, response_mask, float(cliprange_value), loss_agg_mode)
 
 
 def fused_actor_loss(
