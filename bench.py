@@ -36,13 +36,15 @@ LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_rati
                 entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
 
 
-def workload_config(T, world):
+def workload_config(T, world, exchange="nvlink"):
     """`config` of the JSON line — identical for both arms (the reference arm times a bounded sample of it)."""
+    how = ("partials pushed into every rank's gathered buffer by the forward GEMM epilogue (NVSwitch multimem.st, no "
+           "separate all-gather) + NCCL all-reduce of d_hidden"
+           if exchange == "nvlink" else "NCCL all-gather of [4,S,T] partials + NCCL all-reduce of d_hidden")
     return {
         "workload": f"Qwen2.5-7B lm-head (H={HIDDEN}, V={VOCAB}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
                     "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
-        "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), "
-                       "all-gather of [4,S,T] partials + all-reduce of d_hidden",
+        "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), " + how,
         "l2": "inputs exceed L2 (hidden 470 MB + weight shard >= 136 MB per step)",
         "loss": LOSS_CFG,
     }
@@ -195,6 +197,23 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
     _lib.load()
+    exchange = "nccl"
+    if world > 1:
+        from verl_b200.utils.kernel import kernels, peer
+
+        want = args.tp_exchange
+        ok = 0
+        if want in ("auto", "nvlink"):
+            try:  # collective pre-flight: symmetric allocation + NVSwitch multicast binding
+                ok = int(peer.workspace(group, dev).has_multicast)
+            except Exception as e:  # noqa: BLE001
+                print(f"[bench] rank {rank}: NVLink peer workspace unavailable ({type(e).__name__}: {e}); using NCCL",
+                      file=sys.stderr, flush=True)
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        exchange = "nvlink" if int(flag.item()) == 1 else "nccl"
+        kernels.set_vocab_parallel_exchange(exchange)
+        kernels.set_reduce_d_hidden(True, mode=args.tp_reduce)  # the op returns the summed d_hidden
 
     T, H, V = args.tokens, HIDDEN, VOCAB
     assert V % world == 0
@@ -261,9 +280,7 @@ def run_ours(args):
                                                     entropy=ent.view(1, -1), ref_log_prob=src["ref"], **LOSS_CFG)
         if record:
             marks[2].record()
-        loss.backward()
-        if world > 1:  # caller-side reduction of d_hidden, as in the reference (test_linear_cross_entropy_tp.py:313)
-            dist.all_reduce(hidden.grad, group=group)
+        loss.backward()  # world > 1: d_hidden comes back already summed over the ranks (kernels.set_reduce_d_hidden)
         if record:
             marks[3].record()
             seg["_marks"].append(marks)
@@ -332,7 +349,7 @@ def run_ours(args):
             "metric": METRIC, "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(T, world),
+            "config": workload_config(T, world, exchange),
             "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32 * world,
                     "how": "pinned host -> device on a copy stream, double-buffered (step i+1's inputs copy under step "
@@ -376,6 +393,10 @@ def main():
     ap.add_argument("--cpu-tokens", type=int, default=0,
                     help="token sample of the CPU legs (0 = 4096 for cpu_baseline, 2048 per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tp-reduce", choices=["nccl", "multimem"], default="nccl",
+                    help="N > 1: d_hidden all-reduce by NCCL (default) or fused into the d_hidden GEMM (multimem.red)")
+    ap.add_argument("--tp-exchange", choices=["auto", "nccl", "nvlink"], default="auto",
+                    help="N > 1: fused NVLink exchange (default when NVSwitch multicast is available) or NCCL")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -93,6 +93,20 @@ int vpg_lce_fwd_partials(const void* hidden_bf16, const void* weight_bf16, const
 int vpg_lce_finalize(const float* partials /* [4][num_parts][T] */, int num_parts, int64_t T, float temperature,
                      float* logprobs, float* entropy, float* lse, float* eb, void* stream);
 
+/* Vocab-parallel "push" variant of stage 1 — replaces the exchange of verl/utils/kernel/kernels.py:609-661 (all_reduce
+ * MAX + SUM + SUM of per-token partials).  The GEMM epilogue writes this rank's partials straight into the GATHERED
+ * layout [4][part_total][T] at parts [part_split0, part_split0 + num_splits) (part_split0 = rank * num_splits,
+ * part_total = world * num_splits) of EVERY rank, tile by tile, over NVLink:
+ *   partials_is_multicast != 0: `partials` is an NVSwitch multicast address bound to all ranks' buffers (multimem.st);
+ *   n_push > 0: `push_ptrs[0..n_push)` (HOST array of device pointers) are the peer-mapped buffers of all ranks
+ *               (this rank's own included); plain NVLink stores;
+ *   neither: plain local store (the single-GPU entry point above is this with part_split0 = 0).
+ * The caller owns the cross-rank barrier between this launch and vpg_lce_finalize(num_parts = part_total). */
+int vpg_lce_fwd_partials_push(const void* hidden_bf16, const void* weight_bf16, const int64_t* labels, int64_t T,
+                              int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                              float* partials, int part_split0, int part_total, int partials_is_multicast,
+                              void* const* push_ptrs, int n_push, void* stream);
+
 /* Backward.  Replaces verl/utils/kernel/kernels.py:1345-1553 (efficient_entropy_backward; default strategy
  * _Split_Dlogits_N :1230-1342 + two cuBLAS GEMMs :1538-1548).
  *   dlogits[t,v] = ( g_lp[t]*(1[v==label_t] - p) - g_ent[t]*p*(logit - eb[t]) ) / temperature
@@ -107,6 +121,19 @@ int vpg_lce_bwd(const void* hidden_bf16, const void* weight_bf16, const int64_t*
                 const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
                 float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden_bf16, void* d_weight_bf16,
                 void* workspace, size_t workspace_bytes, void* stream);
+
+/* Vocab-parallel backward with the d_hidden all-reduce fused into the d_hidden GEMM (the reference leaves this
+ * all-reduce to the caller: tests/utils/test_linear_cross_entropy_tp.py:313-314).  d_hidden_mc_f32 is an NVSwitch
+ * multicast address bound to an fp32 [T,H] buffer on every rank, zeroed on all ranks (barrier) before the call: the
+ * epilogue of the last vocab chunk's d_hidden GEMM issues multimem.red.add.f32 per tile, so the sum over ranks builds
+ * up in every rank's buffer while the GEMM runs.  After a barrier each rank converts its copy with
+ * vpg_cast_f32_bf16.  d_hidden_mc_f32 == NULL behaves exactly like vpg_lce_bwd (d_hidden may then not be NULL). */
+int vpg_lce_bwd_mcred(const void* hidden_bf16, const void* weight_bf16, const int64_t* labels, const float* lse,
+                      const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
+                      float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden_bf16,
+                      void* d_weight_bf16, void* workspace, size_t workspace_bytes, float* d_hidden_mc_f32,
+                      void* stream);
+int vpg_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
 
 /* Plain bf16 GEMM on the same tcgen05 mainloop (used by the backward; exported for tests):
  *   C[M,N] (bf16 or f32) = A . B with

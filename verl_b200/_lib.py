@@ -26,6 +26,11 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_void_p],
     ),
+    "vpg_lce_fwd_partials_push": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_int, c_int,
+         c_int, c_void_p, c_int, c_void_p],
+    ),
     "vpg_lce_finalize": (
         c_int,
         [c_void_p, c_int, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
@@ -37,6 +42,12 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float,
          c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "vpg_lce_bwd_mcred": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float,
+         c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
+    ),
+    "vpg_cast_f32_bf16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "vpg_gemm_bf16": (
         c_int,
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_int,

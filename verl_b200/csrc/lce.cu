@@ -32,9 +32,22 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // bf16 2-D tensor map over a row-major [outer][inner] matrix with row stride ld (elements), 128B swizzle.
+// cuTensorMapEncodeTiled is a DRIVER entry point: it fails with CUDA_ERROR_INVALID_CONTEXT on a thread that has not
+// bound the device's primary context yet (e.g. autograd's worker thread of device 0 before its first runtime call).
+// cudaFree(nullptr) binds it; once per (thread, device).
+static void bind_primary_context() {
+    static thread_local int bound_dev = -1;
+    int dev = -1;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev != bound_dev) {
+        (void)cudaFree(nullptr);
+        bound_dev = dev;
+    }
+}
+
 static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
                      int box_outer) {
     EncodeTiledFn fn = get_encode_fn();
+    bind_primary_context();
     if (!fn) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld * 2) % 16 != 0)
         return set_error(VPG_ERR_INVALID, "TMA operand must be 16-byte aligned with a 16-byte-multiple row stride");
@@ -86,7 +99,7 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     p.sync_epoch = next_epoch();
     if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
     if (env_int("VPG_HINT_B", -1) >= 0) p.hint_b = env_int("VPG_HINT_B", 0);
-    constexpr int smem = TileCfg<kCG>::kSmemBytes;
+    constexpr int smem = TileCfg<kCG>::kSmemBytes + (kMode == MODE_GEMM ? kRedScratchBytes : 0);
     // per-device attribute: set every call (cheap) so multi-device processes are handled
     cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (attr_err != cudaSuccess)
@@ -177,6 +190,23 @@ __global__ void lce_finalize_kernel(const float* __restrict__ part, int P, long 
     if (eb_out) eb_out[t] = eb;
 }
 
+// fp32 -> bf16 (round to nearest even), 8 elements per thread; used after the fused d_hidden all-reduce
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
+    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+        if (i + 8 <= n) {
+            const float4 a = *reinterpret_cast<const float4*>(src + i);
+            const float4 b = *reinterpret_cast<const float4*>(src + i + 4);
+            uint4 v;
+            v.x = pack_bf16x2(a.x, a.y), v.y = pack_bf16x2(a.z, a.w);
+            v.z = pack_bf16x2(b.x, b.y), v.w = pack_bf16x2(b.z, b.w);
+            *reinterpret_cast<uint4*>(dst + i) = v;
+        } else {
+            for (long long j = i; j < n; ++j) dst[j] = __float2bfloat16_rn(src[j]);
+        }
+    }
+}
+
 static int check_lce_shapes(int64_t T, int64_t H, int64_t V) {
     VPG_CHECK_ARG(T >= 0 && H > 0 && V > 0, "invalid shape T=%lld H=%lld V=%lld", (long long)T, (long long)H,
                   (long long)V);
@@ -202,9 +232,22 @@ int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
 int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
                          int64_t V, float temperature, int64_t label_offset, int num_splits, float* partials,
                          void* stream) {
+    return vpg_lce_fwd_partials_push(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
+                                     0, num_splits, 0, nullptr, 0, stream);
+}
+
+int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
+                              int64_t V, float temperature, int64_t label_offset, int num_splits, float* partials,
+                              int part_split0, int part_total, int partials_is_multicast, void* const* push_ptrs,
+                              int n_push, void* stream) {
     int rc = check_lce_shapes(T, H, V);
     if (rc) return rc;
-    VPG_CHECK_ARG(hidden && weight && labels && partials, "null pointer argument");
+    VPG_CHECK_ARG(hidden && weight && labels && (partials || n_push > 0), "null pointer argument");
+    VPG_CHECK_ARG(part_split0 >= 0 && part_total >= part_split0 + num_splits, "partials slot [%d, %d) exceeds %d parts",
+                  part_split0, part_split0 + num_splits, part_total);
+    VPG_CHECK_ARG(n_push >= 0 && n_push <= kMaxPeers && (n_push == 0 || push_ptrs), "n_push must be in [0, %d]",
+                  kMaxPeers);
+    VPG_CHECK_ARG(!(partials_is_multicast && n_push > 0), "choose multicast or unicast push, not both");
     VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0 (got %f)", temperature);
     if (T == 0) return VPG_OK;
     TcParams p{};
@@ -222,6 +265,14 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
     p.labels = reinterpret_cast<const long long*>(labels);
     p.label_offset = label_offset;
     p.partials = partials;
+    p.part_split0 = part_split0;
+    p.part_total = part_total;
+    p.partials_mc = partials_is_multicast ? 1 : 0;
+    p.n_push = n_push;
+    for (int i = 0; i < n_push; ++i) {
+        VPG_CHECK_ARG(push_ptrs[i], "push_ptrs[%d] is null", i);
+        p.push_ptrs[i] = static_cast<float*>(push_ptrs[i]);
+    }
     p.worker_perm = env_int("VPG_WORKER_PERM", 0) ? num_splits : 0;
     if (const char* e = getenv("VPG_DEBUG_TRACE_PTR")) p.debug_trace = reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0));
     CUtensorMap ta, tb;
@@ -290,9 +341,18 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
                 const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V, float temperature,
                 int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight, void* workspace,
                 size_t workspace_bytes, void* stream_) {
+    return vpg_lce_bwd_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset, chunk_v,
+                             d_hidden, d_weight, workspace, workspace_bytes, nullptr, stream_);
+}
+
+int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* labels, const float* lse, const float* eb,
+                      const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V, float temperature,
+                      int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight, void* workspace,
+                      size_t workspace_bytes, float* d_hidden_mc_f32, void* stream_) {
     int rc = check_lce_shapes(T, H, V);
     if (rc) return rc;
-    VPG_CHECK_ARG(hidden && weight && labels && lse && eb && d_hidden && d_weight, "null pointer argument");
+    VPG_CHECK_ARG(hidden && weight && labels && lse && eb && (d_hidden || d_hidden_mc_f32) && d_weight,
+                  "null pointer argument");
     VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (T == 0) {
@@ -371,7 +431,13 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
             p.tiles_per_split = 1;
             p.M = static_cast<int>(T);
             p.N = static_cast<int>(H);
-            if (num_chunks == 1) {
+            if (d_hidden_mc_f32 && ci == num_chunks - 1) {
+                VPG_CHECK_ARG(H % 32 == 0, "fused d_hidden all-reduce needs H %% 32 == 0");
+                // fused all-reduce: the last chunk's epilogue adds (this rank's fp32 sum over all its vocab chunks)
+                // into every rank's fp32 buffer through the multicast address, tile by tile
+                p.out = d_hidden_mc_f32, p.ldc = H, p.out_mode = OUT_F32_MCRED;
+                p.accum = (num_chunks > 1) ? dh_acc : nullptr, p.ld_accum = H;
+            } else if (num_chunks == 1) {
                 p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16;
             } else if (ci == 0) {
                 p.out = dh_acc, p.ldc = H, p.out_mode = OUT_F32;
@@ -386,6 +452,20 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
             if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream))) return rc;
         }
     }
+    return VPG_OK;
+}
+
+int vpg_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream) {
+    VPG_CHECK_ARG(src && dst_bf16 && n >= 0, "invalid cast arguments");
+    VPG_CHECK_ARG(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst_bf16)) & 15) == 0,
+                  "cast operands must be 16-byte aligned");
+    if (n == 0) return VPG_OK;
+    int64_t g = ceil_div(n, 256 * 8 * 4);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    if (g > cap) g = cap;
+    cast_f32_bf16_kernel<<<static_cast<unsigned>(g), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        src, static_cast<__nv_bfloat16*>(dst_bf16), n);
+    VPG_LAUNCH_CHECK();
     return VPG_OK;
 }
 

@@ -261,6 +261,20 @@ __device__ __forceinline__ float lg2f(float x) {
     return y;
 }
 
+// ---- NVLink SHARP (multimem): stores / reductions on a multicast address reach every GPU bound to it ------------
+__device__ __forceinline__ void multimem_st_f32(float* mc_addr, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc_addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_f32(float* mc_addr, float v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(mc_addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_v4f32(float* mc_addr, float a, float b, float c, float d) {
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(a), "f"(b),
+                 "f"(c), "f"(d)
+                 : "memory");
+}
+
+
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

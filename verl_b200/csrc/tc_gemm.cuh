@@ -52,9 +52,22 @@ constexpr int kMmaWarp = 9;
 constexpr int kAllocWarp = 10;
 constexpr int kNumEpiWarps = 8;
 constexpr int kTmemCols = 512;
+// fused all-reduce epilogue (OUT_F32_MCRED): every epilogue warp transposes 16 rows x 32 columns at a time through
+// shared memory so that 8 lanes cover one contiguous 128-byte row segment per multimem.red (coalesced NVLink packets)
+constexpr int kRedRows = 16;
+constexpr int kRedLd = 36;  // floats per staged row: 144 B keeps float4 accesses aligned and bank-conflict free
+constexpr int kRedScratchBytes = kNumEpiWarps * kRedRows * kRedLd * 4;  // 18 KB
 
 enum : int { MODE_FWD = 0, MODE_DS = 1, MODE_GEMM = 2 };
-enum : int { OUT_BF16 = 0, OUT_F32 = 1, OUT_F32_ACC = 2, OUT_BF16_FROM_ACC = 3, OUT_DEBUG_SKIP = 7 };
+enum : int {
+    OUT_BF16 = 0,
+    OUT_F32 = 1,
+    OUT_F32_ACC = 2,
+    OUT_BF16_FROM_ACC = 3,
+    OUT_F32_MCRED = 4,  // fused all-reduce: multimem.red.add.f32 of (acc [+ accum]) into a multicast fp32 buffer
+    OUT_DEBUG_SKIP = 7
+};
+constexpr int kMaxPeers = 8;
 
 struct TcParams {
     // tiling
@@ -71,7 +84,12 @@ struct TcParams {
     float inv_temp;
     const long long* labels;  // [M]
     long long label_offset;   // subtracted from labels to get a local column
-    float* partials;          // MODE_FWD: [4][num_splits][M]
+    float* partials;          // MODE_FWD: [4][part_total][M]; this launch writes parts [part_split0, +num_splits)
+    int part_split0;          //   vocab-parallel push: rank * num_splits (0 otherwise)
+    int part_total;           //   world * num_splits (num_splits otherwise)
+    int partials_mc;          //   1: `partials` is a multicast address (multimem.st reaches every rank's copy)
+    int n_push;               //   > 0: unicast push, write into every push_ptrs[i] (peer-mapped buffers) instead
+    float* push_ptrs[kMaxPeers];
     const float* lse;         // MODE_DS: [M]
     const float* eb;          // MODE_DS: [M]
     const float* g_lp;        // MODE_DS: [M] or null
@@ -99,6 +117,7 @@ struct SmemLayout {
     uint64_t* tmem_empty;  // [2]
     uint32_t* tmem_ptr;
     float4* scratch;  // [2][128]
+    float* red_scratch;  // MODE_GEMM only: [kNumEpiWarps][kRedRows][kRedLd] transpose staging of the fused all-reduce
 };
 
 __device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw, int stage_bytes_total) {
@@ -112,6 +131,7 @@ __device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw, int stage_bytes_t
     L.tmem_empty = L.tmem_full + 2;
     L.tmem_ptr = reinterpret_cast<uint32_t*>(L.tmem_empty + 2);
     L.scratch = reinterpret_cast<float4*>(aux + 256);
+    L.red_scratch = reinterpret_cast<float*>(aux + 8192);
     return L;
 }
 
@@ -279,6 +299,44 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
 #pragma unroll
             for (int j = 0; j < 32; ++j)
                 if (j < n_valid) o[j] = __uint_as_float(r[j]) + (acc ? o[j] : 0.f);
+        }
+    }
+}
+
+// Fused all-reduce epilogue chunk: this warp's 32 rows x 32 columns of (acc [+ local fp32 partial]) are added into the
+// multicast fp32 buffer.  Lane = row in registers; the staging transpose makes 8 lanes cover 128 contiguous bytes of
+// one row, so each multimem.red instruction issues four full 128-byte segments instead of 32 scattered 16-byte ones.
+// Whole warp must call (rows beyond M are skipped at the red, not at the staging).
+__device__ __forceinline__ void mcred_chunk(const TcParams& p, const uint32_t (&r)[32], long long row, bool row_ok,
+                                            int col, float* stage, int lane) {
+    float d[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) d[j] = __uint_as_float(r[j]);
+    if (p.accum && row_ok) {  // partial sums of the earlier vocab chunks (local fp32)
+        const float4* acc = reinterpret_cast<const float4*>(p.accum + row * p.ld_accum + col);
+#pragma unroll
+        for (int q4 = 0; q4 < 8; ++q4) {
+            const float4 a = acc[q4];
+            d[q4 * 4 + 0] += a.x, d[q4 * 4 + 1] += a.y, d[q4 * 4 + 2] += a.z, d[q4 * 4 + 3] += a.w;
+        }
+    }
+    const long long row0 = row - lane;  // first row of this warp
+    float* out = reinterpret_cast<float*>(p.out);
+#pragma unroll
+    for (int hlf = 0; hlf < 2; ++hlf) {
+        __syncwarp();
+        if ((lane >> 4) == hlf) {
+            float4* dst = reinterpret_cast<float4*>(stage + (lane & 15) * kRedLd);
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4) dst[q4] = make_float4(d[q4 * 4 + 0], d[q4 * 4 + 1], d[q4 * 4 + 2], d[q4 * 4 + 3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < kRedRows / 4; ++i) {
+            const int rr = i * 4 + (lane >> 3);  // staged row
+            const float4 v = *reinterpret_cast<const float4*>(stage + rr * kRedLd + (lane & 7) * 4);
+            const long long grow = row0 + hlf * kRedRows + rr;
+            if (grow < p.M) multimem_red_add_v4f32(out + grow * p.ldc + col + (lane & 7) * 4, v.x, v.y, v.z, v.w);
         }
     }
 }
@@ -582,6 +640,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                        } else if (p.out_mode == OUT_F32_MCRED) {
+                            if (n_valid >= 32) mcred_chunk(p, ra, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
                             if (row_ok) gemm_chunk(p, ra, row, cb, min(n_valid, 32));
                         }
@@ -596,6 +656,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                        } else if (p.out_mode == OUT_F32_MCRED) {
+                            if (n_valid >= 32) mcred_chunk(p, rb, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
                             if (row_ok) gemm_chunk(p, rb, row, cb, min(n_valid, 32));
                         }
@@ -625,12 +687,30 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     b = b * f0 + o.z * f1;
                     const float t = st.tgt + o.w;
                     if (row_ok) {
-                        const long long plane = static_cast<long long>(p.num_splits) * p.M;
-                        float* dst = p.partials + static_cast<long long>(sp) * p.M + row;
-                        dst[0] = m;
-                        dst[plane] = s;
-                        dst[2 * plane] = b;
-                        dst[3 * plane] = t;
+                        const long long plane = static_cast<long long>(p.part_total) * p.M;
+                        const long long off = static_cast<long long>(p.part_split0 + sp) * p.M + row;
+                        if (p.partials_mc) {
+                            // fused all-gather: one store per value lands in every rank's gathered buffer
+                            float* dst = p.partials + off;
+                            multimem_st_f32(dst, m);
+                            multimem_st_f32(dst + plane, s);
+                            multimem_st_f32(dst + 2 * plane, b);
+                            multimem_st_f32(dst + 3 * plane, t);
+                        } else if (p.n_push > 0) {
+                            for (int pr = 0; pr < p.n_push; ++pr) {  // peer-mapped NVLink stores (fire and forget)
+                                float* dst = p.push_ptrs[pr] + off;
+                                dst[0] = m;
+                                dst[plane] = s;
+                                dst[2 * plane] = b;
+                                dst[3 * plane] = t;
+                            }
+                        } else {
+                            float* dst = p.partials + off;
+                            dst[0] = m;
+                            dst[plane] = s;
+                            dst[2 * plane] = b;
+                            dst[3 * plane] = t;
+                        }
                     }
                 }
             }

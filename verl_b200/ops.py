@@ -58,6 +58,63 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
     return part
 
 
+def lce_forward_partials_push(hidden, weight, labels, temperature: float, label_offset: int, num_splits: int,
+                              gathered, part_split0: int, multicast_ptr: int = 0, peer_ptrs=None):
+    """Vocab-parallel stage 1 with the all-gather fused into the GEMM epilogue (vpg_lce_fwd_partials_push).
+
+    ``gathered`` is this rank's [4, P, T] fp32 view of the symmetric buffer (P = world * num_splits); the kernel writes
+    parts [part_split0, part_split0 + num_splits) of EVERY rank's buffer through ``multicast_ptr`` (NVSwitch
+    multicast) or, when that is 0, through ``peer_ptrs`` (peer-mapped addresses of the same view on all ranks)."""
+    import ctypes
+
+    _require_cuda(hidden, weight, labels, gathered)
+    T, H = hidden.shape
+    V = weight.shape[0]
+    four, P, T2 = gathered.shape
+    assert four == 4 and T2 == T and gathered.is_contiguous() and gathered.dtype == _F32
+    if multicast_ptr:
+        dst, is_mc, arr, n_push = int(multicast_ptr), 1, None, 0
+    else:
+        ptrs = [int(x) for x in (peer_ptrs or [])]
+        if not ptrs:
+            raise ValueError("lce_forward_partials_push needs a multicast address or the peer addresses")
+        arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        dst, is_mc, n_push = gathered.data_ptr(), 0, len(ptrs)
+    with torch.cuda.device(hidden.device):
+        check(_lib_().vpg_lce_fwd_partials_push(ptr(hidden), ptr(weight), ptr(labels), T, H, V, float(temperature),
+                                                int(label_offset), int(num_splits), dst, int(part_split0), int(P),
+                                                is_mc, arr, n_push, stream_ptr(hidden.device)))
+    return gathered
+
+
+def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int,
+                       accum_local, accum_multicast_ptr: int, chunk_v: int = 0):
+    """Backward whose d_hidden GEMM reduces into the multicast fp32 [T,H] buffer of every rank (vpg_lce_bwd_mcred).
+    -> d_weight bf16 [V,H]; the summed d_hidden is in ``accum_local`` once all ranks have passed a barrier."""
+    _require_cuda(hidden, weight, labels, lse, eb, accum_local)
+    T, H = hidden.shape
+    V = weight.shape[0]
+    assert accum_local.shape == (T, H) and accum_local.dtype == _F32 and accum_multicast_ptr
+    lib = _lib_()
+    nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
+    ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
+    d_weight = torch.empty_like(weight)
+    with torch.cuda.device(hidden.device):
+        check(lib.vpg_lce_bwd_mcred(ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb), ptr(g_lp), ptr(g_ent),
+                                    T, H, V, float(temperature), int(label_offset), int(chunk_v), None, ptr(d_weight),
+                                    ptr(ws), nbytes, int(accum_multicast_ptr), stream_ptr(hidden.device)))
+    return d_weight
+
+
+def cast_f32_bf16(src):
+    _require_cuda(src)
+    assert src.dtype == _F32 and src.is_contiguous()
+    out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    with torch.cuda.device(src.device):
+        check(_lib_().vpg_cast_f32_bf16(ptr(src), ptr(out), src.numel(), stream_ptr(src.device)))
+    return out
+
+
 def lce_finalize(partials, temperature: float):
     """partials [4, P, T] -> (logprobs, entropy, lse, eb), each fp32 [T]."""
     _require_cuda(partials)

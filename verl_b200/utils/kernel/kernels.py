@@ -6,13 +6,17 @@ Differences a maintainer should know (all outputs match the reference within its
 * the three saved per-token tensors are (lse, 1, eb) in the reference's (maximum, accumulate, entropy_b) slots:
   the reference identity ``logprob = target - maximum - log(accumulate)`` holds with maximum=lse, accumulate=1;
 * vocab-parallel runs exchange ONE all-gather of the packed [4,S,T] partials instead of the reference's three
-  dependent all-reduces (kernels.py:612,617,644);
+  dependent all-reduces (kernels.py:612,617,644) — or, with ``set_vocab_parallel_exchange("nvlink")``, no separate
+  collective at all: the GEMM epilogue stores the partials into every rank's gathered buffer over NVLink
+  (multimem.st / peer stores, see peer.py), and with ``set_reduce_d_hidden(True)`` the d_hidden GEMM reduces into
+  every rank's buffer through the NVSwitch (multimem.red) while it runs;
 * ``BackwardEnum`` values are accepted by ``set_backward_method`` for API compatibility; the backward always uses
   the split-along-vocab strategy (the reference default, ``_Split_Dlogits_N``) on tcgen05 GEMMs.
 """
 
 from __future__ import annotations
 
+import os
 import typing
 from dataclasses import dataclass
 
@@ -64,6 +68,14 @@ class Config:
     _backward: int = BackwardEnum._Split_Dlogits_N
     _use_triton: bool = False  # there is no Triton in this build
     _chunk_v: int = 0  # 0 = library default (vpg_lce_bwd_default_chunk)
+    # vocab-parallel exchange: "nccl" (one all-gather of the partials) or "nvlink" (fused into the GEMM epilogue)
+    _tp_exchange: str = os.environ.get("VPG_TP_EXCHANGE", "nccl")
+    # False = reference semantics (caller all-reduces d_hidden); True = the op returns the summed d_hidden
+    _tp_reduce_d_hidden: bool = False
+    # how the op sums d_hidden when asked to: "nccl" (one all-reduce after the GEMMs) or "multimem" (fused into the
+    # d_hidden GEMM epilogue; every rank multicasts its fp32 tiles, so each GPU's NVLink ingress is world x |d_hidden|:
+    # measured on par with NCCL at 2 GPUs and ~3 ms slower at 8 GPUs for configs[1], hence opt-in)
+    _tp_reduce_mode: str = os.environ.get("VPG_TP_REDUCE", "nccl")
 
 
 _config = Config()
@@ -79,6 +91,31 @@ def set_backward_chunk(chunk_v: int):
     """Vocab columns of dlogits materialised at a time in the backward (multiple of 256; 0 = default)."""
     global _config
     _config._chunk_v = int(chunk_v)
+
+
+def set_vocab_parallel_exchange(mode: str):
+    """"nccl": all-gather of the packed partials after the GEMM.  "nvlink": the GEMM epilogue writes the partials into
+    every rank's symmetric buffer itself (NVSwitch multicast or peer-mapped stores); only a barrier follows."""
+    if mode not in ("nccl", "nvlink"):
+        raise ValueError(f"Invalid vocab-parallel exchange: {mode}")
+    _config._tp_exchange = mode
+
+
+def set_reduce_d_hidden(enabled: bool, mode: str = "nccl"):
+    """True: the backward returns d_hidden already summed over the vocab-parallel group (the reference leaves that
+    all-reduce to its callers).  mode "nccl": one all-reduce after the GEMMs.  mode "multimem" (needs the "nvlink"
+    exchange and NVSwitch multicast): the d_hidden GEMM's epilogue reduces into every rank's fp32 buffer through the
+    switch (multimem.red) while it runs."""
+    if mode not in ("nccl", "multimem"):
+        raise ValueError(f"Invalid d_hidden reduction mode: {mode}")
+    _config._tp_reduce_d_hidden = bool(enabled)
+    _config._tp_reduce_mode = mode
+
+
+def _peer_workspace(group, device):
+    from . import peer
+
+    return peer.workspace(group, device)
 
 
 def _check_inputs(hidden, weight, labels):
@@ -122,9 +159,20 @@ def efficient_entropy_forward(
     world = 1 if dist_process_group is None else dist.get_world_size(dist_process_group)
     vocab_local = weight.shape[0]
 
-    partials = ops.lce_forward_partials(hidden, weight, labels, temperature, label_offset=rank * vocab_local)
-    if world > 1:
-        partials = exchange_partials(partials, dist_process_group)
+    if world > 1 and _config._tp_exchange == "nvlink":
+        # fused GEMM + all-gather: every rank's epilogue pushes its partials into all gathered buffers over NVLink
+        T, H = hidden.shape
+        S = ops.lce_num_splits(T, H, vocab_local)
+        px = _peer_workspace(dist_process_group, hidden.device)
+        gathered, mc_ptr, peer_ptrs = px.partials(S, T)
+        ops.lce_forward_partials_push(hidden, weight, labels, temperature, rank * vocab_local, S, gathered,
+                                      part_split0=rank * S, multicast_ptr=mc_ptr, peer_ptrs=peer_ptrs)
+        px.barrier()
+        partials = gathered
+    else:
+        partials = ops.lce_forward_partials(hidden, weight, labels, temperature, label_offset=rank * vocab_local)
+        if world > 1:
+            partials = exchange_partials(partials, dist_process_group)
     logprobs, entropy, lse, eb = ops.lce_finalize(partials, temperature)
 
     if REDUCTION == EntropyReductionEnum._Sum:
@@ -177,10 +225,31 @@ def efficient_entropy_backward(
 
     # maximum + log(acc) is the log-sum-exp for both this module's and the reference's saved triple
     lse = maximum if acc is None else maximum + torch.log(acc)
-    d_hidden, d_weight = ops.lce_backward(
-        hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
-        label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v,
-    )
+    world = 1 if dist_process_group is None else dist.get_world_size(dist_process_group)
+    fused_reduce = False
+    if (world > 1 and _config._tp_reduce_d_hidden and _config._tp_reduce_mode == "multimem"
+            and _config._tp_exchange == "nvlink"):
+        px = _peer_workspace(dist_process_group, hidden.device)
+        accum, accum_mc = px.d_hidden_accum(hidden.shape[0], hidden.shape[1])
+        fused_reduce = accum_mc != 0
+    if fused_reduce:
+        # fused GEMM + all-reduce: zero every rank's fp32 buffer, barrier, the d_hidden GEMM's epilogue reduces into all
+        # of them through the switch (multimem.red), barrier, convert this rank's copy
+        accum.zero_()
+        px.barrier()
+        d_weight = ops.lce_backward_mcred(
+            hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
+            rank * weight.shape[0], accum, accum_mc, chunk_v=_config._chunk_v,
+        )
+        px.barrier()
+        d_hidden = ops.cast_f32_bf16(accum)
+    else:
+        d_hidden, d_weight = ops.lce_backward(
+            hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
+            label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v,
+        )
+        if world > 1 and _config._tp_reduce_d_hidden:
+            dist.all_reduce(d_hidden, group=dist_process_group)
     if should_return_fp32_grad:
         d_hidden, d_weight = d_hidden.float(), d_weight.float()
     return d_hidden, d_weight

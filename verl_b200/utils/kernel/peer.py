@@ -1,0 +1,98 @@
+"""NVLink peer-memory workspace of one vocab-parallel group (one process per GPU, one 8xB200 NVSwitch box).
+
+The fused lm-head kernels can do their collectives themselves instead of calling NCCL afterwards:
+
+* forward  — the GEMM epilogue stores each token tile's partials {m, s, b, t} straight into the gathered
+  ``[4, world*S, T]`` buffer of EVERY rank (``multimem.st`` on an NVSwitch multicast address, or plain stores to the
+  peer-mapped buffers when multicast is unavailable): the all-gather happens tile by tile under the GEMM;
+* backward — the epilogue of the d_hidden GEMM issues ``multimem.red.add.f32`` on a multicast fp32 ``[T, H]`` buffer,
+  so the all-reduce of d_hidden (left to the caller by the reference, tests/utils/test_linear_cross_entropy_tp.py:
+  313-314) builds up in every rank's memory while the GEMM runs.
+
+This module owns the buffers those kernels write: symmetric allocations made with torch's
+``torch.distributed._symmetric_memory`` (CUDA VMM + fabric handles exchanged through the group's store — plumbing,
+like the caching allocator), their peer / multicast addresses, and the signal-pad barrier between the phases.
+Replaces the exchange of verl/utils/kernel/kernels.py:609-661.
+"""
+
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+_workspaces: dict = {}
+
+
+class PeerWorkspace:
+    """Symmetric buffers of one (process group, device).  Every method that allocates is COLLECTIVE over the group and
+    must be called with the same sizes in the same order on all ranks (true for the lm-head: T, H, S are replicated)."""
+
+    def __init__(self, group, device: torch.device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self._symm = symm_mem
+        self.group = group
+        self.device = device
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self._bufs: dict[str, tuple] = {}  # name -> (tensor, handle, numel)
+        self._parity = 0
+        try:  # older torch versions need the group to be enabled explicitly; newer ones treat this as a no-op
+            symm_mem.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------------------------------ allocation
+    def _buffer(self, name: str, numel: int):
+        cur = self._bufs.get(name)
+        if cur is not None and cur[2] >= numel:
+            return cur
+        t = self._symm.empty(numel, dtype=torch.float32, device=self.device)
+        hdl = self._symm.rendezvous(t, group=self.group.group_name)
+        self._bufs[name] = (t, hdl, numel)
+        return self._bufs[name]
+
+    @staticmethod
+    def _mc_ptr(hdl) -> int:
+        try:
+            return int(hdl.multicast_ptr or 0)
+        except Exception:
+            return 0
+
+    @property
+    def has_multicast(self) -> bool:
+        t, hdl, _ = self._buffer("probe", 1024)
+        return self._mc_ptr(hdl) != 0
+
+    # ------------------------------------------------------------------------------------------ phases
+    def barrier(self):
+        """All ranks' prior work on the current stream is complete and visible before any rank continues."""
+        _, hdl, _ = self._buffer("probe", 1024)
+        hdl.barrier(channel=0)
+
+    def partials(self, S: int, T: int):
+        """-> (local view [4, world*S, T], multicast address | 0, [peer addresses of the same view]).
+        Two slots alternate between calls, so rank A's next forward never overwrites a slot rank B is still reading."""
+        numel = 4 * self.world * S * T
+        self._parity ^= 1
+        t, hdl, _ = self._buffer(f"partials{self._parity}", numel)
+        view = t[:numel].view(4, self.world * S, T)
+        return view, self._mc_ptr(hdl), [int(p) for p in hdl.buffer_ptrs]
+
+    def d_hidden_accum(self, T: int, H: int):
+        """-> (local fp32 view [T, H], multicast address | 0)"""
+        numel = T * H
+        t, hdl, _ = self._buffer("dh_accum", numel)
+        return t[:numel].view(T, H), self._mc_ptr(hdl)
+
+
+def workspace(group, device) -> PeerWorkspace:
+    key = (group.group_name, torch.device(device).index)
+    ws = _workspaces.get(key)
+    if ws is None:
+        ws = _workspaces[key] = PeerWorkspace(group, torch.device(device))
+    return ws
+
+
+def reset():
+    _workspaces.clear()
