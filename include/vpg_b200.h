@@ -166,6 +166,13 @@ int vpg_logits_stats_bwd(const void* logits, int logits_bf16, int64_t T, int64_t
 size_t vpg_unpad_workspace_bytes(int64_t n);
 int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,
                       int32_t* cu_seqlens, int32_t* totals, void* workspace, size_t workspace_bytes, void* stream);
+/* Response-window selection on the rmpad token stream — folds verl/workers/actor/dp_actor.py:135 (roll of the ids),
+ * :221-232 (pad back) and :236-237 (slice [:, -L-1:-1]) into index arithmetic, so the lm-head only has to run on the
+ * rows whose output survives the slice.  indices [T] = padded flat positions (vpg_unpad_indices); per stream token:
+ * keep[i] = 1 if its column s satisfies S-L-1 <= s < S-1; dst[i] = b*L + s-(S-L-1) (row of the [B*L] response
+ * matrix, -1 if dropped); labels[i] = ids_rmpad[(i+1) % T] (labels / ids_rmpad may be NULL). */
+int vpg_response_rows(const int64_t* indices, const int64_t* ids_rmpad, int64_t T, int64_t S, int64_t L,
+                      uint8_t* keep, int64_t* dst, int64_t* labels, void* stream);
 /* out[i, :] = src[indices[i], :]  rows of row_bytes bytes (index_first_axis) */
 int vpg_gather_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
                     void* stream);

@@ -276,7 +276,7 @@ def reinforce_plus_plus_outcome_advantage(token_level_rewards, response_mask, ga
 def remax_outcome_advantage(token_level_rewards, reward_baselines, response_mask):
     """verl/trainer/ppo/core_algos.py:572-605: suffix sums of the masked rewards minus the per-row baseline."""
     masked = (token_level_rewards * response_mask).numpy()
-    returns = torch.from_numpy(np.ascontiguousarray(np.cumsum(masked[:, ::-1], axis=-1, dtype=np.float32)[:, ::-1]))
+    returns = torch.from_numpy(np.cumsum(masked[:, ::-1], axis=-1, dtype=np.float32)[:, ::-1].copy())
     return returns - reward_baselines.unsqueeze(-1) * response_mask, returns
 
 
@@ -379,6 +379,40 @@ def actor_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_l
         total = total + kl_loss * kl_loss_coef
     return total * loss_scale, dict(pg_loss=pg, pg_clipfrac=clipfrac, ppo_kl=ppo_kl, pg_clipfrac_lower=clipfrac_lower,
                                     entropy_loss=ent_loss, kl_loss=kl_loss)
+
+
+def actor_micro_batch(hidden_rmpad, weight, input_ids, attention_mask, old_log_probs, advantages, response_mask, *,
+                      temperature, ref_log_prob=None, cliprange_low=0.2, cliprange_high=0.2, clip_ratio_c=3.0,
+                      entropy_coeff=0.0, kl_loss_coef=0.0, kl_loss_type="low_var_kl", loss_agg_mode="token-mean",
+                      loss_scale=1.0):
+    """One micro-batch of the reference actor update from the transformer's rmpad hidden states, in the reference's
+    order (verl/workers/actor/dp_actor.py): lm-head over ALL stream tokens with labels = roll(ids_rmpad, -1) (:135,
+    dense_common.py:169-185) -> pad_input to [B,S] (:221-232) -> slice [:, -L-1:-1] (:236-237) -> loss composition
+    (:422-469) -> backward.  -> dict(loss, scalars, log_prob, entropy, d_hidden, d_weight)."""
+    B, S = input_ids.shape
+    L = response_mask.shape[-1]
+    idx, _, _, _ = unpad_indices(attention_mask)
+    ids_rmpad = input_ids.reshape(-1)[idx]
+    labels = torch.roll(ids_rmpad, shifts=-1, dims=0)
+    lp_all, ent_all = lce_forward(hidden_rmpad, weight, labels, temperature)
+    lp_leaf = lp_all.clone().requires_grad_(True)
+    ent_leaf = ent_all.clone().requires_grad_(True)
+
+    def window(x):
+        full = torch.zeros(B * S, dtype=x.dtype).index_put((idx,), x)
+        return full.view(B, S)[:, -L - 1:-1]
+
+    log_prob, entropy = window(lp_leaf), window(ent_leaf)
+    loss, scalars = actor_loss(old_log_probs, log_prob, advantages, response_mask, cliprange_low=cliprange_low,
+                               cliprange_high=cliprange_high, clip_ratio_c=clip_ratio_c, loss_agg_mode=loss_agg_mode,
+                               entropy=entropy if entropy_coeff != 0 else None, entropy_coeff=entropy_coeff,
+                               ref_log_prob=ref_log_prob, kl_loss_coef=kl_loss_coef, kl_loss_type=kl_loss_type,
+                               loss_scale=loss_scale)
+    loss.backward()
+    g_ent = ent_leaf.grad if ent_leaf.grad is not None else None
+    dh, dw = lce_backward(hidden_rmpad, weight, labels, lp_leaf.grad, g_ent, temperature)
+    return dict(loss=loss.detach(), scalars=scalars, log_prob=log_prob.detach(), entropy=entropy.detach(),
+                d_hidden=dh, d_weight=dw)
 
 
 # ------------------------------------------------------------------------------------------------ partial format

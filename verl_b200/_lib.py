@@ -67,6 +67,8 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "vpg_response_rows": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vpg_gather_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "vpg_scatter_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int, c_void_p]),
     "vpg_masked_sum": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_void_p, c_void_p]),

@@ -199,11 +199,45 @@ static inline unsigned copy_grid(int64_t total_units) {
     return static_cast<unsigned>(g < 1 ? 1 : g);
 }
 
+
+// Response-window selection on the rmpad stream (verl/workers/actor/dp_actor.py:135,221-237 folded into one pass):
+// token i of the stream sits at padded position indices[i] = b*S + s.  The reference computes log-probs for every
+// token, pads back to [B,S] and keeps columns [S-L-1, S-1); only those tokens matter.  For each stream token:
+//   keep[i]   = 1 if S-L-1 <= s < S-1
+//   dst[i]    = b*L + (s - (S-L-1))        row of the [B*L] response matrix the token lands in (-1 if dropped)
+//   labels[i] = ids_rmpad[(i+1) % T]       torch.roll(input_ids_rmpad, -1)
+__global__ void response_rows_kernel(const long long* __restrict__ indices, const long long* __restrict__ ids_rmpad,
+                                     long long T, long long S, long long L, unsigned char* __restrict__ keep,
+                                     long long* __restrict__ dst, long long* __restrict__ labels) {
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= T) return;
+    const long long pos = indices[i];
+    const long long b = pos / S, s = pos - b * S;
+    const long long j = s - (S - L - 1);
+    const bool k = (j >= 0) && (j < L);
+    keep[i] = k ? 1 : 0;
+    dst[i] = k ? b * L + j : -1;
+    if (labels) labels[i] = ids_rmpad[(i + 1 == T) ? 0 : i + 1];
+}
+
 }  // namespace vpg
 
 using namespace vpg;
 
 extern "C" {
+
+int vpg_response_rows(const int64_t* indices, const int64_t* ids_rmpad, int64_t T, int64_t S, int64_t L,
+                      uint8_t* keep, int64_t* dst, int64_t* labels, void* stream) {
+    VPG_CHECK_ARG(T >= 0 && S > 0 && L >= 0 && L < S, "invalid response window: T=%lld S=%lld L=%lld", (long long)T,
+                  (long long)S, (long long)L);
+    if (T == 0) return VPG_OK;
+    VPG_CHECK_ARG(indices && keep && dst && (!labels || ids_rmpad), "null pointer argument");
+    response_rows_kernel<<<static_cast<unsigned>(ceil_div(T, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const long long*>(indices), reinterpret_cast<const long long*>(ids_rmpad), T, S, L, keep,
+        reinterpret_cast<long long*>(dst), reinterpret_cast<long long*>(labels));
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
 
 size_t vpg_unpad_workspace_bytes(int64_t n) {
     const int64_t tiles = ceil_div(n > 0 ? n : 1, kTile);

@@ -224,6 +224,24 @@ def unpad_indices(mask2d):
     return indices_full[:nnz], seqlens, cu, int(max_seqlen)
 
 
+def response_rows(indices, ids_rmpad, S: int, L: int):
+    """Response-window selection on the rmpad stream (vpg_response_rows + compaction).
+
+    -> (sel i64 [T_sel] ascending stream positions inside the window, dst i64 [T_sel] rows of the [B*L] response
+        matrix, labels i64 [T] = roll(ids_rmpad, -1)).  One device->host read (T_sel)."""
+    _require_cuda(indices, ids_rmpad)
+    T = indices.numel()
+    dev = indices.device
+    keep = torch.empty(max(T, 1), dtype=torch.uint8, device=dev)
+    dst = torch.empty(max(T, 1), dtype=torch.int64, device=dev)
+    labels = torch.empty(max(T, 1), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_response_rows(ptr(indices.contiguous()), ptr(ids_rmpad.contiguous()), T, int(S), int(L),
+                                        ptr(keep), ptr(dst), ptr(labels), stream_ptr(dev)))
+    sel, _, _, _ = unpad_indices(keep[:T].view(1, T)) if T else (indices[:0], None, None, 0)
+    return sel, gather_rows(dst[:T], sel), labels[:T]
+
+
 def gather_rows(src, indices):
     """src [N, ...] contiguous, indices i64 [n] -> [n, ...]  (index_first_axis)."""
     _require_cuda(src, indices)

@@ -461,6 +461,8 @@ def compute_policy_loss(
 def compute_policy_loss_gpg(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean", config=None):
     """GPG policy loss (core_algos.py:797-815): agg_loss(-log_prob * advantages); the three statistics are 0."""
     cfg = dict(cliprange_low=0.2, cliprange_high=0.2, clip_ratio_c=3.0, loss_agg_mode=loss_agg_mode, pg_kind="gpg")
+    if old_log_prob is None:  # unused by GPG (the reference never reads it); the kernel still wants a valid pointer
+        old_log_prob = log_prob.detach()
     loss, _ = _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, None, None, cfg)
     zero = torch.tensor(0.0)
     return loss, zero, zero.clone(), zero.clone()
