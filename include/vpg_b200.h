@@ -259,6 +259,25 @@ int vpg_reinforce_plus_plus(const float* token_level_rewards, const void* mask, 
 int vpg_remax(const float* token_level_rewards, const float* reward_baselines, const void* mask, int mask_dtype,
               int64_t B, int64_t L, float* advantages, float* returns, void* stream);
 
+/* apply_kl_penalty (verl/trainer/ppo/ray_trainer.py:153-193): kld = kl_penalty(old_log_probs, ref_log_prob) * mask;
+ * token_level_rewards = token_level_scores - beta * kld; current_kl[0] = mean over rows of masked_mean(kld, mask, -1).
+ * workspace: vpg_kl_reward_workspace_bytes(B). */
+size_t vpg_kl_reward_workspace_bytes(int64_t B);
+int vpg_kl_reward(const float* token_level_scores, const float* old_log_probs, const float* ref_log_prob,
+                  const void* mask, int mask_dtype, int kind, float beta, int64_t B, int64_t L,
+                  float* token_level_rewards, float* current_kl, void* workspace, size_t workspace_bytes, void* stream);
+
+/* compute_data_metrics (verl/trainer/ppo/metric_utils.py:80-180) in one sweep.  values may be NULL (use_critic=False).
+ * attention_mask is [B,S] (prompt columns [0,S-L), response columns [S-L,S)); response_mask [B,L] is used as a
+ * boolean.  out26 (f32, device): score mean/max/min [0..2], rewards [3..5], advantages [6..8], returns [9..11],
+ * values [12..14], vf_explained_var [15], response_length mean/max/min/clip_ratio [16..19], prompt_length
+ * mean/max/min/clip_ratio [20..23], number of valid tokens [24], reserved [25]. */
+size_t vpg_data_metrics_workspace_bytes(int64_t B);
+int vpg_data_metrics(const float* token_level_scores, const float* token_level_rewards, const float* advantages,
+                     const float* returns, const float* values, const void* response_mask, int rmask_dtype,
+                     const void* attention_mask, int amask_dtype, int64_t B, int64_t L, int64_t S, float* out26,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
 /* compute_gae_advantage_return (core_algos.py:193-241): reverse recurrence per row with masked carry-through,
  * returns = adv + values, then masked_whiten (torch_functional.py:206-223) over the whole batch.
  * status[0] (i32, device) = 0 ok, 1 mask sum == 0, 2 mask sum == 1 (the reference raises ValueError there).

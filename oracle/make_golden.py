@@ -28,6 +28,10 @@ def _np(t):
     return np.asarray(t)
 
 
+def T_(a):
+    return torch.from_numpy(np.asarray(a))
+
+
 def _bf16(shape, gen, lo=-0.5, hi=0.5):
     return (torch.rand(*shape, generator=gen) * (hi - lo) + lo).bfloat16()
 
@@ -267,6 +271,59 @@ def gen_estimators(ref):
     np.savez_compressed(os.path.join(OUT, "estimators.npz"), **out)
 
 
+def gen_driver(ref):
+    """apply_kl_penalty / compute_data_metrics: the reference's function bodies, compiled out of files whose modules
+    cannot be imported here (ray_trainer.py imports ray; metric_utils.py imports verl.DataProto)."""
+    import json
+
+    from oracle import ref_import
+
+    g = torch.Generator().manual_seed(31)
+    B, P, L = 10, 12, 20
+    S = P + L
+    p_len = torch.randint(1, P + 1, (B,), generator=g)
+    r_len = torch.randint(1, L + 1, (B,), generator=g)
+    r_len[0], p_len[1] = L, P  # one response / one prompt at the maximum length (clip_ratio > 0)
+    pos = torch.arange(S)[None]
+    attn = ((pos >= (P - p_len)[:, None]) & (pos < (P + r_len)[:, None])).long()
+    rmask = attn[:, -L:].clone()
+    scores = torch.zeros(B, L)
+    scores[torch.arange(B), r_len - 1] = torch.rand(B, generator=g)
+    old = -torch.rand(B, L, generator=g) * 3
+    refp = old + 0.2 * torch.randn(B, L, generator=g)
+    adv = torch.randn(B, L, generator=g) * rmask
+    values = torch.randn(B, L, generator=g)
+    returns = values + 0.5 * torch.randn(B, L, generator=g)
+
+    class Batch(dict):
+        batch_size = (B,)
+
+    class Data:
+        def __init__(self, **kw):
+            self.batch, self.non_tensor_batch, self.meta_info = Batch(**kw), {}, {}
+
+    fns = ref_import.load_functions("verl/trainer/ppo/ray_trainer.py", ["apply_kl_penalty"],
+                                    dict(core_algos=ref.core_algos, masked_mean=ref.torch_functional.masked_mean, torch=torch))
+    out = dict(attn=_np(attn), rmask=_np(rmask), scores=_np(scores), old=_np(old), ref=_np(refp), adv=_np(adv),
+               values=_np(values), returns=_np(returns))
+    for kind in ("kl", "abs", "mse", "low_var_kl"):
+        ctrl = ref.core_algos.AdaptiveKLController(init_kl_coef=0.05, target_kl=0.1, horizon=1000)
+        data = Data(response_mask=rmask, token_level_scores=scores, old_log_probs=old, ref_log_prob=refp)
+        data, metrics = fns["apply_kl_penalty"](data, ctrl, kl_penalty=kind)
+        out[f"klr|{kind}|rewards"] = _np(data.batch["token_level_rewards"])
+        out[f"klr|{kind}|scalars"] = np.array([metrics["actor/reward_kl_penalty"], metrics["actor/reward_kl_penalty_coeff"],
+                                               ctrl.value], dtype=np.float64)
+    rewards = T_(out["klr|kl|rewards"])
+    mfn = ref_import.load_functions("verl/trainer/ppo/metric_utils.py", ["_compute_response_info", "compute_data_metrics"],
+                                    dict(torch=torch, Any=object, DataProto=object))
+    data = Data(token_level_scores=scores, token_level_rewards=rewards, advantages=adv, returns=returns, values=values,
+                responses=torch.zeros(B, L, dtype=torch.long), attention_mask=attn, response_mask=rmask)
+    for critic in (True, False):
+        m = mfn["compute_data_metrics"](data, use_critic=critic)
+        out[f"dm|critic{int(critic)}"] = np.array(json.dumps({k: float(v) for k, v in m.items()}))
+    np.savez_compressed(os.path.join(OUT, "driver.npz"), **out)
+
+
 def gen_rmpad(ref):
     import flash_attn.bert_padding as bp  # third-party pure-torch file, v2.8.3 in this image
 
@@ -307,7 +364,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_rmpad):
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_rmpad):
         if only and fn.__name__[4:] not in only:
             continue
         fn(ref)

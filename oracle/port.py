@@ -415,6 +415,43 @@ def actor_micro_batch(hidden_rmpad, weight, input_ids, attention_mask, old_log_p
                 d_hidden=dh, d_weight=dw)
 
 
+# ------------------------------------------------------------------------------------------------ driver-side ops
+def kl_reward(token_level_scores, old_log_probs, ref_log_prob, response_mask, kind, beta):
+    """verl/trainer/ppo/ray_trainer.py:153-193 (apply_kl_penalty without the DataProto / controller plumbing):
+    -> (token_level_rewards, current_kl as a python float)"""
+    kld = kl_penalty(old_log_probs, ref_log_prob, kind) * response_mask
+    rewards = token_level_scores - beta * kld
+    per_seq = masked_mean(kld, response_mask, axis=-1)
+    return rewards, torch.mean(per_seq, dim=0).item()
+
+
+def data_metrics(token_level_scores, token_level_rewards, advantages, returns, values, response_mask, attention_mask):
+    """verl/trainer/ppo/metric_utils.py:80-180 -> dict with the reference's keys (values=None: use_critic=False)."""
+    L = response_mask.shape[-1]
+    seq_score, seq_reward = token_level_scores.sum(-1), token_level_rewards.sum(-1)
+    keep = response_mask.bool()
+    prompt_len = attention_mask[:, :-L].sum(-1).float()
+    resp_len = attention_mask[:, -L:].sum(-1).float()
+    out = {}
+
+    def stats(name, x):
+        out[f"{name}/mean"], out[f"{name}/max"], out[f"{name}/min"] = x.mean().item(), x.max().item(), x.min().item()
+
+    stats("critic/score", seq_score)
+    stats("critic/rewards", seq_reward)
+    stats("critic/advantages", advantages[keep])
+    stats("critic/returns", returns[keep])
+    if values is not None:
+        stats("critic/values", values[keep])
+        out["critic/vf_explained_var"] = (1.0 - torch.var(returns[keep] - values[keep]) /
+                                          (torch.var(returns[keep]) + 1e-5)).item()
+    stats("response_length", resp_len)
+    out["response_length/clip_ratio"] = torch.eq(resp_len, L).float().mean().item()
+    stats("prompt_length", prompt_len)
+    out["prompt_length/clip_ratio"] = torch.eq(prompt_len, attention_mask.shape[-1] - L).float().mean().item()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ partial format
 def lce_partials(hidden, weight, labels, temperature, label_offset=0, num_splits=1):
     """CPU restatement of the PARTIAL format the CUDA forward emits (include/vpg_b200.h, vpg_lce_fwd_partials):

@@ -109,6 +109,18 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p,
          c_size_t, c_void_p],
     ),
+    "vpg_kl_reward_workspace_bytes": (c_size_t, [c_int64]),
+    "vpg_kl_reward": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int64, c_int64, c_void_p, c_void_p,
+         c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_data_metrics_workspace_bytes": (c_size_t, [c_int64]),
+    "vpg_data_metrics": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int64, c_int64,
+         c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
     "vpg_gae_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "vpg_gae": (
         c_int,

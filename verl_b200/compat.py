@@ -6,8 +6,9 @@
       179-185, qwen2_vl.py:544, qwen2_5_vl.py:273-279, verl/models/mcore/model_forward_fused.py:302-309)
   verl.utils.kernel.kernels.{set_backward_method, BackwardEnum, EntropyReductionEnum, ...}
   verl.utils.torch_functional.{logprobs_from_logits, entropy_from_logits, masked_mean, ...}
-  verl.trainer.ppo.core_algos.{compute_policy_loss, agg_loss, kl_penalty, compute_grpo_outcome_advantage,
-      compute_gae_advantage_return} (+ registry entries "gae" and "grpo")
+  verl.trainer.ppo.core_algos.{compute_policy_loss, agg_loss, kl_penalty, compute_value_loss, compute_policy_loss_gpg,
+      compute_grpo_outcome_advantage, compute_gae_advantage_return and the seven other estimators}
+      (+ every ADV_ESTIMATOR_REGISTRY entry and the "gpg" POLICY_LOSS_REGISTRY entry)
   flash_attn.bert_padding.{unpad_input, pad_input, index_first_axis}   (only with patch_flash_attn=True)
 
 If the real ``verl`` package is importable its modules are patched attribute by attribute (everything outside the
@@ -34,7 +35,11 @@ _TF_NAMES = [
     "gather_from_labels",
 ]
 _CA_NAMES = ["compute_policy_loss", "agg_loss", "kl_penalty", "compute_grpo_outcome_advantage",
-             "compute_gae_advantage_return", "compute_rewards"]
+             "compute_gae_advantage_return", "compute_rewards", "compute_grpo_passk_outcome_advantage",
+             "compute_reinforce_plus_plus_baseline_outcome_advantage", "compute_rloo_outcome_advantage",
+             "compute_opo_outcome_advantage", "compute_reinforce_plus_plus_outcome_advantage",
+             "compute_remax_outcome_advantage", "compute_gpg_outcome_advantage", "compute_policy_loss_gpg",
+             "compute_value_loss"]
 
 
 def _try_import(name):
@@ -71,8 +76,10 @@ def install(patch_flash_attn: bool = False) -> dict:
             for n in names:
                 setattr(real, n, getattr(src, n))
             if name.endswith("core_algos"):
-                for key in ("gae", "grpo"):
-                    real.ADV_ESTIMATOR_REGISTRY[key] = _ca.ADV_ESTIMATOR_REGISTRY[key]
+                for key, fn in _ca.ADV_ESTIMATOR_REGISTRY.items():
+                    real.ADV_ESTIMATOR_REGISTRY[key] = fn
+                for key, fn in _ca.POLICY_LOSS_REGISTRY.items():  # "gpg"; clip_cov / kl_cov stay the reference's
+                    real.POLICY_LOSS_REGISTRY[key] = fn
             report[name] = "patched"
         else:
             parent, _, leaf = name.rpartition(".")

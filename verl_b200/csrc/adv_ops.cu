@@ -440,3 +440,298 @@ int vpg_remax(const float* rewards, const float* reward_baselines, const void* m
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// Driver-side token ops on the batch tensors
+// =====================================================================================================
+namespace vpg {
+
+__device__ __forceinline__ float kl_value(int kind, float lp, float ref) {
+    if (kind == VPG_KL_K1) return lp - ref;
+    if (kind == VPG_KL_ABS) return fabsf(lp - ref);
+    if (kind == VPG_KL_MSE) {
+        const float d = lp - ref;
+        return 0.5f * (d * d);
+    }
+    const float k = clampf(ref - lp, -20.f, 20.f);  // low_var_kl
+    return clampf(expf(k) - k - 1.f, -10.f, 10.f);
+}
+
+// apply_kl_penalty (verl/trainer/ppo/ray_trainer.py:153-193): kld = kl_penalty(old, ref) * mask;
+// token_level_rewards = scores - beta * kld; current_kl = mean_b( masked_mean(kld, mask, axis=-1) ).
+// ws (doubles): [0] u32 counter | [1, 1+B) row sums of where(m, kld, 0)*m | [1+B, 1+2B) row mask sums
+template <int VEC, typename MT>
+__global__ void kl_reward_kernel(const float* __restrict__ scores, const float* __restrict__ old_lp,
+                                 const float* __restrict__ ref_lp, const MT* __restrict__ mask, long long B, long long L,
+                                 int gx, int kind, float beta, float* __restrict__ rewards, float* __restrict__ out,
+                                 double* ws) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    float a = 0.f, c = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
+        const long long i = base + t;
+        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> sc = ldv<VEC>(scores, i);
+        const Pack<VEC> lo = ldv<VEC>(old_lp, i);
+        const Pack<VEC> lr = ldv<VEC>(ref_lp, i);
+        Pack<VEC> o;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const float kld = kl_value(kind, lo.v[j], lr.v[j]) * m.v[j];
+            o.v[j] = sc.v[j] - beta * kld;
+            a += (m.v[j] != 0.f ? kld : 0.f) * m.v[j];
+            c += m.v[j];
+        }
+        stv<VEC>(rewards, i, o);
+    }
+    const double ta = block_sum<double>(static_cast<double>(a), red);
+    const double tc = block_sum<double>(static_cast<double>(c), red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&ws[1 + b], ta);
+        atomicAdd(&ws[1 + B + b], tc);
+    }
+    if (last_block_done(reinterpret_cast<unsigned int*>(ws), gridDim.x)) {
+        double s = 0.0;
+        for (long long i = threadIdx.x; i < B; i += blockDim.x)
+            s += static_cast<double>(static_cast<float>(__ldcg(&ws[1 + i]) / (__ldcg(&ws[1 + B + i]) + 1e-8)));
+        s = block_sum<double>(s, red);
+        if (threadIdx.x == 0) out[0] = static_cast<float>(s / static_cast<double>(B));
+    }
+}
+
+// ---- compute_data_metrics (verl/trainer/ppo/metric_utils.py:80-180) ------------------------------------------
+// One sweep over the [B,L] tensors.  acc (doubles, zeroed): per masked tensor q in {adv, returns, values}:
+//   [5q+0] sum  [5q+1] sum of squares  then max / min keys (u32, order preserving) in keys[2q], keys[2q+1];
+//   [15] sum (ret - val)  [16] sum (ret - val)^2  [17] count of masked tokens
+// rows (doubles): [0,B) score row sums | [B,2B) reward row sums | [2B,3B) response lengths | [3B,4B) prompt lengths
+constexpr int kDmAcc = 18;
+
+__device__ __forceinline__ unsigned int fkey(float f) {
+    const unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float fkey_inv(unsigned int k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+template <typename MT>
+__global__ void data_metrics_kernel(const float* __restrict__ scores, const float* __restrict__ rewards,
+                                    const float* __restrict__ adv, const float* __restrict__ rets,
+                                    const float* __restrict__ vals, const MT* __restrict__ rmask, long long L, int gx,
+                                    long long B, double* __restrict__ acc, unsigned int* __restrict__ keys,
+                                    double* __restrict__ rows) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x / gx;
+    const int cx = blockIdx.x % gx;
+    const long long base = b * L;
+    float s_sc = 0.f, s_rw = 0.f, cnt = 0.f;
+    float s1[3] = {0.f, 0.f, 0.f}, s2[3] = {0.f, 0.f, 0.f};
+    float mx[3] = {-INFINITY, -INFINITY, -INFINITY}, mn[3] = {INFINITY, INFINITY, INFINITY};
+    float d1 = 0.f, d2 = 0.f;
+    const long long stride = static_cast<long long>(gx) * blockDim.x;
+    for (long long t = static_cast<long long>(cx) * blockDim.x + threadIdx.x; t < L; t += stride) {
+        const long long i = base + t;
+        s_sc += scores[i];
+        s_rw += rewards[i];
+        if (mask_to_float(rmask[i]) != 0.f) {  // response_mask.bool() (metric_utils.py:109)
+            cnt += 1.f;
+            const float q[3] = {adv[i], rets[i], vals ? vals[i] : 0.f};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                s1[k] += q[k];
+                s2[k] += q[k] * q[k];
+                mx[k] = fmaxf(mx[k], q[k]);
+                mn[k] = fminf(mn[k], q[k]);
+            }
+            const float d = q[1] - q[2];
+            d1 += d;
+            d2 += d * d;
+        }
+    }
+    double v[kDmAcc];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) v[5 * k] = s1[k], v[5 * k + 1] = s2[k];
+    v[15] = d1, v[16] = d2, v[17] = cnt;
+    const double r_sc = block_sum<double>(static_cast<double>(s_sc), red);
+    const double r_rw = block_sum<double>(static_cast<double>(s_rw), red);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double a1 = block_sum<double>(v[5 * k], red), a2 = block_sum<double>(v[5 * k + 1], red);
+        if (threadIdx.x == 0) atomicAdd(&acc[5 * k], a1), atomicAdd(&acc[5 * k + 1], a2);
+        // block max / min through warp shuffles on the keys
+        unsigned int kmx = fkey(mx[k]), kmn = fkey(mn[k]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+            kmn = min(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicMax(&keys[2 * k], kmx);
+            atomicMin(&keys[2 * k + 1], kmn);
+        }
+    }
+    const double a15 = block_sum<double>(v[15], red), a16 = block_sum<double>(v[16], red);
+    const double a17 = block_sum<double>(v[17], red);
+    if (threadIdx.x == 0) {
+        atomicAdd(&acc[15], a15), atomicAdd(&acc[16], a16), atomicAdd(&acc[17], a17);
+        atomicAdd(&rows[b], r_sc);
+        atomicAdd(&rows[B + b], r_rw);
+    }
+}
+
+// prompt / response lengths from attention_mask [B,S] (metric_utils.py:57-75): one block per row
+template <typename MT>
+__global__ void seq_lengths_kernel(const MT* __restrict__ attn, long long S, long long L, long long B,
+                                   double* __restrict__ rows) {
+    __shared__ double red[32];
+    const long long base = static_cast<long long>(blockIdx.x) * S;
+    float p = 0.f, r = 0.f;
+    for (long long t = threadIdx.x; t < S; t += blockDim.x) {
+        const float m = mask_to_float(attn[base + t]);
+        if (t < S - L) p += m; else r += m;
+    }
+    const double tp = block_sum<double>(static_cast<double>(p), red);
+    const double tr = block_sum<double>(static_cast<double>(r), red);
+    if (threadIdx.x == 0) {
+        rows[2 * B + blockIdx.x] = tr;
+        rows[3 * B + blockIdx.x] = tp;
+    }
+}
+
+// out[0..25]: score mean/max/min, rewards mean/max/min, adv mean/max/min, returns mean/max/min, values mean/max/min,
+// vf_explained_var, response_length mean/max/min/clip_ratio, prompt_length mean/max/min/clip_ratio, n_valid, (pad)
+__global__ void data_metrics_finalize_kernel(const double* __restrict__ acc, const unsigned int* __restrict__ keys,
+                                             const double* __restrict__ rows, long long B, long long L,
+                                             long long P, int use_critic, float* __restrict__ out) {
+    __shared__ double red[32];
+    __shared__ float fmx[4], fmn[4];
+    // sequence-level: mean / max / min over B of the four row quantities (fp32 values like the reference's tensors)
+    for (int q = 0; q < 4; ++q) {
+        double s = 0.0;
+        float mx = -INFINITY, mn = INFINITY;
+        double clip = 0.0;
+        for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+            const float v = static_cast<float>(rows[q * B + i]);
+            s += v;
+            mx = fmaxf(mx, v);
+            mn = fminf(mn, v);
+            if (q == 2 && v == static_cast<float>(L)) clip += 1.0;
+            if (q == 3 && v == static_cast<float>(P)) clip += 1.0;
+        }
+        s = block_sum<double>(s, red);
+        clip = block_sum<double>(clip, red);
+        unsigned int kmx = fkey(mx), kmn = fkey(mn);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+            kmn = min(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+        }
+        __shared__ unsigned int wmx[32], wmn[32];
+        if ((threadIdx.x & 31) == 0) wmx[threadIdx.x >> 5] = kmx, wmn[threadIdx.x >> 5] = kmn;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned int a = wmx[0], bmin = wmn[0];
+            for (int w = 1; w < (blockDim.x >> 5); ++w) a = max(a, wmx[w]), bmin = min(bmin, wmn[w]);
+            fmx[q] = fkey_inv(a), fmn[q] = fkey_inv(bmin);
+            const int o = (q < 2) ? 3 * q : (q == 2 ? 16 : 20);
+            out[o] = static_cast<float>(s / static_cast<double>(B));
+            out[o + 1] = fmx[q];
+            out[o + 2] = fmn[q];
+            if (q >= 2) out[o + 3] = static_cast<float>(clip / static_cast<double>(B));
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double n = acc[17];
+        for (int k = 0; k < 3; ++k) {
+            out[6 + 3 * k] = static_cast<float>(acc[5 * k] / n);
+            out[7 + 3 * k] = fkey_inv(keys[2 * k]);
+            out[8 + 3 * k] = fkey_inv(keys[2 * k + 1]);
+        }
+        // torch.var (unbiased) of returns and of returns - values over the valid tokens
+        const double var_ret = (acc[6] - acc[5] * acc[5] / n) / (n - 1.0);
+        const double var_diff = (acc[16] - acc[15] * acc[15] / n) / (n - 1.0);
+        out[15] = use_critic ? static_cast<float>(1.0 - var_diff / (var_ret + 1e-5)) : 0.f;
+        out[24] = static_cast<float>(n);
+        out[25] = 0.f;
+    }
+}
+
+}  // namespace vpg
+
+extern "C" {
+
+size_t vpg_kl_reward_workspace_bytes(int64_t B) { return static_cast<size_t>(1 + 2 * (B > 0 ? B : 0)) * sizeof(double); }
+
+int vpg_kl_reward(const float* token_level_scores, const float* old_log_probs, const float* ref_log_prob,
+                  const void* mask, int mask_dtype, int kind, float beta, int64_t B, int64_t L,
+                  float* token_level_rewards, float* current_kl, void* workspace, size_t workspace_bytes,
+                  void* stream_) {
+    VPG_CHECK_ARG(token_level_scores && old_log_probs && ref_log_prob && mask && token_level_rewards && current_kl,
+                  "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
+    if (kind < 0 || kind > 3) return set_error(VPG_ERR_UNSUPPORTED, "kl_penalty kind %d is not implemented", kind);
+    const size_t need = vpg_kl_reward_workspace_bytes(B);
+    if (!workspace || workspace_bytes < need) return set_error(VPG_ERR_WORKSPACE, "kl_reward workspace too small");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+    const bool vec = rows_vec_ok(L, mask, mask_dtype, {token_level_scores, old_log_probs, ref_log_prob, token_level_rewards});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const unsigned grid = static_cast<unsigned>(B * gx);
+    double* ws = static_cast<double*>(workspace);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        const MT* mk = static_cast<const MT*>(mask);
+        if (vec)
+            kl_reward_kernel<4, MT><<<grid, kThreads, 0, stream>>>(token_level_scores, old_log_probs, ref_log_prob, mk, B,
+                                                                   L, gx, kind, beta, token_level_rewards, current_kl, ws);
+        else
+            kl_reward_kernel<1, MT><<<grid, kThreads, 0, stream>>>(token_level_scores, old_log_probs, ref_log_prob, mk, B,
+                                                                   L, gx, kind, beta, token_level_rewards, current_kl, ws);
+    });
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+size_t vpg_data_metrics_workspace_bytes(int64_t B) {
+    return static_cast<size_t>(kDmAcc + 4 * (B > 0 ? B : 0)) * sizeof(double) + 8 * sizeof(unsigned int);
+}
+
+int vpg_data_metrics(const float* token_level_scores, const float* token_level_rewards, const float* advantages,
+                     const float* returns, const float* values, const void* response_mask, int rmask_dtype,
+                     const void* attention_mask, int amask_dtype, int64_t B, int64_t L, int64_t S, float* out26,
+                     void* workspace, size_t workspace_bytes, void* stream_) {
+    VPG_CHECK_ARG(token_level_scores && token_level_rewards && advantages && returns && response_mask &&
+                      attention_mask && out26,
+                  "null pointer argument");
+    VPG_CHECK_ARG(B > 0 && L > 0 && S >= L, "invalid shape B=%lld L=%lld S=%lld", (long long)B, (long long)L, (long long)S);
+    const size_t need = vpg_data_metrics_workspace_bytes(B);
+    if (!workspace || workspace_bytes < need) return set_error(VPG_ERR_WORKSPACE, "data_metrics workspace too small");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    double* acc = static_cast<double*>(workspace);
+    double* rows = acc + kDmAcc;
+    unsigned int* keys = reinterpret_cast<unsigned int*>(rows + 4 * B);
+    VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
+    // min keys start at the largest key (memset 0xff on the three min slots is done by initialising all six keys):
+    static const unsigned int init_keys[8] = {0u, 0xffffffffu, 0u, 0xffffffffu, 0u, 0xffffffffu, 0u, 0u};
+    VPG_CUDA(cudaMemcpyAsync(keys, init_keys, sizeof(init_keys), cudaMemcpyHostToDevice, stream));
+    const int gx = blocks_per_row(B, L, 1);
+    VPG_DISPATCH_MASK(rmask_dtype, MT, {
+        data_metrics_kernel<MT><<<static_cast<unsigned>(B * gx), kThreads, 0, stream>>>(
+            token_level_scores, token_level_rewards, advantages, returns, values, static_cast<const MT*>(response_mask),
+            L, gx, B, acc, keys, rows);
+    });
+    count_launch();
+    VPG_DISPATCH_MASK(amask_dtype, MT, {
+        seq_lengths_kernel<MT><<<static_cast<unsigned>(B), kThreads, 0, stream>>>(static_cast<const MT*>(attention_mask), S,
+                                                                                  L, B, rows);
+    });
+    count_launch();
+    data_metrics_finalize_kernel<<<1, 256, 0, stream>>>(acc, keys, rows, B, L, S - L, values != nullptr, out26);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+}  // extern "C"

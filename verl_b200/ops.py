@@ -436,6 +436,48 @@ def remax(token_level_rewards, reward_baselines, response_mask):
     return adv, ret
 
 
+def kl_reward(token_level_scores, old_log_probs, ref_log_prob, response_mask, kind: str, beta: float):
+    """apply_kl_penalty's math in one pass -> (token_level_rewards fp32 [B,L], current_kl fp32 [1] on the device)."""
+    if kind == "full" or kind not in KL_KINDS:
+        raise NotImplementedError
+    _require_cuda(token_level_scores, old_log_probs, ref_log_prob, response_mask)
+    sc, lo, lr = _f32c(token_level_scores), _f32c(old_log_probs), _f32c(ref_log_prob)
+    m, mdt = mask_arg(response_mask.contiguous())
+    B, L = sc.shape
+    lib = _lib_()
+    out = torch.empty_like(sc)
+    cur = torch.empty(1, dtype=_F32, device=sc.device)
+    ws = _ws(int(lib.vpg_kl_reward_workspace_bytes(B)), sc.device)
+    with torch.cuda.device(sc.device):
+        check(lib.vpg_kl_reward(ptr(sc), ptr(lo), ptr(lr), ptr(m), mdt, KL_KINDS[kind], float(beta), B, L, ptr(out),
+                                ptr(cur), ptr(ws), ws.numel() * 8, stream_ptr(sc.device)))
+    return out, cur
+
+
+DATA_METRIC_SLOTS = {
+    "critic/score": 0, "critic/rewards": 3, "critic/advantages": 6, "critic/returns": 9, "critic/values": 12,
+    "critic/vf_explained_var": 15, "response_length": 16, "prompt_length": 20, "n_valid": 24,
+}
+
+
+def data_metrics(token_level_scores, token_level_rewards, advantages, returns, values, response_mask, attention_mask):
+    """compute_data_metrics' statistics in one sweep -> fp32 [26] device tensor (layout: vpg_data_metrics)."""
+    _require_cuda(token_level_scores, token_level_rewards, advantages, returns, response_mask, attention_mask)
+    sc, rw, adv, ret = (_f32c(t) for t in (token_level_scores, token_level_rewards, advantages, returns))
+    val = _f32c(values) if values is not None else None
+    rm, rdt = mask_arg(response_mask.contiguous())
+    am, adt = mask_arg(attention_mask.contiguous())
+    B, L = sc.shape
+    S = am.shape[-1]
+    lib = _lib_()
+    out = torch.empty(26, dtype=_F32, device=sc.device)
+    ws = _ws(int(lib.vpg_data_metrics_workspace_bytes(B)), sc.device)
+    with torch.cuda.device(sc.device):
+        check(lib.vpg_data_metrics(ptr(sc), ptr(rw), ptr(adv), ptr(ret), ptr(val), ptr(rm), rdt, ptr(am), adt, B, L, S,
+                                   ptr(out), ptr(ws), ws.numel() * 8, stream_ptr(sc.device)))
+    return out
+
+
 def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: int, epsilon: float, norm_by_std: bool):
     _require_cuda(token_level_rewards, response_mask, group_ids)
     r = _f32c(token_level_rewards)
