@@ -85,6 +85,18 @@ def ops_table(d, B, L, n_uid):
         ("grpo_advantage", lambda: ops.grpo_advantage(d["rewards"], d["mask"], gids, ng, 1e-6, True), n * 16),
         ("gae + whiten", lambda: ops.gae(d["rewards"], d["values"], d["mask"], 0.99, 0.95), n * (16 + 8 + 8)),
         ("masked_whiten", lambda: ops.masked_whiten(d["values"], d["mask"]), n * (12 + 8)),
+        ("rloo_advantage (outcome_advantage skeleton)",
+         lambda: ops.outcome_advantage("rloo", d["rewards"], d["mask"], gids, ng), n * (12 + 8 + 4)),
+        ("reinforce++ (reverse scan + whiten*mask)", lambda: ops.reinforce_plus_plus(d["rewards"], d["mask"], 0.99),
+         n * (12 + 4 + 12 + 4)),
+        ("remax (reverse cumsum)", lambda: ops.remax(d["rewards"], d["lens"].float(), d["mask"]), n * (12 + 8)),
+        ("value_loss fwd+grad", lambda: ops.value_loss(d["values"], d["lp"], d["old"], d["mask"], 0.2, "token-mean", True),
+         n * (8 + 8 + 12 + 4)),
+        ("kl_reward (apply_kl_penalty)", lambda: ops.kl_reward(d["rewards"], d["old"], d["ref"], d["mask"], "kl", 0.01),
+         n * (8 + 12 + 4)),
+        ("data_metrics (compute_data_metrics sweep)",
+         lambda: ops.data_metrics(d["rewards"], d["rewards"], d["adv"], d["lp"], d["values"], d["mask"], attn),
+         n * (8 + 20 + 8)),
         ("unpad_indices (int64 mask)", lambda: ops.unpad_indices(attn), n * 16 + nnz * 8),
         ("gather_rows int64 ids (index_first_axis)", lambda: ops.gather_rows(flat_ids, idx), nnz * 24),
         ("pad_input fp32 [nnz,1] -> [B*L,1]", lambda: ops.scatter_rows(vals, idx, n), nnz * 12 + n * 4),

@@ -270,3 +270,40 @@ def test_large_batch_properties(dev):
     # token-mean: per-token gradient scales with 1/N
     close(lp.grad[:half] * (n1 / n2), lp2.grad, rel=1e-5, abs_=1e-12)
     assert n1 == float(mask.sum()) and torch.isfinite(loss)
+
+
+def test_masked_ops_any_axis(dev):
+    """masked_sum / masked_mean over every axis choice of a 3-D tensor (the reference accepts any `axis`)."""
+    from verl_b200.utils import torch_functional as F
+
+    torch.manual_seed(5)
+    v = torch.randn(3, 5, 7)
+    m = (torch.rand(3, 5, 7) > 0.4).long()
+    for axis in (0, 1, 2, -1, -2, (0, 1), (1, 2), (0, 2), [0]):
+        ax = tuple(axis) if isinstance(axis, list) else axis
+        close(F.masked_sum(v.to(dev), m.to(dev), axis=axis), port.masked_sum(v, m, axis=ax), abs_=1e-6)
+        close(F.masked_mean(v.to(dev), m.to(dev), axis=axis), port.masked_mean(v, m, axis=ax), abs_=1e-6)
+
+
+def test_nan_propagates_like_torch(dev):
+    """torch.clamp / maximum / min propagate NaN: a NaN log-prob on a response token must give a NaN loss (that is how
+    a diverged run is noticed); a NaN on a masked-out token must not (masked_mean zeroes it first)."""
+    from verl_b200.trainer.ppo import core_algos as ca
+
+    B, L = 2, 8
+    old = -torch.rand(B, L, device=dev)
+    adv = torch.randn(B, L, device=dev)
+    mask = torch.ones(B, L, dtype=torch.long, device=dev)
+    mask[1, 5:] = 0
+    lp = old.clone()
+    lp[1, 6] = float("nan")  # masked out
+    loss, _ = ca.fused_actor_loss(old, lp, adv, mask, cliprange=0.2)
+    want, _ = port.actor_loss(old.cpu(), lp.cpu(), adv.cpu(), mask.cpu(), cliprange_low=0.2, cliprange_high=0.2)
+    assert torch.isfinite(loss) and torch.isfinite(want)
+    close(loss, want)
+    lp[0, 2] = float("nan")  # a response token
+    loss, _ = ca.fused_actor_loss(old, lp, adv, mask, cliprange=0.2)
+    want, _ = port.actor_loss(old.cpu(), lp.cpu(), adv.cpu(), mask.cpu(), cliprange_low=0.2, cliprange_high=0.2)
+    assert torch.isnan(want) and torch.isnan(loss)
+    kl = ca.kl_penalty(lp, old, "low_var_kl")
+    assert torch.isnan(kl[0, 2]) and torch.isfinite(kl[0, 3])

@@ -212,7 +212,7 @@ template <typename MT, int MODE>
 __global__ void __launch_bounds__(512)
 reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ mask, const float* __restrict__ baselines,
                     long long L, float gamma, float* __restrict__ adv_out, float* __restrict__ ret_out,
-                    double* __restrict__ sums) {
+                    double* __restrict__ sums, int vec) {
     __shared__ Lin warp_maps[32];
     __shared__ float carry;
     __shared__ double red[32];
@@ -227,12 +227,23 @@ reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ ma
         __syncthreads();
         const long long t0 = ck * span + static_cast<long long>(threadIdx.x) * kScanSeg;
         float r[kScanSeg], m[kScanSeg];
+        const bool full = vec && (t0 + kScanSeg <= L);  // 128-bit path: 32 contiguous, aligned bytes per thread
+        if (full) {
 #pragma unroll
-        for (int j = 0; j < kScanSeg; ++j) {
-            const long long t = t0 + j;
-            const bool ok = t < L;
-            r[j] = ok ? rewards[base + t] : 0.f;
-            m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps (see below)
+            for (int q = 0; q < kScanSeg / 4; ++q) {
+                const float4 a = load_f4(rewards, base + t0 + 4 * q);
+                const float4 c = load_mask4<MT>(mask, base + t0 + 4 * q);
+                r[4 * q] = a.x, r[4 * q + 1] = a.y, r[4 * q + 2] = a.z, r[4 * q + 3] = a.w;
+                m[4 * q] = c.x, m[4 * q + 1] = c.y, m[4 * q + 2] = c.z, m[4 * q + 3] = c.w;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < kScanSeg; ++j) {
+                const long long t = t0 + j;
+                const bool ok = t < L;
+                r[j] = ok ? rewards[base + t] : 0.f;
+                m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps (see below)
+            }
         }
         Lin seg{1.f, 0.f};
 #pragma unroll
@@ -281,15 +292,25 @@ reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ ma
         for (int j = 0; j < kScanSeg; ++j) {
             const long long t = t0 + j;
             if (t < L) {
-                ret_out[base + t] = R[j];
+                if (!full) ret_out[base + t] = R[j];
                 if (MODE == 0) {
                     const bool on = m[j] != 0.f;
                     s1 += (on ? R[j] : 0.f) * m[j];
                     s2 += (on ? R[j] * R[j] : 0.f) * m[j];
                     sc += m[j];
-                } else {
+                } else if (!full) {
                     adv_out[base + t] = R[j] - bsl * m[j];
                 }
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int q = 0; q < kScanSeg / 4; ++q) {
+                store_f4(ret_out, base + t0 + 4 * q, make_float4(R[4 * q], R[4 * q + 1], R[4 * q + 2], R[4 * q + 3]));
+                if (MODE == 1)
+                    store_f4(adv_out, base + t0 + 4 * q,
+                             make_float4(R[4 * q] - bsl * m[4 * q], R[4 * q + 1] - bsl * m[4 * q + 1],
+                                         R[4 * q + 2] - bsl * m[4 * q + 2], R[4 * q + 3] - bsl * m[4 * q + 3]));
             }
         }
         __syncthreads();
@@ -411,11 +432,11 @@ int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dty
     VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
     VPG_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
     const int64_t n = B * L;
-    const bool vec = rows_vec_ok(n, mask, mask_dtype, {returns, advantages});
+    const bool vec = rows_vec_ok(n, mask, mask_dtype, {rewards, returns, advantages});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         reverse_scan_kernel<MT, 0><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
-            rewards, mk, nullptr, L, gamma, advantages, returns, sums);
+            rewards, mk, nullptr, L, gamma, advantages, returns, sums, (L % kScanSeg == 0) && vec);
         count_launch();
         if (vec)
             whiten_mask_apply_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(returns, mk, n, sums, advantages, status);
@@ -431,9 +452,10 @@ int vpg_remax(const float* rewards, const float* reward_baselines, const void* m
     VPG_CHECK_ARG(rewards && reward_baselines && mask && advantages && returns, "null pointer argument");
     VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int vec = (L % kScanSeg == 0) && rows_vec_ok(L, mask, mask_dtype, {rewards, advantages, returns});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         reverse_scan_kernel<MT, 1><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
-            rewards, static_cast<const MT*>(mask), reward_baselines, L, 1.f, advantages, returns, nullptr);
+            rewards, static_cast<const MT*>(mask), reward_baselines, L, 1.f, advantages, returns, nullptr, vec);
     });
     VPG_LAUNCH_CHECK();
     return VPG_OK;

@@ -22,31 +22,52 @@ __device__ __forceinline__ bool mask_nonzero(MT m) {
     return m != MT(0);
 }
 
-// nonzero count of every tile
+// Pass 1 — the ONLY pass over the mask: nonzero count of every tile, the nonzero bitmap (one 32-bit ballot per warp and
+// item: 1 bit per element, read back by the write pass instead of the 1-8 byte mask elements), and the per-row sums
+// of the mask VALUES (seqlens).  Layout: element = tile0 + j*256 + tid (coalesced); a warp's 32 elements of one item
+// almost always sit in one row, so lane 0 keeps a running (row, sum) and issues one integer atomic per row change.
 template <typename MT>
-__global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, int* __restrict__ tile_counts) {
+__global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, long long S, int* __restrict__ tile_counts,
+                                  unsigned int* __restrict__ bits, int* __restrict__ seqlens) {
     __shared__ int red[32];
     const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int c = 0;
+    long long cur_row = -1;
+    long long cur_sum = 0;
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
-        // warp-contiguous layout: element = tile0 + j*256 + tid  (coalesced)
         const long long i = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
-        c += (i < n && mask_nonzero(mask[i])) ? 1 : 0;
+        const bool in = i < n;
+        const MT m = in ? mask[i] : MT(0);
+        const bool nz = in && mask_nonzero(m);
+        const unsigned bal = __ballot_sync(0xffffffffu, nz);
+        if (lane == 0) bits[(static_cast<long long>(blockIdx.x) * kItems + j) * (kTileThreads / 32) + w] = bal;
+        c += nz ? 1 : 0;
+        // ---- seqlens
+        const long long first = i - lane;  // element of lane 0
+        if (first < n) {
+            const long long last = (first + 31 < n) ? first + 31 : n - 1;
+            const long long r0 = first / S, r1 = last / S;
+            long long v = in ? static_cast<long long>(m) : 0;
+            if (r0 == r1) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) {
+                    if (r0 != cur_row) {
+                        if (cur_row >= 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], static_cast<int>(cur_sum));
+                        cur_row = r0, cur_sum = 0;
+                    }
+                    cur_sum += v;
+                }
+            } else if (in && v != 0) {  // a row boundary inside the warp's 32 elements (S < 32 or unaligned rows)
+                atomicAdd(&seqlens[i / S], static_cast<int>(v));
+            }
+        }
     }
+    if (lane == 0 && cur_row >= 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], static_cast<int>(cur_sum));
     const int tot = block_sum<int>(c, red);
     if (threadIdx.x == 0) tile_counts[blockIdx.x] = tot;
-}
-
-// per-row integer sums (seqlens); one block per row
-template <typename MT>
-__global__ void row_len_kernel(const MT* __restrict__ mask, long long S, int* __restrict__ seqlens) {
-    __shared__ long long red[32];
-    const long long base = static_cast<long long>(blockIdx.x) * S;
-    long long c = 0;
-    for (long long t = threadIdx.x; t < S; t += blockDim.x) c += static_cast<long long>(mask[base + t]);
-    const long long tot = block_sum<long long>(c, red);
-    if (threadIdx.x == 0) seqlens[blockIdx.x] = static_cast<int>(tot);
 }
 
 // single block: exclusive scan of tile counts -> tile_offsets (long long), inclusive scan of seqlens -> cu_seqlens,
@@ -123,20 +144,16 @@ __global__ void scan_kernel(const int* __restrict__ tile_counts, int num_tiles, 
     }
 }
 
-// ordered write of the nonzero positions of each tile
-template <typename MT>
-__global__ void tile_write_kernel(const MT* __restrict__ mask, long long n, const long long* __restrict__ tile_offsets,
+// Pass 2: ordered write of the nonzero positions of each tile from the bitmap (the mask is not read again)
+__global__ void tile_write_kernel(const unsigned int* __restrict__ bits, const long long* __restrict__ tile_offsets,
                                   long long* __restrict__ indices) {
     __shared__ int warp_cnt[kItems][kTileThreads / 32];
     const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    bool f[kItems];
     unsigned bal[kItems];
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
-        const long long i = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
-        f[j] = (i < n) && mask_nonzero(mask[i]);
-        bal[j] = __ballot_sync(0xffffffffu, f[j]);
+        bal[j] = bits[(static_cast<long long>(blockIdx.x) * kItems + j) * (kTileThreads / 32) + w];
         if (lane == 0) warp_cnt[j][w] = __popc(bal[j]);
     }
     __syncthreads();
@@ -152,7 +169,7 @@ __global__ void tile_write_kernel(const MT* __restrict__ mask, long long n, cons
             before += (ww < w) ? c : 0;
             total_j += c;
         }
-        if (f[j]) {
+        if ((bal[j] >> lane) & 1u) {
             const int r = run + before + __popc(bal[j] & ((1u << lane) - 1u));
             indices[off + r] = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
         }
@@ -241,7 +258,9 @@ int vpg_response_rows(const int64_t* indices, const int64_t* ids_rmpad, int64_t 
 
 size_t vpg_unpad_workspace_bytes(int64_t n) {
     const int64_t tiles = ceil_div(n > 0 ? n : 1, kTile);
-    return static_cast<size_t>(tiles) * sizeof(int) + 16 + static_cast<size_t>(tiles + 1) * sizeof(long long) + 16;
+    // tile offsets (i64) | tile counts (i32) | nonzero bitmap: one u32 per (tile, item, warp) = 1 bit per element
+    return static_cast<size_t>(tiles) * sizeof(int) + 16 + static_cast<size_t>(tiles + 1) * sizeof(long long) + 16 +
+           static_cast<size_t>(tiles) * kItems * (kTileThreads / 32) * sizeof(unsigned int);
 }
 
 int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,
@@ -258,27 +277,22 @@ int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, in
     const int tiles = static_cast<int>(n > 0 ? ceil_div(n, kTile) : 0);
     long long* tile_offsets = static_cast<long long*>(workspace);
     int* tile_counts = reinterpret_cast<int*>(tile_offsets + (ceil_div(n > 0 ? n : 1, kTile) + 1));
+    unsigned int* bits = reinterpret_cast<unsigned int*>(
+        reinterpret_cast<uint8_t*>(tile_counts) + round_up(static_cast<int64_t>(tiles) * sizeof(int), 16));
+    if (B > 0) VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
     VPG_DISPATCH_MASK(mask_dtype, MT, {
-        const MT* mk = static_cast<const MT*>(mask);
         if (tiles > 0) {
-            tile_count_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(mk, n, tile_counts);
-            count_launch();
-        }
-        if (B > 0 && S > 0) {
-            row_len_kernel<MT><<<static_cast<unsigned>(B), 256, 0, stream>>>(mk, S, seqlens);
-            count_launch();
-        } else if (B > 0) {
-            VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
-        }
-        scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, tiles, tile_offsets, seqlens, static_cast<int>(B), cu_seqlens,
-                                            totals);
-        count_launch();
-        if (tiles > 0) {
-            tile_write_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(mk, n, tile_offsets,
-                                                                      reinterpret_cast<long long*>(indices));
+            tile_count_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(static_cast<const MT*>(mask), n, S, tile_counts,
+                                                                      bits, seqlens);
             count_launch();
         }
     });
+    scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, tiles, tile_offsets, seqlens, static_cast<int>(B), cu_seqlens, totals);
+    count_launch();
+    if (tiles > 0) {
+        tile_write_kernel<<<tiles, kTileThreads, 0, stream>>>(bits, tile_offsets, reinterpret_cast<long long*>(indices));
+        count_launch();
+    }
     VPG_CUDA(cudaGetLastError());
     return VPG_OK;
 }

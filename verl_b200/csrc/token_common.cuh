@@ -71,7 +71,11 @@ __device__ __forceinline__ bool last_block_done(unsigned int* counter, unsigned 
     return is_last;
 }
 
-__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+// torch.clamp / torch.maximum / torch.minimum propagate NaN; fminf / fmaxf drop it.  A NaN log-prob must surface as a
+// NaN loss exactly like in the reference (it is how a diverged run is noticed), so the NaN-propagating forms are used.
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return (x != x) ? x : fminf(fmaxf(x, lo), hi); }
+__device__ __forceinline__ float max_nan(float a, float b) { return (a != a || b != b) ? (a + b) : fmaxf(a, b); }
+__device__ __forceinline__ float min_nan(float a, float b) { return (a != a || b != b) ? (a + b) : fminf(a, b); }
 
 static inline int flat_grid(int64_t n, int vec) {
     int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);

@@ -221,9 +221,9 @@ __global__ void ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) 
             const float l1 = -A * ratio;
             const float rc = clampf(ratio, p.ratio_lo, p.ratio_hi);
             const float l2 = -A * rc;
-            const float c1 = fmaxf(l1, l2);
+            const float c1 = max_nan(l1, l2);
             const float l3 = -A * p.clip_c;
-            const float c2 = fminf(l3, c1);
+            const float c2 = min_nan(l3, c1);
             const bool gpg = p.pg_kind == VPG_PG_GPG;
             const float pg = gpg ? (-lp.v[j] * A) : ((A < 0.f) ? c2 : c1);
             const float f_clip = (!gpg && l2 > l1) ? 1.f : 0.f;
@@ -376,11 +376,11 @@ __global__ void value_loss_kernel(const float* __restrict__ vpreds, const float*
         for (int j = 0; j < VEC; ++j) {
             const bool on = m.v[j] != 0.f;
             const float hi = vo.v[j] + cliprange, lo = vo.v[j] - cliprange;
-            const float y = fminf(vp.v[j], hi);
-            const float vpc = fmaxf(y, lo);
+            const float y = min_nan(vp.v[j], hi);
+            const float vpc = max_nan(y, lo);
             const float e1 = vp.v[j] - rt.v[j], e2 = vpc - rt.v[j];
             const float l1 = e1 * e1, l2 = e2 * e2;
-            const float lmax = fmaxf(l1, l2);
+            const float lmax = max_nan(l1, l2);
             a += (on ? lmax : 0.f) * m.v[j];
             r += lmax * m.v[j];
             cf += (on ? ((l2 > l1) ? 1.f : 0.f) : 0.f) * m.v[j];
@@ -524,7 +524,8 @@ __device__ __forceinline__ Affine affine_shfl_down(const Affine& a, int delta) {
 template <typename MT>
 __global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
                            const MT* __restrict__ mask, long long L, float gamma, float lam,
-                           float* __restrict__ adv_out, float* __restrict__ ret_out, double* __restrict__ sums) {
+                           float* __restrict__ adv_out, float* __restrict__ ret_out, double* __restrict__ sums,
+                           int vec) {
     __shared__ Affine warp_maps[32];
     __shared__ float carry[2];
     __shared__ double red[32];
@@ -540,13 +541,26 @@ __global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewa
         __syncthreads();
         const long long t0 = ck * span + static_cast<long long>(threadIdx.x) * kSeg;
         float r[kSeg], v[kSeg], m[kSeg];
+        const bool full = vec && (t0 + kSeg <= L);  // 128-bit path: every thread owns 32 contiguous, aligned bytes
+        if (full) {
 #pragma unroll
-        for (int j = 0; j < kSeg; ++j) {
-            const long long t = t0 + j;
-            const bool ok = t < L;
-            r[j] = ok ? rewards[base + t] : 0.f;
-            v[j] = ok ? values[base + t] : 0.f;
-            m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps
+            for (int q = 0; q < kSeg / 4; ++q) {
+                const float4 a = load_f4(rewards, base + t0 + 4 * q);
+                const float4 b = load_f4(values, base + t0 + 4 * q);
+                const float4 c = load_mask4<MT>(mask, base + t0 + 4 * q);
+                r[4 * q] = a.x, r[4 * q + 1] = a.y, r[4 * q + 2] = a.z, r[4 * q + 3] = a.w;
+                v[4 * q] = b.x, v[4 * q + 1] = b.y, v[4 * q + 2] = b.z, v[4 * q + 3] = b.w;
+                m[4 * q] = c.x, m[4 * q + 1] = c.y, m[4 * q + 2] = c.z, m[4 * q + 3] = c.w;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < kSeg; ++j) {
+                const long long t = t0 + j;
+                const bool ok = t < L;
+                r[j] = ok ? rewards[base + t] : 0.f;
+                v[j] = ok ? values[base + t] : 0.f;
+                m[j] = ok ? mask_to_float(mask[base + t]) : 0.f;  // out-of-range tokens are identity maps
+            }
         }
         // phase 1: compose this segment right-to-left
         Affine seg = affine_identity();
@@ -590,12 +604,23 @@ __global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewa
             lg = lg_ * m[j] + (1.f - m[j]) * lg;
             a[j] = lg;
         }
+        if (full) {
+#pragma unroll
+            for (int q = 0; q < kSeg / 4; ++q) {
+                store_f4(adv_out, base + t0 + 4 * q, make_float4(a[4 * q], a[4 * q + 1], a[4 * q + 2], a[4 * q + 3]));
+                store_f4(ret_out, base + t0 + 4 * q,
+                         make_float4(a[4 * q] + v[4 * q], a[4 * q + 1] + v[4 * q + 1], a[4 * q + 2] + v[4 * q + 2],
+                                     a[4 * q + 3] + v[4 * q + 3]));
+            }
+        }
 #pragma unroll
         for (int j = 0; j < kSeg; ++j) {
             const long long t = t0 + j;
             if (t < L) {
-                adv_out[base + t] = a[j];
-                ret_out[base + t] = a[j] + v[j];
+                if (!full) {
+                    adv_out[base + t] = a[j];
+                    ret_out[base + t] = a[j] + v[j];
+                }
                 s1 += (m[j] != 0.f ? a[j] : 0.f) * m[j];
                 s2 += (m[j] != 0.f ? a[j] * a[j] : 0.f) * m[j];
                 sc += m[j];
@@ -914,9 +939,10 @@ int vpg_gae(const float* rewards, const float* values, const void* mask, int mas
     VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
     int64_t threads = round_up(ceil_div(L, kSeg), 32);
     if (threads > 512) threads = 512;
+    const int vec = (L % kSeg == 0) && rows_vec_ok(L, mask, mask_dtype, {rewards, values, advantages, returns});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         gae_kernel<MT><<<static_cast<unsigned>(B), static_cast<unsigned>(threads), 0, stream>>>(
-            rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums);
+            rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums, vec);
     });
     VPG_LAUNCH_CHECK();
     return whiten_apply(advantages, B * L, sums, 1, advantages, status, stream);

@@ -120,12 +120,6 @@ def entropy_from_logits_with_chunking(logits: torch.Tensor, chunk_size: int = 20
 
 
 # ------------------------------------------------------------------------------------------------- masked ops
-def _is_last_axis(axis, ndim):
-    if isinstance(axis, (tuple, list)):
-        return len(axis) == 1 and _is_last_axis(axis[0], ndim)
-    return axis in (-1, ndim - 1)
-
-
 class _MaskedMean(torch.autograd.Function):
     """masked_mean(axis=None) == agg_loss('token-mean'); backward comes out of the same kernel."""
 
@@ -146,14 +140,25 @@ class _MaskedMean(torch.autograd.Function):
         return (d * g).view(ctx.shape).to(ctx.in_dtype), None
 
 
+def _axis_sums(values, mask, axis):
+    """(sum, count) over an arbitrary axis / tuple of axes: the reduced axes are moved last (a strided copy when they
+    are not already) and the row-sum kernel reduces them."""
+    nd = values.dim()
+    axes = tuple(sorted({a % nd for a in (axis if isinstance(axis, (tuple, list)) else (axis,))}))
+    keep = [d for d in range(nd) if d not in axes]
+    out_shape = [values.shape[d] for d in keep]
+    if axes != tuple(range(nd - len(axes), nd)):
+        values, mask = values.permute(*keep, *axes), mask.permute(*keep, *axes)
+    red = int(torch.Size([values.shape[i] for i in range(len(keep), nd)]).numel())
+    s, c = ops.masked_row_sums(values.reshape(-1, red).contiguous(), mask.reshape(-1, red).contiguous())
+    return s.view(out_shape), c.view(out_shape)
+
+
 def masked_sum(values, mask, axis=None):
     """verl/utils/torch_functional.py:163-168: (where(mask.bool(), values, 0) * mask).sum(axis)."""
     if axis is None:
         return ops.masked_sums(values, mask.expand_as(values))[0].to(torch.float32)
-    if _is_last_axis(axis, values.dim()):
-        s, _ = ops.masked_row_sums(values, mask.expand_as(values))
-        return s.view(values.shape[:-1])
-    raise NotImplementedError("masked_sum: only axis=None or the last axis is implemented in verl_b200")
+    return _axis_sums(values, mask.expand_as(values), axis)[0]
 
 
 def masked_mean(values, mask, axis=None):
@@ -161,10 +166,8 @@ def masked_mean(values, mask, axis=None):
     mask = mask.expand_as(values)
     if axis is None:
         return _MaskedMean.apply(values, mask)
-    if _is_last_axis(axis, values.dim()):
-        s, c = ops.masked_row_sums(values, mask)
-        return (s / (c + 1e-8)).view(values.shape[:-1])
-    raise NotImplementedError("masked_mean: only axis=None or the last axis is implemented in verl_b200")
+    s, c = _axis_sums(values, mask, axis)
+    return s / (c + 1e-8)
 
 
 def masked_var(values, mask, unbiased=True):
