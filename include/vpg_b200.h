@@ -291,6 +291,18 @@ int vpg_gae(const float* token_level_rewards, const float* values, const void* m
 int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
                       int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- dynamic micro-batches (verl/utils/seqlen_balancing.py) ------------------------------------------------------
+ * attention_mask.sum(dim=1) (:282) as exact integers: lengths[b] (i64, device) = sum_s mask[b,s]. */
+int vpg_row_lengths(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* lengths, void* stream);
+/* get_seqlen_balanced_partitions / karmarkar_karp (seqlen_balancing.py:26-190) — HOST scheduler, the one entry point
+ * whose pointers are HOST memory (no device work, no stream): partitions the n sequence lengths into k sets with
+ * the largest-differencing method and the reference's exact tie-breaking (heapq order included), so that the
+ * partition lists are bit-identical.  part_indices [n] holds the partitions back to back, each sorted ascending;
+ * part_offsets [k+1] their bounds.  Errors mirror the reference's assertions (n < k, n % k != 0 with equal_size,
+ * an empty partition) as VPG_ERR_INVALID. */
+int vpg_seqlen_balanced_partitions(const int64_t* seqlens_host, int64_t n, int64_t k, int equal_size,
+                                   int64_t* part_indices_host, int64_t* part_offsets_host);
+
 #ifdef __cplusplus
 }
 #endif

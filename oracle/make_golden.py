@@ -324,6 +324,74 @@ def gen_driver(ref):
     np.savez_compressed(os.path.join(OUT, "driver.npz"), **out)
 
 
+def gen_seqlen(ref):
+    """karmarkar_karp / get_seqlen_balanced_partitions / rearrange_micro_batches (scheduling half) / get_reverse_idx:
+    the reference's own function bodies compiled out of verl/utils/seqlen_balancing.py (the module imports
+    verl.protocol -> ray / tensordict).  rearrange_micro_batches slices a TensorDict row by row; the stand-in batch
+    below answers `batch[i:i+1]` with the row NUMBER, so the returned "micro-batches" are the scheduled row order."""
+    import copy
+    import heapq
+    import json
+    import random
+    from itertools import chain
+
+    from oracle import ref_import
+
+    class _Dist:
+        ReduceOp = None
+
+        @staticmethod
+        def is_initialized():
+            return False
+
+    fns = ref_import.load_functions(
+        "verl/utils/seqlen_balancing.py",
+        ["karmarkar_karp", "get_seqlen_balanced_partitions", "ceildiv", "roundup_divisible", "rearrange_micro_batches",
+         "get_reverse_idx"],
+        dict(heapq=heapq, copy=copy, chain=chain, torch=torch, dist=_Dist, get_device_name=lambda: "cpu"))
+
+    class RowNumbers(dict):
+        def __getitem__(self, key):
+            if isinstance(key, slice):
+                return torch.arange(key.start, key.stop)
+            return dict.__getitem__(self, key)
+
+    rnd = random.Random(20240607)
+    kk = []
+    for trial in range(60):
+        n = rnd.randint(1, 48)
+        k = rnd.randint(1, min(n, 8))
+        hi = rnd.choice([2, 9, 100, 4096])  # small ranges force ties in sums, counts and item lists
+        lens = [rnd.randint(0, hi) for _ in range(n)]
+        for eq in (False, True):
+            if eq and n % k:
+                continue
+            try:
+                merged = fns["karmarkar_karp"](lens, k, eq)
+                parts = fns["get_seqlen_balanced_partitions"](lens, k, eq)
+            except AssertionError as e:  # an empty partition (many zero lengths)
+                merged, parts = None, "AssertionError"
+            kk.append(dict(lens=lens, k=k, equal_size=eq, merge_order=merged, partitions=parts))
+    mb = []
+    g = torch.Generator().manual_seed(11)
+    for B, S, max_tok, min_mb, div, bal in [(20, 100, 300, None, None, True), (20, 100, 300, 4, None, True),
+                                            (33, 64, 128, None, 2, True), (16, 512, 2048, None, None, False),
+                                            (7, 30, 1000, None, None, True), (64, 256, 1024, 3, 4, True)]:
+        lens = torch.randint(S // 4, S + 1, (B,), generator=g)
+        left = torch.randint(0, S // 10 + 1, (B,), generator=g)
+        pos = torch.arange(S)[None]
+        attn = ((pos >= left[:, None]) & (pos < (left + lens)[:, None])).long()
+        rows, idx = fns["rearrange_micro_batches"](RowNumbers(attention_mask=attn), max_tok, num_batches_divided_by=div,
+                                                   min_num_micro_batch=min_mb, use_dynamic_bsz_balance=bal)
+        assert [r.tolist() for r in rows] == idx
+        flat = list(chain.from_iterable(idx))
+        mb.append(dict(B=B, S=S, lens=lens.tolist(), left=left.tolist(), max_token_len=max_tok, min_num_micro_batch=min_mb,
+                       num_batches_divided_by=div, use_dynamic_bsz_balance=bal, micro_bsz_idx=idx,
+                       reverse_idx=fns["get_reverse_idx"](flat)))
+    np.savez_compressed(os.path.join(OUT, "seqlen.npz"), karmarkar_karp=np.array(json.dumps(kk)),
+                        micro_batches=np.array(json.dumps(mb)))
+
+
 def gen_rmpad(ref):
     import flash_attn.bert_padding as bp  # third-party pure-torch file, v2.8.3 in this image
 
@@ -364,7 +432,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_rmpad):
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_seqlen, gen_rmpad):
         if only and fn.__name__[4:] not in only:
             continue
         fn(ref)

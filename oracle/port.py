@@ -486,3 +486,87 @@ def lce_finalize(partials, temperature):
     S, Bv = (s * f).sum(0), (b * f).sum(0)
     lse = (M + torch.log2(S)) * 0.6931471805599453
     return t.sum(0) / temperature - lse, lse - (Bv / S) / temperature
+
+
+# ------------------------------------------------------------------------------------------------ dynamic batches
+class _Entry:
+    """heap entry ordered by a static key only (states never change while they sit in the queue)"""
+
+    __slots__ = ("key", "sets")
+
+    def __init__(self, sets):
+        # sets: descending list of (sum, [(idx, len), ...]).  Pops first: the largest spread, then the largest first
+        # set by (sum, count, items) — verl/utils/seqlen_balancing.py:77-83 with Set.__lt__ :42-47.  Equal-length
+        # item lists compare in reverse when every integer is negated.
+        top_sum, top_items = sets[0]
+        self.sets = sets
+        self.key = (-(top_sum - sets[-1][0]), -top_sum, -len(top_items), [(-i, -v) for i, v in top_items])
+
+    def __lt__(self, other):
+        return self.key < other.key
+
+
+def _set_key(s):
+    return (s[0], len(s[1]), s[1])
+
+
+def karmarkar_karp(seqlen_list, k_partitions, equal_size):
+    """Largest-differencing partition, verl/utils/seqlen_balancing.py:26-127: every state holds k sets in descending
+    order; the two states with the largest spread are merged largest-with-smallest until one state is left."""
+    import heapq
+
+    order = sorted((int(v), i) for i, v in enumerate(seqlen_list))
+    if equal_size:
+        assert len(order) % k_partitions == 0, f"{len(order)} % {k_partitions} != 0"
+        groups = [order[o:o + k_partitions] for o in range(0, len(order), k_partitions)]
+    else:
+        groups = [[item] for item in order]
+    queue = []
+    for grp in groups:
+        sets = [(v, [(i, v)]) for v, i in grp] + [(0, [])] * (k_partitions - len(grp))
+        heapq.heappush(queue, _Entry(sorted(sets, key=_set_key, reverse=True)))
+    while len(queue) > 1:
+        a, b = heapq.heappop(queue), heapq.heappop(queue)
+        merged = [(sa + sb, ia + ib) for (sa, ia), (sb, ib) in zip(a.sets, reversed(b.sets))]
+        heapq.heappush(queue, _Entry(sorted(merged, key=_set_key, reverse=True)))
+    return [[i for i, _ in items] for _, items in queue[0].sets]
+
+
+def seqlen_balanced_partitions(seqlen_list, k_partitions, equal_size):
+    """verl/utils/seqlen_balancing.py:150-190"""
+    assert len(seqlen_list) >= k_partitions
+    parts = karmarkar_karp(seqlen_list, k_partitions, equal_size)
+    assert all(len(p) > 0 for p in parts)
+    assert sorted(i for p in parts for i in p) == list(range(len(seqlen_list)))
+    return [sorted(p) for p in parts]
+
+
+def micro_batch_indices(attention_mask, max_token_len, min_num_micro_batch=None, num_batches_divided_by=None,
+                        use_dynamic_bsz_balance=True):
+    """The scheduling half of rearrange_micro_batches, verl/utils/seqlen_balancing.py:250-306 (single process)."""
+    lens = attention_mask.sum(dim=1).tolist()
+    assert max_token_len >= attention_mask.shape[-1]
+    n = min(len(lens), -(sum(lens) // -max_token_len))
+    if min_num_micro_batch is not None:
+        n = max(min_num_micro_batch, n)
+    if num_batches_divided_by is not None:
+        n = -(n // -num_batches_divided_by) * num_batches_divided_by
+    assert n <= len(lens)
+    parts = seqlen_balanced_partitions(lens, n, equal_size=False)
+    if use_dynamic_bsz_balance:
+        parts.sort(key=lambda p: (sum(lens[i] ** 2 for i in p), min(p) if p else 0), reverse=True)
+    return parts
+
+
+def reverse_idx(idx_map):
+    """verl/utils/seqlen_balancing.py:322-337"""
+    out = [0] * len(idx_map)
+    for i, j in enumerate(idx_map):
+        out[j] = i
+    return out
+
+
+def restore_dynamic_batch(data, batch_idx_list):
+    """verl/utils/seqlen_balancing.py:362-375"""
+    flat = [i for p in batch_idx_list for i in p]
+    return data[torch.tensor(reverse_idx(flat), dtype=torch.long)]

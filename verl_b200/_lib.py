@@ -127,6 +127,8 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_void_p,
          c_void_p, c_size_t, c_void_p],
     ),
+    "vpg_row_lengths": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]),
+    "vpg_seqlen_balanced_partitions": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
     "vpg_masked_whiten": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],

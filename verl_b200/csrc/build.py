@@ -20,7 +20,7 @@ LIB_DIR = PKG / "lib"
 BUILD_DIR = CSRC / "build"
 LIB_PATH = LIB_DIR / "libvpg_b200.so"
 
-SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu"]
+SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "seqlen_balance.cu"]
 HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "token_common.cuh", "../../include/vpg_b200.h"]
 
 NVCC_FLAGS = [

@@ -237,6 +237,21 @@ __global__ void response_rows_kernel(const long long* __restrict__ indices, cons
     if (labels) labels[i] = ids_rmpad[(i + 1 == T) ? 0 : i + 1];
 }
 
+// Integer row sums of a [B,S] mask -> int64 (attention_mask.sum(dim=1), verl/utils/seqlen_balancing.py:282): one warp
+// per row, lanes stride the row (coalesced), exact integer arithmetic.
+template <typename MT>
+__global__ void row_lengths_kernel(const MT* __restrict__ mask, long long B, long long S, long long* __restrict__ out) {
+    const long long row = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= B) return;
+    const MT* m = mask + row * S;
+    long long c = 0;
+    for (long long t = lane; t < S; t += 32) c += static_cast<long long>(m[t]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) out[row] = c;
+}
+
 }  // namespace vpg
 
 using namespace vpg;
@@ -339,6 +354,19 @@ int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int
         case 2: scatter_units_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, n_idx, upr, (uint16_t*)out); break;
         default: scatter_units_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, n_idx, upr, (uint8_t*)out); break;
     }
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_row_lengths(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* lengths, void* stream_) {
+    VPG_CHECK_ARG(B >= 0 && S >= 0, "invalid row_lengths shape");
+    if (B == 0) return VPG_OK;
+    VPG_CHECK_ARG(mask && lengths, "null pointer argument");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        row_lengths_kernel<MT><<<static_cast<unsigned>(ceil_div(B * 32, 256)), 256, 0, stream>>>(
+            static_cast<const MT*>(mask), B, S, reinterpret_cast<long long*>(lengths));
+    });
     VPG_LAUNCH_CHECK();
     return VPG_OK;
 }

@@ -270,6 +270,44 @@ def scatter_rows(src, indices, n_out: int):
     return out
 
 
+def row_lengths(mask2d):
+    """mask [B,S] -> int64 [B] exact integer row sums (attention_mask.sum(dim=1))."""
+    _require_cuda(mask2d)
+    if mask2d.dtype.is_floating_point:
+        raise TypeError("attention masks must be integer or bool")
+    if mask2d.dtype not in (torch.int64, torch.int32, torch.bool, torch.uint8):
+        mask2d = mask2d.to(torch.int64)
+    mask2d = mask2d.contiguous()
+    m, mdt = mask_arg(mask2d)
+    B, S = mask2d.shape
+    out = torch.empty(B, dtype=torch.int64, device=mask2d.device)
+    if B:
+        with torch.cuda.device(mask2d.device):
+            check(_lib_().vpg_row_lengths(ptr(m), mdt, B, S, ptr(out), stream_ptr(mask2d.device)))
+    return out
+
+
+def seqlen_balanced_partitions(seqlen_list, k_partitions: int, equal_size: bool):
+    """HOST scheduler (vpg_seqlen_balanced_partitions): Karmarkar-Karp partitions of `seqlen_list` into k index lists,
+    bit-identical with verl/utils/seqlen_balancing.py:150-190 (each list sorted ascending)."""
+    import ctypes as C
+
+    n = len(seqlen_list)
+    k = int(k_partitions)
+    # the reference's assertions (seqlen_balancing.py:175,102)
+    assert n >= k, f"number of items:[{n}] < k_partitions:[{k}]"
+    if equal_size:
+        assert n % k == 0, f"{n} % {k} != 0"
+    lens = (C.c_int64 * max(n, 1))(*[int(x) for x in seqlen_list])
+    idx = (C.c_int64 * max(n, 1))()
+    off = (C.c_int64 * (k + 1))()
+    rc = _lib_().vpg_seqlen_balanced_partitions(lens, n, k, 1 if equal_size else 0, idx, off)
+    if rc == -1:
+        raise AssertionError(_lib_().vpg_last_error().decode())
+    check(rc)
+    return [list(idx[off[p]:off[p + 1]]) for p in range(k)]
+
+
 # --------------------------------------------------------------------------------------------------- token ops
 def masked_sums(values, mask):
     """-> float64 [2] = {sum(where(m,v,0)*m), sum(m)} over all elements."""
