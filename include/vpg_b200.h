@@ -151,6 +151,14 @@ int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K,
  * ------------------------------------------------------------------------------------------------------------ */
 int vpg_logits_stats(const void* logits, int logits_bf16, int64_t T, int64_t V, int64_t ld, const int64_t* labels,
                      float* logprobs, float* entropy, float* lse, void* stream);
+/* Vocab-sharded materialised logits — verl/utils/megatron/tensor_parallel.py:109-158 (vocab_parallel_entropy,
+ * vocab_parallel_log_probs_from_logits).  logits: this rank's [T, V_local] shard (f32 or bf16); a label hits the shard
+ * when 0 <= label - label_offset < V_local (label_offset = rank * V_local; labels may be NULL).  Writes this rank's
+ * per-token partials [4][T] f32 in the fused lm-head's wire format {max * log2(e), sum exp(x-max), sum x*exp(x-max),
+ * label logit or 0}: ONE all-gather of them followed by vpg_lce_finalize(temperature 1) replaces the reference's
+ * three dependent all-reduces (MAX, SUM, SUM). */
+int vpg_logits_partials(const void* logits, int logits_bf16, int64_t T, int64_t V_local, int64_t ld,
+                        const int64_t* labels, int64_t label_offset, float* partials, void* stream);
 /* backward of the above: dlogits = g_lp*(onehot - p) - g_ent*p*(logit - eb), with eb = lse - entropy */
 int vpg_logits_stats_bwd(const void* logits, int logits_bf16, int64_t T, int64_t V, int64_t ld,
                          const int64_t* labels, const float* lse, const float* entropy, const float* g_lp,
@@ -302,6 +310,23 @@ int vpg_row_lengths(const void* mask, int mask_dtype, int64_t B, int64_t S, int6
  * an empty partition) as VPG_ERR_INVALID. */
 int vpg_seqlen_balanced_partitions(const int64_t* seqlens_host, int64_t n, int64_t k, int equal_size,
                                    int64_t* part_indices_host, int64_t* part_offsets_host);
+
+/* ---- packed ("thd") sequences for the Megatron-side callers (verl/models/mcore/util.py:23-142) --------------------
+ * preprocess_packed_seqs / postprocess_packed_seqs as index arithmetic on the device.
+ * layout: seqlens [B] i32 -> seqlens_padded[b] = seqlens[b] rounded up to a multiple of `align` (= tp_size, or
+ *   tp_size*cp_size*2 with context parallelism, util.py:39-42), cu_seqlens_padded [B+1] i32, totals = {sum, max}.
+ * map: for every valid token n of the rmpad stream (cu_seqlens [B+1] from vpg_unpad_indices): gathered_pos[n] = its
+ *   row in the cp-gathered packed stream (rank-major: rank * (sum/cp) + local slot; chunk r and chunk 2cp-1-r of each
+ *   padded sequence live on rank r, util.py:53-72,124-140), local_dst[n] = its slot in THIS rank's packed stream or
+ *   -1 when another cp rank owns it.  cp_size 1: both = cu_seqlens_padded[b] + j.
+ * permute_rows: out[dst_idx[n], :] = src[src_idx[n], :] (rows of row_bytes bytes; NULL index = identity; dst < 0
+ *   skips the row); `out` (n_out rows) is zero-filled first when zero_fill != 0. */
+int vpg_packed_seq_layout(const int32_t* seqlens, int64_t B, int align, int32_t* seqlens_padded,
+                          int32_t* cu_seqlens_padded, int32_t* totals, void* stream);
+int vpg_packed_seq_map(const int32_t* cu_seqlens, const int32_t* cu_seqlens_padded, int64_t B, int64_t T, int cp_size,
+                       int cp_rank, int64_t* gathered_pos, int64_t* local_dst, void* stream);
+int vpg_permute_rows(const void* src, const int64_t* src_idx, const int64_t* dst_idx, int64_t n_rows, int64_t row_bytes,
+                     void* out, int64_t n_out, int zero_fill, void* stream);
 
 #ifdef __cplusplus
 }

@@ -57,6 +57,8 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "vpg_logits_partials": (
+        c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "vpg_logits_stats_bwd": (
         c_int,
         [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -129,6 +131,9 @@ SIGNATURES: dict[str, tuple] = {
     ),
     "vpg_row_lengths": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]),
     "vpg_seqlen_balanced_partitions": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
+    "vpg_packed_seq_layout": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vpg_packed_seq_map": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "vpg_permute_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int, c_void_p]),
     "vpg_masked_whiten": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],

@@ -43,7 +43,8 @@ __device__ __forceinline__ void osm_update(Osm& st, const float (&x)[N]) {
 template <bool kBf16>
 __global__ void logits_stats_kernel(const void* __restrict__ logits_, long long V, long long ld,
                                     const long long* __restrict__ labels, float* __restrict__ logprobs,
-                                    float* __restrict__ entropy, float* __restrict__ lse_out) {
+                                    float* __restrict__ entropy, float* __restrict__ lse_out,
+                                    float* __restrict__ part, long long T, long long label_offset) {
     __shared__ Osm sh[kRowThreads / 32];
     const long long row = blockIdx.x;
     Osm st{-INFINITY, 0.f, 0.f};
@@ -95,6 +96,23 @@ __global__ void logits_stats_kernel(const void* __restrict__ logits_, long long 
     if (threadIdx.x == 0) {
         Osm t = sh[0];
         for (int i = 1; i < (blockDim.x >> 5); ++i) t = osm_merge(t, sh[i]);
+        if (part) {
+            // vocab-shard partials in the wire format of the fused lm-head (vpg_lce_finalize merges them):
+            // {max in the log2 domain, sum exp(x-max), sum x*exp(x-max), label logit if the label is in this shard}
+            const long long lab = labels ? labels[row] - label_offset : -1;
+            float xl = 0.f;
+            if (lab >= 0 && lab < V) {
+                if constexpr (kBf16)
+                    xl = __bfloat162float((reinterpret_cast<const __nv_bfloat16*>(logits_) + row * ld)[lab]);
+                else
+                    xl = (reinterpret_cast<const float*>(logits_) + row * ld)[lab];
+            }
+            part[row] = t.m * 1.4426950408889634f;
+            part[T + row] = t.s;
+            part[2 * T + row] = t.b;
+            part[3 * T + row] = xl;
+            return;
+        }
         const float lse = t.m + logf(t.s);
         if (lse_out) lse_out[row] = lse;
         if (entropy) entropy[row] = lse - t.b / t.s;
@@ -155,9 +173,23 @@ int vpg_logits_stats(const void* logits, int logits_bf16, int64_t T, int64_t V, 
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const long long* lab = reinterpret_cast<const long long*>(labels);
     if (logits_bf16)
-        logits_stats_kernel<true><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V, ld, lab, logprobs, entropy, lse);
+        logits_stats_kernel<true><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V, ld, lab, logprobs, entropy, lse, nullptr, T, 0);
     else
-        logits_stats_kernel<false><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V, ld, lab, logprobs, entropy, lse);
+        logits_stats_kernel<false><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V, ld, lab, logprobs, entropy, lse, nullptr, T, 0);
+    VPG_LAUNCH_CHECK();
+    return VPG_OK;
+}
+
+int vpg_logits_partials(const void* logits, int logits_bf16, int64_t T, int64_t V_local, int64_t ld,
+                         const int64_t* labels, int64_t label_offset, float* partials, void* stream_) {
+    VPG_CHECK_ARG(logits && partials && T >= 0 && V_local > 0 && ld >= V_local, "invalid logits_partials arguments");
+    if (T == 0) return VPG_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const long long* lab = reinterpret_cast<const long long*>(labels);
+    if (logits_bf16)
+        logits_stats_kernel<true><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V_local, ld, lab, nullptr, nullptr, nullptr, partials, T, label_offset);
+    else
+        logits_stats_kernel<false><<<static_cast<unsigned>(T), kRowThreads, 0, stream>>>(logits, V_local, ld, lab, nullptr, nullptr, nullptr, partials, T, label_offset);
     VPG_LAUNCH_CHECK();
     return VPG_OK;
 }

@@ -179,6 +179,22 @@ def logits_stats(logits2d, labels=None, want_logprobs=True, want_entropy=True):
     return lp, ent, lse
 
 
+def logits_partials(logits2d, labels=None, label_offset: int = 0):
+    """this rank's vocab shard of materialised logits [T,V_local] -> partials f32 [4,1,T] (the lm-head wire format)."""
+    _require_cuda(logits2d, labels)
+    if logits2d.dtype not in (torch.float32, torch.bfloat16):
+        logits2d = logits2d.float()
+    if logits2d.stride(-1) != 1:
+        logits2d = logits2d.contiguous()
+    T, V = logits2d.shape
+    part = torch.empty((4, 1, T), dtype=_F32, device=logits2d.device)
+    ld = logits2d.stride(0) if T > 1 else V
+    with torch.cuda.device(logits2d.device):
+        check(_lib_().vpg_logits_partials(logits2d.data_ptr(), int(logits2d.dtype == torch.bfloat16), T, V, ld,
+                                          ptr(labels), int(label_offset), ptr(part), stream_ptr(logits2d.device)))
+    return part
+
+
 def logits_stats_backward(logits2d, labels, lse, entropy, g_lp, g_ent):
     _require_cuda(logits2d)
     T, V = logits2d.shape
@@ -306,6 +322,50 @@ def seqlen_balanced_partitions(seqlen_list, k_partitions: int, equal_size: bool)
         raise AssertionError(_lib_().vpg_last_error().decode())
     check(rc)
     return [list(idx[off[p]:off[p + 1]]) for p in range(k)]
+
+
+def packed_seq_layout(seqlens_i32, align: int):
+    """seqlens i32 [B] -> (seqlens_padded i32 [B], cu_seqlens_padded i32 [B+1], sum_padded int, max_padded int).
+    One device->host read (the reference reads the same two numbers with .item(), mcore/util.py:47,50)."""
+    _require_cuda(seqlens_i32)
+    B = seqlens_i32.numel()
+    dev = seqlens_i32.device
+    padded = torch.empty(B, dtype=torch.int32, device=dev)
+    cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    totals = torch.empty(2, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_packed_seq_layout(ptr(seqlens_i32.contiguous()), B, int(align), ptr(padded), ptr(cu),
+                                            ptr(totals), stream_ptr(dev)))
+    total, mx = totals.tolist()
+    return padded, cu, int(total), int(mx)
+
+
+def packed_seq_map(cu_seqlens, cu_seqlens_padded, T: int, cp_size: int, cp_rank: int):
+    """-> (gathered_pos i64 [T], local_dst i64 [T]) for the T valid tokens of the rmpad stream (see vpg_b200.h)."""
+    _require_cuda(cu_seqlens, cu_seqlens_padded)
+    dev = cu_seqlens.device
+    gpos = torch.empty(T, dtype=torch.int64, device=dev)
+    ldst = torch.empty(T, dtype=torch.int64, device=dev)
+    if T:
+        with torch.cuda.device(dev):
+            check(_lib_().vpg_packed_seq_map(ptr(cu_seqlens), ptr(cu_seqlens_padded), cu_seqlens.numel() - 1, T,
+                                             int(cp_size), int(cp_rank), ptr(gpos), ptr(ldst), stream_ptr(dev)))
+    return gpos, ldst
+
+
+def permute_rows(src, src_idx, dst_idx, n_out: int, zero_fill: bool = True):
+    """zeros [n_out, ...] with out[dst_idx[n]] = src[src_idx[n]] (None index = identity, dst < 0 skipped)."""
+    _require_cuda(src, src_idx, dst_idx)
+    src = src.contiguous()
+    row_shape = src.shape[1:]
+    row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
+    n = (src_idx if src_idx is not None else dst_idx if dst_idx is not None else src).shape[0]
+    out = torch.empty((n_out, *row_shape), dtype=src.dtype, device=src.device)
+    if n_out and row_bytes:
+        with torch.cuda.device(src.device):
+            check(_lib_().vpg_permute_rows(ptr(src), ptr(src_idx), ptr(dst_idx), n, row_bytes, ptr(out), n_out,
+                                           int(zero_fill), stream_ptr(src.device)))
+    return out
 
 
 # --------------------------------------------------------------------------------------------------- token ops
