@@ -392,6 +392,101 @@ def gen_seqlen(ref):
                         micro_batches=np.array(json.dumps(mb)))
 
 
+class _TorchProxy:
+    """the real torch module with a few attributes replaced (used to stub collectives / torch.compile when a reference
+    function body is compiled stand-alone)"""
+
+    def __init__(self, **over):
+        self._over = over
+
+    def __getattr__(self, name):
+        return self._over[name] if name in self._over else getattr(torch, name)
+
+
+def gen_megatron(ref):
+    """Megatron-side equivalents.
+    * _VocabParallelEntropy (verl/utils/megatron/tensor_parallel.py:109-139): the reference class body, compiled
+      stand-alone with a single-rank `dist` (all_reduce = no-op) and torch.compile -> identity, run on the FULL-vocab
+      logits: forward + backward.  The vocab-sharded result must equal it (the merge is exact algebra).
+    * vocab_parallel_log_probs_from_logits calls megatron.core.tensor_parallel.vocab_parallel_cross_entropy
+      (third-party megatron-core, not in this image; reference pins megatron-core 0.12/0.13 in its Dockerfiles):
+      anchored on the reference's own full-vocab logprobs_from_logits_v2 (same quantity by definition).
+    * preprocess_packed_seqs / postprocess_packed_seqs (verl/models/mcore/util.py:23-142): the reference function
+      bodies with a stub `mpu` (tp/cp sizes and rank) and a fake all_gather fed with the other ranks' outputs."""
+    import types
+
+    from oracle import ref_import
+
+    out = {}
+    g = torch.Generator().manual_seed(77)
+    one_rank = types.SimpleNamespace(all_reduce=lambda *a, **k: None, ReduceOp=types.SimpleNamespace(MAX="max"))
+    mpu1 = types.SimpleNamespace(get_tensor_model_parallel_group=lambda: None)
+    cls = ref_import.load_functions("verl/utils/megatron/tensor_parallel.py", ["_VocabParallelEntropy"],
+                                    dict(torch=_TorchProxy(compile=lambda **kw: (lambda f: f)), dist=one_rank, mpu=mpu1))
+    T, V = 23, 1000
+    logits = (torch.randn(T, V, generator=g) * 3)
+    labels = torch.randint(0, V, (T,), generator=g)
+    g_ent = torch.randn(T, generator=g)
+    g_lp = torch.randn(T, generator=g)
+    x = logits.clone().requires_grad_(True)
+    ent = cls["_VocabParallelEntropy"].apply(x.clone())  # the class works in place on its input
+    ent.backward(g_ent)
+    out.update(vp_logits=_np(logits), vp_labels=_np(labels), vp_g_ent=_np(g_ent), vp_g_lp=_np(g_lp),
+               vp_entropy=_np(ent), vp_entropy_dlogits=_np(x.grad))
+    x2 = logits.clone().requires_grad_(True)
+    lp = ref.torch_functional.logprobs_from_logits_v2(x2, labels)
+    lp.backward(g_lp)
+    out.update(vp_logprobs=_np(lp), vp_logprobs_dlogits=_np(x2.grad))
+
+    # ---- packed sequences
+    B, S, D = 6, 40, 4
+    lens = torch.tensor([40, 8, 17, 9, 33, 26])
+    left = torch.tensor([0, 5, 3, 0, 7, 2])
+    pos = torch.arange(S)[None]
+    attn = (pos >= left[:, None]) & (pos < (left + lens)[:, None])
+    attn[2, 10] = False  # a hole inside a sequence: packing keeps the valid tokens in order
+    ids = torch.randint(1, 500, (B, S), generator=g)
+    table = torch.randn(500, D, generator=g)
+    out.update(pk_ids=_np(ids), pk_attn=_np(attn.long()), pk_table=_np(table))
+
+    class PackedSeqParams:
+        def __init__(self, **kw):
+            self.__dict__.update(kw)
+
+    for tp, cp in [(1, 1), (2, 1), (4, 1), (1, 2), (2, 2), (1, 4)]:
+        per_rank_out = []
+        for rank in range(cp):
+            mpu = types.SimpleNamespace(get_tensor_model_parallel_world_size=lambda tp=tp: tp,
+                                        get_context_parallel_world_size=lambda cp=cp: cp,
+                                        get_context_parallel_rank=lambda rank=rank: rank,
+                                        get_context_parallel_group=lambda: None)
+            fns = ref_import.load_functions("verl/models/mcore/util.py", ["preprocess_packed_seqs"],
+                                            dict(torch=torch, mpu=mpu, PackedSeqParams=PackedSeqParams))
+            packed, params = fns["preprocess_packed_seqs"](ids, attn, pre_process=True)
+            out[f"pk|tp{tp}cp{cp}|r{rank}|packed"] = _np(packed)
+            per_rank_out.append(table[packed[0]].unsqueeze(0))  # stand-in for the model: a row lookup
+        out[f"pk|tp{tp}cp{cp}|cu_padded"] = _np(params.cu_seqlens_q_padded)
+        out[f"pk|tp{tp}cp{cp}|max_seqlen"] = np.array(params.max_seqlen_q)
+        for rank in range(cp):
+            def fake_all_gather(lst, t, group=None):
+                for j in range(cp):
+                    lst[j] = per_rank_out[j].clone()
+
+            mpu = types.SimpleNamespace(get_context_parallel_world_size=lambda cp=cp: cp,
+                                        get_context_parallel_rank=lambda rank=rank: rank,
+                                        get_context_parallel_group=lambda: None)
+            tproxy = _TorchProxy(distributed=types.SimpleNamespace(all_gather=fake_all_gather))
+            fns = ref_import.load_functions("verl/models/mcore/util.py", ["postprocess_packed_seqs"],
+                                            dict(torch=tproxy, mpu=mpu, PackedSeqParams=PackedSeqParams))
+            o = per_rank_out[rank].clone().requires_grad_(True)
+            padded = fns["postprocess_packed_seqs"](o, params, attn, B, S, post_process=True)
+            w = torch.arange(B * S * D, dtype=torch.float32).view(B, S, D) / 100
+            (padded * w).sum().backward()
+            out[f"pk|tp{tp}cp{cp}|r{rank}|padded"] = _np(padded)
+            out[f"pk|tp{tp}cp{cp}|r{rank}|d_output"] = _np(o.grad)
+    np.savez_compressed(os.path.join(OUT, "megatron.npz"), **out)
+
+
 def gen_rmpad(ref):
     import flash_attn.bert_padding as bp  # third-party pure-torch file, v2.8.3 in this image
 
@@ -432,7 +527,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_seqlen, gen_rmpad):
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_seqlen, gen_megatron, gen_rmpad):
         if only and fn.__name__[4:] not in only:
             continue
         fn(ref)

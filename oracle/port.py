@@ -570,3 +570,91 @@ def restore_dynamic_batch(data, batch_idx_list):
     """verl/utils/seqlen_balancing.py:362-375"""
     flat = [i for p in batch_idx_list for i in p]
     return data[torch.tensor(reverse_idx(flat), dtype=torch.long)]
+
+
+# ------------------------------------------------------------------------------------------------ Megatron-side
+def vocab_parallel_entropy(shards):
+    """verl/utils/megatron/tensor_parallel.py:109-130 with the tensor-parallel all-reduces written out over the list of
+    per-rank logit shards [T, V/tp]: MAX of the row maxima, SUM of sum-exp, SUM of sum softmax*logit."""
+    shards = [s.float() for s in shards]
+    row_max = torch.stack([s.max(dim=-1).values for s in shards]).max(dim=0).values[:, None]
+    exps = [(s - row_max).exp() for s in shards]
+    sum_exp = sum(e.sum(dim=-1, keepdim=True) for e in exps)
+    sum_p_x = sum(((e / sum_exp) * s).sum(dim=-1, keepdim=True) for e, s in zip(exps, shards))
+    return (row_max + sum_exp.log() - sum_p_x).squeeze(-1)
+
+
+def vocab_parallel_log_probs(shards, labels):
+    """-vocab_parallel_cross_entropy of megatron-core (third-party; the reference installs core_v0.12.1 /
+    core_r0.13.0, docker/*/Dockerfile.app.*mcore*) as called at tensor_parallel.py:154-158.  Published algorithm:
+    all-reduce MAX of the row maxima, subtract; each rank gathers the label logit if rank*V_local <= label <
+    (rank+1)*V_local (else 0) and the gathered values are SUM-reduced; sum-exp SUM-reduced;
+    loss = log(sum_exp) - predicted."""
+    shards = [s.float() for s in shards]
+    v_local = shards[0].shape[-1]
+    row_max = torch.stack([s.max(dim=-1).values for s in shards]).max(dim=0).values
+    predicted = torch.zeros_like(row_max)
+    sum_exp = torch.zeros_like(row_max)
+    for rank, s in enumerate(shards):
+        z = s - row_max[:, None]
+        local = labels - rank * v_local
+        hit = (local >= 0) & (local < v_local)
+        picked = z.gather(-1, local.clamp(0, v_local - 1)[:, None]).squeeze(-1)
+        predicted = predicted + torch.where(hit, picked, torch.zeros_like(picked))
+        sum_exp = sum_exp + z.exp().sum(dim=-1)
+    return predicted - sum_exp.log()
+
+
+def packed_layout(attention_mask, tp_size, cp_size):
+    """verl/models/mcore/util.py:36-47: per-sequence lengths padded to a multiple of tp (tp*cp*2 with cp) + cumsum"""
+    seqlens = attention_mask.bool().sum(dim=-1).to(torch.int32)
+    align = tp_size * cp_size * 2 if cp_size > 1 else tp_size
+    padded = seqlens + (align - seqlens % align) % align
+    cu_padded = torch.zeros(len(seqlens) + 1, dtype=torch.int32)
+    cu_padded[1:] = torch.cumsum(padded, dim=0)
+    return seqlens, padded, cu_padded
+
+
+def preprocess_packed_seqs(input_ids, attention_mask, tp_size=1, cp_size=1, cp_rank=0):
+    """verl/models/mcore/util.py:23-87: this cp rank's packed stream [1, sum_padded/cp, ...].  Token j of a padded
+    sequence of Lp tokens belongs to chunk j // (Lp / (2 cp)); rank r holds chunks r and 2cp-1-r back to back."""
+    seqlens, padded, cu_padded = packed_layout(attention_mask, tp_size, cp_size)
+    out = torch.zeros((int(padded.sum()) // cp_size, *input_ids.shape[2:]), dtype=input_ids.dtype)
+    for i in range(input_ids.shape[0]):
+        d = input_ids[i][attention_mask[i].bool()]
+        if cp_size <= 1:
+            out[cu_padded[i]:cu_padded[i] + len(d)] = d
+            continue
+        lp = int(padded[i])
+        half = lp // (2 * cp_size)
+        base = int(cu_padded[i]) // cp_size
+        for j in range(len(d)):
+            chunk = j // half
+            owner = chunk if chunk < cp_size else 2 * cp_size - 1 - chunk
+            if owner == cp_rank:
+                out[base + (0 if chunk < cp_size else half) + j % half] = d[j]
+    return out.unsqueeze(0), cu_padded, int(padded.max())
+
+
+def postprocess_packed_seqs(outputs_per_rank, attention_mask, tp_size=1, cp_size=1):
+    """verl/models/mcore/util.py:90-142 with the cp all-gather written out: outputs_per_rank[r] is rank r's
+    [1, sum_padded/cp, ...] stream; -> [B, S, ...] with zeros at masked positions."""
+    seqlens, padded, cu_padded = packed_layout(attention_mask, tp_size, cp_size)
+    B, S = attention_mask.shape
+    o0 = outputs_per_rank[0]
+    out = torch.zeros((B, S, *o0.shape[2:]), dtype=o0.dtype)
+    for i in range(B):
+        lp = int(padded[i])
+        half = lp // (2 * cp_size) if cp_size > 1 else 0
+        base = int(cu_padded[i]) // cp_size
+        seq = []
+        for j in range(int(seqlens[i])):
+            if cp_size <= 1:
+                seq.append(o0[0][base + j])
+                continue
+            chunk = j // half
+            owner = chunk if chunk < cp_size else 2 * cp_size - 1 - chunk
+            seq.append(outputs_per_rank[owner][0][base + (0 if chunk < cp_size else half) + j % half])
+        if seq:
+            out[i, attention_mask[i].bool()] = torch.stack(seq)
+    return out

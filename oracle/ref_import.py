@@ -77,21 +77,23 @@ def load():
 
 
 def load_functions(rel_path: str, names, namespace: dict) -> dict:
-    """Compile ONLY the named top-level function definitions of a reference file whose module cannot be imported here
+    """Compile ONLY the named top-level function / class definitions of a reference file whose module cannot be imported here
     (ray / hydra / tensordict at import time) and execute them, unmodified, in ``namespace`` (which supplies the
     module-level names the bodies use).  -> {name: function}"""
     import ast
 
     path = os.path.join(REFERENCE_ROOT, rel_path)
     tree = ast.parse(open(path).read(), filename=path)
-    picked = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in set(names)]
+    picked = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in set(names)]
     missing = set(names) - {n.name for n in picked}
     if missing:
         raise RuntimeError(f"{rel_path}: functions not found: {sorted(missing)}")
-    for fn in picked:  # annotations may name types that are not importable here; they are never evaluated by the body
-        fn.returns = None
-        for a in fn.args.args + fn.args.kwonlyargs:
-            a.annotation = None
+    for top in picked:  # annotations may name types that are not importable here; the bodies never evaluate them
+        for fn in ast.walk(top):
+            if isinstance(fn, ast.FunctionDef):
+                fn.returns = None
+                for a in fn.args.args + fn.args.kwonlyargs:
+                    a.annotation = None
     mod = ast.Module(body=picked, type_ignores=[])
     ns = dict(namespace)
     exec(compile(mod, path, "exec"), ns)

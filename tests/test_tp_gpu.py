@@ -24,3 +24,14 @@ def test_nvlink_fused_exchange_matches_nccl(shape):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MISMATCH" not in r.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_megatron_side_equivalents_on_real_ranks():
+    """vocab_parallel_entropy / log-probs over NCCL and the context-parallel packed-seq round trip"""
+    n = 2 if torch.cuda.device_count() < 4 else 4
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "scripts", "tp_megatron_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "MISMATCH" not in r.stdout
