@@ -328,6 +328,31 @@ int vpg_packed_seq_map(const int32_t* cu_seqlens, const int32_t* cu_seqlens_padd
 int vpg_permute_rows(const void* src, const int64_t* src_idx, const int64_t* dst_idx, int64_t n_rows, int64_t row_bytes,
                      void* out, int64_t n_out, int zero_fill, void* stream);
 
+/* ---- covariance-gated policy losses (verl/trainer/ppo/core_algos.py:818-972) --------------------------------------
+ * Both produce the loss MATRIX pg_losses [n] and its elementwise derivative w.r.t. log_prob d_pg_losses [n]
+ * (n = B*L flat); aggregate with vpg_agg_loss.  workspace: vpg_cov_workspace_bytes() bytes, 8-byte aligned; the first
+ * double of it is sum(mask) after vpg_clip_cov_flags (the host needs it for clip_num, core_algos.py:879).
+ * clip_cov (:818-905), two calls around the host's random draw (torch.randperm on the host generator, :884-886):
+ *   vpg_clip_cov_flags: eligible[i] = 1 where cov_lb < cov < cov_ub, mask > 0 and the PPO clip did not cut the token,
+ *     cov = (A - masked_mean(A)) * (lp - masked_mean(lp));
+ *   vpg_clip_cov_loss (same workspace): zeroed[i] != 0 marks the drawn tokens (corr = 0);
+ *     pg_losses = max(-A*ratio, -A*clamp(ratio, 1-low, 1+high)) * corr;  out3 = {ppo_kl, pg_clipfrac, sum(mask)}.
+ * kl_cov (:908-972), one call: the k = max(1, int(N_valid * kl_cov_ratio)) valid tokens with the largest
+ *   cov = (A - mean_valid A) * (lp - mean_valid lp) get pg_losses = -A*ratio + ppo_kl_coef*|lp - old|, the others
+ *   -A*ratio (ties at the threshold go to the lower flat index; the reference's CPU torch.topk leaves them
+ *   unspecified).  out3 = {ppo_kl_abs, number of tokens selected, sum(mask)}. */
+size_t vpg_cov_workspace_bytes(void);
+int vpg_clip_cov_flags(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
+                       int mask_dtype, int64_t n, float cliprange_low, float cliprange_high, float cov_lb, float cov_ub,
+                       uint8_t* eligible, void* workspace, size_t workspace_bytes, void* stream);
+int vpg_clip_cov_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
+                      int mask_dtype, int64_t n, float cliprange_low, float cliprange_high, const uint8_t* zeroed,
+                      float* pg_losses, float* d_pg_losses, float* out3, void* workspace, size_t workspace_bytes,
+                      void* stream);
+int vpg_kl_cov_loss(const float* old_log_prob, const float* log_prob, const float* advantages, const void* mask,
+                    int mask_dtype, int64_t n, double kl_cov_ratio, float ppo_kl_coef, float* pg_losses,
+                    float* d_pg_losses, float* out3, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -211,6 +211,48 @@ def gen_loss(ref):
     np.savez_compressed(os.path.join(OUT, "loss.npz"), **out)
 
 
+def gen_cov(ref):
+    """compute_policy_loss_clip_cov / compute_policy_loss_kl_cov (core_algos.py:818-972): the unmodified reference
+    functions; clip_cov's random subset is made reproducible by seeding the host generator right before the call."""
+    import types
+
+    g = torch.Generator().manual_seed(41)
+    ca = ref.core_algos
+    out = {}
+    B, L = 12, 40
+    mask, _ = _response_mask(B, L, g)
+    old = -torch.rand(B, L, generator=g) * 3
+    lp = old + 0.3 * torch.randn(B, L, generator=g)
+    adv = torch.randn(B, L, generator=g) * 2.5  # wide enough that some cov values land in (clip_cov_lb, clip_cov_ub)
+    out.update(mask=_np(mask), old=_np(old), lp=_np(lp), adv=_np(adv))
+    modes = ["token-mean", "seq-mean-token-sum", "seq-mean-token-mean", "seq-mean-token-sum-norm"]
+    cases = {
+        "default": dict(clip_ratio=0.2, clip_ratio_low=None, clip_ratio_high=None, clip_cov_ratio=None, clip_cov_lb=None,
+                        clip_cov_ub=None, kl_cov_ratio=None, ppo_kl_coef=None),
+        "wide": dict(clip_ratio=0.2, clip_ratio_low=0.2, clip_ratio_high=0.28, clip_cov_ratio=0.05, clip_cov_lb=0.5,
+                     clip_cov_ub=6.0, kl_cov_ratio=0.04, ppo_kl_coef=0.7),
+    }
+    for cname, c in cases.items():
+        cfg = types.SimpleNamespace(clip_ratio=c["clip_ratio"], clip_ratio_low=c["clip_ratio_low"],
+                                    clip_ratio_high=c["clip_ratio_high"],
+                                    policy_loss=types.SimpleNamespace(**{k: c[k] for k in (
+                                        "clip_cov_ratio", "clip_cov_lb", "clip_cov_ub", "kl_cov_ratio", "ppo_kl_coef")}))
+        for mode in modes:
+            lpg = lp.clone().requires_grad_(True)
+            torch.manual_seed(1234)
+            loss, clipfrac, ppo_kl, _ = ca.compute_policy_loss_clip_cov(old, lpg, adv, mask, mode, cfg)
+            loss.backward()
+            out[f"clip_cov|{cname}|{mode}|scalars"] = np.array([_np(loss), _np(clipfrac), _np(ppo_kl)], dtype=np.float32)
+            out[f"clip_cov|{cname}|{mode}|d_lp"] = _np(lpg.grad)
+            lpg = lp.clone().requires_grad_(True)
+            loss, _, ppo_kl_abs, _ = ca.compute_policy_loss_kl_cov(old, lpg, adv, mask, mode, cfg)
+            loss.backward()
+            out[f"kl_cov|{cname}|{mode}|scalars"] = np.array([_np(loss), _np(ppo_kl_abs)], dtype=np.float32)
+            out[f"kl_cov|{cname}|{mode}|d_lp"] = _np(lpg.grad)
+        out[cname + "|cfg"] = np.array([np.nan if v is None else v for v in c.values()], dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "cov.npz"), **out)
+
+
 def gen_estimators(ref):
     """The other registered advantage estimators + value loss + GPG loss."""
     g = torch.Generator().manual_seed(29)
@@ -527,7 +569,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_estimators, gen_driver, gen_seqlen, gen_megatron, gen_rmpad):
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_cov, gen_estimators, gen_driver, gen_seqlen, gen_megatron, gen_rmpad):
         if only and fn.__name__[4:] not in only:
             continue
         fn(ref)

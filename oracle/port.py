@@ -333,6 +333,55 @@ def policy_loss(old_log_prob, log_prob, advantages, response_mask, cliprange=Non
     return agg_loss(per_token, response_mask, loss_agg_mode), pg_clipfrac, ppo_kl, pg_clipfrac_lower
 
 
+def policy_loss_clip_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean", clip_ratio=0.2,
+                         clip_ratio_low=None, clip_ratio_high=None, clip_cov_ratio=0.0002, clip_cov_lb=1.0,
+                         clip_cov_ub=5.0):
+    """verl/trainer/ppo/core_algos.py:818-905 -> (pg_loss, pg_clipfrac, ppo_kl).  The random subset is drawn with
+    torch.randperm on the global host generator at the same point as the reference, so seeding reproduces it."""
+    lo = clip_ratio if clip_ratio_low is None else clip_ratio_low
+    hi = clip_ratio if clip_ratio_high is None else clip_ratio_high
+    delta = log_prob - old_log_prob
+    ratio = torch.exp(delta)
+    ppo_kl = masked_mean(-delta, response_mask)
+    unclipped = -advantages * ratio
+    clipped = -advantages * torch.clamp(ratio, 1 - lo, 1 + hi)
+    valid = response_mask > 0
+    cut_by_ppo = (clipped > unclipped) & valid
+    cov = (advantages - masked_mean(advantages, response_mask)) * (
+        log_prob.detach() - masked_mean(log_prob.detach(), response_mask))
+    cov = torch.where((response_mask == 0) | cut_by_ppo, torch.full_like(cov, -torch.inf), cov)
+    n_drop = max(int(clip_cov_ratio * response_mask.sum().item()), 1)
+    eligible = torch.nonzero(((cov < clip_cov_ub) & (cov > clip_cov_lb) & valid).reshape(-1)).squeeze(-1)
+    keep = torch.ones(cov.numel())
+    if eligible.numel() > 0:
+        order = torch.randperm(eligible.numel())
+        keep[eligible[order[: min(n_drop, eligible.numel())]]] = 0
+    keep = keep.view_as(cov)
+    pg_clipfrac = masked_mean((keep == 0).float(), response_mask)
+    per_token = torch.maximum(unclipped, clipped) * keep
+    return agg_loss(per_token, response_mask, loss_agg_mode), pg_clipfrac, ppo_kl
+
+
+def policy_loss_kl_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean",
+                       kl_cov_ratio=0.0002, ppo_kl_coef=1.0):
+    """verl/trainer/ppo/core_algos.py:908-972 -> (pg_loss, ppo_kl_abs)"""
+    delta = log_prob - old_log_prob
+    ppo_kl_abs = masked_mean(delta.abs(), response_mask)
+    plain = -advantages * torch.exp(delta)
+    with_kl = plain + ppo_kl_coef * delta.abs()
+    valid = (response_mask > 0).reshape(-1)
+    pos = torch.nonzero(valid).squeeze(-1)
+    a = advantages.detach().reshape(-1)[pos]
+    l = log_prob.detach().reshape(-1)[pos]
+    pick = torch.zeros(valid.numel(), dtype=torch.bool)
+    if pos.numel() > 0:
+        cov = (a - a.mean()) * (l - l.mean())
+        k = max(1, int(pos.numel() * kl_cov_ratio))
+        pick[pos[torch.topk(cov, k, largest=True).indices]] = True
+    per_token = torch.where(pick.view_as(plain), with_kl, plain)
+    return agg_loss(per_token, response_mask, loss_agg_mode), ppo_kl_abs
+
+
 def policy_loss_gpg(log_prob, advantages, response_mask, loss_agg_mode="token-mean"):
     """verl/trainer/ppo/core_algos.py:797-815"""
     return agg_loss(-log_prob * advantages, response_mask, loss_agg_mode)

@@ -134,6 +134,22 @@ SIGNATURES: dict[str, tuple] = {
     "vpg_packed_seq_layout": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vpg_packed_seq_map": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "vpg_permute_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int, c_void_p]),
+    "vpg_cov_workspace_bytes": (c_size_t, []),
+    "vpg_clip_cov_flags": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_float, c_float, c_float, c_float, c_void_p,
+         c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_clip_cov_loss": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_float, c_float, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "vpg_kl_cov_loss": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, C.c_double, c_float, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_size_t, c_void_p],
+    ),
     "vpg_masked_whiten": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],

@@ -8,7 +8,7 @@
   verl.utils.torch_functional.{logprobs_from_logits, entropy_from_logits, masked_mean, ...}
   verl.trainer.ppo.core_algos.{compute_policy_loss, agg_loss, kl_penalty, compute_value_loss, compute_policy_loss_gpg,
       compute_grpo_outcome_advantage, compute_gae_advantage_return and the seven other estimators}
-      (+ every ADV_ESTIMATOR_REGISTRY entry and the "gpg" POLICY_LOSS_REGISTRY entry)
+      (+ every ADV_ESTIMATOR_REGISTRY entry and the "gpg" / "clip_cov" / "kl_cov" POLICY_LOSS_REGISTRY entries)
   flash_attn.bert_padding.{unpad_input, pad_input, index_first_axis}   (only with patch_flash_attn=True)
 
 If the real ``verl`` package is importable its modules are patched attribute by attribute (everything outside the
@@ -39,7 +39,8 @@ _CA_NAMES = ["compute_policy_loss", "agg_loss", "kl_penalty", "compute_grpo_outc
              "compute_reinforce_plus_plus_baseline_outcome_advantage", "compute_rloo_outcome_advantage",
              "compute_opo_outcome_advantage", "compute_reinforce_plus_plus_outcome_advantage",
              "compute_remax_outcome_advantage", "compute_gpg_outcome_advantage", "compute_policy_loss_gpg",
-             "compute_value_loss"]
+             "compute_value_loss", "compute_policy_loss_clip_cov", "compute_policy_loss_kl_cov",
+             "compute_entropy_loss"]
 
 
 def _try_import(name):
@@ -78,7 +79,7 @@ def install(patch_flash_attn: bool = False) -> dict:
             if name.endswith("core_algos"):
                 for key, fn in _ca.ADV_ESTIMATOR_REGISTRY.items():
                     real.ADV_ESTIMATOR_REGISTRY[key] = fn
-                for key, fn in _ca.POLICY_LOSS_REGISTRY.items():  # "gpg"; clip_cov / kl_cov stay the reference's
+                for key, fn in _ca.POLICY_LOSS_REGISTRY.items():  # "gpg", "clip_cov", "kl_cov"
                     real.POLICY_LOSS_REGISTRY[key] = fn
             report[name] = "patched"
         else:

@@ -20,7 +20,7 @@ LIB_DIR = PKG / "lib"
 BUILD_DIR = CSRC / "build"
 LIB_PATH = LIB_DIR / "libvpg_b200.so"
 
-SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "seqlen_balance.cu", "packed_seqs.cu"]
+SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "seqlen_balance.cu", "packed_seqs.cu", "cov_loss.cu"]
 HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "token_common.cuh", "../../include/vpg_b200.h"]
 
 NVCC_FLAGS = [
@@ -58,10 +58,10 @@ def _fingerprint(flags_per_src: dict[str, list[str]]) -> str:
 
 def _flags_for(src: str) -> list[str]:
     flags = list(NVCC_FLAGS)
-    if src in ("token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "packed_seqs.cu", "seqlen_balance.cu"):
+    if src in ("token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "packed_seqs.cu", "seqlen_balance.cu", "cov_loss.cu"):
         # bit-faithful fp32 arithmetic for the parity-critical memory-bound ops
         flags.remove("--use_fast_math")
-        flags += ["--fmad=false"] if src in ("token_ops.cu", "adv_ops.cu") else []
+        flags += ["--fmad=false"] if src in ("token_ops.cu", "adv_ops.cu", "cov_loss.cu") else []
     return flags
 
 

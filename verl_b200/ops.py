@@ -447,6 +447,61 @@ def ppo_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low
     return metrics, d_lp, d_ent
 
 
+def _cov_ws(dev):
+    return _ws(int(_lib_().vpg_cov_workspace_bytes()), dev)
+
+
+def clip_cov_flags(old_log_prob, log_prob, advantages, response_mask, cliprange_low, cliprange_high, cov_lb, cov_ub):
+    """-> (eligible u8 [n], workspace) — the workspace carries the masked sums into clip_cov_loss; its first double is
+    sum(mask)."""
+    old, lp, adv = _f32c(old_log_prob), _f32c(log_prob), _f32c(advantages)
+    _require_cuda(old, lp, adv, response_mask)
+    m, mdt = mask_arg(response_mask.contiguous())
+    n = lp.numel()
+    dev = lp.device
+    ws = _cov_ws(dev)
+    flags = torch.empty(n, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_clip_cov_flags(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(cliprange_low),
+                                         float(cliprange_high), float(cov_lb), float(cov_ub), ptr(flags), ptr(ws),
+                                         ws.numel() * 8, stream_ptr(dev)))
+    return flags, ws
+
+
+def clip_cov_loss(old_log_prob, log_prob, advantages, response_mask, cliprange_low, cliprange_high, zeroed, ws):
+    """-> (pg_losses f32 [n], d pg_losses / d log_prob f32 [n], out3 = {ppo_kl, pg_clipfrac, sum mask})"""
+    old, lp, adv = _f32c(old_log_prob), _f32c(log_prob), _f32c(advantages)
+    m, mdt = mask_arg(response_mask.contiguous())
+    n = lp.numel()
+    dev = lp.device
+    pg = torch.empty(n, dtype=_F32, device=dev)
+    dpg = torch.empty(n, dtype=_F32, device=dev)
+    out3 = torch.empty(3, dtype=_F32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_clip_cov_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(cliprange_low),
+                                        float(cliprange_high), ptr(zeroed), ptr(pg), ptr(dpg), ptr(out3), ptr(ws),
+                                        ws.numel() * 8, stream_ptr(dev)))
+    return pg, dpg, out3
+
+
+def kl_cov_loss(old_log_prob, log_prob, advantages, response_mask, kl_cov_ratio: float, ppo_kl_coef: float):
+    """-> (pg_losses f32 [n], d pg_losses / d log_prob f32 [n], out3 = {ppo_kl_abs, #selected, sum mask})"""
+    old, lp, adv = _f32c(old_log_prob), _f32c(log_prob), _f32c(advantages)
+    _require_cuda(old, lp, adv, response_mask)
+    m, mdt = mask_arg(response_mask.contiguous())
+    n = lp.numel()
+    dev = lp.device
+    ws = _cov_ws(dev)
+    pg = torch.empty(n, dtype=_F32, device=dev)
+    dpg = torch.empty(n, dtype=_F32, device=dev)
+    out3 = torch.empty(3, dtype=_F32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib_().vpg_kl_cov_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(kl_cov_ratio),
+                                      float(ppo_kl_coef), ptr(pg), ptr(dpg), ptr(out3), ptr(ws), ws.numel() * 8,
+                                      stream_ptr(dev)))
+    return pg, dpg, out3
+
+
 def agg_loss_fwd(loss_mat, loss_mask, loss_agg_mode: str, want_grad: bool):
     if loss_agg_mode not in AGG_MODES:
         raise ValueError(f"Invalid loss_agg_mode: {loss_agg_mode}")

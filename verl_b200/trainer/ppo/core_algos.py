@@ -468,6 +468,92 @@ def compute_policy_loss_gpg(old_log_prob, log_prob, advantages, response_mask, l
     return loss, zero, zero.clone(), zero.clone()
 
 
+class _LossMatrix(torch.autograd.Function):
+    """A per-token loss matrix whose elementwise derivative w.r.t. log_prob came out of the same kernel."""
+
+    @staticmethod
+    def forward(ctx, log_prob, pg_losses, d_pg_losses):
+        ctx.save_for_backward(d_pg_losses)
+        ctx.meta = (log_prob.shape, log_prob.dtype)
+        return pg_losses.view(log_prob.shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        return (g.reshape(-1) * d).view(ctx.meta[0]).to(ctx.meta[1]), None, None
+
+
+def _policy_loss_cfg(config, name, default):
+    """config.policy_loss.<name> (None -> default); attribute- or dict-style configs (core_algos.py:861-866,940-941)."""
+    pl = config.get("policy_loss") if isinstance(config, dict) else getattr(config, "policy_loss", None)
+    val = pl.get(name) if isinstance(pl, dict) else getattr(pl, name, None)
+    return default if val is None else val
+
+
+@register_policy_loss("clip_cov")
+def compute_policy_loss_clip_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean",
+                                 config=None):
+    """Clip-Cov policy loss (core_algos.py:818-905).  A random subset (size max(int(clip_cov_ratio * sum mask), 1)) of the
+    tokens with clip_cov_lb < cov < clip_cov_ub that PPO's clip left alone is detached from the loss (corr = 0).
+
+    The eligible set and the loss run on the device; the draw is `torch.randperm(n_eligible)` on the host generator,
+    exactly the reference's call, so a seeded run selects the same tokens.  Host syncs: one (n_eligible and sum(mask),
+    the reference has the same two).  Returns (pg_loss, pg_clipfrac, ppo_kl, 0)."""
+    clip_cov_ratio = _policy_loss_cfg(config, "clip_cov_ratio", 0.0002)
+    cliprange = _cfg_get(config, "clip_ratio", None)
+    low, high = _cfg_get(config, "clip_ratio_low", None), _cfg_get(config, "clip_ratio_high", None)
+    cliprange_low = low if low is not None else cliprange
+    cliprange_high = high if high is not None else cliprange
+    clip_cov_ub = _policy_loss_cfg(config, "clip_cov_ub", 5.0)
+    clip_cov_lb = _policy_loss_cfg(config, "clip_cov_lb", 1.0)
+    assert clip_cov_ratio > 0, "clip_ratio should be larger than 0."
+
+    lp_d = log_prob.detach()
+    flags, ws = ops.clip_cov_flags(old_log_prob, lp_d, advantages, response_mask, cliprange_low, cliprange_high,
+                                   clip_cov_lb, clip_cov_ub)
+    eligible, _, _, _ = ops.unpad_indices(flags.view(1, -1))  # ascending flat positions == torch.nonzero order
+    clip_num = max(int(clip_cov_ratio * float(ws[0].item())), 1)
+    n = flags.numel()
+    if eligible.numel() > 0:
+        perm = torch.randperm(eligible.numel())
+        chosen = ops.gather_rows(eligible, perm[: min(clip_num, eligible.numel())].to(eligible.device))
+        ones = torch.ones((chosen.numel(), 1), dtype=torch.uint8, device=flags.device)
+        zeroed = ops.scatter_rows(ones, chosen, n).view(-1)
+    else:
+        zeroed = torch.zeros(n, dtype=torch.uint8, device=flags.device)
+    pg, dpg, out3 = ops.clip_cov_loss(old_log_prob, lp_d, advantages, response_mask, cliprange_low, cliprange_high,
+                                      zeroed, ws)
+    pg_losses = _LossMatrix.apply(log_prob, pg, dpg)
+    pg_loss = agg_loss(loss_mat=pg_losses, loss_mask=response_mask, loss_agg_mode=loss_agg_mode)
+    return pg_loss, out3[1], out3[0], torch.tensor(0.0)
+
+
+@register_policy_loss("kl_cov")
+def compute_policy_loss_kl_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean",
+                               config=None):
+    """KL-Cov policy loss (core_algos.py:908-972): the max(1, int(N_valid * kl_cov_ratio)) valid tokens with the largest
+    covariance (A - mean A)(log_prob - mean log_prob) pay an extra ppo_kl_coef * |log_prob - old_log_prob|.
+
+    The reference moves the valid tokens to the CPU for torch.topk; here the k-th largest is found on the device
+    (radix select), no host sync at all.  Returns (pg_loss, 0, ppo_kl_abs, 0)."""
+    kl_cov_ratio = _policy_loss_cfg(config, "kl_cov_ratio", 0.0002)
+    ppo_kl_coef = _policy_loss_cfg(config, "ppo_kl_coef", 1.0)
+    assert kl_cov_ratio > 0, "kl_cov_ratio should be larger than 0."
+    pg, dpg, out3 = ops.kl_cov_loss(old_log_prob, log_prob.detach(), advantages, response_mask, kl_cov_ratio, ppo_kl_coef)
+    pg_losses = _LossMatrix.apply(log_prob, pg, dpg)
+    pg_loss = agg_loss(loss_mat=pg_losses, loss_mask=response_mask, loss_agg_mode=loss_agg_mode)
+    return pg_loss, torch.tensor(0.0), out3[0], torch.tensor(0.0)
+
+
+def compute_entropy_loss(logits, response_mask, loss_agg_mode: str = "token-mean"):
+    """core_algos.py:975-989 (kept by the reference for backward compatibility): agg_loss of the per-token entropy of
+    materialised logits [bs, response_length, vocab]."""
+    from verl_b200.utils import torch_functional as verl_F
+
+    token_entropy = verl_F.entropy_from_logits(logits)
+    return agg_loss(loss_mat=token_entropy, loss_mask=response_mask, loss_agg_mode=loss_agg_mode)
+
+
 class _ValueLoss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, vpreds, returns, values, response_mask, cliprange_value, mode):
