@@ -539,7 +539,7 @@ __device__ __forceinline__ float fkey_inv(unsigned int k) {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
-template <typename MT>
+template <int VEC, typename MT>
 __global__ void data_metrics_kernel(const float* __restrict__ scores, const float* __restrict__ rewards,
                                     const float* __restrict__ adv, const float* __restrict__ rets,
                                     const float* __restrict__ vals, const MT* __restrict__ rmask, long long L, int gx,
@@ -553,24 +553,38 @@ __global__ void data_metrics_kernel(const float* __restrict__ scores, const floa
     float s1[3] = {0.f, 0.f, 0.f}, s2[3] = {0.f, 0.f, 0.f};
     float mx[3] = {-INFINITY, -INFINITY, -INFINITY}, mn[3] = {INFINITY, INFINITY, INFINITY};
     float d1 = 0.f, d2 = 0.f;
-    const long long stride = static_cast<long long>(gx) * blockDim.x;
-    for (long long t = static_cast<long long>(cx) * blockDim.x + threadIdx.x; t < L; t += stride) {
+    // every operand is loaded unconditionally (128-bit when VEC == 4): five independent streams in flight per thread,
+    // the response_mask.bool() test (metric_utils.py:109) only gates the arithmetic
+    const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
+    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
         const long long i = base + t;
-        s_sc += scores[i];
-        s_rw += rewards[i];
-        if (mask_to_float(rmask[i]) != 0.f) {  // response_mask.bool() (metric_utils.py:109)
-            cnt += 1.f;
-            const float q[3] = {adv[i], rets[i], vals ? vals[i] : 0.f};
+        const Pack<VEC> sc = ldv<VEC>(scores, i), rw = ldv<VEC>(rewards, i), a = ldv<VEC>(adv, i), r = ldv<VEC>(rets, i);
+        const Pack<VEC> m = ldm<VEC, MT>(rmask, i);
+        Pack<VEC> vl;
+        if (vals) {
+            vl = ldv<VEC>(vals, i);
+        } else {
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                s1[k] += q[k];
-                s2[k] += q[k] * q[k];
-                mx[k] = fmaxf(mx[k], q[k]);
-                mn[k] = fminf(mn[k], q[k]);
+            for (int j = 0; j < VEC; ++j) vl.v[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            s_sc += sc.v[j];
+            s_rw += rw.v[j];
+            if (m.v[j] != 0.f) {
+                cnt += 1.f;
+                const float q[3] = {a.v[j], r.v[j], vl.v[j]};
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    s1[k] += q[k];
+                    s2[k] += q[k] * q[k];
+                    mx[k] = fmaxf(mx[k], q[k]);
+                    mn[k] = fminf(mn[k], q[k]);
+                }
+                const float d = q[1] - q[2];
+                d1 += d;
+                d2 += d * d;
             }
-            const float d = q[1] - q[2];
-            d1 += d;
-            d2 += d * d;
         }
     }
     double v[kDmAcc];
@@ -739,11 +753,18 @@ int vpg_data_metrics(const float* token_level_scores, const float* token_level_r
     // min keys start at the largest key (memset 0xff on the three min slots is done by initialising all six keys):
     static const unsigned int init_keys[8] = {0u, 0xffffffffu, 0u, 0xffffffffu, 0u, 0xffffffffu, 0u, 0u};
     VPG_CUDA(cudaMemcpyAsync(keys, init_keys, sizeof(init_keys), cudaMemcpyHostToDevice, stream));
-    const int gx = blocks_per_row(B, L, 1);
+    const bool vec = rows_vec_ok(L, response_mask, rmask_dtype,
+                                 {token_level_scores, token_level_rewards, advantages, returns, values});
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
     VPG_DISPATCH_MASK(rmask_dtype, MT, {
-        data_metrics_kernel<MT><<<static_cast<unsigned>(B * gx), kThreads, 0, stream>>>(
-            token_level_scores, token_level_rewards, advantages, returns, values, static_cast<const MT*>(response_mask),
-            L, gx, B, acc, keys, rows);
+        if (vec)
+            data_metrics_kernel<4, MT><<<static_cast<unsigned>(B * gx), kThreads, 0, stream>>>(
+                token_level_scores, token_level_rewards, advantages, returns, values,
+                static_cast<const MT*>(response_mask), L, gx, B, acc, keys, rows);
+        else
+            data_metrics_kernel<1, MT><<<static_cast<unsigned>(B * gx), kThreads, 0, stream>>>(
+                token_level_scores, token_level_rewards, advantages, returns, values,
+                static_cast<const MT*>(response_mask), L, gx, B, acc, keys, rows);
     });
     count_launch();
     VPG_DISPATCH_MASK(amask_dtype, MT, {

@@ -21,7 +21,7 @@ BUILD_DIR = CSRC / "build"
 LIB_PATH = LIB_DIR / "libvpg_b200.so"
 
 SOURCES = ["common.cu", "lce.cu", "token_ops.cu", "adv_ops.cu", "rmpad.cu", "logits_ops.cu", "seqlen_balance.cu", "packed_seqs.cu", "cov_loss.cu"]
-HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "token_common.cuh", "../../include/vpg_b200.h"]
+HEADERS = ["common.h", "ptx.cuh", "tc_gemm.cuh", "reduce.cuh", "token_common.cuh", "row_copy.cuh", "../../include/vpg_b200.h"]
 
 NVCC_FLAGS = [
     "-gencode",

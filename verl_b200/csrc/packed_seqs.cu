@@ -5,8 +5,8 @@
 // context-parallel chunk, several .item() syncs).  Here the whole layout is index arithmetic on the device:
 //   packed_layout_kernel  seqlens -> padded seqlens (multiple of `align`), padded cu_seqlens, {sum, max}   (1 block)
 //   packed_map_kernel     valid token n = (sequence i, j-th valid token) -> its slot in the packed stream
-//   permute_rows_kernel   out[dst[n]] = src[src_idx[n]] in the widest unit the row size allows (one pass; used for
-//                         both directions and for the backward of the post-processing)
+//   permute_rows_kernel   (row_copy.cuh) out[dst[n]] = src[src_idx[n]], one pass; used for both directions and for
+//                         the backward of the post-processing
 // Context parallelism (cp): a padded sequence of Lp tokens is cut into 2*cp chunks of half = Lp/(2*cp); rank r owns
 // chunk r and chunk 2*cp-1-r (causal-mask load balance), stored back to back in its local stream at offset
 // cu_padded[i]/cp.  The cp-gathered stream is rank-major: position = r * (sum Lp / cp) + local slot.
@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 
 #include "common.h"
+#include "row_copy.cuh"
 
 namespace vpg {
 
@@ -101,31 +102,6 @@ __global__ void packed_map_kernel(const int* __restrict__ cu_seqlens, const int*
     local_dst[n] = (r == cp_rank) ? slot : -1;
 }
 
-// out[dst[n]*upr + c] = src[sidx[n]*upr + c]; a null index array is the identity; dst < 0 skips the row
-template <typename U>
-__global__ void permute_rows_kernel(const U* __restrict__ src, const long long* __restrict__ sidx,
-                                    const long long* __restrict__ didx, long long n_rows, long long upr,
-                                    U* __restrict__ out) {
-    const long long total = n_rows * upr;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < total; u += stride) {
-        const long long r = u / upr, c = u - r * upr;
-        const long long d = didx ? didx[r] : r;
-        if (d < 0) continue;
-        const long long s = sidx ? sidx[r] : r;
-        out[d * upr + c] = src[s * upr + c];
-    }
-}
-
-static inline int row_unit(const void* a, const void* b, int64_t row_bytes) {
-    const uintptr_t x = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | static_cast<uintptr_t>(row_bytes);
-    if ((x & 15) == 0) return 16;
-    if ((x & 7) == 0) return 8;
-    if ((x & 3) == 0) return 4;
-    if ((x & 1) == 0) return 2;
-    return 1;
-}
-
 }  // namespace vpg
 
 using namespace vpg;
@@ -165,22 +141,9 @@ int vpg_permute_rows(const void* src, const int64_t* src_idx, const int64_t* dst
     }
     if (n_rows == 0) return VPG_OK;
     VPG_CHECK_ARG(src && out, "null pointer argument");
-    const long long* si = reinterpret_cast<const long long*>(src_idx);
-    const long long* di = reinterpret_cast<const long long*>(dst_idx);
-    const int u = row_unit(src, out, row_bytes);
-    const int64_t upr = row_bytes / u;
-    int64_t g = ceil_div(n_rows * upr, 256);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
-    if (g > cap) g = cap;
-    const unsigned grid = static_cast<unsigned>(g < 1 ? 1 : g);
-    switch (u) {
-        case 16: permute_rows_kernel<uint4><<<grid, 256, 0, stream>>>((const uint4*)src, si, di, n_rows, upr, (uint4*)out); break;
-        case 8: permute_rows_kernel<uint2><<<grid, 256, 0, stream>>>((const uint2*)src, si, di, n_rows, upr, (uint2*)out); break;
-        case 4: permute_rows_kernel<uint32_t><<<grid, 256, 0, stream>>>((const uint32_t*)src, si, di, n_rows, upr, (uint32_t*)out); break;
-        case 2: permute_rows_kernel<uint16_t><<<grid, 256, 0, stream>>>((const uint16_t*)src, si, di, n_rows, upr, (uint16_t*)out); break;
-        default: permute_rows_kernel<uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)src, si, di, n_rows, upr, (uint8_t*)out); break;
-    }
-    VPG_LAUNCH_CHECK();
+    VPG_CUDA(launch_permute_rows(src, reinterpret_cast<const long long*>(src_idx),
+                                 reinterpret_cast<const long long*>(dst_idx), n_rows, row_bytes, out, stream));
+    count_launch();
     return VPG_OK;
 }
 

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include "common.h"
+#include "row_copy.cuh"
 #include "reduce.cuh"
 
 namespace vpg {
@@ -35,9 +36,19 @@ __global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, long
     int c = 0;
     long long cur_row = -1;
     long long cur_sum = 0;
+    // row arithmetic without per-element 64-bit divisions: ONE division per thread locates the tile; inside the tile an
+    // element is < S + kTile past that row's start, so its row offset is a compare (S >= kTile) or a 32-bit division
+    const long long tile_row = tile0 / S;
+    const long long tile_off = tile0 - tile_row * S;
+    const bool wide = S >= kTile;
+    const unsigned int S32 = static_cast<unsigned int>(wide ? 1 : S);
+    auto row_of = [&](long long loc) -> long long {
+        return tile_row + (wide ? (loc >= S ? 1 : 0) : static_cast<long long>(static_cast<unsigned int>(loc) / S32));
+    };
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
-        const long long i = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
+        const int e = j * kTileThreads + threadIdx.x;  // element inside the tile
+        const long long i = tile0 + e;
         const bool in = i < n;
         const MT m = in ? mask[i] : MT(0);
         const bool nz = in && mask_nonzero(m);
@@ -48,11 +59,17 @@ __global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, long
         const long long first = i - lane;  // element of lane 0
         if (first < n) {
             const long long last = (first + 31 < n) ? first + 31 : n - 1;
-            const long long r0 = first / S, r1 = last / S;
+            const long long r0 = row_of(tile_off + (e - lane)), r1 = row_of(tile_off + (e - lane) + (last - first));
             long long v = in ? static_cast<long long>(m) : 0;
             if (r0 == r1) {
+                // 0/1 masks (the usual case): the warp's sum is the popcount of the ballot already taken; any other
+                // mask value falls back to the shuffle tree
+                if (__all_sync(0xffffffffu, v == (nz ? 1 : 0))) {
+                    v = __popc(bal);
+                } else {
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                }
                 if (lane == 0) {
                     if (r0 != cur_row) {
                         if (cur_row >= 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], static_cast<int>(cur_sum));
@@ -61,7 +78,7 @@ __global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, long
                     cur_sum += v;
                 }
             } else if (in && v != 0) {  // a row boundary inside the warp's 32 elements (S < 32 or unaligned rows)
-                atomicAdd(&seqlens[i / S], static_cast<int>(v));
+                atomicAdd(&seqlens[row_of(tile_off + e)], static_cast<int>(v));
             }
         }
     }
@@ -144,78 +161,47 @@ __global__ void scan_kernel(const int* __restrict__ tile_counts, int num_tiles, 
     }
 }
 
-// Pass 2: ordered write of the nonzero positions of each tile from the bitmap (the mask is not read again)
+// Pass 2: ordered write of the nonzero positions of each tile from the bitmap (the mask is not read again).
+// The tile's 128 ballots (item-major, warp-minor == element order) are loaded once, coalesced; their popcounts are
+// scanned by four warps; every thread then places its own elements with one shared-memory read per item.
 __global__ void tile_write_kernel(const unsigned int* __restrict__ bits, const long long* __restrict__ tile_offsets,
                                   long long* __restrict__ indices) {
-    __shared__ int warp_cnt[kItems][kTileThreads / 32];
+    constexpr int kWords = kItems * (kTileThreads / 32);  // 128
+    __shared__ unsigned int sbits[kWords];
+    __shared__ int excl[kWords];
+    __shared__ int wtot[kWords / 32];
     const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    unsigned bal[kItems];
+    int inc = 0, cnt = 0;
+    if (threadIdx.x < kWords) {
+        const unsigned int b = bits[static_cast<long long>(blockIdx.x) * kWords + threadIdx.x];
+        sbits[threadIdx.x] = b;
+        cnt = __popc(b);
+        inc = cnt;
 #pragma unroll
-    for (int j = 0; j < kItems; ++j) {
-        bal[j] = bits[(static_cast<long long>(blockIdx.x) * kItems + j) * (kTileThreads / 32) + w];
-        if (lane == 0) warp_cnt[j][w] = __popc(bal[j]);
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) wtot[w] = inc;
     }
     __syncthreads();
-    // element order inside the tile is (j, warp, lane): rank = sum of counts of all earlier (j', w') + lane prefix
-    long long off = tile_offsets[blockIdx.x];
-    int run = 0;
+    if (threadIdx.x < kWords) {
+        int pre = 0;
+        for (int ww = 0; ww < w; ++ww) pre += wtot[ww];
+        excl[threadIdx.x] = pre + inc - cnt;
+    }
+    __syncthreads();
+    const long long off = tile_offsets[blockIdx.x];
+    const unsigned int below = (1u << lane) - 1u;
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
-        int before = 0, total_j = 0;
-#pragma unroll
-        for (int ww = 0; ww < kTileThreads / 32; ++ww) {
-            const int c = warp_cnt[j][ww];
-            before += (ww < w) ? c : 0;
-            total_j += c;
-        }
-        if ((bal[j] >> lane) & 1u) {
-            const int r = run + before + __popc(bal[j] & ((1u << lane) - 1u));
-            indices[off + r] = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
-        }
-        run += total_j;
+        const int q = j * (kTileThreads / 32) + w;
+        const unsigned int bal = sbits[q];
+        if ((bal >> lane) & 1u)
+            indices[off + excl[q] + __popc(bal & below)] = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
     }
 }
-
-// out[i*upr + c] = src[idx[i]*upr + c]  (units of U bytes)
-template <typename U>
-__global__ void gather_units_kernel(const U* __restrict__ src, const long long* __restrict__ idx, long long n_idx,
-                                    long long upr, U* __restrict__ out) {
-    const long long total = n_idx * upr;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < total; u += stride) {
-        const long long r = u / upr, c = u - r * upr;
-        out[u] = src[idx[r] * upr + c];
-    }
-}
-template <typename U>
-__global__ void scatter_units_kernel(const U* __restrict__ src, const long long* __restrict__ idx, long long n_idx,
-                                     long long upr, U* __restrict__ out) {
-    const long long total = n_idx * upr;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < total; u += stride) {
-        const long long r = u / upr, c = u - r * upr;
-        out[idx[r] * upr + c] = src[u];
-    }
-}
-
-static inline int unit_bytes(const void* a, const void* b, int64_t row_bytes) {
-    const uintptr_t x = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
-                        static_cast<uintptr_t>(row_bytes);
-    if ((x & 15) == 0) return 16;
-    if ((x & 7) == 0) return 8;
-    if ((x & 3) == 0) return 4;
-    if ((x & 1) == 0) return 2;
-    return 1;
-}
-
-static inline unsigned copy_grid(int64_t total_units) {
-    int64_t g = ceil_div(total_units, 256);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
-    if (g > cap) g = cap;
-    return static_cast<unsigned>(g < 1 ? 1 : g);
-}
-
 
 // Response-window selection on the rmpad stream (verl/workers/actor/dp_actor.py:135,221-237 folded into one pass):
 // token i of the stream sits at padded position indices[i] = b*S + s.  The reference computes log-probs for every
@@ -317,19 +303,9 @@ int vpg_gather_rows(const void* src, const int64_t* indices, int64_t n_idx, int6
     VPG_CHECK_ARG(n_idx >= 0 && row_bytes > 0, "invalid gather_rows arguments");
     if (n_idx == 0) return VPG_OK;
     VPG_CHECK_ARG(src && indices && out, "null pointer argument");
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    const long long* idx = reinterpret_cast<const long long*>(indices);
-    const int u = unit_bytes(src, out, row_bytes);
-    const int64_t upr = row_bytes / u;
-    const unsigned g = copy_grid(n_idx * upr);
-    switch (u) {
-        case 16: gather_units_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, n_idx, upr, (uint4*)out); break;
-        case 8: gather_units_kernel<uint2><<<g, 256, 0, stream>>>((const uint2*)src, idx, n_idx, upr, (uint2*)out); break;
-        case 4: gather_units_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, idx, n_idx, upr, (uint32_t*)out); break;
-        case 2: gather_units_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, n_idx, upr, (uint16_t*)out); break;
-        default: gather_units_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, n_idx, upr, (uint8_t*)out); break;
-    }
-    VPG_LAUNCH_CHECK();
+    VPG_CUDA(launch_permute_rows(src, reinterpret_cast<const long long*>(indices), nullptr, n_idx, row_bytes, out,
+                                 static_cast<cudaStream_t>(stream_)));
+    count_launch();
     return VPG_OK;
 }
 
@@ -343,18 +319,8 @@ int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int
     }
     if (n_idx == 0) return VPG_OK;
     VPG_CHECK_ARG(src && indices && out, "null pointer argument");
-    const long long* idx = reinterpret_cast<const long long*>(indices);
-    const int u = unit_bytes(src, out, row_bytes);
-    const int64_t upr = row_bytes / u;
-    const unsigned g = copy_grid(n_idx * upr);
-    switch (u) {
-        case 16: scatter_units_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, n_idx, upr, (uint4*)out); break;
-        case 8: scatter_units_kernel<uint2><<<g, 256, 0, stream>>>((const uint2*)src, idx, n_idx, upr, (uint2*)out); break;
-        case 4: scatter_units_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, idx, n_idx, upr, (uint32_t*)out); break;
-        case 2: scatter_units_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, n_idx, upr, (uint16_t*)out); break;
-        default: scatter_units_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, n_idx, upr, (uint8_t*)out); break;
-    }
-    VPG_LAUNCH_CHECK();
+    VPG_CUDA(launch_permute_rows(src, nullptr, reinterpret_cast<const long long*>(indices), n_idx, row_bytes, out, stream));
+    count_launch();
     return VPG_OK;
 }
 

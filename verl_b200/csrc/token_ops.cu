@@ -185,7 +185,7 @@ __device__ __forceinline__ double agg_finalize(int mode, const double* row_sum, 
 }
 
 template <int VEC, typename MT>
-__global__ void ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) {
+__global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask) {
     __shared__ double red[32];
     const long long b = blockIdx.x / p.gx;
     const int cx = blockIdx.x % p.gx;
