@@ -62,9 +62,40 @@ def _namespace(name):
     return mod
 
 
-def install(patch_flash_attn: bool = False) -> dict:
-    """Route the reference's hot-path imports to verl_b200.  Returns {module name: 'patched' | 'shadowed'}."""
+_EXTRA_TARGETS = {
+    # §8(f).3 / (f).4 callers' plumbing: module -> (verl_b200 module, names)
+    "verl.utils.seqlen_balancing": ("verl_b200.utils.seqlen_balancing", [
+        "karmarkar_karp", "get_seqlen_balanced_partitions", "rearrange_micro_batches", "prepare_dynamic_batch",
+        "restore_dynamic_batch", "get_reverse_idx", "log_seqlen_unbalance", "ceildiv", "roundup_divisible"]),
+    "verl.utils.ulysses": ("verl_b200.utils.ulysses", [
+        "gather_outputs_and_unpad", "ulysses_pad", "ulysses_pad_and_slice_inputs", "slice_input_tensor", "Gather"]),
+    "verl.utils.megatron.tensor_parallel": ("verl_b200.utils.megatron.tensor_parallel", [
+        "vocab_parallel_entropy", "vocab_parallel_log_probs_from_logits",
+        "vocab_parallel_log_probs_from_logits_response_rmpad"]),
+    "verl.models.mcore.util": ("verl_b200.models.mcore.util", ["preprocess_packed_seqs", "postprocess_packed_seqs"]),
+}
+
+
+def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
+    """Route the reference's hot-path imports to verl_b200.  Returns {module name: 'patched' | 'shadowed'}.
+
+    The §8(f).3/(f).4 plumbing modules (seqlen_balancing, ulysses, megatron.tensor_parallel, mcore.util) are shadowed
+    when the reference module is not importable; an importable one is only patched with patch_extras=True (its
+    callers then receive plain dicts of tensor views instead of TensorDicts from rearrange_micro_batches)."""
     report = {}
+    for name, (src_name, names) in _EXTRA_TARGETS.items():
+        src = importlib.import_module(src_name)
+        real = _try_import(name)
+        if real is not None and real is not src:
+            if patch_extras:
+                for n in names:
+                    setattr(real, n, getattr(src, n))
+                report[name] = "patched"
+        else:
+            parent, _, leaf = name.rpartition(".")
+            sys.modules[name] = src
+            setattr(_namespace(parent), leaf, src)
+            report[name] = "shadowed"
     targets = {
         "verl.utils.kernel.linear_cross_entropy": (_lce, ["LinearCrossEntropy", "linear_cross_entropy"]),
         "verl.utils.kernel.kernels": (_k, [n for n in dir(_k) if not n.startswith("__")]),
