@@ -171,7 +171,10 @@ def test_compat_install_shadows_reference_paths():
         "from verl.utils.kernel.linear_cross_entropy import linear_cross_entropy as a;"
         "from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy as b;"
         "import verl.trainer.ppo.core_algos as ca, verl.utils.torch_functional as F;"
+        "from verl.utils.seqlen_balancing import get_seqlen_balanced_partitions as kk;"
+        "from verl.models.mcore.util import preprocess_packed_seqs; from verl.utils.ulysses import ulysses_pad;"
+        "from verl.utils.megatron.tensor_parallel import vocab_parallel_entropy;"
         "assert a is b and hasattr(ca, 'compute_policy_loss') and hasattr(F, 'masked_mean'); print('ok', len(r))"
     )
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "ok 4" in out.stdout, out.stderr
+    assert out.returncode == 0 and "ok 8" in out.stdout, out.stderr
