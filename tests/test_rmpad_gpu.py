@@ -55,6 +55,43 @@ def test_unpad_vs_oracle_shapes(B, S, dtype, dev):
     assert mx == w_mx
 
 
+@pytest.mark.parametrize("B,S", [(300, 4100), (5000, 40), (4500, 1000), (2, 1 << 20)])
+def test_unpad_many_tiles_rows_and_groups(B, S, dev):
+    """more than 128 tiles (two-level offsets), more than 2048 rows (several row-scan blocks), rows that are not a
+    multiple of 32 (row boundaries inside a warp's 32 elements)"""
+    from verl_b200 import ops
+
+    g = torch.Generator().manual_seed(B + S)
+    lens = torch.randint(0, S + 1, (B,), generator=g)
+    mask = (torch.arange(S)[None] < lens[:, None])
+    mask = torch.where(torch.rand(B, 1, generator=g) < 0.5, mask, mask.flip(1))  # left- and right-padded rows
+    idx, seqlens, cu, mx = ops.unpad_indices(mask.long().to(dev))
+    w_idx, w_len, w_cu, w_mx = port.unpad_indices(mask.long())
+    assert torch.equal(idx.cpu(), w_idx) and torch.equal(seqlens.cpu(), w_len) and torch.equal(cu.cpu(), w_cu)
+    assert mx == w_mx
+
+
+@pytest.mark.parametrize("dtype", [torch.int64, torch.int32, torch.uint8])
+def test_unpad_unaligned_base_and_non_binary_values(dtype, dev):
+    """a mask view whose base pointer is not 16-byte aligned takes the guarded-load path; mask values other than 0/1
+    count as valid tokens and are SUMMED into seqlens, as the reference's mask.sum(-1) does"""
+    from verl_b200 import ops
+
+    B, S = 37, 1111
+    g = torch.Generator().manual_seed(5)
+    vals = torch.randint(0, 4, (B * S + 3,), generator=g).to(dtype)
+    vals[torch.rand(B * S + 3, generator=g) < 0.4] = 0
+    buf = vals.to(dev)
+    for shift in (0, 1, 3):
+        m = buf[shift:shift + B * S].view(B, S)
+        idx, seqlens, cu, mx = ops.unpad_indices(m)
+        ref = m.cpu().long()
+        assert torch.equal(idx.cpu(), ref.flatten().nonzero().flatten())
+        assert torch.equal(seqlens.cpu().long(), ref.sum(-1))
+        assert torch.equal(cu.cpu().long(), torch.nn.functional.pad(ref.sum(-1).cumsum(0), (1, 0)))
+        assert mx == int(ref.sum(-1).max())
+
+
 def test_all_masked_and_all_valid(dev):
     from verl_b200 import ops
 

@@ -96,6 +96,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
 }
+// 1-D bulk copy global -> shared (no tensor map): `bytes` % 16 == 0, src and dst 16-byte aligned; completes `bytes` on
+// mbarrier `bar` (own CTA).  One instruction moves the whole chunk: no registers, no L1 miss tracking.
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // 2-D tiled load: coordinates {c0 (innermost), c1}; completes `bytes` on mbarrier `bar` (own CTA)
 __device__ __forceinline__ void tma_load_2d(const void* tmap, uint64_t* bar, void* dst, int c0, int c1) {
     asm volatile(

@@ -7,10 +7,13 @@
 // Integer outputs are bit-exact.  Stream compaction: tile counts -> single-block scan -> ordered tile write with
 // ballot/popc ranks, so the index list is produced in ascending order without a sort.
 #include <cuda_runtime.h>
+#include <limits.h>
 
 #include "common.h"
+#include "ptx.cuh"
 #include "row_copy.cuh"
 #include "reduce.cuh"
+#include "token_common.cuh"
 
 namespace vpg {
 
@@ -23,158 +26,233 @@ __device__ __forceinline__ bool mask_nonzero(MT m) {
     return m != MT(0);
 }
 
-// Pass 1 — the ONLY pass over the mask: nonzero count of every tile, the nonzero bitmap (one 32-bit ballot per warp and
-// item: 1 bit per element, read back by the write pass instead of the 1-8 byte mask elements), and the per-row sums
-// of the mask VALUES (seqlens).  Layout: element = tile0 + j*256 + tid (coalesced); a warp's 32 elements of one item
-// almost always sit in one row, so lane 0 keeps a running (row, sum) and issues one integer atomic per row change.
+// Stream compaction in two launches, the mask read ONCE:
+//   unpad_count_kernel — streaming pass over the mask.  Warps are autonomous (no block barrier, no tail block): a warp
+//     owns a contiguous run of 4096-element tiles and walks them in chunks of 512 elements.  A chunk is staged in shared
+//     memory by ONE bulk-copy instruction issued kStages chunks ahead (cp.async.bulk + mbarrier), so the bytes in flight
+//     are bounded by shared memory, not by registers or L1 miss tracking.  Per chunk: 16 ballots -> 64 bytes of a flat
+//     1-bit-per-element bitmap; per tile: the nonzero count (plain store, the warp owns the tile); per group of 128
+//     tiles: one RED on a super-count.  Per-row sums of the mask VALUES (seqlens): for 0/1 masks the popcounts already
+//     taken; the row of a chunk costs one 32-bit division per chunk; lane 0 keeps a running (row, sum) and issues one
+//     RED per row change — consecutive chunks of a warp are consecutive in memory, so that is one RED per row.
+//   unpad_write_kernel — block t writes the ascending int64 indices of tile t from its 512-byte bitmap (the 1-8 byte
+//     mask elements are not read again).  Its output offset is a two-level sum (super-counts before its group + tile
+//     counts inside the group) taken by one otherwise idle warp under the bitmap load: no scan launch, no chained
+//     spinning.  Extra blocks at the end of the grid turn seqlens into cu_seqlens / max_seqlen off the critical path.
+constexpr int kWarps = kTileThreads / 32;
+constexpr int kWords = kItems * kWarps;      // 128 ballots per tile
+constexpr int kStages = 4;                   // bulk copies in flight per warp
+constexpr int kSuper = 128;                  // tiles per super-count
+constexpr int kRowsPerBlock = 8 * kTileThreads;  // rows scanned by one extra block of the write kernel
+constexpr unsigned int kChunk = 32 * kItems;     // 512 elements
+constexpr int kChunksPerTile = kTile / kChunk;   // 8
+
+struct UnpadHeader {             // first 16 bytes of the workspace, zeroed before the count pass
+    unsigned int extra_done;     // extra blocks of the write kernel that finished
+    unsigned int max_biased;     // max row sum, stored as (value ^ 0x80000000) so that 0 is INT_MIN
+    unsigned int pad[2];
+};
+
 template <typename MT>
-__global__ void tile_count_kernel(const MT* __restrict__ mask, long long n, long long S, int* __restrict__ tile_counts,
-                                  unsigned int* __restrict__ bits, int* __restrict__ seqlens) {
-    __shared__ int red[32];
-    const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
+__global__ void __launch_bounds__(kTileThreads)
+unpad_count_kernel(const MT* __restrict__ mask, unsigned int n, unsigned int S, int num_tiles, int tiles_per_warp,
+                   int* __restrict__ tile_counts, int* __restrict__ super_counts, unsigned int* __restrict__ bits,
+                   int* __restrict__ seqlens) {
+    extern __shared__ __align__(128) unsigned char stage_smem[];
+    __shared__ __align__(8) uint64_t bars[kWarps * kStages];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    int c = 0;
-    long long cur_row = -1;
-    long long cur_sum = 0;
-    // row arithmetic without per-element 64-bit divisions: ONE division per thread locates the tile; inside the tile an
-    // element is < S + kTile past that row's start, so its row offset is a compare (S >= kTile) or a 32-bit division
-    const long long tile_row = tile0 / S;
-    const long long tile_off = tile0 - tile_row * S;
-    const bool wide = S >= kTile;
-    const unsigned int S32 = static_cast<unsigned int>(wide ? 1 : S);
-    auto row_of = [&](long long loc) -> long long {
-        return tile_row + (wide ? (loc >= S ? 1 : 0) : static_cast<long long>(static_cast<unsigned int>(loc) / S32));
+    const int t_begin = (blockIdx.x * kWarps + w) * tiles_per_warp;
+    const int t_end = min(t_begin + tiles_per_warp, num_tiles);
+    if (t_begin >= t_end) return;
+    const unsigned int ch_begin = static_cast<unsigned int>(t_begin) * kChunksPerTile;
+    const unsigned int ch_end = static_cast<unsigned int>(t_end) * kChunksPerTile;  // whole tiles: no bitmap holes
+    constexpr unsigned int kChunkBytes = kChunk * sizeof(MT);
+    const bool aligned = (reinterpret_cast<uintptr_t>(mask) & 15) == 0;
+    MT* const my_stage = reinterpret_cast<MT*>(stage_smem) + static_cast<size_t>(w) * kStages * kChunk;
+    uint64_t* const my_bars = bars + w * kStages;
+    // a chunk cut by the end of the mask, or a mask whose base is not 16-byte aligned, is read with guarded loads
+    auto staged = [&](unsigned int ch) { return aligned && ch * kChunk + kChunk <= n; };
+    auto issue = [&](unsigned int ch, int s) {  // lane 0 only
+        if (ch < ch_end && staged(ch)) {
+            mbar_arrive_expect_tx(&my_bars[s], kChunkBytes);
+            tma_load_1d(my_stage + s * kChunk, mask + static_cast<size_t>(ch) * kChunk, kChunkBytes, &my_bars[s]);
+        }
     };
+    if (lane == 0) {
+        for (int s = 0; s < kStages; ++s) mbar_init(&my_bars[s], 1);
+        fence_barrier_init();
+        fence_proxy_async();
+        for (int s = 0; s < kStages; ++s) issue(ch_begin + s, s);
+    }
+    __syncwarp();
+    unsigned int cur_row = 0xffffffffu;
+    int cur_sum = 0;
+    auto add_row = [&](unsigned int row, int v) {
+        if (row != cur_row) {
+            if (lane == 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], cur_sum);
+            cur_row = row, cur_sum = 0;
+        }
+        cur_sum += v;
+    };
+    int tile_cnt = 0, super_cnt = 0;
+    unsigned int k = 0;
+    for (unsigned int ch = ch_begin; ch < ch_end; ++ch, ++k) {
+        const unsigned int c0 = ch * kChunk;
+        const int s = k % kStages;
+        MT m[kItems];
+        if (staged(ch)) {
+            mbar_wait(&my_bars[s], (k / kStages) & 1);
+            const MT* buf = my_stage + s * kChunk;
 #pragma unroll
-    for (int j = 0; j < kItems; ++j) {
-        const int e = j * kTileThreads + threadIdx.x;  // element inside the tile
-        const long long i = tile0 + e;
-        const bool in = i < n;
-        const MT m = in ? mask[i] : MT(0);
-        const bool nz = in && mask_nonzero(m);
-        const unsigned bal = __ballot_sync(0xffffffffu, nz);
-        if (lane == 0) bits[(static_cast<long long>(blockIdx.x) * kItems + j) * (kTileThreads / 32) + w] = bal;
-        c += nz ? 1 : 0;
-        // ---- seqlens
-        const long long first = i - lane;  // element of lane 0
-        if (first < n) {
-            const long long last = (first + 31 < n) ? first + 31 : n - 1;
-            const long long r0 = row_of(tile_off + (e - lane)), r1 = row_of(tile_off + (e - lane) + (last - first));
-            long long v = in ? static_cast<long long>(m) : 0;
-            if (r0 == r1) {
-                // 0/1 masks (the usual case): the warp's sum is the popcount of the ballot already taken; any other
-                // mask value falls back to the shuffle tree
-                if (__all_sync(0xffffffffu, v == (nz ? 1 : 0))) {
-                    v = __popc(bal);
-                } else {
+            for (int j = 0; j < kItems; ++j) m[j] = buf[j * 32 + lane];
+            __syncwarp();  // every lane has read the stage: refill it kStages chunks ahead
+            if (lane == 0) issue(ch + kStages, s);
+        } else {
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) {
+                const unsigned int i = c0 + j * 32 + lane;
+                m[j] = (i < n) ? mask[i] : MT(0);
+            }
+        }
+        unsigned int mine = 0;
+        int cnt = 0;
+        bool weird = false;
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            weird |= !(m[j] == MT(0) || m[j] == MT(1));
+            const unsigned bal = __ballot_sync(0xffffffffu, mask_nonzero(m[j]));  // elements past n were read as 0
+            if (lane == j) mine = bal;  // word j of the chunk's bitmap
+            cnt += __popc(bal);
+        }
+        if (lane < kItems) bits[static_cast<size_t>(ch) * kItems + lane] = mine;  // flat bitmap, element order
+        tile_cnt += cnt;
+        if ((ch & (kChunksPerTile - 1)) == kChunksPerTile - 1) {  // last chunk of a tile this warp owns
+            const int tile = static_cast<int>(ch / kChunksPerTile);
+            if (lane == 0) tile_counts[tile] = tile_cnt;
+            super_cnt += tile_cnt;
+            tile_cnt = 0;
+            if ((tile + 1) % kSuper == 0) {
+                if (lane == 0 && super_cnt != 0) atomicAdd(&super_counts[tile / kSuper], super_cnt);
+                super_cnt = 0;
+            }
+        }
+        if (cnt == 0) continue;
+        // ---- seqlens: sum of the mask VALUES per row
+        unsigned int row = c0 / S, off = c0 - row * S;
+        const bool binary = !__any_sync(0xffffffffu, weird);
+        if (binary && off + (kChunk - 1) < S) {  // 0/1 mask, whole chunk inside one row (the usual case)
+            add_row(row, cnt);
+            continue;
+        }
+#pragma unroll 1
+        for (int j = 0; j < kItems; ++j) {
+            const unsigned bal = __shfl_sync(0xffffffffu, mine, j);
+            long long mv = 0;  // this lane's element of item j
+#pragma unroll
+            for (int jj = 0; jj < kItems; ++jj) mv = (jj == j) ? static_cast<long long>(m[jj]) : mv;
+            if (off + 31 < S) {  // the item's 32 elements sit in one row
+                int v = __popc(bal);
+                if (!binary) {
+                    v = static_cast<int>(mv);
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
                 }
-                if (lane == 0) {
-                    if (r0 != cur_row) {
-                        if (cur_row >= 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], static_cast<int>(cur_sum));
-                        cur_row = r0, cur_sum = 0;
-                    }
-                    cur_sum += v;
-                }
-            } else if (in && v != 0) {  // a row boundary inside the warp's 32 elements (S < 32 or unaligned rows)
-                atomicAdd(&seqlens[row_of(tile_off + e)], static_cast<int>(v));
+                add_row(row, v);
+            } else if ((bal >> lane) & 1u) {  // a row boundary inside the 32 elements (S % 32 != 0 or S < 32)
+                atomicAdd(&seqlens[row + (off + lane) / S], static_cast<int>(mv));
             }
+            off += 32;
+            if (S >= 32 && off >= S) off -= S, row += 1;  // S < 32: (off + lane) / S above absorbs the growth
         }
     }
-    if (lane == 0 && cur_row >= 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], static_cast<int>(cur_sum));
-    const int tot = block_sum<int>(c, red);
-    if (threadIdx.x == 0) tile_counts[blockIdx.x] = tot;
+    if (lane == 0 && cur_sum != 0) atomicAdd(&seqlens[cur_row], cur_sum);
+    if (lane == 0 && super_cnt != 0) atomicAdd(&super_counts[(t_end - 1) / kSuper], super_cnt);
 }
 
-// single block: exclusive scan of tile counts -> tile_offsets (long long), inclusive scan of seqlens -> cu_seqlens,
-// totals = {nnz, max_seqlen}
-__global__ void scan_kernel(const int* __restrict__ tile_counts, int num_tiles, long long* __restrict__ tile_offsets,
-                            const int* __restrict__ seqlens, int B, int* __restrict__ cu_seqlens,
-                            int* __restrict__ totals) {
-    __shared__ long long warp_tot[32];
-    __shared__ long long carry_s;
-    __shared__ int max_s[32];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    // ---- tiles
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    for (int base = 0; base < num_tiles; base += blockDim.x) {
-        const int i = base + threadIdx.x;
-        const long long v = (i < num_tiles) ? tile_counts[i] : 0;
-        long long inc = v;
+// extra block e of the write kernel: cu_seqlens[r + 1] for rows [e*R, (e+1)*R) (int32 running sums wrap like torch's
+// int32 cumsum would), and the max row sum through a biased atomicMax; the extra block that finishes last publishes it
+__device__ void unpad_rows_block(int e, int num_extra, const int* __restrict__ seqlens, int B,
+                                 int* __restrict__ cu_seqlens, int* __restrict__ totals, UnpadHeader* hdr) {
+    __shared__ int red[32];
+    __shared__ int s_base;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int r_begin = e * kRowsPerBlock;
+    int part = 0;  // sum of the rows before this block's range (nothing to do for the first block)
+    for (int r = threadIdx.x; r < r_begin; r += kTileThreads) part += seqlens[r];
+    part = block_sum<int>(part, red);
+    if (threadIdx.x == 0) s_base = part;
+    int v[8], mx = INT_MIN, run = 0;
+    const int r0 = r_begin + threadIdx.x * 8;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const long long o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-        }
-        if (lane == 31) warp_tot[w] = inc;
-        __syncthreads();
-        long long pre = 0;
-        for (int ww = 0; ww < w; ++ww) pre += warp_tot[ww];
-        const long long carry = carry_s;
-        if (i < num_tiles) tile_offsets[i] = carry + pre + inc - v;
-        __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) carry_s = carry + pre + inc;
-        __syncthreads();
+    for (int i = 0; i < 8; ++i) {
+        v[i] = (r0 + i < B) ? seqlens[r0 + i] : 0;
+        if (r0 + i < B) mx = max(mx, v[i]);
+        run += v[i];
     }
-    if (threadIdx.x == 0) {
-        tile_offsets[num_tiles] = carry_s;
-        totals[0] = static_cast<int>(carry_s);
-    }
-    __syncthreads();
-    // ---- rows: int32 cumsum (wraps like torch's int32 cumsum would)
-    if (threadIdx.x == 0) {
-        carry_s = 0;
-        cu_seqlens[0] = 0;
-    }
-    int mx = 0;
-    __syncthreads();
-    for (int base = 0; base < B; base += blockDim.x) {
-        const int i = base + threadIdx.x;
-        const int v = (i < B) ? seqlens[i] : 0;
-        if (i < B) mx = max(mx, v);
-        long long inc = v;
+    int sc = run;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const long long o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-        }
-        if (lane == 31) warp_tot[w] = inc;
-        __syncthreads();
-        long long pre = 0;
-        for (int ww = 0; ww < w; ++ww) pre += warp_tot[ww];
-        const long long carry = carry_s;
-        if (i < B) cu_seqlens[i + 1] = static_cast<int>(carry + pre + inc);
-        __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) carry_s = carry + pre + inc;
-        __syncthreads();
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, sc, d);
+        if (lane >= d) sc += o;
+    }
+    __syncthreads();  // s_base visible, red[] free again
+    if (lane == 31) red[w] = sc;
+    __syncthreads();
+    int pre = s_base;
+    for (int ww = 0; ww < w; ++ww) pre += red[ww];
+    int acc = pre + sc - run;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        acc += v[i];
+        if (r0 + i < B) cu_seqlens[r0 + i + 1] = acc;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) max_s[w] = mx;
+    __syncthreads();
+    if (lane == 0) red[w] = mx;
     __syncthreads();
     if (threadIdx.x == 0) {
-        int m = 0;
-        for (int ww = 0; ww < nw; ++ww) m = max(m, max_s[ww]);
-        totals[1] = (B > 0) ? m : 0;
+        for (int ww = 1; ww < kWarps; ++ww) mx = max(mx, red[ww]);
+        if (e == 0) cu_seqlens[0] = 0;
+        atomicMax(&hdr->max_biased, static_cast<unsigned int>(mx) ^ 0x80000000u);
+        __threadfence();
+        if (atomicAdd(&hdr->extra_done, 1u) == static_cast<unsigned int>(num_extra - 1))
+            totals[1] = static_cast<int>(atomicMax(&hdr->max_biased, 0u) ^ 0x80000000u);
     }
 }
 
-// Pass 2: ordered write of the nonzero positions of each tile from the bitmap (the mask is not read again).
-// The tile's 128 ballots (item-major, warp-minor == element order) are loaded once, coalesced; their popcounts are
-// scanned by four warps; every thread then places its own elements with one shared-memory read per item.
-__global__ void tile_write_kernel(const unsigned int* __restrict__ bits, const long long* __restrict__ tile_offsets,
-                                  long long* __restrict__ indices) {
-    constexpr int kWords = kItems * (kTileThreads / 32);  // 128
+__global__ void __launch_bounds__(kTileThreads)
+unpad_write_kernel(const unsigned int* __restrict__ bits, const int* __restrict__ tile_counts,
+                   const int* __restrict__ super_counts, int num_tiles, long long* __restrict__ indices,
+                   const int* __restrict__ seqlens, int B, int* __restrict__ cu_seqlens, int* __restrict__ totals,
+                   UnpadHeader* hdr) {
+    if (static_cast<int>(blockIdx.x) >= num_tiles) {
+        unpad_rows_block(static_cast<int>(blockIdx.x) - num_tiles, static_cast<int>(gridDim.x) - num_tiles, seqlens, B,
+                         cu_seqlens, totals, hdr);
+        return;
+    }
     __shared__ unsigned int sbits[kWords];
     __shared__ int excl[kWords];
     __shared__ int wtot[kWords / 32];
-    const long long tile0 = static_cast<long long>(blockIdx.x) * kTile;
+    __shared__ int s_prefix;
+    const int tile = static_cast<int>(blockIdx.x);
+    const long long tile0 = static_cast<long long>(tile) * kTile;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (w == kWarps - 1) {  // nonzeros before this tile: super-counts before its group + tile counts inside the group
+        const int sup = tile / kSuper;
+        int acc = 0;
+        for (int i = lane; i < sup; i += 32) acc += super_counts[i];
+        for (int t = sup * kSuper + lane; t < tile; t += 32) acc += tile_counts[t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) {
+            s_prefix = acc;
+            if (tile == num_tiles - 1) totals[0] = acc + tile_counts[tile];  // nnz
+        }
+    }
     int inc = 0, cnt = 0;
     if (threadIdx.x < kWords) {
-        const unsigned int b = bits[static_cast<long long>(blockIdx.x) * kWords + threadIdx.x];
+        const unsigned int b = bits[static_cast<size_t>(tile) * kWords + threadIdx.x];
         sbits[threadIdx.x] = b;
         cnt = __popc(b);
         inc = cnt;
@@ -192,11 +270,11 @@ __global__ void tile_write_kernel(const unsigned int* __restrict__ bits, const l
         excl[threadIdx.x] = pre + inc - cnt;
     }
     __syncthreads();
-    const long long off = tile_offsets[blockIdx.x];
+    const long long off = s_prefix;
     const unsigned int below = (1u << lane) - 1u;
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
-        const int q = j * (kTileThreads / 32) + w;
+        const int q = j * kWarps + w;
         const unsigned int bal = sbits[q];
         if ((bal >> lane) & 1u)
             indices[off + excl[q] + __popc(bal & below)] = tile0 + static_cast<long long>(j) * kTileThreads + threadIdx.x;
@@ -259,9 +337,9 @@ int vpg_response_rows(const int64_t* indices, const int64_t* ids_rmpad, int64_t 
 
 size_t vpg_unpad_workspace_bytes(int64_t n) {
     const int64_t tiles = ceil_div(n > 0 ? n : 1, kTile);
-    // tile offsets (i64) | tile counts (i32) | nonzero bitmap: one u32 per (tile, item, warp) = 1 bit per element
-    return static_cast<size_t>(tiles) * sizeof(int) + 16 + static_cast<size_t>(tiles + 1) * sizeof(long long) + 16 +
-           static_cast<size_t>(tiles) * kItems * (kTileThreads / 32) * sizeof(unsigned int);
+    // header | super-counts (i32) | tile counts (i32) | bitmap: 1 bit per element
+    return sizeof(UnpadHeader) + round_up(ceil_div(tiles, kSuper) * sizeof(int), 16) + round_up(tiles * sizeof(int), 16) +
+           static_cast<size_t>(tiles) * kWords * sizeof(unsigned int);
 }
 
 int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,
@@ -276,24 +354,42 @@ int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, in
         return set_error(VPG_ERR_WORKSPACE, "unpad workspace too small: need %zu, got %zu", need, workspace_bytes);
     VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 7) == 0, "workspace must be 8-byte aligned");
     const int tiles = static_cast<int>(n > 0 ? ceil_div(n, kTile) : 0);
-    long long* tile_offsets = static_cast<long long*>(workspace);
-    int* tile_counts = reinterpret_cast<int*>(tile_offsets + (ceil_div(n > 0 ? n : 1, kTile) + 1));
-    unsigned int* bits = reinterpret_cast<unsigned int*>(
-        reinterpret_cast<uint8_t*>(tile_counts) + round_up(static_cast<int64_t>(tiles) * sizeof(int), 16));
-    if (B > 0) VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
-    VPG_DISPATCH_MASK(mask_dtype, MT, {
-        if (tiles > 0) {
-            tile_count_kernel<MT><<<tiles, kTileThreads, 0, stream>>>(static_cast<const MT*>(mask), n, S, tile_counts,
-                                                                      bits, seqlens);
-            count_launch();
-        }
-    });
-    scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, tiles, tile_offsets, seqlens, static_cast<int>(B), cu_seqlens, totals);
-    count_launch();
-    if (tiles > 0) {
-        tile_write_kernel<<<tiles, kTileThreads, 0, stream>>>(bits, tile_offsets, reinterpret_cast<long long*>(indices));
-        count_launch();
+    if (tiles == 0) {  // empty mask: no valid token, every row length 0
+        VPG_CUDA(cudaMemsetAsync(cu_seqlens, 0, static_cast<size_t>(B + 1) * sizeof(int), stream));
+        VPG_CUDA(cudaMemsetAsync(totals, 0, 2 * sizeof(int), stream));
+        if (B > 0) VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
+        return VPG_OK;
     }
+    uint8_t* ws = static_cast<uint8_t*>(workspace);
+    const size_t sup_bytes = round_up(ceil_div(static_cast<int64_t>(tiles), kSuper) * sizeof(int), 16);
+    const size_t cnt_bytes = round_up(static_cast<int64_t>(tiles) * sizeof(int), 16);
+    UnpadHeader* hdr = reinterpret_cast<UnpadHeader*>(ws);
+    int* super_counts = reinterpret_cast<int*>(ws + sizeof(UnpadHeader));
+    int* tile_counts = reinterpret_cast<int*>(ws + sizeof(UnpadHeader) + sup_bytes);
+    unsigned int* bits = reinterpret_cast<unsigned int*>(ws + sizeof(UnpadHeader) + sup_bytes + cnt_bytes);
+    VPG_CUDA(cudaMemsetAsync(ws, 0, sizeof(UnpadHeader) + sup_bytes, stream));  // header + super-counts
+    VPG_CUDA(cudaMemsetAsync(seqlens, 0, static_cast<size_t>(B) * sizeof(int), stream));
+    VPG_DISPATCH_MASK(mask_dtype, MT, {
+        // one block per SM ring budget: as many resident blocks as the staging rings allow (<= 4 per SM); every warp
+        // owns a contiguous run of tiles
+        const size_t smem = static_cast<size_t>(kWarps) * kStages * kChunk * sizeof(MT);
+        VPG_CUDA(cudaFuncSetAttribute(unpad_count_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));  // per device, cheap: set on every call
+        int per_sm = static_cast<int>(200 * 1024 / (smem + 1024));
+        per_sm = per_sm < 1 ? 1 : per_sm > 4 ? 4 : per_sm;
+        const int max_warps = sm_count() * per_sm * kWarps;
+        const int tiles_per_warp = static_cast<int>(ceil_div(static_cast<int64_t>(tiles), max_warps));
+        const int blocks = static_cast<int>(ceil_div(ceil_div(static_cast<int64_t>(tiles), tiles_per_warp), kWarps));
+        unpad_count_kernel<MT><<<blocks, kTileThreads, smem, stream>>>(
+            static_cast<const MT*>(mask), static_cast<unsigned int>(n), static_cast<unsigned int>(S), tiles,
+            tiles_per_warp, tile_counts, super_counts, bits, seqlens);
+        count_launch();
+    });
+    const int extra = static_cast<int>(ceil_div(B, static_cast<int64_t>(kRowsPerBlock)));
+    unpad_write_kernel<<<tiles + extra, kTileThreads, 0, stream>>>(bits, tile_counts, super_counts, tiles,
+                                                                  reinterpret_cast<long long*>(indices), seqlens,
+                                                                  static_cast<int>(B), cu_seqlens, totals, hdr);
+    count_launch();
     VPG_CUDA(cudaGetLastError());
     return VPG_OK;
 }
