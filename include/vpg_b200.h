@@ -30,6 +30,10 @@ extern "C" {
 #define VPG_ERR_UNSUPPORTED (-4)
 
 /* mask / value element types */
+/* 16-bit operand type of the lm-head kernels (*_dt entry points) */
+#define VPG_DT_BF16 0
+#define VPG_DT_F16 1
+
 #define VPG_MASK_I64 0
 #define VPG_MASK_I32 1
 #define VPG_MASK_U8 2
@@ -92,6 +96,11 @@ int vpg_lce_fwd_partials(const void* hidden_bf16, const void* weight_bf16, const
                          float* partials /* [4][num_splits][T] */, void* stream);
 int vpg_lce_finalize(const float* partials /* [4][num_parts][T] */, int num_parts, int64_t T, float temperature,
                      float* logprobs, float* entropy, float* lse, float* eb, void* stream);
+/* Same as vpg_lce_fwd_partials for 16-bit operands of type `dtype` (VPG_DT_BF16 | VPG_DT_F16): the reference kernel
+ * takes hidden / weight in any float dtype (kernels.py:485-490); bf16 and fp16 run on tcgen05 kind::f16 unchanged. */
+int vpg_lce_fwd_partials_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
+                            int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                            float* partials /* [4][num_splits][T] */, void* stream);
 
 /* Vocab-parallel "push" variant of stage 1 — replaces the exchange of verl/utils/kernel/kernels.py:609-661 (all_reduce
  * MAX + SUM + SUM of per-token partials).  The GEMM epilogue writes this rank's partials straight into the GATHERED
@@ -121,6 +130,12 @@ int vpg_lce_bwd(const void* hidden_bf16, const void* weight_bf16, const int64_t*
                 const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
                 float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden_bf16, void* d_weight_bf16,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* Same as vpg_lce_bwd for 16-bit operands of type `dtype`: the dlogits workspace, d_hidden and d_weight are written in
+ * that type (the reference returns gradients in hidden.dtype, kernels.py:1393-1394). */
+int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, const float* lse,
+                   const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
+                   float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight,
+                   void* workspace, size_t workspace_bytes, void* stream);
 
 /* Vocab-parallel backward with the d_hidden all-reduce fused into the d_hidden GEMM (the reference leaves this
  * all-reduce to the caller: tests/utils/test_linear_cross_entropy_tp.py:313-314).  d_hidden_mc_f32 is an NVSwitch

@@ -211,6 +211,84 @@ def test_full_size_properties(dev):
     torch.testing.assert_close(dh_c.float(), 2 * dh_a.float() + dh_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
 
 
+@pytest.mark.parametrize("name,Tn,H,V,world", [
+    ("configs[3] Llama-3-70B, 8-way shard", 65536, 8192, 128256, 8),
+    ("configs[4] Qwen2.5-32B DAPO micro-batch, 8-way shard", 262144, 5120, 152064, 8),
+])
+def test_full_size_vocab_shard_shapes(name, Tn, H, V, world, dev):
+    """BASELINE configs[3] / configs[4] at full size, one rank's shard of the vocab-parallel path (V/8 = 16032 and
+    19008 columns: neither is a multiple of the 256-column tile, so the masked vocab tail runs at full size).  The
+    other ranks' partials are replaced by the exact fp32 statistics of a row sample, so the merged result must equal
+    the full-vocab fp32 reference on those rows."""
+    from verl_b200 import ops
+
+    v_local = V // world
+    rank = 5
+    g = torch.Generator(device=dev).manual_seed(11)
+    hidden = (torch.rand(Tn, H, device=dev, generator=g) - 0.5).bfloat16()
+    w_local = (torch.rand(v_local, H, device=dev, generator=g) - 0.5).bfloat16()
+    labels = torch.randint(0, V, (Tn,), device=dev, generator=g)
+    part = ops.lce_forward_partials(hidden, w_local, labels, 1.0, label_offset=rank * v_local)  # [4, S, T]
+    assert torch.isfinite(part).all()
+    lp, ent, lse, eb = ops.lce_finalize(part, 1.0)  # as if this shard were the whole vocabulary
+    in_shard = (labels >= rank * v_local) & (labels < (rank + 1) * v_local)
+    assert (ent >= -1e-3).all() and (ent <= np.log(v_local) + 1e-3).all()
+    assert (lp[in_shard] <= 1e-4).all()
+    rows = torch.randperm(Tn, device=dev, generator=g)[:384]
+    logits = hidden[rows].float() @ w_local.float().t()
+    lse_r = torch.logsumexp(logits, -1)
+    p = torch.softmax(logits, -1)
+    torch.testing.assert_close(lse[rows], lse_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent[rows], lse_r - (p * logits).sum(-1), atol=LP_ATOL, rtol=0)
+    hit = in_shard[rows]
+    tgt = logits.gather(-1, (labels[rows] - rank * v_local).clamp(0, v_local - 1)[:, None]).squeeze(-1)
+    torch.testing.assert_close(lp[rows][hit], (tgt - lse_r)[hit], atol=LP_ATOL, rtol=0)
+    del logits, p
+    # backward on a 2048-token slice at full H and shard width: linearity in (g_lp, g_ent), d_weight rows of labels
+    sl = slice(0, 2048)
+    h, lab = hidden[sl].contiguous(), labels[sl].contiguous()
+    g1 = torch.rand(2048, device=dev, generator=g) * 2 - 1
+    g2 = torch.rand(2048, device=dev, generator=g) - 0.5
+    args = (h, w_local, lab, lse[sl].contiguous(), eb[sl].contiguous())
+    dh_a, dw_a = ops.lce_backward(*args, g1, None, 1.0, label_offset=rank * v_local)
+    dh_b, dw_b = ops.lce_backward(*args, None, g2, 1.0, label_offset=rank * v_local)
+    dh_c, dw_c = ops.lce_backward(*args, 2 * g1, g2, 1.0, label_offset=rank * v_local)
+    torch.testing.assert_close(dh_c.float(), 2 * dh_a.float() + dh_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(dw_c.float(), 2 * dw_a.float() + dw_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+
+
+def test_fp16_operands(dev):
+    """fp16 hidden / weight (the reference kernel takes any float dtype, verl/utils/kernel/kernels.py:485-490): same
+    tcgen05 kind::f16 path with the fp16 operand format; gradients come back in fp16 (kernels.py:1393-1394).
+    Multi-chunk backward so that the fp32 d_hidden accumulation and the fp16 conversions of the last chunk run."""
+    from verl_b200.utils.kernel import kernels
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    Tn, H, V, temp = 777, 384, 3000, 1.5
+    g = torch.Generator(device="cpu").manual_seed(3)
+    hidden = ((torch.rand(Tn, H, generator=g) - 0.5)).half().to(dev).requires_grad_(True)
+    weight = ((torch.rand(V, H, generator=g) - 0.5)).half().to(dev).requires_grad_(True)
+    labels = torch.randint(0, V, (Tn,), generator=g).to(dev)
+    g_lp = (torch.rand(Tn, generator=g) * 2 - 1).to(dev)
+    g_ent = (torch.rand(Tn, generator=g) - 0.5).to(dev)
+    lp_r, ent_r, dh_r, dw_r = _gpu_fp32_reference(hidden.detach(), weight.detach(), labels, temp, g_lp, g_ent)
+    kernels.set_backward_chunk(1024)
+    try:
+        lp, ent = linear_cross_entropy(hidden, weight, labels, temp, "none")
+        (lp * g_lp + ent * g_ent).sum().backward()
+    finally:
+        kernels.set_backward_chunk(0)
+    assert lp.dtype == torch.float32 and hidden.grad.dtype == torch.float16 and weight.grad.dtype == torch.float16
+    torch.testing.assert_close(lp, lp_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent, ent_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(hidden.grad.float(), dh_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(weight.grad.float(), dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    with pytest.raises((AssertionError, TypeError)):
+        linear_cross_entropy(hidden.float(), weight.float(), labels, temp, "none")
+    with pytest.raises((AssertionError, TypeError)):
+        linear_cross_entropy(hidden.detach().bfloat16(), weight, labels, temp, "none")
+
+
 def test_gemm_all_majors(dev):
     from verl_b200 import ops
 

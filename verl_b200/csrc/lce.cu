@@ -44,6 +44,15 @@ static void bind_primary_context() {
     }
 }
 
+// 16-bit type of the operands (and 16-bit outputs) of the launches made by the current host call: set by the *_dt
+// entry points for the duration of the call (the plain entry points are bf16)
+static thread_local int tl_operand_f16 = 0;
+struct OperandDtypeScope {
+    int prev;
+    explicit OperandDtypeScope(int dtype) : prev(tl_operand_f16) { tl_operand_f16 = (dtype == VPG_DT_F16) ? 1 : 0; }
+    ~OperandDtypeScope() { tl_operand_f16 = prev; }
+};
+
 static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
                      int box_outer) {
     EncodeTiledFn fn = get_encode_fn();
@@ -55,7 +64,7 @@ static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t o
     cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+    CUresult r = fn(tm, tl_operand_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
@@ -95,6 +104,7 @@ template <int kMode, bool kAMn, bool kBMn, int kCG>
 static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
     auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG>;
     TcParams p = p_in;
+    p.f16 = tl_operand_f16;
     p.sync_slack = env_int("VPG_SYNC_SLACK", 2);
     p.sync_epoch = next_epoch();
     if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
@@ -234,6 +244,25 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
                          void* stream) {
     return vpg_lce_fwd_partials_push(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
                                      0, num_splits, 0, nullptr, 0, stream);
+}
+
+int vpg_lce_fwd_partials_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
+                            int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                            float* partials, void* stream) {
+    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16, "operand dtype must be VPG_DT_BF16 or VPG_DT_F16");
+    OperandDtypeScope scope(dtype);
+    return vpg_lce_fwd_partials(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
+                                stream);
+}
+
+int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, const float* lse,
+                   const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
+                   float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight,
+                   void* workspace, size_t workspace_bytes, void* stream) {
+    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16, "operand dtype must be VPG_DT_BF16 or VPG_DT_F16");
+    OperandDtypeScope scope(dtype);
+    return vpg_lce_bwd(hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset, chunk_v,
+                       d_hidden, d_weight, workspace, workspace_bytes, stream);
 }
 
 int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,

@@ -18,6 +18,7 @@
 // keep per-row softmax state in registers across the n tiles of a unit; the plain GEMM uses 1 tile per unit.
 #pragma once
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 #include "ptx.cuh"
 
@@ -106,6 +107,7 @@ struct TcParams {
     int hint_a, hint_b;  // L2 eviction priority of the A / B operand loads: 0 normal, 1 evict-first, 2 evict-last
     int worker_perm;  // 0/1: identity; S > 1: group physical neighbours on residues mod S (see kernel)
     float* accum;  // OUT_F32_ACC: same as out; OUT_BF16_FROM_ACC: fp32 partial to add
+    int f16;       // 1: the 16-bit operands AND 16-bit outputs (OUT_BF16*, ds) are IEEE fp16 instead of bf16
     long long ld_accum;
 };
 
@@ -195,6 +197,17 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
+// two floats -> one 32-bit word of the launch's 16-bit type (round to nearest even); `f16` is uniform over the grid
+__device__ __forceinline__ uint32_t pack_16x2(float lo, float hi, int f16) {
+    if (f16) {
+        __half2 v = __floats2half2_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+    return pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ unsigned short cvt_16(float x, int f16) {
+    return f16 ? __half_as_ushort(__float2half_rn(x)) : __bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
 
 struct DsRow {
     float lse2;  // lse * log2(e)
@@ -205,7 +218,7 @@ struct DsRow {
 
 // dlogits chunk: d = -p*(a + b*x) (+ glp at the label column), zero for columns >= n_valid
 __device__ __forceinline__ void ds_chunk(const DsRow& rw, const uint32_t (&r)[32], float c, int lab_rel, int n_valid,
-                                         __nv_bfloat16* dst) {
+                                         __nv_bfloat16* dst, int f16) {
     float d[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -228,10 +241,10 @@ __device__ __forceinline__ void ds_chunk(const DsRow& rw, const uint32_t (&r)[32
 #pragma unroll
     for (int q4 = 0; q4 < 4; ++q4) {
         uint4 v;
-        v.x = pack_bf16x2(d[q4 * 8 + 0], d[q4 * 8 + 1]);
-        v.y = pack_bf16x2(d[q4 * 8 + 2], d[q4 * 8 + 3]);
-        v.z = pack_bf16x2(d[q4 * 8 + 4], d[q4 * 8 + 5]);
-        v.w = pack_bf16x2(d[q4 * 8 + 6], d[q4 * 8 + 7]);
+        v.x = pack_16x2(d[q4 * 8 + 0], d[q4 * 8 + 1], f16);
+        v.y = pack_16x2(d[q4 * 8 + 2], d[q4 * 8 + 3], f16);
+        v.z = pack_16x2(d[q4 * 8 + 4], d[q4 * 8 + 5], f16);
+        v.w = pack_16x2(d[q4 * 8 + 6], d[q4 * 8 + 7], f16);
         o[q4] = v;
     }
 }
@@ -266,16 +279,16 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
                 uint4 v;
-                v.x = pack_bf16x2(d[q4 * 8 + 0], d[q4 * 8 + 1]);
-                v.y = pack_bf16x2(d[q4 * 8 + 2], d[q4 * 8 + 3]);
-                v.z = pack_bf16x2(d[q4 * 8 + 4], d[q4 * 8 + 5]);
-                v.w = pack_bf16x2(d[q4 * 8 + 6], d[q4 * 8 + 7]);
+                v.x = pack_16x2(d[q4 * 8 + 0], d[q4 * 8 + 1], p.f16);
+                v.y = pack_16x2(d[q4 * 8 + 2], d[q4 * 8 + 3], p.f16);
+                v.z = pack_16x2(d[q4 * 8 + 4], d[q4 * 8 + 5], p.f16);
+                v.w = pack_16x2(d[q4 * 8 + 6], d[q4 * 8 + 7], p.f16);
                 o4[q4] = v;
             }
         } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-                if (j < n_valid) o[j] = __float2bfloat16_rn(d[j]);
+                if (j < n_valid) reinterpret_cast<unsigned short*>(o)[j] = cvt_16(d[j], p.f16);
         }
     } else {
         float* o = reinterpret_cast<float*>(p.out) + row * p.ldc + col;
@@ -522,7 +535,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             st_relaxed_u32(&g_progress[worker], epoch | 0xFFFFFu);  // done: never hold anybody back
     } else if (warp == kMmaWarp && is_leader) {
         // ===================================================================== MMA issuer (leader CTA)
-        constexpr uint32_t idesc = make_idesc_bf16(kBlockM * kCG, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u);
+        // kind::f16 takes bf16 (format 1) or fp16 (format 0) operands: clear the A / B format bits for fp16 launches
+        const uint32_t idesc = make_idesc_bf16(kBlockM * kCG, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u) &
+                               (p.f16 ? ~((1u << 7) | (1u << 10)) : ~0u);
         int stage = 0;
         uint32_t phase = 0;
         uint32_t acc_iter = 0;
@@ -639,7 +654,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             if (n_valid >= 32) fwd_chunk<false>(st, ra, c, lab - cb, 32);
                             else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
-                            ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                            ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, ra, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
@@ -655,7 +670,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             if (n_valid >= 32) fwd_chunk<false>(st, rb, c, lab - cb, 32);
                             else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
-                            ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb);
+                            ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, rb, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {

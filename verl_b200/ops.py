@@ -53,9 +53,21 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
     S = num_splits or lce_num_splits(T, H, V)
     part = torch.empty((4, S, T), dtype=_F32, device=hidden.device)
     with torch.cuda.device(hidden.device):
-        check(_lib_().vpg_lce_fwd_partials(ptr(hidden), ptr(weight), ptr(labels), T, H, V, float(temperature),
-                                           int(label_offset), S, ptr(part), stream_ptr(hidden.device)))
+        check(_lib_().vpg_lce_fwd_partials_dt(operand_dtype(hidden, weight), ptr(hidden), ptr(weight), ptr(labels), T,
+                                              H, V, float(temperature), int(label_offset), S, ptr(part),
+                                              stream_ptr(hidden.device)))
     return part
+
+
+def operand_dtype(hidden, weight) -> int:
+    """VPG_DT_* of the lm-head operands: bf16 or fp16, both tensors alike (tcgen05 kind::f16)."""
+    if hidden.dtype != weight.dtype:
+        raise TypeError(f"hidden ({hidden.dtype}) and weight ({weight.dtype}) must have the same dtype")
+    if hidden.dtype == torch.bfloat16:
+        return 0
+    if hidden.dtype == torch.float16:
+        return 1
+    raise TypeError(f"the sm_100a lm-head kernels take bf16 or fp16 operands, got {hidden.dtype}")
 
 
 def lce_forward_partials_push(hidden, weight, labels, temperature: float, label_offset: int, num_splits: int,
@@ -128,7 +140,7 @@ def lce_finalize(partials, temperature: float):
 
 def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int = 0,
                  chunk_v: int = 0):
-    """-> (d_hidden bf16 [T,H], d_weight bf16 [V,H])."""
+    """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (bf16 or fp16)."""
     _require_cuda(hidden, weight, labels, lse, eb)
     T, H = hidden.shape
     V = weight.shape[0]
@@ -138,9 +150,9 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
     d_hidden = torch.empty_like(hidden)
     d_weight = torch.empty_like(weight)
     with torch.cuda.device(hidden.device):
-        check(lib.vpg_lce_bwd(ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb), ptr(g_lp), ptr(g_ent), T, H, V,
-                              float(temperature), int(label_offset), int(chunk_v), ptr(d_hidden), ptr(d_weight),
-                              ptr(ws), nbytes, stream_ptr(hidden.device)))
+        check(lib.vpg_lce_bwd_dt(operand_dtype(hidden, weight), ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb),
+                                 ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset), int(chunk_v),
+                                 ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes, stream_ptr(hidden.device)))
     return d_hidden, d_weight
 
 

@@ -126,7 +126,8 @@ def _check_inputs(hidden, weight, labels):
     assert hidden.is_contiguous() and weight.is_contiguous() and labels.is_contiguous()
     assert hidden.shape[0] == labels.shape[0] and hidden.shape[1] == weight.shape[1]
     assert hidden.shape[1] % 64 == 0  # the reference asks for % 128 (kernels.py:504); one 128-byte TMA row here
-    assert hidden.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16, "the sm_100a kernels take bf16 operands"
+    assert hidden.dtype == weight.dtype and hidden.dtype in (torch.bfloat16, torch.float16), (
+        "the sm_100a kernels take bf16 or fp16 operands (tcgen05 kind::f16); fp32 operands are not supported")
     assert labels.dtype == torch.int64
 
 
@@ -159,7 +160,7 @@ def efficient_entropy_forward(
     world = 1 if dist_process_group is None else dist.get_world_size(dist_process_group)
     vocab_local = weight.shape[0]
 
-    if world > 1 and _config._tp_exchange == "nvlink":
+    if world > 1 and _config._tp_exchange == "nvlink" and hidden.dtype == torch.bfloat16:  # push kernels: bf16 only
         # fused GEMM + all-gather: every rank's epilogue pushes its partials into all gathered buffers over NVLink
         T, H = hidden.shape
         S = ops.lce_num_splits(T, H, vocab_local)
@@ -228,7 +229,7 @@ def efficient_entropy_backward(
     world = 1 if dist_process_group is None else dist.get_world_size(dist_process_group)
     fused_reduce = False
     if (world > 1 and _config._tp_reduce_d_hidden and _config._tp_reduce_mode == "multimem"
-            and _config._tp_exchange == "nvlink"):
+            and _config._tp_exchange == "nvlink" and hidden.dtype == torch.bfloat16):
         px = _peer_workspace(dist_process_group, hidden.device)
         accum, accum_mc = px.d_hidden_accum(hidden.shape[0], hidden.shape[1])
         fused_reduce = accum_mc != 0
