@@ -33,6 +33,7 @@ extern "C" {
 /* 16-bit operand type of the lm-head kernels (*_dt entry points) */
 #define VPG_DT_BF16 0
 #define VPG_DT_F16 1
+#define VPG_DT_F32 2 /* fp32 operands multiplied as TF32 (the reference's tl.dot on fp32 inputs does the same) */
 
 #define VPG_MASK_I64 0
 #define VPG_MASK_I32 1
@@ -96,8 +97,9 @@ int vpg_lce_fwd_partials(const void* hidden_bf16, const void* weight_bf16, const
                          float* partials /* [4][num_splits][T] */, void* stream);
 int vpg_lce_finalize(const float* partials /* [4][num_parts][T] */, int num_parts, int64_t T, float temperature,
                      float* logprobs, float* entropy, float* lse, float* eb, void* stream);
-/* Same as vpg_lce_fwd_partials for 16-bit operands of type `dtype` (VPG_DT_BF16 | VPG_DT_F16): the reference kernel
- * takes hidden / weight in any float dtype (kernels.py:485-490); bf16 and fp16 run on tcgen05 kind::f16 unchanged. */
+/* Same as vpg_lce_fwd_partials for operands of type `dtype` (VPG_DT_BF16 | VPG_DT_F16 | VPG_DT_F32): the reference
+ * kernel takes hidden / weight in any float dtype (kernels.py:485-490); bf16 and fp16 run on tcgen05 kind::f16, fp32 on
+ * kind::tf32 (half the tensor rate). */
 int vpg_lce_fwd_partials_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
                             int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
                             float* partials /* [4][num_splits][T] */, void* stream);
@@ -136,6 +138,14 @@ int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int6
                    const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
                    float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight,
                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* fp32 operands: the logits recompute runs as TF32 on the fp32 operands (consistent with the forward), dlogits are
+ * bf16, and the two gradient GEMMs read bf16 copies of hidden / weight supplied by the caller; d_hidden [T,H] and
+ * d_weight [V,H] are written in fp32. */
+int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* hidden_bf16, const void* weight_bf16,
+                    const int64_t* labels, const float* lse, const float* eb, const float* g_lp, const float* g_ent,
+                    int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
+                    void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Vocab-parallel backward with the d_hidden all-reduce fused into the d_hidden GEMM (the reference leaves this
  * all-reduce to the caller: tests/utils/test_linear_cross_entropy_tp.py:313-314).  d_hidden_mc_f32 is an NVSwitch

@@ -35,6 +35,11 @@ SIGNATURES: dict[str, tuple] = {
         [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64,
          c_float, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "vpg_lce_bwd_f32": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64,
+         c_int64, c_float, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
     "vpg_lce_fwd_partials_push": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_int, c_int,

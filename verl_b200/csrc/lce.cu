@@ -46,25 +46,32 @@ static void bind_primary_context() {
 
 // 16-bit type of the operands (and 16-bit outputs) of the launches made by the current host call: set by the *_dt
 // entry points for the duration of the call (the plain entry points are bf16)
-static thread_local int tl_operand_f16 = 0;
+static thread_local int tl_operand_dt = VPG_DT_BF16;
+// fp32 operands (VPG_DT_F32): the two gradient GEMMs of the backward run on 16-bit copies supplied by the caller
+static thread_local const void* tl_hidden16 = nullptr;
+static thread_local const void* tl_weight16 = nullptr;
 struct OperandDtypeScope {
     int prev;
-    explicit OperandDtypeScope(int dtype) : prev(tl_operand_f16) { tl_operand_f16 = (dtype == VPG_DT_F16) ? 1 : 0; }
-    ~OperandDtypeScope() { tl_operand_f16 = prev; }
+    explicit OperandDtypeScope(int dtype) : prev(tl_operand_dt) { tl_operand_dt = dtype; }
+    ~OperandDtypeScope() { tl_operand_dt = prev; }
 };
 
 static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
-                     int box_outer) {
+                     int box_outer, int dt) {
+    const int esz = (dt == VPG_DT_F32) ? 4 : 2;
     EncodeTiledFn fn = get_encode_fn();
     bind_primary_context();
     if (!fn) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld * 2) % 16 != 0)
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld * esz) % 16 != 0)
         return set_error(VPG_ERR_INVALID, "TMA operand must be 16-byte aligned with a 16-byte-multiple row stride");
     cuuint64_t dims[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
-    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * esz};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(tm, tl_operand_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+    const CUtensorMapDataType ty = dt == VPG_DT_F32   ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32  // rounds to TF32 on the way in (no truncation bias)
+                                   : dt == VPG_DT_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                      : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    CUresult r = fn(tm, ty, 2, const_cast<void*>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
@@ -73,9 +80,10 @@ static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t o
 
 // K-major operand stored [rows][K]; MN-major operand stored [K][rows]
 static int make_operand_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int64_t ld, bool mn_major,
-                             int tile_rows) {
-    if (!mn_major) return make_tmap(tm, base, K, rows, ld, kBlockK, tile_rows);
-    return make_tmap(tm, base, rows, K, ld, 64, kBlockK);
+                             int tile_rows, int dt = VPG_DT_BF16) {
+    if (!mn_major) return make_tmap(tm, base, K, rows, ld, dt == VPG_DT_F32 ? kBlockK / 2 : kBlockK, tile_rows, dt);
+    if (dt == VPG_DT_F32) return set_error(VPG_ERR_UNSUPPORTED, "fp32 (TF32) operands must be K-major");
+    return make_tmap(tm, base, rows, K, ld, 64, kBlockK, dt);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -100,11 +108,10 @@ static int tile_m() { return kBlockM * cta_group(); }
 static int num_workers() { return cta_group() == 2 ? sm_count() / 2 : sm_count(); }
 static int b_tile_rows() { return kBlockN / cta_group(); }
 
-template <int kMode, bool kAMn, bool kBMn, int kCG>
+template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
 static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
-    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG>;
+    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG, kTf32>;
     TcParams p = p_in;
-    p.f16 = tl_operand_f16;
     p.sync_slack = env_int("VPG_SYNC_SLACK", 2);
     p.sync_epoch = next_epoch();
     if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
@@ -142,6 +149,14 @@ template <int kMode, bool kAMn, bool kBMn>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
     if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream);
     return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream);
+}
+// lm-head statistics / dlogits launches in the operand type `dt` of the call: bf16 / fp16 (kind::f16) or fp32 (TF32)
+template <int kMode>
+static int launch_tc_lmhead(const CUtensorMap& ta, const CUtensorMap& tb, TcParams p, int dt, cudaStream_t stream) {
+    p.f16 = (dt == VPG_DT_F16);
+    if (dt != VPG_DT_F32) return launch_tc<kMode, false, false>(ta, tb, p, stream);
+    if (cta_group() == 2) return launch_tc_cg<kMode, false, false, 2, true>(ta, tb, p, stream);
+    return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream);
 }
 
 // balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
@@ -249,7 +264,7 @@ int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* 
 int vpg_lce_fwd_partials_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
                             int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
                             float* partials, void* stream) {
-    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16, "operand dtype must be VPG_DT_BF16 or VPG_DT_F16");
+    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16 || dtype == VPG_DT_F32, "unknown operand dtype %d", dtype);
     OperandDtypeScope scope(dtype);
     return vpg_lce_fwd_partials(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
                                 stream);
@@ -263,6 +278,19 @@ int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int6
     OperandDtypeScope scope(dtype);
     return vpg_lce_bwd(hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset, chunk_v,
                        d_hidden, d_weight, workspace, workspace_bytes, stream);
+}
+
+int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* hidden_bf16, const void* weight_bf16,
+                    const int64_t* labels, const float* lse, const float* eb, const float* g_lp, const float* g_ent,
+                    int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
+                    void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream) {
+    VPG_CHECK_ARG(hidden_bf16 && weight_bf16, "fp32 backward needs the bf16 copies of hidden and weight");
+    OperandDtypeScope scope(VPG_DT_F32);
+    tl_hidden16 = hidden_bf16, tl_weight16 = weight_bf16;
+    const int rc = vpg_lce_bwd(hidden_f32, weight_f32, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset,
+                               chunk_v, d_hidden_f32, d_weight_f32, workspace, workspace_bytes, stream);
+    tl_hidden16 = tl_weight16 = nullptr;
+    return rc;
 }
 
 int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
@@ -282,7 +310,10 @@ int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int6
     TcParams p{};
     p.num_m_tiles = static_cast<int>(ceil_div(T, tile_m()));
     p.num_n_tiles = static_cast<int>(ceil_div(V, kBlockN));
-    p.num_k_blocks = static_cast<int>(H / kBlockK);
+    const int dt = tl_operand_dt;
+    VPG_CHECK_ARG(dt == VPG_DT_BF16 || (n_push == 0 && !partials_is_multicast),
+                  "the push variants take bf16 operands only");
+    p.num_k_blocks = static_cast<int>(H / (dt == VPG_DT_F32 ? kBlockK / 2 : kBlockK));
     VPG_CHECK_ARG(num_splits >= 1 && num_splits <= p.num_n_tiles, "num_splits %d out of range [1,%d]", num_splits,
                   p.num_n_tiles);
     p.num_splits = num_splits;
@@ -305,9 +336,9 @@ int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int6
     p.worker_perm = env_int("VPG_WORKER_PERM", 0) ? num_splits : 0;
     if (const char* e = getenv("VPG_DEBUG_TRACE_PTR")) p.debug_trace = reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0));
     CUtensorMap ta, tb;
-    if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
-    if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, b_tile_rows()))) return rc;
-    return launch_tc<MODE_FWD, false, false>(ta, tb, p, static_cast<cudaStream_t>(stream));
+    if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM, dt))) return rc;
+    if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, b_tile_rows(), dt))) return rc;
+    return launch_tc_lmhead<MODE_FWD>(ta, tb, p, dt, static_cast<cudaStream_t>(stream));
 }
 
 int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temperature, float* logprobs,
@@ -384,8 +415,18 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
                   "null pointer argument");
     VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    // operand type of the call.  fp32: the recompute runs as TF32 on the fp32 operands like the forward, dlogits are
+    // bf16, the two gradient GEMMs read the caller's bf16 copies and write fp32 gradients.
+    const int dt = tl_operand_dt;
+    const bool f32 = (dt == VPG_DT_F32);
+    const int dt16 = f32 ? VPG_DT_BF16 : dt;
+    const void* hidden16 = f32 ? tl_hidden16 : hidden;
+    const void* weight16 = f32 ? tl_weight16 : weight;
+    const int64_t gsz = f32 ? 4 : 2;  // bytes per gradient element
+    VPG_CHECK_ARG(!f32 || (hidden16 && weight16 && !d_hidden_mc_f32), "fp32 operands: use vpg_lce_bwd_f32");
+    VPG_CHECK_ARG(dt == VPG_DT_BF16 || !d_hidden_mc_f32, "the fused d_hidden all-reduce takes bf16 operands only");
     if (T == 0) {
-        VPG_CUDA(cudaMemsetAsync(d_weight, 0, static_cast<size_t>(V) * H * 2, stream));
+        VPG_CUDA(cudaMemsetAsync(d_weight, 0, static_cast<size_t>(V) * H * gsz, stream));
         return VPG_OK;
     }
     if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
@@ -408,14 +449,15 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
     for (int ci = 0; ci < num_chunks; ++ci) {
         const int64_t v0 = static_cast<int64_t>(ci) * chunk_v;
         const int64_t vc = (V - v0) < chunk_v ? (V - v0) : chunk_v;
-        const __nv_bfloat16* w_chunk = reinterpret_cast<const __nv_bfloat16*>(weight) + v0 * H;
+        const uint8_t* w_chunk = reinterpret_cast<const uint8_t*>(weight) + v0 * H * (f32 ? 4 : 2);
+        const __nv_bfloat16* w16_chunk = reinterpret_cast<const __nv_bfloat16*>(weight16) + v0 * H;
         const int n_tiles_c = static_cast<int>(ceil_div(vc, kBlockN));
         CUtensorMap ta, tb;
         {  // 1. recompute logits tile -> dlogits chunk (bf16)
             TcParams p{};
             p.num_m_tiles = m_tiles_t;
             p.num_n_tiles = n_tiles_c;
-            p.num_k_blocks = static_cast<int>(H / kBlockK);
+            p.num_k_blocks = static_cast<int>(H / (f32 ? kBlockK / 2 : kBlockK));
             p.num_splits = choose_splits(m_tiles_t, n_tiles_c, num_workers());
             p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
             p.M = static_cast<int>(T);
@@ -430,9 +472,9 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.g_ent = g_ent;
             p.ds = ds;
             p.ldds = ldds;
-            if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM))) return rc;
-            if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, b_tile_rows()))) return rc;
-            if ((rc = launch_tc<MODE_DS, false, false>(ta, tb, p, stream))) return rc;
+            if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM, dt))) return rc;
+            if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, b_tile_rows(), dt))) return rc;
+            if ((rc = launch_tc_lmhead<MODE_DS>(ta, tb, p, dt, stream))) return rc;
         }
         const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
         {  // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
@@ -444,11 +486,12 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.tiles_per_split = 1;
             p.M = static_cast<int>(vc);
             p.N = static_cast<int>(H);
-            p.out = reinterpret_cast<__nv_bfloat16*>(d_weight) + v0 * H;
+            p.out = reinterpret_cast<uint8_t*>(d_weight) + v0 * H * gsz;
             p.ldc = H;
-            p.out_mode = OUT_BF16;
-            if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM))) return rc;
-            if ((rc = make_operand_tmap(&tb, hidden, H, T, H, true, kBlockN))) return rc;
+            p.out_mode = f32 ? OUT_F32 : OUT_BF16;
+            p.f16 = (dt16 == VPG_DT_F16);
+            if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM, dt16))) return rc;
+            if ((rc = make_operand_tmap(&tb, hidden16, H, T, H, true, kBlockN, dt16))) return rc;
             if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream))) return rc;
         }
         {  // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
@@ -466,6 +509,9 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
                 // into every rank's fp32 buffer through the multicast address, tile by tile
                 p.out = d_hidden_mc_f32, p.ldc = H, p.out_mode = OUT_F32_MCRED;
                 p.accum = (num_chunks > 1) ? dh_acc : nullptr, p.ld_accum = H;
+            } else if (f32) {  // fp32 gradients accumulate in place
+                p.out = d_hidden, p.ldc = H, p.out_mode = (ci == 0) ? OUT_F32 : OUT_F32_ACC;
+                p.accum = reinterpret_cast<float*>(d_hidden), p.ld_accum = H;
             } else if (num_chunks == 1) {
                 p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16;
             } else if (ci == 0) {
@@ -476,8 +522,9 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
                 p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16_FROM_ACC;
                 p.accum = dh_acc, p.ld_accum = H;
             }
-            if ((rc = make_operand_tmap(&ta, ds, t_pad, vc_cols, ldds, false, kBlockM))) return rc;
-            if ((rc = make_operand_tmap(&tb, w_chunk, H, vc, H, true, kBlockN))) return rc;
+            p.f16 = (dt16 == VPG_DT_F16);
+            if ((rc = make_operand_tmap(&ta, ds, t_pad, vc_cols, ldds, false, kBlockM, dt16))) return rc;
+            if ((rc = make_operand_tmap(&tb, w16_chunk, H, vc, H, true, kBlockN, dt16))) return rc;
             if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream))) return rc;
         }
     }

@@ -407,11 +407,15 @@ __device__ __forceinline__ bool pace_wait(int worker, int num_workers, uint32_t 
 //   K-major operand : one TMA box {64 (k), rows}            -> rows x 128 B, SBO = 1024 B, K step = +32 B
 //   MN-major operand: rows/64 TMA boxes {64 (mn), 64 (k)}   -> blocks of 64 k-rows x 128 B (8 KB),
 //                     LBO = 8192 B (next 64 mn), SBO = 1024 B (next 8 k), K step (16 rows) = +2048 B
-template <int kMode, bool kAMn, bool kBMn, int kCG>
+// kTf32: the operands are fp32, staged with the same 128-byte k-blocks (32 elements instead of 64) and multiplied as
+// TF32 (kind::tf32, 4 x K=8 per k-block instead of 4 x K=16) — K-major operands only (MODE_FWD / MODE_DS).
+template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const TcParams p) {
     using Cfg = TileCfg<kCG>;
+    static_assert(!kTf32 || (!kAMn && !kBMn), "TF32 operands are K-major only");
+    constexpr int kElemsK = kTf32 ? kBlockK / 2 : kBlockK;  // elements per 128-byte k-block row
     constexpr int kStages = Cfg::kStages;
     constexpr int kStageBytes = Cfg::kStageBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -491,14 +495,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         if (kCG == 1) {
                             mbar_arrive_expect_tx(&L.full[stage], kStageBytes);
                             if (!kAMn) {
-                                tma_load_2d_hint(&tmap_a, &L.full[stage], sa, kb * kBlockK, m0, hint_a);
+                                tma_load_2d_hint(&tmap_a, &L.full[stage], sa, kb * kElemsK, m0, hint_a);
                             } else {
 #pragma unroll
                                 for (int j = 0; j < kBlockM / 64; ++j)
                                     tma_load_2d_hint(&tmap_a, &L.full[stage], sa + j * 8192, m0 + j * 64, kb * kBlockK, hint_a);
                             }
                             if (!kBMn) {
-                                tma_load_2d_hint(&tmap_b, &L.full[stage], sb, kb * kBlockK, n0, hint_b);
+                                tma_load_2d_hint(&tmap_b, &L.full[stage], sb, kb * kElemsK, n0, hint_b);
                             } else {
 #pragma unroll
                                 for (int j = 0; j < Cfg::kBRows / 64; ++j)
@@ -508,14 +512,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             const uint32_t full_leader = mapa(smem_u32(&L.full[stage]), 0);
                             if (is_leader) mbar_arrive_expect_tx(&L.full[stage], 2 * kStageBytes);
                             if (!kAMn) {
-                                tma_load_2d_2sm_hint(&tmap_a, full_leader, sa, kb * kBlockK, m0, hint_a);
+                                tma_load_2d_2sm_hint(&tmap_a, full_leader, sa, kb * kElemsK, m0, hint_a);
                             } else {
 #pragma unroll
                                 for (int j = 0; j < kBlockM / 64; ++j)
                                     tma_load_2d_2sm_hint(&tmap_a, full_leader, sa + j * 8192, m0 + j * 64, kb * kBlockK, hint_a);
                             }
                             if (!kBMn) {
-                                tma_load_2d_2sm_hint(&tmap_b, full_leader, sb, kb * kBlockK, n0, hint_b);
+                                tma_load_2d_2sm_hint(&tmap_b, full_leader, sb, kb * kElemsK, n0, hint_b);
                             } else {
 #pragma unroll
                                 for (int j = 0; j < Cfg::kBRows / 64; ++j)
@@ -536,8 +540,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else if (warp == kMmaWarp && is_leader) {
         // ===================================================================== MMA issuer (leader CTA)
         // kind::f16 takes bf16 (format 1) or fp16 (format 0) operands: clear the A / B format bits for fp16 launches
-        const uint32_t idesc = make_idesc_bf16(kBlockM * kCG, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u) &
-                               (p.f16 ? ~((1u << 7) | (1u << 10)) : ~0u);
+        // kind::tf32: operand format 2 for A and B
+        const uint32_t idesc =
+            kTf32 ? ((make_idesc_bf16(kBlockM * kCG, kBlockN, 0u, 0u) & ~((7u << 7) | (7u << 10))) | (2u << 7) | (2u << 10))
+                  : (make_idesc_bf16(kBlockM * kCG, kBlockN, kAMn ? 1u : 0u, kBMn ? 1u : 0u) &
+                     (p.f16 ? ~((1u << 7) | (1u << 10)) : ~0u));
         int stage = 0;
         uint32_t phase = 0;
         uint32_t acc_iter = 0;
@@ -572,7 +579,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             // advance the 14-bit start-address field (units of 16 B)
                             const uint64_t a_adv = kAMn ? (k * 2048) >> 4 : (k * 32) >> 4;
                             const uint64_t b_adv = kBMn ? (k * 2048) >> 4 : (k * 32) >> 4;
-                            umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                            if constexpr (kTf32)
+                                umma_tf32<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                            else
+                                umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
                         }
                         // frees the smem slot (in both CTAs) once these MMAs retire
                         if (kCG == 1) umma_commit(&L.empty[stage]); else umma_commit_2sm(&L.empty[stage], 3);

@@ -60,14 +60,16 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
 
 
 def operand_dtype(hidden, weight) -> int:
-    """VPG_DT_* of the lm-head operands: bf16 or fp16, both tensors alike (tcgen05 kind::f16)."""
+    """VPG_DT_* of the lm-head operands, both tensors alike: bf16 / fp16 (tcgen05 kind::f16) or fp32 (kind::tf32)."""
     if hidden.dtype != weight.dtype:
         raise TypeError(f"hidden ({hidden.dtype}) and weight ({weight.dtype}) must have the same dtype")
     if hidden.dtype == torch.bfloat16:
         return 0
     if hidden.dtype == torch.float16:
         return 1
-    raise TypeError(f"the sm_100a lm-head kernels take bf16 or fp16 operands, got {hidden.dtype}")
+    if hidden.dtype == torch.float32:
+        return 2
+    raise TypeError(f"the sm_100a lm-head kernels take bf16, fp16 or fp32 operands, got {hidden.dtype}")
 
 
 def lce_forward_partials_push(hidden, weight, labels, temperature: float, label_offset: int, num_splits: int,
@@ -149,8 +151,17 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
     ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
     d_hidden = torch.empty_like(hidden)
     d_weight = torch.empty_like(weight)
+    dt = operand_dtype(hidden, weight)
+    if dt == 2:  # fp32: TF32 recompute on the fp32 operands, gradient GEMMs on bf16 copies, fp32 gradients
+        h16, w16 = hidden.to(torch.bfloat16), weight.to(torch.bfloat16)
+        with torch.cuda.device(hidden.device):
+            check(lib.vpg_lce_bwd_f32(ptr(hidden), ptr(weight), ptr(h16), ptr(w16), ptr(labels), ptr(lse), ptr(eb),
+                                      ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset),
+                                      int(chunk_v), ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes,
+                                      stream_ptr(hidden.device)))
+        return d_hidden, d_weight
     with torch.cuda.device(hidden.device):
-        check(lib.vpg_lce_bwd_dt(operand_dtype(hidden, weight), ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb),
+        check(lib.vpg_lce_bwd_dt(dt, ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb),
                                  ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset), int(chunk_v),
                                  ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes, stream_ptr(hidden.device)))
     return d_hidden, d_weight

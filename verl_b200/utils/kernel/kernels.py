@@ -126,8 +126,8 @@ def _check_inputs(hidden, weight, labels):
     assert hidden.is_contiguous() and weight.is_contiguous() and labels.is_contiguous()
     assert hidden.shape[0] == labels.shape[0] and hidden.shape[1] == weight.shape[1]
     assert hidden.shape[1] % 64 == 0  # the reference asks for % 128 (kernels.py:504); one 128-byte TMA row here
-    assert hidden.dtype == weight.dtype and hidden.dtype in (torch.bfloat16, torch.float16), (
-        "the sm_100a kernels take bf16 or fp16 operands (tcgen05 kind::f16); fp32 operands are not supported")
+    assert hidden.dtype == weight.dtype and hidden.dtype in (torch.bfloat16, torch.float16, torch.float32), (
+        "the sm_100a kernels take bf16 / fp16 (tcgen05 kind::f16) or fp32 (kind::tf32) operands, both alike")
     assert labels.dtype == torch.int64
 
 
