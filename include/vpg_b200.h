@@ -127,7 +127,11 @@ int vpg_lce_fwd_partials_push(const void* hidden_bf16, const void* weight_bf16, 
  * Workspace size: vpg_lce_bwd_workspace_bytes().  g_lp / g_ent may be NULL (treated as zeros).
  * d_hidden: bf16 [T,H]; d_weight: bf16 [V,H].  For vocab-parallel shards the caller all-reduces d_hidden. */
 size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v);
-int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V);
+int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V); /* budget: $VPG_BWD_WS_MB (default 4096) MiB */
+/* Largest chunk whose dlogits buffer fits `budget_bytes`, then the chunk count (up to +8) that wastes the fewest waves
+ * of the persistent grid.  Fewer chunks = fewer launches and fp32 d_hidden round trips: one 20 GB chunk at configs[1]
+ * is 2.5 % faster than seven 2.85 GB chunks. */
+int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t budget_bytes);
 int vpg_lce_bwd(const void* hidden_bf16, const void* weight_bf16, const int64_t* labels, const float* lse,
                 const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
                 float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden_bf16, void* d_weight_bf16,

@@ -51,6 +51,7 @@ SIGNATURES: dict[str, tuple] = {
     ),
     "vpg_lce_bwd_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64]),
     "vpg_lce_bwd_default_chunk": (c_int64, [c_int64, c_int64, c_int64]),
+    "vpg_lce_bwd_chunk_for_budget": (c_int64, [c_int64, c_int64, c_int64, c_int64]),
     "vpg_lce_bwd": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float,

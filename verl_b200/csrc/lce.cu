@@ -354,11 +354,15 @@ int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temp
 }
 
 int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
+    return vpg_lce_bwd_chunk_for_budget(T, H, V, static_cast<int64_t>(env_int("VPG_BWD_WS_MB", 4096)) << 20);
+}
+
+int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t budget) {
     // Largest chunk whose bf16 dlogits buffer fits the budget, then the chunk count (up to +8) that wastes the fewest
     // waves of the persistent grid in the three kernels of a chunk (cost in units of tile x k-block).
     const int64_t t_pad = round_up(T > 0 ? T : 1, 2 * kBlockM);
     const int64_t v_tiles = ceil_div(V, kBlockN);
-    const int64_t budget = static_cast<int64_t>(env_int("VPG_BWD_WS_MB", 4096)) << 20;  // bf16 dlogits workspace
+    if (budget < (1 << 20)) budget = 1 << 20;  // bytes of the 16-bit dlogits workspace
     int64_t max_tiles = budget / (t_pad * 2) / kBlockN;
     if (max_tiles < 1) max_tiles = 1;
     if (max_tiles > v_tiles) max_tiles = v_tiles;

@@ -59,6 +59,21 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
     return part
 
 
+def backward_chunk(T: int, H: int, V: int, device, chunk_v: int = 0) -> int:
+    """Vocab columns of dlogits materialised at a time by the backward.  An explicit ``chunk_v`` or $VPG_BWD_WS_MB wins;
+    otherwise the budget follows the memory that is free right now — a quarter of it, between 1 and 24 GiB — because
+    fewer chunks are faster (configs[1]: one 20 GB chunk 206 ms / step, seven 2.85 GB chunks 211.5 ms)."""
+    import os
+
+    if chunk_v and chunk_v > 0:
+        return int(chunk_v)
+    if os.environ.get("VPG_BWD_WS_MB"):
+        return 0  # the library default reads the variable
+    free, _total = torch.cuda.mem_get_info(device)
+    budget = min(max(free // 4, 1 << 30), 24 << 30)
+    return int(_lib_().vpg_lce_bwd_chunk_for_budget(T, H, V, int(budget)))
+
+
 def operand_dtype(hidden, weight) -> int:
     """VPG_DT_* of the lm-head operands, both tensors alike: bf16 / fp16 (tcgen05 kind::f16) or fp32 (kind::tf32)."""
     if hidden.dtype != weight.dtype:
@@ -110,6 +125,7 @@ def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature
     V = weight.shape[0]
     assert accum_local.shape == (T, H) and accum_local.dtype == _F32 and accum_multicast_ptr
     lib = _lib_()
+    chunk_v = backward_chunk(T, H, V, hidden.device, chunk_v)
     nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
     ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
     d_weight = torch.empty_like(weight)
@@ -147,6 +163,7 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
     T, H = hidden.shape
     V = weight.shape[0]
     lib = _lib_()
+    chunk_v = backward_chunk(T, H, V, hidden.device, chunk_v)
     nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
     ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
     d_hidden = torch.empty_like(hidden)
