@@ -253,6 +253,46 @@ def gen_cov(ref):
     np.savez_compressed(os.path.join(OUT, "cov.npz"), **out)
 
 
+def gen_pfppo(ref):
+    """compute_pf_ppo_reweight_data (core_algos.py:1072-1148), the unmodified reference function fed a DataProto
+    stand-in (a dict subclass carrying batch_size, numpy object arrays, meta_info); the multinomial draw is made
+    reproducible by seeding the host generator right before the call."""
+
+    class TD(dict):
+        batch_size = None
+
+    class Data:
+        pass
+
+    g = torch.Generator().manual_seed(77)
+    B, L = 24, 33
+    out = {}
+    scores = torch.zeros(B, L)
+    lens = torch.randint(1, L + 1, (B,), generator=g)
+    scores[torch.arange(B), lens - 1] = torch.randn(B, generator=g).round(decimals=1)  # ties in max / min on purpose
+    other = torch.randn(B, L, 3, generator=g)
+    ids = torch.randint(0, 1000, (B, L), generator=g)
+    uid = np.array([f"u{i // 4}" for i in range(B)], dtype=object)
+    out.update(token_level_scores=_np(scores), other=_np(other), ids=_np(ids))
+    for method, pw in (("pow", 2.0), ("pow", 0.5), ("max_min", 2.0), ("max_random", 2.0)):
+        d = Data()
+        d.batch = TD(token_level_scores=scores.clone(), other=other.clone(), ids=ids.clone())
+        d.batch.batch_size = [B]
+        d.non_tensor_batch = {"uid": uid.copy(), "as_list": list(range(B))}
+        d.meta_info = {"per_sample": list(range(100, 100 + B)), "scalar": 3, "short_list": [1, 2]}
+        torch.manual_seed(4321)
+        r = ref.core_algos.compute_pf_ppo_reweight_data(d, method, pw)
+        key = f"{method}|{pw}"
+        out[key + "|scores"] = _np(r.batch["token_level_scores"])
+        out[key + "|other"] = _np(r.batch["other"])
+        out[key + "|ids"] = _np(r.batch["ids"])
+        out[key + "|uid"] = np.array([str(u) for u in r.non_tensor_batch["uid"]])
+        out[key + "|as_list"] = np.array(r.non_tensor_batch["as_list"])
+        out[key + "|per_sample"] = np.array(r.meta_info["per_sample"])
+        assert r.meta_info["scalar"] == 3 and r.meta_info["short_list"] == [1, 2]
+    np.savez_compressed(os.path.join(OUT, "pfppo.npz"), **out)
+
+
 def gen_estimators(ref):
     """The other registered advantage estimators + value loss + GPG loss."""
     g = torch.Generator().manual_seed(29)
@@ -569,7 +609,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     only = set(sys.argv[1:])  # e.g. `python -m oracle.make_golden estimators` regenerates one fixture
-    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_cov, gen_estimators, gen_driver, gen_seqlen, gen_megatron, gen_rmpad):
+    for fn in (gen_lce, gen_logits, gen_masked, gen_grpo, gen_gae, gen_loss, gen_cov, gen_pfppo, gen_estimators, gen_driver, gen_seqlen, gen_megatron, gen_rmpad):
         if only and fn.__name__[4:] not in only:
             continue
         fn(ref)

@@ -707,3 +707,19 @@ def postprocess_packed_seqs(outputs_per_rank, attention_mask, tp_size=1, cp_size
         if seq:
             out[i, attention_mask[i].bool()] = torch.stack(seq)
     return out
+
+
+def pf_ppo_sample_indices(token_level_scores, reweight_method="pow", weight_pow=2.0):
+    """compute_pf_ppo_reweight_data's draw — verl/trainer/ppo/core_algos.py:1103-1121: importance weights from the row
+    sums of token_level_scores, then B indices drawn with replacement from the host generator."""
+    scores = token_level_scores.sum(dim=-1)
+    if reweight_method == "pow":
+        weights = torch.pow(torch.abs(scores), weight_pow)
+    elif reweight_method == "max_min":
+        weights = torch.where((scores == scores.max()) | (scores == scores.min()), 1.0, 0.0)
+    elif reweight_method == "max_random":
+        weights = torch.where(scores == scores.max(), 0.4, 0.1)
+    else:
+        raise ValueError(f"Unsupported reweight_method: {reweight_method}")
+    weights = torch.clamp(weights + 1e-8, min=1e-8)
+    return torch.multinomial(weights, scores.shape[0], replacement=True)

@@ -44,3 +44,17 @@ def test_cov_losses_golden(cname, mode):
     want = g[f"kl_cov|{cname}|{mode}|scalars"]
     np.testing.assert_allclose([loss.item(), ppo_kl_abs.item()], want, rtol=1e-6, atol=1e-7)
     torch.testing.assert_close(lp.grad, T(g[f"kl_cov|{cname}|{mode}|d_lp"]), rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("method,pw", [("pow", 2.0), ("pow", 0.5), ("max_min", 2.0), ("max_random", 2.0)])
+def test_pf_ppo_draw_golden(method, pw):
+    """compute_pf_ppo_reweight_data (core_algos.py:1072-1148): with the host generator seeded as the golden run was,
+    the oracle draws the same rows as the unmodified reference function."""
+    g = load_golden("pfppo")
+    scores = T(g["token_level_scores"])
+    torch.manual_seed(4321)
+    idx = port.pf_ppo_sample_indices(scores, method, pw)
+    key = f"{method}|{pw}"
+    assert torch.equal(scores[idx], T(g[key + "|scores"]))
+    assert torch.equal(T(g["other"])[idx], T(g[key + "|other"]))
+    assert np.array_equal(np.arange(100, 100 + scores.shape[0])[idx.numpy()], g[key + "|per_sample"])

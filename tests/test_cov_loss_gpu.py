@@ -122,3 +122,39 @@ def test_kl_cov_selection_count_and_ties(dev):
     # no valid token: nothing selected, loss matrix is the plain one
     _, _, out3 = ops.kl_cov_loss(old, lp, adv, torch.zeros_like(mask), 0.0002, 1.0)
     assert int(out3[1]) == 0
+
+
+@pytest.mark.parametrize("method,pw", [("pow", 2.0), ("pow", 0.5), ("max_min", 2.0), ("max_random", 2.0)])
+def test_pf_ppo_reweight_data_golden(method, pw):
+    """compute_pf_ppo_reweight_data on a DataProto stand-in with CUDA tensors: same resampled rows (every tensor, the
+    numpy / list side data, the per-sample meta lists) as the unmodified reference with the same host seed."""
+
+    class TD(dict):
+        batch_size = None
+
+    class Data:
+        pass
+
+    g = load_golden("pfppo")
+    dev = torch.device("cuda:0")
+    B = g["token_level_scores"].shape[0]
+    d = Data()
+    d.batch = TD(token_level_scores=T(g["token_level_scores"]).to(dev), other=T(g["other"]).to(dev),
+                 ids=T(g["ids"]).to(dev))
+    d.batch.batch_size = [B]
+    d.non_tensor_batch = {"uid": np.array([f"u{i // 4}" for i in range(B)], dtype=object), "as_list": list(range(B))}
+    d.meta_info = {"per_sample": list(range(100, 100 + B)), "scalar": 3, "short_list": [1, 2]}
+    torch.manual_seed(4321)
+    r = ca.compute_pf_ppo_reweight_data(d, method, pw)
+    key = f"{method}|{pw}"
+    assert isinstance(r.batch, TD) and r.batch.batch_size == [B] and r is not d
+    assert torch.equal(r.batch["token_level_scores"].cpu(), T(g[key + "|scores"]))
+    assert torch.equal(r.batch["other"].cpu(), T(g[key + "|other"]))
+    assert torch.equal(r.batch["ids"].cpu(), T(g[key + "|ids"]))
+    assert [str(u) for u in r.non_tensor_batch["uid"]] == list(g[key + "|uid"])
+    assert list(r.non_tensor_batch["as_list"]) == list(g[key + "|as_list"])
+    assert r.meta_info["per_sample"] == list(g[key + "|per_sample"])
+    assert r.meta_info["scalar"] == 3 and r.meta_info["short_list"] == [1, 2]
+    assert d.batch["ids"].shape == r.batch["ids"].shape  # the input is left untouched
+    with pytest.raises(ValueError):
+        ca.compute_pf_ppo_reweight_data(d, "nope", 1.0)

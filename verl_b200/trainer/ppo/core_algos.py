@@ -53,6 +53,7 @@ __all__ = [
     "compute_policy_loss",
     "kl_penalty",
     "fused_actor_loss",
+    "compute_pf_ppo_reweight_data",
     "group_ids_from_index",
 ]
 
@@ -622,3 +623,55 @@ def fused_actor_loss(
                kl_loss_coef=kl_loss_coef, kl_loss_type=kl_loss_type, loss_scale=loss_scale)
     return _PolicyLoss.apply(log_prob, old_log_prob, advantages, response_mask, entropy if use_ent else None,
                              ref_log_prob, cfg)
+
+
+def compute_pf_ppo_reweight_data(data, reweight_method: str = "pow", weight_pow: float = 2.0):
+    """verl/trainer/ppo/core_algos.py:1072-1148: resample the batch with replacement, rows weighted by their score.
+
+    ``data`` is anything with DataProto's ``.batch`` (mapping of [B, ...] CUDA tensors incl. "token_level_scores"),
+    ``.non_tensor_batch`` (numpy arrays or lists) and ``.meta_info``.  The row sums run on the device, the B weights and
+    the multinomial draw stay on the host generator exactly as in the reference (a seeded run resamples the same rows),
+    and every tensor of the batch is resampled by ONE row-gather pass.  Returns a shallow copy of ``data`` with the three
+    fields replaced (the reference deep-copies everything first and then overwrites the same three fields)."""
+    import copy
+
+    tls = data.batch["token_level_scores"]
+    ones = torch.ones(tls.shape, dtype=torch.uint8, device=tls.device)
+    scores = ops.masked_row_sums(tls, ones)[0].view(tls.shape[:-1]).cpu()
+    if reweight_method == "pow":
+        weights = torch.pow(torch.abs(scores), weight_pow)
+    elif reweight_method == "max_min":
+        weights = torch.where((scores == torch.max(scores)) | (scores == torch.min(scores)), 1.0, 0.0)
+    elif reweight_method == "max_random":
+        weights = torch.where(scores == torch.max(scores), 0.4, 0.1)
+    else:
+        raise ValueError(f"Unsupported reweight_method: {reweight_method}")
+    weights = torch.clamp(weights + 1e-8, min=1e-8)
+    batch_size = scores.shape[0]
+    sample_indices = torch.multinomial(weights, batch_size, replacement=True)
+    idx_dev = sample_indices.to(tls.device)
+    resampled_batch = {key: ops.gather_rows(tensor, idx_dev) for key, tensor in data.batch.items()}
+    sample_indices_np = sample_indices.numpy()
+    resampled_non_tensor_batch = {}
+    for key, array in getattr(data, "non_tensor_batch", {}).items():
+        if isinstance(array, np.ndarray):
+            resampled_non_tensor_batch[key] = array[sample_indices_np]
+        else:
+            resampled_non_tensor_batch[key] = [array[i] for i in sample_indices_np]
+    resampled_meta_info = {}
+    for key, value in getattr(data, "meta_info", {}).items():
+        if isinstance(value, list) and len(value) == batch_size:
+            resampled_meta_info[key] = [value[i] for i in sample_indices_np]
+        else:
+            resampled_meta_info[key] = value
+    resampled_data = copy.copy(data)
+    try:
+        new_batch = type(data.batch)(resampled_batch)
+        if hasattr(data.batch, "batch_size"):
+            new_batch.batch_size = data.batch.batch_size
+    except Exception:  # a mapping type that cannot be rebuilt from a dict
+        new_batch = resampled_batch
+    resampled_data.batch = new_batch
+    resampled_data.non_tensor_batch = resampled_non_tensor_batch
+    resampled_data.meta_info = resampled_meta_info
+    return resampled_data
