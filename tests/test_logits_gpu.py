@@ -69,3 +69,44 @@ def test_extreme_logits(dev):
     lp, ent = F.logprobs_from_logits(x, labels), F.entropy_from_logits(x)
     torch.testing.assert_close(lp.cpu(), port.logprobs_from_logits(x.cpu(), labels.cpu()), atol=1e-5, rtol=1e-5)
     torch.testing.assert_close(ent.cpu(), port.entropy_from_logits(x.cpu()), atol=1e-5, rtol=1e-5)
+
+
+def test_log_probs_from_logits_response(dev):
+    """verl/utils/torch_functional.py:421-435 against the reference's own composition (slice + log_softmax gather)"""
+    from verl_b200.utils import torch_functional as F
+
+    g = torch.Generator().manual_seed(12)
+    B, S, V, L = 3, 17, 301, 6
+    logits = torch.randn(B, S, V, generator=g) * 3
+    ids = torch.randint(0, V, (B, S), generator=g)
+    want = torch.log_softmax(logits[:, -L - 1:-1], -1).gather(-1, ids[:, -L:, None]).squeeze(-1)
+    got = F.log_probs_from_logits_response(ids.to(dev), logits.to(dev), L)
+    assert got.shape == (B, L)
+    torch.testing.assert_close(got.cpu(), want, atol=1e-5, rtol=1e-5)
+
+
+def test_distributed_stats_single_rank_group():
+    """distributed_masked_mean / distributed_mean_max_min_std (verl/utils/torch_functional.py:709-771) over a one-rank
+    NCCL group in a child process (the multi-rank case runs in scripts/tp_megatron_check.py under torchrun)."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import torch, torch.distributed as dist\n"
+        "from verl_b200.utils import torch_functional as F\n"
+        "dist.init_process_group('nccl', init_method='tcp://127.0.0.1:29571', world_size=1, rank=0)\n"
+        "torch.cuda.set_device(0)\n"
+        "g = torch.Generator().manual_seed(1)\n"
+        "x = torch.randn(7, 33, generator=g); m = (torch.rand(7, 33, generator=g) < 0.6).long()\n"
+        "mm = F.distributed_masked_mean(x.cuda(), m.cuda())\n"
+        "assert abs(float(mm) - float((x * m).sum() / m.sum())) < 1e-6, float(mm)\n"
+        "mean, mx, mn, std = F.distributed_mean_max_min_std(x.cuda())\n"
+        "assert abs(float(mean) - float(x.mean())) < 1e-6 and float(mx) == float(x.max()) and float(mn) == float(x.min())\n"
+        "assert abs(float(std) - float(x.std())) < 1e-5\n"
+        "assert F.distributed_mean_max_min_std(x.cuda(), False, False, False)[1:] == (None, None, None)\n"
+        "dist.destroy_process_group(); print('DIST_OK')\n"
+    )
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

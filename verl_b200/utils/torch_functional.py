@@ -227,3 +227,44 @@ def log_probs_from_logits_all_rmpad(input_ids_rmpad, logits_rmpad, indices, batc
         hidden_states=full_log_probs_rmpad.unsqueeze(-1), indices=indices, batch=batch_size, seqlen=seqlen
     )
     return full_output.squeeze(-1)[:, -response_length - 1 : -1]
+
+
+def log_probs_from_logits_response(input_ids, logits, response_length):
+    """verl/utils/torch_functional.py:421-435: logits [B,S,V] = model(input_ids) -> log-probs of the last
+    ``response_length`` tokens, [B, response_length]."""
+    response_logits = logits[:, -response_length - 1 : -1]
+    response = input_ids[:, -response_length:]
+    return logprobs_from_logits(logits=response_logits, labels=response)
+
+
+# ------------------------------------------------------------------------------------------------- distributed stats
+def distributed_masked_mean(local_tensor, local_mask):
+    """verl/utils/torch_functional.py:752-771: global mean of the valid elements across the default process group.
+    One masked-sum pass gives {sum, count}; ONE all-reduce of the pair replaces the reference's two."""
+    import torch.distributed as dist
+
+    pair = ops.masked_sums(local_tensor, local_mask)  # float64 [2]
+    dist.all_reduce(pair, op=dist.ReduceOp.SUM)
+    return (pair[0] / pair[1]).to(torch.float32)
+
+
+def distributed_mean_max_min_std(local_tensor, compute_max=True, compute_min=True, compute_std=True):
+    """verl/utils/torch_functional.py:709-749 -> (mean, max, min, std), None for disabled entries.  Metrics-side helper
+    (a handful of scalars per call): torch reductions locally, the reference's collectives packed into at most three."""
+    import torch.distributed as dist
+
+    x = local_tensor.float()
+    sums = torch.stack([x.sum(), x.new_tensor(float(x.numel()))])
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    global_mean = sums[0] / sums[1]
+    local_max = local_min = global_std = None
+    if compute_max or compute_min:
+        ext = torch.stack([x.max(), -x.min()])  # one MAX all-reduce serves both
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX)
+        local_max = ext[0] if compute_max else None
+        local_min = -ext[1] if compute_min else None
+    if compute_std:
+        square_diff = torch.sum(torch.pow(x - global_mean, 2))
+        dist.all_reduce(square_diff, op=dist.ReduceOp.SUM)
+        global_std = torch.sqrt(square_diff / (sums[1] - 1))
+    return global_mean, local_max, local_min, global_std
