@@ -328,6 +328,91 @@ def test_fp32_operands_tf32(dev):
     torch.testing.assert_close(weight.grad, dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
 
 
+def test_fused_linear_for_ppo_torch_backend_contract(dev):
+    """FusedLinearForPPO (verl/utils/experimental/torch_functional.py:201-216, the reference's default fused backend):
+    [B,S,H] in -> [B,S] out in the hidden dtype, gradients in the operand dtypes; values against the fp32 reference at
+    bf16 resolution (the outputs are rounded to bf16 exactly as the reference's new_zeros buffers are)."""
+    from verl_b200.utils.experimental.torch_functional import FusedLinearForPPO
+
+    B, S, H, V, temp = 3, 50, 256, 1500, 1.5
+    g = torch.Generator().manual_seed(21)
+    hidden = (torch.rand(B, S, H, generator=g) - 0.5).bfloat16().to(dev).requires_grad_(True)
+    weight = (torch.rand(V, H, generator=g) - 0.5).bfloat16().to(dev).requires_grad_(True)
+    ids = torch.randint(0, V, (B, S), generator=g).to(dev)
+    g_lp = (torch.rand(B, S, generator=g) * 2 - 1).to(dev)
+    g_ent = (torch.rand(B, S, generator=g) - 0.5).to(dev)
+    lp, ent = FusedLinearForPPO()(hidden, weight, ids.int(), temperature=temp)
+    assert lp.shape == (B, S) and ent.shape == (B, S) and lp.dtype == torch.bfloat16 and ent.dtype == torch.bfloat16
+    (lp.float() * g_lp + ent.float() * g_ent).sum().backward()
+    lp_r, ent_r, dh_r, dw_r = _gpu_fp32_reference(hidden.detach().view(-1, H), weight.detach(), ids.view(-1), temp,
+                                                  g_lp.view(-1), g_ent.view(-1))
+    torch.testing.assert_close(lp.float().view(-1), lp_r, atol=6e-2, rtol=8e-3)   # one bf16 ulp of a value <= 16
+    torch.testing.assert_close(ent.float().view(-1), ent_r, atol=6e-2, rtol=8e-3)
+    assert hidden.grad.shape == (B, S, H) and hidden.grad.dtype == torch.bfloat16
+    torch.testing.assert_close(hidden.grad.float().view(-1, H), dh_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    torch.testing.assert_close(weight.grad.float(), dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    lp2, ent2 = FusedLinearForPPO()(hidden.detach().view(-1, H), weight.detach(), ids.view(-1))  # 2-D in -> flat out
+    assert lp2.shape == (B * S,) and ent2.shape == (B * S,)
+
+
+def test_hf_forward_shims(dev):
+    """forward_with_{torch,triton}_backend (verl/models/transformers/dense_common.py:73-193) on a stand-in causal LM:
+    `.log_probs` / `.entropy` of the rolled labels, the rmpad ([1,T]) and padded ([B,S]) call shapes of
+    verl/workers/actor/dp_actor.py:163-178,254-256, and the backend switch of monkey_patch.py:148-192."""
+    import types
+
+    from verl_b200.models.transformers import dense_common as dc
+
+    H, V = 128, 700
+
+    class Body(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(V, H)
+
+        def forward(self, input_ids=None, inputs_embeds=None, **kw):
+            return torch.tanh(self.emb(input_ids) if inputs_embeds is None else inputs_embeds)
+
+    class LM(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.config = types.SimpleNamespace(output_attentions=False, output_hidden_states=False, model_type="x")
+            self.body = Body()
+            self.lm_head = torch.nn.Linear(H, V, bias=False)
+
+        def model(self, **kw):
+            h = self.body(**kw)
+
+            class Out(tuple):
+                past_key_values = None
+                hidden_states = None
+                attentions = None
+
+            return Out((h,))
+
+    torch.manual_seed(0)
+    lm = LM().to(dev).bfloat16()
+    ids = torch.randint(0, V, (2, 24), device=dev)
+    h = torch.tanh(lm.body.emb(ids)).float()
+    logits = (h @ lm.lm_head.weight.float().t()) / 1.3
+    rolled = torch.roll(ids, -1, -1)
+    want_lp = torch.log_softmax(logits, -1).gather(-1, rolled[..., None]).squeeze(-1)
+    dc.patch_forward_with_backends(lm, use_fused_kernels=True, fused_kernels_backend="triton")
+    out = lm(input_ids=ids, temperature=1.3, return_dict=True)
+    assert isinstance(out, dc.CausalLMOutputForPPO) and out.log_probs.shape == (2, 24) and out.log_probs.dtype == torch.float32
+    torch.testing.assert_close(out.log_probs, want_lp, atol=LP_ATOL, rtol=0)
+    out1 = lm(input_ids=ids.view(1, -1), temperature=1.3, return_dict=True)  # rmpad call: [1,T] -> flat [T]
+    assert out1.log_probs.shape == (48,) and out1.entropy.shape == (48,)
+    dc.patch_forward_with_backends(lm, use_fused_kernels=True, fused_kernels_backend="torch")
+    out2 = lm(input_ids=ids, temperature=1.3, return_dict=True)
+    assert out2.log_probs.shape == (2, 24) and out2.log_probs.dtype == torch.bfloat16
+    torch.testing.assert_close(out2.log_probs.float(), want_lp, atol=6e-2, rtol=8e-3)
+    with pytest.raises(NotImplementedError):
+        lm(input_ids=ids, temperature=1.3, return_dict=False)
+    with pytest.raises(RuntimeError):
+        lm(inputs_embeds=h.bfloat16(), temperature=1.3, return_dict=True)  # neither labels nor input_ids
+
+
 def test_gemm_all_majors(dev):
     from verl_b200 import ops
 

@@ -9,6 +9,9 @@
   verl.trainer.ppo.core_algos.{compute_policy_loss, agg_loss, kl_penalty, compute_value_loss, compute_policy_loss_gpg,
       compute_grpo_outcome_advantage, compute_gae_advantage_return and the seven other estimators}
       (+ every ADV_ESTIMATOR_REGISTRY entry and the "gpg" / "clip_cov" / "kl_cov" POLICY_LOSS_REGISTRY entries)
+  verl.utils.experimental.torch_functional.{FusedLinearForPPO, FusedLinearForPPOFunction}   (the DEFAULT "torch"
+      fused backend, verl/models/transformers/dense_common.py:88-121)
+  verl.models.transformers.dense_common.{forward_with_torch_backend, forward_with_triton_backend, ...}
   flash_attn.bert_padding.{unpad_input, pad_input, index_first_axis}   (only with patch_flash_attn=True)
 
 If the real ``verl`` package is importable its modules are patched attribute by attribute (everything outside the
@@ -27,12 +30,14 @@ from .trainer.ppo import core_algos as _ca
 from .utils import torch_functional as _tf
 from .utils.kernel import kernels as _k
 from .utils.kernel import linear_cross_entropy as _lce
+from .utils.experimental import torch_functional as _xtf
+from .models.transformers import dense_common as _dc
 
 _TF_NAMES = [
     "logprobs_from_logits", "logprobs_from_logits_v2", "logprobs_from_logits_naive", "logprobs_from_logits_flash_attn",
     "entropy_from_logits", "entropy_from_logits_with_chunking", "masked_sum", "masked_mean", "masked_var",
     "masked_whiten", "get_unpad_data", "log_probs_from_logits_response_rmpad", "log_probs_from_logits_all_rmpad",
-    "gather_from_labels",
+    "gather_from_labels", "log_probs_from_logits_response", "distributed_masked_mean", "distributed_mean_max_min_std",
 ]
 _CA_NAMES = ["compute_policy_loss", "agg_loss", "kl_penalty", "compute_grpo_outcome_advantage",
              "compute_gae_advantage_return", "compute_rewards", "compute_grpo_passk_outcome_advantage",
@@ -40,7 +45,7 @@ _CA_NAMES = ["compute_policy_loss", "agg_loss", "kl_penalty", "compute_grpo_outc
              "compute_opo_outcome_advantage", "compute_reinforce_plus_plus_outcome_advantage",
              "compute_remax_outcome_advantage", "compute_gpg_outcome_advantage", "compute_policy_loss_gpg",
              "compute_value_loss", "compute_policy_loss_clip_cov", "compute_policy_loss_kl_cov",
-             "compute_entropy_loss"]
+             "compute_entropy_loss", "compute_pf_ppo_reweight_data"]
 
 
 def _try_import(name):
@@ -101,6 +106,10 @@ def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
         "verl.utils.kernel.kernels": (_k, [n for n in dir(_k) if not n.startswith("__")]),
         "verl.utils.torch_functional": (_tf, _TF_NAMES),
         "verl.trainer.ppo.core_algos": (_ca, _CA_NAMES),
+        # the reference's DEFAULT fused backend ("torch", ppo_trainer.yaml:90-94) and the HF forward shims that pick one
+        "verl.utils.experimental.torch_functional": (_xtf, ["FusedLinearForPPOFunction", "FusedLinearForPPO"]),
+        "verl.models.transformers.dense_common": (_dc, ["CausalLMOutputForPPO", "forward_base_model",
+                                                        "forward_with_torch_backend", "forward_with_triton_backend"]),
     }
     for name, (src, names) in targets.items():
         real = _try_import(name)
