@@ -174,7 +174,9 @@ def test_compat_install_shadows_reference_paths():
         "from verl.utils.seqlen_balancing import get_seqlen_balanced_partitions as kk;"
         "from verl.models.mcore.util import preprocess_packed_seqs; from verl.utils.ulysses import ulysses_pad;"
         "from verl.utils.megatron.tensor_parallel import vocab_parallel_entropy;"
+        "from verl.utils.experimental.torch_functional import FusedLinearForPPO;"
+        "from verl.models.transformers.dense_common import forward_with_torch_backend, forward_with_triton_backend;"
         "assert a is b and hasattr(ca, 'compute_policy_loss') and hasattr(F, 'masked_mean'); print('ok', len(r))"
     )
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "ok 8" in out.stdout, out.stderr
+    assert out.returncode == 0 and "ok 10" in out.stdout, out.stderr
