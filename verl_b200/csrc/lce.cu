@@ -114,8 +114,17 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     TcParams p = p_in;
     p.sync_slack = env_int("VPG_SYNC_SLACK", 2);
     p.sync_epoch = next_epoch();
+    p.ds_stcs = env_int("VPG_DS_STCS", 0);
     if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
     if (env_int("VPG_HINT_B", -1) >= 0) p.hint_b = env_int("VPG_HINT_B", 0);
+    {   // per-kernel overrides: VPG_HINT_{A,B}_{FWD,DS,DH,DW}
+        const char* tag = kMode == MODE_FWD ? "FWD" : kMode == MODE_DS ? "DS" : kAMn ? "DW" : "DH";
+        char name[32];
+        snprintf(name, sizeof(name), "VPG_HINT_A_%s", tag);
+        if (env_int(name, -1) >= 0) p.hint_a = env_int(name, 0);
+        snprintf(name, sizeof(name), "VPG_HINT_B_%s", tag);
+        if (env_int(name, -1) >= 0) p.hint_b = env_int(name, 0);
+    }
     constexpr int smem = TileCfg<kCG>::kSmemBytes + (kMode == MODE_GEMM ? kRedScratchBytes : 0);
     // per-device attribute: set every call (cheap) so multi-device processes are handled
     cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

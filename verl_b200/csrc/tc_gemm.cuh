@@ -107,6 +107,7 @@ struct TcParams {
     int hint_a, hint_b;  // L2 eviction priority of the A / B operand loads: 0 normal, 1 evict-first, 2 evict-last
     int worker_perm;  // 0/1: identity; S > 1: group physical neighbours on residues mod S (see kernel)
     float* accum;  // OUT_F32_ACC: same as out; OUT_BF16_FROM_ACC: fp32 partial to add
+    int ds_stcs;   // MODE_DS: 1 = dlogits stores carry the streaming (evict-first) policy
     int f16;       // 1: the 16-bit operands AND 16-bit outputs (OUT_BF16*, ds) are IEEE fp16 instead of bf16
     long long ld_accum;
 };
@@ -218,7 +219,7 @@ struct DsRow {
 
 // dlogits chunk: d = -p*(a + b*x) (+ glp at the label column), zero for columns >= n_valid
 __device__ __forceinline__ void ds_chunk(const DsRow& rw, const uint32_t (&r)[32], float c, int lab_rel, int n_valid,
-                                         __nv_bfloat16* dst, int f16) {
+                                         __nv_bfloat16* dst, int f16, int stcs) {
     float d[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -245,7 +246,7 @@ __device__ __forceinline__ void ds_chunk(const DsRow& rw, const uint32_t (&r)[32
         v.y = pack_16x2(d[q4 * 8 + 2], d[q4 * 8 + 3], f16);
         v.z = pack_16x2(d[q4 * 8 + 4], d[q4 * 8 + 5], f16);
         v.w = pack_16x2(d[q4 * 8 + 6], d[q4 * 8 + 7], f16);
-        o[q4] = v;
+        if (stcs) __stcs(o + q4, v); else o[q4] = v;
     }
 }
 
@@ -664,7 +665,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             if (n_valid >= 32) fwd_chunk<false>(st, ra, c, lab - cb, 32);
                             else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
-                            ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16);
+                            ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, ra, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
@@ -680,7 +681,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             if (n_valid >= 32) fwd_chunk<false>(st, rb, c, lab - cb, 32);
                             else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
-                            ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16);
+                            ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, rb, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {

@@ -688,16 +688,32 @@ __global__ void whiten_apply_kernel(const float* values, long long n, const doub
     var_d = var_d * (N / (N - 1.0));
     const float mean = static_cast<float>(mean_d);
     const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-8f);
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
-    for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC; i < n; i += stride) {
-        Pack<VEC> v = ldv<VEC>(values, i);
+    // kIlp independent 128-bit loads per thread are issued before the first store: the pass has one input stream only,
+    // so a single load in flight per thread leaves the HBM queues half empty (values may alias out: no __restrict__,
+    // hence the explicit staging instead of relying on the compiler to hoist loads over stores)
+    constexpr int kIlp = 4;
+    const long long tile = static_cast<long long>(blockDim.x) * VEC;  // elements one block covers per sub-step
+    const long long stride = static_cast<long long>(gridDim.x) * tile * kIlp;
+    for (long long i0 = static_cast<long long>(blockIdx.x) * tile * kIlp + static_cast<long long>(threadIdx.x) * VEC;
+         i0 < n; i0 += stride) {
+        Pack<VEC> v[kIlp];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            float wv = (v.v[j] - mean) * rstd;
-            if (!shift_mean) wv += mean;
-            v.v[j] = wv;
+        for (int u = 0; u < kIlp; ++u) {
+            const long long i = i0 + u * tile;
+            if (i < n) v[u] = ldv<VEC>(values, i);
         }
-        stv<VEC>(out, i, v);
+#pragma unroll
+        for (int u = 0; u < kIlp; ++u) {
+            const long long i = i0 + u * tile;
+            if (i >= n) break;
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                float wv = (v[u].v[j] - mean) * rstd;
+                if (!shift_mean) wv += mean;
+                v[u].v[j] = wv;
+            }
+            stv<VEC>(out, i, v[u]);
+        }
     }
 }
 
