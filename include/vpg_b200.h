@@ -286,13 +286,13 @@ int vpg_outcome_advantage(int kind, const float* token_level_rewards, const void
                           size_t workspace_bytes, void* stream);
 
 /* compute_reinforce_plus_plus_outcome_advantage (core_algos.py:533-569): discounted reverse return with reset after
- * masked-out tokens, advantages = masked_whiten(returns) * mask.  status as vpg_gae.
+ * masked-out tokens, advantages = masked_whiten(returns) * mask.  status / status_event as vpg_gae.
  * compute_remax_outcome_advantage (core_algos.py:572-605): returns = reverse cumsum of rewards*mask,
  * advantages = returns - reward_baselines[b] * mask. */
 size_t vpg_reverse_scan_workspace_bytes(int64_t B, int64_t L);
 int vpg_reinforce_plus_plus(const float* token_level_rewards, const void* mask, int mask_dtype, int64_t B, int64_t L,
                             float gamma, float* advantages, float* returns, int32_t* status, void* workspace,
-                            size_t workspace_bytes, void* stream);
+                            size_t workspace_bytes, void* stream, void* status_event);
 int vpg_remax(const float* token_level_rewards, const float* reward_baselines, const void* mask, int mask_dtype,
               int64_t B, int64_t L, float* advantages, float* returns, void* stream);
 
@@ -317,16 +317,19 @@ int vpg_data_metrics(const float* token_level_scores, const float* token_level_r
 
 /* compute_gae_advantage_return (core_algos.py:193-241): reverse recurrence per row with masked carry-through,
  * returns = adv + values, then masked_whiten (torch_functional.py:206-223) over the whole batch.
- * status[0] (i32, device) = 0 ok, 1 mask sum == 0, 2 mask sum == 1 (the reference raises ValueError there).
+ * status[0] (i32) = 0 ok, 1 mask sum == 0, 2 mask sum == 1 (the reference raises ValueError there).  The word is
+ * written by a one-thread kernel BETWEEN the recurrence / statistics pass and the normalisation pass; it may live in
+ * device memory or in pinned host memory (UVA-mapped).  status_event (cudaEvent_t, may be NULL) is recorded right
+ * behind that kernel, so a host that waits on it learns the status while the normalisation pass is still running.
  * workspace: vpg_gae_workspace_bytes(B, L). */
 size_t vpg_gae_workspace_bytes(int64_t B, int64_t L);
 int vpg_gae(const float* token_level_rewards, const float* values, const void* mask, int mask_dtype, int64_t B,
             int64_t L, float gamma, float lam, float* advantages, float* returns, int32_t* status, void* workspace,
-            size_t workspace_bytes, void* stream);
+            size_t workspace_bytes, void* stream, void* status_event);
 
-/* masked_whiten (torch_functional.py:206-223) over all elements. status as above. */
+/* masked_whiten (torch_functional.py:206-223) over all elements. status / status_event as above. */
 int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
-                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream);
+                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream, void* status_event);
 
 /* ---- dynamic micro-batches (verl/utils/seqlen_balancing.py) ------------------------------------------------------
  * attention_mask.sum(dim=1) (:282) as exact integers: lengths[b] (i64, device) = sum_s mask[b,s]. */

@@ -113,7 +113,7 @@ SIGNATURES: dict[str, tuple] = {
     "vpg_reinforce_plus_plus": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
-         c_void_p],
+         c_void_p, c_void_p],
     ),
     "vpg_remax": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "vpg_agg_loss": (
@@ -142,7 +142,7 @@ SIGNATURES: dict[str, tuple] = {
     "vpg_gae": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_float, c_float, c_void_p, c_void_p, c_void_p,
-         c_void_p, c_size_t, c_void_p],
+         c_void_p, c_size_t, c_void_p, c_void_p],
     ),
     "vpg_row_lengths": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]),
     "vpg_seqlen_balanced_partitions": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
@@ -167,7 +167,7 @@ SIGNATURES: dict[str, tuple] = {
     ),
     "vpg_masked_whiten": (
         c_int,
-        [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+        [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
     ),
 }
 

@@ -331,13 +331,9 @@ reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ ma
 // advantages = masked_whiten(returns, mask) * mask  (core_algos.py:565-566; torch_functional.py:206-223)
 template <int VEC, typename MT>
 __global__ void whiten_mask_apply_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
-                                         const double* __restrict__ sums, float* __restrict__ out,
-                                         int* __restrict__ status) {
+                                         const double* __restrict__ sums, float* __restrict__ out) {
     const double N = sums[2];
-    if (N == 0.0 || N == 1.0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = (N == 0.0) ? 1 : 2;
-        return;
-    }
+    if (N == 0.0 || N == 1.0) return;  // status word: whiten_status_kernel
     const double den = N + 1e-8;
     const double mean_d = sums[0] / den;
     double var_d = (sums[1] - 2.0 * mean_d * sums[0] + mean_d * mean_d * N) / den;
@@ -422,7 +418,7 @@ static inline unsigned scan_threads(int64_t L) {
 
 int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dtype, int64_t B, int64_t L, float gamma,
                             float* advantages, float* returns, int32_t* status, void* workspace,
-                            size_t workspace_bytes, void* stream_) {
+                            size_t workspace_bytes, void* stream_, void* status_event) {
     VPG_CHECK_ARG(rewards && mask && advantages && returns && status, "null pointer argument");
     VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
     if (!workspace || workspace_bytes < vpg_reverse_scan_workspace_bytes(B, L))
@@ -430,7 +426,6 @@ int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dty
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     double* sums = static_cast<double*>(workspace);
     VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
-    VPG_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
     const int64_t n = B * L;
     const bool vec = rows_vec_ok(n, mask, mask_dtype, {rewards, returns, advantages});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
@@ -438,10 +433,11 @@ int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dty
         reverse_scan_kernel<MT, 0><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
             rewards, mk, nullptr, L, gamma, advantages, returns, sums, (L % kScanSeg == 0) && vec);
         count_launch();
+        VPG_CUDA(publish_whiten_status(sums, status, status_event, stream));
         if (vec)
-            whiten_mask_apply_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(returns, mk, n, sums, advantages, status);
+            whiten_mask_apply_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(returns, mk, n, sums, advantages);
         else
-            whiten_mask_apply_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(returns, mk, n, sums, advantages, status);
+            whiten_mask_apply_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(returns, mk, n, sums, advantages);
     });
     VPG_LAUNCH_CHECK();
     return VPG_OK;

@@ -95,4 +95,21 @@ static inline bool rows_vec_ok(int64_t L, const void* mask, int mask_dtype, std:
 }
 
 
+// masked_whiten's error status (torch_functional.py:195-200: the reference raises when the mask sums to 0 or 1),
+// published by a one-thread kernel BETWEEN the statistics pass and the normalisation pass: `status` may be a pinned
+// (UVA-mapped) host word and `status_event` a cudaEvent_t recorded right behind it, so the host can learn the
+// status — and raise like the reference — while the normalisation pass is still running.
+static __global__ void whiten_status_kernel(const double* __restrict__ sums, int* status) {
+    const double N = sums[2];
+    *status = (N == 0.0) ? 1 : (N == 1.0) ? 2 : 0;
+    __threadfence_system();
+}
+static inline cudaError_t publish_whiten_status(const double* sums, int* status, void* status_event,
+                                                cudaStream_t stream) {
+    whiten_status_kernel<<<1, 1, 0, stream>>>(sums, status);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && status_event) e = cudaEventRecord(static_cast<cudaEvent_t>(status_event), stream);
+    return e;
+}
+
 }  // namespace vpg

@@ -674,13 +674,10 @@ __global__ void whiten_stats_kernel(const float* __restrict__ values, const MT* 
 // out = (x - mean) * rsqrt(var + 1e-8) (+ mean if !shift_mean).  In place allowed (values == out).
 template <int VEC>
 __global__ void whiten_apply_kernel(const float* values, long long n, const double* __restrict__ sums,
-                                    int shift_mean, float* out, int* __restrict__ status) {
+                                    int shift_mean, float* out) {
     const double N = sums[2];
-    if (N == 0.0 || N == 1.0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = (N == 0.0) ? 1 : 2;
-        return;  // the reference raises ValueError (torch_functional.py:195-200); outputs are left untouched
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = 0;
+    if (N == 0.0 || N == 1.0) return;  // the reference raises ValueError (torch_functional.py:195-200; status word
+                                       // from whiten_status_kernel); outputs are left untouched
     const double den = N + 1e-8;
     const double mean_d = sums[0] / den;
     // sum((x-mean)^2 m) = S2 - 2 mean S1 + mean^2 N
@@ -934,18 +931,19 @@ size_t vpg_gae_workspace_bytes(int64_t B, int64_t L) {
 }
 
 static int whiten_apply(const float* values, int64_t n, const double* sums, int shift_mean, float* out,
-                        int32_t* status, cudaStream_t stream) {
+                        int32_t* status, void* status_event, cudaStream_t stream) {
+    VPG_CUDA(publish_whiten_status(sums, status, status_event, stream));
     if (n % 4 == 0 && aligned16(values) && aligned16(out))
-        whiten_apply_kernel<4><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, n, sums, shift_mean, out, status);
+        whiten_apply_kernel<4><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, n, sums, shift_mean, out);
     else
-        whiten_apply_kernel<1><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, n, sums, shift_mean, out, status);
+        whiten_apply_kernel<1><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, n, sums, shift_mean, out);
     VPG_LAUNCH_CHECK();
     return VPG_OK;
 }
 
 int vpg_gae(const float* rewards, const float* values, const void* mask, int mask_dtype, int64_t B, int64_t L,
             float gamma, float lam, float* advantages, float* returns, int32_t* status, void* workspace,
-            size_t workspace_bytes, void* stream_) {
+            size_t workspace_bytes, void* stream_, void* status_event) {
     VPG_CHECK_ARG(rewards && values && mask && advantages && returns && status, "null pointer argument");
     VPG_CHECK_ARG(B > 0 && L > 0, "empty batch");
     if (!workspace || workspace_bytes < vpg_gae_workspace_bytes(B, L))
@@ -961,11 +959,11 @@ int vpg_gae(const float* rewards, const float* values, const void* mask, int mas
             rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums, vec);
     });
     VPG_LAUNCH_CHECK();
-    return whiten_apply(advantages, B * L, sums, 1, advantages, status, stream);
+    return whiten_apply(advantages, B * L, sums, 1, advantages, status, status_event, stream);
 }
 
 int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
-                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+                      int32_t* status, void* workspace, size_t workspace_bytes, void* stream_, void* status_event) {
     VPG_CHECK_ARG(values && mask && out && status && n > 0, "invalid masked_whiten arguments");
     if (!workspace || workspace_bytes < 4 * sizeof(double))
         return set_error(VPG_ERR_WORKSPACE, "masked_whiten workspace too small");
@@ -981,7 +979,7 @@ int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int
             whiten_stats_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, mk, n, sums);
     });
     VPG_LAUNCH_CHECK();
-    return whiten_apply(values, n, sums, shift_mean, out, status, stream);
+    return whiten_apply(values, n, sums, shift_mean, out, status, status_event, stream);
 }
 
 }  // extern "C"

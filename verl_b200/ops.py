@@ -9,6 +9,8 @@ from __future__ import annotations
 
 import math
 
+import threading
+
 import torch
 
 from . import _lib
@@ -608,12 +610,12 @@ def reinforce_plus_plus(token_level_rewards, response_mask, gamma: float):
     B, L = r.shape
     lib = _lib_()
     adv, ret = torch.empty_like(r), torch.empty_like(r)
-    status = torch.empty(1, dtype=torch.int32, device=r.device)
+    slot = _StatusSlot.get(r.device)
     ws = _ws(int(lib.vpg_reverse_scan_workspace_bytes(B, L)), r.device)
     with torch.cuda.device(r.device):
-        check(lib.vpg_reinforce_plus_plus(ptr(r), ptr(m), mdt, B, L, float(gamma), ptr(adv), ptr(ret), ptr(status),
-                                          ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
-    _raise_whiten_status(status)
+        check(lib.vpg_reinforce_plus_plus(ptr(r), ptr(m), mdt, B, L, float(gamma), ptr(adv), ptr(ret), slot.word_ptr,
+                                          ptr(ws), ws.numel() * 8, stream_ptr(r.device), slot.event_ptr))
+    slot.wait_and_raise()
     return adv, ret
 
 
@@ -685,8 +687,36 @@ def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: in
     return adv
 
 
-def _raise_whiten_status(status: torch.Tensor):
-    _raise_whiten_code(int(status.item()))
+class _StatusSlot:
+    """Pinned host status word + CUDA event, one per (thread, device).  The whitening entry points write the status
+    word from a one-thread kernel that runs BEFORE their normalisation pass and record the event right behind it, so
+    waiting for the event costs the statistics pass only: the ValueError of the reference (torch_functional.py:
+    195-200) is still raised synchronously, but the normalisation pass overlaps the host's wake-up."""
+
+    _tls = threading.local()
+
+    def __init__(self, device):
+        self.word = torch.zeros(1, dtype=torch.int32).pin_memory()  # UVA: the same pointer is valid on the device
+        self.word_ptr = self.word.data_ptr()
+        self.event = torch.cuda.Event()
+        with torch.cuda.device(device):
+            self.event.record()  # torch creates the cudaEvent_t lazily, at the first record
+        self.event.synchronize()
+        self.event_ptr = int(self.event.cuda_event)
+        assert self.event_ptr, "torch.cuda.Event did not expose its handle"
+
+    @classmethod
+    def get(cls, device) -> "_StatusSlot":
+        slots = cls._tls.__dict__.setdefault("slots", {})
+        idx = torch.device(device).index
+        idx = torch.cuda.current_device() if idx is None else idx
+        if idx not in slots:
+            slots[idx] = cls(idx)
+        return slots[idx]
+
+    def wait_and_raise(self):
+        self.event.synchronize()
+        _raise_whiten_code(int(self.word[0]))
 
 
 def _raise_whiten_code(code: int):
@@ -703,12 +733,12 @@ def gae(token_level_rewards, values, response_mask, gamma: float, lam: float):
     B, L = r.shape
     lib = _lib_()
     adv, ret = torch.empty_like(r), torch.empty_like(r)
-    status = torch.zeros(1, dtype=torch.int32, device=r.device)
+    slot = _StatusSlot.get(r.device)
     ws = _ws(int(lib.vpg_gae_workspace_bytes(B, L)), r.device)
     with torch.cuda.device(r.device):
-        check(lib.vpg_gae(ptr(r), ptr(v), ptr(m), mdt, B, L, float(gamma), float(lam), ptr(adv), ptr(ret), ptr(status),
-                          ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
-    _raise_whiten_status(status)
+        check(lib.vpg_gae(ptr(r), ptr(v), ptr(m), mdt, B, L, float(gamma), float(lam), ptr(adv), ptr(ret),
+                          slot.word_ptr, ptr(ws), ws.numel() * 8, stream_ptr(r.device), slot.event_ptr))
+    slot.wait_and_raise()
     return adv, ret
 
 
@@ -717,10 +747,10 @@ def masked_whiten(values, mask, shift_mean=True):
     v = _f32c(values)
     m, mdt = mask_arg(mask.contiguous())
     out = torch.empty_like(v)
-    status = torch.zeros(1, dtype=torch.int32, device=v.device)
+    slot = _StatusSlot.get(v.device)
     ws = _ws(32, v.device)
     with torch.cuda.device(v.device):
-        check(_lib_().vpg_masked_whiten(ptr(v), ptr(m), mdt, v.numel(), int(bool(shift_mean)), ptr(out), ptr(status),
-                                        ptr(ws), ws.numel() * 8, stream_ptr(v.device)))
-    _raise_whiten_status(status)
+        check(_lib_().vpg_masked_whiten(ptr(v), ptr(m), mdt, v.numel(), int(bool(shift_mean)), ptr(out),
+                                        slot.word_ptr, ptr(ws), ws.numel() * 8, stream_ptr(v.device), slot.event_ptr))
+    slot.wait_and_raise()
     return out
