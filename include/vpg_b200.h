@@ -198,7 +198,9 @@ int vpg_logits_stats_bwd(const void* logits, int logits_bf16, int64_t T, int64_t
  * used at verl/workers/actor/dp_actor.py:110-125,221-232, and verl/utils/torch_functional.py:629-638
  * (get_unpad_data).  Integer outputs are bit-exact.
  *   mask [B,S] -> indices i64 [nnz] (ascending flat positions of non-zero mask), seqlens i32 [B],
- *   cu_seqlens i32 [B+1], totals i32 [2] = {nnz, max_seqlen}.  workspace: vpg_unpad_workspace_bytes(B*S).
+ *   cu_seqlens i32 [B+1], totals i32 [2] = {nnz, max_seqlen} (write-only for the kernels: device memory or a
+ *   pinned, UVA-mapped host pair the caller reads after a stream synchronize).
+ *   workspace: vpg_unpad_workspace_bytes(B*S).
  * ------------------------------------------------------------------------------------------------------------ */
 size_t vpg_unpad_workspace_bytes(int64_t n);
 int vpg_unpad_indices(const void* mask, int mask_dtype, int64_t B, int64_t S, int64_t* indices, int32_t* seqlens,

@@ -272,14 +272,15 @@ def unpad_indices(mask2d):
     indices_full = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     seqlens = torch.empty(B, dtype=torch.int32, device=dev)
     cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
-    totals = torch.empty(2, dtype=torch.int32, device=dev)
+    slot = _StatusSlot.get(dev)  # the kernels write {nnz, max_seqlen} straight into pinned host memory (UVA)
     nbytes = int(lib.vpg_unpad_workspace_bytes(n))
     ws = _ws(nbytes, dev)
     with torch.cuda.device(dev):
-        check(lib.vpg_unpad_indices(ptr(m), mdt, B, S, ptr(indices_full), ptr(seqlens), ptr(cu), ptr(totals), ptr(ws),
+        check(lib.vpg_unpad_indices(ptr(m), mdt, B, S, ptr(indices_full), ptr(seqlens), ptr(cu), slot.pair_ptr, ptr(ws),
                                     ws.numel() * 8, stream_ptr(dev)))
-    nnz, max_seqlen = totals.tolist()
-    return indices_full[:nnz], seqlens, cu, int(max_seqlen)
+        torch.cuda.current_stream(dev).synchronize()
+    nnz, max_seqlen = int(slot.pair[0]), int(slot.pair[1])
+    return indices_full[:nnz], seqlens, cu, max_seqlen
 
 
 def response_rows(indices, ids_rmpad, S: int, L: int):
@@ -698,6 +699,8 @@ class _StatusSlot:
     def __init__(self, device):
         self.word = torch.zeros(1, dtype=torch.int32).pin_memory()  # UVA: the same pointer is valid on the device
         self.word_ptr = self.word.data_ptr()
+        self.pair = torch.zeros(2, dtype=torch.int32).pin_memory()  # {nnz, max_seqlen} of unpad_indices
+        self.pair_ptr = self.pair.data_ptr()
         self.event = torch.cuda.Event()
         with torch.cuda.device(device):
             self.event.record()  # torch creates the cudaEvent_t lazily, at the first record
