@@ -236,12 +236,53 @@ def run_ours(args):
     assert T % world == 0
     rows = T // world
     staging = [{k: torch.empty_like(v, device=dev) for k, v in host.items()} for _ in range(2)]
+    # N > 1: the replicated `hidden` is assembled WITHOUT SM work: its two staging slots are symmetric (peer-mapped)
+    # allocations, each rank copies its T/N rows from the host and pulls the other ranks' rows with copy-engine
+    # peer-to-peer DMA over NVLink on the copy stream, between two signal-pad barriers.  An NCCL all-gather here would
+    # put ~16 CTAs next to a persistent 1-CTA-per-SM GEMM whose static schedule then waits for the delayed workers.
+    gather = "none"
+    peer_views = [None, None]
+    sym_handles = [None, None]
+    if world > 1:
+        gather = args.e2e_gather
+        if gather == "ce":
+            ok = 1
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+
+                try:
+                    import warnings
+
+                    with warnings.catch_warnings():  # deprecated no-op on newer torch
+                        warnings.simplefilter("ignore")
+                        symm_mem.enable_symm_mem_for_group(group.group_name)
+                except Exception:  # noqa: BLE001  (newer torch: implicit)
+                    pass
+                for s_ in range(2):
+                    buf = symm_mem.empty(T * H, dtype=torch.bfloat16, device=dev)
+                    hdl = symm_mem.rendezvous(buf, group=group.group_name)
+                    staging[s_]["hidden"] = buf.view(T, H)
+                    peer_views[s_] = [hdl.get_buffer(r, (T, H), torch.bfloat16) for r in range(world)]
+                    sym_handles[s_] = hdl
+            except Exception as e:  # noqa: BLE001
+                ok = 0
+                print(f"[bench] rank {rank}: symmetric staging unavailable ({type(e).__name__}: {e}); NCCL all-gather",
+                      file=sys.stderr, flush=True)
+            flag = torch.tensor([ok], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) != 1:
+                gather = "nccl"
+                for s_ in range(2):
+                    staging[s_]["hidden"] = torch.empty_like(host["hidden"], device=dev)
     copy_stream = torch.cuda.Stream(device=dev)
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
     small_bytes = sum(v.numel() * v.element_size() for k, v in host.items() if k != "hidden")
     h2d_bytes = host["hidden"].numel() * host["hidden"].element_size() + world * small_bytes  # whole job, per step
-    metrics_host = torch.empty(8, dtype=torch.float32).pin_memory()
+    metrics_host = torch.empty(2, 8, dtype=torch.float32).pin_memory()
+    read_back = [torch.cuda.Event() for _ in range(2)]
+    last_read = [None]  # slot whose metrics the host has not read yet
+    host_loss = [0.0]
 
     def enqueue_h2d(slot: int):
         with torch.cuda.stream(copy_stream):
@@ -252,6 +293,15 @@ def run_ours(args):
                     staging[slot][k][sl].copy_(host[k][sl], non_blocking=True)
                 else:
                     staging[slot][k].copy_(host[k], non_blocking=True)
+            if gather == "ce":
+                hdl = sym_handles[slot]
+                hdl.barrier(channel=0)  # every rank's rows of this slot are in place (and nobody still computes on it)
+                dst = staging[slot]["hidden"]
+                for i in range(1, world):  # staggered: at any moment every rank reads from a different peer
+                    r = (rank + i) % world
+                    sl = slice(r * rows, (r + 1) * rows)
+                    dst[sl].copy_(peer_views[slot][r][sl], non_blocking=True)  # contiguous same-dtype: cudaMemcpyAsync
+                hdl.barrier(channel=0)  # all pulls done: a rank may overwrite its rows at the slot's next use
             ready[slot].record(copy_stream)
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -264,7 +314,7 @@ def run_ours(args):
             if prefetch:
                 enqueue_h2d(slot ^ 1)
             src = staging[slot]
-            if world > 1:
+            if gather == "nccl":
                 dist.all_gather_into_tensor(src["hidden"], src["hidden"][rank * rows:(rank + 1) * rows], group=group)
         else:
             src = dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d, mask=mask_d)
@@ -286,8 +336,14 @@ def run_ours(args):
             seg["_marks"].append(marks)
         if e2e:
             consumed[slot].record()
-            metrics_host.copy_(metrics, non_blocking=True)
-            torch.cuda.current_stream().synchronize()  # the host reads the step's loss / metrics
+            # the host reads EVERY step's loss / metrics, one step behind the launches: step i's 32 bytes are waited
+            # for after step i+1 has been enqueued, so the GPU never idles while Python builds the next step
+            metrics_host[slot].copy_(metrics, non_blocking=True)
+            read_back[slot].record()
+            if last_read[0] is not None:
+                read_back[last_read[0]].synchronize()
+                host_loss[0] = float(metrics_host[last_read[0]][0])
+            last_read[0] = slot
         return metrics
 
     def timed(e2e: bool, steps: int, record: bool):
@@ -301,6 +357,10 @@ def run_ours(args):
             enqueue_h2d(0)  # step 0's inputs: inside the timed region, not hidden behind anything
         for i in range(steps):
             step(e2e, record, slot=i & 1, prefetch=i + 1 < steps)
+        if e2e and last_read[0] is not None:  # the last step's metrics are read inside the timed region too
+            read_back[last_read[0]].synchronize()
+            host_loss[0] = float(metrics_host[last_read[0]][0])
+            last_read[0] = None
         e1.record()
         if world > 1:
             dist.barrier()
@@ -317,6 +377,7 @@ def run_ours(args):
     enqueue_h2d(0)
     step(True, False)
     torch.cuda.synchronize()
+    last_read[0] = None
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -355,7 +416,10 @@ def run_ours(args):
                     "how": "pinned host -> device on a copy stream, double-buffered (step i+1's inputs copy under step "
                            "i's compute; every copy is inside the timed region)"
                            + ("" if world == 1 else f"; each rank copies T/{world} rows of hidden and the ranks "
-                              "all-gather the replicated tensor over NVLink") + "; metrics[8] read back every step"},
+                              + ("pull the other rows peer-to-peer with copy-engine DMA over NVLink (symmetric staging "
+                                 "slots, no SM work)" if gather == "ce" else
+                                 "all-gather the replicated tensor over NVLink (NCCL)"))
+                           + "; metrics[8] of every step read by the host, one step behind the launches"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
@@ -395,6 +459,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tp-reduce", choices=["nccl", "multimem"], default="nccl",
                     help="N > 1: d_hidden all-reduce by NCCL (default) or fused into the d_hidden GEMM (multimem.red)")
+    ap.add_argument("--e2e-gather", choices=["ce", "nccl"], default="ce",
+                    help="N>1 end-to-end leg: how the replicated hidden is assembled from the per-rank H2D shards")
     ap.add_argument("--tp-exchange", choices=["auto", "nccl", "nvlink"], default="auto",
                     help="N > 1: fused NVLink exchange (default when NVSwitch multicast is available) or NCCL")
     args = ap.parse_args()

@@ -38,7 +38,11 @@ class PeerWorkspace:
         self._bufs: dict[str, tuple] = {}  # name -> (tensor, handle, numel)
         self._parity = 0
         try:  # older torch versions need the group to be enabled explicitly; newer ones treat this as a no-op
-            symm_mem.enable_symm_mem_for_group(group.group_name)
+            import warnings
+
+            with warnings.catch_warnings():  # deprecated no-op on newer torch
+                warnings.simplefilter("ignore")
+                symm_mem.enable_symm_mem_for_group(group.group_name)
         except Exception:
             pass
 
