@@ -38,9 +38,11 @@ LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_rati
 
 def workload_config(T, world, exchange="nvlink"):
     """`config` of the JSON line — identical for both arms (the reference arm times a bounded sample of it)."""
+    red = ("NCCL all-reduce of d_hidden (on a second stream under the d_weight GEMM where the cost model says the "
+           "hidden all-reduce pays for the SMs that GEMM spares; see the line's tp_reduce)")
     how = ("partials pushed into every rank's gathered buffer by the forward GEMM epilogue (NVSwitch multimem.st, no "
-           "separate all-gather) + NCCL all-reduce of d_hidden"
-           if exchange == "nvlink" else "NCCL all-gather of [4,S,T] partials + NCCL all-reduce of d_hidden")
+           "separate all-gather) + " + red
+           if exchange == "nvlink" else "NCCL all-gather of [4,S,T] partials + " + red)
     return {
         "workload": f"Qwen2.5-7B lm-head (H={HIDDEN}, V={VOCAB}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
                     "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
@@ -198,6 +200,7 @@ def run_ours(args):
         group = dist.group.WORLD
     _lib.load()
     exchange = "nccl"
+    reduce_how = "nccl"
     if world > 1:
         from verl_b200.utils.kernel import kernels, peer
 
@@ -214,6 +217,9 @@ def run_ours(args):
         exchange = "nvlink" if int(flag.item()) == 1 else "nccl"
         kernels.set_vocab_parallel_exchange(exchange)
         kernels.set_reduce_d_hidden(True, mode=args.tp_reduce)  # the op returns the summed d_hidden
+        reduce_how = args.tp_reduce
+        if reduce_how == "auto":
+            reduce_how = "overlap" if kernels._overlap_plan(args.tokens, HIDDEN, VOCAB // world, world, dev)[0] else "nccl"
 
     T, H, V = args.tokens, HIDDEN, VOCAB
     assert V % world == 0
@@ -410,7 +416,7 @@ def run_ours(args):
             "metric": METRIC, "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(T, world, exchange),
+            "config": workload_config(T, world, exchange), "tp_reduce": reduce_how,
             "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32 * world,
                     "how": "pinned host -> device on a copy stream, double-buffered (step i+1's inputs copy under step "
@@ -457,8 +463,9 @@ def main():
     ap.add_argument("--cpu-tokens", type=int, default=0,
                     help="token sample of the CPU legs (0 = 4096 for cpu_baseline, 2048 per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--tp-reduce", choices=["nccl", "multimem"], default="nccl",
-                    help="N > 1: d_hidden all-reduce by NCCL (default) or fused into the d_hidden GEMM (multimem.red)")
+    ap.add_argument("--tp-reduce", choices=["auto", "nccl", "multimem", "overlap"], default="auto",
+                    help="N > 1: d_hidden all-reduce after the GEMMs (nccl), under the d_weight GEMM (overlap), chosen by the "
+                         "cost model (auto, default) or fused into the d_hidden GEMM (multimem.red)")
     ap.add_argument("--e2e-gather", choices=["ce", "nccl"], default="ce",
                     help="N>1 end-to-end leg: how the replicated hidden is assembled from the per-rank H2D shards")
     ap.add_argument("--tp-exchange", choices=["auto", "nccl", "nvlink"], default="auto",

@@ -151,6 +151,16 @@ int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* 
                     int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
                     void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream);
 
+/* One-shot option of the NEXT vpg_lce_bwd* call on the calling thread (vocab-parallel runs): `d_hidden_ready_event`
+ * (cudaEvent_t) is recorded on the call's stream as soon as d_hidden is complete.  The backward then computes d_hidden
+ * BEFORE its last d_weight GEMM and gives that GEMM the fewest persistent workers that keep its number of scheduling
+ * rounds, so the all-reduce of d_hidden the reference leaves to its callers
+ * (tests/utils/test_linear_cross_entropy_tp.py:313-314) can run on a second stream, on the freed SMs, under the
+ * d_weight GEMM.  reserve_cta_pairs > 0 additionally keeps at least that many CTA pairs (2 SMs each) free during the
+ * d_weight GEMM, at the price of extra scheduling rounds (NCCL's all-reduce kernel only overlaps when all of its
+ * ~16 CTAs are resident at once).  Ignored by vpg_lce_bwd_mcred's fused all-reduce. */
+int vpg_lce_bwd_overlap_next(void* d_hidden_ready_event, int reserve_cta_pairs);
+
 /* Vocab-parallel backward with the d_hidden all-reduce fused into the d_hidden GEMM (the reference leaves this
  * all-reduce to the caller: tests/utils/test_linear_cross_entropy_tp.py:313-314).  d_hidden_mc_f32 is an NVSwitch
  * multicast address bound to an fp32 [T,H] buffer on every rank, zeroed on all ranks (barrier) before the call: the

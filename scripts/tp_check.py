@@ -54,7 +54,8 @@ def main():
     ref = run("nccl", False)
     ok = True
     for tag, mode, inside in (("nvlink", "nvlink", False), ("nvlink+mcred", "nvlink", "multimem"),
-                              ("nvlink+nccl reduce", "nvlink", "nccl"), ("nccl+reduce", "nccl", "nccl")):
+                              ("nvlink+nccl reduce", "nvlink", "nccl"), ("nccl+reduce", "nccl", "nccl"),
+                              ("nvlink+overlapped reduce", "nvlink", "overlap")):
         for rep in range(3):  # repeated: exercises the double-buffered slots and the re-zeroed accumulator
             got = run(mode, inside)
         errs = [float((a.float() - b.float()).abs().max()) for a, b in zip(got, ref)]

@@ -165,6 +165,7 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, C.c_double, c_float, c_void_p, c_void_p, c_void_p,
          c_void_p, c_size_t, c_void_p],
     ),
+    "vpg_lce_bwd_overlap_next": (c_int, [c_void_p, c_int]),
     "vpg_masked_whiten": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],

@@ -49,6 +49,12 @@ static void bind_primary_context() {
 static thread_local int tl_operand_dt = VPG_DT_BF16;
 // fp32 operands (VPG_DT_F32): the two gradient GEMMs of the backward run on 16-bit copies supplied by the caller
 static thread_local const void* tl_hidden16 = nullptr;
+// one-shot option of the NEXT backward call on this thread (vpg_lce_bwd_overlap_next): a cudaEvent_t to record as soon
+// as d_hidden is complete; the backward then computes d_hidden BEFORE the last d_weight GEMM and leaves that GEMM the
+// fewest workers that keep its number of scheduling rounds, so the caller's all-reduce of d_hidden runs on the freed
+// SMs under the d_weight GEMM
+static thread_local void* tl_dh_ready_event = nullptr;
+static thread_local int tl_dw_reserve_pairs = 0;
 static thread_local const void* tl_weight16 = nullptr;
 struct OperandDtypeScope {
     int prev;
@@ -132,7 +138,8 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
         return set_error(VPG_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(attr_err));
     const int64_t units = static_cast<int64_t>(p.num_m_tiles) * p.num_splits;
     if (units <= 0) return VPG_OK;
-    const int workers = static_cast<int>(units < num_workers() ? units : num_workers());
+    int workers = static_cast<int>(units < num_workers() ? units : num_workers());
+    if (p.max_workers > 0 && workers > p.max_workers) workers = p.max_workers;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(static_cast<unsigned>(workers * kCG));
     cfg.blockDim = dim3(kNumThreads);
@@ -428,6 +435,10 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
                   "null pointer argument");
     VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    void* dh_ready_event = tl_dh_ready_event;  // one-shot
+    const int dw_reserve_pairs = tl_dw_reserve_pairs;
+    tl_dh_ready_event = nullptr, tl_dw_reserve_pairs = 0;
+    if (d_hidden_mc_f32) dh_ready_event = nullptr;  // the fused all-reduce variant has its own schedule
     // operand type of the call.  fp32: the recompute runs as TF32 on the fp32 operands like the forward, dlogits are
     // bf16, the two gradient GEMMs read the caller's bf16 copies and write fp32 gradients.
     const int dt = tl_operand_dt;
@@ -490,7 +501,10 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             if ((rc = launch_tc_lmhead<MODE_DS>(ta, tb, p, dt, stream))) return rc;
         }
         const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
-        {  // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
+        // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
+        auto run_d_weight = [&](int max_workers) -> int {
+            int rc = 0;
+            CUtensorMap ta, tb;
             TcParams p{};
             p.num_m_tiles = static_cast<int>(ceil_div(vc, tile_m()));
             p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
@@ -503,11 +517,16 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.ldc = H;
             p.out_mode = f32 ? OUT_F32 : OUT_BF16;
             p.f16 = (dt16 == VPG_DT_F16);
+            p.max_workers = max_workers;
             if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM, dt16))) return rc;
             if ((rc = make_operand_tmap(&tb, hidden16, H, T, H, true, kBlockN, dt16))) return rc;
             if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream))) return rc;
-        }
-        {  // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
+            return VPG_OK;
+        };
+        // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
+        auto run_d_hidden = [&]() -> int {
+            int rc = 0;
+            CUtensorMap ta, tb;
             TcParams p{};
             p.num_m_tiles = m_tiles_t;
             p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
@@ -539,8 +558,33 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             if ((rc = make_operand_tmap(&ta, ds, t_pad, vc_cols, ldds, false, kBlockM, dt16))) return rc;
             if ((rc = make_operand_tmap(&tb, w16_chunk, H, vc, H, true, kBlockN, dt16))) return rc;
             if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream))) return rc;
+            return VPG_OK;
+        };
+        const bool overlap = dh_ready_event && ci == num_chunks - 1;
+        if (!overlap) {
+            if ((rc = run_d_weight(0))) return rc;
+            if ((rc = run_d_hidden())) return rc;
+        } else {
+            // d_hidden first; the event releases the caller's all-reduce, which then runs under the d_weight GEMM on
+            // the SMs that GEMM can spare for free: the fewest workers with the same number of scheduling rounds
+            if ((rc = run_d_hidden())) return rc;
+            VPG_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(dh_ready_event), stream));
+            const int64_t tiles = ceil_div(vc, static_cast<int64_t>(tile_m())) * ceil_div(H, static_cast<int64_t>(kBlockN));
+            const int64_t rounds = ceil_div(tiles, static_cast<int64_t>(num_workers()));
+            int spare_cap = static_cast<int>(ceil_div(tiles, rounds));
+            // at least this many CTA pairs are left to the collective (caller's choice; env override for tuning)
+            const int reserve = env_int("VPG_BWD_RESERVE_PAIRS", dw_reserve_pairs);
+            if (reserve > 0 && spare_cap > num_workers() - reserve) spare_cap = num_workers() - reserve;
+            if ((rc = run_d_weight(spare_cap < 1 ? 1 : spare_cap))) return rc;
         }
     }
+    return VPG_OK;
+}
+
+int vpg_lce_bwd_overlap_next(void* d_hidden_ready_event, int reserve_cta_pairs) {
+    VPG_CHECK_ARG(reserve_cta_pairs >= 0, "reserve_cta_pairs must be >= 0");
+    tl_dh_ready_event = d_hidden_ready_event;
+    tl_dw_reserve_pairs = reserve_cta_pairs;
     return VPG_OK;
 }
 

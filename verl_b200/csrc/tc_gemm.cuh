@@ -107,6 +107,7 @@ struct TcParams {
     int hint_a, hint_b;  // L2 eviction priority of the A / B operand loads: 0 normal, 1 evict-first, 2 evict-last
     int worker_perm;  // 0/1: identity; S > 1: group physical neighbours on residues mod S (see kernel)
     float* accum;  // OUT_F32_ACC: same as out; OUT_BF16_FROM_ACC: fp32 partial to add
+    int max_workers;  // host only: > 0 caps the number of persistent workers (CTA pairs) of this launch
     int ds_stcs;   // MODE_DS: 1 = dlogits stores carry the streaming (evict-first) policy
     int f16;       // 1: the 16-bit operands AND 16-bit outputs (OUT_BF16*, ds) are IEEE fp16 instead of bf16
     long long ld_accum;

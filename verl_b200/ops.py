@@ -159,8 +159,12 @@ def lce_finalize(partials, temperature: float):
 
 
 def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int = 0,
-                 chunk_v: int = 0):
-    """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (bf16 or fp16)."""
+                 chunk_v: int = 0, d_hidden_ready_event: int = 0, reserve_cta_pairs: int = 0):
+    """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (bf16 or fp16).
+
+    d_hidden_ready_event (raw cudaEvent_t, 0 = none): recorded as soon as d_hidden is complete; the d_weight GEMM then
+    runs last and spares SMs (at least reserve_cta_pairs CTA pairs) for the caller's all-reduce
+    (vpg_lce_bwd_overlap_next)."""
     _require_cuda(hidden, weight, labels, lse, eb)
     T, H = hidden.shape
     V = weight.shape[0]
@@ -180,6 +184,8 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
                                       stream_ptr(hidden.device)))
         return d_hidden, d_weight
     with torch.cuda.device(hidden.device):
+        if d_hidden_ready_event:
+            check(lib.vpg_lce_bwd_overlap_next(int(d_hidden_ready_event), int(reserve_cta_pairs)))
         check(lib.vpg_lce_bwd_dt(dt, ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb),
                                  ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset), int(chunk_v),
                                  ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes, stream_ptr(hidden.device)))

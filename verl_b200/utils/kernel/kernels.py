@@ -105,11 +105,57 @@ def set_reduce_d_hidden(enabled: bool, mode: str = "nccl"):
     """True: the backward returns d_hidden already summed over the vocab-parallel group (the reference leaves that
     all-reduce to its callers).  mode "nccl": one all-reduce after the GEMMs.  mode "multimem" (needs the "nvlink"
     exchange and NVSwitch multicast): the d_hidden GEMM's epilogue reduces into every rank's fp32 buffer through the
-    switch (multimem.red) while it runs."""
-    if mode not in ("nccl", "multimem"):
+    switch (multimem.red) while it runs.  mode "overlap": d_hidden is computed before the last d_weight GEMM, which
+    spares the SMs it does not need for its number of scheduling rounds; the NCCL all-reduce runs on a second stream
+    under that GEMM.  mode "auto": "overlap" when `_overlap_plan` says the hidden all-reduce is worth the extra
+    scheduling rounds of the d_weight GEMM (8-way shards of the BASELINE shapes), else "nccl"."""
+    if mode not in ("nccl", "multimem", "overlap", "auto"):
         raise ValueError(f"Invalid d_hidden reduction mode: {mode}")
     _config._tp_reduce_d_hidden = bool(enabled)
     _config._tp_reduce_mode = mode
+
+
+_overlap_streams: dict = {}
+
+
+def _overlap_stream(device):
+    """(second stream, event, raw cudaEvent_t) of `device` for the overlapped d_hidden all-reduce."""
+    idx = torch.device(device).index
+    idx = torch.cuda.current_device() if idx is None else idx
+    cur = _overlap_streams.get(idx)
+    if cur is None:
+        with torch.cuda.device(idx):
+            side = torch.cuda.Stream(device=idx)
+            ready = torch.cuda.Event()
+            ready.record()  # torch creates the cudaEvent_t at the first record
+            ready.synchronize()
+        cur = _overlap_streams[idx] = (side, ready, int(ready.cuda_event))
+    return cur
+
+
+# NCCL's all-reduce kernel only makes progress under a persistent one-CTA-per-SM GEMM when ALL its CTAs (16 channels
+# on an NVSwitch box) are resident at once; measured at 8 GPUs / configs[1]: 8 free SMs -> slower than the serial
+# all-reduce, 16 free SMs -> the all-reduce disappears under the d_weight GEMM (backward 22.3 -> 20.4 ms).
+_OVERLAP_PAIRS = int(os.environ.get("VPG_TP_OVERLAP_PAIRS", "8"))
+_SM_TFLOPS = 9.3          # sustained bf16 TFLOP/s of one SM inside a long step (1380 / 148)
+_ALLREDUCE_BUSBW = 400e9  # bytes/s, NCCL NVLS all-reduce of a few hundred MB on one NVSwitch box
+
+
+def _overlap_plan(T: int, H: int, v_local: int, world: int, device):
+    """-> (pays, reserve_cta_pairs): does hiding the d_hidden all-reduce under the last d_weight GEMM pay for the extra
+    scheduling rounds that GEMM needs when `_OVERLAP_PAIRS` CTA pairs are kept free?  (single-chunk backward assumed:
+    with several vocab chunks the last chunk's GEMM is shorter and the estimate is conservative)"""
+    workers = torch.cuda.get_device_properties(device).multi_processor_count // 2
+    tiles = -(-v_local // 256) * -(-H // 256)
+    free_rounds = -(-tiles // workers)
+    left = workers - _OVERLAP_PAIRS
+    if left < 1:
+        return False, 0
+    reserved_rounds = -(-tiles // min(left, -(-tiles // free_rounds)))
+    round_ms = 2.0 * 256 * 256 * T / (2 * _SM_TFLOPS * 1e12) * 1e3
+    cost_ms = (reserved_rounds - free_rounds) * round_ms
+    allreduce_ms = T * H * 2 * 2.0 * (world - 1) / world / _ALLREDUCE_BUSBW * 1e3
+    return allreduce_ms > 1.5 * cost_ms + 0.2, _OVERLAP_PAIRS
 
 
 def _peer_workspace(group, device):
@@ -245,11 +291,28 @@ def efficient_entropy_backward(
         px.barrier()
         d_hidden = ops.cast_f32_bf16(accum)
     else:
+        reduce = world > 1 and _config._tp_reduce_d_hidden
+        overlap, reserve = False, 0
+        if reduce and _config._tp_reduce_mode in ("overlap", "auto") and hidden.dtype != torch.float32:
+            pays, reserve = _overlap_plan(hidden.shape[0], hidden.shape[1], weight.shape[0], world, hidden.device)
+            overlap = pays or _config._tp_reduce_mode == "overlap"
+        side = ready = None
+        if overlap:
+            side, ready, ready_ptr = _overlap_stream(hidden.device)
         d_hidden, d_weight = ops.lce_backward(
             hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
             label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v,
+            d_hidden_ready_event=ready_ptr if overlap else 0, reserve_cta_pairs=reserve if overlap else 0,
         )
-        if world > 1 and _config._tp_reduce_d_hidden:
+        if overlap:
+            # the kernels recorded `ready` right behind the d_hidden GEMM: the all-reduce starts there, on the SMs the
+            # d_weight GEMM spared, and the caller's stream joins after both
+            main = torch.cuda.current_stream(hidden.device)
+            side.wait_event(ready)
+            with torch.cuda.stream(side):
+                dist.all_reduce(d_hidden, group=dist_process_group)
+            main.wait_stream(side)
+        elif reduce:
             dist.all_reduce(d_hidden, group=dist_process_group)
     if should_return_fp32_grad:
         d_hidden, d_weight = d_hidden.float(), d_weight.float()
