@@ -180,3 +180,19 @@ def test_compat_install_shadows_reference_paths():
     )
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "ok 10" in out.stdout, out.stderr
+
+
+def test_d_hidden_allreduce_overlap_plan():
+    """Cost model behind set_reduce_d_hidden(True, "auto"): hiding the d_hidden all-reduce under the last d_weight GEMM
+    costs that GEMM extra scheduling rounds (16 SMs are kept free for NCCL); it must pick the overlap for the 8-way
+    shards of the BASELINE shapes (measured win, profiles/r1_tp8_dhidden_allreduce_overlap_ab.json) and keep the serial
+    all-reduce at 2 and 4 GPUs, where the extra rounds cost more than the all-reduce takes."""
+    from verl_b200.utils.kernel.kernels import _overlap_plan
+
+    w = 74  # CTA pairs of a 148-SM B200
+    for world, want in ((2, False), (4, False), (8, True)):
+        assert _overlap_plan(65536, 3584, 152064 // world, world, None, workers=w)[0] is want   # configs[1]
+        assert _overlap_plan(65536, 8192, 128256 // world, world, None, workers=w)[0] is want   # configs[3]
+    pays, pairs = _overlap_plan(262144, 5120, 19008, 8, None, workers=w)                        # configs[4]
+    assert pays and pairs == 8
+    assert _overlap_plan(1024, 3584, 19008, 8, None, workers=4) == (False, 0)  # fewer pairs than the reserve

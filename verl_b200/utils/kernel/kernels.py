@@ -141,11 +141,11 @@ _SM_TFLOPS = 9.3          # sustained bf16 TFLOP/s of one SM inside a long step 
 _ALLREDUCE_BUSBW = 400e9  # bytes/s, NCCL NVLS all-reduce of a few hundred MB on one NVSwitch box
 
 
-def _overlap_plan(T: int, H: int, v_local: int, world: int, device):
+def _overlap_plan(T: int, H: int, v_local: int, world: int, device, workers: int = 0):
     """-> (pays, reserve_cta_pairs): does hiding the d_hidden all-reduce under the last d_weight GEMM pay for the extra
     scheduling rounds that GEMM needs when `_OVERLAP_PAIRS` CTA pairs are kept free?  (single-chunk backward assumed:
     with several vocab chunks the last chunk's GEMM is shorter and the estimate is conservative)"""
-    workers = torch.cuda.get_device_properties(device).multi_processor_count // 2
+    workers = workers or torch.cuda.get_device_properties(device).multi_processor_count // 2  # CTA pairs
     tiles = -(-v_local // 256) * -(-H // 256)
     free_rounds = -(-tiles // workers)
     left = workers - _OVERLAP_PAIRS
