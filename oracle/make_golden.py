@@ -574,6 +574,7 @@ def gen_rmpad(ref):
 
     out = {}
     torch.manual_seed(23)
+    np.random.seed(23)  # create_random_mask (verl/utils/model.py:176-216) draws from numpy's global RNG
     B, S = 8, 64
     if ref.model is not None:
         mask = ref.model.create_random_mask(torch.zeros(B, S, dtype=torch.long), max_ratio_of_valid_token=0.8,

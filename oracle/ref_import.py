@@ -13,7 +13,9 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("VERL_REFERENCE_ROOT", "/root/reference")
+_SNAPSHOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")  # oracle/vendor_ref.py (travels to the GPU box)
+REFERENCE_ROOT = os.environ.get("VERL_REFERENCE_ROOT") or (
+    "/root/reference" if os.path.isdir("/root/reference/verl") else _SNAPSHOT)
 
 
 def available() -> bool:
@@ -74,6 +76,14 @@ def load():
         ns.model = None
     _loaded = ns
     return ns
+
+
+def load_kernel():
+    """-> (kernels module, linear_cross_entropy module) of the reference's Triton op (needs triton; runs on a GPU only)."""
+    load()
+    _pkg("verl.utils.kernel", os.path.join(REFERENCE_ROOT, "verl", "utils", "kernel"))
+    return (importlib.import_module("verl.utils.kernel.kernels"),
+            importlib.import_module("verl.utils.kernel.linear_cross_entropy"))
 
 
 def load_functions(rel_path: str, names, namespace: dict) -> dict:

@@ -99,3 +99,65 @@ def test_driver_ops_vs_oracle_config_shapes(B, P, L, dev):
     data = compute_advantage(data, "rloo")
     torch.testing.assert_close(data.batch["advantages"].cpu(), port.rloo_outcome_advantage(want_r, rmask, uid),
                                rtol=1e-5, atol=1e-6)
+
+
+def test_driver_ops_accept_host_tensors_like_the_reference_driver(dev):
+    """The reference runs these on the DRIVER with CPU tensors (verl/trainer/ppo/ray_trainer.py:1283-1305).  Host tensors
+    in -> staged through pinned buffers -> kernels on the device -> host tensors out (verl_b200/staging.py); results
+    identical to the device-tensor call."""
+    from verl_b200.trainer.ppo import core_algos as ca
+    from verl_b200.trainer.ppo.metric_utils import compute_data_metrics
+    from verl_b200.trainer.ppo.ray_trainer import apply_kl_penalty, compute_advantage
+
+    g = load_golden("driver")
+    host = dict(response_mask=torch.from_numpy(g["rmask"]), token_level_scores=torch.from_numpy(g["scores"]),
+                old_log_probs=torch.from_numpy(g["old"]), ref_log_prob=torch.from_numpy(g["ref"]),
+                values=torch.from_numpy(g["values"]), attention_mask=torch.from_numpy(g["attn"]))
+    B = host["token_level_scores"].shape[0]
+    uid = np.array([f"u{i // 2}" for i in range(B)], dtype=object)
+    outs = []
+    for where in ("cpu", dev):
+        data = Data(**{k: v.clone().to(where) for k, v in host.items()})
+        data.non_tensor_batch["uid"] = uid
+        data, m = apply_kl_penalty(data, ca.FixedKLController(0.05), "low_var_kl")
+        data = compute_advantage(data, ca.AdvantageEstimator.GAE, gamma=0.99, lam=0.95)
+        gae = (data.batch["advantages"], data.batch["returns"])
+        data = compute_advantage(data, ca.AdvantageEstimator.GRPO)
+        assert data.batch["advantages"] is data.batch["returns"]  # the reference returns the SAME tensor twice
+        dm = compute_data_metrics(data, use_critic=True)
+        for t in (data.batch["token_level_rewards"], *gae, data.batch["advantages"]):
+            assert t.device.type == torch.device(where).type, (where, t.device)
+        outs.append((m, data.batch["token_level_rewards"].cpu(), gae[0].cpu(), gae[1].cpu(),
+                     data.batch["advantages"].cpu(), dm))
+    (m0, r0, a0, t0, g0, d0), (m1, r1, a1, t1, g1, d1) = outs
+    assert m0 == m1 and d0 == d1
+    for x, y in ((r0, r1), (a0, a1), (t0, t1), (g0, g1)):
+        assert torch.equal(x, y)
+    torch.testing.assert_close(r0, torch.from_numpy(g["klr|low_var_kl|rewards"]) if "klr|low_var_kl|rewards" in g.files
+                               else r1, rtol=1e-5, atol=1e-7)
+
+
+def test_host_tensor_losses_keep_autograd(dev):
+    """compute_policy_loss / agg_loss / masked_mean on HOST tensors that require grad: the graph runs on the device and the
+    leaf gradient comes back on the host, equal to the device-tensor call."""
+    from verl_b200.trainer.ppo import core_algos as ca
+    from verl_b200.utils import torch_functional as F
+
+    torch.manual_seed(5)
+    B, L = 7, 33
+    old = -torch.rand(B, L) * 3
+    adv = torch.randn(B, L)
+    mask = (torch.rand(B, L) < 0.8).long()
+    grads = []
+    for where in ("cpu", dev):
+        lp = (old + 0.05 * torch.ones(B, L)).to(where).requires_grad_(True)
+        loss, clipfrac, kl, clip_low = ca.compute_policy_loss(old.to(where), lp, adv.to(where), mask.to(where),
+                                                              cliprange=0.2, clip_ratio_c=3.0)
+        extra = F.masked_mean(lp * lp, mask.to(where))
+        (loss + 0.1 * extra).backward()
+        assert loss.device.type == torch.device(where).type and lp.grad.device.type == torch.device(where).type
+        grads.append((float(loss), float(extra), lp.grad.cpu()))
+    assert grads[0][0] == grads[1][0] and grads[0][1] == grads[1][1]
+    assert torch.equal(grads[0][2], grads[1][2])
+    with pytest.raises(NotImplementedError):
+        F.masked_sum(torch.ones(2, 2, requires_grad=True), torch.ones(2, 2))

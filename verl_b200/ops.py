@@ -26,7 +26,8 @@ def _lib_():
 def _require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
-            raise RuntimeError("verl_b200 ops require CUDA tensors (there is no CPU fallback)")
+            raise RuntimeError("verl_b200 ops require CUDA tensors (there is no CPU fallback; the reference-named "
+                               "driver-side functions stage host tensors through verl_b200.staging)")
 
 
 def _f32c(t: torch.Tensor | None) -> torch.Tensor | None:
@@ -245,6 +246,8 @@ def logits_partials(logits2d, labels=None, label_offset: int = 0):
 
 def logits_stats_backward(logits2d, labels, lse, entropy, g_lp, g_ent):
     _require_cuda(logits2d)
+    if logits2d.dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError(f"logits_stats_backward reads fp32 or bf16 logits, got {logits2d.dtype} (upcast first)")
     T, V = logits2d.shape
     assert logits2d.is_contiguous()
     d = torch.empty_like(logits2d)

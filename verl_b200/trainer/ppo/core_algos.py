@@ -27,6 +27,7 @@ import numpy as np
 import torch
 
 from ... import ops
+from ...staging import staged
 
 __all__ = [
     "register_policy_loss",
@@ -177,6 +178,7 @@ def group_ids_from_index(index) -> tuple[np.ndarray, int]:
 
 
 @register_adv_est(AdvantageEstimator.GAE)
+@staged
 def compute_gae_advantage_return(
     token_level_rewards: torch.Tensor,
     values: torch.Tensor,
@@ -195,6 +197,7 @@ def compute_gae_advantage_return(
 
 
 @register_adv_est(AdvantageEstimator.GRPO)
+@staged
 def compute_grpo_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -232,6 +235,7 @@ def _cfg_get(config, key, default):
 
 
 @register_adv_est(AdvantageEstimator.GRPO_PASSK)
+@staged
 def compute_grpo_passk_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -249,6 +253,7 @@ def compute_grpo_passk_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.REINFORCE_PLUS_PLUS_BASELINE)
+@staged
 def compute_reinforce_plus_plus_baseline_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -264,6 +269,7 @@ def compute_reinforce_plus_plus_baseline_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.RLOO)
+@staged
 def compute_rloo_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -277,6 +283,7 @@ def compute_rloo_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.OPO)
+@staged
 def compute_opo_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -290,6 +297,7 @@ def compute_opo_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.REINFORCE_PLUS_PLUS)
+@staged
 def compute_reinforce_plus_plus_outcome_advantage(
     token_level_rewards: torch.Tensor, response_mask: torch.Tensor, config: Optional[Any] = None, **kwargs
 ) -> tuple[torch.Tensor, torch.Tensor]:
@@ -303,6 +311,7 @@ def compute_reinforce_plus_plus_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.REMAX)
+@staged
 def compute_remax_outcome_advantage(
     token_level_rewards: torch.Tensor,
     reward_baselines: torch.Tensor,
@@ -318,6 +327,7 @@ def compute_remax_outcome_advantage(
 
 
 @register_adv_est(AdvantageEstimator.GPG)
+@staged
 def compute_gpg_outcome_advantage(
     token_level_rewards: torch.Tensor,
     response_mask: torch.Tensor,
@@ -333,6 +343,7 @@ def compute_gpg_outcome_advantage(
     return _outcome("gpg", token_level_rewards, response_mask, index, epsilon=float(epsilon), f_norm=float(f_norm))
 
 
+@staged
 def compute_rewards(token_level_scores, old_log_prob, ref_log_prob, kl_ratio):
     """token_level_scores - (old_log_prob - ref_log_prob) * kl_ratio (core_algos.py:670-684)."""
     kl, _ = ops.kl_penalty_fwd(old_log_prob, ref_log_prob, "kl", want_grad=False)
@@ -355,6 +366,7 @@ class _AggLoss(torch.autograd.Function):
         return (d * g).view(ctx.shape).to(ctx.in_dtype), None, None
 
 
+@staged
 def agg_loss(loss_mat: torch.Tensor, loss_mask: torch.Tensor, loss_agg_mode: str):
     """Aggregate a (bs, response_length) loss matrix into a scalar (core_algos.py:686-719).
 
@@ -386,6 +398,7 @@ class _KlPenalty(torch.autograd.Function):
         return d_lp, d_ref, None
 
 
+@staged
 def kl_penalty(logprob: torch.FloatTensor, ref_logprob: torch.FloatTensor, kl_penalty) -> torch.FloatTensor:
     """kl / k1, abs, mse / k2, low_var_kl / k3 (core_algos.py:1034-1069); "full" and unknown kinds raise
     NotImplementedError like the reference."""
@@ -428,6 +441,7 @@ class _PolicyLoss(torch.autograd.Function):
         return g_lp, None, None, None, g_ent, None, None
 
 
+@staged
 def compute_policy_loss(
     old_log_prob,
     log_prob,
@@ -459,6 +473,7 @@ def compute_policy_loss(
 
 
 @register_policy_loss("gpg")
+@staged
 def compute_policy_loss_gpg(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean", config=None):
     """GPG policy loss (core_algos.py:797-815): agg_loss(-log_prob * advantages); the three statistics are 0."""
     cfg = dict(cliprange_low=0.2, cliprange_high=0.2, clip_ratio_c=3.0, loss_agg_mode=loss_agg_mode, pg_kind="gpg")
@@ -492,6 +507,7 @@ def _policy_loss_cfg(config, name, default):
 
 
 @register_policy_loss("clip_cov")
+@staged
 def compute_policy_loss_clip_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean",
                                  config=None):
     """Clip-Cov policy loss (core_algos.py:818-905).  A random subset (size max(int(clip_cov_ratio * sum mask), 1)) of the
@@ -530,6 +546,7 @@ def compute_policy_loss_clip_cov(old_log_prob, log_prob, advantages, response_ma
 
 
 @register_policy_loss("kl_cov")
+@staged
 def compute_policy_loss_kl_cov(old_log_prob, log_prob, advantages, response_mask, loss_agg_mode="token-mean",
                                config=None):
     """KL-Cov policy loss (core_algos.py:908-972): the max(1, int(N_valid * kl_cov_ratio)) valid tokens with the largest
@@ -546,6 +563,7 @@ def compute_policy_loss_kl_cov(old_log_prob, log_prob, advantages, response_mask
     return pg_loss, torch.tensor(0.0), out3[0], torch.tensor(0.0)
 
 
+@staged
 def compute_entropy_loss(logits, response_mask, loss_agg_mode: str = "token-mean"):
     """core_algos.py:975-989 (kept by the reference for backward compatibility): agg_loss of the per-token entropy of
     materialised logits [bs, response_length, vocab]."""
@@ -573,6 +591,7 @@ class _ValueLoss(torch.autograd.Function):
         return (d * g).view(ctx.meta[0]).to(ctx.meta[1]), None, None, None, None, None
 
 
+@staged
 def compute_value_loss(
     vpreds: torch.Tensor,
     returns: torch.Tensor,
@@ -587,6 +606,7 @@ def compute_value_loss(
     return _ValueLoss.apply(vpreds, returns, values, response_mask, float(cliprange_value), loss_agg_mode)
 
 
+@staged
 def fused_actor_loss(
     old_log_prob,
     log_prob,
@@ -628,14 +648,23 @@ def fused_actor_loss(
 def compute_pf_ppo_reweight_data(data, reweight_method: str = "pow", weight_pow: float = 2.0):
     """verl/trainer/ppo/core_algos.py:1072-1148: resample the batch with replacement, rows weighted by their score.
 
-    ``data`` is anything with DataProto's ``.batch`` (mapping of [B, ...] CUDA tensors incl. "token_level_scores"),
+    ``data`` is anything with DataProto's ``.batch`` (mapping of [B, ...] tensors incl. "token_level_scores"; host
+    tensors, as on the reference's driver, are staged through verl_b200.staging and come back on the host),
     ``.non_tensor_batch`` (numpy arrays or lists) and ``.meta_info``.  The row sums run on the device, the B weights and
     the multinomial draw stay on the host generator exactly as in the reference (a seeded run resamples the same rows),
     and every tensor of the batch is resampled by ONE row-gather pass.  Returns a shallow copy of ``data`` with the three
     fields replaced (the reference deep-copies everything first and then overwrites the same three fields)."""
     import copy
 
+    from ... import staging
+
     tls = data.batch["token_level_scores"]
+    on_host = not tls.is_cuda
+    if on_host:  # stage the whole batch once: every tensor is row-gathered on the device
+        dev_batch = {k: staging.to_device(v) if not v.is_cuda else v for k, v in data.batch.items()}
+        tls = dev_batch["token_level_scores"]
+    else:
+        dev_batch = data.batch
     ones = torch.ones(tls.shape, dtype=torch.uint8, device=tls.device)
     scores = ops.masked_row_sums(tls, ones)[0].view(tls.shape[:-1]).cpu()
     if reweight_method == "pow":
@@ -650,7 +679,9 @@ def compute_pf_ppo_reweight_data(data, reweight_method: str = "pow", weight_pow:
     batch_size = scores.shape[0]
     sample_indices = torch.multinomial(weights, batch_size, replacement=True)
     idx_dev = sample_indices.to(tls.device)
-    resampled_batch = {key: ops.gather_rows(tensor, idx_dev) for key, tensor in data.batch.items()}
+    resampled_batch = {key: ops.gather_rows(tensor, idx_dev) for key, tensor in dev_batch.items()}
+    if on_host:
+        resampled_batch = {key: staging.to_host(tensor) for key, tensor in resampled_batch.items()}
     sample_indices_np = sample_indices.numpy()
     resampled_non_tensor_batch = {}
     for key, array in getattr(data, "non_tensor_batch", {}).items():

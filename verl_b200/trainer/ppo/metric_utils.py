@@ -6,14 +6,14 @@ from __future__ import annotations
 
 from typing import Any
 
-from ... import ops
+from ... import ops, staging
 
 __all__ = ["compute_data_metrics"]
 
 
 def compute_data_metrics(batch, use_critic: bool = True) -> dict[str, Any]:
     b = batch.batch
-    out = ops.data_metrics(b["token_level_scores"], b["token_level_rewards"], b["advantages"], b["returns"],
+    out = staging.call(ops.data_metrics, b["token_level_scores"], b["token_level_rewards"], b["advantages"], b["returns"],
                            b["values"] if use_critic else None, b["response_mask"], b["attention_mask"]).tolist()
     metrics: dict[str, Any] = {}
     for name in ("critic/score", "critic/rewards", "critic/advantages", "critic/returns"):

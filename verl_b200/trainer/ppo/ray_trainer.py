@@ -3,14 +3,15 @@ apply_kl_penalty :153-193, compute_response_mask :196-211, compute_advantage :21
 
 The Ray trainer itself (RayPPOTrainer, resource pools, worker groups) is out of scope.  ``data`` is duck-typed: any
 object with ``.batch`` (mapping name -> tensor; a TensorDict or a plain dict), ``.non_tensor_batch`` (mapping) and
-``.meta_info`` works — verl's DataProto does.  Tensors must be on the GPU (the reference runs these on the driver's CPU
-tensors, ray_trainer.py:1291-1305; there is no CPU fallback here)."""
+``.meta_info`` works — verl's DataProto does.  The reference runs these on the driver's CPU tensors
+(ray_trainer.py:1283-1305): host tensors are staged to the current CUDA device through pinned buffers, the kernels run
+there, and the results are returned on the host (verl_b200/staging.py — input staging, no host arithmetic)."""
 
 from __future__ import annotations
 
 import torch
 
-from ... import ops
+from ... import ops, staging
 from . import core_algos
 from .core_algos import AdvantageEstimator
 
@@ -25,8 +26,8 @@ def apply_kl_penalty(data, kl_ctrl, kl_penalty="kl"):
     batch_size = scores.shape[0]
     beta = kl_ctrl.value
     with torch.no_grad():
-        rewards, cur = ops.kl_reward(scores, batch["old_log_probs"], batch["ref_log_prob"], batch["response_mask"],
-                                     kl_penalty, float(beta))
+        rewards, cur = staging.call(ops.kl_reward, scores, batch["old_log_probs"], batch["ref_log_prob"],
+                                    batch["response_mask"], kl_penalty, float(beta))
     current_kl = cur.item()
     kl_ctrl.update(current_kl=current_kl, n_steps=batch_size)
     batch["token_level_rewards"] = rewards
@@ -48,8 +49,13 @@ def compute_advantage(data, adv_estimator, gamma=1.0, lam=1.0, num_repeat=1, nor
         advantages, returns = core_algos.compute_gae_advantage_return(
             token_level_rewards=batch["token_level_rewards"], values=batch["values"],
             response_mask=batch["response_mask"], gamma=gamma, lam=lam)
-        if config is not None and config.get("use_pf_ppo", False):
-            raise NotImplementedError("pf_ppo resampling reshuffles the DataProto on the driver; out of scope")
+        batch["advantages"] = advantages
+        batch["returns"] = returns
+        if config is not None and core_algos._cfg_get(config, "use_pf_ppo", False):  # ray_trainer.py:256-261
+            pf = core_algos._cfg_get(config, "pf_ppo", None)
+            return core_algos.compute_pf_ppo_reweight_data(
+                data, core_algos._cfg_get(pf, "reweight_method", "pow"), core_algos._cfg_get(pf, "weight_pow", 2.0))
+        return data
     elif adv_estimator == AdvantageEstimator.GRPO:
         advantages, returns = core_algos.compute_grpo_outcome_advantage(
             token_level_rewards=batch["token_level_rewards"], response_mask=batch["response_mask"],

@@ -64,6 +64,8 @@ class _VocabParallelEntropy(torch.autograd.Function):
     def forward(ctx, vocab_parallel_logits: torch.Tensor, group=None) -> torch.Tensor:
         lead = vocab_parallel_logits.shape[:-1]
         x = vocab_parallel_logits.reshape(-1, vocab_parallel_logits.shape[-1])
+        if x.dtype not in (torch.float32, torch.bfloat16):  # the kernels read fp32 / bf16; save what they will read
+            x = x.float()
         _, entropy, lse, _ = _merged_stats(x, None, group)
         ctx.save_for_backward(x, lse, entropy)
         ctx.in_shape, ctx.in_dtype = vocab_parallel_logits.shape, vocab_parallel_logits.dtype
@@ -81,6 +83,8 @@ class _VocabParallelLogProbs(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits: torch.Tensor, labels: torch.Tensor, group=None) -> torch.Tensor:
         x = logits.reshape(-1, logits.shape[-1])
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            x = x.float()
         lab = labels.reshape(-1).to(torch.int64).contiguous()
         logprobs, _, lse, _ = _merged_stats(x, lab, group)
         rank, _ = _rank_world(group)

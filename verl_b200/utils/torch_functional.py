@@ -14,6 +14,7 @@ from __future__ import annotations
 import torch
 
 from .. import bert_padding, ops
+from ..staging import staged
 
 __all__ = [
     "gather_from_labels",
@@ -35,8 +36,18 @@ __all__ = [
 ]
 
 
+def _no_autograd(name, t):
+    """These three are forward-only kernels here; the reference versions are differentiable torch compositions whose
+    in-tree callers all run under no_grad.  Fail loudly instead of returning a silently detached result."""
+    if torch.is_grad_enabled() and t.requires_grad:
+        raise NotImplementedError(f"verl_b200.{name} has no backward: call it under torch.no_grad() (masked_mean, "
+                                  "agg_loss and logprobs_from_logits are the differentiable entry points)")
+
+
+@staged
 def gather_from_labels(data, label):
     """verl/utils/torch_functional.py:49-61 — data (..., V), label (...) -> (...)."""
+    _no_autograd("gather_from_labels", data)
     flat = data.reshape(-1, data.shape[-1]).contiguous()
     idx = label.reshape(-1).to(torch.int64) + torch.arange(flat.shape[0], device=flat.device) * flat.shape[1]
     return ops.gather_rows(flat.view(-1, 1), idx).view(label.shape)
@@ -81,6 +92,7 @@ def _stats(logits, labels, want_lp, want_ent):
     return lp, ent
 
 
+@staged
 def logprobs_from_logits(logits, labels, inplace_backward=True):
     """verl/utils/torch_functional.py:64-92.  Output has logits' dtype and shape logits.shape[:-1]."""
     lp, _ = _stats(logits, labels, True, False)
@@ -107,12 +119,14 @@ def clip_by_value(x, tensor_min, tensor_max):
     return torch.max(torch.min(x, tensor_max), tensor_min)
 
 
+@staged
 def entropy_from_logits(logits: torch.Tensor):
     """verl/utils/torch_functional.py:145-149.  Output has logits' dtype."""
     _, ent = _stats(logits, None, False, True)
     return ent.view(logits.shape[:-1]).to(logits.dtype)
 
 
+@staged
 def entropy_from_logits_with_chunking(logits: torch.Tensor, chunk_size: int = 2048):
     """verl/utils/torch_functional.py:152-160 — returns fp32; chunking is unnecessary here (one pass, no temporaries)."""
     _, ent = _stats(logits, None, False, True)
@@ -154,13 +168,16 @@ def _axis_sums(values, mask, axis):
     return s.view(out_shape), c.view(out_shape)
 
 
+@staged
 def masked_sum(values, mask, axis=None):
     """verl/utils/torch_functional.py:163-168: (where(mask.bool(), values, 0) * mask).sum(axis)."""
+    _no_autograd("masked_sum", values)
     if axis is None:
         return ops.masked_sums(values, mask.expand_as(values))[0].to(torch.float32)
     return _axis_sums(values, mask.expand_as(values), axis)[0]
 
 
+@staged
 def masked_mean(values, mask, axis=None):
     """verl/utils/torch_functional.py:171-185: masked_sum / (mask.sum(axis) + 1e-8)."""
     mask = mask.expand_as(values)
@@ -170,6 +187,7 @@ def masked_mean(values, mask, axis=None):
     return s / (c + 1e-8)
 
 
+@staged
 def masked_var(values, mask, unbiased=True):
     """verl/utils/torch_functional.py:188-203"""
     mean = masked_mean(values, mask)
@@ -186,8 +204,10 @@ def masked_var(values, mask, unbiased=True):
     return variance
 
 
+@staged
 def masked_whiten(values, mask, shift_mean=True):
     """verl/utils/torch_functional.py:206-223 (two sweeps: statistics, then normalise)."""
+    _no_autograd("masked_whiten", values)
     return ops.masked_whiten(values, mask.expand_as(values), shift_mean).view(values.shape)
 
 
@@ -198,12 +218,14 @@ def get_response_mask(response_id: torch.Tensor, eos_token: int | list[int] = 2,
 
 
 # ------------------------------------------------------------------------------------------------- rmpad
+@staged
 def get_unpad_data(attention_mask):
     """verl/utils/torch_functional.py:629-638 -> (indices, cu_seqlens, max_seqlen_in_batch)."""
     indices, _, cu_seqlens, max_seqlen = ops.unpad_indices(attention_mask)
     return indices, cu_seqlens, max_seqlen
 
 
+@staged
 def log_probs_from_logits_response_rmpad(input_ids, attention_mask, logits_rmpad, response_length):
     """verl/utils/torch_functional.py:438-462"""
     batch_size, seqlen = input_ids.shape
@@ -217,6 +239,7 @@ def log_probs_from_logits_response_rmpad(input_ids, attention_mask, logits_rmpad
     return full_output.squeeze(-1)[:, -response_length - 1 : -1]
 
 
+@staged
 def log_probs_from_logits_all_rmpad(input_ids_rmpad, logits_rmpad, indices, batch_size, seqlen, response_length):
     """verl/utils/torch_functional.py:465-490"""
     input_ids_rmpad = input_ids_rmpad.transpose(0, 1)  # transpose back to [total_nnz, 1]
@@ -229,6 +252,7 @@ def log_probs_from_logits_all_rmpad(input_ids_rmpad, logits_rmpad, indices, batc
     return full_output.squeeze(-1)[:, -response_length - 1 : -1]
 
 
+@staged
 def log_probs_from_logits_response(input_ids, logits, response_length):
     """verl/utils/torch_functional.py:421-435: logits [B,S,V] = model(input_ids) -> log-probs of the last
     ``response_length`` tokens, [B, response_length]."""
