@@ -1,20 +1,27 @@
 #!/usr/bin/env python
 """Benchmark of the per-token policy-gradient hot path (BASELINE.json metric: fused lm-head logprob+entropy tokens/s
-at Qwen2.5-7B shape, 1-8 B200).
+at Qwen2.5-7B shape, 1-8 B200; % of the BF16 tensor-core peak).
 
-One "step" = one pass of the hot path over one rmpad micro-batch of synthetic hidden states:
-    fused lm-head forward (log-prob + entropy, logits never materialised)
-    -> fused PPO actor loss (clip / dual-clip, entropy bonus, low-var KL, token-mean) forward + closed-form gradient
-    -> fused lm-head backward (recompute tiles -> d_hidden, d_weight)
-through the public API (linear_cross_entropy autograd op + core_algos.fused_actor_loss).
+    python bench.py [--config c1|c2|c3|c4|c5] [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--tokens T]
+One "step" = one pass of the hot path over one batch of synthetic input, through the public (reference-named) API:
 
-N = 1: BASELINE configs[1] (H=3584, V=152064, T=65536 rmpad tokens).  N > 1 (torchrun): the same micro-batch with the
-lm-head weight vocab-parallel over N ranks (V/N rows each), one all-gather of the packed per-token partials in the
-forward and one all-reduce of d_hidden in the backward -> strong scaling.
---impl reference: the reference algorithm's CPU path (oracle port, all host threads) on a bounded token sample.
-Prints ONE JSON line on rank 0.
+  c2 (default, the configuration the metric is quoted on)  Qwen2.5-7B lm-head, H=3584 V=152064, rmpad T=65536:
+      fused lm-head forward (log-prob + entropy, logits never materialised) -> fused PPO actor loss (clip / dual-clip,
+      entropy bonus, low-var KL, token-mean) forward + closed-form gradient -> fused lm-head backward
+  c1  Qwen2.5-0.5B, H=896 V=151936, GRPO batch 8 prompts x 5 rollouts x 512 tokens: lm-head fwd -> GRPO outcome
+      advantage (uid groups) -> PPO clip loss -> lm-head bwd
+  c3  Qwen2.5-VL-7B GRPO actor update: mini-batch of 128 sequences (16 uid x 8) x (1k prompt + 1k response) in
+      micro-batches of 16 through fused_actor_step (response-window rows only), KL loss low_var_kl 0.01, token-mean
+  c4  Llama-3-70B lm-head, H=8192 V=128256, T=65536 (vocab-parallel over the N ranks)
+  c5  Qwen2.5-32B DAPO micro-batch, H=5120 V=152064, T=262144 (16 x 16384), clip 0.2/0.28, dual-clip c=10, entropy bonus
+
+N > 1 (torchrun): the lm-head weight is vocab-parallel over N ranks (V/N rows each); the per-token partials are pushed
+into every rank's gathered buffer by the forward GEMM epilogue and d_hidden is all-reduced inside the d_weight GEMM
+kernel (NVLS) -> strong scaling.  --impl reference: the reference's own CPU implementation of the path (snapshot under
+oracle/_ref, else the oracle port) on all host threads, on a bounded sample of the same workload.
+Prints ONE JSON line on rank 0.  A parity probe (fp32 PyTorch from the full weight, sampled rows) runs outside the timed
+region at every N and is reported as "parity".
 """
 
 from __future__ import annotations
@@ -30,25 +37,52 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-HIDDEN, VOCAB, TOKENS = 3584, 152064, 65536  # Qwen2.5-7B lm-head, rmpad 64k tokens (BASELINE.json configs[1])
-METRIC = "fused lm-head logprob+entropy fwd+bwd tokens/s (Qwen2.5-7B shape)"
-LOSS_CFG = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0, loss_agg_mode="token-mean",
-                entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
+LOSS_C2 = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0, loss_agg_mode="token-mean",
+               entropy_coeff=1e-3, kl_loss_coef=0.01, kl_loss_type="low_var_kl")
+LOSS_C1 = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.2, clip_ratio_c=3.0, loss_agg_mode="token-mean",
+               entropy_coeff=1e-3, kl_loss_coef=0.0, kl_loss_type="low_var_kl")
+LOSS_C5 = dict(cliprange=0.2, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=10.0, loss_agg_mode="token-mean",
+               entropy_coeff=1e-3, kl_loss_coef=0.0, kl_loss_type="low_var_kl")  # recipe/dapo/run_dapo_qwen2.5_32b.sh:14-15,78
+LOSS_C3 = dict(clip_ratio=0.2, entropy_coeff=0.0, use_kl_loss=True, kl_loss_coef=0.01, kl_loss_type="low_var_kl",
+               loss_agg_mode="token-mean")  # examples/grpo_trainer/run_qwen2_5_vl-7b.sh:19-22
+
+CONFIGS = {
+    "c1": dict(kind="grpo", model="Qwen2.5-0.5B", H=896, V=151936, B=40, L=512, T=40 * 512, n=5, loss=LOSS_C1,
+               what="GRPO batch 8 prompts x 5 rollouts x 512 tokens: fused lm-head logprob+entropy fwd -> GRPO group "
+                    "advantage -> PPO clip loss -> fused bwd"),
+    "c2": dict(kind="lce", model="Qwen2.5-7B", H=3584, V=152064, T=65536, loss=LOSS_C2,
+               what="rmpad T=65536 tokens: fused logprob+entropy fwd -> PPO clip/dual-clip + entropy bonus + low_var_kl "
+                    "token-mean loss -> fused bwd (d_hidden, d_weight)"),
+    "c3": dict(kind="actor", model="Qwen2.5-VL-7B", H=3584, V=152064, B=128, micro=16, P=1024, L=1024, n=8, loss=LOSS_C3,
+               what="GRPO actor update of one mini-batch: 128 sequences (16 uid x 8 rollouts) x (<=1k prompt + <=1k "
+                    "response), micro-batches of 16 through fused_actor_step, KL loss low_var_kl 0.01, token-mean"),
+    "c4": dict(kind="lce", model="Llama-3-70B", H=8192, V=128256, T=65536, loss=LOSS_C2,
+               what="rmpad T=65536 tokens: fused logprob+entropy fwd -> PPO loss -> fused bwd, vocab-parallel lm-head"),
+    "c5": dict(kind="lce", model="Qwen2.5-32B", H=5120, V=152064, T=262144, loss=LOSS_C5,
+               what="DAPO micro-batch 16 x 16384 = 262144 tokens: fused logprob+entropy fwd -> dual-clip (c=10) PPO + "
+                    "entropy bonus, token-mean -> fused bwd"),
+}
 
 
-def workload_config(T, world, exchange="nvlink"):
+def metric_name(cfg):
+    return f"fused lm-head logprob+entropy fwd+bwd tokens/s ({cfg['model']} shape)"
+
+
+def workload_config(name, cfg, world, exchange="nvlink", reduce_how="fused"):
     """`config` of the JSON line — identical for both arms (the reference arm times a bounded sample of it)."""
-    red = ("NCCL all-reduce of d_hidden (on a second stream under the d_weight GEMM where the cost model says the "
-           "hidden all-reduce pays for the SMs that GEMM spares; see the line's tp_reduce)")
+    red = {"fused": "d_hidden all-reduced INSIDE the d_weight GEMM kernel (NVLS multimem.ld_reduce / multimem.st by its idle warps)",
+           "overlap": "NCCL all-reduce of d_hidden on a second stream under the d_weight GEMM",
+           "nccl": "NCCL all-reduce of d_hidden after the GEMMs",
+           "multimem": "multimem.red of d_hidden from the d_hidden GEMM epilogue"}.get(reduce_how, reduce_how)
     how = ("partials pushed into every rank's gathered buffer by the forward GEMM epilogue (NVSwitch multimem.st, no "
-           "separate all-gather) + " + red
-           if exchange == "nvlink" else "NCCL all-gather of [4,S,T] partials + " + red)
+           "separate all-gather) + " if exchange == "nvlink" else "NCCL all-gather of [4,S,T] partials + ") + red
+    hidden_mb = cfg["T"] * cfg["H"] * 2 / 1e6 if "T" in cfg else None
     return {
-        "workload": f"Qwen2.5-7B lm-head (H={HIDDEN}, V={VOCAB}), rmpad T={T} tokens: fused logprob+entropy fwd -> "
-                    "PPO clip/dual-clip + entropy bonus + low_var_kl token-mean loss -> fused bwd (d_hidden, d_weight)",
+        "workload": f"BASELINE configs[{int(name[1]) - 1}] ({name}): {cfg['model']} lm-head (H={cfg['H']}, V={cfg['V']}), {cfg['what']}",
         "parallelism": "single GPU" if world == 1 else f"vocab-parallel lm-head over {world} GPUs (V/{world} rows each), " + how,
-        "l2": "inputs exceed L2 (hidden 470 MB + weight shard >= 136 MB per step)",
-        "loss": LOSS_CFG,
+        "l2": "inputs exceed L2 (hidden %s MB + weight shard %.0f MB per step)" % (
+            "%.0f" % hidden_mb if hidden_mb else "~90/micro-batch", cfg["V"] / world * cfg["H"] * 2 / 1e6),
+        "loss": cfg["loss"],
     }
 
 
@@ -110,80 +144,242 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
 
 
+class EnergyMeter:
+    """NVML total-energy counter (mJ since driver load) of one GPU: joules of a region = difference of two reads."""
+
+    def __init__(self, index: int):
+        self.h = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.read()
+        except Exception:
+            self.h = None
+
+    def read(self):
+        if self.h is None:
+            return None
+        try:
+            return self.nv.nvmlDeviceGetTotalEnergyConsumption(self.h) / 1e3
+        except Exception:
+            self.h = None
+            return None
+
+
 # ----------------------------------------------------------------------------------------------- CPU reference arm
-_CPU_INPUTS: dict = {}
+_CPU: dict = {}
 
 
-def cpu_reference_sample(sample_tokens: int, threads: int, repeats: int = 1):
-    """The reference algorithm on the host cores: chunked (512) lm-head log-prob/entropy forward + hand-written
-    backward (verl/utils/experimental/torch_functional.py:20-72) and the actor loss composition
-    (verl/trainer/ppo/core_algos.py + dp_actor.py:422-469), via the oracle port.  Returns tokens/s."""
+def _cpu_modules():
+    """The reference's own modules from the snapshot oracle/_ref (kind "reference"), else the oracle port."""
+    if "mods" not in _CPU:
+        try:
+            from oracle import ref_import
+
+            if not ref_import.available():
+                raise RuntimeError("no reference tree / snapshot")
+            ns = ref_import.load()
+            _CPU["mods"] = ("reference", ns)
+        except Exception as e:  # noqa: BLE001
+            from oracle import port
+
+            print(f"[bench] reference snapshot unavailable ({type(e).__name__}: {e}); timing the oracle port",
+                  file=sys.stderr, flush=True)
+            _CPU["mods"] = ("port", port)
+    return _CPU["mods"]
+
+
+def cpu_reference_sample(name, cfg, sample_tokens: int, threads: int):
+    """One pass of the reference's CPU implementation over a ``sample_tokens``-token sample of the workload at full H and
+    V: FusedLinearForPPO (chunk 512) forward + its hand-written backward (verl/utils/experimental/torch_functional.py:
+    20-216), compute_policy_loss / kl_penalty / agg_loss (verl/trainer/ppo/core_algos.py:686-794,1034-1069) composed as
+    in dp_actor.py:422-469, and for c1 compute_grpo_outcome_advantage on the whole batch.  -> (tokens/s, seconds, kind)"""
+    import numpy as np
     import torch
 
-    from oracle import port
-
+    kind, mod = _cpu_modules()
     torch.set_num_threads(threads)
-    if _CPU_INPUTS.get("n") != sample_tokens:  # synthetic inputs are built once, outside every timed region
+    H, V = cfg["H"], cfg["V"]
+    key = (name, sample_tokens)
+    if _CPU.get("key") != key:  # synthetic inputs are built once, outside every timed region
         g = torch.Generator().manual_seed(233376)
-        _CPU_INPUTS.update(
-            n=sample_tokens,
-            hidden=(torch.rand(sample_tokens, HIDDEN, generator=g) - 0.5).bfloat16(),
-            w32=(torch.rand(VOCAB, HIDDEN, generator=g) - 0.5).bfloat16().float(),  # parameter cast: not part of a step
-            labels=torch.randint(0, VOCAB, (sample_tokens,), generator=g),
-            old=-torch.rand(1, sample_tokens, generator=g) * 3,
-            adv=torch.randn(1, sample_tokens, generator=g),
-            mask=(torch.rand(1, sample_tokens, generator=g) < 0.9).long(),
+        n = sample_tokens
+        _CPU.update(
+            key=key,
+            hidden=(torch.rand(n, H, generator=g) - 0.5).bfloat16().float(),
+            weight=(torch.rand(V, H, generator=g) - 0.5).bfloat16().float(),  # parameter: built once, like a model load
+            labels=torch.randint(0, V, (n,), generator=g),
+            old=-torch.rand(1, n, generator=g) * 3,
+            adv=torch.randn(1, n, generator=g),
+            mask=(torch.rand(1, n, generator=g) < 0.9).long(),
         )
-    hidden, w32, labels = _CPU_INPUTS["hidden"], _CPU_INPUTS["w32"], _CPU_INPUTS["labels"]
-    old, adv, mask = _CPU_INPUTS["old"], _CPU_INPUTS["adv"], _CPU_INPUTS["mask"]
-    best = float("inf")
-    for _ in range(repeats):
-        t0 = time.perf_counter()
-        lp, ent = port.lce_forward(hidden, w32, labels, 1.0)
+        if cfg["kind"] == "grpo":
+            B, L = cfg["B"], cfg["L"]
+            rew = torch.zeros(B, L)
+            rew[:, -1] = torch.rand(B, generator=g)
+            _CPU.update(rew=rew, rmask=torch.ones(B, L, dtype=torch.long),
+                        uid=np.repeat(np.arange(B // cfg["n"]), cfg["n"]).astype(str).astype(object))
+    c = _CPU
+    loss = cfg["loss"]
+    lo = loss.get("cliprange_low", loss.get("clip_ratio", 0.2))
+    hi = loss.get("cliprange_high", loss.get("clip_ratio", 0.2))
+    t0 = time.perf_counter()
+    if kind == "reference":
+        ca, fused = mod.core_algos, mod.fused_torch
+        hidden = c["hidden"].clone().requires_grad_(True)
+        weight = c["weight"].requires_grad_(True)
+        weight.grad = None
+        lp, ent = fused.FusedLinearForPPO(chunk_size=512)(hidden, weight, c["labels"], temperature=1.0)
+        lp, ent = lp.view(1, -1), ent.view(1, -1)
+        adv = c["adv"]
+        if cfg["kind"] == "grpo":
+            a, _ = ca.compute_grpo_outcome_advantage(c["rew"], c["rmask"], c["uid"])
+            adv = a.reshape(1, -1)[:, :lp.shape[1]]
+        pg_loss, _, _, _ = ca.compute_policy_loss(c["old"], lp, adv, c["mask"], cliprange=0.2, cliprange_low=lo,
+                                                  cliprange_high=hi, clip_ratio_c=loss.get("clip_ratio_c", 3.0),
+                                                  loss_agg_mode="token-mean")
+        total = pg_loss
+        if loss.get("entropy_coeff", 0.0):
+            total = total - loss["entropy_coeff"] * ca.agg_loss(ent, c["mask"], "token-mean")
+        if loss.get("kl_loss_coef", 0.0):
+            kld = ca.kl_penalty(lp, c["old"], loss.get("kl_loss_type", "low_var_kl"))
+            total = total + loss["kl_loss_coef"] * ca.agg_loss(kld, c["mask"], "token-mean")
+        total.backward()
+    else:
+        port = mod
+        lp, ent = port.lce_forward(c["hidden"].bfloat16(), c["weight"], c["labels"], 1.0)
         lp_ = lp.view(1, -1).clone().requires_grad_(True)
         ent_ = ent.view(1, -1).clone().requires_grad_(True)
-        loss, _ = port.actor_loss(old, lp_, adv, mask, cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0,
-                                  entropy=ent_, entropy_coeff=1e-3, ref_log_prob=old, kl_loss_coef=0.01)
-        loss.backward()
-        port.lce_backward(hidden, w32, labels, lp_.grad.view(-1), ent_.grad.view(-1), 1.0)
-        best = min(best, time.perf_counter() - t0)
-    return sample_tokens / best, best
+        total, _ = port.actor_loss(c["old"], lp_, c["adv"], c["mask"], cliprange_low=lo, cliprange_high=hi,
+                                   clip_ratio_c=loss.get("clip_ratio_c", 3.0), entropy=ent_,
+                                   entropy_coeff=loss.get("entropy_coeff", 0.0), ref_log_prob=c["old"],
+                                   kl_loss_coef=loss.get("kl_loss_coef", 0.0))
+        total.backward()
+        port.lce_backward(c["hidden"].bfloat16(), c["weight"], c["labels"], lp_.grad.view(-1), ent_.grad.view(-1), 1.0)
+    dt = time.perf_counter() - t0
+    return sample_tokens / dt, dt, kind
 
 
-def run_reference(args):
+def run_reference(args, name, cfg):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     sample = args.cpu_tokens or 2048
-    times = []
+    times, kind = [], "port"
     for i in range(args.warmup + args.steps):
-        tps, dt = cpu_reference_sample(sample, threads)
+        _tps, dt, kind = cpu_reference_sample(name, cfg, sample, threads)
         if i >= args.warmup:
             times.append(dt)
     ms = 1e3 * sum(times) / len(times)
     value = sample / (ms * 1e-3)
+    what = ("the reference's own FusedLinearForPPO (chunk 512) + core_algos (snapshot oracle/_ref, unmodified)"
+            if kind == "reference" else "oracle port of the reference's chunk-512 CPU path")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": metric_name(cfg), "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f32 (bf16 inputs upcast, CPU)", "data": "synthetic",
-        "config": workload_config(args.tokens, max(args.gpus, 1)),
-        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": "port",
-                         "sample": f"{sample}-token sample of the workload per step at full H and V, oracle port of the reference's "
-                                   "chunk-512 CPU path (tokens/s is linear in T)"},
+        "vs_baseline": None, "dtype": "f32 (bf16-valued inputs, CPU)", "data": "synthetic",
+        "config": workload_config(name, cfg, max(args.gpus, 1)),
+        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": kind,
+                         "sample": f"{sample}-token sample of the workload per step at full H and V, {what} "
+                                   "(tokens/s is linear in T)"},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
+# ----------------------------------------------------------------------------------------------- parity probe
+def parity_probe(torch, dist, linear_cross_entropy, hidden, w_local, labels, group, rank, world, dev, n_rows=256):
+    """fp32 PyTorch reference from the FULL (all-gathered) weight on sampled rows, outside every timed region: log-prob /
+    entropy and d_hidden on `n_rows` sampled tokens, d_weight on `n_rows` sampled vocab rows (all T tokens contribute).
+    Tolerances: 2e-3 abs on log-prob / entropy (north star), atol 2e-2 + rtol 4e-2 on gradients (the reference's own
+    kernel-test bar, tests/utils/test_linear_cross_entropy.py:270-275; its TP test: test_linear_cross_entropy_tp.py:
+    364-427 compares the sharded kernel with an all-gather torch implementation in the same way)."""
+    T, H = hidden.shape
+    v_local = w_local.shape[0]
+    V = v_local * world
+    temp = 1.0
+    g = torch.Generator(device=dev).manual_seed(777)  # same on all ranks
+    g_lp = torch.rand(T, device=dev, generator=g) * 2 - 1
+    g_ent = torch.rand(T, device=dev, generator=g) - 0.5
+    tok = torch.randperm(T, device=dev, generator=g)[:n_rows]
+    voc = torch.cat([torch.randperm(V, device=dev, generator=g)[:n_rows - 64], labels[tok[:32]],
+                     torch.arange(V - 32, V, device=dev)])
+    h = hidden.detach().clone().requires_grad_(True)
+    w = w_local.detach().clone().requires_grad_(True)
+    lp, ent = linear_cross_entropy(h, w, labels, temp, "none", group)
+    torch.autograd.backward([lp, ent], [g_lp, g_ent])
+    lp, ent, dh, dw = lp.detach(), ent.detach(), h.grad.clone(), w.grad
+    if world > 1:
+        w_full = torch.empty(V, H, dtype=w_local.dtype, device=dev)
+        dist.all_gather_into_tensor(w_full, w_local.detach().contiguous(), group=group)
+    else:
+        w_full = w_local.detach()
+    # sampled token rows: whole logits row in fp32, autograd for d_hidden (already summed over the vocabulary = ranks)
+    hs = hidden[tok].float().requires_grad_(True)
+    z = (hs @ w_full.float().t()) / temp
+    lse_r = torch.logsumexp(z, -1)
+    p = torch.softmax(z, -1)
+    eb_r = (p * z).sum(-1)
+    lp_r = z.gather(-1, labels[tok, None]).squeeze(-1) - lse_r
+    ent_r = lse_r - eb_r
+    (lp_r * g_lp[tok] + ent_r * g_ent[tok]).sum().backward()
+    dh_r = hs.grad
+    del z, p
+    # per-token scalars of ALL tokens from the op's own outputs (checked on the sample)
+    tgt = torch.empty(T, dtype=torch.float32, device=dev)
+    for s in range(0, T, 16384):
+        e = min(T, s + 16384)
+        tgt[s:e] = (hidden[s:e].float() * w_full[labels[s:e]].float()).sum(-1) / temp
+    lse = tgt - lp
+    eb = lse - ent
+    mine = (voc >= rank * v_local) & (voc < (rank + 1) * v_local)
+    voc_m = voc[mine]
+    dw_r = torch.zeros(voc_m.numel(), H, dtype=torch.float32, device=dev)
+    wv = w_full[voc_m].float()
+    for s in range(0, T, 16384):
+        e = min(T, s + 16384)
+        hf = hidden[s:e].float()
+        zz = (hf @ wv.t()) / temp
+        pp = torch.exp(zz - lse[s:e, None])
+        onehot = (labels[s:e, None] == voc_m[None, :]).float()
+        d = (g_lp[s:e, None] * (onehot - pp) - g_ent[s:e, None] * pp * (zz - eb[s:e, None])) / temp
+        dw_r += d.t() @ hf
+
+    def excess(got, ref):
+        if ref.numel() == 0:
+            return -1.0
+        return float(((got.float() - ref).abs() - (2e-2 + 4e-2 * ref.abs())).max())
+
+    def rel(got, ref):
+        return float((got.float() - ref).abs().max() / ref.abs().max().clamp_min(1e-12)) if ref.numel() else 0.0
+
+    out = torch.tensor([float((lp[tok] - lp_r).abs().max()), float((ent[tok] - ent_r).abs().max()),
+                        float((lse[tok] - lse_r).abs().max()), rel(dh[tok], dh_r), rel(dw[voc_m - rank * v_local], dw_r),
+                        excess(dh[tok], dh_r), excess(dw[voc_m - rank * v_local], dw_r)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(out, op=dist.ReduceOp.MAX, group=group)
+    o = [float(x) for x in out.tolist()]
+    ok = o[0] <= 2e-3 and o[1] <= 2e-3 and o[5] <= 0 and o[6] <= 0
+    return {"lp_max_abs": o[0], "ent_max_abs": o[1], "lse_max_abs": o[2], "dh_max_rel": o[3], "dw_max_rel": o[4],
+            "dh_excess_over_tol": o[5], "dw_excess_over_tol": o[6], "rows": int(n_rows), "vocab_rows": int(voc.numel()),
+            "reference": "fp32 PyTorch from the full (all-gathered) weight; tol lp/ent 2e-3 abs, grads 2e-2 + 4e-2*|ref|; "
+                         "max over ranks", "ok": bool(ok)}
+
+
 # ----------------------------------------------------------------------------------------------- our arm
-def run_ours(args):
+def run_ours(args, name, cfg):
+    import numpy as np
     import torch
     import torch.distributed as dist
 
-    from verl_b200 import _lib
+    from verl_b200 import _lib, ops
     from verl_b200.trainer.ppo import core_algos
+    from verl_b200.utils.kernel import kernels
     from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
 
     rank = int(os.environ.get("RANK", "0"))
@@ -199,16 +395,22 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
     _lib.load()
-    exchange = "nccl"
-    reduce_how = "nccl"
+    kind = cfg["kind"]
+    if kind != "lce" and world > 1:
+        raise SystemExit(f"--config {name} is a single-GPU configuration (BASELINE.json); run it with --gpus 1")
+    H, V = cfg["H"], cfg["V"]
+    T = args.tokens or cfg.get("T", 0)
+    exchange, reduce_how = "nccl", "nccl"
+    if args.bwd_ws_mb:
+        kernels.set_backward_chunk(int(ops._lib_().vpg_lce_bwd_chunk_for_budget(T or 32768, H, V // world, args.bwd_ws_mb << 20)))
     if world > 1:
-        from verl_b200.utils.kernel import kernels, peer
+        from verl_b200.utils.kernel import peer
 
-        want = args.tp_exchange
-        ok = 0
+        want, ok = args.tp_exchange, 0
         if want in ("auto", "nvlink"):
-            try:  # collective pre-flight: symmetric allocation + NVSwitch multicast binding
-                ok = int(peer.workspace(group, dev).has_multicast)
+            try:  # collective pre-flight: symmetric allocation + NVSwitch multicast binding, all buffers reserved NOW
+                px = kernels.init_vocab_parallel(group, dev, T, H, V // world)
+                ok = int(px.has_multicast)
             except Exception as e:  # noqa: BLE001
                 print(f"[bench] rank {rank}: NVLink peer workspace unavailable ({type(e).__name__}: {e}); using NCCL",
                       file=sys.stderr, flush=True)
@@ -216,49 +418,81 @@ def run_ours(args):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         exchange = "nvlink" if int(flag.item()) == 1 else "nccl"
         kernels.set_vocab_parallel_exchange(exchange)
-        kernels.set_reduce_d_hidden(True, mode=args.tp_reduce)  # the op returns the summed d_hidden
         reduce_how = args.tp_reduce
         if reduce_how == "auto":
-            reduce_how = "overlap" if kernels._overlap_plan(args.tokens, HIDDEN, VOCAB // world, world, dev)[0] else "nccl"
-
-    T, H, V = args.tokens, HIDDEN, VOCAB
+            reduce_how = "fused" if exchange == "nvlink" else (
+                "overlap" if kernels._overlap_plan(T, H, V // world, world, dev)[0] else "nccl")
+        if reduce_how == "fused" and exchange != "nvlink":
+            reduce_how = "nccl"
+        kernels.set_reduce_d_hidden(True, mode=reduce_how)  # the op returns the summed d_hidden
     assert V % world == 0
     v_local = V // world
     gen = torch.Generator(device=dev).manual_seed(233376)  # same on all ranks: hidden / labels are replicated
-    # ---- synthetic inputs: pinned host copies for the end-to-end leg, device copies for `value`
-    hidden_d = (torch.rand(T, H, device=dev, generator=gen) - 0.5).bfloat16()
-    labels_d = torch.randint(0, V, (T,), device=dev, generator=gen)
-    old_d = -torch.rand(1, T, device=dev, generator=gen) * 3
-    ref_d = old_d + 0.05 * torch.randn(1, T, device=dev, generator=gen)
-    adv_d = torch.randn(1, T, device=dev, generator=gen)
-    mask_d = (torch.rand(1, T, device=dev, generator=gen) < 0.9).long()
     wgen = torch.Generator(device=dev).manual_seed(1000 + rank)
     weight = (torch.rand(v_local, H, device=dev, generator=wgen) - 0.5).bfloat16().requires_grad_(True)
-    host = {k: v.cpu().pin_memory() for k, v in dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d,
-                                                     mask=mask_d).items()}
-    # end-to-end leg: two staging slots filled by a copy stream, so the H2D copy of step i+1 runs under the compute of
-    # step i (every step's copy is inside the timed region).  With N ranks `hidden` is replicated: each rank copies
-    # only its T/N rows over PCIe and the ranks all-gather the rest over NVLink.
-    assert T % world == 0
-    rows = T // world
-    staging = [{k: torch.empty_like(v, device=dev) for k, v in host.items()} for _ in range(2)]
-    # N > 1: the replicated `hidden` is assembled WITHOUT SM work: its two staging slots are symmetric (peer-mapped)
-    # allocations, each rank copies its T/N rows from the host and pulls the other ranks' rows with copy-engine
-    # peer-to-peer DMA over NVLink on the copy stream, between two signal-pad barriers.  An NCCL all-gather here would
-    # put ~16 CTAs next to a persistent 1-CTA-per-SM GEMM whose static schedule then waits for the delayed workers.
-    gather = "none"
-    peer_views = [None, None]
-    sym_handles = [None, None]
+
+    # ---- synthetic inputs.  A step is a list of micro-batches; each micro-batch is a dict of device tensors
+    micros = []
+    if kind in ("lce", "grpo"):
+        d = dict(hidden=(torch.rand(T, H, device=dev, generator=gen) - 0.5).bfloat16(),
+                 labels=torch.randint(0, V, (T,), device=dev, generator=gen))
+        if kind == "lce":
+            d.update(old=-torch.rand(1, T, device=dev, generator=gen) * 3)
+            d.update(ref=d["old"] + 0.05 * torch.randn(1, T, device=dev, generator=gen),
+                     adv=torch.randn(1, T, device=dev, generator=gen),
+                     mask=(torch.rand(1, T, device=dev, generator=gen) < 0.9).long())
+        else:
+            B, L = cfg["B"], cfg["L"]
+            lens = torch.randint(L // 4, L + 1, (B,), device=dev, generator=gen)
+            d.update(old=-torch.rand(B, L, device=dev, generator=gen) * 3,
+                     mask=(torch.arange(L, device=dev)[None] < lens[:, None]).long())
+            rew = torch.zeros(B, L, device=dev)
+            rew[torch.arange(B, device=dev), lens - 1] = torch.rand(B, device=dev, generator=gen)
+            d.update(rewards=rew)
+        micros.append(d)
+        tokens_per_step = T
+        uid = np.repeat(np.array([f"uid-{i}" for i in range(cfg.get("B", 0) // cfg.get("n", 1))], dtype=object),
+                        cfg.get("n", 1)) if kind == "grpo" else None
+    else:  # actor: 128 sequences in micro-batches of 16, left-padded prompts + right-padded responses
+        from verl_b200.workers.actor.dp_actor import fused_actor_step
+
+        B, mb, P, L = cfg["B"], cfg["micro"], cfg["P"], cfg["L"]
+        S = P + L
+        tokens_per_step = 0
+        for _ in range(B // mb):
+            p_len = torch.randint(P // 2, P + 1, (mb,), device=dev, generator=gen)
+            r_len = torch.randint(L // 4, L + 1, (mb,), device=dev, generator=gen)
+            pos = torch.arange(S, device=dev)[None]
+            attn = ((pos >= (P - p_len)[:, None]) & (pos < (P + r_len)[:, None])).long()
+            Tm = int(attn.sum())
+            d = dict(hidden=(torch.rand(Tm, H, device=dev, generator=gen) - 0.5).bfloat16(),
+                     ids=torch.randint(0, V, (mb, S), device=dev, generator=gen), attn=attn,
+                     rmask=attn[:, P:].contiguous(), old=-torch.rand(mb, L, device=dev, generator=gen) * 3,
+                     adv=torch.randn(mb, L, device=dev, generator=gen))
+            d.update(ref=d["old"] + 0.05 * torch.randn(mb, L, device=dev, generator=gen))
+            micros.append(d)
+            tokens_per_step += Tm
+        T = tokens_per_step
+    host = [{k: v.cpu().pin_memory() for k, v in m.items()} for m in micros]
+
+    # end-to-end leg: two staging slots filled by a copy stream, so the H2D copy of micro-batch i+1 runs under the compute
+    # of micro-batch i (every copy is inside the timed region).  With N ranks `hidden` is replicated: each rank copies only
+    # its T/N rows over PCIe and pulls the other rows peer-to-peer (copy engines, symmetric staging slots, no SM work).
+    big = max(range(len(host)), key=lambda i: host[i]["hidden"].numel())
+    staging = [{k: torch.empty_like(v, device=dev) for k, v in host[big].items()} for _ in range(2)]
+    rows = (T // world) if kind == "lce" else 0
+    gather, peer_views, sym_handles = "none", [None, None], [None, None]
     if world > 1:
+        assert T % world == 0
         gather = args.e2e_gather
         if gather == "ce":
             ok = 1
             try:
+                import warnings
+
                 import torch.distributed._symmetric_memory as symm_mem
 
                 try:
-                    import warnings
-
                     with warnings.catch_warnings():  # deprecated no-op on newer torch
                         warnings.simplefilter("ignore")
                         symm_mem.enable_symm_mem_for_group(group.group_name)
@@ -279,78 +513,114 @@ def run_ours(args):
             if int(flag.item()) != 1:
                 gather = "nccl"
                 for s_ in range(2):
-                    staging[s_]["hidden"] = torch.empty_like(host["hidden"], device=dev)
+                    staging[s_]["hidden"] = torch.empty_like(host[0]["hidden"], device=dev)
     copy_stream = torch.cuda.Stream(device=dev)
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
-    small_bytes = sum(v.numel() * v.element_size() for k, v in host.items() if k != "hidden")
-    h2d_bytes = host["hidden"].numel() * host["hidden"].element_size() + world * small_bytes  # whole job, per step
+    h2d_bytes = 0
+    for hm in host:
+        small = sum(v.numel() * v.element_size() for k, v in hm.items() if k != "hidden")
+        h2d_bytes += hm["hidden"].numel() * hm["hidden"].element_size() + world * small  # whole job, per step
     metrics_host = torch.empty(2, 8, dtype=torch.float32).pin_memory()
     read_back = [torch.cuda.Event() for _ in range(2)]
     last_read = [None]  # slot whose metrics the host has not read yet
     host_loss = [0.0]
 
-    def enqueue_h2d(slot: int):
+    def views(slot: int, mi: int):
+        """device views of staging slot `slot` shaped like micro-batch `mi`"""
+        return {k: staging[slot][k].reshape(-1)[:v.numel()].view(v.shape) if k != "hidden" or world == 1
+                else staging[slot][k] for k, v in host[mi].items()}
+
+    def enqueue_h2d(slot: int, mi: int):
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[slot])
-            for k in host:
+            dst = views(slot, mi)
+            for k, v in host[mi].items():
                 if k == "hidden" and world > 1:
                     sl = slice(rank * rows, (rank + 1) * rows)
-                    staging[slot][k][sl].copy_(host[k][sl], non_blocking=True)
+                    dst[k][sl].copy_(v[sl], non_blocking=True)
                 else:
-                    staging[slot][k].copy_(host[k], non_blocking=True)
+                    dst[k].copy_(v, non_blocking=True)
             if gather == "ce":
                 hdl = sym_handles[slot]
                 hdl.barrier(channel=0)  # every rank's rows of this slot are in place (and nobody still computes on it)
-                dst = staging[slot]["hidden"]
                 for i in range(1, world):  # staggered: at any moment every rank reads from a different peer
                     r = (rank + i) % world
                     sl = slice(r * rows, (r + 1) * rows)
-                    dst[sl].copy_(peer_views[slot][r][sl], non_blocking=True)  # contiguous same-dtype: cudaMemcpyAsync
+                    dst["hidden"][sl].copy_(peer_views[slot][r][sl], non_blocking=True)  # cudaMemcpyAsync, copy engine
                 hdl.barrier(channel=0)  # all pulls done: a rank may overwrite its rows at the slot's next use
             ready[slot].record(copy_stream)
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    seg = {"fwd": [], "loss": [], "bwd": []}
+    seg = {"_marks": []}
+    n_micro = len(micros)
+    scale = 1.0 / n_micro
 
-    def step(e2e: bool, record: bool, slot: int = 0, prefetch: bool = False):
-        if e2e:
-            cur = torch.cuda.current_stream()
-            cur.wait_event(ready[slot])
-            if prefetch:
-                enqueue_h2d(slot ^ 1)
-            src = staging[slot]
-            if gather == "nccl":
-                dist.all_gather_into_tensor(src["hidden"], src["hidden"][rank * rows:(rank + 1) * rows], group=group)
-        else:
-            src = dict(hidden=hidden_d, labels=labels_d, old=old_d, ref=ref_d, adv=adv_d, mask=mask_d)
+    def compute(src, record):
+        """one micro-batch of the hot path through the public API -> metrics[8] (device)"""
         hidden = src["hidden"].detach().requires_grad_(True)
-        weight.grad = None
         marks = [ev() for _ in range(4)] if record else None
         if record:
             marks[0].record()
+        if kind == "actor":
+            _loss, metrics, _lp, _ent = fused_actor_step(hidden, weight, src["ids"], src["attn"], src["old"], src["adv"],
+                                                         src["rmask"], temperature=1.0, ref_log_prob=src["ref"],
+                                                         loss_scale=scale, **cfg["loss"])
+            if record:
+                marks[3].record()
+                seg["_marks"].append((marks[0], None, None, marks[3]))
+            return metrics
         lp, ent = linear_cross_entropy(hidden, weight, src["labels"], 1.0, "none", group)
         if record:
             marks[1].record()
-        loss, metrics = core_algos.fused_actor_loss(src["old"], lp.view(1, -1), src["adv"], src["mask"],
-                                                    entropy=ent.view(1, -1), ref_log_prob=src["ref"], **LOSS_CFG)
+        if kind == "grpo":
+            B, L = cfg["B"], cfg["L"]
+            adv, _ = core_algos.compute_grpo_outcome_advantage(src["rewards"], src["mask"], uid)
+            loss, metrics = core_algos.fused_actor_loss(src["old"], lp.view(B, L), adv, src["mask"], entropy=ent.view(B, L),
+                                                        **cfg["loss"])
+        else:
+            loss, metrics = core_algos.fused_actor_loss(src["old"], lp.view(1, -1), src["adv"], src["mask"],
+                                                        entropy=ent.view(1, -1), ref_log_prob=src["ref"], **cfg["loss"])
         if record:
             marks[2].record()
         loss.backward()  # world > 1: d_hidden comes back already summed over the ranks (kernels.set_reduce_d_hidden)
         if record:
             marks[3].record()
             seg["_marks"].append(marks)
-        if e2e:
-            consumed[slot].record()
-            # the host reads EVERY step's loss / metrics, one step behind the launches: step i's 32 bytes are waited
-            # for after step i+1 has been enqueued, so the GPU never idles while Python builds the next step
-            metrics_host[slot].copy_(metrics, non_blocking=True)
-            read_back[slot].record()
-            if last_read[0] is not None:
-                read_back[last_read[0]].synchronize()
-                host_loss[0] = float(metrics_host[last_read[0]][0])
-            last_read[0] = slot
         return metrics
+
+    counter = [0]  # micro-batches enqueued by the e2e leg (slot = counter & 1)
+
+    def step(e2e: bool, record: bool, last_step: bool = False):
+        weight.grad = None
+        for mi in range(n_micro):
+            if e2e:
+                slot = counter[0] & 1
+                cur = torch.cuda.current_stream()
+                cur.wait_event(ready[slot])
+                nxt = mi + 1
+                if nxt < n_micro or not last_step:
+                    enqueue_h2d(slot ^ 1, nxt % n_micro)
+                src = views(slot, mi)
+                if gather == "nccl":
+                    dist.all_gather_into_tensor(src["hidden"], src["hidden"][rank * rows:(rank + 1) * rows], group=group)
+            else:
+                src = micros[mi]
+            metrics = compute(src, record)
+            if e2e:
+                consumed[slot].record()
+                # the host reads EVERY micro-batch's loss / metrics, one behind the launches: micro-batch i's 32 bytes are
+                # waited for after i+1 has been enqueued, so the GPU never idles while Python builds the next one
+                metrics_host[slot].copy_(metrics, non_blocking=True)
+                read_back[slot].record()
+                if last_read[0] is not None:
+                    read_back[last_read[0]].synchronize()
+                    host_loss[0] = float(metrics_host[last_read[0]][0])
+                last_read[0] = slot
+                counter[0] += 1
+        return metrics
+
+    energy = EnergyMeter(local_rank)
 
     def timed(e2e: bool, steps: int, record: bool):
         seg["_marks"] = []
@@ -358,12 +628,14 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = ev(), ev()
+        j0 = energy.read()
         e0.record()
         if e2e:
-            enqueue_h2d(0)  # step 0's inputs: inside the timed region, not hidden behind anything
+            counter[0] = 0
+            enqueue_h2d(0, 0)  # the first micro-batch's inputs: inside the timed region, not hidden behind anything
         for i in range(steps):
-            step(e2e, record, slot=i & 1, prefetch=i + 1 < steps)
-        if e2e and last_read[0] is not None:  # the last step's metrics are read inside the timed region too
+            step(e2e, record, last_step=(i + 1 == steps))
+        if e2e and last_read[0] is not None:  # the last metrics are read inside the timed region too
             read_back[last_read[0]].synchronize()
             host_loss[0] = float(metrics_host[last_read[0]][0])
             last_read[0] = None
@@ -371,110 +643,188 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+        j1 = energy.read()
         ms = e0.elapsed_time(e1) / steps
         if world > 1:
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms
+        return ms, ((j1 - j0) / steps if (j0 is not None and j1 is not None) else None)
 
     for _ in range(max(args.warmup, 3)):
         step(False, False)
-    enqueue_h2d(0)
-    step(True, False)
+    counter[0] = 0
+    enqueue_h2d(0, 0)
+    step(True, False, last_step=True)
     torch.cuda.synchronize()
     last_read[0] = None
 
+    # ---- parity probe (outside every timed region; vocab-parallel modes are the ones the timed region uses)
+    parity = None
+    if not args.no_parity and kind in ("lce", "grpo"):
+        parity = parity_probe(torch, dist, linear_cross_entropy, micros[0]["hidden"], weight, micros[0]["labels"], group,
+                              rank, world, dev)
+        weight.grad = None
+        torch.cuda.synchronize()
+
+    torch.cuda.reset_peak_memory_stats(dev)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     launches0 = _lib.launch_count()
-    ms_dev = timed(False, args.steps, True)
+    _lib.timing_enable(True)
+    ms_dev, joules = timed(False, args.steps, True)
+    per_launch = _lib.timing_collect()
+    _lib.timing_enable(False)
     launches = _lib.launch_count() - launches0
     marks = seg["_marks"]
-    ms_e2e = timed(True, args.steps, False)
+    peak_mem = torch.cuda.max_memory_allocated(dev)
+    ms_e2e, joules_e2e = timed(True, args.steps, False)
     clocks = sampler.stop() if rank == 0 else None
 
-    fwd_ms = sum(m[0].elapsed_time(m[1]) for m in marks) / len(marks)
-    loss_ms = sum(m[1].elapsed_time(m[2]) for m in marks) / len(marks)
-    bwd_ms = sum(m[2].elapsed_time(m[3]) for m in marks) / len(marks)
+    def seg_ms(a, b):
+        vals = [m[a].elapsed_time(m[b]) for m in marks if m[a] is not None and m[b] is not None]
+        return n_micro * sum(vals) / len(vals) if vals else None
+
+    fwd_ms, loss_ms, bwd_ms = seg_ms(0, 1), seg_ms(1, 2), seg_ms(2, 3)
 
     if rank == 0:
         peaks = _peaks()
-        flops_fwd = 2.0 * T * H * v_local  # per GPU
-        fwd_tf = flops_fwd / (fwd_ms * 1e-3) / 1e12
-        step_useful_tf = 3 * flops_fwd / (ms_dev * 1e-3) / 1e12
-        step_exec_tf = 4 * flops_fwd / (ms_dev * 1e-3) / 1e12
+        # per-kernel roofline: algorithmic flops of one launch of each tcgen05 kernel / its CUDA-event duration
+        t_rows = T if kind != "actor" else None
+        kern = {}
+        for k, ms in per_launch:
+            if ms >= 0:
+                kern.setdefault(k, []).append(ms)
+        ws = ops.lce_backward_workspace_info(T if kind != "actor" else 16384, H, v_local, dev,
+                                             kernels._config._chunk_v)
+        flops_fwd = 2.0 * (t_rows or 0) * H * v_local  # per GPU, per launch of the forward kernel
+        kernels_out = {}
+        for k, v in kern.items():
+            per_step = len(v) / args.steps
+            tot = sum(v) / args.steps
+            entry = {"launches_per_step": per_step, "ms_per_step": tot}
+            if kind != "actor" and k in ("lm_head_fwd", "dlogits_recompute", "d_weight_gemm", "d_hidden_gemm"):
+                tf = flops_fwd / (tot * 1e-3) / 1e12  # each of the four covers 2*T*H*V/N flops per step
+                entry.update(algorithmic_flops_per_step=flops_fwd, tflops=tf, frac_of_sustained=tf / peaks["sustained"],
+                             frac_of_burst=tf / peaks["burst"])
+            kernels_out[k] = entry
+        fwd_kernel_ms = kernels_out.get("lm_head_fwd", {}).get("ms_per_step") or fwd_ms
+        fwd_tf = flops_fwd / (fwd_kernel_ms * 1e-3) / 1e12 if (fwd_kernel_ms and flops_fwd) else None
+        step_useful_tf = 3 * flops_fwd / (ms_dev * 1e-3) / 1e12 if flops_fwd else None
+        step_exec_tf = 4 * flops_fwd / (ms_dev * 1e-3) / 1e12 if flops_fwd else None
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             n_cpu = args.cpu_tokens or 4096
-            tps, dt = cpu_reference_sample(n_cpu, threads)
-            cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port",
-                   "sample": f"{n_cpu} tokens at full H and V, fp32 math on bf16 inputs, {dt:.1f} s"}
+            tps, dt, ckind = cpu_reference_sample(name, cfg, n_cpu, threads)
+            cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": ckind,
+                   "sample": f"{n_cpu} tokens of the workload at full H and V, "
+                             + ("the reference's FusedLinearForPPO + core_algos (oracle/_ref snapshot)" if ckind == "reference"
+                                else "oracle port") + f", fp32 math on bf16-valued inputs, {dt:.1f} s"}
         line = {
-            "metric": METRIC, "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(T, world, exchange), "tp_reduce": reduce_how,
+            "metric": metric_name(cfg), "value": T / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(name, cfg, world, exchange, reduce_how), "tp_reduce": reduce_how,
             "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32 * world,
-                    "how": "pinned host -> device on a copy stream, double-buffered (step i+1's inputs copy under step "
-                           "i's compute; every copy is inside the timed region)"
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 32 * world * n_micro,
+                    "how": "pinned host -> device on a copy stream, double-buffered (micro-batch i+1's inputs copy under "
+                           "micro-batch i's compute; every copy is inside the timed region)"
                            + ("" if world == 1 else f"; each rank copies T/{world} rows of hidden and the ranks "
                               + ("pull the other rows peer-to-peer with copy-engine DMA over NVLink (symmetric staging "
                                  "slots, no SM work)" if gather == "ce" else
                                  "all-gather the replicated tensor over NVLink (NCCL)"))
-                           + "; metrics[8] of every step read by the host, one step behind the launches"},
+                           + "; metrics[8] of every micro-batch read by the host, one behind the launches"},
             "gpu_launches": int(launches),
             "clocks": clocks,
+            "parity": parity,
             "roofline": {
                 "kernel": "tc_gemm_kernel<MODE_FWD> (tcgen05 lm-head forward with fused online-softmax epilogue)",
                 "bound": "tensor", "achieved": fwd_tf, "peak": peaks["sustained"], "unit": "TFLOP/s",
-                "frac": fwd_tf / peaks["sustained"], "traffic": _traffic(T, H, v_local),
+                "frac": fwd_tf / peaks["sustained"] if fwd_tf else None,
+                "traffic": _traffic(T, H, v_local),
                 "traffic_unit": "bytes of DRAM read+write per launch (ncu --set full, profiles/roofline_traffic.json); "
                                 "algorithmic operand bytes = 2*(T*H + V*H) + 16*S*T",
                 "peak_source": peaks["source"] + ", sustained bf16 figure (kernel timed inside a long step)",
-                "frac_of_burst_peak": fwd_tf / peaks["burst"],
-                "algorithmic_flops_per_launch": flops_fwd, "launch_ms": fwd_ms,
+                "frac_of_burst_peak": fwd_tf / peaks["burst"] if fwd_tf else None,
+                "algorithmic_flops_per_launch": flops_fwd, "launch_ms": fwd_kernel_ms,
+                "timed_with": "CUDA events around the launch on its own stream (vpg_timing_*), averaged over the timed steps",
             },
+            "roofline_kernels": kernels_out,
             "roofline_step": {
                 "useful_tflops": step_useful_tf, "executed_tflops": step_exec_tf,
-                "useful_frac_of_sustained": step_useful_tf / peaks["sustained"],
-                "useful_frac_of_burst": step_useful_tf / peaks["burst"],
-                "executed_frac_of_sustained": step_exec_tf / peaks["sustained"],
+                "useful_frac_of_sustained": step_useful_tf / peaks["sustained"] if step_useful_tf else None,
+                "useful_frac_of_burst": step_useful_tf / peaks["burst"] if step_useful_tf else None,
+                "executed_frac_of_sustained": step_exec_tf / peaks["sustained"] if step_exec_tf else None,
                 "segments_ms": {"lm_head_fwd": fwd_ms, "ppo_loss": loss_ms, "lm_head_bwd(+allreduce)": bwd_ms},
-                "note": "useful = 6*T*H*V/N per GPU (fwd + dH + dW), executed = 8*T*H*V/N (tile recompute in the backward)",
+                "note": "useful = 6*T*H*V/N per GPU (fwd + dH + dW), executed = 8*T*H*V/N (tile recompute in the backward)"
+                        + ("; c3: the lm-head runs on response-window rows only, tokens/s counts every rmpad stream token"
+                           if kind == "actor" else ""),
             },
+            "energy": {"joules_per_step": joules, "joules_per_step_e2e": joules_e2e,
+                       "tokens_per_joule": (T / joules) if joules else None,
+                       "source": "NVML total-energy counter of GPU 0 around the timed region"},
+            "memory": {"bwd_workspace_bytes": ws["workspace_bytes"], "bwd_chunks": ws["chunks"], "bwd_chunk_v": ws["chunk_v"],
+                       "peak_allocated_bytes_in_timed_region": int(peak_mem),
+                       "budget": f"{args.bwd_ws_mb} MiB (--bwd-ws-mb)" if args.bwd_ws_mb else
+                                 "library default: $VPG_BWD_WS_MB or 4096 MiB of dlogits (the [T,V] logits are never stored)"},
             "cpu_baseline": cpu,
         }
+        if args.token_ops and world == 1:
+            line["extra"] = {"token_ops": token_ops_table(torch, dev, peaks)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+def token_ops_table(torch, dev, peaks, log2_tokens: int = 24):
+    """HBM-roofline rows of the memory-bound token kernels (scripts/bench_token_ops.py) at 2^24 tokens: achieved GB/s of
+    algorithmic bytes against the measured HBM peak.  Driver-visible copy of profiles/*token_ops_hbm_roofline*.jsonl."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import bench_token_ops as bto
+
+    L = 16384
+    B = (1 << log2_tokens) // L
+    d = bto.make(B, L, dev)
+    out = []
+    for op, fn, nbytes in bto.ops_table(d, B, L, 8):
+        ms = bto.timeit(fn, iters=5, warmup=2)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"op": op, "tokens": B * L, "ms": round(ms, 4), "achieved_gbs": round(gbs, 1),
+                    "frac_of_hbm_peak": round(gbs / peaks["hbm"], 3)})
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--config", choices=sorted(CONFIGS), default="c2", help="BASELINE.json configs[i-1]; c2 = the metric's")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--tokens", type=int, default=TOKENS)
+    ap.add_argument("--tokens", type=int, default=0, help="override the configuration's token count (lce kinds)")
     ap.add_argument("--cpu-tokens", type=int, default=0,
                     help="token sample of the CPU legs (0 = 4096 for cpu_baseline, 2048 per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--tp-reduce", choices=["auto", "nccl", "multimem", "overlap"], default="auto",
-                    help="N > 1: d_hidden all-reduce after the GEMMs (nccl), under the d_weight GEMM (overlap), chosen by the "
-                         "cost model (auto, default) or fused into the d_hidden GEMM (multimem.red)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the fp32 parity probe (outside the timed region)")
+    ap.add_argument("--token-ops", action="store_true", help="N=1: add the token-op HBM roofline table as `extra`")
+    ap.add_argument("--bwd-ws-mb", type=int, default=0,
+                    help="dlogits workspace budget of the backward in MiB (0 = library default, 4096)")
+    ap.add_argument("--tp-reduce", choices=["auto", "fused", "nccl", "multimem", "overlap"], default="auto",
+                    help="N > 1: d_hidden all-reduce inside the d_weight GEMM kernel (fused; default when NVSwitch multicast "
+                         "is available), after the GEMMs (nccl), under the d_weight GEMM on a second stream (overlap) or "
+                         "from the d_hidden GEMM epilogue (multimem.red)")
     ap.add_argument("--e2e-gather", choices=["ce", "nccl"], default="ce",
                     help="N>1 end-to-end leg: how the replicated hidden is assembled from the per-rank H2D shards")
     ap.add_argument("--tp-exchange", choices=["auto", "nccl", "nvlink"], default="auto",
                     help="N > 1: fused NVLink exchange (default when NVSwitch multicast is available) or NCCL")
     args = ap.parse_args()
+    cfg = CONFIGS[args.config]
     if args.impl == "reference":
-        run_reference(args)
+        run_reference(args, args.config, cfg)
     else:
-        run_ours(args)
+        run_ours(args, args.config, cfg)
 
 
 if __name__ == "__main__":

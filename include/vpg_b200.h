@@ -151,15 +151,68 @@ int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* 
                     int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
                     void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream);
 
-/* One-shot option of the NEXT vpg_lce_bwd* call on the calling thread (vocab-parallel runs): `d_hidden_ready_event`
- * (cudaEvent_t) is recorded on the call's stream as soon as d_hidden is complete.  The backward then computes d_hidden
- * BEFORE its last d_weight GEMM and gives that GEMM the fewest persistent workers that keep its number of scheduling
- * rounds, so the all-reduce of d_hidden the reference leaves to its callers
- * (tests/utils/test_linear_cross_entropy_tp.py:313-314) can run on a second stream, on the freed SMs, under the
- * d_weight GEMM.  reserve_cta_pairs > 0 additionally keeps at least that many CTA pairs (2 SMs each) free during the
- * d_weight GEMM, at the price of extra scheduling rounds (NCCL's all-reduce kernel only overlaps when all of its
- * ~16 CTAs are resident at once).  Ignored by vpg_lce_bwd_mcred's fused all-reduce. */
-int vpg_lce_bwd_overlap_next(void* d_hidden_ready_event, int reserve_cta_pairs);
+/* Backward with every option as an explicit argument (the entry points above are thin wrappers over it).
+ * Replaces verl/utils/kernel/kernels.py:1345-1553 plus, for vocab-parallel shards, the d_hidden all-reduce the
+ * reference leaves to its callers (tests/utils/test_linear_cross_entropy_tp.py:313-314).  Zero-initialise the struct,
+ * set struct_size = sizeof(vpg_lce_bwd_args), fill what applies.  Three mutually exclusive ways to reduce d_hidden
+ * across the vocab-parallel group, all optional:
+ *  (a) ar_world > 1 — IN-KERNEL NVLS all-reduce: d_hidden must be this rank's address of a symmetric (peer-mapped,
+ *      multicast-bound) bf16 [T,H] buffer and ar_d_hidden_mc the multicast address of the same buffer.  The backward
+ *      computes d_hidden BEFORE its last d_weight GEMM; that GEMM's otherwise idle warp (one per CTA) then pulls the
+ *      switch-reduced sum of this rank's 1/world slice (multimem.ld_reduce) and broadcasts it into every rank's buffer
+ *      (multimem.st) while the tensor cores work on d_weight.  ar_flags: this rank's 17 uint32 flags (zeroed once at
+ *      allocation) in symmetric memory; ar_peer_flags[r]: rank r's flag array as mapped into this process (HOST array
+ *      of ar_world device pointers, own rank included); ar_epoch: call counter, identical on all ranks, never 0.
+ *      When the call's kernels have completed on a rank, its d_hidden holds the sum over all ranks.
+ *  (b) d_hidden_ready_event (cudaEvent_t) — recorded as soon as d_hidden is complete; d_hidden is computed before the
+ *      last d_weight GEMM, which runs on the fewest persistent workers that keep its number of scheduling rounds
+ *      (at least reserve_cta_pairs CTA pairs stay free), so the caller's own all-reduce (NCCL on a second stream)
+ *      overlaps it.
+ *  (c) d_hidden_mc_f32 — multimem.red.add.f32 in the epilogue of the d_hidden GEMM (see vpg_lce_bwd_mcred). */
+typedef struct vpg_lce_bwd_args {
+    size_t struct_size;
+    int dtype;               /* VPG_DT_BF16 | VPG_DT_F16 | VPG_DT_F32 */
+    const void* hidden;      /* [T,H] in `dtype` */
+    const void* weight;      /* [V,H] in `dtype` */
+    const void* hidden16;    /* VPG_DT_F32 only: bf16 copies read by the two gradient GEMMs */
+    const void* weight16;
+    const int64_t* labels;
+    const float* lse;
+    const float* eb;
+    const float* g_lp;       /* may be NULL */
+    const float* g_ent;      /* may be NULL */
+    int64_t T, H, V;
+    float temperature;
+    int64_t label_offset;
+    int64_t chunk_v;         /* 0 = vpg_lce_bwd_default_chunk */
+    void* d_hidden;          /* [T,H] in `dtype` (fp32 for VPG_DT_F32) */
+    void* d_weight;          /* [V,H] likewise */
+    void* workspace;
+    size_t workspace_bytes;  /* >= vpg_lce_bwd_workspace_bytes() */
+    void* stream;
+    float* d_hidden_mc_f32;        /* (c) */
+    void* d_hidden_ready_event;    /* (b) */
+    int reserve_cta_pairs;         /* (b) */
+    int ar_world, ar_rank;         /* (a) */
+    uint32_t ar_epoch;
+    void* ar_d_hidden_mc;
+    uint32_t* ar_flags;
+    uint32_t* const* ar_peer_flags;
+} vpg_lce_bwd_args;
+int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args);
+
+/* Forward stage 1 with every option explicit: operand dtype + the push arguments of vpg_lce_fwd_partials_push. */
+int vpg_lce_fwd_partials_ex(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
+                            int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                            float* partials, int part_split0, int part_total, int partials_is_multicast,
+                            void* const* push_ptrs, int n_push, void* stream);
+
+/* Per-launch device timing of the tcgen05 kernels (bench.py's per-kernel roofline): while enabled, every launch is
+ * bracketed by two CUDA events on the stream it is launched on.  vpg_timing_collect synchronises those events and
+ * returns up to max_n (kind, milliseconds) pairs in launch order, clearing the record.
+ * kind: 0 lm-head forward, 1 dlogits recompute, 2 d_weight GEMM, 3 d_hidden GEMM, 4 plain GEMM, 5 split-K reduce. */
+int vpg_timing_enable(int on);
+int vpg_timing_collect(int* kinds, float* ms, int max_n);
 
 /* Vocab-parallel backward with the d_hidden all-reduce fused into the d_hidden GEMM (the reference leaves this
  * all-reduce to the caller: tests/utils/test_linear_cross_entropy_tp.py:313-314).  d_hidden_mc_f32 is an NVSwitch
@@ -182,6 +235,13 @@ int vpg_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream)
 int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
                   int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
                   int64_t ld_accum, void* stream);
+/* Same with a scratch buffer (vpg_gemm_splitk_workspace_bytes(), 16-byte aligned) that enables the split-K tail: the
+ * tiles of the last, partial scheduling round of the persistent grid are cut along K into fp32 partial tiles, summed in
+ * a fixed order by a second small launch, so that round costs 1/ksplit of a tile time. */
+size_t vpg_gemm_splitk_workspace_bytes(void);
+int vpg_gemm_bf16_ws(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                     int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
+                     int64_t ld_accum, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Materialised-logits variants — verl/utils/torch_functional.py:64-133 (logprobs_from_logits*) and :145-160

@@ -211,6 +211,48 @@ def test_full_size_properties(dev):
     torch.testing.assert_close(dh_c.float(), 2 * dh_a.float() + dh_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
 
 
+@pytest.mark.parametrize("chunk_v", [0, 9472, -1])
+def test_full_size_backward_sampled_rows_vs_fp32(chunk_v, dev):
+    """BASELINE configs[1] at FULL size through the autograd op: d_hidden for 256 sampled tokens and d_weight for 256
+    sampled vocab rows against an fp32 PyTorch reference (the reference's own gradient bar: atol 2e-2, rtol 4e-2,
+    tests/utils/test_linear_cross_entropy.py:270-275), for the default workspace budget (chunk_v 0), the reference's
+    default split width of 9 504 columns rounded to the tile (9 472, 17 chunks) and the whole vocabulary in one chunk
+    (-1: 20 GB of dlogits).  Catches what linearity cannot: a dropped k-block in the 65 536-deep K loop, a mis-strided
+    MN-major tensor map at ldds = 152 064, a tail bug in the last vocab chunk or in the split-K tail."""
+    from lce_reference import excess, sampled_d_weight_reference, sampled_rows_reference
+    from verl_b200.utils.kernel import kernels
+    from verl_b200.utils.kernel.linear_cross_entropy import linear_cross_entropy
+
+    Tn, H, V, temp = 65536, 3584, 152064, 1.0
+    g = torch.Generator(device=dev).manual_seed(21)
+    hidden = (torch.rand(Tn, H, device=dev, generator=g) - 0.5).bfloat16().requires_grad_(True)
+    weight = (torch.rand(V, H, device=dev, generator=g) - 0.5).bfloat16().requires_grad_(True)
+    labels = torch.randint(0, V, (Tn,), device=dev, generator=g)
+    g_lp = torch.rand(Tn, device=dev, generator=g) * 2 - 1
+    g_ent = torch.rand(Tn, device=dev, generator=g) - 0.5
+    tok = torch.randperm(Tn, device=dev, generator=g)[:256]
+    voc = torch.cat([torch.randperm(V, device=dev, generator=g)[:192], labels[tok[:32]],  # label rows carry the one-hot term
+                     torch.arange(V - 32, V, device=dev)])                                 # the last rows of the last chunk
+    kernels.set_backward_chunk(((V + 255) // 256) * 256 if chunk_v < 0 else chunk_v)
+    try:
+        lp, ent = linear_cross_entropy(hidden, weight, labels, temp, "none")
+        torch.autograd.backward([lp, ent], [g_lp, g_ent])
+    finally:
+        kernels.set_backward_chunk(0)
+    lp, ent = lp.detach(), ent.detach()
+    lp_r, ent_r, lse_r, eb_r, dh_r = sampled_rows_reference(hidden.detach(), weight.detach(), labels, temp, g_lp, g_ent, tok)
+    torch.testing.assert_close(lp[tok], lp_r, atol=LP_ATOL, rtol=0)
+    torch.testing.assert_close(ent[tok], ent_r, atol=LP_ATOL, rtol=0)
+    assert excess(hidden.grad[tok], dh_r, GRAD_ATOL, GRAD_RTOL) <= 0
+    # per-token scalars of ALL tokens from the kernel's outputs (verified on the sample just above)
+    tgt = (hidden.detach().float() * weight.detach()[labels].float()).sum(-1) / temp
+    lse = tgt - lp
+    eb = lse - ent
+    torch.testing.assert_close(lse[tok], lse_r, atol=LP_ATOL, rtol=0)
+    dw_r = sampled_d_weight_reference(hidden.detach(), weight.detach()[voc], voc, labels, lse, eb, temp, g_lp, g_ent)
+    assert excess(weight.grad[voc], dw_r, GRAD_ATOL, GRAD_RTOL) <= 0
+
+
 @pytest.mark.parametrize("name,Tn,H,V,world", [
     ("configs[3] Llama-3-70B, 8-way shard", 65536, 8192, 128256, 8),
     ("configs[4] Qwen2.5-32B DAPO micro-batch, 8-way shard", 262144, 5120, 152064, 8),
@@ -255,6 +297,48 @@ def test_full_size_vocab_shard_shapes(name, Tn, H, V, world, dev):
     dh_c, dw_c = ops.lce_backward(*args, 2 * g1, g2, 1.0, label_offset=rank * v_local)
     torch.testing.assert_close(dh_c.float(), 2 * dh_a.float() + dh_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
     torch.testing.assert_close(dw_c.float(), 2 * dw_a.float() + dw_b.float(), atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    del dh_a, dh_b, dh_c, dw_a, dw_b, dw_c
+    # FULL-size backward of this shard (all T tokens; per-token scalars of the shard-as-vocabulary statistics, which is a
+    # consistent soft-max over the shard's columns) vs fp32 torch on 256 sampled tokens / 256 sampled shard rows
+    from lce_reference import excess, sampled_d_weight_reference
+
+    g_lp = torch.rand(Tn, device=dev, generator=g) * 2 - 1
+    g_ent = torch.rand(Tn, device=dev, generator=g) - 0.5
+    dh, dw = ops.lce_backward(hidden, w_local, labels, lse, eb, g_lp, g_ent, 1.0, label_offset=rank * v_local)
+    tok = torch.randperm(Tn, device=dev, generator=g)[:256]
+    voc = torch.cat([torch.randperm(v_local, device=dev, generator=g)[:224], torch.arange(v_local - 32, v_local, device=dev)])
+    z = hidden[tok].float() @ w_local.float().t()
+    p = torch.exp(z - lse[tok, None])
+    onehot = ((labels[tok] - rank * v_local)[:, None] == torch.arange(v_local, device=dev)[None]).float()
+    d = g_lp[tok, None] * (onehot - p) - g_ent[tok, None] * p * (z - eb[tok, None])
+    assert excess(dh[tok], d @ w_local.float(), GRAD_ATOL, GRAD_RTOL) <= 0
+    del z, p, onehot, d
+    dw_r = sampled_d_weight_reference(hidden, w_local[voc], voc + rank * v_local, labels, lse, eb, 1.0, g_lp, g_ent)
+    assert excess(dw[voc], dw_r, GRAD_ATOL, GRAD_RTOL) <= 0
+
+
+def test_split_k_tail_gemm(dev):
+    """Plain tcgen05 GEMM with the split-K tail: the tiles of the last partial round are cut along K into fp32 partial
+    tiles and summed in a fixed order — results equal the unsplit GEMM to bf16 rounding, fp32 output to 1e-4 rel, for
+    every operand-major combination and a ragged shape (M, N, K not multiples of the tile)."""
+    from verl_b200 import ops
+
+    g = torch.Generator(device=dev).manual_seed(4)
+    for (M, N, K) in [(19008, 3584, 8192), (1000, 700, 4160), (256 * 80, 256, 2048)]:
+        A = (torch.rand(M, K, device=dev, generator=g) - 0.5).bfloat16()
+        B = (torch.rand(N, K, device=dev, generator=g) - 0.5).bfloat16()
+        ref = A.float() @ B.float().t()
+        for a_k, b_k in ((True, True), (False, True), (True, False), (False, False)):
+            Aop = A if a_k else A.t().contiguous()
+            Bop = B if b_k else B.t().contiguous()
+            if (not a_k and M % 8) or (not b_k and N % 8):
+                continue  # MN-major operands need a 16-byte row stride
+            c32 = ops.gemm_bf16(Aop, Bop, a_k, b_k, out_dtype=torch.float32, split_k=True)
+            c16 = ops.gemm_bf16(Aop, Bop, a_k, b_k, out_dtype=torch.bfloat16, split_k=True)
+            base = ops.gemm_bf16(Aop, Bop, a_k, b_k, out_dtype=torch.float32, split_k=False)
+            torch.testing.assert_close(c32, ref, atol=2e-3, rtol=1e-4)
+            torch.testing.assert_close(c32, base, atol=2e-3, rtol=1e-4)
+            torch.testing.assert_close(c16.float(), ref, atol=2e-1, rtol=1e-2)
 
 
 def test_fp16_operands(dev):

@@ -165,12 +165,45 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, C.c_double, c_float, c_void_p, c_void_p, c_void_p,
          c_void_p, c_size_t, c_void_p],
     ),
-    "vpg_lce_bwd_overlap_next": (c_int, [c_void_p, c_int]),
+    "vpg_lce_bwd_ex": (c_int, [c_void_p]),  # const vpg_lce_bwd_args* (LceBwdArgs below)
+    "vpg_lce_fwd_partials_ex": (
+        c_int,
+        [c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_int, c_int,
+         c_int, c_void_p, c_int, c_void_p],
+    ),
+    "vpg_timing_enable": (c_int, [c_int]),
+    "vpg_timing_collect": (c_int, [c_void_p, c_void_p, c_int]),
+    "vpg_gemm_splitk_workspace_bytes": (c_size_t, []),
+    "vpg_gemm_bf16_ws": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_int,
+         c_void_p, c_int64, c_void_p, c_size_t, c_void_p],
+    ),
     "vpg_masked_whiten": (
         c_int,
         [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
     ),
 }
+
+
+
+class LceBwdArgs(C.Structure):
+    """vpg_lce_bwd_args (include/vpg_b200.h) — every option of the lm-head backward as an explicit field."""
+
+    _fields_ = [
+        ("struct_size", c_size_t), ("dtype", c_int), ("hidden", c_void_p), ("weight", c_void_p),
+        ("hidden16", c_void_p), ("weight16", c_void_p), ("labels", c_void_p), ("lse", c_void_p), ("eb", c_void_p),
+        ("g_lp", c_void_p), ("g_ent", c_void_p), ("T", c_int64), ("H", c_int64), ("V", c_int64),
+        ("temperature", c_float), ("label_offset", c_int64), ("chunk_v", c_int64), ("d_hidden", c_void_p),
+        ("d_weight", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t), ("stream", c_void_p),
+        ("d_hidden_mc_f32", c_void_p), ("d_hidden_ready_event", c_void_p), ("reserve_cta_pairs", c_int),
+        ("ar_world", c_int), ("ar_rank", c_int), ("ar_epoch", C.c_uint32), ("ar_d_hidden_mc", c_void_p),
+        ("ar_flags", c_void_p), ("ar_peer_flags", C.POINTER(c_void_p)),
+    ]
+
+
+TIMING_KINDS = {0: "lm_head_fwd", 1: "dlogits_recompute", 2: "d_weight_gemm", 3: "d_hidden_gemm", 4: "gemm",
+                5: "splitk_reduce"}
 
 MASK_I64, MASK_I32, MASK_U8, MASK_F32 = 0, 1, 2, 3
 AGG_MODES = {
@@ -251,3 +284,15 @@ def mask_arg(mask: torch.Tensor):
 
 def launch_count() -> int:
     return int(load().vpg_launch_count())
+
+
+def timing_enable(on: bool) -> None:
+    check(load().vpg_timing_enable(int(bool(on))))
+
+
+def timing_collect(max_n: int = 4096) -> list[tuple[str, float]]:
+    """[(kernel kind, milliseconds)] of the tcgen05 launches recorded since the last call (synchronises their events)."""
+    kinds = (C.c_int * max_n)()
+    ms = (C.c_float * max_n)()
+    n = int(load().vpg_timing_collect(kinds, ms, max_n))
+    return [(TIMING_KINDS.get(int(kinds[i]), str(int(kinds[i]))), float(ms[i])) for i in range(n)]

@@ -7,6 +7,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <vector>
 
 #include "common.h"
 #include "tc_gemm.cuh"
@@ -44,22 +45,88 @@ static void bind_primary_context() {
     }
 }
 
-// 16-bit type of the operands (and 16-bit outputs) of the launches made by the current host call: set by the *_dt
-// entry points for the duration of the call (the plain entry points are bf16)
-static thread_local int tl_operand_dt = VPG_DT_BF16;
-// fp32 operands (VPG_DT_F32): the two gradient GEMMs of the backward run on 16-bit copies supplied by the caller
-static thread_local const void* tl_hidden16 = nullptr;
-// one-shot option of the NEXT backward call on this thread (vpg_lce_bwd_overlap_next): a cudaEvent_t to record as soon
-// as d_hidden is complete; the backward then computes d_hidden BEFORE the last d_weight GEMM and leaves that GEMM the
-// fewest workers that keep its number of scheduling rounds, so the caller's all-reduce of d_hidden runs on the freed
-// SMs under the d_weight GEMM
-static thread_local void* tl_dh_ready_event = nullptr;
-static thread_local int tl_dw_reserve_pairs = 0;
-static thread_local const void* tl_weight16 = nullptr;
-struct OperandDtypeScope {
-    int prev;
-    explicit OperandDtypeScope(int dtype) : prev(tl_operand_dt) { tl_operand_dt = dtype; }
-    ~OperandDtypeScope() { tl_operand_dt = prev; }
+// Tuning knobs: read from the environment ONCE, at the first launch of the process (never per launch).
+struct Tuning {
+    int cta_group = 2;       // VPG_CTA_GROUP=1 selects single-CTA tiles (A/B and odd SM counts)
+    int sync_slack = 2;      // VPG_SYNC_SLACK: pacing slack in checkpoints (0 disables the soft lock-step)
+    int ds_stcs = 0;         // VPG_DS_STCS=1: streaming stores for dlogits
+    int worker_perm = 0;     // VPG_WORKER_PERM=1: neighbour workers stream the same vocab split
+    int cluster1 = 1;        // VPG_CLUSTER1=2: launch single-CTA tiles as clusters of two
+    int reserve_pairs = -1;  // VPG_BWD_RESERVE_PAIRS: override of the caller's reserve_cta_pairs
+    int bwd_ws_mb = 4096;    // VPG_BWD_WS_MB: default dlogits workspace budget (MiB)
+    int splitk = 1;          // VPG_SPLITK=0 disables the split-K tail of the gradient GEMMs
+    int hint_a[4] = {0, 0, 0, 0}, hint_b[4] = {0, 0, 0, 0};  // L2 eviction hints per kernel {FWD, DS, DH, DW}
+};
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+static const Tuning& tuning() {
+    static Tuning t = [] {
+        Tuning t;
+        const char* cg = getenv("VPG_CTA_GROUP");
+        t.cta_group = (cg && cg[0] == '1') ? 1 : 2;
+        t.sync_slack = env_int("VPG_SYNC_SLACK", 2);
+        t.ds_stcs = env_int("VPG_DS_STCS", 0);
+        t.worker_perm = env_int("VPG_WORKER_PERM", 0);
+        t.cluster1 = env_int("VPG_CLUSTER1", 1);
+        t.reserve_pairs = env_int("VPG_BWD_RESERVE_PAIRS", -1);
+        t.bwd_ws_mb = env_int("VPG_BWD_WS_MB", 4096);
+        t.splitk = env_int("VPG_SPLITK", 1);
+        const char* tags[4] = {"FWD", "DS", "DH", "DW"};
+        for (int i = 0; i < 4; ++i) {
+            char name[32];
+            t.hint_a[i] = env_int("VPG_HINT_A", 0);
+            t.hint_b[i] = env_int("VPG_HINT_B", 0);
+            snprintf(name, sizeof(name), "VPG_HINT_A_%s", tags[i]);
+            t.hint_a[i] = env_int(name, t.hint_a[i]);
+            snprintf(name, sizeof(name), "VPG_HINT_B_%s", tags[i]);
+            t.hint_b[i] = env_int(name, t.hint_b[i]);
+        }
+        return t;
+    }();
+    return t;
+}
+
+// ------------------------------------------------------------------------------------ per-launch timing (bench)
+// vpg_timing_enable(1): every tcgen05 launch (and split-K reduce) is bracketed by two CUDA events on ITS stream;
+// vpg_timing_collect() synchronises them and returns (kind, milliseconds) per launch.  Off by default: no events.
+enum : int { TK_FWD = 0, TK_DS = 1, TK_DW = 2, TK_DH = 3, TK_GEMM = 4, TK_SPLITK = 5 };
+struct TimedLaunch {
+    int kind;
+    cudaEvent_t e0, e1;
+};
+static std::atomic<int> g_timing_on{0};
+static std::mutex g_timing_mu;
+static std::vector<TimedLaunch> g_timed;
+static std::vector<cudaEvent_t> g_event_pool;
+
+static cudaEvent_t timing_event() {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
+    if (!g_event_pool.empty()) {
+        cudaEvent_t e = g_event_pool.back();
+        g_event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+    return e;
+}
+struct TimingScope {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int kind;
+    cudaStream_t stream;
+    TimingScope(int kind_, cudaStream_t s) : kind(kind_), stream(s) {
+        if (!g_timing_on.load(std::memory_order_relaxed)) return;
+        e0 = timing_event(), e1 = timing_event();
+        if (e0 && e1) (void)cudaEventRecord(e0, stream);
+    }
+    ~TimingScope() {
+        if (!e0 || !e1) return;
+        (void)cudaEventRecord(e1, stream);
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        g_timed.push_back({kind, e0, e1});
+    }
 };
 
 static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
@@ -92,54 +159,64 @@ static int make_operand_tmap(CUtensorMap* tm, const void* base, int64_t rows, in
     return make_tmap(tm, base, rows, K, ld, 64, kBlockK, dt);
 }
 
-static int env_int(const char* name, int dflt) {
-    const char* e = getenv(name);
-    return e ? atoi(e) : dflt;
-}
-
-static unsigned int next_epoch() {  // one counter for all tc_gemm_kernel instantiations
-    static std::atomic<unsigned int> epoch_counter{1};
-    return epoch_counter.fetch_add(1) & 0x7FFu;
+static unsigned int next_launch_id() {  // one counter for all tc_gemm_kernel instantiations
+    static std::atomic<unsigned int> counter{1};
+    return counter.fetch_add(1);
 }
 
 // cta_group used by every tcgen05 launch: 2 (CTA pairs, 256x256 tiles) unless VPG_CTA_GROUP=1 is set
-static int cta_group() {
-    static int cg = [] {
-        const char* e = getenv("VPG_CTA_GROUP");
-        return (e && e[0] == '1') ? 1 : 2;
-    }();
-    return cg;
-}
+static int cta_group() { return tuning().cta_group; }
 static int tile_m() { return kBlockM * cta_group(); }
 static int num_workers() { return cta_group() == 2 ? sm_count() / 2 : sm_count(); }
 static int b_tile_rows() { return kBlockN / cta_group(); }
+// fp32 scratch of the split-K tail of one gradient GEMM: at most one partial tile per worker
+static size_t splitk_scratch_bytes() { return static_cast<size_t>(num_workers()) * tile_m() * kBlockN * 4; }
+
+// Split-K plan of a MODE_GEMM launch on `workers` persistent workers: the tiles of the last, partial scheduling round
+// (tiles % workers of them) are cut into ksplit K ranges, so that round costs 1/ksplit of a tile time.
+static void plan_splitk(TcParams& p, int workers, float* scratch) {
+    const int64_t tiles = static_cast<int64_t>(p.num_m_tiles) * p.num_n_tiles;
+    p.tiles_full = static_cast<int>(tiles);
+    p.ksplit = 1;
+    p.splitk_ws = nullptr;
+    if (!scratch || !tuning().splitk || workers <= 0 || tiles <= 0) return;
+    const int64_t r = tiles % workers;
+    if (r == 0) return;
+    int ks = static_cast<int>(workers / r);
+    if (ks > 8) ks = 8;
+    while (ks > 1 && p.num_k_blocks / ks < 16) --ks;  // every part keeps a mainloop worth starting
+    if (ks <= 1) return;
+    p.tiles_full = static_cast<int>(tiles - r);
+    p.ksplit = ks;
+    p.splitk_ws = scratch;
+}
 
 template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
-static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
+static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream,
+                        int timing_kind) {
     auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG, kTf32>;
+    const Tuning& tn = tuning();
     TcParams p = p_in;
-    p.sync_slack = env_int("VPG_SYNC_SLACK", 2);
-    p.sync_epoch = next_epoch();
-    p.ds_stcs = env_int("VPG_DS_STCS", 0);
-    if (env_int("VPG_HINT_A", -1) >= 0) p.hint_a = env_int("VPG_HINT_A", 0);  // tuning overrides
-    if (env_int("VPG_HINT_B", -1) >= 0) p.hint_b = env_int("VPG_HINT_B", 0);
-    {   // per-kernel overrides: VPG_HINT_{A,B}_{FWD,DS,DH,DW}
-        const char* tag = kMode == MODE_FWD ? "FWD" : kMode == MODE_DS ? "DS" : kAMn ? "DW" : "DH";
-        char name[32];
-        snprintf(name, sizeof(name), "VPG_HINT_A_%s", tag);
-        if (env_int(name, -1) >= 0) p.hint_a = env_int(name, 0);
-        snprintf(name, sizeof(name), "VPG_HINT_B_%s", tag);
-        if (env_int(name, -1) >= 0) p.hint_b = env_int(name, 0);
-    }
+    const unsigned int id = next_launch_id();
+    p.sync_slack = tn.sync_slack;
+    p.sync_epoch = id & 0x7FFu;
+    p.pace_slot = static_cast<int>(id % kPaceSlots);
+    p.ds_stcs = tn.ds_stcs;
+    const int hk = kMode == MODE_FWD ? 0 : kMode == MODE_DS ? 1 : kAMn ? 3 : 2;
+    p.hint_a = tn.hint_a[hk];
+    p.hint_b = tn.hint_b[hk];
+    if (kMode != MODE_GEMM) p.tiles_full = p.num_m_tiles * p.num_splits, p.ksplit = 1, p.splitk_ws = nullptr;
     constexpr int smem = TileCfg<kCG>::kSmemBytes + (kMode == MODE_GEMM ? kRedScratchBytes : 0);
     // per-device attribute: set every call (cheap) so multi-device processes are handled
     cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (attr_err != cudaSuccess)
         return set_error(VPG_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(attr_err));
-    const int64_t units = static_cast<int64_t>(p.num_m_tiles) * p.num_splits;
+    const int64_t tiles = static_cast<int64_t>(p.num_m_tiles) * p.num_splits;
+    const int64_t units = (kMode == MODE_GEMM) ? p.tiles_full + (tiles - p.tiles_full) * p.ksplit : tiles;
     if (units <= 0) return VPG_OK;
     int workers = static_cast<int>(units < num_workers() ? units : num_workers());
     if (p.max_workers > 0 && workers > p.max_workers) workers = p.max_workers;
+    if (p.ar_world > 1) workers = p.max_workers > 0 ? p.max_workers : num_workers();  // all-reduce warps of every CTA
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(static_cast<unsigned>(workers * kCG));
     cfg.blockDim = dim3(kNumThreads);
@@ -147,32 +224,47 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (kCG == 1 && env_int("VPG_CLUSTER1", 1) == 2 && (workers % 2) == 0) ? 2 : kCG;
+    attr[0].val.clusterDim.x = (kCG == 1 && tn.cluster1 == 2 && (workers % 2) == 0) ? 2 : kCG;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+    cudaError_t e;
+    {
+        TimingScope ts(timing_kind, stream);
+        e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+    }
     count_launch();
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
         return set_error(VPG_ERR_CUDA, "tc_gemm_kernel launch failed: %s", cudaGetErrorString(e));
     }
+    if (kMode == MODE_GEMM && p.ksplit > 1) {
+        const int tail_tiles = static_cast<int>(tiles) - p.tiles_full;
+        const int64_t threads = static_cast<int64_t>(tail_tiles) * (kBlockM * kCG) * kBlockN / 4;
+        TimingScope ts(TK_SPLITK, stream);
+        splitk_reduce_kernel<<<static_cast<unsigned>(ceil_div(threads, 256)), 256, 0, stream>>>(
+            p.splitk_ws, tail_tiles, p.ksplit, p.tiles_full, p.num_n_tiles, kBlockM * kCG, p.M, p.N, p.out, p.ldc,
+            p.out_mode, p.accum, p.ld_accum, p.f16);
+        VPG_LAUNCH_CHECK();
+    }
     return VPG_OK;
 }
 
 template <int kMode, bool kAMn, bool kBMn>
-static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
-    if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream);
-    return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream);
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream,
+                     int timing_kind) {
+    if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream, timing_kind);
+    return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream, timing_kind);
 }
 // lm-head statistics / dlogits launches in the operand type `dt` of the call: bf16 / fp16 (kind::f16) or fp32 (TF32)
 template <int kMode>
 static int launch_tc_lmhead(const CUtensorMap& ta, const CUtensorMap& tb, TcParams p, int dt, cudaStream_t stream) {
     p.f16 = (dt == VPG_DT_F16);
-    if (dt != VPG_DT_F32) return launch_tc<kMode, false, false>(ta, tb, p, stream);
-    if (cta_group() == 2) return launch_tc_cg<kMode, false, false, 2, true>(ta, tb, p, stream);
-    return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream);
+    const int tk = kMode == MODE_FWD ? TK_FWD : TK_DS;
+    if (dt != VPG_DT_F32) return launch_tc<kMode, false, false>(ta, tb, p, stream, tk);
+    if (cta_group() == 2) return launch_tc_cg<kMode, false, false, 2, true>(ta, tb, p, stream, tk);
+    return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream, tk);
 }
 
 // balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
@@ -262,6 +354,34 @@ using namespace vpg;
 
 extern "C" {
 
+int vpg_timing_enable(int on) {
+    g_timing_on.store(on ? 1 : 0);
+    if (!on) {  // drop whatever was recorded and not collected
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        for (auto& t : g_timed) g_event_pool.push_back(t.e0), g_event_pool.push_back(t.e1);
+        g_timed.clear();
+    }
+    return VPG_OK;
+}
+
+int vpg_timing_collect(int* kinds, float* ms, int max_n) {
+    std::vector<TimedLaunch> taken;
+    {
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        taken.swap(g_timed);
+    }
+    int n = 0;
+    for (auto& t : taken) {
+        float dt = -1.f;
+        if (cudaEventSynchronize(t.e1) == cudaSuccess) (void)cudaEventElapsedTime(&dt, t.e0, t.e1);
+        if (n < max_n && kinds && ms) kinds[n] = t.kind, ms[n] = dt, ++n;
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        g_event_pool.push_back(t.e0), g_event_pool.push_back(t.e1);
+    }
+    (void)cudaGetLastError();
+    return n;
+}
+
 int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
     (void)H;
     if (T <= 0 || V <= 0) return 1;
@@ -273,48 +393,32 @@ int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
 int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
                          int64_t V, float temperature, int64_t label_offset, int num_splits, float* partials,
                          void* stream) {
-    return vpg_lce_fwd_partials_push(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
-                                     0, num_splits, 0, nullptr, 0, stream);
+    return vpg_lce_fwd_partials_ex(VPG_DT_BF16, hidden, weight, labels, T, H, V, temperature, label_offset, num_splits,
+                                   partials, 0, num_splits, 0, nullptr, 0, stream);
 }
 
 int vpg_lce_fwd_partials_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
                             int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
                             float* partials, void* stream) {
-    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16 || dtype == VPG_DT_F32, "unknown operand dtype %d", dtype);
-    OperandDtypeScope scope(dtype);
-    return vpg_lce_fwd_partials(hidden, weight, labels, T, H, V, temperature, label_offset, num_splits, partials,
-                                stream);
-}
-
-int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, const float* lse,
-                   const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
-                   float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight,
-                   void* workspace, size_t workspace_bytes, void* stream) {
-    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16, "operand dtype must be VPG_DT_BF16 or VPG_DT_F16");
-    OperandDtypeScope scope(dtype);
-    return vpg_lce_bwd(hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset, chunk_v,
-                       d_hidden, d_weight, workspace, workspace_bytes, stream);
-}
-
-int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* hidden_bf16, const void* weight_bf16,
-                    const int64_t* labels, const float* lse, const float* eb, const float* g_lp, const float* g_ent,
-                    int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
-                    void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream) {
-    VPG_CHECK_ARG(hidden_bf16 && weight_bf16, "fp32 backward needs the bf16 copies of hidden and weight");
-    OperandDtypeScope scope(VPG_DT_F32);
-    tl_hidden16 = hidden_bf16, tl_weight16 = weight_bf16;
-    const int rc = vpg_lce_bwd(hidden_f32, weight_f32, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset,
-                               chunk_v, d_hidden_f32, d_weight_f32, workspace, workspace_bytes, stream);
-    tl_hidden16 = tl_weight16 = nullptr;
-    return rc;
+    return vpg_lce_fwd_partials_ex(dtype, hidden, weight, labels, T, H, V, temperature, label_offset, num_splits,
+                                   partials, 0, num_splits, 0, nullptr, 0, stream);
 }
 
 int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
                               int64_t V, float temperature, int64_t label_offset, int num_splits, float* partials,
                               int part_split0, int part_total, int partials_is_multicast, void* const* push_ptrs,
                               int n_push, void* stream) {
+    return vpg_lce_fwd_partials_ex(VPG_DT_BF16, hidden, weight, labels, T, H, V, temperature, label_offset, num_splits,
+                                   partials, part_split0, part_total, partials_is_multicast, push_ptrs, n_push, stream);
+}
+
+int vpg_lce_fwd_partials_ex(int dt, const void* hidden, const void* weight, const int64_t* labels, int64_t T,
+                            int64_t H, int64_t V, float temperature, int64_t label_offset, int num_splits,
+                            float* partials, int part_split0, int part_total, int partials_is_multicast,
+                            void* const* push_ptrs, int n_push, void* stream) {
     int rc = check_lce_shapes(T, H, V);
     if (rc) return rc;
+    VPG_CHECK_ARG(dt == VPG_DT_BF16 || dt == VPG_DT_F16 || dt == VPG_DT_F32, "unknown operand dtype %d", dt);
     VPG_CHECK_ARG(hidden && weight && labels && (partials || n_push > 0), "null pointer argument");
     VPG_CHECK_ARG(part_split0 >= 0 && part_total >= part_split0 + num_splits, "partials slot [%d, %d) exceeds %d parts",
                   part_split0, part_split0 + num_splits, part_total);
@@ -326,7 +430,6 @@ int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int6
     TcParams p{};
     p.num_m_tiles = static_cast<int>(ceil_div(T, tile_m()));
     p.num_n_tiles = static_cast<int>(ceil_div(V, kBlockN));
-    const int dt = tl_operand_dt;
     VPG_CHECK_ARG(dt == VPG_DT_BF16 || (n_push == 0 && !partials_is_multicast),
                   "the push variants take bf16 operands only");
     p.num_k_blocks = static_cast<int>(H / (dt == VPG_DT_F32 ? kBlockK / 2 : kBlockK));
@@ -349,8 +452,7 @@ int vpg_lce_fwd_partials_push(const void* hidden, const void* weight, const int6
         VPG_CHECK_ARG(push_ptrs[i], "push_ptrs[%d] is null", i);
         p.push_ptrs[i] = static_cast<float*>(push_ptrs[i]);
     }
-    p.worker_perm = env_int("VPG_WORKER_PERM", 0) ? num_splits : 0;
-    if (const char* e = getenv("VPG_DEBUG_TRACE_PTR")) p.debug_trace = reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0));
+    p.worker_perm = tuning().worker_perm ? num_splits : 0;
     CUtensorMap ta, tb;
     if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM, dt))) return rc;
     if ((rc = make_operand_tmap(&tb, weight, V, H, H, false, b_tile_rows(), dt))) return rc;
@@ -370,12 +472,13 @@ int vpg_lce_finalize(const float* partials, int num_parts, int64_t T, float temp
 }
 
 int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V) {
-    return vpg_lce_bwd_chunk_for_budget(T, H, V, static_cast<int64_t>(env_int("VPG_BWD_WS_MB", 4096)) << 20);
+    return vpg_lce_bwd_chunk_for_budget(T, H, V, static_cast<int64_t>(tuning().bwd_ws_mb) << 20);
 }
 
 int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t budget) {
     // Largest chunk whose bf16 dlogits buffer fits the budget, then the chunk count (up to +8) that wastes the fewest
-    // waves of the persistent grid in the three kernels of a chunk (cost in units of tile x k-block).
+    // waves of the persistent grid in the three kernels of a chunk (cost in units of tile x k-block; the gradient
+    // GEMMs cut the tiles of their last partial round along K, so that round costs 1/ksplit of a tile).
     const int64_t t_pad = round_up(T > 0 ? T : 1, 2 * kBlockM);
     const int64_t v_tiles = ceil_div(V, kBlockN);
     if (budget < (1 << 20)) budget = 1 << 20;  // bytes of the 16-bit dlogits workspace
@@ -387,15 +490,22 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
     const int64_t min_chunks = ceil_div(v_tiles, max_tiles);
     int64_t best_c = max_tiles;
     double best_cost = 1e300;
+    auto rounds = [&](int64_t tiles) -> double {  // scheduling rounds of a gradient GEMM with the split-K tail
+        const int64_t r = tiles % W;
+        if (r == 0 || !tuning().splitk) return static_cast<double>(ceil_div(tiles, W));
+        int64_t ks = W / r;
+        if (ks > 8) ks = 8;
+        return static_cast<double>(tiles / W) + 1.0 / static_cast<double>(ks < 1 ? 1 : ks);
+    };
     for (int64_t nc = min_chunks; nc <= min_chunks + 8 && nc <= v_tiles; ++nc) {
         const int64_t c = ceil_div(v_tiles, nc);
         double cost = 0;
         for (int64_t done = 0; done < v_tiles; done += c) {
             const int64_t ct = (v_tiles - done) < c ? (v_tiles - done) : c;  // tiles in this chunk
-            cost += static_cast<double>(ceil_div(m_t * ct, W)) * (H / kBlockK);                       // dlogits
-            cost += static_cast<double>(ceil_div(ceil_div(ct * kBlockN, tm) * n_h, W)) * (t_pad / kBlockK);  // d_weight
-            cost += static_cast<double>(ceil_div(m_t * n_h, W)) * (ct * kBlockN / kBlockK);            // d_hidden
-            cost += 0.02 * (t_pad / kBlockK);                                                           // launches, fp32 RMW
+            cost += static_cast<double>(ceil_div(m_t * ct, W)) * (H / kBlockK);                  // dlogits
+            cost += rounds(ceil_div(ct * kBlockN, tm) * n_h) * (t_pad / kBlockK);                 // d_weight
+            cost += rounds(m_t * n_h) * (ct * kBlockN / kBlockK);                                 // d_hidden
+            cost += 0.02 * (t_pad / kBlockK);                                                     // launches, fp32 RMW
         }
         if (cost < best_cost) {
             best_cost = cost;
@@ -413,7 +523,8 @@ size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chun
     if (chunk_v > v_pad) chunk_v = v_pad;
     size_t bytes = static_cast<size_t>(t_pad) * chunk_v * 2;
     bytes = round_up(bytes, 256);
-    if (chunk_v < v_pad) bytes += static_cast<size_t>(T) * H * 4;  // fp32 d_hidden accumulator
+    if (chunk_v < v_pad) bytes += round_up(static_cast<int64_t>(T) * H * 4, 256);  // fp32 d_hidden accumulator
+    bytes += splitk_scratch_bytes();                                               // split-K tail partial tiles
     return bytes + 256;
 }
 
@@ -421,59 +532,116 @@ int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, c
                 const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V, float temperature,
                 int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight, void* workspace,
                 size_t workspace_bytes, void* stream_) {
-    return vpg_lce_bwd_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset, chunk_v,
-                             d_hidden, d_weight, workspace, workspace_bytes, nullptr, stream_);
+    return vpg_lce_bwd_dt(VPG_DT_BF16, hidden, weight, labels, lse, eb, g_lp, g_ent, T, H, V, temperature, label_offset,
+                          chunk_v, d_hidden, d_weight, workspace, workspace_bytes, stream_);
+}
+
+int vpg_lce_bwd_dt(int dtype, const void* hidden, const void* weight, const int64_t* labels, const float* lse,
+                   const float* eb, const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V,
+                   float temperature, int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight,
+                   void* workspace, size_t workspace_bytes, void* stream) {
+    VPG_CHECK_ARG(dtype == VPG_DT_BF16 || dtype == VPG_DT_F16, "operand dtype must be VPG_DT_BF16 or VPG_DT_F16");
+    vpg_lce_bwd_args a{};
+    a.struct_size = sizeof(a);
+    a.dtype = dtype, a.hidden = hidden, a.weight = weight, a.labels = labels, a.lse = lse, a.eb = eb;
+    a.g_lp = g_lp, a.g_ent = g_ent, a.T = T, a.H = H, a.V = V, a.temperature = temperature;
+    a.label_offset = label_offset, a.chunk_v = chunk_v, a.d_hidden = d_hidden, a.d_weight = d_weight;
+    a.workspace = workspace, a.workspace_bytes = workspace_bytes, a.stream = stream;
+    return vpg_lce_bwd_ex(&a);
+}
+
+int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* hidden_bf16, const void* weight_bf16,
+                    const int64_t* labels, const float* lse, const float* eb, const float* g_lp, const float* g_ent,
+                    int64_t T, int64_t H, int64_t V, float temperature, int64_t label_offset, int64_t chunk_v,
+                    void* d_hidden_f32, void* d_weight_f32, void* workspace, size_t workspace_bytes, void* stream) {
+    vpg_lce_bwd_args a{};
+    a.struct_size = sizeof(a);
+    a.dtype = VPG_DT_F32, a.hidden = hidden_f32, a.weight = weight_f32, a.hidden16 = hidden_bf16;
+    a.weight16 = weight_bf16, a.labels = labels, a.lse = lse, a.eb = eb, a.g_lp = g_lp, a.g_ent = g_ent;
+    a.T = T, a.H = H, a.V = V, a.temperature = temperature, a.label_offset = label_offset, a.chunk_v = chunk_v;
+    a.d_hidden = d_hidden_f32, a.d_weight = d_weight_f32, a.workspace = workspace, a.workspace_bytes = workspace_bytes;
+    a.stream = stream;
+    return vpg_lce_bwd_ex(&a);
 }
 
 int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* labels, const float* lse, const float* eb,
                       const float* g_lp, const float* g_ent, int64_t T, int64_t H, int64_t V, float temperature,
                       int64_t label_offset, int64_t chunk_v, void* d_hidden, void* d_weight, void* workspace,
-                      size_t workspace_bytes, float* d_hidden_mc_f32, void* stream_) {
+                      size_t workspace_bytes, float* d_hidden_mc_f32, void* stream) {
+    vpg_lce_bwd_args a{};
+    a.struct_size = sizeof(a);
+    a.dtype = VPG_DT_BF16, a.hidden = hidden, a.weight = weight, a.labels = labels, a.lse = lse, a.eb = eb;
+    a.g_lp = g_lp, a.g_ent = g_ent, a.T = T, a.H = H, a.V = V, a.temperature = temperature;
+    a.label_offset = label_offset, a.chunk_v = chunk_v, a.d_hidden = d_hidden, a.d_weight = d_weight;
+    a.workspace = workspace, a.workspace_bytes = workspace_bytes, a.d_hidden_mc_f32 = d_hidden_mc_f32, a.stream = stream;
+    return vpg_lce_bwd_ex(&a);
+}
+
+int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
+    VPG_CHECK_ARG(args && args->struct_size == sizeof(vpg_lce_bwd_args), "vpg_lce_bwd_args: struct_size mismatch");
+    const vpg_lce_bwd_args& a = *args;
+    const int64_t T = a.T, H = a.H, V = a.V;
     int rc = check_lce_shapes(T, H, V);
     if (rc) return rc;
-    VPG_CHECK_ARG(hidden && weight && labels && lse && eb && (d_hidden || d_hidden_mc_f32) && d_weight,
+    const int dt = a.dtype;
+    VPG_CHECK_ARG(dt == VPG_DT_BF16 || dt == VPG_DT_F16 || dt == VPG_DT_F32, "unknown operand dtype %d", dt);
+    VPG_CHECK_ARG(a.hidden && a.weight && a.labels && a.lse && a.eb && (a.d_hidden || a.d_hidden_mc_f32) && a.d_weight,
                   "null pointer argument");
-    VPG_CHECK_ARG(temperature > 0.f, "temperature must be > 0");
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    void* dh_ready_event = tl_dh_ready_event;  // one-shot
-    const int dw_reserve_pairs = tl_dw_reserve_pairs;
-    tl_dh_ready_event = nullptr, tl_dw_reserve_pairs = 0;
-    if (d_hidden_mc_f32) dh_ready_event = nullptr;  // the fused all-reduce variant has its own schedule
+    VPG_CHECK_ARG(a.temperature > 0.f, "temperature must be > 0");
+    cudaStream_t stream = static_cast<cudaStream_t>(a.stream);
+    float* d_hidden_mc_f32 = a.d_hidden_mc_f32;
+    void* dh_ready_event = d_hidden_mc_f32 ? nullptr : a.d_hidden_ready_event;  // the multimem.red variant has its own schedule
+    const bool fused_ar = a.ar_world > 1;
     // operand type of the call.  fp32: the recompute runs as TF32 on the fp32 operands like the forward, dlogits are
     // bf16, the two gradient GEMMs read the caller's bf16 copies and write fp32 gradients.
-    const int dt = tl_operand_dt;
     const bool f32 = (dt == VPG_DT_F32);
     const int dt16 = f32 ? VPG_DT_BF16 : dt;
-    const void* hidden16 = f32 ? tl_hidden16 : hidden;
-    const void* weight16 = f32 ? tl_weight16 : weight;
+    const void* hidden16 = f32 ? a.hidden16 : a.hidden;
+    const void* weight16 = f32 ? a.weight16 : a.weight;
     const int64_t gsz = f32 ? 4 : 2;  // bytes per gradient element
-    VPG_CHECK_ARG(!f32 || (hidden16 && weight16 && !d_hidden_mc_f32), "fp32 operands: use vpg_lce_bwd_f32");
-    VPG_CHECK_ARG(dt == VPG_DT_BF16 || !d_hidden_mc_f32, "the fused d_hidden all-reduce takes bf16 operands only");
+    VPG_CHECK_ARG(!f32 || (hidden16 && weight16 && !d_hidden_mc_f32), "fp32 operands need the bf16 copies (hidden16, weight16)");
+    VPG_CHECK_ARG(dt == VPG_DT_BF16 || !d_hidden_mc_f32, "the fused d_hidden reduction takes bf16 operands only");
+    if (fused_ar) {
+        VPG_CHECK_ARG(dt == VPG_DT_BF16 && !d_hidden_mc_f32 && !dh_ready_event,
+                      "the in-kernel all-reduce takes bf16 operands and excludes the other d_hidden reduction modes");
+        VPG_CHECK_ARG(a.ar_world <= kMaxPeers && a.ar_rank >= 0 && a.ar_rank < a.ar_world && a.ar_d_hidden_mc &&
+                          a.ar_flags && a.ar_peer_flags && a.d_hidden,
+                      "in-kernel all-reduce: world in [2,%d], rank, multicast address, flags and peer flags required",
+                      kMaxPeers);
+        VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(a.ar_d_hidden_mc) & 15) == 0 && (T * H) % 8 == 0,
+                      "in-kernel all-reduce: the buffer must be a whole number of aligned 16-byte vectors");
+    }
     if (T == 0) {
-        VPG_CUDA(cudaMemsetAsync(d_weight, 0, static_cast<size_t>(V) * H * gsz, stream));
+        VPG_CUDA(cudaMemsetAsync(a.d_weight, 0, static_cast<size_t>(V) * H * gsz, stream));
         return VPG_OK;
     }
+    int64_t chunk_v = a.chunk_v;
     if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
     VPG_CHECK_ARG(chunk_v % kBlockN == 0, "chunk_v must be a multiple of %d", kBlockN);
     const int64_t t_pad = round_up(T, 2 * kBlockM);  // dlogits rows: multiple of the largest m tile (256)
     const int64_t v_pad = round_up(V, kBlockN);
     if (chunk_v > v_pad) chunk_v = v_pad;
     const size_t need = vpg_lce_bwd_workspace_bytes(T, H, V, chunk_v);
-    if (!workspace || workspace_bytes < need)
+    if (!a.workspace || a.workspace_bytes < need)
         return set_error(VPG_ERR_WORKSPACE, "lce_bwd workspace too small: need %zu bytes, got %zu", need,
-                         workspace_bytes);
-    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "workspace must be 256-byte aligned");
-    __nv_bfloat16* ds = reinterpret_cast<__nv_bfloat16*>(workspace);
+                         a.workspace_bytes);
+    VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, "workspace must be 256-byte aligned");
+    uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
+    __nv_bfloat16* ds = reinterpret_cast<__nv_bfloat16*>(ws);
     const int64_t ldds = chunk_v;
-    float* dh_acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) +
-                                             round_up(static_cast<int64_t>(t_pad) * chunk_v * 2, 256));
+    size_t off = round_up(static_cast<int64_t>(t_pad) * chunk_v * 2, 256);
+    float* dh_acc = reinterpret_cast<float*>(ws + off);
+    if (chunk_v < v_pad) off += round_up(static_cast<int64_t>(T) * H * 4, 256);
+    float* splitk_scratch = reinterpret_cast<float*>(ws + off);
     const int num_chunks = static_cast<int>(ceil_div(v_pad, chunk_v));
     const int m_tiles_t = static_cast<int>(t_pad / tile_m());
+    const uint8_t* weight = reinterpret_cast<const uint8_t*>(a.weight);
+    void* d_hidden = a.d_hidden;
 
     for (int ci = 0; ci < num_chunks; ++ci) {
         const int64_t v0 = static_cast<int64_t>(ci) * chunk_v;
         const int64_t vc = (V - v0) < chunk_v ? (V - v0) : chunk_v;
-        const uint8_t* w_chunk = reinterpret_cast<const uint8_t*>(weight) + v0 * H * (f32 ? 4 : 2);
+        const uint8_t* w_chunk = weight + v0 * H * (f32 ? 4 : 2);
         const __nv_bfloat16* w16_chunk = reinterpret_cast<const __nv_bfloat16*>(weight16) + v0 * H;
         const int n_tiles_c = static_cast<int>(ceil_div(vc, kBlockN));
         CUtensorMap ta, tb;
@@ -486,23 +654,23 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
             p.M = static_cast<int>(T);
             p.N = static_cast<int>(vc);
-            p.scale_log2 = 1.4426950408889634f / temperature;
-            p.inv_temp = 1.0f / temperature;
-            p.labels = reinterpret_cast<const long long*>(labels);
-            p.label_offset = label_offset + v0;
-            p.lse = lse;
-            p.eb = eb;
-            p.g_lp = g_lp;
-            p.g_ent = g_ent;
+            p.scale_log2 = 1.4426950408889634f / a.temperature;
+            p.inv_temp = 1.0f / a.temperature;
+            p.labels = reinterpret_cast<const long long*>(a.labels);
+            p.label_offset = a.label_offset + v0;
+            p.lse = a.lse;
+            p.eb = a.eb;
+            p.g_lp = a.g_lp;
+            p.g_ent = a.g_ent;
             p.ds = ds;
             p.ldds = ldds;
-            if ((rc = make_operand_tmap(&ta, hidden, T, H, H, false, kBlockM, dt))) return rc;
+            if ((rc = make_operand_tmap(&ta, a.hidden, T, H, H, false, kBlockM, dt))) return rc;
             if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, b_tile_rows(), dt))) return rc;
             if ((rc = launch_tc_lmhead<MODE_DS>(ta, tb, p, dt, stream))) return rc;
         }
         const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
         // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
-        auto run_d_weight = [&](int max_workers) -> int {
+        auto run_d_weight = [&](int max_workers, bool with_allreduce) -> int {
             int rc = 0;
             CUtensorMap ta, tb;
             TcParams p{};
@@ -513,14 +681,25 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.tiles_per_split = 1;
             p.M = static_cast<int>(vc);
             p.N = static_cast<int>(H);
-            p.out = reinterpret_cast<uint8_t*>(d_weight) + v0 * H * gsz;
+            p.out = reinterpret_cast<uint8_t*>(a.d_weight) + v0 * H * gsz;
             p.ldc = H;
             p.out_mode = f32 ? OUT_F32 : OUT_BF16;
             p.f16 = (dt16 == VPG_DT_F16);
             p.max_workers = max_workers;
+            plan_splitk(p, max_workers > 0 && max_workers < num_workers() ? max_workers : num_workers(), splitk_scratch);
+            if (with_allreduce) {
+                p.ar_world = a.ar_world, p.ar_rank = a.ar_rank, p.ar_epoch = a.ar_epoch;
+                p.ar_mc = a.ar_d_hidden_mc;
+                p.ar_nvec = T * H / 8;
+                p.ar_flags = a.ar_flags;
+                for (int i = 0; i < a.ar_world; ++i) {
+                    VPG_CHECK_ARG(a.ar_peer_flags[i], "ar_peer_flags[%d] is null", i);
+                    p.ar_peer_flags[i] = a.ar_peer_flags[i];
+                }
+            }
             if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM, dt16))) return rc;
             if ((rc = make_operand_tmap(&tb, hidden16, H, T, H, true, kBlockN, dt16))) return rc;
-            if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream))) return rc;
+            if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream, TK_DW))) return rc;
             return VPG_OK;
         };
         // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
@@ -535,12 +714,14 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             p.tiles_per_split = 1;
             p.M = static_cast<int>(T);
             p.N = static_cast<int>(H);
+            bool splitk_ok = true;
             if (d_hidden_mc_f32 && ci == num_chunks - 1) {
                 VPG_CHECK_ARG(H % 32 == 0, "fused d_hidden all-reduce needs H %% 32 == 0");
                 // fused all-reduce: the last chunk's epilogue adds (this rank's fp32 sum over all its vocab chunks)
                 // into every rank's fp32 buffer through the multicast address, tile by tile
                 p.out = d_hidden_mc_f32, p.ldc = H, p.out_mode = OUT_F32_MCRED;
                 p.accum = (num_chunks > 1) ? dh_acc : nullptr, p.ld_accum = H;
+                splitk_ok = false;
             } else if (f32) {  // fp32 gradients accumulate in place
                 p.out = d_hidden, p.ldc = H, p.out_mode = (ci == 0) ? OUT_F32 : OUT_F32_ACC;
                 p.accum = reinterpret_cast<float*>(d_hidden), p.ld_accum = H;
@@ -555,16 +736,19 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
                 p.accum = dh_acc, p.ld_accum = H;
             }
             p.f16 = (dt16 == VPG_DT_F16);
+            plan_splitk(p, num_workers(), splitk_ok ? splitk_scratch : nullptr);
             if ((rc = make_operand_tmap(&ta, ds, t_pad, vc_cols, ldds, false, kBlockM, dt16))) return rc;
             if ((rc = make_operand_tmap(&tb, w16_chunk, H, vc, H, true, kBlockN, dt16))) return rc;
-            if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream))) return rc;
+            if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream, TK_DH))) return rc;
             return VPG_OK;
         };
-        const bool overlap = dh_ready_event && ci == num_chunks - 1;
-        if (!overlap) {
-            if ((rc = run_d_weight(0))) return rc;
+        const bool last = ci == num_chunks - 1;
+        if (last && fused_ar) {
+            // d_hidden first (it is complete on every rank before that rank enters the next kernel); the d_weight GEMM
+            // then carries the all-reduce of d_hidden in its spare warps, on all its SMs
             if ((rc = run_d_hidden())) return rc;
-        } else {
+            if ((rc = run_d_weight(0, true))) return rc;
+        } else if (last && dh_ready_event) {
             // d_hidden first; the event releases the caller's all-reduce, which then runs under the d_weight GEMM on
             // the SMs that GEMM can spare for free: the fewest workers with the same number of scheduling rounds
             if ((rc = run_d_hidden())) return rc;
@@ -573,18 +757,14 @@ int vpg_lce_bwd_mcred(const void* hidden, const void* weight, const int64_t* lab
             const int64_t rounds = ceil_div(tiles, static_cast<int64_t>(num_workers()));
             int spare_cap = static_cast<int>(ceil_div(tiles, rounds));
             // at least this many CTA pairs are left to the collective (caller's choice; env override for tuning)
-            const int reserve = env_int("VPG_BWD_RESERVE_PAIRS", dw_reserve_pairs);
+            const int reserve = tuning().reserve_pairs >= 0 ? tuning().reserve_pairs : a.reserve_cta_pairs;
             if (reserve > 0 && spare_cap > num_workers() - reserve) spare_cap = num_workers() - reserve;
-            if ((rc = run_d_weight(spare_cap < 1 ? 1 : spare_cap))) return rc;
+            if ((rc = run_d_weight(spare_cap < 1 ? 1 : spare_cap, false))) return rc;
+        } else {
+            if ((rc = run_d_weight(0, false))) return rc;
+            if ((rc = run_d_hidden())) return rc;
         }
     }
-    return VPG_OK;
-}
-
-int vpg_lce_bwd_overlap_next(void* d_hidden_ready_event, int reserve_cta_pairs) {
-    VPG_CHECK_ARG(reserve_cta_pairs >= 0, "reserve_cta_pairs must be >= 0");
-    tl_dh_ready_event = d_hidden_ready_event;
-    tl_dw_reserve_pairs = reserve_cta_pairs;
     return VPG_OK;
 }
 
@@ -605,11 +785,23 @@ int vpg_cast_f32_bf16(const float* src, void* dst_bf16, int64_t n, void* stream)
 int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
                   int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
                   int64_t ld_accum, void* stream_) {
+    return vpg_gemm_bf16_ws(A, B, M, N, K, lda, ldb, a_kmajor, b_kmajor, C, ldc, out_mode, accum_f32, ld_accum,
+                            nullptr, 0, stream_);
+}
+
+size_t vpg_gemm_splitk_workspace_bytes(void) { return splitk_scratch_bytes(); }
+
+int vpg_gemm_bf16_ws(const void* A, const void* B, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                     int a_kmajor, int b_kmajor, void* C, int64_t ldc, int out_mode, float* accum_f32,
+                     int64_t ld_accum, void* workspace, size_t workspace_bytes, void* stream_) {
     VPG_CHECK_ARG(A && B && C, "null pointer argument");
     VPG_CHECK_ARG(M > 0 && N > 0 && K > 0, "invalid GEMM shape");
     VPG_CHECK_ARG(out_mode >= 0 && out_mode <= 3, "invalid out_mode %d", out_mode);
     VPG_CHECK_ARG(ldc % 8 == 0, "ldc must be a multiple of 8");
     VPG_CHECK_ARG(out_mode != OUT_BF16_FROM_ACC || (accum_f32 && ld_accum % 4 == 0), "accum buffer required");
+    VPG_CHECK_ARG(!workspace || (workspace_bytes >= splitk_scratch_bytes() &&
+                                 (reinterpret_cast<uintptr_t>(workspace) & 15) == 0),
+                  "split-K workspace too small or misaligned (vpg_gemm_splitk_workspace_bytes)");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     TcParams p{};
     p.num_m_tiles = static_cast<int>(ceil_div(M, tile_m()));
@@ -621,17 +813,18 @@ int vpg_gemm_bf16(const void* A, const void* B, int64_t M, int64_t N, int64_t K,
     p.N = static_cast<int>(N);
     p.out = C;
     p.ldc = ldc;
-    p.out_mode = env_int("VPG_DEBUG_SKIP_EPI", 0) ? OUT_DEBUG_SKIP : out_mode;
+    p.out_mode = out_mode;
     p.accum = accum_f32;
     p.ld_accum = ld_accum;
+    plan_splitk(p, num_workers(), static_cast<float*>(workspace));
     CUtensorMap ta, tb;
     int rc;
     if ((rc = make_operand_tmap(&ta, A, M, K, lda, !a_kmajor, kBlockM))) return rc;
     if ((rc = make_operand_tmap(&tb, B, N, K, ldb, !b_kmajor, b_tile_rows()))) return rc;
-    if (a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, false, false>(ta, tb, p, stream);
-    if (a_kmajor && !b_kmajor) return launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream);
-    if (!a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, true, false>(ta, tb, p, stream);
-    return launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream);
+    if (a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, false, false>(ta, tb, p, stream, TK_GEMM);
+    if (a_kmajor && !b_kmajor) return launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream, TK_GEMM);
+    if (!a_kmajor && b_kmajor) return launch_tc<MODE_GEMM, true, false>(ta, tb, p, stream, TK_GEMM);
+    return launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream, TK_GEMM);
 }
 
 }  // extern "C"

@@ -7,7 +7,8 @@
 //   warp 8      TMA producer (lane 0 issues cp.async.bulk.tensor)
 //   warp 9      MMA issuer   (lane 0 issues tcgen05.mma / tcgen05.commit)
 //   warp 10     TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
-//   warp 11     idle
+//   warp 11     MODE_GEMM with TcParams::ar_world > 1: NVLS all-reduce worker (multimem.ld_reduce / multimem.st over the
+//               NVSwitch) of a [T,H] bf16 buffer while the GEMM runs; idle otherwise
 // With kCG = 2 the same roles run in both CTAs of a pair except the MMA issuer (leader CTA only); TMA transaction
 // bytes of both CTAs are signalled on the leader's full barrier, tcgen05.commit multicasts to both CTAs.
 //
@@ -66,7 +67,9 @@ enum : int {
     OUT_F32_ACC = 2,
     OUT_BF16_FROM_ACC = 3,
     OUT_F32_MCRED = 4,  // fused all-reduce: multimem.red.add.f32 of (acc [+ accum]) into a multicast fp32 buffer
+#ifdef VPG_DEBUG_TOOLS
     OUT_DEBUG_SKIP = 7
+#endif
 };
 constexpr int kMaxPeers = 8;
 
@@ -103,7 +106,23 @@ struct TcParams {
     int out_mode;
     int sync_slack;           // > 0: soft lock-step of the workers (tiles of slack), see pace_wait
     unsigned int sync_epoch;  // launch counter (host), distinguishes stale progress counters
+    int pace_slot;            // row of g_progress owned by this launch (host: launch counter % kPaceSlots)
+#ifdef VPG_DEBUG_TOOLS
     unsigned long long* debug_trace;  // profiling only: [workers][4096][2] or null
+#endif
+    // ---- MODE_GEMM split-K tail: units [0, tiles_full) are whole tiles; every later tile is cut into `ksplit`
+    // K ranges, each a unit that stores an fp32 partial tile into splitk_ws (summed by splitk_reduce_kernel)
+    int tiles_full;
+    int ksplit;
+    float* splitk_ws;         // [(tiles - tiles_full) * ksplit][kTileM * kBlockN]
+    // ---- MODE_GEMM fused all-reduce (warp 11): sums the bf16 buffer behind the multicast address `ar_mc` over the
+    // `ar_world` ranks in place (this rank reduces vectors [rank, rank+1) * ar_nvec / world and broadcasts them)
+    int ar_world, ar_rank;
+    unsigned int ar_epoch;    // call counter, identical on all ranks; flags carry it
+    void* ar_mc;              // multicast address of the symmetric buffer
+    long long ar_nvec;        // 16-byte vectors in the buffer
+    unsigned int* ar_flags;   // this rank's flags: [0, 8) ready[peer], [8, 16) done[peer], [16] local done counter
+    unsigned int* ar_peer_flags[8];  // peer-mapped addresses of every rank's flag array
     int hint_a, hint_b;  // L2 eviction priority of the A / B operand loads: 0 normal, 1 evict-first, 2 evict-last
     int worker_perm;  // 0/1: identity; S > 1: group physical neighbours on residues mod S (see kernel)
     float* accum;  // OUT_F32_ACC: same as out; OUT_BF16_FROM_ACC: fp32 partial to add
@@ -318,6 +337,15 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
     }
 }
 
+// split-K unit: 32 fp32 columns of this thread's row of the unit's partial tile (row-major [kTileM][kBlockN] scratch)
+__device__ __forceinline__ void store_partial_chunk(float* dst, const uint32_t (&r)[32]) {
+    float4* o4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+    for (int q4 = 0; q4 < 8; ++q4)
+        o4[q4] = make_float4(__uint_as_float(r[q4 * 4 + 0]), __uint_as_float(r[q4 * 4 + 1]),
+                             __uint_as_float(r[q4 * 4 + 2]), __uint_as_float(r[q4 * 4 + 3]));
+}
+
 // Fused all-reduce epilogue chunk: this warp's 32 rows x 32 columns of (acc [+ local fp32 partial]) are added into the
 // multicast fp32 buffer.  Lane = row in registers; the staging transpose makes 8 lanes cover 128 contiguous bytes of
 // one row, so each multimem.red instruction issues four full 128-byte segments instead of 32 scattered 16-byte ones.
@@ -364,9 +392,13 @@ __device__ __forceinline__ void mcred_chunk(const TcParams& p, const uint32_t (&
 // 60-165 GB instead of 15 GB for the configs[1] forward).  Each leader-CTA producer publishes its tile counter and
 // waits (bounded) until the slowest worker is at most `slack` checkpoints (of kPaceKBlocks k-blocks) behind.  This only shapes timing: a timeout
 // (non-resident workers, concurrent launches sharing the counters) disables it for the rest of the launch.
-constexpr int kMaxWorkers = 96;
+constexpr int kMaxWorkers = 160;   // >= SM count: one worker per CTA (cta_group 1) or per CTA pair
+constexpr int kPaceSlots = 128;    // launches in flight (all streams) that can pace independently
 constexpr uint32_t kPaceKBlocks = 32;  // checkpoint period in 64-wide k-blocks (~16k clocks of MMA work)
-__device__ unsigned int g_progress[kMaxWorkers];
+// One row of counters per launch (row = launch counter % kPaceSlots), so launches that overlap in time — other streams,
+// other chunks queued behind each other — never read each other's progress.  A value from another epoch means "that
+// worker has not started in THIS launch" and is ignored (a CTA that is not resident yet holds nobody back).
+__device__ unsigned int g_progress[kPaceSlots][kMaxWorkers];
 
 __device__ __forceinline__ void st_relaxed_u32(unsigned int* p, unsigned int v) {
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -382,17 +414,17 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     return t;
 }
 // whole warp; returns false when pacing should be abandoned
-__device__ __forceinline__ bool pace_wait(int worker, int num_workers, uint32_t epoch, uint32_t tile_iter, int slack,
-                                          int lane) {
-    if (lane == 0) st_relaxed_u32(&g_progress[worker], epoch | (tile_iter & 0xFFFFFu));
+__device__ __forceinline__ bool pace_wait(unsigned int* progress, int worker, int num_workers, uint32_t epoch,
+                                          uint32_t tile_iter, int slack, int lane) {
+    if (lane == 0) st_relaxed_u32(&progress[worker], epoch | (tile_iter & 0xFFFFFu));
     if (tile_iter < static_cast<uint32_t>(slack)) return true;
     const uint32_t need = tile_iter - static_cast<uint32_t>(slack);
     unsigned long long t0 = 0;
     for (int spin = 0;; ++spin) {
         uint32_t mn = 0xFFFFFu;
         for (int i = lane; i < num_workers; i += 32) {
-            const uint32_t v = ld_relaxed_u32(&g_progress[i]);
-            const uint32_t it = ((v ^ epoch) >> 20) ? 0u : (v & 0xFFFFFu);  // other epoch: not started yet
+            const uint32_t v = ld_relaxed_u32(&progress[i]);
+            const uint32_t it = ((v ^ epoch) >> 20) ? 0xFFFFFu : (v & 0xFFFFFu);  // other epoch: not started, ignore
             mn = min(mn, it);
         }
 #pragma unroll
@@ -404,6 +436,115 @@ __device__ __forceinline__ bool pace_wait(int worker, int num_workers, uint32_t 
     }
 }
 
+// ------------------------------------------------------------------------------------------------ units
+// A unit is what one worker (CTA or CTA pair) computes between two scheduling decisions:
+//   lm-head modes: (m tile, contiguous range [nb, ne) of n tiles), per-row soft-max state carried across the range;
+//   MODE_GEMM    : one output tile over the k-blocks [kb0, kb1) — the whole K for the first `tiles_full` tiles; the
+//                  tiles of the last, partial scheduling round are cut into `ksplit` K ranges so that the round costs
+//                  1/ksplit of a tile time instead of a whole one (fp32 partials, summed by splitk_reduce_kernel).
+struct Unit {
+    int m_tile, sp, nb, ne;
+    int kb0, kb1;
+    int part;  // >= 0: index of this unit's fp32 partial tile in splitk_ws
+};
+
+template <int kMode>
+__device__ __forceinline__ Unit decode_unit(const TcParams& p, int u) {
+    Unit w;
+    w.part = -1;
+    w.kb0 = 0;
+    w.kb1 = p.num_k_blocks;
+    int t = u;
+    if (kMode == MODE_GEMM && u >= p.tiles_full) {
+        const int v = u - p.tiles_full;
+        const int tt = v / p.ksplit;
+        const int part = v - tt * p.ksplit;
+        t = p.tiles_full + tt;
+        const int base = p.num_k_blocks / p.ksplit, rem = p.num_k_blocks - base * p.ksplit;
+        w.kb0 = part * base + min(part, rem);
+        w.kb1 = w.kb0 + base + (part < rem ? 1 : 0);
+        w.part = v;
+    }
+    w.m_tile = t / p.num_splits;
+    w.sp = t - w.m_tile * p.num_splits;
+    w.nb = w.sp * p.tiles_per_split;
+    w.ne = min(w.nb + p.tiles_per_split, p.num_n_tiles);
+    return w;
+}
+
+// ------------------------------------------------------------------------------------------------ fused all-reduce
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_addr) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc_addr)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc_addr, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+// Two-shot NVLS all-reduce of a bf16 buffer that every rank holds at the same offset of a symmetric (multicast-bound)
+// allocation, executed by ONE otherwise idle warp of every CTA of the d_weight GEMM: rank r pulls the switch-reduced sum
+// of its 1/world slice (multimem.ld_reduce: the NVSwitch reads the slice from all ranks and adds in fp32) and broadcasts
+// it (multimem.st) into every rank's buffer.  Link traffic per GPU = |buffer| out + |buffer| in, no SM beyond this
+// warp, and the GEMM's own warps never wait for it.
+//   ready[peer] : set by `peer` when its partial sums are complete (it entered this kernel: the d_hidden GEMM precedes
+//                 it on the stream) — nobody reads a peer's partials earlier;
+//   done[peer]  : set by `peer` when all its broadcasts have been issued and fenced — the kernel does not exit before
+//                 all peers are done, so kernel completion means the local buffer holds the complete sum (and no peer
+//                 still reads this rank's partials).
+// Flags carry the call's epoch (same on all ranks, collective call order), so they never need resetting.
+__device__ __forceinline__ void allreduce_worker(const TcParams& p, int cta, int num_ctas, int lane) {
+    const int world = p.ar_world;
+    const unsigned int epoch = p.ar_epoch;
+    if (cta == 0 && lane < world) st_release_sys_u32(p.ar_peer_flags[lane] + p.ar_rank, epoch);
+    if (lane < world) {
+        while (ld_acquire_sys_u32(p.ar_flags + lane) != epoch) __nanosleep(100);
+    }
+    __syncwarp();
+    const long long per = (p.ar_nvec + world - 1) / world;
+    const long long v0 = per * p.ar_rank;
+    const long long v1 = min(p.ar_nvec, v0 + per);
+    uint4* base = reinterpret_cast<uint4*>(p.ar_mc);
+    constexpr int kInFlight = 8;
+    const long long stride = static_cast<long long>(num_ctas) * 32 * kInFlight;
+    for (long long i = v0 + static_cast<long long>(cta) * 32 * kInFlight + lane; i < v1; i += stride) {
+        uint4 v[kInFlight];
+#pragma unroll
+        for (int j = 0; j < kInFlight; ++j)
+            if (i + j * 32 < v1) v[j] = multimem_ld_reduce_bf16x8(base + i + j * 32);
+#pragma unroll
+        for (int j = 0; j < kInFlight; ++j)
+            if (i + j * 32 < v1) multimem_st_bf16x8(base + i + j * 32, v[j]);
+    }
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    __syncwarp();
+    unsigned int last = 0;
+    if (lane == 0) last = (atomicAdd(p.ar_flags + 16, 1u) == static_cast<unsigned int>(num_ctas - 1)) ? 1u : 0u;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (last) {  // every warp of this rank has fenced its broadcasts
+        if (lane == 0) p.ar_flags[16] = 0;
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        if (lane < world) st_release_sys_u32(p.ar_peer_flags[lane] + 8 + p.ar_rank, epoch);
+    }
+    if (cta == 0 && lane < world) {
+        while (ld_acquire_sys_u32(p.ar_flags + 8 + lane) != epoch) __nanosleep(200);
+    }
+    __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------------ kernel
 // kAMn / kBMn: operand is MN-major in global memory (stored [K][MN]); otherwise K-major (stored [MN][K]).
 //   K-major operand : one TMA box {64 (k), rows}            -> rows x 128 B, SBO = 1024 B, K step = +32 B
@@ -411,10 +552,12 @@ __device__ __forceinline__ bool pace_wait(int worker, int num_workers, uint32_t 
 //                     LBO = 8192 B (next 64 mn), SBO = 1024 B (next 8 k), K step (16 rows) = +2048 B
 // kTf32: the operands are fp32, staged with the same 128-byte k-blocks (32 elements instead of 64) and multiplied as
 // TF32 (kind::tf32, 4 x K=8 per k-block instead of 4 x K=16) — K-major operands only (MODE_FWD / MODE_DS).
+constexpr int kArWarp = 11;
+
 template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const TcParams p) {
+               const __grid_constant__ TcParams p) {
     using Cfg = TileCfg<kCG>;
     static_assert(!kTf32 || (!kAMn && !kBMn), "TF32 operands are K-major only");
     constexpr int kElemsK = kTf32 ? kBlockK / 2 : kBlockK;  // elements per 128-byte k-block row
@@ -468,28 +611,29 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *L.tmem_ptr;
 
-    const int num_units = p.num_m_tiles * p.num_splits;
+    const int num_units = (kMode == MODE_GEMM)
+                              ? p.tiles_full + (p.num_m_tiles * p.num_splits - p.tiles_full) * p.ksplit
+                              : p.num_m_tiles * p.num_splits;
 
     if (warp == kTmaWarp) {
         // ===================================================================== TMA producer (every CTA)
         const uint64_t hint_a = l2_hint(p.hint_a), hint_b = l2_hint(p.hint_b);
         int stage = 0;
         uint32_t phase = 0;
-        // Soft lock-step (see g_progress): keep every worker within `sync_slack` tiles of the slowest one.
-        bool pace = (p.sync_slack > 0) && is_leader && num_workers <= kMaxWorkers;
+        // Soft lock-step (see g_progress): keep every worker within `sync_slack` checkpoints of the slowest one.
+        unsigned int* progress = g_progress[p.pace_slot];
+        const bool pace_on = (p.sync_slack > 0) && is_leader && num_workers <= kMaxWorkers;
+        bool pace = pace_on;
         uint32_t kb_total = 0;  // k-blocks issued so far; pacing checkpoints every kPaceKBlocks of them
         const uint32_t epoch = p.sync_epoch << 20;
         for (int u = worker; u < num_units; u += num_workers) {
-            const int m_tile = u / p.num_splits;
-            const int sp = u - m_tile * p.num_splits;
-            const int nb = sp * p.tiles_per_split;
-            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
-            const int m0 = m_tile * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
-            for (int n = nb; n < ne; ++n) {
+            const Unit w = decode_unit<kMode>(p, u);
+            const int m0 = w.m_tile * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
+            for (int n = w.nb; n < w.ne; ++n) {
                 const int n0 = n * kBlockN + static_cast<int>(cta_rank) * Cfg::kBRows;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++kb_total) {
+                for (int kb = w.kb0; kb < w.kb1; ++kb, ++kb_total) {
                     if (pace && (kb_total % kPaceKBlocks) == 0)
-                        pace = pace_wait(worker, num_workers, epoch, kb_total / kPaceKBlocks, p.sync_slack, lane);
+                        pace = pace_wait(progress, worker, num_workers, epoch, kb_total / kPaceKBlocks, p.sync_slack, lane);
                     mbar_wait(&L.empty[stage], phase ^ 1);
                     if (elect_one()) {
                         uint8_t* sa = L.stages + stage * kStageBytes;
@@ -537,8 +681,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         }
-        if ((p.sync_slack > 0) && is_leader && num_workers <= kMaxWorkers && lane == 0)
-            st_relaxed_u32(&g_progress[worker], epoch | 0xFFFFFu);  // done: never hold anybody back
+        if (pace_on && lane == 0) st_relaxed_u32(&progress[worker], epoch | 0xFFFFFu);  // done: never hold anybody back
     } else if (warp == kMmaWarp && is_leader) {
         // ===================================================================== MMA issuer (leader CTA)
         // kind::f16 takes bf16 (format 1) or fp16 (format 0) operands: clear the A / B format bits for fp16 launches
@@ -551,11 +694,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint32_t phase = 0;
         uint32_t acc_iter = 0;
         for (int u = worker; u < num_units; u += num_workers) {
-            const int m_tile = u / p.num_splits;
-            const int sp = u - m_tile * p.num_splits;
-            const int nb = sp * p.tiles_per_split;
-            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
-            for (int n = nb; n < ne; ++n, ++acc_iter) {
+            const Unit w = decode_unit<kMode>(p, u);
+            for (int n = w.nb; n < w.ne; ++n, ++acc_iter) {
+#ifdef VPG_DEBUG_TOOLS
                 if (p.debug_trace && lane == 0 && acc_iter < 4096u) {  // profiling: (globaltimer, n tile) per tile start
                     unsigned long long t;
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -563,12 +704,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     p.debug_trace[(static_cast<long long>(worker) * 4096 + acc_iter) * 2 + 1] =
                         (static_cast<unsigned long long>(u) << 32) | static_cast<unsigned>(n);
                 }
+#endif
                 const uint32_t buf = acc_iter & 1u;
                 const uint32_t acc_phase = (acc_iter >> 1) & 1u;
                 mbar_wait(&L.tmem_empty[buf], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * kBlockN;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                for (int kb = w.kb0; kb < w.kb1; ++kb) {
                     mbar_wait(&L.full[stage], phase);
                     tc_fence_after();
                     if (elect_one()) {
@@ -576,19 +718,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         const uint32_t sb = sa + kABytes;
                         const uint64_t adesc = kAMn ? make_smem_desc(sa, 8192, 1024) : make_smem_desc(sa, 16, 1024);
                         const uint64_t bdesc = kBMn ? make_smem_desc(sb, 8192, 1024) : make_smem_desc(sb, 16, 1024);
+                        const int first = (kb == w.kb0) ? 0 : 1;
 #pragma unroll
                         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                             // advance the 14-bit start-address field (units of 16 B)
                             const uint64_t a_adv = kAMn ? (k * 2048) >> 4 : (k * 32) >> 4;
                             const uint64_t b_adv = kBMn ? (k * 2048) >> 4 : (k * 32) >> 4;
                             if constexpr (kTf32)
-                                umma_tf32<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                                umma_tf32<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (first | k) != 0 ? 1u : 0u);
                             else
-                                umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                                umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (first | k) != 0 ? 1u : 0u);
                         }
                         // frees the smem slot (in both CTAs) once these MMAs retire
                         if (kCG == 1) umma_commit(&L.empty[stage]); else umma_commit_2sm(&L.empty[stage], 3);
-                        if (kb == p.num_k_blocks - 1) {
+                        if (kb == w.kb1 - 1) {
                             if (kCG == 1) umma_commit(&L.tmem_full[buf]); else umma_commit_2sm(&L.tmem_full[buf], 3);
                         }
                     }
@@ -611,11 +754,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint32_t acc_iter = 0;
         uint32_t unit_iter = 0;
         for (int u = worker; u < num_units; u += num_workers, ++unit_iter) {
-            const int m_tile = u / p.num_splits;
-            const int sp = u - m_tile * p.num_splits;
-            const int nb = sp * p.tiles_per_split;
-            const int ne = min(nb + p.tiles_per_split, p.num_n_tiles);
-            const long long row = static_cast<long long>(m_tile) * Cfg::kTileM + cta_rank * kBlockM + row_in_tile;
+            const Unit w = decode_unit<kMode>(p, u);
+            const int sp = w.sp;
+            const long long row = static_cast<long long>(w.m_tile) * Cfg::kTileM + cta_rank * kBlockM + row_in_tile;
             const bool row_ok = row < p.M;
 
             FwdState st;
@@ -644,8 +785,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     rw.glp = glp * p.inv_temp;
                 }
             }
+            // split-K unit: this thread's row of the unit's fp32 partial tile
+            float* part_row = nullptr;
+            if (kMode == MODE_GEMM && w.part >= 0)
+                part_row = p.splitk_ws + static_cast<long long>(w.part) * (Cfg::kTileM * kBlockN) +
+                           (static_cast<int>(cta_rank) * kBlockM + row_in_tile) * kBlockN + half * 128;
 
-            for (int n = nb; n < ne; ++n, ++acc_iter) {
+            for (int n = w.nb; n < w.ne; ++n, ++acc_iter) {
                 const uint32_t buf = acc_iter & 1u;
                 const uint32_t acc_phase = (acc_iter >> 1) & 1u;
                 mbar_wait(&L.tmem_full[buf], acc_phase);
@@ -653,7 +799,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int col0 = n * kBlockN + half * 128;
                 const uint32_t taddr = tmem_base + t_lane + buf * kBlockN + half * 128;
                 uint32_t ra[32], rb[32];
+#ifdef VPG_DEBUG_TOOLS
                 const bool skip_epilogue = (kMode == MODE_GEMM) && p.out_mode == OUT_DEBUG_SKIP;  // profiling only
+#else
+                constexpr bool skip_epilogue = false;
+#endif
                 if (!skip_epilogue) tmem_ld_32x32(taddr, ra);
 #pragma unroll
                 for (int cc = 0; cc < 4 && !skip_epilogue; cc += 2) {
@@ -667,6 +817,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
+                        } else if (part_row) {
+                            store_partial_chunk(part_row + cc * 32, ra);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, ra, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
@@ -683,6 +835,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
+                        } else if (part_row) {
+                            store_partial_chunk(part_row + (cc + 1) * 32, rb);
                         } else if (p.out_mode == OUT_F32_MCRED) {
                             if (n_valid >= 32) mcred_chunk(p, rb, row, row_ok, cb, L.red_scratch + ew * kRedRows * kRedLd, lane);
                         } else {
@@ -742,6 +896,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         }
+    } else if (kMode == MODE_GEMM && warp == kArWarp) {
+        // ===================================================================== fused NVLS all-reduce (every CTA)
+        if (p.ar_world > 1) allreduce_worker(p, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x), lane);
     }
 
     tc_fence_before();
@@ -749,6 +906,52 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (warp == kAllocWarp) {
         tc_fence_after();
         tmem_dealloc<kCG>(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ split-K reduce
+// Sums the `ksplit` fp32 partial tiles of every tail tile in a fixed order (deterministic) and applies the launch's
+// output mode.  One thread per 4 consecutive columns.  HBM-bound: ksplit * 256 KB read per tile, a few tiles per launch.
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int tail_tiles, int ksplit, int tile0,
+                                     int num_n_tiles, int tile_m, int M, int N, void* out, long long ldc, int out_mode,
+                                     const float* accum, long long ld_accum, int f16) {
+    const int per_tile = tile_m * kBlockN / 4;
+    const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (gid >= static_cast<long long>(tail_tiles) * per_tile) return;
+    const int tt = static_cast<int>(gid / per_tile);
+    const int e = static_cast<int>(gid - static_cast<long long>(tt) * per_tile);
+    const int r = e / (kBlockN / 4), c4 = (e - r * (kBlockN / 4)) * 4;
+    const int t = tile0 + tt;
+    const int m_tile = t / num_n_tiles, n_tile = t - m_tile * num_n_tiles;
+    const long long row = static_cast<long long>(m_tile) * tile_m + r;
+    const int col = n_tile * kBlockN + c4;
+    if (row >= M || col >= N) return;
+    const float* src = ws + (static_cast<long long>(tt) * ksplit) * (tile_m * kBlockN) + r * kBlockN + c4;
+    float4 a = *reinterpret_cast<const float4*>(src);
+    for (int k = 1; k < ksplit; ++k) {
+        const float4 b = *reinterpret_cast<const float4*>(src + static_cast<long long>(k) * (tile_m * kBlockN));
+        a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+    }
+    float v[4] = {a.x, a.y, a.z, a.w};
+    const int nv = min(4, N - col);
+    if (out_mode == OUT_F32_ACC || out_mode == OUT_BF16_FROM_ACC) {
+        const float* acc = (out_mode == OUT_F32_ACC ? reinterpret_cast<const float*>(out) + row * ldc
+                                                    : accum + row * ld_accum) + col;
+        for (int j = 0; j < nv; ++j) v[j] += acc[j];
+    }
+    if (out_mode == OUT_BF16 || out_mode == OUT_BF16_FROM_ACC) {
+        unsigned short* o = reinterpret_cast<unsigned short*>(out) + row * ldc + col;
+        if (nv == 4 && ((reinterpret_cast<uintptr_t>(o) & 7) == 0)) {
+            uint2 pk;
+            pk.x = pack_16x2(v[0], v[1], f16);
+            pk.y = pack_16x2(v[2], v[3], f16);
+            *reinterpret_cast<uint2*>(o) = pk;
+        } else {
+            for (int j = 0; j < nv; ++j) o[j] = cvt_16(v[j], f16);
+        }
+    } else {
+        float* o = reinterpret_cast<float*>(out) + row * ldc + col;
+        for (int j = 0; j < nv; ++j) o[j] = v[j];
     }
 }
 

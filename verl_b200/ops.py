@@ -63,18 +63,20 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
 
 
 def backward_chunk(T: int, H: int, V: int, device, chunk_v: int = 0) -> int:
-    """Vocab columns of dlogits materialised at a time by the backward.  An explicit ``chunk_v`` or $VPG_BWD_WS_MB wins;
-    otherwise the budget follows the memory that is free right now — a quarter of it, between 1 and 24 GiB — because
-    fewer chunks are faster (configs[1]: one 20 GB chunk 206 ms / step, seven 2.85 GB chunks 211.5 ms)."""
-    import os
-
+    """Vocab columns of dlogits materialised at a time by the backward.  An explicit ``chunk_v`` wins; otherwise the
+    library default: the widest chunk whose 16-bit ``[T, chunk]`` buffer fits $VPG_BWD_WS_MB (default 4096 MiB — the
+    same order as the reference's default 9 504-column split, kernels.py:1492-1501, at 64k tokens), never more than the
+    free memory allows.  The whole-vocabulary single chunk (20 GB at BASELINE configs[1]) is opt-in through
+    ``kernels.set_backward_chunk`` or the environment variable."""
     if chunk_v and chunk_v > 0:
         return int(chunk_v)
-    if os.environ.get("VPG_BWD_WS_MB"):
-        return 0  # the library default reads the variable
+    lib = _lib_()
+    chunk = int(lib.vpg_lce_bwd_default_chunk(T, H, V))
     free, _total = torch.cuda.mem_get_info(device)
-    budget = min(max(free // 4, 1 << 30), 24 << 30)
-    return int(_lib_().vpg_lce_bwd_chunk_for_budget(T, H, V, int(budget)))
+    # under memory pressure: the largest chunk that leaves half of what is free right now to the caller
+    while chunk > 256 and int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, chunk)) > free // 2:
+        chunk = max(256, (chunk // 2) // 256 * 256)
+    return chunk
 
 
 def operand_dtype(hidden, weight) -> int:
@@ -119,6 +121,21 @@ def lce_forward_partials_push(hidden, weight, labels, temperature: float, label_
     return gathered
 
 
+def _bwd_workspace(T, H, V, device, chunk_v):
+    lib = _lib_()
+    chunk_v = backward_chunk(T, H, V, device, chunk_v)
+    nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
+    return chunk_v, nbytes, torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+
+
+def lce_backward_workspace_info(T: int, H: int, V: int, device, chunk_v: int = 0) -> dict:
+    """{chunk_v, chunks, workspace_bytes} the backward would use right now (bench.py reports it)."""
+    chunk_v = backward_chunk(T, H, V, device, chunk_v)
+    v_pad = (V + 255) // 256 * 256
+    return {"chunk_v": int(min(chunk_v, v_pad)), "chunks": int(-(-v_pad // min(chunk_v, v_pad))),
+            "workspace_bytes": int(_lib_().vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))}
+
+
 def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int,
                        accum_local, accum_multicast_ptr: int, chunk_v: int = 0):
     """Backward whose d_hidden GEMM reduces into the multicast fp32 [T,H] buffer of every rank (vpg_lce_bwd_mcred).
@@ -128,9 +145,7 @@ def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature
     V = weight.shape[0]
     assert accum_local.shape == (T, H) and accum_local.dtype == _F32 and accum_multicast_ptr
     lib = _lib_()
-    chunk_v = backward_chunk(T, H, V, hidden.device, chunk_v)
-    nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
-    ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
+    chunk_v, nbytes, ws = _bwd_workspace(T, H, V, hidden.device, chunk_v)
     d_weight = torch.empty_like(weight)
     with torch.cuda.device(hidden.device):
         check(lib.vpg_lce_bwd_mcred(ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb), ptr(g_lp), ptr(g_ent),
@@ -160,40 +175,56 @@ def lce_finalize(partials, temperature: float):
 
 
 def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int = 0,
-                 chunk_v: int = 0, d_hidden_ready_event: int = 0, reserve_cta_pairs: int = 0):
-    """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (bf16 or fp16).
+                 chunk_v: int = 0, d_hidden_ready_event: int = 0, reserve_cta_pairs: int = 0, allreduce=None):
+    """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (fp32 gradients for fp32 operands).  One call of
+    vpg_lce_bwd_ex: every option is an explicit field of its argument struct.
 
     d_hidden_ready_event (raw cudaEvent_t, 0 = none): recorded as soon as d_hidden is complete; the d_weight GEMM then
-    runs last and spares SMs (at least reserve_cta_pairs CTA pairs) for the caller's all-reduce
-    (vpg_lce_bwd_overlap_next)."""
+    runs last and spares SMs (at least reserve_cta_pairs CTA pairs) for the caller's all-reduce.
+    allreduce: dict(out=[T,H] bf16 view of a symmetric buffer, mc=its multicast address, flags=uint32 tensor,
+    peer_flags=[addresses], world, rank, epoch) — d_hidden is written into ``out`` and summed over the ranks by the
+    d_weight GEMM kernel itself (in-kernel NVLS all-reduce); ``out`` is returned as d_hidden."""
+    import ctypes
+
     _require_cuda(hidden, weight, labels, lse, eb)
     T, H = hidden.shape
     V = weight.shape[0]
     lib = _lib_()
-    chunk_v = backward_chunk(T, H, V, hidden.device, chunk_v)
-    nbytes = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))
-    ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
-    d_hidden = torch.empty_like(hidden)
-    d_weight = torch.empty_like(weight)
+    chunk_v, nbytes, ws = _bwd_workspace(T, H, V, hidden.device, chunk_v)
     dt = operand_dtype(hidden, weight)
+    d_hidden = allreduce["out"] if allreduce else torch.empty_like(hidden)
+    d_weight = torch.empty_like(weight)
+    a = _lib.LceBwdArgs()
+    a.struct_size = ctypes.sizeof(_lib.LceBwdArgs)
+    a.dtype = dt
+    keep = []
     if dt == 2:  # fp32: TF32 recompute on the fp32 operands, gradient GEMMs on bf16 copies, fp32 gradients
         h16, w16 = hidden.to(torch.bfloat16), weight.to(torch.bfloat16)
-        with torch.cuda.device(hidden.device):
-            check(lib.vpg_lce_bwd_f32(ptr(hidden), ptr(weight), ptr(h16), ptr(w16), ptr(labels), ptr(lse), ptr(eb),
-                                      ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset),
-                                      int(chunk_v), ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes,
-                                      stream_ptr(hidden.device)))
-        return d_hidden, d_weight
+        keep += [h16, w16]
+        a.hidden16, a.weight16 = ptr(h16), ptr(w16)
+    a.hidden, a.weight, a.labels, a.lse, a.eb = ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb)
+    a.g_lp, a.g_ent = ptr(g_lp), ptr(g_ent)
+    a.T, a.H, a.V = T, H, V
+    a.temperature, a.label_offset, a.chunk_v = float(temperature), int(label_offset), int(chunk_v)
+    a.d_hidden, a.d_weight = ptr(d_hidden), ptr(d_weight)
+    a.workspace, a.workspace_bytes = ptr(ws), nbytes
+    a.stream = stream_ptr(hidden.device)
+    if d_hidden_ready_event and dt != 2:
+        a.d_hidden_ready_event, a.reserve_cta_pairs = int(d_hidden_ready_event), int(reserve_cta_pairs)
+    if allreduce:
+        assert dt == 0 and d_hidden.shape == (T, H) and d_hidden.dtype == torch.bfloat16 and d_hidden.is_contiguous()
+        peers = [int(x) for x in allreduce["peer_flags"]]
+        arr = (ctypes.c_void_p * len(peers))(*peers)
+        keep.append(arr)
+        a.ar_world, a.ar_rank, a.ar_epoch = int(allreduce["world"]), int(allreduce["rank"]), int(allreduce["epoch"])
+        a.ar_d_hidden_mc, a.ar_flags = int(allreduce["mc"]), ptr(allreduce["flags"])
+        a.ar_peer_flags = ctypes.cast(arr, ctypes.POINTER(ctypes.c_void_p))
     with torch.cuda.device(hidden.device):
-        if d_hidden_ready_event:
-            check(lib.vpg_lce_bwd_overlap_next(int(d_hidden_ready_event), int(reserve_cta_pairs)))
-        check(lib.vpg_lce_bwd_dt(dt, ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb),
-                                 ptr(g_lp), ptr(g_ent), T, H, V, float(temperature), int(label_offset), int(chunk_v),
-                                 ptr(d_hidden), ptr(d_weight), ptr(ws), nbytes, stream_ptr(hidden.device)))
+        check(lib.vpg_lce_bwd_ex(ctypes.byref(a)))
     return d_hidden, d_weight
 
 
-def gemm_bf16(A, B, a_kmajor=True, b_kmajor=True, out_dtype=torch.bfloat16):
+def gemm_bf16(A, B, a_kmajor=True, b_kmajor=True, out_dtype=torch.bfloat16, split_k: bool = False):
     """C = op(A) @ op(B)^T on the tcgen05 mainloop.  A: [M,K] (k-major) or [K,M]; B: [N,K] (k-major) or [K,N]."""
     _require_cuda(A, B)
     M, K = (A.shape if a_kmajor else A.shape[::-1])
@@ -201,8 +232,15 @@ def gemm_bf16(A, B, a_kmajor=True, b_kmajor=True, out_dtype=torch.bfloat16):
     assert K == K2
     C = torch.empty((M, N), dtype=out_dtype, device=A.device)
     mode = 0 if out_dtype == torch.bfloat16 else 1
+    lib = _lib_()
     with torch.cuda.device(A.device):
-        check(_lib_().vpg_gemm_bf16(ptr(A), ptr(B), M, N, K, A.stride(0), B.stride(0), int(a_kmajor), int(b_kmajor),
+        if split_k:
+            nbytes = int(lib.vpg_gemm_splitk_workspace_bytes())
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=A.device)
+            check(lib.vpg_gemm_bf16_ws(ptr(A), ptr(B), M, N, K, A.stride(0), B.stride(0), int(a_kmajor), int(b_kmajor),
+                                       ptr(C), C.stride(0), mode, None, 0, ptr(ws), nbytes, stream_ptr(A.device)))
+        else:
+            check(lib.vpg_gemm_bf16(ptr(A), ptr(B), M, N, K, A.stride(0), B.stride(0), int(a_kmajor), int(b_kmajor),
                                     ptr(C), C.stride(0), mode, None, 0, stream_ptr(A.device)))
     return C
 

@@ -72,9 +72,10 @@ class Config:
     _tp_exchange: str = os.environ.get("VPG_TP_EXCHANGE", "nccl")
     # False = reference semantics (caller all-reduces d_hidden); True = the op returns the summed d_hidden
     _tp_reduce_d_hidden: bool = False
-    # how the op sums d_hidden when asked to: "nccl" (one all-reduce after the GEMMs) or "multimem" (fused into the
-    # d_hidden GEMM epilogue; every rank multicasts its fp32 tiles, so each GPU's NVLink ingress is world x |d_hidden|:
-    # measured on par with NCCL at 2 GPUs and ~3 ms slower at 8 GPUs for configs[1], hence opt-in)
+    # how the op sums d_hidden when asked to: "fused" (in-kernel NVLS all-reduce inside the d_weight GEMM), "nccl" (one
+    # all-reduce after the GEMMs), "overlap" (NCCL on a second stream under a d_weight GEMM that spares SMs) or
+    # "multimem" (multimem.red from the d_hidden GEMM epilogue; each GPU's NVLink ingress is world x |d_hidden|:
+    # ~3 ms slower than NCCL at 8 GPUs for configs[1], hence opt-in); "auto" = fused when NVSwitch multicast is there
     _tp_reduce_mode: str = os.environ.get("VPG_TP_REDUCE", "nccl")
 
 
@@ -107,9 +108,13 @@ def set_reduce_d_hidden(enabled: bool, mode: str = "nccl"):
     exchange and NVSwitch multicast): the d_hidden GEMM's epilogue reduces into every rank's fp32 buffer through the
     switch (multimem.red) while it runs.  mode "overlap": d_hidden is computed before the last d_weight GEMM, which
     spares the SMs it does not need for its number of scheduling rounds; the NCCL all-reduce runs on a second stream
-    under that GEMM.  mode "auto": "overlap" when `_overlap_plan` says the hidden all-reduce is worth the extra
-    scheduling rounds of the d_weight GEMM (8-way shards of the BASELINE shapes), else "nccl"."""
-    if mode not in ("nccl", "multimem", "overlap", "auto"):
+    under that GEMM.  mode "fused" (needs the "nvlink" exchange, NVSwitch multicast and bf16 operands): d_hidden is written
+    into a symmetric slot and all-reduced INSIDE the d_weight GEMM kernel by its idle warps (two-shot NVLS:
+    multimem.ld_reduce + multimem.st), no SM and no launch of its own; the returned d_hidden is a view of one of two
+    alternating symmetric slots (valid until the backward after next).  mode "auto": "fused" when available, else
+    "overlap" when `_overlap_plan` says the hidden all-reduce is worth the extra scheduling rounds of the d_weight GEMM,
+    else "nccl"."""
+    if mode not in ("nccl", "multimem", "overlap", "auto", "fused"):
         raise ValueError(f"Invalid d_hidden reduction mode: {mode}")
     _config._tp_reduce_d_hidden = bool(enabled)
     _config._tp_reduce_mode = mode
@@ -162,6 +167,19 @@ def _peer_workspace(group, device):
     from . import peer
 
     return peer.workspace(group, device)
+
+
+def init_vocab_parallel(group, device, max_tokens: int, hidden_size: int, vocab_local: int = 0):
+    """COLLECTIVE, explicit initialisation of the NVLink-fused vocab-parallel path: allocates (and rendezvouses) every
+    symmetric buffer for up to ``max_tokens`` tokens now, so that no forward / backward allocates later.  Without it
+    the buffers are created on first use (also collectively; a size disagreement between ranks raises)."""
+    S = ops.lce_num_splits(max_tokens, hidden_size, vocab_local) if vocab_local else 16
+    return _peer_workspace(group, device).reserve(int(max_tokens), int(hidden_size), max(int(S), 1))
+
+
+def _fused_allreduce_ok(hidden, world) -> bool:
+    return (world > 1 and _config._tp_reduce_d_hidden and _config._tp_reduce_mode in ("fused", "auto")
+            and _config._tp_exchange == "nvlink" and hidden.dtype == torch.bfloat16)
 
 
 def _check_inputs(hidden, weight, labels):
@@ -279,7 +297,20 @@ def efficient_entropy_backward(
         px = _peer_workspace(dist_process_group, hidden.device)
         accum, accum_mc = px.d_hidden_accum(hidden.shape[0], hidden.shape[1])
         fused_reduce = accum_mc != 0
-    if fused_reduce:
+    ar = None
+    if not fused_reduce and _fused_allreduce_ok(hidden, world):
+        px = _peer_workspace(dist_process_group, hidden.device)
+        if px.has_multicast:
+            ar = px.d_hidden_slot(hidden.shape[0], hidden.shape[1])
+        elif _config._tp_reduce_mode == "fused":
+            raise RuntimeError("set_reduce_d_hidden(mode='fused') needs NVSwitch multicast on this group")
+    if ar is not None:
+        # GEMM + all-reduce in ONE kernel: d_hidden lands in the symmetric slot, the d_weight GEMM's idle warps sum it
+        # over the ranks through the switch while the tensor cores run; kernel completion = reduction complete
+        d_hidden, d_weight = ops.lce_backward(
+            hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
+            label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v, allreduce=ar)
+    elif fused_reduce:
         # fused GEMM + all-reduce: zero every rank's fp32 buffer, barrier, the d_hidden GEMM's epilogue reduces into all
         # of them through the switch (multimem.red), barrier, convert this rank's copy
         accum.zero_()

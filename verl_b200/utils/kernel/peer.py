@@ -5,9 +5,11 @@ The fused lm-head kernels can do their collectives themselves instead of calling
 * forward  — the GEMM epilogue stores each token tile's partials {m, s, b, t} straight into the gathered
   ``[4, world*S, T]`` buffer of EVERY rank (``multimem.st`` on an NVSwitch multicast address, or plain stores to the
   peer-mapped buffers when multicast is unavailable): the all-gather happens tile by tile under the GEMM;
-* backward — the epilogue of the d_hidden GEMM issues ``multimem.red.add.f32`` on a multicast fp32 ``[T, H]`` buffer,
-  so the all-reduce of d_hidden (left to the caller by the reference, tests/utils/test_linear_cross_entropy_tp.py:
-  313-314) builds up in every rank's memory while the GEMM runs.
+* backward — d_hidden is written into a symmetric bf16 ``[T, H]`` slot and summed over the ranks INSIDE the d_weight GEMM
+  kernel: one otherwise idle warp per CTA runs a two-shot NVLS all-reduce (``multimem.ld_reduce`` of this rank's 1/world
+  slice, ``multimem.st`` of the sum into every rank's slot) while the tensor cores work, so the all-reduce the reference
+  leaves to its callers (tests/utils/test_linear_cross_entropy_tp.py:313-314) costs no SM and no extra launch.  (The
+  older variant — ``multimem.red.add.f32`` from the d_hidden GEMM's epilogue into an fp32 buffer — is kept, opt-in.)
 
 This module owns the buffers those kernels write: symmetric allocations made with torch's
 ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric handles exchanged through the group's store — plumbing,
@@ -47,14 +49,37 @@ class PeerWorkspace:
             pass
 
     # ------------------------------------------------------------------------------------------ allocation
-    def _buffer(self, name: str, numel: int):
+    def _buffer(self, name: str, numel: int, zero: bool = False):
         cur = self._bufs.get(name)
         if cur is not None and cur[2] >= numel:
             return cur
+        # (Re)allocation is COLLECTIVE.  Ranks that disagree on the size (different T) would deadlock in the rendezvous:
+        # agree on it first and raise on every rank instead.
+        if self.world > 1 and dist.is_initialized():
+            want = torch.tensor([numel, -numel], dtype=torch.int64, device=self.device)
+            dist.all_reduce(want, op=dist.ReduceOp.MAX, group=self.group)
+            lo, hi = -int(want[1]), int(want[0])
+            if lo != hi:
+                raise RuntimeError(f"symmetric buffer '{name}': ranks ask for different sizes ({lo} .. {hi} elements); the "
+                                   "vocab-parallel lm-head needs the same token count on every rank (hidden is replicated)")
         t = self._symm.empty(numel, dtype=torch.float32, device=self.device)
         hdl = self._symm.rendezvous(t, group=self.group.group_name)
+        if zero:
+            t.zero_()
+            torch.cuda.current_stream(self.device).synchronize()
+            hdl.barrier(channel=0)
         self._bufs[name] = (t, hdl, numel)
         return self._bufs[name]
+
+    def reserve(self, max_tokens: int, hidden_size: int, num_splits: int = 16):
+        """Explicit collective initialisation: allocate every symmetric buffer the lm-head needs for up to
+        ``max_tokens`` tokens NOW, so that no forward / backward call allocates (or rendezvouses) later."""
+        for parity in (0, 1):
+            self._buffer(f"partials{parity}", 4 * self.world * num_splits * max_tokens)
+            self._buffer(f"dh{parity}", (max_tokens * hidden_size + 1) // 2)
+        self._buffer("ar_flags", 64, zero=True)
+        self._buffer("probe", 1024)
+        return self
 
     @staticmethod
     def _mc_ptr(hdl) -> int:
@@ -82,6 +107,22 @@ class PeerWorkspace:
         t, hdl, _ = self._buffer(f"partials{self._parity}", numel)
         view = t[:numel].view(4, self.world * S, T)
         return view, self._mc_ptr(hdl), [int(p) for p in hdl.buffer_ptrs]
+
+    def d_hidden_slot(self, T: int, H: int) -> dict:
+        """Arguments of the in-kernel all-reduce (ops.lce_backward(allreduce=...)): a bf16 [T,H] view of one of two
+        alternating symmetric slots (the caller's d_hidden of step i stays intact while step i+1 runs), its multicast
+        address, the flag words and the call's epoch.  Same call order on all ranks (it is a collective's argument)."""
+        self._dh_parity = getattr(self, "_dh_parity", 0) ^ 1
+        self._ar_epoch = getattr(self, "_ar_epoch", 0) + 1
+        numel = (T * H + 1) // 2  # fp32 elements holding T*H bf16
+        t, hdl, _ = self._buffer(f"dh{self._dh_parity}", numel)
+        ft, fh, _ = self._buffer("ar_flags", 64, zero=True)
+        mc = self._mc_ptr(hdl)
+        if not mc:
+            raise RuntimeError("the in-kernel all-reduce needs NVSwitch multicast (no multicast address for the slot)")
+        return dict(out=t.view(torch.bfloat16)[:T * H].view(T, H), mc=mc, flags=ft.view(torch.int32),
+                    peer_flags=[int(p) for p in fh.buffer_ptrs], world=self.world, rank=self.rank,
+                    epoch=self._ar_epoch & 0x7FFFFFFF or 1)
 
     def d_hidden_accum(self, T: int, H: int):
         """-> (local fp32 view [T, H], multicast address | 0)"""
