@@ -329,6 +329,7 @@ def parity_probe(torch, dist, linear_cross_entropy, hidden, w_local, labels, gro
     ent_r = lse_r - eb_r
     (lp_r * g_lp[tok] + ent_r * g_ent[tok]).sum().backward()
     dh_r = hs.grad
+    lp_r, ent_r, lse_r = lp_r.detach(), ent_r.detach(), lse_r.detach()
     del z, p
     # per-token scalars of ALL tokens from the op's own outputs (checked on the sample)
     tgt = torch.empty(T, dtype=torch.float32, device=dev)
@@ -765,7 +766,8 @@ def run_ours(args, name, cfg):
             "energy": {"joules_per_step": joules, "joules_per_step_e2e": joules_e2e,
                        "tokens_per_joule": (T / joules) if joules else None,
                        "source": "NVML total-energy counter of GPU 0 around the timed region"},
-            "memory": {"bwd_workspace_bytes": ws["workspace_bytes"], "bwd_chunks": ws["chunks"], "bwd_chunk_v": ws["chunk_v"],
+            "memory": {"bwd_workspace_bytes": ws["workspace_bytes"], "bwd_chunks": ws["chunks"], "bwd_chunk": ws["chunk"],
+                       "bwd_chunking": ws["mode"],
                        "peak_allocated_bytes_in_timed_region": int(peak_mem),
                        "budget": f"{args.bwd_ws_mb} MiB (--bwd-ws-mb)" if args.bwd_ws_mb else
                                  "library default: $VPG_BWD_WS_MB or 4096 MiB of dlogits (the [T,V] logits are never stored)"},

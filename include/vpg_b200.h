@@ -184,7 +184,9 @@ typedef struct vpg_lce_bwd_args {
     int64_t T, H, V;
     float temperature;
     int64_t label_offset;
-    int64_t chunk_v;         /* 0 = vpg_lce_bwd_default_chunk */
+    int64_t chunk_v;         /* > 0: dlogits in column chunks of this width (multiple of 256) */
+    int64_t chunk_t;         /* > 0 (and chunk_v == 0): dlogits in row chunks of this height (multiple of 256);
+                                both 0: the library plans (vpg_lce_bwd_plan) */
     void* d_hidden;          /* [T,H] in `dtype` (fp32 for VPG_DT_F32) */
     void* d_weight;          /* [V,H] likewise */
     void* workspace;
@@ -200,6 +202,12 @@ typedef struct vpg_lce_bwd_args {
     uint32_t* const* ar_peer_flags;
 } vpg_lce_bwd_args;
 int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args);
+/* The chunking the backward will use for (chunk_v, chunk_t) as passed to vpg_lce_bwd_ex:
+ * out4 = {mode (0 one block, 1 column chunks with an fp32 [T,H] d_hidden accumulator — the reference's _Split_Dlogits_N,
+ * 2 row chunks with an fp32 [V,H] d_weight accumulator — its _Split_Dlogits_M), chunk width / height, number of chunks,
+ * workspace bytes}.  With both 0 the dlogits block is bounded by $VPG_BWD_WS_MB (default 4096 MiB) and the orientation
+ * with the smaller accumulator is taken (row chunks when T > V, e.g. a vocab shard of a long micro-batch). */
+int vpg_lce_bwd_plan(int64_t T, int64_t H, int64_t V, int64_t chunk_v, int64_t chunk_t, int64_t* out4);
 
 /* Forward stage 1 with every option explicit: operand dtype + the push arguments of vpg_lce_fwd_partials_push. */
 int vpg_lce_fwd_partials_ex(int dtype, const void* hidden, const void* weight, const int64_t* labels, int64_t T,

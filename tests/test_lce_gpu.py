@@ -317,6 +317,32 @@ def test_full_size_vocab_shard_shapes(name, Tn, H, V, world, dev):
     assert excess(dw[voc], dw_r, GRAD_ATOL, GRAD_RTOL) <= 0
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_backward_token_chunks_match_vocab_chunks(dtype, dev):
+    """The three ways of cutting the dlogits workspace — one block, column chunks (fp32 d_hidden accumulator; the
+    reference's _Split_Dlogits_N, kernels.py:1492-1548) and row chunks (fp32 d_weight accumulator; its _Split_Dlogits_M)
+    — give the same gradients, and the row-chunked result equals the fp32 reference.  Ragged T and V (neither a
+    multiple of the 256 tile), three chunks each way."""
+    from verl_b200 import ops
+
+    Tn, H, V, temp = 700, 256, 1900, 1.3
+    hidden, weight, labels, g_lp, g_ent = _inputs(Tn, H, V, 17, dev)
+    hidden, weight = hidden.to(dtype), weight.to(dtype)
+    lp_r, ent_r, dh_r, dw_r = _gpu_fp32_reference(hidden, weight, labels, temp, g_lp, g_ent)
+    part = ops.lce_forward_partials(hidden, weight, labels, temp)
+    _, _, lse, eb = ops.lce_finalize(part, temp)
+    one = ops.lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temp, chunk_v=2048)
+    cols = ops.lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temp, chunk_v=768)
+    rows = ops.lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temp, chunk_t=256)
+    assert ops.backward_plan(Tn, H, V, 0, 256)["mode"].startswith("token") and ops.backward_plan(Tn, H, V, 0, 256)["chunks"] == 3
+    for got in (one, cols, rows):
+        torch.testing.assert_close(got[0].float(), dh_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+        torch.testing.assert_close(got[1].float(), dw_r, atol=GRAD_ATOL, rtol=GRAD_RTOL)
+    # d_hidden rows are final per row chunk (no accumulation across chunks): equal to the one-block result up to the
+    # summation order of the split-K tail tiles
+    torch.testing.assert_close(rows[0].float(), one[0].float(), atol=4e-3, rtol=1e-2)
+
+
 def test_split_k_tail_gemm(dev):
     """Plain tcgen05 GEMM with the split-K tail: the tiles of the last partial round are cut along K into fp32 partial
     tiles and summed in a fixed order — results equal the unsplit GEMM to bf16 rounding, fp32 output to 1e-4 rel, for
@@ -324,7 +350,7 @@ def test_split_k_tail_gemm(dev):
     from verl_b200 import ops
 
     g = torch.Generator(device=dev).manual_seed(4)
-    for (M, N, K) in [(19008, 3584, 8192), (1000, 700, 4160), (256 * 80, 256, 2048)]:
+    for (M, N, K) in [(19008, 3584, 8192), (1000, 704, 4160), (256 * 80, 256, 2048)]:
         A = (torch.rand(M, K, device=dev, generator=g) - 0.5).bfloat16()
         B = (torch.rand(N, K, device=dev, generator=g) - 0.5).bfloat16()
         ref = A.float() @ B.float().t()

@@ -162,5 +162,3 @@ def test_ulysses_without_group_is_identity():
     assert U.ulysses_pad(ids, None, sp_size=1) == (ids, None, 0)
     with pytest.raises(AssertionError):
         U.validate_ulysses_config(28, 8)
-    with pytest.raises(RuntimeError):
-        U.gather_outpus_and_unpad(x)

@@ -171,6 +171,7 @@ SIGNATURES: dict[str, tuple] = {
         [c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_float, c_int64, c_int, c_void_p, c_int, c_int,
          c_int, c_void_p, c_int, c_void_p],
     ),
+    "vpg_lce_bwd_plan": (c_int, [c_int64, c_int64, c_int64, c_int64, c_int64, c_void_p]),
     "vpg_timing_enable": (c_int, [c_int]),
     "vpg_timing_collect": (c_int, [c_void_p, c_void_p, c_int]),
     "vpg_gemm_splitk_workspace_bytes": (c_size_t, []),
@@ -194,7 +195,7 @@ class LceBwdArgs(C.Structure):
         ("struct_size", c_size_t), ("dtype", c_int), ("hidden", c_void_p), ("weight", c_void_p),
         ("hidden16", c_void_p), ("weight16", c_void_p), ("labels", c_void_p), ("lse", c_void_p), ("eb", c_void_p),
         ("g_lp", c_void_p), ("g_ent", c_void_p), ("T", c_int64), ("H", c_int64), ("V", c_int64),
-        ("temperature", c_float), ("label_offset", c_int64), ("chunk_v", c_int64), ("d_hidden", c_void_p),
+        ("temperature", c_float), ("label_offset", c_int64), ("chunk_v", c_int64), ("chunk_t", c_int64), ("d_hidden", c_void_p),
         ("d_weight", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t), ("stream", c_void_p),
         ("d_hidden_mc_f32", c_void_p), ("d_hidden_ready_event", c_void_p), ("reserve_cta_pairs", c_int),
         ("ar_world", c_int), ("ar_rank", c_int), ("ar_epoch", C.c_uint32), ("ar_d_hidden_mc", c_void_p),

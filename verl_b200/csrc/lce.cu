@@ -55,6 +55,7 @@ struct Tuning {
     int reserve_pairs = -1;  // VPG_BWD_RESERVE_PAIRS: override of the caller's reserve_cta_pairs
     int bwd_ws_mb = 4096;    // VPG_BWD_WS_MB: default dlogits workspace budget (MiB)
     int splitk = 1;          // VPG_SPLITK=0 disables the split-K tail of the gradient GEMMs
+    int ds_tma = 1;          // VPG_DS_TMA=0: dlogits by per-lane global stores instead of smem + TMA tensor stores
     int hint_a[4] = {0, 0, 0, 0}, hint_b[4] = {0, 0, 0, 0};  // L2 eviction hints per kernel {FWD, DS, DH, DW}
 };
 static int env_int(const char* name, int dflt) {
@@ -73,6 +74,7 @@ static const Tuning& tuning() {
         t.reserve_pairs = env_int("VPG_BWD_RESERVE_PAIRS", -1);
         t.bwd_ws_mb = env_int("VPG_BWD_WS_MB", 4096);
         t.splitk = env_int("VPG_SPLITK", 1);
+        t.ds_tma = env_int("VPG_DS_TMA", 1);
         const char* tags[4] = {"FWD", "DS", "DH", "DW"};
         for (int i = 0; i < 4; ++i) {
             char name[32];
@@ -130,7 +132,7 @@ struct TimingScope {
 };
 
 static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_inner,
-                     int box_outer, int dt) {
+                     int box_outer, int dt, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
     const int esz = (dt == VPG_DT_F32) ? 4 : 2;
     EncodeTiledFn fn = get_encode_fn();
     bind_primary_context();
@@ -145,7 +147,7 @@ static int make_tmap(CUtensorMap* tm, const void* base, int64_t inner, int64_t o
                                    : dt == VPG_DT_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                       : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     CUresult r = fn(tm, ty, 2, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(VPG_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return VPG_OK;
@@ -193,7 +195,7 @@ static void plan_splitk(TcParams& p, int workers, float* scratch) {
 
 template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
 static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream,
-                        int timing_kind) {
+                        int timing_kind, const CUtensorMap* tc = nullptr) {
     auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG, kTf32>;
     const Tuning& tn = tuning();
     TcParams p = p_in;
@@ -202,11 +204,13 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     p.sync_epoch = id & 0x7FFu;
     p.pace_slot = static_cast<int>(id % kPaceSlots);
     p.ds_stcs = tn.ds_stcs;
+    p.ds_tma = (kMode == MODE_DS && tc && tn.ds_tma) ? 1 : 0;
     const int hk = kMode == MODE_FWD ? 0 : kMode == MODE_DS ? 1 : kAMn ? 3 : 2;
     p.hint_a = tn.hint_a[hk];
     p.hint_b = tn.hint_b[hk];
     if (kMode != MODE_GEMM) p.tiles_full = p.num_m_tiles * p.num_splits, p.ksplit = 1, p.splitk_ws = nullptr;
-    constexpr int smem = TileCfg<kCG>::kSmemBytes + (kMode == MODE_GEMM ? kRedScratchBytes : 0);
+    constexpr int smem = kMode == MODE_DS ? TileCfg<kCG>::kSmemBytesDs
+                                          : TileCfg<kCG>::kSmemBytes + (kMode == MODE_GEMM ? kRedScratchBytes : 0);
     // per-device attribute: set every call (cheap) so multi-device processes are handled
     cudaError_t attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (attr_err != cudaSuccess)
@@ -232,7 +236,7 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     cudaError_t e;
     {
         TimingScope ts(timing_kind, stream);
-        e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+        e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc ? *tc : ta, p);
     }
     count_launch();
     if (e != cudaSuccess) {
@@ -253,18 +257,19 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
 
 template <int kMode, bool kAMn, bool kBMn>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream,
-                     int timing_kind) {
-    if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream, timing_kind);
-    return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream, timing_kind);
+                     int timing_kind, const CUtensorMap* tc = nullptr) {
+    if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream, timing_kind, tc);
+    return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream, timing_kind, tc);
 }
 // lm-head statistics / dlogits launches in the operand type `dt` of the call: bf16 / fp16 (kind::f16) or fp32 (TF32)
 template <int kMode>
-static int launch_tc_lmhead(const CUtensorMap& ta, const CUtensorMap& tb, TcParams p, int dt, cudaStream_t stream) {
+static int launch_tc_lmhead(const CUtensorMap& ta, const CUtensorMap& tb, TcParams p, int dt, cudaStream_t stream,
+                            const CUtensorMap* tc = nullptr) {
     p.f16 = (dt == VPG_DT_F16);
     const int tk = kMode == MODE_FWD ? TK_FWD : TK_DS;
-    if (dt != VPG_DT_F32) return launch_tc<kMode, false, false>(ta, tb, p, stream, tk);
-    if (cta_group() == 2) return launch_tc_cg<kMode, false, false, 2, true>(ta, tb, p, stream, tk);
-    return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream, tk);
+    if (dt != VPG_DT_F32) return launch_tc<kMode, false, false>(ta, tb, p, stream, tk, tc);
+    if (cta_group() == 2) return launch_tc_cg<kMode, false, false, 2, true>(ta, tb, p, stream, tk, tc);
+    return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream, tk, tc);
 }
 
 // balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
@@ -515,17 +520,64 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
     return best_c * kBlockN;
 }
 
+// How the backward cuts its dlogits workspace.  SINGLE: the whole [T, V] block fits the budget.  VOCAB: column chunks
+// (the reference's default _Split_Dlogits_N, kernels.py:1492-1548): d_weight rows are final per chunk, d_hidden accumulates
+// in an fp32 [T, H] buffer.  TOKEN: row chunks (the reference's _Split_Dlogits_M): d_hidden rows are final per chunk,
+// d_weight accumulates in an fp32 [V, H] buffer.  Auto picks the orientation with the SMALLER accumulator: a vocab shard
+// of a long micro-batch (BASELINE configs[4]: T = 262144, V/8 = 19008) accumulates 0.39 GB instead of 5.4 GB per chunk.
+enum : int { BWD_SINGLE = 0, BWD_VOCAB = 1, BWD_TOKEN = 2 };
+struct BwdPlan {
+    int mode;
+    int64_t chunk;  // columns (VOCAB / SINGLE) or rows (TOKEN) of the dlogits block
+    int n_chunks;
+    size_t off_acc, off_splitk, bytes;
+};
+static BwdPlan plan_bwd(int64_t T, int64_t H, int64_t V, int64_t chunk_v, int64_t chunk_t) {
+    BwdPlan pl{};
+    const int64_t t_pad = round_up(T > 0 ? T : 1, 2 * kBlockM);
+    const int64_t v_pad = round_up(V, kBlockN);
+    const int64_t budget = static_cast<int64_t>(tuning().bwd_ws_mb) << 20;
+    if (chunk_v > 0) {
+        pl.mode = chunk_v >= v_pad ? BWD_SINGLE : BWD_VOCAB;
+        pl.chunk = chunk_v >= v_pad ? v_pad : chunk_v;
+    } else if (chunk_t > 0) {
+        pl.mode = chunk_t >= t_pad ? BWD_SINGLE : BWD_TOKEN;
+        pl.chunk = chunk_t >= t_pad ? v_pad : chunk_t;
+    } else if (t_pad * v_pad * 2 <= budget) {
+        pl.mode = BWD_SINGLE, pl.chunk = v_pad;
+    } else if (T > V) {
+        int64_t rows = budget / (v_pad * 2) / (2 * kBlockM) * (2 * kBlockM);
+        if (rows < 2 * kBlockM) rows = 2 * kBlockM;
+        const int64_t n = ceil_div(t_pad, rows);
+        pl.mode = BWD_TOKEN, pl.chunk = round_up(ceil_div(t_pad, n), 2 * kBlockM);
+    } else {
+        pl.chunk = vpg_lce_bwd_chunk_for_budget(T, H, V, budget);
+        pl.mode = pl.chunk >= v_pad ? BWD_SINGLE : BWD_VOCAB;
+        if (pl.chunk > v_pad) pl.chunk = v_pad;
+    }
+    const int64_t ds_rows = pl.mode == BWD_TOKEN ? pl.chunk : t_pad;
+    const int64_t ds_cols = pl.mode == BWD_TOKEN ? v_pad : pl.chunk;
+    pl.n_chunks = static_cast<int>(pl.mode == BWD_TOKEN ? ceil_div(t_pad, pl.chunk) : ceil_div(v_pad, pl.chunk));
+    size_t bytes = round_up(ds_rows * ds_cols * 2, 256);
+    pl.off_acc = bytes;
+    if (pl.mode == BWD_VOCAB) bytes += round_up(T * H * 4, 256);  // fp32 d_hidden accumulator
+    if (pl.mode == BWD_TOKEN) bytes += round_up(V * H * 4, 256);  // fp32 d_weight accumulator
+    pl.off_splitk = bytes;
+    bytes += splitk_scratch_bytes();  // split-K tail partial tiles
+    pl.bytes = bytes + 256;
+    return pl;
+}
+
 size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v) {
     if (T <= 0) return 0;
-    if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
-    const int64_t t_pad = round_up(T, 2 * kBlockM);
-    const int64_t v_pad = round_up(V, kBlockN);
-    if (chunk_v > v_pad) chunk_v = v_pad;
-    size_t bytes = static_cast<size_t>(t_pad) * chunk_v * 2;
-    bytes = round_up(bytes, 256);
-    if (chunk_v < v_pad) bytes += round_up(static_cast<int64_t>(T) * H * 4, 256);  // fp32 d_hidden accumulator
-    bytes += splitk_scratch_bytes();                                               // split-K tail partial tiles
-    return bytes + 256;
+    return plan_bwd(T, H, V, chunk_v, 0).bytes;
+}
+
+int vpg_lce_bwd_plan(int64_t T, int64_t H, int64_t V, int64_t chunk_v, int64_t chunk_t, int64_t* out4) {
+    VPG_CHECK_ARG(out4 && T > 0 && H > 0 && V > 0, "invalid arguments");
+    const BwdPlan pl = plan_bwd(T, H, V, chunk_v, chunk_t);
+    out4[0] = pl.mode, out4[1] = pl.chunk, out4[2] = pl.n_chunks, out4[3] = static_cast<int64_t>(pl.bytes);
+    return VPG_OK;
 }
 
 int vpg_lce_bwd(const void* hidden, const void* weight, const int64_t* labels, const float* lse, const float* eb,
@@ -615,61 +667,67 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
         VPG_CUDA(cudaMemsetAsync(a.d_weight, 0, static_cast<size_t>(V) * H * gsz, stream));
         return VPG_OK;
     }
-    int64_t chunk_v = a.chunk_v;
-    if (chunk_v <= 0) chunk_v = vpg_lce_bwd_default_chunk(T, H, V);
-    VPG_CHECK_ARG(chunk_v % kBlockN == 0, "chunk_v must be a multiple of %d", kBlockN);
-    const int64_t t_pad = round_up(T, 2 * kBlockM);  // dlogits rows: multiple of the largest m tile (256)
+    VPG_CHECK_ARG(a.chunk_v % kBlockN == 0 && a.chunk_t % (2 * kBlockM) == 0,
+                  "chunk_v must be a multiple of %d and chunk_t of %d", kBlockN, 2 * kBlockM);
+    const BwdPlan pl = plan_bwd(T, H, V, a.chunk_v, a.chunk_t);
     const int64_t v_pad = round_up(V, kBlockN);
-    if (chunk_v > v_pad) chunk_v = v_pad;
-    const size_t need = vpg_lce_bwd_workspace_bytes(T, H, V, chunk_v);
-    if (!a.workspace || a.workspace_bytes < need)
-        return set_error(VPG_ERR_WORKSPACE, "lce_bwd workspace too small: need %zu bytes, got %zu", need,
+    if (!a.workspace || a.workspace_bytes < pl.bytes)
+        return set_error(VPG_ERR_WORKSPACE, "lce_bwd workspace too small: need %zu bytes, got %zu", pl.bytes,
                          a.workspace_bytes);
     VPG_CHECK_ARG((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, "workspace must be 256-byte aligned");
     uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
     __nv_bfloat16* ds = reinterpret_cast<__nv_bfloat16*>(ws);
-    const int64_t ldds = chunk_v;
-    size_t off = round_up(static_cast<int64_t>(t_pad) * chunk_v * 2, 256);
-    float* dh_acc = reinterpret_cast<float*>(ws + off);
-    if (chunk_v < v_pad) off += round_up(static_cast<int64_t>(T) * H * 4, 256);
-    float* splitk_scratch = reinterpret_cast<float*>(ws + off);
-    const int num_chunks = static_cast<int>(ceil_div(v_pad, chunk_v));
-    const int m_tiles_t = static_cast<int>(t_pad / tile_m());
-    const uint8_t* weight = reinterpret_cast<const uint8_t*>(a.weight);
-    void* d_hidden = a.d_hidden;
+    float* acc_buf = reinterpret_cast<float*>(ws + pl.off_acc);  // fp32 d_hidden (VOCAB) or d_weight (TOKEN) accumulator
+    float* splitk_scratch = reinterpret_cast<float*>(ws + pl.off_splitk);
+    const bool by_token = pl.mode == BWD_TOKEN;
+    const int num_chunks = pl.n_chunks;
+    const int64_t ldds = by_token ? v_pad : pl.chunk;
+    const int64_t esz = f32 ? 4 : 2;
 
     for (int ci = 0; ci < num_chunks; ++ci) {
-        const int64_t v0 = static_cast<int64_t>(ci) * chunk_v;
-        const int64_t vc = (V - v0) < chunk_v ? (V - v0) : chunk_v;
-        const uint8_t* w_chunk = weight + v0 * H * (f32 ? 4 : 2);
+        // this chunk's block of the [T, V] dlogits: rows [t0, t0 + tn), columns [v0, v0 + vc)
+        const int64_t t0 = by_token ? static_cast<int64_t>(ci) * pl.chunk : 0;
+        const int64_t tn = by_token ? ((T - t0) < pl.chunk ? (T - t0) : pl.chunk) : T;
+        const int64_t v0 = by_token ? 0 : static_cast<int64_t>(ci) * pl.chunk;
+        const int64_t vc = by_token ? V : ((V - v0) < pl.chunk ? (V - v0) : pl.chunk);
+        const int64_t t_pad = round_up(tn, 2 * kBlockM);  // dlogits rows: multiple of the largest m tile (256)
+        const int m_tiles_t = static_cast<int>(t_pad / tile_m());
+        const uint8_t* h_chunk = reinterpret_cast<const uint8_t*>(a.hidden) + t0 * H * esz;
+        const __nv_bfloat16* h16_chunk = reinterpret_cast<const __nv_bfloat16*>(hidden16) + t0 * H;
+        const uint8_t* w_chunk = reinterpret_cast<const uint8_t*>(a.weight) + v0 * H * esz;
         const __nv_bfloat16* w16_chunk = reinterpret_cast<const __nv_bfloat16*>(weight16) + v0 * H;
+        uint8_t* d_hidden = a.d_hidden ? reinterpret_cast<uint8_t*>(a.d_hidden) + t0 * H * gsz : nullptr;
         const int n_tiles_c = static_cast<int>(ceil_div(vc, kBlockN));
+        const bool first = ci == 0, last = ci == num_chunks - 1;
         CUtensorMap ta, tb;
-        {  // 1. recompute logits tile -> dlogits chunk (bf16)
+        {  // 1. recompute logits tile -> dlogits block (16-bit)
             TcParams p{};
             p.num_m_tiles = m_tiles_t;
             p.num_n_tiles = n_tiles_c;
             p.num_k_blocks = static_cast<int>(H / (f32 ? kBlockK / 2 : kBlockK));
             p.num_splits = choose_splits(m_tiles_t, n_tiles_c, num_workers());
             p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
-            p.M = static_cast<int>(T);
+            p.M = static_cast<int>(tn);
             p.N = static_cast<int>(vc);
             p.scale_log2 = 1.4426950408889634f / a.temperature;
             p.inv_temp = 1.0f / a.temperature;
-            p.labels = reinterpret_cast<const long long*>(a.labels);
+            p.labels = reinterpret_cast<const long long*>(a.labels) + t0;
             p.label_offset = a.label_offset + v0;
-            p.lse = a.lse;
-            p.eb = a.eb;
-            p.g_lp = a.g_lp;
-            p.g_ent = a.g_ent;
+            p.lse = a.lse + t0;
+            p.eb = a.eb + t0;
+            p.g_lp = a.g_lp ? a.g_lp + t0 : nullptr;
+            p.g_ent = a.g_ent ? a.g_ent + t0 : nullptr;
             p.ds = ds;
             p.ldds = ldds;
-            if ((rc = make_operand_tmap(&ta, a.hidden, T, H, H, false, kBlockM, dt))) return rc;
+            if ((rc = make_operand_tmap(&ta, h_chunk, tn, H, H, false, kBlockM, dt))) return rc;
             if ((rc = make_operand_tmap(&tb, w_chunk, vc, H, H, false, b_tile_rows(), dt))) return rc;
-            if ((rc = launch_tc_lmhead<MODE_DS>(ta, tb, p, dt, stream))) return rc;
+            // dlogits store map: [t_pad][ldds] 16-bit, 32 x 32 boxes in the 64-byte-swizzle layout of the staging tiles
+            CUtensorMap tc;
+            if ((rc = make_tmap(&tc, ds, ldds, t_pad, ldds, 32, 32, dt16, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+            if ((rc = launch_tc_lmhead<MODE_DS>(ta, tb, p, dt, stream, &tc))) return rc;
         }
         const int64_t vc_cols = static_cast<int64_t>(n_tiles_c) * kBlockN;  // dlogits columns actually written
-        // 2. d_weight[v0:v0+vc, :] = dlogits^T . hidden      (M = vc, N = H, K = T_pad)
+        // 2. d_weight[v0:v0+vc, :] (+)= dlogits^T . hidden[t0:t0+tn]      (M = vc, N = H, K = t_pad)
         auto run_d_weight = [&](int max_workers, bool with_allreduce) -> int {
             int rc = 0;
             CUtensorMap ta, tb;
@@ -681,9 +739,21 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             p.tiles_per_split = 1;
             p.M = static_cast<int>(vc);
             p.N = static_cast<int>(H);
-            p.out = reinterpret_cast<uint8_t*>(a.d_weight) + v0 * H * gsz;
+            uint8_t* dw = reinterpret_cast<uint8_t*>(a.d_weight) + v0 * H * gsz;
             p.ldc = H;
-            p.out_mode = f32 ? OUT_F32 : OUT_BF16;
+            if (!by_token || num_chunks == 1) {  // rows of this vocab chunk are final
+                p.out = dw, p.out_mode = f32 ? OUT_F32 : OUT_BF16;
+            } else if (f32) {  // fp32 gradients accumulate in place over the token chunks
+                p.out = dw, p.out_mode = first ? OUT_F32 : OUT_F32_ACC;
+                p.accum = reinterpret_cast<float*>(dw), p.ld_accum = H;
+            } else if (first) {
+                p.out = acc_buf, p.out_mode = OUT_F32;
+            } else if (!last) {
+                p.out = acc_buf, p.out_mode = OUT_F32_ACC;
+            } else {
+                p.out = dw, p.out_mode = OUT_BF16_FROM_ACC;
+                p.accum = acc_buf, p.ld_accum = H;
+            }
             p.f16 = (dt16 == VPG_DT_F16);
             p.max_workers = max_workers;
             plan_splitk(p, max_workers > 0 && max_workers < num_workers() ? max_workers : num_workers(), splitk_scratch);
@@ -698,11 +768,11 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
                 }
             }
             if ((rc = make_operand_tmap(&ta, ds, vc_cols, t_pad, ldds, true, kBlockM, dt16))) return rc;
-            if ((rc = make_operand_tmap(&tb, hidden16, H, T, H, true, kBlockN, dt16))) return rc;
+            if ((rc = make_operand_tmap(&tb, h16_chunk, H, tn, H, true, kBlockN, dt16))) return rc;
             if ((rc = launch_tc<MODE_GEMM, true, true>(ta, tb, p, stream, TK_DW))) return rc;
             return VPG_OK;
         };
-        // 3. d_hidden (+)= dlogits . W[v0:v0+vc, :]          (M = T, N = H, K = vc)
+        // 3. d_hidden[t0:t0+tn] (+)= dlogits . W[v0:v0+vc, :]          (M = tn, N = H, K = vc)
         auto run_d_hidden = [&]() -> int {
             int rc = 0;
             CUtensorMap ta, tb;
@@ -712,28 +782,29 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             p.num_k_blocks = static_cast<int>(ceil_div(vc, kBlockK));
             p.num_splits = p.num_n_tiles;
             p.tiles_per_split = 1;
-            p.M = static_cast<int>(T);
+            p.M = static_cast<int>(tn);
             p.N = static_cast<int>(H);
+            p.ldc = H;
             bool splitk_ok = true;
-            if (d_hidden_mc_f32 && ci == num_chunks - 1) {
+            if (d_hidden_mc_f32 && (by_token || last)) {
                 VPG_CHECK_ARG(H % 32 == 0, "fused d_hidden all-reduce needs H %% 32 == 0");
-                // fused all-reduce: the last chunk's epilogue adds (this rank's fp32 sum over all its vocab chunks)
-                // into every rank's fp32 buffer through the multicast address, tile by tile
-                p.out = d_hidden_mc_f32, p.ldc = H, p.out_mode = OUT_F32_MCRED;
-                p.accum = (num_chunks > 1) ? dh_acc : nullptr, p.ld_accum = H;
+                // multimem.red variant: the epilogue adds this rank's fp32 sum (over all its vocab chunks) into every
+                // rank's fp32 buffer through the multicast address, tile by tile
+                p.out = d_hidden_mc_f32 + t0 * H, p.out_mode = OUT_F32_MCRED;
+                p.accum = (!by_token && num_chunks > 1) ? acc_buf : nullptr, p.ld_accum = H;
                 splitk_ok = false;
-            } else if (f32) {  // fp32 gradients accumulate in place
-                p.out = d_hidden, p.ldc = H, p.out_mode = (ci == 0) ? OUT_F32 : OUT_F32_ACC;
+            } else if (by_token || num_chunks == 1) {  // rows of this token chunk are final
+                p.out = d_hidden, p.out_mode = f32 ? OUT_F32 : OUT_BF16;
+            } else if (f32) {  // fp32 gradients accumulate in place over the vocab chunks
+                p.out = d_hidden, p.out_mode = first ? OUT_F32 : OUT_F32_ACC;
                 p.accum = reinterpret_cast<float*>(d_hidden), p.ld_accum = H;
-            } else if (num_chunks == 1) {
-                p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16;
-            } else if (ci == 0) {
-                p.out = dh_acc, p.ldc = H, p.out_mode = OUT_F32;
-            } else if (ci < num_chunks - 1) {
-                p.out = dh_acc, p.ldc = H, p.out_mode = OUT_F32_ACC;
+            } else if (first) {
+                p.out = acc_buf, p.out_mode = OUT_F32;
+            } else if (!last) {
+                p.out = acc_buf, p.out_mode = OUT_F32_ACC;
             } else {
-                p.out = d_hidden, p.ldc = H, p.out_mode = OUT_BF16_FROM_ACC;
-                p.accum = dh_acc, p.ld_accum = H;
+                p.out = d_hidden, p.out_mode = OUT_BF16_FROM_ACC;
+                p.accum = acc_buf, p.ld_accum = H;
             }
             p.f16 = (dt16 == VPG_DT_F16);
             plan_splitk(p, num_workers(), splitk_ok ? splitk_scratch : nullptr);
@@ -742,7 +813,6 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             if ((rc = launch_tc<MODE_GEMM, false, true>(ta, tb, p, stream, TK_DH))) return rc;
             return VPG_OK;
         };
-        const bool last = ci == num_chunks - 1;
         if (last && fused_ar) {
             // d_hidden first (it is complete on every rank before that rank enters the next kernel); the d_weight GEMM
             // then carries the all-reduce of d_hidden in its spare warps, on all its SMs

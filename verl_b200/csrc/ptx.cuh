@@ -122,6 +122,21 @@ __device__ __forceinline__ void tma_load_2d_2sm(const void* tmap, uint32_t bar_c
         : "memory");
 }
 
+// 2-D tiled STORE shared::cta -> global (bulk async-group completion): the box at `src` (written by this CTA, made
+// visible with fence.proxy.async) goes to coordinates {c0 (innermost), c1}; out-of-bounds parts are clipped
+__device__ __forceinline__ void tma_store_2d(const void* tmap, const void* src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(tmap)),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until at most kPending of this thread's bulk groups have not finished READING their shared-memory source
+template <int kPending>
+__device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
+}
+
 // L2 eviction-priority hints for TMA loads (the fixed createpolicy encodings CUTLASS calls TMA::CacheHintSm90)
 constexpr uint64_t kHintEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kHintEvictFirst = 0x12F0000000000000ull;

@@ -62,18 +62,32 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
     return part
 
 
+_BWD_MODES = {0: "single block", 1: "vocab chunks (fp32 d_hidden accumulator)", 2: "token chunks (fp32 d_weight accumulator)"}
+
+
+def backward_plan(T: int, H: int, V: int, chunk_v: int = 0, chunk_t: int = 0) -> dict:
+    """How the backward will cut its dlogits workspace (vpg_lce_bwd_plan): mode, chunk, chunks, workspace_bytes."""
+    import ctypes
+
+    out = (ctypes.c_int64 * 4)()
+    check(_lib_().vpg_lce_bwd_plan(int(T), int(H), int(V), int(chunk_v), int(chunk_t), out))
+    return {"mode": _BWD_MODES[int(out[0])], "chunk": int(out[1]), "chunks": int(out[2]), "workspace_bytes": int(out[3])}
+
+
 def backward_chunk(T: int, H: int, V: int, device, chunk_v: int = 0) -> int:
-    """Vocab columns of dlogits materialised at a time by the backward.  An explicit ``chunk_v`` wins; otherwise the
-    library default: the widest chunk whose 16-bit ``[T, chunk]`` buffer fits $VPG_BWD_WS_MB (default 4096 MiB — the
-    same order as the reference's default 9 504-column split, kernels.py:1492-1501, at 64k tokens), never more than the
-    free memory allows.  The whole-vocabulary single chunk (20 GB at BASELINE configs[1]) is opt-in through
-    ``kernels.set_backward_chunk`` or the environment variable."""
+    """Explicit column-chunk width to pass to the backward, or 0 = let the library plan.  An explicit ``chunk_v`` wins.
+    Otherwise the library bounds the 16-bit dlogits block by $VPG_BWD_WS_MB (default 4096 MiB — the order of the
+    reference's default 9 504-column split, kernels.py:1492-1501, at 64k tokens) and chunks along the vocabulary or along
+    the tokens, whichever needs the smaller fp32 accumulator.  Only under memory pressure (the planned workspace exceeds
+    half of what is free right now) this falls back to narrower vocabulary chunks.  The whole-vocabulary single block
+    (20 GB at BASELINE configs[1]) is opt-in: ``kernels.set_backward_chunk`` or the environment variable."""
     if chunk_v and chunk_v > 0:
         return int(chunk_v)
     lib = _lib_()
-    chunk = int(lib.vpg_lce_bwd_default_chunk(T, H, V))
     free, _total = torch.cuda.mem_get_info(device)
-    # under memory pressure: the largest chunk that leaves half of what is free right now to the caller
+    if int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, 0)) <= free // 2:
+        return 0
+    chunk = int(lib.vpg_lce_bwd_default_chunk(T, H, V))
     while chunk > 256 and int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, chunk)) > free // 2:
         chunk = max(256, (chunk // 2) // 256 * 256)
     return chunk
@@ -129,11 +143,8 @@ def _bwd_workspace(T, H, V, device, chunk_v):
 
 
 def lce_backward_workspace_info(T: int, H: int, V: int, device, chunk_v: int = 0) -> dict:
-    """{chunk_v, chunks, workspace_bytes} the backward would use right now (bench.py reports it)."""
-    chunk_v = backward_chunk(T, H, V, device, chunk_v)
-    v_pad = (V + 255) // 256 * 256
-    return {"chunk_v": int(min(chunk_v, v_pad)), "chunks": int(-(-v_pad // min(chunk_v, v_pad))),
-            "workspace_bytes": int(_lib_().vpg_lce_bwd_workspace_bytes(T, H, V, int(chunk_v)))}
+    """{mode, chunk, chunks, workspace_bytes} the backward would use right now (bench.py reports it)."""
+    return backward_plan(T, H, V, backward_chunk(T, H, V, device, chunk_v))
 
 
 def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int,
@@ -175,7 +186,8 @@ def lce_finalize(partials, temperature: float):
 
 
 def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: float, label_offset: int = 0,
-                 chunk_v: int = 0, d_hidden_ready_event: int = 0, reserve_cta_pairs: int = 0, allreduce=None):
+                 chunk_v: int = 0, d_hidden_ready_event: int = 0, reserve_cta_pairs: int = 0, allreduce=None,
+                 chunk_t: int = 0):
     """-> (d_hidden [T,H], d_weight [V,H]) in the operands' dtype (fp32 gradients for fp32 operands).  One call of
     vpg_lce_bwd_ex: every option is an explicit field of its argument struct.
 
@@ -190,7 +202,12 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
     T, H = hidden.shape
     V = weight.shape[0]
     lib = _lib_()
-    chunk_v, nbytes, ws = _bwd_workspace(T, H, V, hidden.device, chunk_v)
+    if chunk_t and not chunk_v:  # explicit row chunks (multiple of 256)
+        nbytes = backward_plan(T, H, V, 0, chunk_t)["workspace_bytes"]
+        ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=hidden.device)
+    else:
+        chunk_t = 0
+        chunk_v, nbytes, ws = _bwd_workspace(T, H, V, hidden.device, chunk_v)
     dt = operand_dtype(hidden, weight)
     d_hidden = allreduce["out"] if allreduce else torch.empty_like(hidden)
     d_weight = torch.empty_like(weight)
@@ -205,7 +222,7 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
     a.hidden, a.weight, a.labels, a.lse, a.eb = ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb)
     a.g_lp, a.g_ent = ptr(g_lp), ptr(g_ent)
     a.T, a.H, a.V = T, H, V
-    a.temperature, a.label_offset, a.chunk_v = float(temperature), int(label_offset), int(chunk_v)
+    a.temperature, a.label_offset, a.chunk_v, a.chunk_t = float(temperature), int(label_offset), int(chunk_v), int(chunk_t)
     a.d_hidden, a.d_weight = ptr(d_hidden), ptr(d_weight)
     a.workspace, a.workspace_bytes = ptr(ws), nbytes
     a.stream = stream_ptr(hidden.device)

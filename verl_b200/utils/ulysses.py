@@ -1,158 +1,152 @@
-"""Ulysses sequence-parallel plumbing on either side of the per-token path (mirror of verl/utils/ulysses.py,
-SURVEY.md §8(f).4): the rmpad token stream is padded to a multiple of sp_size and sliced per rank before the model
-(`ulysses_pad_and_slice_inputs`, :278-321, called dp_actor.py:139-160), and the per-token log-probs / entropies of
-the ranks are gathered back and un-padded after the lm-head (`gather_outputs_and_unpad`, :243-275, called
-dp_actor.py:206-219).
+"""Sequence-parallel (Ulysses) plumbing on either side of the per-token path — SURVEY.md §8(f).4.
 
-This is collective plumbing, not a kernel: one `all_gather_into_tensor` (NCCL over NVLink on the GPU box, gloo in the
-CPU tests) and views.  The head/sequence all-to-all of the attention layers (`gather_seq_scatter_heads`, :62-101)
-belongs to the transformer body and is out of scope.
+The reference (verl/utils/ulysses.py) pads the rmpad token stream to a multiple of the sequence-parallel size and hands
+every rank one contiguous slice before the model (`ulysses_pad_and_slice_inputs` :296-321, called from dp_actor.py:
+139-160), then gathers the per-token log-probs / entropies of the ranks and drops the padding after the lm-head
+(`gather_outputs_and_unpad` :243-275, called from dp_actor.py:206-219).  Only those two call sites are on the path, so
+this module provides exactly the names they (and `compat.install`) need, with the reference's argument meaning.  The
+head/sequence all-to-all inside attention belongs to the transformer body and is out of scope.
+
+Implementation notes (nothing here is a kernel — one `all_gather_into_tensor` over NCCL/NVLink, gloo in the CPU tests):
+* the gather is ONE collective into a `[world, ...]` buffer; gathering along axis 0 is then a free reshape, any other
+  axis one `movedim` + `reshape` (a single strided copy), never a per-rank `cat`;
+* padding uses `torch.nn.functional.pad`; slices are `narrow` views made contiguous once.
 """
 
 from __future__ import annotations
 
-from typing import Any, Optional
+from typing import Optional
 
 import torch
 import torch.distributed as dist
-from torch import Tensor
-from torch.distributed import ProcessGroup
+import torch.nn.functional as F
 
-_ULYSSES_SEQUENCE_PARALLEL_GROUP = None
+__all__ = [
+    "set_ulysses_sequence_parallel_group", "get_ulysses_sequence_parallel_group",
+    "get_ulysses_sequence_parallel_world_size", "get_ulysses_sequence_parallel_rank", "slice_input_tensor", "Gather",
+    "gather_outputs_and_unpad", "ulysses_pad", "ulysses_pad_and_slice_inputs", "validate_ulysses_config",
+]
 
-
-def set_ulysses_sequence_parallel_group(group: dist.ProcessGroup):
-    global _ULYSSES_SEQUENCE_PARALLEL_GROUP
-    _ULYSSES_SEQUENCE_PARALLEL_GROUP = group
-
-
-def get_ulysses_sequence_parallel_group() -> Optional[dist.ProcessGroup]:
-    return _ULYSSES_SEQUENCE_PARALLEL_GROUP
+_state = {"group": None}
 
 
-def get_ulysses_sequence_parallel_world_size(group: ProcessGroup = None) -> int:
-    group = get_ulysses_sequence_parallel_group() if group is None else group
-    return dist.get_world_size(group) if group else 1
+def set_ulysses_sequence_parallel_group(group):
+    _state["group"] = group
 
 
-def get_ulysses_sequence_parallel_rank(group: ProcessGroup = None) -> int:
-    group = get_ulysses_sequence_parallel_group() if group is None else group
-    return dist.get_rank(group) if group else 0
+def get_ulysses_sequence_parallel_group():
+    return _state["group"]
 
 
-def _pad_tensor(x: Tensor, dim: int, padding_size: int) -> Tensor:
-    """zero-extend `dim` by padding_size (ulysses.py:104-108)"""
-    tail = list(x.shape)
-    tail[dim] = padding_size
-    return torch.cat((x, x.new_zeros(tail)), dim=dim)
+def _resolve(group):
+    return _state["group"] if group is None else group
 
 
-def _unpad_tensor(x: Tensor, dim: int, padding_size: int) -> Tensor:
-    """drop the last padding_size entries of `dim` (ulysses.py:111-114); a view"""
-    return x.narrow(dim, 0, x.size(dim) - padding_size)
+def get_ulysses_sequence_parallel_world_size(group=None) -> int:
+    g = _resolve(group)
+    return 1 if g is None else dist.get_world_size(g)
 
 
-def slice_input_tensor(x: Tensor, dim: int, padding: bool = True, group: ProcessGroup = None) -> Tensor:
-    """ulysses.py:117-130: this rank's contiguous 1/sp slice along `dim` (zero-padded first when it does not divide)."""
-    group = get_ulysses_sequence_parallel_group() if group is None else group
-    world, rank = dist.get_world_size(group), get_ulysses_sequence_parallel_rank(group)
-    rem = x.size(dim) % world
-    if padding and rem:
-        x = _pad_tensor(x, dim, world - rem)
-    per_rank = x.size(dim) // world
-    return x.narrow(dim, rank * per_rank, per_rank).contiguous()
+def get_ulysses_sequence_parallel_rank(group=None) -> int:
+    g = _resolve(group)
+    return 0 if g is None else dist.get_rank(g)
 
 
-def all_gather_tensor(local_tensor: Tensor, group: Optional[dist.ProcessGroup] = None, async_op: bool = False):
-    """ulysses.py:155-162: concatenation of every rank's tensor along axis 0."""
-    group = get_ulysses_sequence_parallel_group() if group is None else group
-    sp_world_size = dist.get_world_size(group=group)
-    output_shape = list(local_tensor.shape)
-    output_shape[0] = output_shape[0] * sp_world_size
-    output = torch.empty(output_shape, dtype=local_tensor.dtype, device=local_tensor.device)
-    dist.all_gather_into_tensor(output, local_tensor.contiguous(), group=group, async_op=async_op)
-    return output
+def _zero_extend(x: torch.Tensor, dim: int, extra: int) -> torch.Tensor:
+    """`extra` zeros appended along `dim`"""
+    if extra <= 0:
+        return x
+    dim %= x.dim()
+    spec = [0, 0] * (x.dim() - 1 - dim) + [0, extra]  # F.pad counts axes from the last one
+    return F.pad(x, spec)
+
+
+def slice_input_tensor(x: torch.Tensor, dim: int, padding: bool = True, group=None) -> torch.Tensor:
+    """This rank's contiguous 1/world share of `x` along `dim`; with ``padding`` the axis is zero-extended to a multiple
+    of the group size first (verl/utils/ulysses.py:117-130)."""
+    g = _resolve(group)
+    world, rank = dist.get_world_size(g), dist.get_rank(g)
+    if padding:
+        x = _zero_extend(x, dim, -x.size(dim) % world)
+    share = x.size(dim) // world
+    return x.narrow(dim, rank * share, share).contiguous()
 
 
 class Gather(torch.autograd.Function):
-    """ulysses.py:194-234: all-gather along `gather_dim`; the backward keeps this rank's slice of the gradient,
-    multiplied by the group size when grad_scaler is set (the loss is averaged over the sp ranks' replicas)."""
+    """Differentiable all-gather along `gather_dim` (verl/utils/ulysses.py:194-234).  Backward: this rank's slice of the
+    incoming gradient, times the group size when ``grad_scaler`` (every sp rank holds a replica of the loss)."""
 
     @staticmethod
-    def forward(ctx: Any, group: dist.ProcessGroup, local_tensor: Tensor, gather_dim: int, grad_scaler: bool = True,
-                async_op=False) -> Tensor:
-        ctx.group = group
-        ctx.gather_dim = gather_dim
-        ctx.grad_scaler = grad_scaler
-        ctx.sp_world_size = dist.get_world_size(group=group)
-        ctx.sp_rank = dist.get_rank(group=group)
-        ctx.part_size = local_tensor.size(gather_dim)
-        output = all_gather_tensor(local_tensor, group, async_op)
-        if gather_dim % max(local_tensor.dim(), 1) == 0:
-            return output  # the all-gather already concatenates along axis 0: no second copy
-        return torch.cat(output.split(local_tensor.size(0), dim=0), dim=gather_dim)
+    def forward(ctx, group, local_tensor, gather_dim, grad_scaler=True, async_op=False):
+        world = dist.get_world_size(group)
+        ctx.meta = (dist.get_rank(group), world, gather_dim % max(local_tensor.dim(), 1), local_tensor.size(gather_dim),
+                    bool(grad_scaler))
+        src = local_tensor.contiguous()
+        stacked = src.new_empty((world, *src.shape))
+        dist.all_gather_into_tensor(stacked.view(world * src.shape[0], *src.shape[1:]) if src.dim() else stacked, src,
+                                    group=group)
+        axis = ctx.meta[2]
+        if src.dim() == 0:
+            return stacked
+        if axis == 0:
+            return stacked.view(world * src.shape[0], *src.shape[1:])
+        # [world, d0, .., d_axis, ..] -> [d0, .., world * d_axis, ..]: rank-major along the gathered axis
+        out_shape = list(src.shape)
+        out_shape[axis] *= world
+        return stacked.movedim(0, axis).reshape(out_shape)
 
     @staticmethod
-    def backward(ctx: Any, grad_output: Tensor) -> Any:
-        if ctx.grad_scaler:
-            grad_output = grad_output * ctx.sp_world_size
-        return (None, grad_output.split(ctx.part_size, dim=ctx.gather_dim)[ctx.sp_rank].contiguous(), None, None, None)
+    def backward(ctx, grad_output):
+        rank, world, axis, width, scale = ctx.meta
+        mine = grad_output.narrow(axis, rank * width, width)
+        mine = mine * world if scale else mine.contiguous()
+        return None, mine.contiguous(), None, None, None
 
 
-def gather_outpus_and_unpad(*args, **kwargs):
-    raise RuntimeError(
-        "please use verl.utils.ulysses.gather_outputs_and_unpad instead of verl.utils.ulysses.gather_outpus_and_unpad"
-    )
-
-
-def gather_outputs_and_unpad(x: Tensor, gather_dim: int, unpad_dim: int = None, padding_size: int = 0,
-                             grad_scaler: bool = True, group: Optional[dist.ProcessGroup] = None):
-    """ulysses.py:243-275: gather `x` across the sp group and drop `padding_size` trailing elements of `unpad_dim`
-    (the ulysses_pad padding).  Without a group `x` is returned unchanged."""
-    group = get_ulysses_sequence_parallel_group() if group is None else group
-    if group is None:
+def gather_outputs_and_unpad(x: torch.Tensor, gather_dim: int, unpad_dim: Optional[int] = None, padding_size: int = 0,
+                             grad_scaler: bool = True, group=None) -> torch.Tensor:
+    """Gather `x` over the sequence-parallel group along `gather_dim`, then cut the `padding_size` trailing entries that
+    `ulysses_pad` added along `unpad_dim` (verl/utils/ulysses.py:243-275).  No group configured: `x` itself."""
+    g = _resolve(group)
+    if g is None:
         return x
-    x = Gather.apply(group, x, gather_dim, grad_scaler)
-    if unpad_dim is not None:
-        assert isinstance(padding_size, int), "padding size is not given or is not an integer"
-        if padding_size == 0:
-            return x
-        x = _unpad_tensor(x, unpad_dim, padding_size)
-    return x
+    full = Gather.apply(g, x, gather_dim, grad_scaler)
+    if unpad_dim is None:
+        return full
+    if not isinstance(padding_size, int):
+        raise AssertionError("padding size is not given or is not an integer")
+    return full if padding_size == 0 else full.narrow(unpad_dim, 0, full.size(unpad_dim) - padding_size)
 
 
 def ulysses_pad(input_ids_rmpad: torch.Tensor, position_ids_rmpad: Optional[torch.Tensor] = None, sp_size: int = 1):
-    """ulysses.py:278-293: right-pad the [1,T] id stream with 0 and the position ids with 0..pad-1 ([1,T] or mrope
-    [3,1,T]) so that T divides by sp_size.  -> (ids, position_ids, pad_size)."""
+    """Make the token axis of the `[1, T]` id stream divisible by `sp_size` (verl/utils/ulysses.py:278-293): ids get
+    zeros, position ids (`[1, T]`, or mrope `[3, 1, T]`) continue with 0, 1, .., pad-1.  -> (ids, position_ids, pad)."""
     if position_ids_rmpad is not None:
         assert position_ids_rmpad.size(-2) == 1
         assert input_ids_rmpad.size(-1) == position_ids_rmpad.size(-1)
-    if sp_size <= 1:
+    pad = -input_ids_rmpad.shape[1] % sp_size if sp_size > 1 else 0
+    if pad == 0:
         return input_ids_rmpad, position_ids_rmpad, 0
-    pad_size = -input_ids_rmpad.shape[1] % sp_size
-    if pad_size == 0:
-        return input_ids_rmpad, position_ids_rmpad, 0
-    input_ids_rmpad = _pad_tensor(input_ids_rmpad, 1, pad_size)
-    if position_ids_rmpad is not None:
-        ramp = torch.arange(pad_size, device=position_ids_rmpad.device, dtype=torch.int64)
-        ramp = ramp.expand(*position_ids_rmpad.shape[:-1], pad_size)  # [1,pad] or [3,1,pad]
-        position_ids_rmpad = torch.cat((position_ids_rmpad, ramp), dim=-1)
-    return input_ids_rmpad, position_ids_rmpad, pad_size
+    ids = _zero_extend(input_ids_rmpad, 1, pad)
+    pos = position_ids_rmpad
+    if pos is not None:
+        pos = _zero_extend(pos, -1, pad)
+        pos[..., -pad:] = torch.arange(pad, device=pos.device, dtype=pos.dtype)
+    return ids, pos, pad
 
 
 def ulysses_pad_and_slice_inputs(input_ids_rmpad: torch.Tensor, position_ids_rmpad: Optional[torch.Tensor] = None,
                                  sp_size: int = 1):
-    """ulysses.py:296-321: pad, then keep this rank's slice of the stream (ids along dim 1; position ids along the
-    reference's `dim=1` as well, i.e. the token axis of [1,T])."""
-    input_ids_rmpad, position_ids_rmpad, pad_size = ulysses_pad(input_ids_rmpad, position_ids_rmpad, sp_size)
-    input_ids_rmpad = slice_input_tensor(input_ids_rmpad, dim=1, padding=False)
-    if position_ids_rmpad is not None:
-        position_ids_rmpad = slice_input_tensor(position_ids_rmpad, dim=1, padding=False)
-    return input_ids_rmpad, position_ids_rmpad, pad_size
+    """`ulysses_pad`, then each rank keeps its slice of dim 1 of both tensors (verl/utils/ulysses.py:296-321; dim 1 is
+    the token axis of `[1, T]` position ids — the reference slices mrope position ids along the same dim)."""
+    ids, pos, pad = ulysses_pad(input_ids_rmpad, position_ids_rmpad, sp_size)
+    ids = slice_input_tensor(ids, dim=1, padding=False)
+    if pos is not None:
+        pos = slice_input_tensor(pos, dim=1, padding=False)
+    return ids, pos, pad
 
 
 def validate_ulysses_config(num_heads, ulysses_sequence_size):
-    if ulysses_sequence_size > 1:
-        assert num_heads % ulysses_sequence_size == 0, (
-            f"num_heads ({num_heads}) must be divisible by ulysses sequence size({ulysses_sequence_size})"
-        )
+    """the head axis must split evenly over the sequence-parallel ranks (verl/utils/ulysses.py:324-328)"""
+    if ulysses_sequence_size > 1 and num_heads % ulysses_sequence_size != 0:
+        raise AssertionError(f"num_heads ({num_heads}) must be divisible by ulysses sequence size({ulysses_sequence_size})")
