@@ -293,8 +293,10 @@ int vpg_response_rows(const int64_t* indices, const int64_t* ids_rmpad, int64_t 
 /* out[i, :] = src[indices[i], :]  rows of row_bytes bytes (index_first_axis) */
 int vpg_gather_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
                     void* stream);
-/* out[indices[i], :] = src[i, :]; `out` has n_out rows and is zero-filled first when zero_fill != 0 (pad_input);
- * accumulate_f32 != 0 does out += (float rows; backward of index_first_axis with repeated indices not needed). */
+/* out[indices[i], :] = src[i, :]; `out` has n_out rows (pad_input / index_put_first_axis, flash-attn bert_padding).
+ * zero_fill 0: the other rows are left as they are; 1: `out` is zero-filled first (memset + scatter, any index order);
+ * 2: the caller guarantees STRICTLY ASCENDING indices (what vpg_unpad_indices produces) and ONE pass writes every output
+ * row exactly once — scattered rows and the zero gaps between them — with no memset and no second write. */
 int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int64_t row_bytes, void* out,
                      int64_t n_out, int zero_fill, void* stream);
 

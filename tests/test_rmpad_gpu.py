@@ -163,3 +163,43 @@ def test_response_rmpad_helpers(dev):
     want = port.logprobs_from_logits(logits[:, -R - 1:-1].cpu(), ids[:, -R:].cpu())
     torch.testing.assert_close(got.cpu(), want, atol=1e-5, rtol=1e-5)
     torch.testing.assert_close(got2.cpu(), want, atol=1e-5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("row", [1, 3, 8, 96])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.int64])
+def test_pad_input_one_pass_gap_fill(row, dtype, dev):
+    """pad_input with indices that come straight from unpad_input takes the one-pass gap-filling kernel (every output row
+    written once, no memset); the result must be bit-identical to the memset + scatter path an unmarked copy of the same
+    indices takes, and to flash-attn's definition (zeros elsewhere).  Masks with empty rows, a masked head and a masked
+    tail, one valid token, everything valid."""
+    from verl_b200 import bert_padding, ops
+
+    g = torch.Generator().manual_seed(row)
+    masks = [(torch.rand(7, 53, generator=g) < 0.6).long(), torch.ones(3, 17, dtype=torch.long)]
+    m = torch.zeros(5, 40, dtype=torch.long)
+    m[1, 5:9] = 1
+    m[3, 39] = 1
+    masks.append(m)
+    one = torch.zeros(4, 9, dtype=torch.long)
+    one[2, 4] = 1
+    masks.append(one)
+    big = (torch.rand(64, 4096, generator=g) < 0.63).long()
+    big[5] = 0
+    big[:, :100] = 0
+    big[:, -300:] = 0
+    masks.append(big)
+    for mask in masks:
+        B, S = mask.shape
+        md = mask.to(dev)
+        idx, _, _, _ = ops.unpad_indices(md)
+        assert getattr(idx, "_vpg_ascending", False)
+        n = idx.numel()
+        vals = (torch.randn(n, row, generator=g) * 100).to(dtype).to(dev)
+        fast = ops.scatter_rows(vals, idx, B * S)
+        slow = ops.scatter_rows(vals, idx.clone(), B * S)
+        assert torch.equal(fast, slow)
+        ref = torch.zeros(B * S, row, dtype=dtype, device=dev)
+        ref[idx] = vals
+        assert torch.equal(fast, ref)
+        out = bert_padding.pad_input(vals, idx, B, S)
+        assert torch.equal(out.reshape(B * S, row), ref)

@@ -409,6 +409,14 @@ int vpg_scatter_rows(const void* src, const int64_t* indices, int64_t n_idx, int
                      int64_t n_out, int zero_fill, void* stream_) {
     VPG_CHECK_ARG(n_idx >= 0 && row_bytes > 0 && n_out >= 0, "invalid scatter_rows arguments");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (zero_fill == 2 && n_idx > 0 && n_out > 0) {
+        // the caller guarantees STRICTLY ASCENDING indices (unpad_input's): one pass writes every output byte once
+        VPG_CHECK_ARG(src && indices && out, "null pointer argument");
+        VPG_CUDA(launch_scatter_rows_gapfill(src, reinterpret_cast<const long long*>(indices), n_idx, n_out, row_bytes,
+                                             out, stream));
+        count_launch();
+        return VPG_OK;
+    }
     if (zero_fill && n_out > 0) {
         VPG_CHECK_ARG(out, "null output");
         VPG_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(n_out) * row_bytes, stream));

@@ -344,7 +344,9 @@ def unpad_indices(mask2d):
                                     ws.numel() * 8, stream_ptr(dev)))
         torch.cuda.current_stream(dev).synchronize()
     nnz, max_seqlen = int(slot.pair[0]), int(slot.pair[1])
-    return indices_full[:nnz], seqlens, cu, max_seqlen
+    indices = indices_full[:nnz]
+    indices._vpg_ascending = True  # provenance mark: pad_input may then fill gaps in one pass (see scatter_rows)
+    return indices, seqlens, cu, max_seqlen
 
 
 def response_rows(indices, ids_rmpad, S: int, L: int):
@@ -380,8 +382,13 @@ def gather_rows(src, indices):
 
 
 def scatter_rows(src, indices, n_out: int):
-    """zeros [n_out, ...] with out[indices[i]] = src[i]  (pad_input / index_put_first_axis)."""
+    """zeros [n_out, ...] with out[indices[i]] = src[i]  (pad_input / index_put_first_axis).
+
+    Indices that come straight out of ``unpad_indices`` (strictly ascending by construction; the tensor object carries
+    the mark ``_vpg_ascending``) take the ONE-pass kernel: every output row — scattered row or zero gap — is written
+    exactly once.  Any other index tensor (the API does not promise an order) takes memset + scatter."""
     _require_cuda(src, indices)
+    fill = 2 if getattr(indices, "_vpg_ascending", False) else 1
     src = src.contiguous()
     row_shape = src.shape[1:]
     row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
@@ -389,7 +396,7 @@ def scatter_rows(src, indices, n_out: int):
     if n_out and row_bytes:
         with torch.cuda.device(src.device):
             check(_lib_().vpg_scatter_rows(ptr(src), ptr(indices.contiguous()), indices.numel(), row_bytes, ptr(out),
-                                           n_out, 1, stream_ptr(src.device)))
+                                           n_out, fill, stream_ptr(src.device)))
     return out
 
 
