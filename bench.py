@@ -780,8 +780,8 @@ def run_ours(args, name, cfg):
         dist.destroy_process_group()
 
 
-def token_ops_table(torch, dev, peaks, log2_tokens: int = 24):
-    """HBM-roofline rows of the memory-bound token kernels (scripts/bench_token_ops.py) at 2^24 tokens: achieved GB/s of
+def token_ops_table(torch, dev, peaks, log2_tokens: int = 25):
+    """HBM-roofline rows of the memory-bound token kernels (scripts/bench_token_ops.py) at 2^25 tokens: achieved GB/s of
     algorithmic bytes against the measured HBM peak.  Driver-visible copy of profiles/*token_ops_hbm_roofline*.jsonl."""
     sys.path.insert(0, os.path.join(ROOT, "scripts"))
     import bench_token_ops as bto
@@ -791,7 +791,7 @@ def token_ops_table(torch, dev, peaks, log2_tokens: int = 24):
     d = bto.make(B, L, dev)
     out = []
     for op, fn, nbytes in bto.ops_table(d, B, L, 8):
-        ms = bto.timeit(fn, iters=5, warmup=2)
+        ms = bto.timeit(fn, iters=10, warmup=3)
         gbs = nbytes / (ms * 1e-3) / 1e9
         out.append({"op": op, "tokens": B * L, "ms": round(ms, 4), "achieved_gbs": round(gbs, 1),
                     "frac_of_hbm_peak": round(gbs / peaks["hbm"], 3)})

@@ -188,6 +188,8 @@ def test_pad_input_one_pass_gap_fill(row, dtype, dev):
     big[:, :100] = 0
     big[:, -300:] = 0
     masks.append(big)
+    ragged = (torch.arange(1237)[None] < torch.randint(0, 1238, (129, 1), generator=g)).long()  # many narrow-row tiles
+    masks.append(ragged)
     for mask in masks:
         B, S = mask.shape
         md = mask.to(dev)

@@ -502,6 +502,11 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
         if (ks > 8) ks = 8;
         return static_cast<double>(tiles / W) + 1.0 / static_cast<double>(ks < 1 ? 1 : ks);
     };
+    // Fixed cost of one more chunk, in the same unit (one 256x256x64 tile step of one worker ~ 0.44 us at the sustained
+    // rate): three launches with their ramps (~0.12 ms) plus the read-modify-write of the fp32 [T, H] accumulator in the
+    // d_hidden epilogue (8 B per element at HBM rate).  Measured at configs[1]: 8 chunks cost 4.2 ms more than one block
+    // (profiles/r2_bench_c2_n1*.json), i.e. ~0.6 ms per chunk.
+    const double chunk_overhead = 300.0 + 3.0e-6 * static_cast<double>(t_pad) * static_cast<double>(H);
     for (int64_t nc = min_chunks; nc <= min_chunks + 8 && nc <= v_tiles; ++nc) {
         const int64_t c = ceil_div(v_tiles, nc);
         double cost = 0;
@@ -510,7 +515,7 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
             cost += static_cast<double>(ceil_div(m_t * ct, W)) * (H / kBlockK);                  // dlogits
             cost += rounds(ceil_div(ct * kBlockN, tm) * n_h) * (t_pad / kBlockK);                 // d_weight
             cost += rounds(m_t * n_h) * (ct * kBlockN / kBlockK);                                 // d_hidden
-            cost += 0.02 * (t_pad / kBlockK);                                                     // launches, fp32 RMW
+            cost += chunk_overhead;                                                               // launches, fp32 RMW
         }
         if (cost < best_cost) {
             best_cost = cost;
