@@ -689,6 +689,47 @@ def run_ours(args, name, cfg):
 
     fwd_ms, loss_ms, bwd_ms = seg_ms(0, 1), seg_ms(1, 2), seg_ms(2, 3)
 
+    per_rank = None
+    if world > 1:  # every rank's own view of the step (the headline is the max over ranks): kernels, segments
+        mine = {}
+        for k, ms in per_launch:
+            if ms >= 0:
+                mine[k] = mine.get(k, 0.0) + ms / args.steps
+        mine = {k: round(v, 3) for k, v in mine.items()}
+        mine.update(seg_fwd=round(fwd_ms or 0, 3), seg_bwd=round(bwd_ms or 0, 3))
+        # ... and step by step (kernel durations summed per step; the forward segment of every step), so that the spread a
+        # synchronising exchange has to absorb is visible: the step costs max-over-ranks at every sync point
+        by_kind = {}
+        for k, ms in per_launch:
+            if ms >= 0:
+                by_kind.setdefault(k, []).append(ms)
+        steps_view = {}
+        for k, v in by_kind.items():
+            per = max(len(v) // args.steps, 1)
+            steps_view[k] = [round(sum(v[i * per:(i + 1) * per]), 3) for i in range(args.steps)]
+        steps_view["seg_fwd"] = [round(m[0].elapsed_time(m[1]), 3) for m in marks if m[1] is not None]
+        steps_view["seg_bwd"] = [round(m[2].elapsed_time(m[3]), 3) for m in marks if m[2] is not None]
+        gathered_rows = [None] * world
+        dist.all_gather_object(gathered_rows, (mine, steps_view))
+        per_rank = {k: [g[0].get(k) for g in gathered_rows] for k in mine}
+        per_rank["per_step"] = {k: [g[1].get(k) for g in gathered_rows] for k in steps_view}
+
+    if args.trace:
+        from torch.profiler import ProfilerActivity, profile
+
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(3):
+                step(False, False)
+            torch.cuda.synchronize()
+        evs = [{"name": e.name[:96], "ts_us": e.time_range.start, "dur_us": e.time_range.end - e.time_range.start}
+               for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+        evs.sort(key=lambda e: e["ts_us"])
+        with open(f"{args.trace}.rank{rank}.json", "w") as f:
+            json.dump({"rank": rank, "world": world, "config": name, "tp_reduce": reduce_how, "events": evs}, f)
+
     if rank == 0:
         peaks = _peaks()
         # per-kernel roofline: algorithmic flops of one launch of each tcgen05 kernel / its CUDA-event duration
@@ -753,6 +794,7 @@ def run_ours(args, name, cfg):
                 "timed_with": "CUDA events around the launch on its own stream (vpg_timing_*), averaged over the timed steps",
             },
             "roofline_kernels": kernels_out,
+            "per_rank_ms": per_rank,
             "roofline_step": {
                 "useful_tflops": step_useful_tf, "executed_tflops": step_exec_tf,
                 "useful_frac_of_sustained": step_useful_tf / peaks["sustained"] if step_useful_tf else None,
@@ -821,6 +863,8 @@ def main():
                     help="N>1 end-to-end leg: how the replicated hidden is assembled from the per-rank H2D shards")
     ap.add_argument("--tp-exchange", choices=["auto", "nccl", "nvlink"], default="auto",
                     help="N > 1: fused NVLink exchange (default when NVSwitch multicast is available) or NCCL")
+    ap.add_argument("--trace", default="", help="after the timed runs, record 3 more steps under torch.profiler (CUPTI) "
+                    "and write every rank's kernel timeline to <path>.rank<r>.json (scripts/trace_summary.py reads them)")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     if args.impl == "reference":

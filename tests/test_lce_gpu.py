@@ -527,7 +527,8 @@ def test_gemm_all_majors(dev):
     from verl_b200 import ops
 
     torch.manual_seed(0)
-    for (M, N, K) in [(128, 256, 64), (304, 520, 192), (1000, 1024, 1024)]:
+    # N = 904 / 1496 / 1024 take the 256 x 512 tiles of CTA pairs (ragged last tile across both column groups)
+    for (M, N, K) in [(128, 256, 64), (304, 520, 192), (1000, 1024, 1024), (304, 904, 192), (520, 1496, 320)]:
         A = (torch.rand(M, K, device=dev) - 0.5).bfloat16()
         B = (torch.rand(N, K, device=dev) - 0.5).bfloat16()
         ref = A.float() @ B.float().t()

@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/vpg_b200.h"
 
@@ -34,6 +35,11 @@ int sm_count();  // SMs of the current device (cached per device)
         VPG_CUDA(cudaGetLastError());       \
     } while (0)
 
+// tuning knobs: read from the environment ONCE (callers keep the value in a function-local static)
+static inline int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
 

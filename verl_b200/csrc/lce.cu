@@ -55,13 +55,10 @@ struct Tuning {
     int reserve_pairs = -1;  // VPG_BWD_RESERVE_PAIRS: override of the caller's reserve_cta_pairs
     int bwd_ws_mb = 4096;    // VPG_BWD_WS_MB: default dlogits workspace budget (MiB)
     int splitk = 1;          // VPG_SPLITK=0 disables the split-K tail of the gradient GEMMs
+    int wide = 3;            // VPG_GEMM_WIDE bit mask: 256x512 tiles of CTA pairs in d_weight / plain GEMMs (1), d_hidden (2)
     int ds_tma = 1;          // VPG_DS_TMA=0: dlogits by per-lane global stores instead of smem + TMA tensor stores
     int hint_a[4] = {0, 0, 0, 0}, hint_b[4] = {0, 0, 0, 0};  // L2 eviction hints per kernel {FWD, DS, DH, DW}
 };
-static int env_int(const char* name, int dflt) {
-    const char* e = getenv(name);
-    return e ? atoi(e) : dflt;
-}
 static const Tuning& tuning() {
     static Tuning t = [] {
         Tuning t;
@@ -75,6 +72,7 @@ static const Tuning& tuning() {
         t.bwd_ws_mb = env_int("VPG_BWD_WS_MB", 4096);
         t.splitk = env_int("VPG_SPLITK", 1);
         t.ds_tma = env_int("VPG_DS_TMA", 1);
+        t.wide = env_int("VPG_GEMM_WIDE", 3);
         const char* tags[4] = {"FWD", "DS", "DH", "DW"};
         for (int i = 0; i < 4; ++i) {
             char name[32];
@@ -172,7 +170,25 @@ static int tile_m() { return kBlockM * cta_group(); }
 static int num_workers() { return cta_group() == 2 ? sm_count() / 2 : sm_count(); }
 static int b_tile_rows() { return kBlockN / cta_group(); }
 // fp32 scratch of the split-K tail of one gradient GEMM: at most one partial tile per worker
-static size_t splitk_scratch_bytes() { return static_cast<size_t>(num_workers()) * tile_m() * kBlockN * 4; }
+// Output-tile width of a MODE_GEMM launch with N columns: 512 (wide tiles, CTA pairs only) when that pads N no further
+// than 256-column tiles would, else 256.
+enum : int { WIDE_DW = 1, WIDE_DH = 2 };
+static int gemm_tile_n(int64_t N, int which = WIDE_DW) {
+    if (cta_group() == 2 && (tuning().wide & which) && round_up(N, 2 * kBlockN) == round_up(N, kBlockN)) return 2 * kBlockN;
+    return kBlockN;
+}
+// tiling fields of a plain GEMM with an M x N output (one tile per unit)
+static void set_gemm_tiling(TcParams& p, int64_t M, int64_t N, int which = WIDE_DW) {
+    const int tn = gemm_tile_n(N, which);
+    p.wide = tn > kBlockN ? 1 : 0;
+    p.num_m_tiles = static_cast<int>(ceil_div(M, tile_m()));
+    p.num_n_tiles = static_cast<int>(ceil_div(N, tn));
+    p.num_splits = p.num_n_tiles;
+    p.tiles_per_split = 1;
+    p.M = static_cast<int>(M);
+    p.N = static_cast<int>(N);
+}
+static size_t splitk_scratch_bytes() { return static_cast<size_t>(num_workers()) * tile_m() * (2 * kBlockN) * 4; }
 
 // Split-K plan of a MODE_GEMM launch on `workers` persistent workers: the tiles of the last, partial scheduling round
 // (tiles % workers of them) are cut into ksplit K ranges, so that round costs 1/ksplit of a tile time.
@@ -193,10 +209,11 @@ static void plan_splitk(TcParams& p, int workers, float* scratch) {
     p.splitk_ws = scratch;
 }
 
-template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
+template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false, bool kWide = false>
 static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream,
                         int timing_kind, const CUtensorMap* tc = nullptr) {
-    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG, kTf32>;
+    auto kern = tc_gemm_kernel<kMode, kAMn, kBMn, kCG, kTf32, kWide>;
+    constexpr int kTileN = kWide ? 2 * kBlockN : kBlockN;
     const Tuning& tn = tuning();
     TcParams p = p_in;
     const unsigned int id = next_launch_id();
@@ -245,10 +262,10 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
     }
     if (kMode == MODE_GEMM && p.ksplit > 1) {
         const int tail_tiles = static_cast<int>(tiles) - p.tiles_full;
-        const int64_t threads = static_cast<int64_t>(tail_tiles) * (kBlockM * kCG) * kBlockN / 4;
+        const int64_t threads = static_cast<int64_t>(tail_tiles) * (kBlockM * kCG) * kTileN / 4;
         TimingScope ts(TK_SPLITK, stream);
         splitk_reduce_kernel<<<static_cast<unsigned>(ceil_div(threads, 256)), 256, 0, stream>>>(
-            p.splitk_ws, tail_tiles, p.ksplit, p.tiles_full, p.num_n_tiles, kBlockM * kCG, p.M, p.N, p.out, p.ldc,
+            p.splitk_ws, tail_tiles, p.ksplit, p.tiles_full, p.num_n_tiles, kBlockM * kCG, kTileN, p.M, p.N, p.out, p.ldc,
             p.out_mode, p.accum, p.ld_accum, p.f16);
         VPG_LAUNCH_CHECK();
     }
@@ -258,6 +275,12 @@ static int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPa
 template <int kMode, bool kAMn, bool kBMn>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream,
                      int timing_kind, const CUtensorMap* tc = nullptr) {
+    if constexpr (kMode == MODE_GEMM) {
+        if (p.wide) {
+            if (cta_group() != 2) return set_error(VPG_ERR_INVALID, "wide GEMM tiles need CTA pairs");
+            return launch_tc_cg<kMode, kAMn, kBMn, 2, false, true>(ta, tb, p, stream, timing_kind, tc);
+        }
+    }
     if (cta_group() == 2) return launch_tc_cg<kMode, kAMn, kBMn, 2>(ta, tb, p, stream, timing_kind, tc);
     return launch_tc_cg<kMode, kAMn, kBMn, 1>(ta, tb, p, stream, timing_kind, tc);
 }
@@ -491,7 +514,9 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
     if (max_tiles < 1) max_tiles = 1;
     if (max_tiles > v_tiles) max_tiles = v_tiles;
     const int64_t W = num_workers(), tm = tile_m();
-    const int64_t m_t = ceil_div(t_pad, tm), n_h = ceil_div(H, kBlockN);
+    // a wide tile step costs `scale` 256-column steps
+    const int64_t tn_w = gemm_tile_n(H, WIDE_DW), tn_h = gemm_tile_n(H, WIDE_DH), sc_w = tn_w / kBlockN, sc_h = tn_h / kBlockN;
+    const int64_t m_t = ceil_div(t_pad, tm), n_w = ceil_div(H, tn_w), n_h = ceil_div(H, tn_h);
     const int64_t min_chunks = ceil_div(v_tiles, max_tiles);
     int64_t best_c = max_tiles;
     double best_cost = 1e300;
@@ -513,8 +538,8 @@ int64_t vpg_lce_bwd_chunk_for_budget(int64_t T, int64_t H, int64_t V, int64_t bu
         for (int64_t done = 0; done < v_tiles; done += c) {
             const int64_t ct = (v_tiles - done) < c ? (v_tiles - done) : c;  // tiles in this chunk
             cost += static_cast<double>(ceil_div(m_t * ct, W)) * (H / kBlockK);                  // dlogits
-            cost += rounds(ceil_div(ct * kBlockN, tm) * n_h) * (t_pad / kBlockK);                 // d_weight
-            cost += rounds(m_t * n_h) * (ct * kBlockN / kBlockK);                                 // d_hidden
+            cost += rounds(ceil_div(ct * kBlockN, tm) * n_w) * (t_pad / kBlockK) * sc_w;          // d_weight
+            cost += rounds(m_t * n_h) * (ct * kBlockN / kBlockK) * sc_h;                          // d_hidden
             cost += chunk_overhead;                                                               // launches, fp32 RMW
         }
         if (cost < best_cost) {
@@ -737,13 +762,8 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             int rc = 0;
             CUtensorMap ta, tb;
             TcParams p{};
-            p.num_m_tiles = static_cast<int>(ceil_div(vc, tile_m()));
-            p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
+            set_gemm_tiling(p, vc, H);
             p.num_k_blocks = static_cast<int>(t_pad / kBlockK);
-            p.num_splits = p.num_n_tiles;
-            p.tiles_per_split = 1;
-            p.M = static_cast<int>(vc);
-            p.N = static_cast<int>(H);
             uint8_t* dw = reinterpret_cast<uint8_t*>(a.d_weight) + v0 * H * gsz;
             p.ldc = H;
             if (!by_token || num_chunks == 1) {  // rows of this vocab chunk are final
@@ -782,13 +802,9 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             int rc = 0;
             CUtensorMap ta, tb;
             TcParams p{};
+            set_gemm_tiling(p, tn, H, WIDE_DH);
             p.num_m_tiles = m_tiles_t;
-            p.num_n_tiles = static_cast<int>(ceil_div(H, kBlockN));
             p.num_k_blocks = static_cast<int>(ceil_div(vc, kBlockK));
-            p.num_splits = p.num_n_tiles;
-            p.tiles_per_split = 1;
-            p.M = static_cast<int>(tn);
-            p.N = static_cast<int>(H);
             p.ldc = H;
             bool splitk_ok = true;
             if (d_hidden_mc_f32 && (by_token || last)) {
@@ -828,7 +844,7 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             // the SMs that GEMM can spare for free: the fewest workers with the same number of scheduling rounds
             if ((rc = run_d_hidden())) return rc;
             VPG_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(dh_ready_event), stream));
-            const int64_t tiles = ceil_div(vc, static_cast<int64_t>(tile_m())) * ceil_div(H, static_cast<int64_t>(kBlockN));
+            const int64_t tiles = ceil_div(vc, static_cast<int64_t>(tile_m())) * ceil_div(H, static_cast<int64_t>(gemm_tile_n(H)));
             const int64_t rounds = ceil_div(tiles, static_cast<int64_t>(num_workers()));
             int spare_cap = static_cast<int>(ceil_div(tiles, rounds));
             // at least this many CTA pairs are left to the collective (caller's choice; env override for tuning)
@@ -879,13 +895,8 @@ int vpg_gemm_bf16_ws(const void* A, const void* B, int64_t M, int64_t N, int64_t
                   "split-K workspace too small or misaligned (vpg_gemm_splitk_workspace_bytes)");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     TcParams p{};
-    p.num_m_tiles = static_cast<int>(ceil_div(M, tile_m()));
-    p.num_n_tiles = static_cast<int>(ceil_div(N, kBlockN));
+    set_gemm_tiling(p, M, N);
     p.num_k_blocks = static_cast<int>(ceil_div(K, kBlockK));
-    p.num_splits = p.num_n_tiles;
-    p.tiles_per_split = 1;
-    p.M = static_cast<int>(M);
-    p.N = static_cast<int>(N);
     p.out = C;
     p.ldc = ldc;
     p.out_mode = out_mode;

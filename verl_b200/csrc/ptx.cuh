@@ -321,7 +321,12 @@ __device__ __forceinline__ void multimem_red_add_v4f32(float* mc_addr, float a, 
                  "f"(c), "f"(d)
                  : "memory");
 }
-
+// fire-and-forget fp32 accumulation of four consecutive floats (16-byte aligned) in global memory: the L2 does the
+// read-modify-write, the issuing warp never waits for the old value
+__device__ __forceinline__ void red_add_v4f32(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
 
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

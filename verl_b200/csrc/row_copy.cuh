@@ -123,16 +123,17 @@ scatter_rows_gapfill_kernel(const U* __restrict__ src, const long long* __restri
 // store 4-byte units one by one behind a per-row map.  Here the output tile (tile_rows rows, <= 32 KB) is assembled in
 // shared memory — zeroed with 128-bit stores, the source rows of the tile dropped in by destination, then written out as
 // full 128-bit vectors — so every global access is coalesced and every output byte is still written exactly once.  The
-// start of a block's run is found by a block-wide 256-ary lower bound (4 probes rounds at 2^25 rows instead of 25
+// start of a block's run is found by a block-wide NT-ary lower bound (3-4 probe rounds at 2^25 rows instead of 25
 // dependent loads of one thread); the number of source rows a tile consumed is the sum of per-thread hit counts.
-__device__ __forceinline__ long long block_lower_bound_256(const long long* __restrict__ a, long long n, long long key) {
+template <int NT>
+__device__ __forceinline__ long long block_lower_bound(const long long* __restrict__ a, long long n, long long key) {
     long long lo = 0, hi = n;  // invariant: the answer lies in [lo, hi]; every thread holds the same pair
     while (lo < hi) {
-        const long long step = (hi - lo + 255) >> 8;
+        const long long step = (hi - lo + NT - 1) / NT;
         long long q = lo + (static_cast<long long>(threadIdx.x) + 1) * step - 1;
         if (q > hi - 1) q = hi - 1;
         const int c = __syncthreads_count(a[q] < key);  // probes ascend with threadIdx, so the predicate is a prefix
-        if (c == 256) return hi;
+        if (c == NT) return hi;
         const long long qc = lo + (static_cast<long long>(c) + 1) * step - 1;
         lo += static_cast<long long>(c) * step;
         hi = qc < hi - 1 ? qc : hi - 1;
@@ -140,8 +141,8 @@ __device__ __forceinline__ long long block_lower_bound_256(const long long* __re
     return lo;
 }
 
-template <typename U>
-__global__ void __launch_bounds__(256)
+template <typename U, int NT>
+__global__ void __launch_bounds__(NT)
 scatter_narrow_gapfill_kernel(const U* __restrict__ src, const long long* __restrict__ didx, long long n_rows,
                               long long n_out, int tile_rows, long long tiles_per_block, U* __restrict__ out) {
     extern __shared__ uint4 stage4[];
@@ -151,7 +152,7 @@ scatter_narrow_gapfill_kernel(const U* __restrict__ src, const long long* __rest
     const long long t_beg = static_cast<long long>(blockIdx.x) * tiles_per_block;
     const long long t_end = t_beg + tiles_per_block < n_tiles ? t_beg + tiles_per_block : n_tiles;
     if (t_beg >= t_end) return;
-    long long r_cur = block_lower_bound_256(didx, n_rows, t_beg * tile_rows);
+    long long r_cur = block_lower_bound<NT>(didx, n_rows, t_beg * tile_rows);
     if (threadIdx.x < 2) s_count[threadIdx.x] = 0;
     const int tile_vecs = static_cast<int>(static_cast<size_t>(tile_rows) * sizeof(U) / 16);
     const uint4 z4 = make_uint4(0, 0, 0, 0);
@@ -159,15 +160,15 @@ scatter_narrow_gapfill_kernel(const U* __restrict__ src, const long long* __rest
     for (long long t = t_beg; t < t_end; ++t, flip ^= 1) {
         const long long o0 = t * tile_rows;
         const int n_here = static_cast<int>((n_out - o0) < tile_rows ? (n_out - o0) : tile_rows);
-        for (int j = threadIdx.x; j < tile_vecs; j += 256) stage4[j] = z4;
+        for (int j = threadIdx.x; j < tile_vecs; j += NT) stage4[j] = z4;
         __syncthreads();
         int mine = 0;
-        for (int i0 = threadIdx.x; i0 < n_here; i0 += 1024) {  // ascending indices: at most n_here source rows land here
+        for (int i0 = threadIdx.x; i0 < n_here; i0 += 4 * NT) {  // ascending indices: at most n_here source rows land here
             long long d[4];
             U v[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const long long r = r_cur + i0 + k * 256;
+                const long long r = r_cur + i0 + k * NT;
                 const bool ok = r < n_rows;
                 d[k] = ok ? didx[r] - o0 : static_cast<long long>(n_here);
                 if (ok) v[k] = src[r];
@@ -184,8 +185,8 @@ scatter_narrow_gapfill_kernel(const U* __restrict__ src, const long long* __rest
         const size_t bytes_here = static_cast<size_t>(n_here) * sizeof(U);
         const int vecs_here = static_cast<int>(bytes_here / 16);
         uint4* o4 = reinterpret_cast<uint4*>(out + o0);
-        for (int j = threadIdx.x; j < vecs_here; j += 256) o4[j] = stage4[j];
-        for (int j = vecs_here * static_cast<int>(16 / sizeof(U)) + threadIdx.x; j < n_here; j += 256) out[o0 + j] = stage[j];
+        for (int j = threadIdx.x; j < vecs_here; j += NT) o4[j] = stage4[j];
+        for (int j = vecs_here * static_cast<int>(16 / sizeof(U)) + threadIdx.x; j < n_here; j += NT) out[o0 + j] = stage[j];
         __syncthreads();
         r_cur += count;
     }
@@ -227,11 +228,13 @@ static inline cudaError_t launch_scatter_rows_gapfill(const void* src, const lon
     const int u = row_copy_unit(src, out, row_bytes);
     const int64_t upr = row_bytes / u;
     if (upr == 1 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {  // narrow rows: shared-memory staged tiles
-        int64_t tile = (32 * 1024) / u;
+        static const int nt = env_int("VPG_PAD_NT", 256), tile_kb = env_int("VPG_PAD_TILE_KB", 16),
+                         bps = env_int("VPG_PAD_BPS", 6);  // measured best of the A/B in profiles/r2_ab_pad_input.jsonl
+        int64_t tile = (static_cast<int64_t>(tile_kb) * 1024) / u;
         if (tile > 8192) tile = 8192;
         const int64_t n_tiles = ceil_div(n_out, tile);
         int64_t g = n_tiles;
-        const int64_t cap = static_cast<int64_t>(sm_count()) * 6;
+        const int64_t cap = static_cast<int64_t>(sm_count()) * bps;
         if (g > cap) g = cap;
         if (g < 1) g = 1;
         const int64_t tpb = ceil_div(n_tiles, g);
@@ -239,13 +242,17 @@ static inline cudaError_t launch_scatter_rows_gapfill(const void* src, const lon
         const unsigned grid = static_cast<unsigned>(gr < 1 ? 1 : gr);
         const size_t smem = static_cast<size_t>(tile) * u;
         const int tr = static_cast<int>(tile);
+#define VPG_NARROW(U, NT) scatter_narrow_gapfill_kernel<U, NT><<<grid, NT, smem, stream>>>((const U*)src, didx, n_rows, n_out, tr, tpb, (U*)out)
+#define VPG_NARROW_NT(U) do { if (nt == 1024) VPG_NARROW(U, 1024); else if (nt == 512) VPG_NARROW(U, 512); else if (nt == 128) VPG_NARROW(U, 128); else VPG_NARROW(U, 256); } while (0)
         switch (u) {
-            case 16: scatter_narrow_gapfill_kernel<uint4><<<grid, 256, smem, stream>>>((const uint4*)src, didx, n_rows, n_out, tr, tpb, (uint4*)out); break;
-            case 8: scatter_narrow_gapfill_kernel<uint2><<<grid, 256, smem, stream>>>((const uint2*)src, didx, n_rows, n_out, tr, tpb, (uint2*)out); break;
-            case 4: scatter_narrow_gapfill_kernel<uint32_t><<<grid, 256, smem, stream>>>((const uint32_t*)src, didx, n_rows, n_out, tr, tpb, (uint32_t*)out); break;
-            case 2: scatter_narrow_gapfill_kernel<uint16_t><<<grid, 256, smem, stream>>>((const uint16_t*)src, didx, n_rows, n_out, tr, tpb, (uint16_t*)out); break;
-            default: scatter_narrow_gapfill_kernel<uint8_t><<<grid, 256, smem, stream>>>((const uint8_t*)src, didx, n_rows, n_out, tr, tpb, (uint8_t*)out); break;
+            case 16: VPG_NARROW_NT(uint4); break;
+            case 8: VPG_NARROW_NT(uint2); break;
+            case 4: VPG_NARROW_NT(uint32_t); break;
+            case 2: VPG_NARROW_NT(uint16_t); break;
+            default: VPG_NARROW_NT(uint8_t); break;
         }
+#undef VPG_NARROW_NT
+#undef VPG_NARROW
         return cudaGetLastError();
     }
     int lg = 0;

@@ -116,7 +116,8 @@ struct TcParams {
     // K ranges, each a unit that stores an fp32 partial tile into splitk_ws (summed by splitk_reduce_kernel)
     int tiles_full;
     int ksplit;
-    float* splitk_ws;         // [(tiles - tiles_full) * ksplit][kTileM * kBlockN]
+    float* splitk_ws;         // [(tiles - tiles_full) * ksplit][kTileM * tile_n]  (tile_n = 256, or 512 for wide tiles)
+    int wide;                 // host only: 1 = launch the 256 x 512 tile variant (num_n_tiles counts 512-column tiles)
     // ---- MODE_GEMM fused all-reduce (warp 11): sums the bf16 buffer behind the multicast address `ar_mc` over the
     // `ar_world` ranks in place (this rank reduces vectors [rank, rank+1) * ar_nvec / world and broadcasts them)
     int ar_world, ar_rank;
@@ -372,14 +373,10 @@ __device__ __forceinline__ void gemm_chunk(const TcParams& p, const uint32_t (&r
             for (int q4 = 0; q4 < 8; ++q4) {
                 float4 v = make_float4(__uint_as_float(r[q4 * 4 + 0]), __uint_as_float(r[q4 * 4 + 1]),
                                        __uint_as_float(r[q4 * 4 + 2]), __uint_as_float(r[q4 * 4 + 3]));
-                if (acc) {
-                    float4 a = o4[q4];
-                    v.x += a.x;
-                    v.y += a.y;
-                    v.z += a.z;
-                    v.w += a.w;
-                }
-                o4[q4] = v;
+                // accumulate: one writer per element and launch, so old + v is the same fp32 sum wherever it is formed;
+                // the reduction is issued and forgotten instead of a load the epilogue would have to wait for
+                if (acc) red_add_v4f32(o + q4 * 4, v.x, v.y, v.z, v.w);
+                else o4[q4] = v;
             }
         } else {
 #pragma unroll
@@ -606,16 +603,25 @@ __device__ __forceinline__ void allreduce_worker(const TcParams& p, int cta, int
 // TF32 (kind::tf32, 4 x K=8 per k-block instead of 4 x K=16) — K-major operands only (MODE_FWD / MODE_DS).
 constexpr int kArWarp = 11;
 
-template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false>
+// kWide (MODE_GEMM, kCG = 2 only): the pair computes a 256 x 512 tile — ONE 512-column TMEM accumulator (all of TMEM, so
+// the epilogue no longer overlaps the next tile's MMAs: < 0.5 % when K >= 16k), two N = 256 MMAs per k-step against two
+// 128-row groups of B per CTA.  Per flop the pair pulls 27 % fewer operand bytes from L2 (96 KB instead of 2 x 64 KB per
+// 256 x 512 x 64 block) and the A operand is re-streamed half as often; the step is power-capped, so bytes moved are time.
+template <int kMode, bool kAMn, bool kBMn, int kCG, bool kTf32 = false, bool kWide = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c /* MODE_DS: dlogits store map */,
                const __grid_constant__ TcParams p) {
     using Cfg = TileCfg<kCG>;
     static_assert(!kTf32 || (!kAMn && !kBMn), "TF32 operands are K-major only");
+    static_assert(!kWide || (kMode == MODE_GEMM && kCG == 2 && !kTf32), "wide tiles: plain 16-bit GEMM on CTA pairs");
     constexpr int kElemsK = kTf32 ? kBlockK / 2 : kBlockK;  // elements per 128-byte k-block row
-    constexpr int kStages = Cfg::kStages;
-    constexpr int kStageBytes = Cfg::kStageBytes;
+    constexpr int kGroups = kWide ? 2 : 1;                   // 256-column groups of the tile (one MMA each per k-step)
+    constexpr int kTileN = kBlockN * kGroups;
+    constexpr int kAccBufs = kWide ? 1 : 2;                  // TMEM accumulators in flight
+    constexpr int kStageBytes = kABytes + kGroups * Cfg::kBBytes;
+    constexpr int kStages = kWide ? 4 : Cfg::kStages;        // 4 x 48 KB = 6 x 32 KB: same shared-memory footprint
+    static_assert(kStages * kStageBytes <= Cfg::kStages * Cfg::kStageBytes, "wide stages must fit the same ring");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     SmemLayout L = carve_smem(smem_raw, kStages * kStageBytes);
     const int warp = threadIdx.x >> 5;
@@ -684,7 +690,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const Unit w = decode_unit<kMode>(p, u);
             const int m0 = w.m_tile * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
             for (int n = w.nb; n < w.ne; ++n) {
-                const int n0 = n * kBlockN + static_cast<int>(cta_rank) * Cfg::kBRows;
+                // group g of the tile: columns [g*256, g*256+256), of which this CTA stages rows cta_rank*kBRows.. (the
+                // MMA of group g reads the halves of both CTAs), so TMEM column c is tile column c
+                const int n0 = n * kTileN + static_cast<int>(cta_rank) * Cfg::kBRows;
                 for (int kb = w.kb0; kb < w.kb1; ++kb, ++kb_total) {
                     if (pace && (kb_total % kPaceKBlocks) == 0)
                         pace = pace_wait(progress, worker, num_workers, epoch, kb_total / kPaceKBlocks, p.sync_slack, lane);
@@ -718,12 +726,17 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 for (int j = 0; j < kBlockM / 64; ++j)
                                     tma_load_2d_2sm_hint(&tmap_a, full_leader, sa + j * 8192, m0 + j * 64, kb * kBlockK, hint_a);
                             }
-                            if (!kBMn) {
-                                tma_load_2d_2sm_hint(&tmap_b, full_leader, sb, kb * kElemsK, n0, hint_b);
-                            } else {
 #pragma unroll
-                                for (int j = 0; j < Cfg::kBRows / 64; ++j)
-                                    tma_load_2d_2sm_hint(&tmap_b, full_leader, sb + j * 8192, n0 + j * 64, kb * kBlockK, hint_b);
+                            for (int g = 0; g < kGroups; ++g) {
+                                uint8_t* sbg = sb + g * Cfg::kBBytes;
+                                const int ng = n0 + g * kBlockN;
+                                if (!kBMn) {
+                                    tma_load_2d_2sm_hint(&tmap_b, full_leader, sbg, kb * kElemsK, ng, hint_b);
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < Cfg::kBRows / 64; ++j)
+                                        tma_load_2d_2sm_hint(&tmap_b, full_leader, sbg + j * 8192, ng + j * 64, kb * kBlockK, hint_b);
+                                }
                             }
                         }
                     }
@@ -759,11 +772,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         (static_cast<unsigned long long>(u) << 32) | static_cast<unsigned>(n);
                 }
 #endif
-                const uint32_t buf = acc_iter & 1u;
-                const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+                const uint32_t buf = acc_iter % kAccBufs;
+                const uint32_t acc_phase = (acc_iter / kAccBufs) & 1u;
                 mbar_wait(&L.tmem_empty[buf], acc_phase ^ 1);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + buf * kBlockN;
+                const uint32_t d_tmem = tmem_base + buf * kTileN;
                 for (int kb = w.kb0; kb < w.kb1; ++kb) {
                     mbar_wait(&L.full[stage], phase);
                     tc_fence_after();
@@ -778,10 +791,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             // advance the 14-bit start-address field (units of 16 B)
                             const uint64_t a_adv = kAMn ? (k * 2048) >> 4 : (k * 32) >> 4;
                             const uint64_t b_adv = kBMn ? (k * 2048) >> 4 : (k * 32) >> 4;
-                            if constexpr (kTf32)
+                            if constexpr (kTf32) {
                                 umma_tf32<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (first | k) != 0 ? 1u : 0u);
-                            else
-                                umma_bf16<kCG>(d_tmem, adesc + a_adv, bdesc + b_adv, idesc, (first | k) != 0 ? 1u : 0u);
+                            } else {
+#pragma unroll
+                                for (int g = 0; g < kGroups; ++g)  // group g: B rows at +g*kBBytes, TMEM columns +g*256
+                                    umma_bf16<kCG>(d_tmem + g * kBlockN, adesc + a_adv,
+                                                   bdesc + b_adv + ((static_cast<uint64_t>(g) * Cfg::kBBytes) >> 4), idesc,
+                                                   (first | k) != 0 ? 1u : 0u);
+                            }
                         }
                         // frees the smem slot (in both CTAs) once these MMAs retire
                         if (kCG == 1) umma_commit(&L.empty[stage]); else umma_commit_2sm(&L.empty[stage], 3);
@@ -801,7 +819,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // ===================================================================== epilogue (every CTA, own 128 rows)
         const int ew = warp - kEpiWarp0;  // 0..7
         const int quarter = warp & 3;     // TMEM lane quarter this warp may access
-        const int half = ew >> 2;         // column half: 0 -> [0,128), 1 -> [128,256)
+        const int half = ew >> 2;         // column half of the tile: 0 -> [0, kTileN/2), 1 -> [kTileN/2, kTileN)
+        constexpr int kHalfCols = kTileN / 2;
+        constexpr int kChunks = kHalfCols / 32;
         const int row_in_tile = quarter * 32 + lane;
         const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
         const float c = p.scale_log2;
@@ -845,16 +865,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             // split-K unit: this thread's row of the unit's fp32 partial tile
             float* part_row = nullptr;
             if (kMode == MODE_GEMM && w.part >= 0)
-                part_row = p.splitk_ws + static_cast<long long>(w.part) * (Cfg::kTileM * kBlockN) +
-                           (static_cast<int>(cta_rank) * kBlockM + row_in_tile) * kBlockN + half * 128;
+                part_row = p.splitk_ws + static_cast<long long>(w.part) * (Cfg::kTileM * kTileN) +
+                           (static_cast<int>(cta_rank) * kBlockM + row_in_tile) * kTileN + half * kHalfCols;
 
             for (int n = w.nb; n < w.ne; ++n, ++acc_iter) {
-                const uint32_t buf = acc_iter & 1u;
-                const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+                const uint32_t buf = acc_iter % kAccBufs;
+                const uint32_t acc_phase = (acc_iter / kAccBufs) & 1u;
                 mbar_wait(&L.tmem_full[buf], acc_phase);
                 tc_fence_after();
-                const int col0 = n * kBlockN + half * 128;
-                const uint32_t taddr = tmem_base + t_lane + buf * kBlockN + half * 128;
+                const int col0 = n * kTileN + half * kHalfCols;
+                const uint32_t taddr = tmem_base + t_lane + buf * kTileN + half * kHalfCols;
                 uint32_t ra[32], rb[32];
 #ifdef VPG_DEBUG_TOOLS
                 const bool skip_epilogue = (kMode == MODE_GEMM) && p.out_mode == OUT_DEBUG_SKIP;  // profiling only
@@ -863,7 +883,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #endif
                 if (!skip_epilogue) tmem_ld_32x32(taddr, ra);
 #pragma unroll
-                for (int cc = 0; cc < 4 && !skip_epilogue; cc += 2) {
+                for (int cc = 0; cc < kChunks && !skip_epilogue; cc += 2) {
                     tmem_ld_wait_dep(ra);
                     tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
                     {
@@ -886,7 +906,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         }
                     }
                     tmem_ld_wait_dep(rb);
-                    if (cc + 2 < 4) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
+                    if (cc + 2 < kChunks) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
                     {
                         const int cb = col0 + (cc + 1) * 32;
                         const int n_valid = p.N - cb;
@@ -977,23 +997,23 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // Sums the `ksplit` fp32 partial tiles of every tail tile in a fixed order (deterministic) and applies the launch's
 // output mode.  One thread per 4 consecutive columns.  HBM-bound: ksplit * 256 KB read per tile, a few tiles per launch.
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int tail_tiles, int ksplit, int tile0,
-                                     int num_n_tiles, int tile_m, int M, int N, void* out, long long ldc, int out_mode,
-                                     const float* accum, long long ld_accum, int f16) {
-    const int per_tile = tile_m * kBlockN / 4;
+                                     int num_n_tiles, int tile_m, int tile_n, int M, int N, void* out, long long ldc,
+                                     int out_mode, const float* accum, long long ld_accum, int f16) {
+    const int per_tile = tile_m * tile_n / 4;
     const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (gid >= static_cast<long long>(tail_tiles) * per_tile) return;
     const int tt = static_cast<int>(gid / per_tile);
     const int e = static_cast<int>(gid - static_cast<long long>(tt) * per_tile);
-    const int r = e / (kBlockN / 4), c4 = (e - r * (kBlockN / 4)) * 4;
+    const int r = e / (tile_n / 4), c4 = (e - r * (tile_n / 4)) * 4;
     const int t = tile0 + tt;
     const int m_tile = t / num_n_tiles, n_tile = t - m_tile * num_n_tiles;
     const long long row = static_cast<long long>(m_tile) * tile_m + r;
-    const int col = n_tile * kBlockN + c4;
+    const int col = n_tile * tile_n + c4;
     if (row >= M || col >= N) return;
-    const float* src = ws + (static_cast<long long>(tt) * ksplit) * (tile_m * kBlockN) + r * kBlockN + c4;
+    const float* src = ws + (static_cast<long long>(tt) * ksplit) * (tile_m * tile_n) + r * tile_n + c4;
     float4 a = *reinterpret_cast<const float4*>(src);
     for (int k = 1; k < ksplit; ++k) {
-        const float4 b = *reinterpret_cast<const float4*>(src + static_cast<long long>(k) * (tile_m * kBlockN));
+        const float4 b = *reinterpret_cast<const float4*>(src + static_cast<long long>(k) * (tile_m * tile_n));
         a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
     }
     float v[4] = {a.x, a.y, a.z, a.w};
