@@ -63,38 +63,59 @@ outcome_group_kernel(int kind, const double* __restrict__ scores, const double* 
     __shared__ double bc[4];
     // pass 1: count / sum (+ length-weighted sums, + group arg-max).  Scores are rounded to fp32 first: the reference
     // holds them in an fp32 tensor.
+    // Sums per group are warp-shuffle segmented reductions: `__match_any_sync` on the group id yields the lanes of a
+    // warp's 32 consecutive rows that share a group, the partial is summed over that set in lane order and its lowest
+    // lane issues one atomic per (warp, group) and quantity.
     double nnz_local = 0.0;
-    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
-        const int g = gid[i];
-        const float sf = static_cast<float>(scores[i]);
-        const double s = static_cast<double>(sf);
-        atomicAdd(&gstat[kGStat * g + 0], 1.0);
-        atomicAdd(&gstat[kGStat * g + 1], s);
-        if (kind == VPG_ADV_OPO) {
-            const double len = lens[i];
-            atomicAdd(&gstat[kGStat * g + 3], len);
-            // fp32 product as in (len_tensor * score_tensor), core_algos.py:522
-            atomicAdd(&gstat[kGStat * g + 4], static_cast<double>(static_cast<float>(len) * sf));
+    const int lane = threadIdx.x & 31;
+    for (long long r0 = threadIdx.x - lane; r0 < B; r0 += blockDim.x) {
+        const long long i = r0 + lane;
+        const bool ok = i < B;
+        const int g = ok ? gid[i] : -1;
+        const float sf = ok ? static_cast<float>(scores[i]) : 0.f;
+        const double len = (ok && kind == VPG_ADV_OPO) ? lens[i] : 0.0;
+        const unsigned peers = __match_any_sync(0xffffffffu, g);
+        const bool lead = ok && lane == __ffs(peers) - 1;
+        const double sum = segment_sum(static_cast<double>(sf), peers);
+        if (lead) {
+            atomicAdd(&gstat[kGStat * g + 0], static_cast<double>(__popc(peers)));
+            atomicAdd(&gstat[kGStat * g + 1], sum);
         }
-        if (kind == VPG_ADV_GRPO_PASSK) {
+        if (kind == VPG_ADV_OPO) {
+            const double sl = segment_sum(len, peers);
+            // fp32 product as in (len_tensor * score_tensor), core_algos.py:522
+            const double slw = segment_sum(static_cast<double>(static_cast<float>(len) * sf), peers);
+            if (lead) {
+                atomicAdd(&gstat[kGStat * g + 3], sl);
+                atomicAdd(&gstat[kGStat * g + 4], slw);
+            }
+        }
+        if (ok && kind == VPG_ADV_GRPO_PASSK) {
             const unsigned long long key = (static_cast<unsigned long long>(float_key(sf)) << 32) |
                                            static_cast<unsigned long long>(0xffffffffu - static_cast<unsigned int>(i));
             atomicMax(&top[g], key);
         }
-        if (sf != 0.f) nnz_local += 1.0;
+        if (ok && sf != 0.f) nnz_local += 1.0;
     }
     __syncthreads();
     const double nnz = block_sum<double>(nnz_local, red);
     if (threadIdx.x == 0) bc[0] = nnz;
     // pass 2: squared deviations from the group mean (+ runner-up for pass@k)
-    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
-        const int g = gid[i];
-        const double n = gstat[kGStat * g + 0];
-        const double mean = gstat[kGStat * g + 1] / n;
-        const float sf = static_cast<float>(scores[i]);
-        const double d = static_cast<double>(sf) - mean;
-        atomicAdd(&gstat[kGStat * g + 2], d * d);
-        if (kind == VPG_ADV_GRPO_PASSK) {
+    for (long long r0 = threadIdx.x - lane; r0 < B; r0 += blockDim.x) {
+        const long long i = r0 + lane;
+        const bool ok = i < B;
+        const int g = ok ? gid[i] : -1;
+        double d = 0.0, n = 0.0;
+        float sf = 0.f;
+        if (ok) {
+            n = gstat[kGStat * g + 0];
+            sf = static_cast<float>(scores[i]);
+            d = static_cast<double>(sf) - gstat[kGStat * g + 1] / n;
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, g);
+        const double sq = segment_sum(d * d, peers);
+        if (ok && lane == __ffs(peers) - 1) atomicAdd(&gstat[kGStat * g + 2], sq);
+        if (ok && kind == VPG_ADV_GRPO_PASSK) {
             const unsigned int arg = 0xffffffffu - static_cast<unsigned int>(top[g] & 0xffffffffull);
             if (static_cast<unsigned int>(i) != arg) {
                 const unsigned long long key = (static_cast<unsigned long long>(float_key(sf)) << 32) |

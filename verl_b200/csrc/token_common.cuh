@@ -112,4 +112,16 @@ static inline cudaError_t publish_whiten_status(const double* sums, int* status,
     return e;
 }
 
+// Warp-shuffle segmented reduction: sum of `v` over the lanes in `peers` (the lane set `__match_any_sync` returned for this
+// lane's key), accumulated in lane order so the result does not depend on which lane asks.  All 32 lanes must call.
+__device__ __forceinline__ double segment_sum(double v, unsigned peers) {
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const double o = __shfl_sync(0xffffffffu, v, j);
+        if ((peers >> j) & 1u) acc += o;
+    }
+    return acc;
+}
+
 }  // namespace vpg

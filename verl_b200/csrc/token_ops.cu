@@ -7,6 +7,7 @@
 // quantity.  Scalars that depend on a global sum (token-mean normaliser) are produced by a first, mask-only pass;
 // the "last block done" pattern folds the tiny finalisation into the same launch.  Compiled with --fmad=false so
 // that elementwise results follow the reference's separately rounded fp32 operations.
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include "token_common.cuh"
@@ -453,37 +454,74 @@ __global__ void row_score_kernel(const float* __restrict__ rewards, long long L,
     if (threadIdx.x == 0) atomicAdd(&scores[b], bs);
 }
 
-// single block: group statistics and the per-row scalar advantage (written as float into adv_row[B])
-__global__ void grpo_group_kernel(const double* __restrict__ scores, const int* __restrict__ gid, long long B,
-                                  long long G, float eps, int norm_by_std, double* __restrict__ gstat,
-                                  float* __restrict__ adv_row) {
+// Group statistics and the per-row scalar advantage (written as float into adv_row[B]).
+// Warp-shuffle SEGMENTED reduction over uid groups: a warp takes 32 consecutive rows, `__match_any_sync` on the group id
+// gives every lane the set of lanes of its group (contiguous runs of the n rollouts of a prompt in practice, any
+// arrangement in general), the per-group partial is summed over that lane set in lane order with shuffles, and the lowest
+// lane of each set issues ONE double atomic per (warp, group) instead of one per row.  Two sweeps like the reference's
+// torch.mean / torch.std (sum, then squared deviations from the group mean); the phases are separated by a block barrier
+// (one block: up to kGroupRowsPerBlock rows) or a cooperative grid barrier (larger batches: one block per kGroupRowsPerBlock
+// rows, at most one per SM, launched cooperatively).
+constexpr int kGroupThreads = 1024;
+constexpr int kGroupRowsPerBlock = 4096;
+
+template <bool kMultiBlock>
+__global__ void __launch_bounds__(kGroupThreads)
+grpo_group_kernel(const double* __restrict__ scores, const int* __restrict__ gid, long long B, long long G, float eps,
+                  int norm_by_std, double* __restrict__ gstat, float* __restrict__ adv_row) {
+    namespace cg = cooperative_groups;
+    const int lane = threadIdx.x & 31;
+    const long long first = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) - lane;  // row of lane 0
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    auto phase_barrier = [&]() {
+        if (kMultiBlock) {
+            __threadfence();
+            cg::this_grid().sync();
+        } else {
+            __syncthreads();
+        }
+    };
     // pass 1: count and sum (scores are rounded to fp32 first: the reference holds them in an fp32 tensor)
-    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
-        const int g = gid[i];
-        const double s = static_cast<double>(static_cast<float>(scores[i]));
-        atomicAdd(&gstat[3 * g + 0], 1.0);
-        atomicAdd(&gstat[3 * g + 1], s);
+    for (long long r0 = first; r0 < B; r0 += stride) {
+        const long long i = r0 + lane;
+        const bool ok = i < B;
+        const int g = ok ? gid[i] : -1;
+        const double s = ok ? static_cast<double>(static_cast<float>(scores[i])) : 0.0;
+        const unsigned peers = __match_any_sync(0xffffffffu, g);
+        const double sum = segment_sum(s, peers);
+        if (ok && lane == __ffs(peers) - 1) {
+            atomicAdd(&gstat[3 * g + 0], static_cast<double>(__popc(peers)));
+            atomicAdd(&gstat[3 * g + 1], sum);
+        }
     }
-    __syncthreads();
+    phase_barrier();
     // pass 2: squared deviations from the group mean
-    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
-        const int g = gid[i];
-        const double n = gstat[3 * g + 0];
-        const double mean = gstat[3 * g + 1] / n;
-        const double d = static_cast<double>(static_cast<float>(scores[i])) - mean;
-        atomicAdd(&gstat[3 * g + 2], d * d);
+    for (long long r0 = first; r0 < B; r0 += stride) {
+        const long long i = r0 + lane;
+        const bool ok = i < B;
+        const int g = ok ? gid[i] : -1;
+        double d = 0.0;
+        if (ok) {
+            const double n = __ldcg(&gstat[3 * g + 0]);
+            d = static_cast<double>(static_cast<float>(scores[i])) - __ldcg(&gstat[3 * g + 1]) / n;
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, g);
+        const double sq = segment_sum(d * d, peers);
+        if (ok && lane == __ffs(peers) - 1) atomicAdd(&gstat[3 * g + 2], sq);
     }
-    __syncthreads();
-    for (long long i = threadIdx.x; i < B; i += blockDim.x) {
+    phase_barrier();
+    for (long long r0 = first; r0 < B; r0 += stride) {
+        const long long i = r0 + lane;
+        if (i >= B) continue;
         const int g = gid[i];
-        const double n = gstat[3 * g + 0];
+        const double n = __ldcg(&gstat[3 * g + 0]);
         float mean, stdv;
         if (n <= 1.0) {  // singleton group: mean 0, std 1 (core_algos.py:293-295)
             mean = 0.f;
             stdv = 1.f;
         } else {
-            mean = static_cast<float>(gstat[3 * g + 1] / n);
-            stdv = static_cast<float>(sqrt(gstat[3 * g + 2] / (n - 1.0)));  // unbiased, torch.std
+            mean = static_cast<float>(__ldcg(&gstat[3 * g + 1]) / n);
+            stdv = static_cast<float>(sqrt(__ldcg(&gstat[3 * g + 2]) / (n - 1.0)));  // unbiased, torch.std
         }
         const float sc = static_cast<float>(scores[i]);
         adv_row[i] = norm_by_std ? (sc - mean) / (stdv + eps) : (sc - mean);
@@ -938,8 +976,26 @@ int vpg_grpo_advantage(const float* rewards, const void* mask, int mask_dtype, c
     else
         row_score_kernel<1, float><<<grid, kThreads, 0, stream>>>(rewards, L, gx, scores);
     count_launch();
-    grpo_group_kernel<<<1, 1024, 0, stream>>>(scores, group_ids, B, G, epsilon, norm_by_std, gstat, adv_row);
-    count_launch();
+    {
+        int64_t blocks = ceil_div(B, kGroupRowsPerBlock);
+        if (blocks > sm_count()) blocks = sm_count();
+        if (blocks <= 1) {
+            grpo_group_kernel<false><<<1, kGroupThreads, 0, stream>>>(scores, group_ids, B, G, epsilon, norm_by_std, gstat,
+                                                                      adv_row);
+        } else {  // grid barrier between the sweeps: every block must be resident -> cooperative launch
+            const double* a0 = scores;
+            const int* a1 = group_ids;
+            long long a2 = B, a3 = G;
+            float a4 = epsilon;
+            int a5 = norm_by_std;
+            double* a6 = gstat;
+            float* a7 = adv_row;
+            void* kargs[] = {&a0, &a1, &a2, &a3, &a4, &a5, &a6, &a7};
+            VPG_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(grpo_group_kernel<true>),
+                                                 dim3(static_cast<unsigned>(blocks)), dim3(kGroupThreads), kargs, 0, stream));
+        }
+        count_launch();
+    }
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         if (vec)
