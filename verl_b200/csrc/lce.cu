@@ -295,11 +295,23 @@ static int launch_tc_lmhead(const CUtensorMap& ta, const CUtensorMap& tb, TcPara
     return launch_tc_cg<kMode, false, false, 1, true>(ta, tb, p, stream, tk, tc);
 }
 
-// balance-driven choice of the number of vocab splits per token tile (static round-robin schedule simulated)
-static int choose_splits(int num_m_tiles, int num_n_tiles, int grid) {
+// Choice of the number of vocab splits per token tile (a unit = token tile x one split's run of vocab tiles, dealt
+// round-robin to the persistent workers).  Cost of a split count s, in milliseconds:
+//   * the static schedule itself, simulated: the most loaded worker's vocab tiles x the time of one tile step;
+//   * DRAM traffic, which is time because the step is power-capped (~0.1 ms per GB, from the split sweeps in
+//     profiles/r2_sweep_fwd_splits.jsonl): the weight shard streams through L2 once per round of grid/s token tiles
+//     (traffic grows with s), and the grid/s token tiles in flight (tile_m x H each) are re-fetched for every vocab tile
+//     once they no longer fit beside those streams (~48 MB; traffic grows as s falls).  Qwen2.5-7B (H = 3584): 4 splits,
+//     17 GB; Llama-3-70B (H = 8192): 6-8 splits (4 splits: 111.1 ms, 8 splits: 106.7 ms for the forward).
+// `row_bytes` = bytes of one operand row (H x element size); 0 keeps the balance-only choice.
+static int choose_splits(int num_m_tiles, int num_n_tiles, int grid, int64_t row_bytes = 0) {
     int best_s = 1;
     double best_cost = 1e30;
     const int max_s = num_n_tiles < 64 ? num_n_tiles : 64;
+    // one 256-column tile step of one worker at the sustained rate (2 * tile_m * 256 * K flops; K = row_bytes / 2)
+    const double tile_ms = row_bytes > 0 ? 2.0 * tile_m() * kBlockN * (row_bytes / 2.0) / (1.4e15 / num_workers()) * 1e3 : 1.0;
+    const double w_gb = static_cast<double>(num_n_tiles) * kBlockN * row_bytes / 1e9;
+    const double a_tile_gb = static_cast<double>(tile_m()) * row_bytes / 1e9;
     for (int s = 1; s <= max_s; ++s) {
         const int tps = (num_n_tiles + s - 1) / s;
         const int s_eff = (num_n_tiles + tps - 1) / tps;  // non-empty splits
@@ -314,8 +326,18 @@ static int choose_splits(int num_m_tiles, int num_n_tiles, int grid) {
             for (int64_t u = cta; u < units; u += g) load += ((u % s) == s - 1) ? last : tps;
             if (load > worst) worst = load;
         }
-        // mild preference for >= 4 concurrent vocab streams (L2 reuse of the token tile) and fewer partials
-        double cost = static_cast<double>(worst) * (1.0 + 0.002 * s) * (s < 4 && num_m_tiles * s >= grid ? 1.03 : 1.0);
+        double cost;
+        if (row_bytes > 0) {
+            const double in_flight = static_cast<double>(ceil_div(g, s) < num_m_tiles ? ceil_div(g, s) : num_m_tiles);
+            const double rounds = static_cast<double>(num_m_tiles) / in_flight;       // sweeps of the weight shard
+            const double foot_mb = in_flight * a_tile_gb * 1e9 / 1048576.0;
+            const double thrash = foot_mb > 48.0 ? 1.0 - 48.0 / foot_mb : 0.0;          // share of token-tile reads that miss
+            const double dram_gb = w_gb * rounds + num_m_tiles * a_tile_gb * (1.0 + thrash * (tps - 1));
+            cost = static_cast<double>(worst) * tile_ms * (1.0 + 0.002 * s) + 0.1 * dram_gb;
+        } else {
+            // mild preference for >= 4 concurrent vocab streams (L2 reuse of the token tile) and fewer partials
+            cost = static_cast<double>(worst) * (1.0 + 0.002 * s) * (s < 4 && num_m_tiles * s >= grid ? 1.03 : 1.0);
+        }
         if (cost < best_cost) {
             best_cost = cost;
             best_s = s;
@@ -415,7 +437,7 @@ int vpg_lce_num_splits(int64_t T, int64_t H, int64_t V, int sm) {
     if (T <= 0 || V <= 0) return 1;
     if (sm <= 0) sm = sm_count();
     const int workers = cta_group() == 2 ? sm / 2 : sm;
-    return choose_splits(static_cast<int>(ceil_div(T, tile_m())), static_cast<int>(ceil_div(V, kBlockN)), workers);
+    return choose_splits(static_cast<int>(ceil_div(T, tile_m())), static_cast<int>(ceil_div(V, kBlockN)), workers, H * 2);
 }
 
 int vpg_lce_fwd_partials(const void* hidden, const void* weight, const int64_t* labels, int64_t T, int64_t H,
@@ -735,7 +757,7 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
             p.num_m_tiles = m_tiles_t;
             p.num_n_tiles = n_tiles_c;
             p.num_k_blocks = static_cast<int>(H / (f32 ? kBlockK / 2 : kBlockK));
-            p.num_splits = choose_splits(m_tiles_t, n_tiles_c, num_workers());
+            p.num_splits = choose_splits(m_tiles_t, n_tiles_c, num_workers(), H * esz);
             p.tiles_per_split = static_cast<int>(ceil_div(n_tiles_c, p.num_splits));
             p.M = static_cast<int>(tn);
             p.N = static_cast<int>(vc);
