@@ -9,7 +9,7 @@ for f in sys.argv[1:]:
             if "ms_per_step" not in d:
                 print(f, json.dumps(d)[:400]); continue
             rk = {k: round(v["ms_per_step"], 2) for k, v in (d.get("roofline_kernels") or {}).items()}
-            seg = {k: round(v, 2) for k, v in ((d.get("roofline_step") or {}).get("segments_ms") or {}).items()}
+            seg = {k: (round(v, 2) if v is not None else None) for k, v in ((d.get("roofline_step") or {}).get("segments_ms") or {}).items()}
             mem = d.get("memory") or {}
             print(f"{f}: N={d['n_gpus']} {d['ms_per_step']:.2f} ms/step {d['value']:.0f} tok/s e2e {d['e2e']['ms_per_step']:.2f} ms "
                   f"reduce={d.get('tp_reduce')} parity={(d.get('parity') or {}).get('ok')} chunks={mem.get('bwd_chunks')} "
