@@ -1,7 +1,7 @@
 set -x
 mkdir -p gpurun_out
 N=${N:-8}
-TAG=${TAG:-r2g}
+TAG=${TAG:-r2r}
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 timeout 300 $TR --master-port 29511 scripts/tp_check.py --time > gpurun_out/${TAG}_tp${N}_check.log 2>&1; echo "tp_check rc=$?" | tee -a gpurun_out/${TAG}_tp${N}_check.log
 timeout 600 python -m pytest tests/test_tp_gpu.py -m gpu -q > gpurun_out/${TAG}_tp${N}_pytest.log 2>&1; echo "pytest tp rc=$?" | tee -a gpurun_out/${TAG}_tp${N}_pytest.log
