@@ -73,13 +73,13 @@ def ops_table(d, B, L, n_uid):
         ("ppo_loss fwd+grad (clip + entropy + low_var_kl, token-mean)",
          lambda: ops.ppo_loss(d["old"], d["lp"], d["adv"], d["mask"], cliprange_low=0.2, cliprange_high=0.28,
                               entropy=d["ent"], entropy_coeff=1e-3, ref_log_prob=d["ref"], kl_loss_coef=0.01),
-         n * (8 + 8 + 4 * 5 + 4 * 2)),  # mask twice, old/lp/adv/ent/ref, d_lp/d_ent
+         n * (8 + 4 * 5 + 4 * 2)),  # SURVEY 8(d) floor: mask once, old/lp/adv/ent/ref, d_lp/d_ent (the kernels move 38)
         ("ppo_loss fwd only (vanilla)",
          lambda: ops.ppo_loss(d["old"], d["lp"], d["adv"], d["mask"], cliprange_low=0.2, cliprange_high=0.2,
                               want_grad=False),
-         n * (8 + 8 + 12)),
+         n * (8 + 12)),
         ("agg_loss token-mean (masked_mean)", lambda: ops.agg_loss_fwd(d["ent"], d["mask"], "token-mean", False),
-         n * (8 + 8 + 4)),
+         n * (8 + 4)),
         ("masked_sum", lambda: ops.masked_sums(d["ent"], d["mask"]), n * 12),
         ("kl_penalty low_var_kl", lambda: ops.kl_penalty_fwd(d["lp"], d["ref"], "low_var_kl", False), n * 12),
         ("grpo_advantage", lambda: ops.grpo_advantage(d["rewards"], d["mask"], gids, ng, 1e-6, True), n * 16),
@@ -91,7 +91,7 @@ def ops_table(d, B, L, n_uid):
          n * (12 + 4 + 12 + 4)),
         ("remax (reverse cumsum)", lambda: ops.remax(d["rewards"], d["lens"].float(), d["mask"]), n * (12 + 8)),
         ("value_loss fwd+grad", lambda: ops.value_loss(d["values"], d["lp"], d["old"], d["mask"], 0.2, "token-mean", True),
-         n * (8 + 8 + 12 + 4)),
+         n * (8 + 12 + 4)),
         ("kl_reward (apply_kl_penalty)", lambda: ops.kl_reward(d["rewards"], d["old"], d["ref"], d["mask"], "kl", 0.01),
          n * (8 + 12 + 4)),
         ("data_metrics (compute_data_metrics sweep)",

@@ -34,9 +34,11 @@ def main():
             hi = fwd_idx[which + 1] if which + 1 < len(fwd_idx) else len(ev)
         rows.append((r["rank"], ev[lo:hi]))
         t0 = ev[lo]["ts_us"] if t0 is None else min(t0, ev[lo]["ts_us"])
-    print(f"config {ranks[0]['config']} world {ranks[0]['world']} tp_reduce {ranks[0]['tp_reduce']}; times in ms from the "
-          f"earliest forward start of the step")
+    print(f"config {ranks[0]['config']} world {ranks[0]['world']} tp_reduce {ranks[0]['tp_reduce']}; times in ms from each "
+          f"rank's own forward start (CUPTI clocks of different processes are not aligned to better than the profiler's "
+          f"per-process start, so cross-rank offsets are not shown)")
     for rank, ev in rows:
+        t0 = ev[0]["ts_us"]
         print(f"-- rank {rank}")
         prev_end = None
         busy = 0.0
