@@ -8,6 +8,12 @@ oracle/_ref) on this GPU, unmodified, in one of two modes:
                      rtol 4e-2 against three PyTorch implementations, 5 shapes) judge the tcgen05 kernels.
 
     python scripts/run_ref_lce_test.py --mode ours
+    torchrun --nproc-per-node 2 --master-addr 127.0.0.1 scripts/run_ref_lce_test.py --mode ours --tp
+
+--tp runs the reference's TENSOR-PARALLEL test script (tests/utils/test_linear_cross_entropy_tp.py) instead: every rank
+holds its own vocab shard, the sharded op is compared with PyTorch on the all-gathered weight (logprobs / entropy atol 1e-1
+rtol 1e-2 as the script states them, grads atol 2e-2 rtol 4e-2), d_hidden all-reduced by the script itself.  With
+VPG_TP_EXCHANGE=nvlink the forward's exchange is the NVLink-fused one (symmetric buffers created collectively on first use).
 """
 import argparse
 import os
@@ -27,7 +33,13 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mode", choices=["reference", "ours"], required=True)
+    ap.add_argument("--tp", action="store_true", help="the reference's tensor-parallel test script (run under torchrun)")
     args = ap.parse_args()
+    if args.tp:
+        import torch
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
     from oracle import ref_import
 
     ref_import.load()  # verl, verl.utils, verl.utils.torch_functional, verl.utils.experimental.* from the snapshot
@@ -46,7 +58,8 @@ def main():
         sys.modules["verl.utils.kernel.linear_cross_entropy"] = lce
         pkg.kernels, pkg.linear_cross_entropy = k, lce
         sys.modules["verl.utils"].kernel = pkg
-    script = os.path.join(ref_import.REFERENCE_ROOT, "tests", "utils", "test_linear_cross_entropy.py")
+    script = os.path.join(ref_import.REFERENCE_ROOT, "tests", "utils",
+                          "test_linear_cross_entropy_tp.py" if args.tp else "test_linear_cross_entropy.py")
     print(f"[run_ref_lce_test] mode={args.mode} script={script}", flush=True)
     runpy.run_path(script, run_name="__main__")
     print(f"[run_ref_lce_test] mode={args.mode}: all cases passed", flush=True)

@@ -35,3 +35,22 @@ def test_megatron_side_equivalents_on_real_ranks():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MISMATCH" not in r.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.skipif(not os.path.isfile(os.path.join(ROOT, "oracle", "_ref", "tests", "utils",
+                                                    "test_linear_cross_entropy_tp.py")),
+                    reason="reference snapshot (oracle/_ref) not built")
+@pytest.mark.parametrize("exchange", ["nccl", "nvlink"])
+def test_reference_own_tensor_parallel_test_passes(exchange):
+    """The reference's OWN tensor-parallel kernel test (tests/utils/test_linear_cross_entropy_tp.py, all five shapes,
+    unmodified, from the oracle/_ref snapshot) with `verl.utils.kernel.linear_cross_entropy` resolved to verl_b200: the
+    sharded op against PyTorch on the all-gathered weight, d_hidden all-reduced by the script, on two real ranks; once
+    with the NCCL exchange of the partials and once with the exchange fused into the GEMM epilogue over NVLink."""
+    env = dict(os.environ, VPG_TP_EXCHANGE=exchange, VERL_REFERENCE_ROOT=os.path.join(ROOT, "oracle", "_ref"))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "scripts", "run_ref_lce_test.py"), "--mode", "ours",
+           "--tp"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("[PASS]: Verified kernel forward & backward correctness.") == 5, r.stdout[-3000:]
