@@ -130,6 +130,13 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, const void* src, 
                  "r"(smem_u32(src)), "r"(c0), "r"(c1)
                  : "memory");
 }
+// the same store with an L2 eviction-priority hint on the written lines (streaming outputs: evict-first)
+__device__ __forceinline__ void tma_store_2d_hint(const void* tmap, const void* src, int c0, int c1, uint64_t hint) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(
+                     reinterpret_cast<uint64_t>(tmap)),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1), "l"(hint)
+                 : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // wait until at most kPending of this thread's bulk groups have not finished READING their shared-memory source
 template <int kPending>

@@ -250,7 +250,7 @@ struct DsRow {
 // Two tiles per warp alternate; a tile is rewritten only after the store that read it has finished reading.
 __device__ __forceinline__ void ds_chunk_tma(const DsRow& rw, const uint32_t (&r)[32], float c, int lab_rel, int n_valid,
                                              uint8_t* tile, const CUtensorMap* tmap, int col, int row0, int f16,
-                                             int lane) {
+                                             int lane, int stcs = 0) {
     float d[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -285,7 +285,8 @@ __device__ __forceinline__ void ds_chunk_tma(const DsRow& rw, const uint32_t (&r
     fence_proxy_async();  // generic-proxy writes -> visible to the async proxy (TMA)
     __syncwarp();
     if (lane == 0) {
-        tma_store_2d(tmap, tile, col, row0);
+        if (stcs) tma_store_2d_hint(tmap, tile, col, row0, kHintEvictFirst);  // streaming output: first out of L2
+        else tma_store_2d(tmap, tile, col, row0);
         tma_store_commit();
     }
 }
@@ -894,7 +895,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, ra, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             if (p.ds_tma)
-                                ds_chunk_tma(rw, ra, c, lab - cb, n_valid, ds_tile0, &tmap_c, cb, ds_row0, p.f16, lane);
+                                ds_chunk_tma(rw, ra, c, lab - cb, n_valid, ds_tile0, &tmap_c, cb, ds_row0, p.f16, lane, p.ds_stcs);
                             else
                                 ds_chunk(rw, ra, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
                         } else if (part_row) {
@@ -915,7 +916,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             else if (n_valid > 0) fwd_chunk<true>(st, rb, c, lab - cb, n_valid);
                         } else if (kMode == MODE_DS) {
                             if (p.ds_tma)
-                                ds_chunk_tma(rw, rb, c, lab - cb, n_valid, ds_tile0 + 2048, &tmap_c, cb, ds_row0, p.f16, lane);
+                                ds_chunk_tma(rw, rb, c, lab - cb, n_valid, ds_tile0 + 2048, &tmap_c, cb, ds_row0, p.f16, lane, p.ds_stcs);
                             else
                                 ds_chunk(rw, rb, c, lab - cb, n_valid, p.ds + row * p.ldds + cb, p.f16, p.ds_stcs);
                         } else if (part_row) {
