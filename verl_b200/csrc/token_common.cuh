@@ -48,11 +48,15 @@ __device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pa
     }
 }
 
-// blocks per row so that the grid has >= ~4 waves when the problem is large enough, never more than needed
+// Blocks per row.  The grid should be MANY waves of the resident blocks (4-8 per SM) whenever the problem allows it: with
+// ~2.5 waves (2048 rows, one block each) the last, partial wave costs 10-25 % of the sweep.  Target: `VPG_TOK_BLOCKS_PER_SM`
+// blocks per SM in total, never less than two iterations of work per block.  Default 8: more blocks cost more than the
+// partial last wave in every kernel that ends in per-block atomics (A/B at 8..128 per SM: profiles/r2_ab_token_grid.txt).
 static inline int blocks_per_row(int64_t B, int64_t L, int vec) {
+    static const int per_sm = env_int("VPG_TOK_BLOCKS_PER_SM", 8);
     const int64_t per_block = static_cast<int64_t>(kThreads) * vec * 2;
     int64_t need = ceil_div(L, per_block);
-    int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * 8, B > 0 ? B : 1);
+    int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * per_sm, B > 0 ? B : 1);
     int64_t g = need < want ? need : want;
     return static_cast<int>(g < 1 ? 1 : g);
 }

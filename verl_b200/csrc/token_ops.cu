@@ -152,8 +152,7 @@ __global__ void mask_count_kernel(const MT* __restrict__ mask, long long B, long
     float c = 0.f;
     bool wide = false;
     const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
-    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
-        const Pack<VEC> m = ldm<VEC, MT>(mask, base + t);
+    auto take = [&](const Pack<VEC>& m, long long t) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) c += m.v[j];
         if (cmask) {
@@ -169,7 +168,16 @@ __global__ void mask_count_kernel(const MT* __restrict__ mask, long long B, long
                 cmask[base + t] = q[0];
             }
         }
+    };
+    // two packs per iteration: both loads are issued before either is consumed (the sweep is latency-bound otherwise)
+    long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC;
+    for (; t + stride < L; t += 2 * stride) {
+        const Pack<VEC> m0 = ldm<VEC, MT>(mask, base + t);
+        const Pack<VEC> m1 = ldm<VEC, MT>(mask, base + t + stride);
+        take(m0, t);
+        take(m1, t + stride);
     }
+    if (t < L) take(ldm<VEC, MT>(mask, base + t), t);
     if (cmask && __syncthreads_or(wide ? 1 : 0) && threadIdx.x == 0) ws[8] = 1.0;  // benign race: every writer stores 1
     const double bc = block_sum<double>(static_cast<double>(c), red);
     if (threadIdx.x == 0) atomicAdd(&ws[kWsHeader + b], bc);
@@ -204,18 +212,21 @@ __device__ __forceinline__ double agg_finalize(int mode, const double* row_sum, 
     return s / static_cast<double>(B);
 }
 
-template <int VEC, typename MT>
+// kCount: forward only with token-mean aggregation — nothing needs the normaliser before the sweep, so the mask count is
+// taken in the same pass (no mask_count_kernel launch, the mask read once).
+template <int VEC, typename MT, bool kCount>
 __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask,
                                                                const unsigned char* __restrict__ cmask) {
     __shared__ double red[32];
-    const bool compact = cmask != nullptr && p.ws[8] == 0.0;  // the one-byte copy holds every mask value exactly
+    const bool compact = !kCount && cmask != nullptr && p.ws[8] == 0.0;  // the one-byte copy holds every mask value exactly
     const long long b = blockIdx.x / p.gx;
     const int cx = blockIdx.x % p.gx;
     const long long base = b * p.L;
     double* ws = p.ws;
-    const double n_total = ws[1];
-    const double row_cnt = ws[kWsHeader + b];
-    const float coef = agg_coef(p.agg_mode, n_total, row_cnt, p.B, p.L) * p.loss_scale;
+    double n_total = kCount ? 0.0 : ws[1];
+    const double row_cnt = kCount ? 1.0 : ws[kWsHeader + b];
+    const float coef = kCount ? 0.f : agg_coef(p.agg_mode, n_total, row_cnt, p.B, p.L) * p.loss_scale;
+    float a_cnt = 0.f;
     const bool where_w = (p.agg_mode == VPG_AGG_TOKEN_MEAN);
     const bool has_ent = p.entropy != nullptr;
     const bool has_kl = p.ref_lp != nullptr && p.kl_kind >= 0;
@@ -236,6 +247,7 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
         for (int j = 0; j < VEC; ++j) {
             const float mj = m.v[j];
             const bool on = mj != 0.f;
+            if (kCount) a_cnt += mj;
             const float A = adv.v[j];
             const float lr_raw = lp.v[j] - old.v[j];
             const float lr = clampf(lr_raw, -20.f, 20.f);
@@ -279,8 +291,8 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
                 dent.v[j] = -(coef * w) * p.entropy_coeff;
             }
         }
-        if (p.d_lp) stv<VEC>(p.d_lp, i, dlp);
-        if (p.d_ent && has_ent) stv<VEC>(p.d_ent, i, dent);
+        if (!kCount && p.d_lp) stv<VEC>(p.d_lp, i, dlp);  // kCount: no gradient outputs, the gradient arithmetic is dead code
+        if (!kCount && p.d_ent && has_ent) stv<VEC>(p.d_ent, i, dent);
     }
     float acc[9] = {a_pg, a_lr, a_clip, a_low, a_ent, a_kl, r_pg, r_ent, r_kl};
     double tot[9];
@@ -294,8 +306,13 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
         atomicAdd(&rows[p.B + b], tot[7]);
         atomicAdd(&rows[2 * p.B + b], tot[8]);
     }
+    if (kCount) {
+        const double tc = block_sum<double>(static_cast<double>(a_cnt), red);
+        if (threadIdx.x == 0) atomicAdd(&ws[1], tc);
+    }
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
     if (last_block_done(&counters[1], gridDim.x)) {
+        if (kCount) n_total = __ldcg(&ws[1]);
         const double* rcnt = ws + kWsHeader;
         const double* rows = ws + kWsHeader + p.B;
         const double G0 = __ldcg(&ws[2]), G1 = __ldcg(&ws[3]), G2 = __ldcg(&ws[4]), G3 = __ldcg(&ws[5]);
@@ -324,42 +341,52 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
 }
 
 // agg_loss for an arbitrary loss matrix: forward sums + gradient d loss / d loss_mat
-template <int VEC, typename MT>
+// kCount: the token-mean FORWARD alone needs no normaliser before its sweep, so the mask count is taken in the same pass
+// (no mask_count_kernel launch, the mask read once: 12 B/token).  Otherwise the counts come from mask_count_kernel and,
+// for 4- / 8-byte integer masks, the mask is re-read from its one-byte copy (`cmask`, see mask_count_kernel).
+template <int VEC, typename MT, bool kCount>
 __global__ void agg_loss_kernel(const float* __restrict__ loss_mat, const MT* __restrict__ mask, long long B,
                                 long long L, int gx, int mode, float* __restrict__ out, float* __restrict__ d_mat,
-                                double* ws) {
+                                double* ws, const unsigned char* __restrict__ cmask) {
     __shared__ double red[32];
+    const bool compact = !kCount && cmask != nullptr && ws[8] == 0.0;
     const long long b = blockIdx.x / gx;
     const int cx = blockIdx.x % gx;
     const long long base = b * L;
-    const double n_total = ws[1];
-    const double row_cnt = ws[kWsHeader + b];
-    const float coef = agg_coef(mode, n_total, row_cnt, B, L);
+    const double n_known = kCount ? 0.0 : ws[1];
+    const double row_cnt = kCount ? 1.0 : ws[kWsHeader + b];
+    const float coef = kCount ? 0.f : agg_coef(mode, n_known, row_cnt, B, L);
     const bool where_w = (mode == VPG_AGG_TOKEN_MEAN);
-    float a = 0.f, r = 0.f;
+    float a = 0.f, r = 0.f, c = 0.f;
     const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
     for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
         const long long i = base + t;
-        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> m = compact ? ldm<VEC, unsigned char>(cmask, i) : ldm<VEC, MT>(mask, i);
         const Pack<VEC> v = ldv<VEC>(loss_mat, i);
         Pack<VEC> d;
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
             const bool on = m.v[j] != 0.f;
             a += (on ? v.v[j] : 0.f) * m.v[j];
-            r += v.v[j] * m.v[j];
-            d.v[j] = coef * (where_w ? (on ? m.v[j] : 0.f) : m.v[j]);
+            if (kCount) {
+                c += m.v[j];
+            } else {
+                r += v.v[j] * m.v[j];
+                d.v[j] = coef * (where_w ? (on ? m.v[j] : 0.f) : m.v[j]);
+            }
         }
-        if (d_mat) stv<VEC>(d_mat, i, d);
+        if (!kCount && d_mat) stv<VEC>(d_mat, i, d);
     }
     const double ta = block_sum<double>(static_cast<double>(a), red);
-    const double tr = block_sum<double>(static_cast<double>(r), red);
+    const double tr = block_sum<double>(static_cast<double>(kCount ? c : r), red);
     if (threadIdx.x == 0) {
         atomicAdd(&ws[2], ta);
-        atomicAdd(&ws[kWsHeader + B + b], tr);
+        if (kCount) atomicAdd(&ws[1], tr);
+        else atomicAdd(&ws[kWsHeader + B + b], tr);
     }
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
     if (last_block_done(&counters[1], gridDim.x)) {
+        const double n_total = kCount ? __ldcg(&ws[1]) : n_known;
         const double v = agg_finalize(mode, ws + kWsHeader + B, ws + kWsHeader, __ldcg(&ws[2]), n_total, B, L, red);
         if (threadIdx.x == 0) out[0] = static_cast<float>(v);
     }
@@ -376,8 +403,9 @@ template <int VEC, typename MT>
 __global__ void value_loss_kernel(const float* __restrict__ vpreds, const float* __restrict__ returns,
                                   const float* __restrict__ values, const MT* __restrict__ mask, long long B,
                                   long long L, int gx, float cliprange, int mode, float* __restrict__ out,
-                                  float* __restrict__ d_vpreds, double* ws) {
+                                  float* __restrict__ d_vpreds, double* ws, const unsigned char* __restrict__ cmask) {
     __shared__ double red[32];
+    const bool compact = cmask != nullptr && ws[8] == 0.0;  // the one-byte copy holds every mask value exactly
     const long long b = blockIdx.x / gx;
     const int cx = blockIdx.x % gx;
     const long long base = b * L;
@@ -389,7 +417,7 @@ __global__ void value_loss_kernel(const float* __restrict__ vpreds, const float*
     const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
     for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < L; t += stride) {
         const long long i = base + t;
-        const Pack<VEC> m = ldm<VEC, MT>(mask, i);
+        const Pack<VEC> m = compact ? ldm<VEC, unsigned char>(cmask, i) : ldm<VEC, MT>(mask, i);
         const Pack<VEC> vp = ldv<VEC>(vpreds, i);
         const Pack<VEC> rt = ldv<VEC>(returns, i);
         const Pack<VEC> vo = ldv<VEC>(values, i);
@@ -870,16 +898,21 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
     p.loss_scale = loss_scale;
     p.metrics = metrics, p.d_lp = d_log_prob, p.d_ent = d_entropy;
     p.ws = static_cast<double*>(workspace);
+    // forward only + token-mean: one sweep, the mask count taken on the way
+    const bool one_pass = (agg_mode == VPG_AGG_TOKEN_MEAN) && !p.d_lp && !p.d_ent;
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
-        if (vec) {
+        if (one_pass) {
+            if (vec) ppo_loss_kernel<4, MT, true><<<grid, kThreads, 0, stream>>>(p, mk, nullptr);
+            else ppo_loss_kernel<1, MT, true><<<grid, kThreads, 0, stream>>>(p, mk, nullptr);
+        } else if (vec) {
             mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws, cmask);
             count_launch();
-            ppo_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
+            ppo_loss_kernel<4, MT, false><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
         } else {
             mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws, cmask);
             count_launch();
-            ppo_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
+            ppo_loss_kernel<1, MT, false><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
         }
     });
     VPG_LAUNCH_CHECK();
@@ -900,16 +933,26 @@ int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {loss_mat, d_loss_mat});
     const int gx = blocks_per_row(B, L, vec ? 4 : 1);
     const unsigned grid = static_cast<unsigned>(B * gx);
+    // one-byte mask copy for the second sweep when the caller's workspace has room for it (the ppo_loss size)
+    unsigned char* cmask = ((mask_dtype == VPG_MASK_I64 || mask_dtype == VPG_MASK_I32) &&
+                            workspace_bytes >= vpg_ppo_loss_workspace_bytes(B, L))
+                               ? static_cast<unsigned char*>(workspace) + need : nullptr;
+    const bool one_pass = (agg_mode == VPG_AGG_TOKEN_MEAN) && !d_loss_mat;  // forward only: count in the same sweep
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
-        if (vec) {
-            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, nullptr);
+        if (one_pass) {
+            if (vec)
+                agg_loss_kernel<4, MT, true><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, nullptr, ws, nullptr);
+            else
+                agg_loss_kernel<1, MT, true><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, nullptr, ws, nullptr);
+        } else if (vec) {
+            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, cmask);
             count_launch();
-            agg_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws);
+            agg_loss_kernel<4, MT, false><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws, cmask);
         } else {
-            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, nullptr);
+            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, cmask);
             count_launch();
-            agg_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws);
+            agg_loss_kernel<1, MT, false><<<grid, kThreads, 0, stream>>>(loss_mat, mk, B, L, gx, agg_mode, out, d_loss_mat, ws, cmask);
         }
     });
     VPG_LAUNCH_CHECK();
@@ -931,18 +974,22 @@ int vpg_value_loss(const float* vpreds, const float* returns, const float* value
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {vpreds, returns, values, d_vpreds});
     const int gx = blocks_per_row(B, L, vec ? 4 : 1);
     const unsigned grid = static_cast<unsigned>(B * gx);
+    // one-byte mask copy for the second sweep when the caller's workspace has room for it (the ppo_loss size)
+    unsigned char* cmask = ((mask_dtype == VPG_MASK_I64 || mask_dtype == VPG_MASK_I32) &&
+                            workspace_bytes >= vpg_ppo_loss_workspace_bytes(B, L))
+                               ? static_cast<unsigned char*>(workspace) + need : nullptr;
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         if (vec) {
-            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, nullptr);
+            mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, cmask);
             count_launch();
             value_loss_kernel<4, MT><<<grid, kThreads, 0, stream>>>(vpreds, returns, values, mk, B, L, gx,
-                                                                    cliprange_value, agg_mode, out, d_vpreds, ws);
+                                                                    cliprange_value, agg_mode, out, d_vpreds, ws, cmask);
         } else {
-            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, nullptr);
+            mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, ws, cmask);
             count_launch();
             value_loss_kernel<1, MT><<<grid, kThreads, 0, stream>>>(vpreds, returns, values, mk, B, L, gx,
-                                                                    cliprange_value, agg_mode, out, d_vpreds, ws);
+                                                                    cliprange_value, agg_mode, out, d_vpreds, ws, cmask);
         }
     });
     VPG_LAUNCH_CHECK();
