@@ -815,8 +815,11 @@ def run_ours(args, name, cfg):
                                  "library default: $VPG_BWD_WS_MB or 4096 MiB of dlogits (the [T,V] logits are never stored)"},
             "cpu_baseline": cpu,
         }
-        if args.token_ops and world == 1:
-            line["extra"] = {"token_ops": token_ops_table(torch, dev, peaks)}
+        if args.token_ops and world == 1:  # outside the timed region; a few seconds
+            try:
+                line["extra"] = {"token_ops": token_ops_table(torch, dev, peaks)}
+            except Exception as e:  # the headline line must not depend on the side table
+                line["extra"] = {"token_ops_error": f"{type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -852,7 +855,8 @@ def main():
                     help="token sample of the CPU legs (0 = 4096 for cpu_baseline, 2048 per step for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the fp32 parity probe (outside the timed region)")
-    ap.add_argument("--token-ops", action="store_true", help="N=1: add the token-op HBM roofline table as `extra`")
+    ap.add_argument("--token-ops", action=argparse.BooleanOptionalAction, default=True,
+                    help="N=1: add the token-op HBM roofline table as `extra` (default on; --no-token-ops skips it)")
     ap.add_argument("--bwd-ws-mb", type=int, default=0,
                     help="dlogits workspace budget of the backward in MiB (0 = library default, 4096)")
     ap.add_argument("--tp-reduce", choices=["auto", "fused", "nccl", "multimem", "overlap"], default="auto",

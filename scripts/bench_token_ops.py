@@ -97,7 +97,11 @@ def ops_table(d, B, L, n_uid):
         ("data_metrics (compute_data_metrics sweep)",
          lambda: ops.data_metrics(d["rewards"], d["rewards"], d["adv"], d["lp"], d["values"], d["mask"], attn),
          n * (8 + 20 + 8)),
-        ("unpad_indices (int64 mask)", lambda: ops.unpad_indices(attn), n * 16 + nnz * 8),
+        # mask read once + one int64 index per valid token (the 1-bit map adds n/4 bytes, not counted).  The
+        # call ends in a host read of {nnz, max_seqlen} like the reference's nonzero() / .item(); the second row times the
+        # two kernels alone (launches back to back, no host read).
+        ("unpad_indices (int64 mask, incl. host read of nnz)", lambda: ops.unpad_indices(attn), n * 8 + nnz * 8),
+        ("unpad_indices (int64 mask, device time)", lambda: ops.unpad_indices_launch(attn), n * 8 + nnz * 8),
         ("gather_rows int64 ids (index_first_axis)", lambda: ops.gather_rows(flat_ids, idx), nnz * 24),
         ("pad_input fp32 [nnz,1] -> [B*L,1]", lambda: ops.scatter_rows(vals, idx, n), nnz * 12 + n * 4),
     ]

@@ -54,3 +54,19 @@ def test_reference_own_tensor_parallel_test_passes(exchange):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("[PASS]: Verified kernel forward & backward correctness.") == 5, r.stdout[-3000:]
+
+
+@pytest.mark.skipif(not os.path.isfile(os.path.join(ROOT, "oracle", "_ref", "tests", "utils",
+                                                    "test_linear_cross_entropy.py")),
+                    reason="reference snapshot (oracle/_ref) not built")
+def test_reference_own_kernel_test_passes_on_one_gpu():
+    """The reference's OWN single-GPU kernel test (tests/utils/test_linear_cross_entropy.py, unmodified, from the
+    oracle/_ref snapshot) with `verl.utils.kernel.linear_cross_entropy` resolved to verl_b200: its five shapes, its three
+    PyTorch comparators (plain, FusedLinearForPPO, chunked entropy) and its tolerances (log-probs atol 1e-3, entropy 5e-3,
+    gradients atol 2e-2 / rtol 4e-2) judge the tcgen05 kernels, forward and backward."""
+    env = dict(os.environ, VERL_REFERENCE_ROOT=os.path.join(ROOT, "oracle", "_ref"))
+    cmd = [sys.executable, os.path.join(ROOT, "scripts", "run_ref_lce_test.py"), "--mode", "ours"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "mode=ours: all cases passed" in r.stdout, r.stdout[-3000:]
+    assert r.stdout.count("Verified forward & backward correctness.") == 5, r.stdout[-3000:]

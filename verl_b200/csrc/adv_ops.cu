@@ -562,7 +562,6 @@ __global__ void data_metrics_kernel(const float* __restrict__ scores, const floa
                                     const float* __restrict__ vals, const MT* __restrict__ rmask, long long L, int gx,
                                     long long B, double* __restrict__ acc, unsigned int* __restrict__ keys,
                                     double* __restrict__ rows) {
-    __shared__ double red[32];
     const long long b = blockIdx.x / gx;
     const int cx = blockIdx.x % gx;
     const long long base = b * L;
@@ -604,47 +603,76 @@ __global__ void data_metrics_kernel(const float* __restrict__ scores, const floa
             }
         }
     }
-    double v[kDmAcc];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) v[5 * k] = s1[k], v[5 * k + 1] = s2[k];
-    v[15] = d1, v[16] = d2, v[17] = cnt;
-    const double r_sc = block_sum<double>(static_cast<double>(s_sc), red);
-    const double r_rw = block_sum<double>(static_cast<double>(s_rw), red);
+    // epilogue: the eleven block sums share one barrier pair, the six max / min keys a second one; thread 0 issues every
+    // atomic (the per-block cost is what bounds how finely the sweep can be cut: profiles/r2_ab_token_grid.txt)
+    __shared__ double red_n[11 * 32];
+    __shared__ unsigned int red_k[6 * 32];
+    double v[11] = {s1[0], s2[0], s1[1], s2[1], s1[2], s2[2], d1, d2, cnt, s_sc, s_rw};
+    block_sum_n<11>(v, red_n);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    unsigned int key[6];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const double a1 = block_sum<double>(v[5 * k], red), a2 = block_sum<double>(v[5 * k + 1], red);
-        if (threadIdx.x == 0) atomicAdd(&acc[5 * k], a1), atomicAdd(&acc[5 * k + 1], a2);
-        // block max / min through warp shuffles on the keys
         unsigned int kmx = fkey(mx[k]), kmn = fkey(mn[k]);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
             kmn = min(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMax(&keys[2 * k], kmx);
-            atomicMin(&keys[2 * k + 1], kmn);
-        }
+        key[2 * k] = kmx, key[2 * k + 1] = kmn;
     }
-    const double a15 = block_sum<double>(v[15], red), a16 = block_sum<double>(v[16], red);
-    const double a17 = block_sum<double>(v[17], red);
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) red_k[k * 32 + w] = key[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        const int k = threadIdx.x;
+        unsigned int r = red_k[k * 32];
+        for (int ww = 1; ww < nw; ++ww) r = (k & 1) ? min(r, red_k[k * 32 + ww]) : max(r, red_k[k * 32 + ww]);
+        if (k & 1) atomicMin(&keys[k], r);
+        else atomicMax(&keys[k], r);
+    }
     if (threadIdx.x == 0) {
-        atomicAdd(&acc[15], a15), atomicAdd(&acc[16], a16), atomicAdd(&acc[17], a17);
-        atomicAdd(&rows[b], r_sc);
-        atomicAdd(&rows[B + b], r_rw);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) atomicAdd(&acc[5 * k], v[2 * k]), atomicAdd(&acc[5 * k + 1], v[2 * k + 1]);
+        atomicAdd(&acc[15], v[6]), atomicAdd(&acc[16], v[7]), atomicAdd(&acc[17], v[8]);
+        atomicAdd(&rows[b], v[9]);
+        atomicAdd(&rows[B + b], v[10]);
     }
 }
 
 // prompt / response lengths from attention_mask [B,S] (metric_utils.py:57-75): one block per row
 template <typename MT>
 __global__ void seq_lengths_kernel(const MT* __restrict__ attn, long long S, long long L, long long B,
-                                   double* __restrict__ rows) {
+                                   double* __restrict__ rows, int vec) {
     __shared__ double red[32];
     const long long base = static_cast<long long>(blockIdx.x) * S;
+    const long long P = S - L;
     float p = 0.f, r = 0.f;
-    for (long long t = threadIdx.x; t < S; t += blockDim.x) {
-        const float m = mask_to_float(attn[base + t]);
-        if (t < S - L) p += m; else r += m;
+    if (vec) {  // 4 mask elements per load, two loads in flight (rows are 16-byte aligned, S % 4 == 0)
+        const long long step = static_cast<long long>(blockDim.x) * 4;
+        long long t = static_cast<long long>(threadIdx.x) * 4;
+        auto take = [&](const float4& m, long long t0) {
+            const float q[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (t0 + j < P) p += q[j];
+                else r += q[j];
+            }
+        };
+        for (; t + step < S; t += 2 * step) {
+            const float4 m0 = load_mask4<MT>(attn, base + t);
+            const float4 m1 = load_mask4<MT>(attn, base + t + step);
+            take(m0, t);
+            take(m1, t + step);
+        }
+        if (t < S) take(load_mask4<MT>(attn, base + t), t);
+    } else {
+        for (long long t = threadIdx.x; t < S; t += blockDim.x) {
+            const float m = mask_to_float(attn[base + t]);
+            if (t < P) p += m; else r += m;
+        }
     }
     const double tp = block_sum<double>(static_cast<double>(p), red);
     const double tr = block_sum<double>(static_cast<double>(r), red);
@@ -785,8 +813,8 @@ int vpg_data_metrics(const float* token_level_scores, const float* token_level_r
     });
     count_launch();
     VPG_DISPATCH_MASK(amask_dtype, MT, {
-        seq_lengths_kernel<MT><<<static_cast<unsigned>(B), kThreads, 0, stream>>>(static_cast<const MT*>(attention_mask), S,
-                                                                                  L, B, rows);
+        seq_lengths_kernel<MT><<<static_cast<unsigned>(B), kThreads, 0, stream>>>(
+            static_cast<const MT*>(attention_mask), S, L, B, rows, (S % 4 == 0) && mask_aligned(attention_mask, amask_dtype));
     });
     count_launch();
     data_metrics_finalize_kernel<<<1, 256, 0, stream>>>(acc, keys, rows, B, L, S - L, values != nullptr, out26);

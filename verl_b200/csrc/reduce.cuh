@@ -28,6 +28,26 @@ __device__ __forceinline__ T block_sum(T v, T* smem) {
     return v;
 }
 
+// N block sums behind ONE pair of barriers (block_sum pays two per value).  Same summation order as block_sum, value by
+// value; results valid in thread 0.  `smem` must hold N * 32 values of T.  Safe to call repeatedly.
+template <int N, typename T>
+__device__ __forceinline__ void block_sum_n(T (&v)[N], T* smem) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < N; ++k) v[k] = warp_sum(v[k]);
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) smem[k * 32 + w] = v[k];
+    }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+        for (int k = 0; k < N; ++k) v[k] = warp_sum((lane < nw) ? smem[k * 32 + lane] : T(0));
+    }
+}
+
 // ---- mask element -> float
 template <typename MT>
 __device__ __forceinline__ float mask_to_float(MT m) {

@@ -77,9 +77,19 @@ __device__ __forceinline__ bool last_block_done(unsigned int* counter, unsigned 
 
 // torch.clamp / torch.maximum / torch.minimum propagate NaN; fminf / fmaxf drop it.  A NaN log-prob must surface as a
 // NaN loss exactly like in the reference (it is how a diverged run is noticed), so the NaN-propagating forms are used.
-__device__ __forceinline__ float clampf(float x, float lo, float hi) { return (x != x) ? x : fminf(fmaxf(x, lo), hi); }
-__device__ __forceinline__ float max_nan(float a, float b) { return (a != a || b != b) ? (a + b) : fmaxf(a, b); }
-__device__ __forceinline__ float min_nan(float a, float b) { return (a != a || b != b) ? (a + b) : fminf(a, b); }
+// `max.NaN.f32` / `min.NaN.f32` are ONE instruction each (FMNMX.NAN) where the select-on-isnan form costs four to five;
+// the loss kernels are issue-bound, not HBM-bound, without them (ncu: sm throughput 66-72 % at 55 % of DRAM peak).
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float d;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+__device__ __forceinline__ float min_nan(float a, float b) {
+    float d;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return min_nan(max_nan(x, lo), hi); }
 
 static inline int flat_grid(int64_t n, int vec) {
     int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);

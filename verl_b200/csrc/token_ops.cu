@@ -214,7 +214,11 @@ __device__ __forceinline__ double agg_finalize(int mode, const double* row_sum, 
 
 // kCount: forward only with token-mean aggregation — nothing needs the normaliser before the sweep, so the mask count is
 // taken in the same pass (no mask_count_kernel launch, the mask read once).
-template <int VEC, typename MT, bool kCount>
+// kSpec: 0 = every option read at run time; 1 / 2 = the two configurations the BASELINE recipes run (clip loss,
+// token-mean, 1: no KL term, 2: low_var_kl) with the options folded at compile time — the sweep is ISSUE-bound (ncu of the
+// generic body: ~150 instructions per token, sm throughput 66-72 % at 55 % of DRAM peak), so dead accumulators, option
+// tests and the select-on-isnan clamps are what the specialisation removes (~90 per token).
+template <int VEC, typename MT, bool kCount, int kSpec>
 __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask,
                                                                const unsigned char* __restrict__ cmask) {
     __shared__ double red[32];
@@ -227,12 +231,16 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
     const double row_cnt = kCount ? 1.0 : ws[kWsHeader + b];
     const float coef = kCount ? 0.f : agg_coef(p.agg_mode, n_total, row_cnt, p.B, p.L) * p.loss_scale;
     float a_cnt = 0.f;
-    const bool where_w = (p.agg_mode == VPG_AGG_TOKEN_MEAN);
+    const bool where_w = kSpec ? true : (p.agg_mode == VPG_AGG_TOKEN_MEAN);
+    const bool gpg = kSpec ? false : (p.pg_kind == VPG_PG_GPG);
     const bool has_ent = p.entropy != nullptr;
-    const bool has_kl = p.ref_lp != nullptr && p.kl_kind >= 0;
+    const bool has_kl = kSpec == 1 ? false : kSpec == 2 ? true : (p.ref_lp != nullptr && p.kl_kind >= 0);
+    const int kl_kind = kSpec == 2 ? static_cast<int>(VPG_KL_LOW_VAR) : p.kl_kind;
+    const bool want_grad = !kCount && p.d_lp != nullptr;  // kCount: no gradient outputs, the gradient arithmetic is dead code
+    const float ent_g = -p.entropy_coeff;
 
     float a_pg = 0.f, a_lr = 0.f, a_clip = 0.f, a_low = 0.f, a_ent = 0.f, a_kl = 0.f;  // where-weighted
-    float r_pg = 0.f, r_ent = 0.f, r_kl = 0.f;                                           // plain v*m
+    float r_pg = 0.f, r_ent = 0.f, r_kl = 0.f;                                           // plain v*m (row sums)
     const long long stride = static_cast<long long>(p.gx) * blockDim.x * VEC;
     for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < p.L; t += stride) {
         const long long i = base + t;
@@ -258,57 +266,60 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
             const float c1 = max_nan(l1, l2);
             const float l3 = -A * p.clip_c;
             const float c2 = min_nan(l3, c1);
-            const bool gpg = p.pg_kind == VPG_PG_GPG;
             const float pg = gpg ? (-lp.v[j] * A) : ((A < 0.f) ? c2 : c1);
-            const float f_clip = (!gpg && l2 > l1) ? 1.f : 0.f;
-            const float f_low = gpg ? 0.f : ((c1 > l3) ? 1.f : 0.f) * ((A < 0.f) ? 1.f : 0.f);
+            const bool clipped = !gpg && (l2 > l1);
+            const bool low = !gpg && (c1 > l3) && (A < 0.f);
             a_pg += (on ? pg : 0.f) * mj;
-            a_lr += (on && !gpg ? -lr : 0.f) * mj;
-            a_clip += (on ? f_clip : 0.f) * mj;
-            a_low += (on ? f_low : 0.f) * mj;
-            r_pg += pg * mj;
-            // ---- gradient of pg wrt log_prob (ties of maximum/min split 1/2, as torch autograd does)
-            const bool in_lr = (lr_raw >= -20.f) && (lr_raw <= 20.f);
-            const float dl1 = in_lr ? -A * ratio : 0.f;
-            const bool in_clip = (ratio >= p.ratio_lo) && (ratio <= p.ratio_hi);
-            const float dl2 = (in_lr && in_clip) ? -A * ratio : 0.f;
-            const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
-            const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
-            float g = (A < 0.f) ? g_c2 : g_c1;
-            if (p.pg_kind == VPG_PG_GPG) g = -A;
+            a_lr += ((on && !gpg) ? -lr : 0.f) * mj;
+            a_clip += ((on && clipped) ? 1.f : 0.f) * mj;
+            a_low += ((on && low) ? 1.f : 0.f) * mj;
+            if (!where_w) r_pg += pg * mj;
+            float g = 0.f;
+            if (want_grad) {
+                // gradient of pg wrt log_prob (ties of maximum / min split 1/2, as torch autograd does); d l1 = l1
+                const bool in_lr = (lr_raw >= -20.f) && (lr_raw <= 20.f);
+                const float dl1 = in_lr ? l1 : 0.f;
+                const bool in_clip = (ratio >= p.ratio_lo) && (ratio <= p.ratio_hi);
+                const float dl2 = in_clip ? dl1 : 0.f;
+                const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
+                const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
+                g = gpg ? -A : ((A < 0.f) ? g_c2 : g_c1);
+            }
             if (has_kl) {
                 float kv, kg;
-                kl_term(p.kl_kind, lp.v[j], ref.v[j], kv, kg);
+                kl_term(kl_kind, lp.v[j], ref.v[j], kv, kg);
                 a_kl += (on ? kv : 0.f) * mj;
-                r_kl += kv * mj;
+                if (!where_w) r_kl += kv * mj;
                 g += p.kl_coef * kg;
             }
-            const float w = where_w ? (on ? mj : 0.f) : mj;
-            dlp.v[j] = coef * w * g;
+            const float cw = coef * (where_w ? (on ? mj : 0.f) : mj);
+            dlp.v[j] = cw * g;
             if (has_ent) {
                 a_ent += (on ? ent.v[j] : 0.f) * mj;
-                r_ent += ent.v[j] * mj;
-                dent.v[j] = -(coef * w) * p.entropy_coeff;
+                if (!where_w) r_ent += ent.v[j] * mj;
+                dent.v[j] = cw * ent_g;
             }
         }
-        if (!kCount && p.d_lp) stv<VEC>(p.d_lp, i, dlp);  // kCount: no gradient outputs, the gradient arithmetic is dead code
+        if (want_grad) stv<VEC>(p.d_lp, i, dlp);
         if (!kCount && p.d_ent && has_ent) stv<VEC>(p.d_ent, i, dent);
     }
-    float acc[9] = {a_pg, a_lr, a_clip, a_low, a_ent, a_kl, r_pg, r_ent, r_kl};
-    double tot[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) tot[k] = block_sum<double>(static_cast<double>(acc[k]), red);
+    // one barrier pair for the block sums of the sweep (six global sums + the mask count), a second one for the three row
+    // sums of the seq-mean modes
+    __shared__ double red_n[7 * 32];
+    double tot[7] = {a_pg, a_lr, a_clip, a_low, a_ent, a_kl, a_cnt};
+    block_sum_n<7>(tot, red_n);
+    double rtot[3] = {r_pg, r_ent, r_kl};
+    if (!where_w) block_sum_n<3>(rtot, red_n);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) atomicAdd(&ws[2 + k], tot[k]);
-        double* rows = ws + kWsHeader + p.B;
-        atomicAdd(&rows[b], tot[6]);
-        atomicAdd(&rows[p.B + b], tot[7]);
-        atomicAdd(&rows[2 * p.B + b], tot[8]);
-    }
-    if (kCount) {
-        const double tc = block_sum<double>(static_cast<double>(a_cnt), red);
-        if (threadIdx.x == 0) atomicAdd(&ws[1], tc);
+        if (kCount) atomicAdd(&ws[1], tot[6]);
+        if (!where_w) {  // row sums feed the seq-mean modes only
+            double* rows = ws + kWsHeader + p.B;
+            atomicAdd(&rows[b], rtot[0]);
+            atomicAdd(&rows[p.B + b], rtot[1]);
+            atomicAdd(&rows[2 * p.B + b], rtot[2]);
+        }
     }
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
     if (last_block_done(&counters[1], gridDim.x)) {
@@ -432,8 +443,8 @@ __global__ void value_loss_kernel(const float* __restrict__ vpreds, const float*
             const float l1 = e1 * e1, l2 = e2 * e2;
             const float lmax = max_nan(l1, l2);
             a += (on ? lmax : 0.f) * m.v[j];
-            r += lmax * m.v[j];
-            cf += (on ? ((l2 > l1) ? 1.f : 0.f) : 0.f) * m.v[j];
+            if (!where_w) r += lmax * m.v[j];
+            cf += ((on && l2 > l1) ? 1.f : 0.f) * m.v[j];
             // d vpc / d vp through torch.min / torch.max (ties split 1/2 like torch autograd)
             const float dmin = (vp.v[j] < hi) ? 1.f : ((vp.v[j] == hi) ? 0.5f : 0.f);
             const float dmax = (y > lo) ? 1.f : ((y == lo) ? 0.5f : 0.f);
@@ -444,12 +455,12 @@ __global__ void value_loss_kernel(const float* __restrict__ vpreds, const float*
         if (d_vpreds) stv<VEC>(d_vpreds, i, d);
     }
     const double ta = block_sum<double>(static_cast<double>(a), red);
-    const double tr = block_sum<double>(static_cast<double>(r), red);
+    const double tr = where_w ? 0.0 : block_sum<double>(static_cast<double>(r), red);  // row sums: seq-mean modes only
     const double tc = block_sum<double>(static_cast<double>(cf), red);
     if (threadIdx.x == 0) {
         atomicAdd(&ws[2], ta);
         atomicAdd(&ws[3], tc);
-        atomicAdd(&ws[kWsHeader + B + b], tr);
+        if (!where_w) atomicAdd(&ws[kWsHeader + B + b], tr);
     }
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
     if (last_block_done(&counters[1], gridDim.x)) {
@@ -857,6 +868,12 @@ int vpg_kl_penalty(const float* logprob, const float* ref_logprob, int kind, int
     return VPG_OK;
 }
 
+// VPG_TOK_SPEC=0 keeps every loss sweep on its generic (run-time option) body: the A/B switch of the folded bodies
+static bool spec_enabled() {
+    static const int on = env_int("VPG_TOK_SPEC", 1);
+    return on != 0;
+}
+
 static size_t ppo_ws_header_bytes(int64_t B) {
     return round_up(static_cast<int64_t>(kWsHeader + 4 * (B > 0 ? B : 0)) * sizeof(double), 16);
 }
@@ -900,21 +917,33 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
     p.ws = static_cast<double*>(workspace);
     // forward only + token-mean: one sweep, the mask count taken on the way
     const bool one_pass = (agg_mode == VPG_AGG_TOKEN_MEAN) && !p.d_lp && !p.d_ent;
+    // compile-time folded bodies for the recipes' configurations (vector path only)
+    const bool kl_on = ref_log_prob != nullptr && kl_kind >= 0;
+    int spec = 0;
+    if (vec && pg_kind == VPG_PG_CLIP && agg_mode == VPG_AGG_TOKEN_MEAN && spec_enabled())
+        spec = !kl_on ? 1 : (kl_kind == VPG_KL_LOW_VAR ? 2 : 0);
+#define VPG_PPO_LAUNCH(V, COUNT, CM)                                                             \
+    do {                                                                                         \
+        if (V == 4 && spec == 1) ppo_loss_kernel<V, MT, COUNT, (V == 4 ? 1 : 0)><<<grid, kThreads, 0, stream>>>(p, mk, CM); \
+        else if (V == 4 && spec == 2) ppo_loss_kernel<V, MT, COUNT, (V == 4 ? 2 : 0)><<<grid, kThreads, 0, stream>>>(p, mk, CM); \
+        else ppo_loss_kernel<V, MT, COUNT, 0><<<grid, kThreads, 0, stream>>>(p, mk, CM);          \
+    } while (0)
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         if (one_pass) {
-            if (vec) ppo_loss_kernel<4, MT, true><<<grid, kThreads, 0, stream>>>(p, mk, nullptr);
-            else ppo_loss_kernel<1, MT, true><<<grid, kThreads, 0, stream>>>(p, mk, nullptr);
+            if (vec) VPG_PPO_LAUNCH(4, true, nullptr);
+            else VPG_PPO_LAUNCH(1, true, nullptr);
         } else if (vec) {
             mask_count_kernel<4, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws, cmask);
             count_launch();
-            ppo_loss_kernel<4, MT, false><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
+            VPG_PPO_LAUNCH(4, false, cmask);
         } else {
             mask_count_kernel<1, MT><<<grid, kThreads, 0, stream>>>(mk, B, L, gx, p.ws, cmask);
             count_launch();
-            ppo_loss_kernel<1, MT, false><<<grid, kThreads, 0, stream>>>(p, mk, cmask);
+            VPG_PPO_LAUNCH(1, false, cmask);
         }
     });
+#undef VPG_PPO_LAUNCH
     VPG_LAUNCH_CHECK();
     return VPG_OK;
 }

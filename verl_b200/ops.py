@@ -314,11 +314,11 @@ def logits_stats_backward(logits2d, labels, lse, entropy, g_lp, g_ent):
 
 
 # --------------------------------------------------------------------------------------------------- rmpad
-def unpad_indices(mask2d):
-    """mask [B,S] -> (indices i64 [nnz], seqlens i32 [B], cu_seqlens i32 [B+1], max_seqlen int).
-
-    One device->host read of {nnz, max_seqlen} (the reference syncs here too: nonzero() and .item()).
-    """
+def unpad_indices_launch(mask2d):
+    """Enqueue the two unpad kernels and return WITHOUT waiting: (indices_full i64 [B*S] — the first nnz entries are the
+    result —, seqlens i32 [B], cu_seqlens i32 [B+1], slot).  ``slot.pair`` = {nnz, max_seqlen} in pinned host memory, valid
+    once the stream has passed the launch (``unpad_indices`` waits for it; a caller with other work to enqueue first can
+    wait later)."""
     _require_cuda(mask2d)
     if mask2d.dtype.is_floating_point:
         raise TypeError("attention masks must be integer or bool")
@@ -330,9 +330,6 @@ def unpad_indices(mask2d):
     dev = mask2d.device
     lib = _lib_()
     n = B * S
-    if n == 0:  # nothing to scan: no launch
-        return (torch.empty(0, dtype=torch.int64, device=dev), torch.zeros(B, dtype=torch.int32, device=dev),
-                torch.zeros(B + 1, dtype=torch.int32, device=dev), 0)
     indices_full = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     seqlens = torch.empty(B, dtype=torch.int32, device=dev)
     cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
@@ -342,7 +339,24 @@ def unpad_indices(mask2d):
     with torch.cuda.device(dev):
         check(lib.vpg_unpad_indices(ptr(m), mdt, B, S, ptr(indices_full), ptr(seqlens), ptr(cu), slot.pair_ptr, ptr(ws),
                                     ws.numel() * 8, stream_ptr(dev)))
-        torch.cuda.current_stream(dev).synchronize()
+    return indices_full, seqlens, cu, slot
+
+
+def unpad_indices(mask2d):
+    """mask [B,S] -> (indices i64 [nnz], seqlens i32 [B], cu_seqlens i32 [B+1], max_seqlen int).
+
+    One device->host read of {nnz, max_seqlen} (the reference syncs here too: nonzero() and .item()).
+    """
+    _require_cuda(mask2d)
+    B, S = mask2d.shape
+    dev = mask2d.device
+    if B * S == 0:  # nothing to scan: no launch
+        if mask2d.dtype.is_floating_point:
+            raise TypeError("attention masks must be integer or bool")
+        return (torch.empty(0, dtype=torch.int64, device=dev), torch.zeros(B, dtype=torch.int32, device=dev),
+                torch.zeros(B + 1, dtype=torch.int32, device=dev), 0)
+    indices_full, seqlens, cu, slot = unpad_indices_launch(mask2d)
+    torch.cuda.current_stream(dev).synchronize()
     nnz, max_seqlen = int(slot.pair[0]), int(slot.pair[1])
     indices = indices_full[:nnz]
     indices._vpg_ascending = True  # provenance mark: pad_input may then fill gaps in one pass (see scatter_rows)
