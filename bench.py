@@ -372,6 +372,109 @@ def parity_probe(torch, dist, linear_cross_entropy, hidden, w_local, labels, gro
                          "max over ranks", "ok": bool(ok)}
 
 
+def actor_parity_probe(torch, fused_actor_step, m, weight, cfg, scale, dev, n_rows=128):
+    """c3: one micro-batch of fused_actor_step against fp32 PyTorch written from the reference flow
+    (dp_actor.py:80-270, 393-470): lm-head over the rmpad stream, labels = roll(ids, -1), pad back to [B,S], slice
+    [:, -L-1:-1], clip loss + low_var_kl, token-mean.  Log-probs of EVERY response-window row, loss and metrics, d_hidden
+    on `n_rows` sampled window rows (and exactly zero outside the window), d_weight on sampled vocab rows."""
+    loss_cfg, P, L = cfg["loss"], cfg["P"], cfg["L"]
+    temp = 1.0
+    mb, S = m["attn"].shape
+    h = m["hidden"].detach().clone().requires_grad_(True)
+    w = weight.detach().clone().requires_grad_(True)
+    loss, metrics, lp, _ent = fused_actor_step(h, w, m["ids"], m["attn"], m["old"], m["adv"], m["rmask"], temperature=temp,
+                                               ref_log_prob=m["ref"], loss_scale=scale, **loss_cfg)
+    dh, dw = h.grad, w.grad
+    # ---- reference index plumbing in plain torch
+    flat = m["attn"].reshape(-1)
+    idx = flat.nonzero().squeeze(-1)                       # padded positions of the stream rows
+    T = idx.numel()
+    row_of = torch.full((mb * S,), -1, dtype=torch.long, device=dev)
+    row_of[idx] = torch.arange(T, device=dev)
+    ids_rmpad = m["ids"].reshape(-1)[idx]
+    labels = torch.roll(ids_rmpad, -1)
+    win = row_of.view(mb, S)[:, S - L - 1:S - 1]           # stream row feeding response slot (b, t), -1 = padding
+    valid = win >= 0
+    rows = win[valid]                                      # [T_sel]
+    wf = weight.detach().float()
+    lp_rows = torch.empty(rows.numel(), dtype=torch.float32, device=dev)
+    lse_rows = torch.empty_like(lp_rows)
+    for s0 in range(0, rows.numel(), 2048):
+        r = rows[s0:s0 + 2048]
+        z = (m["hidden"][r].float() @ wf.t()) / temp
+        lse = torch.logsumexp(z, -1)
+        lp_rows[s0:s0 + 2048] = z.gather(-1, labels[r, None]).squeeze(-1) - lse
+        lse_rows[s0:s0 + 2048] = lse
+        del z
+    lp_ref = torch.zeros(mb, L, dtype=torch.float32, device=dev)
+    lp_ref[valid] = lp_rows
+    lp_ref.requires_grad_(True)
+    mask = m["rmask"].float()
+    lo = loss_cfg.get("clip_ratio_low") or loss_cfg["clip_ratio"]
+    hi = loss_cfg.get("clip_ratio_high") or loss_cfg["clip_ratio"]
+    cc = loss_cfg.get("clip_ratio_c", 3.0)
+    mm = lambda x: (x * mask).sum() / (mask.sum() + 1e-8)  # noqa: E731
+    lr = (lp_ref - m["old"]).clamp(-20, 20)
+    ratio = lr.exp()
+    l1, l2 = -m["adv"] * ratio, -m["adv"] * ratio.clamp(1 - lo, 1 + hi)
+    c1 = torch.maximum(l1, l2)
+    pg = torch.where(m["adv"] < 0, torch.minimum(-m["adv"] * cc, c1), c1)
+    k = (m["ref"] - lp_ref).clamp(-20, 20)
+    kl = (k.exp() - k - 1).clamp(-10, 10)
+    pg_loss, kl_loss = mm(pg), mm(kl)
+    loss_ref = (pg_loss + loss_cfg["kl_loss_coef"] * kl_loss) * scale
+    loss_ref.backward()
+    g_lp_rows = lp_ref.grad[valid]                        # d loss / d log_prob of every window row
+    # ---- d_hidden: sampled window rows through fp32 autograd; rows outside the window carry exactly zero
+    g = torch.Generator(device=dev).manual_seed(778)
+    pick = torch.randperm(rows.numel(), device=dev, generator=g)[:n_rows]
+    hs = m["hidden"][rows[pick]].float().requires_grad_(True)
+    z = (hs @ wf.t()) / temp
+    lps = z.gather(-1, labels[rows[pick], None]).squeeze(-1) - torch.logsumexp(z, -1)
+    (lps * g_lp_rows[pick]).sum().backward()
+    dh_r = hs.grad
+    outside = torch.ones(T, dtype=torch.bool, device=dev)
+    outside[rows] = False
+    dh_outside = float(dh[outside].float().abs().max()) if bool(outside.any()) else 0.0
+    # ---- d_weight on sampled vocab rows: every window row contributes
+    voc = torch.cat([torch.randperm(wf.shape[0], device=dev, generator=g)[:n_rows - 32], labels[rows[pick[:32]]]])
+    wv = wf[voc]
+    dw_r = torch.zeros(voc.numel(), wf.shape[1], dtype=torch.float32, device=dev)
+    for s0 in range(0, rows.numel(), 4096):
+        r = rows[s0:s0 + 4096]
+        hf = m["hidden"][r].float()
+        zz = (hf @ wv.t()) / temp
+        pp = torch.exp(zz - lse_rows[s0:s0 + 4096, None])
+        onehot = (labels[r, None] == voc[None, :]).float()
+        dw_r += ((g_lp_rows[s0:s0 + 4096, None] * (onehot - pp)) / temp).t() @ hf
+
+    def excess(got, ref):
+        return float(((got.float() - ref).abs() - (2e-2 + 4e-2 * ref.abs())).max())
+
+    def rel(got, ref):
+        return float((got.float() - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+
+    unscale = float(mask.sum()) / scale  # gradients of the token-SUM loss: O(1) like the upstream gradients of the c2 probe
+    lp_err = float((lp - lp_ref.detach()).abs().max())
+    loss_err = abs(float(loss) - float(loss_ref)) / max(abs(float(loss_ref)), 1e-12)
+    met = [float(x) for x in metrics.tolist()]
+    met_err = max(abs(met[1] - float(pg_loss)), abs(met[6] - float(kl_loss)), abs(met[7] - float(mask.sum())) / float(mask.sum()))
+    out = {"lp_max_abs": lp_err, "loss_rel": loss_err, "metrics_max_abs": met_err,
+           "dh_max_rel": rel(dh[rows[pick]], dh_r), "dw_max_rel": rel(dw[voc], dw_r),
+           "dh_excess_over_tol": excess(dh[rows[pick]] * unscale, dh_r * unscale),
+           "dw_excess_over_tol": excess(dw[voc] * unscale, dw_r * unscale),
+           "dh_outside_window_max_abs": dh_outside, "window_rows": int(rows.numel()), "stream_rows": int(T),
+           "rows": int(pick.numel()), "vocab_rows": int(voc.numel()),
+           "reference": "fp32 PyTorch of the reference flow (lm-head on the stream, roll labels, pad, slice [:, -L-1:-1], "
+                        "clip + low_var_kl token-mean loss, autograd); tol lp 2e-3 abs, loss 1e-3 rel, grads 2e-2 + "
+                        "4e-2*|ref| on the gradient of the token-SUM loss (x mask_sum / loss_scale) and 2e-2 of the largest "
+                        "reference entry, zero outside the window"}
+    out["ok"] = bool(lp_err <= 2e-3 and loss_err <= 1e-3 and met_err <= 2e-3 and out["dh_excess_over_tol"] <= 0
+                     and out["dw_excess_over_tol"] <= 0 and out["dh_max_rel"] <= 2e-2 and out["dw_max_rel"] <= 2e-2
+                     and dh_outside == 0.0)
+    return out
+
+
 # ----------------------------------------------------------------------------------------------- our arm
 def run_ours(args, name, cfg):
     import numpy as np
@@ -455,11 +558,12 @@ def run_ours(args, name, cfg):
         uid = np.repeat(np.array([f"uid-{i}" for i in range(cfg.get("B", 0) // cfg.get("n", 1))], dtype=object),
                         cfg.get("n", 1)) if kind == "grpo" else None
     else:  # actor: 128 sequences in micro-batches of 16, left-padded prompts + right-padded responses
-        from verl_b200.workers.actor.dp_actor import fused_actor_step
+        from verl_b200.workers.actor.dp_actor import fused_actor_step, response_window
 
         B, mb, P, L = cfg["B"], cfg["micro"], cfg["P"], cfg["L"]
         S = P + L
         tokens_per_step = 0
+        window_rows = []
         for _ in range(B // mb):
             p_len = torch.randint(P // 2, P + 1, (mb,), device=dev, generator=gen)
             r_len = torch.randint(L // 4, L + 1, (mb,), device=dev, generator=gen)
@@ -473,6 +577,8 @@ def run_ours(args, name, cfg):
             d.update(ref=d["old"] + 0.05 * torch.randn(mb, L, device=dev, generator=gen))
             micros.append(d)
             tokens_per_step += Tm
+            # rows the lm-head actually runs on (the response window of the stream): the roofline's flop count
+            window_rows.append(int(response_window(d["ids"], attn, L)["sel"].numel()))
         T = tokens_per_step
     host = [{k: v.cpu().pin_memory() for k, v in m.items()} for m in micros]
 
@@ -667,6 +773,10 @@ def run_ours(args, name, cfg):
                               rank, world, dev)
         weight.grad = None
         torch.cuda.synchronize()
+    elif not args.no_parity and kind == "actor" and world == 1:
+        parity = actor_parity_probe(torch, fused_actor_step, micros[0], weight, cfg, scale, dev)
+        weight.grad = None
+        torch.cuda.synchronize()
 
     torch.cuda.reset_peak_memory_stats(dev)
     sampler = ClockSampler(local_rank)
@@ -733,7 +843,7 @@ def run_ours(args, name, cfg):
     if rank == 0:
         peaks = _peaks()
         # per-kernel roofline: algorithmic flops of one launch of each tcgen05 kernel / its CUDA-event duration
-        t_rows = T if kind != "actor" else None
+        t_rows = T if kind != "actor" else sum(window_rows)  # actor: the lm-head runs on the response-window rows only
         kern = {}
         for k, ms in per_launch:
             if ms >= 0:
@@ -746,12 +856,13 @@ def run_ours(args, name, cfg):
             per_step = len(v) / args.steps
             tot = sum(v) / args.steps
             entry = {"launches_per_step": per_step, "ms_per_step": tot}
-            if kind != "actor" and k in ("lm_head_fwd", "dlogits_recompute", "d_weight_gemm", "d_hidden_gemm"):
+            if k in ("lm_head_fwd", "dlogits_recompute", "d_weight_gemm", "d_hidden_gemm"):
                 tf = flops_fwd / (tot * 1e-3) / 1e12  # each of the four covers 2*T*H*V/N flops per step
                 entry.update(algorithmic_flops_per_step=flops_fwd, tflops=tf, frac_of_sustained=tf / peaks["sustained"],
                              frac_of_burst=tf / peaks["burst"])
             kernels_out[k] = entry
         fwd_kernel_ms = kernels_out.get("lm_head_fwd", {}).get("ms_per_step") or fwd_ms
+        n_fwd = kernels_out.get("lm_head_fwd", {}).get("launches_per_step") or 1.0  # c3: one launch per micro-batch
         fwd_tf = flops_fwd / (fwd_kernel_ms * 1e-3) / 1e12 if (fwd_kernel_ms and flops_fwd) else None
         step_useful_tf = 3 * flops_fwd / (ms_dev * 1e-3) / 1e12 if flops_fwd else None
         step_exec_tf = 4 * flops_fwd / (ms_dev * 1e-3) / 1e12 if flops_fwd else None
@@ -790,7 +901,8 @@ def run_ours(args, name, cfg):
                                 "algorithmic operand bytes = 2*(T*H + V*H) + 16*S*T",
                 "peak_source": peaks["source"] + ", sustained bf16 figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": fwd_tf / peaks["burst"] if fwd_tf else None,
-                "algorithmic_flops_per_launch": flops_fwd, "launch_ms": fwd_kernel_ms,
+                "algorithmic_flops_per_launch": flops_fwd / n_fwd, "launch_ms": fwd_kernel_ms / n_fwd if fwd_kernel_ms else None,
+                "launches_per_step": n_fwd,
                 "timed_with": "CUDA events around the launch on its own stream (vpg_timing_*), averaged over the timed steps",
             },
             "roofline_kernels": kernels_out,
