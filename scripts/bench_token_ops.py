@@ -110,7 +110,10 @@ def ops_table(d, B, L, n_uid):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--tokens-log2", type=int, default=25)
+    ap.add_argument("--only", default="", help="comma-separated substrings: run only the ops whose name contains one")
+    ap.add_argument("--no-configs", action="store_true", help="skip the latencies at the BASELINE config sizes")
     args = ap.parse_args()
+    only = [x for x in args.only.split(",") if x]
     dev = torch.device("cuda:0")
     peak, src = peak_hbm()
     out = []
@@ -118,6 +121,8 @@ def main():
     B = (1 << args.tokens_log2) // L
     d = make(B, L, dev)
     for name, fn, nbytes in ops_table(d, B, L, 8):
+        if only and not any(o in name for o in only):
+            continue
         ms = timeit(fn)
         gbs = nbytes / (ms * 1e-3) / 1e9
         rec = {"op": name, "tokens": B * L, "ms": round(ms, 4), "algorithmic_bytes": nbytes, "achieved_gbs": round(gbs, 1),
@@ -125,10 +130,14 @@ def main():
         out.append(rec)
         print(json.dumps(rec), flush=True)
     del d
+    if args.no_configs:
+        return
     # latencies at config sizes: C1 40x512, C3 128x1024 (n=8), C5 16x16384
     for cname, (B, L, n_uid) in {"C1 40x512": (40, 512, 5), "C3 128x1024": (128, 1024, 8), "C5 16x16384": (16, 16384, 4)}.items():
         d = make(B, L, dev)
         for name, fn, nbytes in ops_table(d, B, L, n_uid):
+            if only and not any(o in name for o in only):
+                continue
             ms = timeit(fn, iters=50, warmup=5)
             print(json.dumps({"config": cname, "op": name, "tokens": B * L, "us": round(ms * 1e3, 2)}), flush=True)
 

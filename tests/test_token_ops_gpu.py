@@ -96,6 +96,51 @@ def test_policy_loss_mask_dtypes_and_unaligned(mask_dtype, L, dev):
     close(lp_g.grad, lp_c.grad, rel=REL, abs_=1e-9)
 
 
+@pytest.mark.parametrize("mask_kind", ["binary_i64", "float_weights", "int_two", "int_wide"])
+@pytest.mark.parametrize("kl", [False, True])
+@pytest.mark.parametrize("shape", [(9, 64), (3, 4096), (700, 1024)])
+def test_fused_actor_loss_weighted_masks(mask_kind, kl, shape, dev):
+    """Token-mean loss WITH gradients over masks that are weights rather than 0/1 flags (the reference's masked_mean takes
+    any mask values): float weights, an integer 2, a value that does not fit a byte.  The vector path of this call is the
+    cooperative single-pass kernel (mask bits kept in shared memory for 0/1 masks, the mask re-read otherwise); the three
+    shapes give one slice unit per block, several units per block, and more blocks than one wave of SMs."""
+    from verl_b200.trainer.ppo import core_algos as ca
+
+    torch.manual_seed(11)
+    B, L = shape
+    lens = torch.randint(1, L + 1, (B,))
+    on = (torch.arange(L)[None] < lens[:, None])
+    if mask_kind == "binary_i64":
+        mask = on.long()
+    elif mask_kind == "float_weights":
+        mask = on.float() * (0.25 + torch.rand(B, L))
+    elif mask_kind == "int_two":
+        mask = on.long() * torch.randint(1, 3, (B, L))
+    else:
+        mask = on.long() * torch.where(torch.rand(B, L) < 0.1, 300, 1)
+    old = -torch.rand(B, L) * 3
+    lp = old + 0.3 * torch.randn(B, L)
+    ref = old + 0.2 * torch.randn(B, L)
+    adv = torch.randn(B, L)
+    ent = torch.rand(B, L)
+    kw = dict(cliprange_low=0.2, cliprange_high=0.28, clip_ratio_c=3.0, entropy_coeff=1e-3, kl_loss_coef=0.01 if kl else 0.0,
+              loss_scale=0.5)
+    lp_c, ent_c = lp.clone().requires_grad_(True), ent.clone().requires_grad_(True)
+    want, sc = port.actor_loss(old, lp_c, adv, mask, entropy=ent_c, ref_log_prob=ref if kl else None, **kw)
+    want.backward()
+    lp_g, ent_g = lp.to(dev).requires_grad_(True), ent.to(dev).requires_grad_(True)
+    loss, metrics = ca.fused_actor_loss(old.to(dev), lp_g, adv.to(dev), mask.to(dev), entropy=ent_g,
+                                        ref_log_prob=ref.to(dev) if kl else None, **kw)
+    loss.backward()
+    np.testing.assert_allclose(float(loss), float(want), rtol=REL, atol=1e-8)
+    got = metrics.cpu().numpy()
+    np.testing.assert_allclose(got[1:5], [float(sc[k]) for k in ("pg_loss", "pg_clipfrac", "ppo_kl", "pg_clipfrac_lower")],
+                               rtol=REL, atol=1e-8)
+    np.testing.assert_allclose(got[7], float(mask.sum()), rtol=1e-6)
+    close(lp_g.grad, lp_c.grad, rel=REL, abs_=1e-9)
+    close(ent_g.grad, ent_c.grad, rel=REL, abs_=1e-10)
+
+
 def test_agg_loss_and_kl_penalty(dev):
     from verl_b200.trainer.ppo import core_algos as ca
 

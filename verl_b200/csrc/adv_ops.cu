@@ -233,7 +233,7 @@ template <typename MT, int MODE>
 __global__ void __launch_bounds__(512)
 reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ mask, const float* __restrict__ baselines,
                     long long L, float gamma, float* __restrict__ adv_out, float* __restrict__ ret_out,
-                    double* __restrict__ sums, int vec) {
+                    double* __restrict__ sums, int vec, int* status) {
     __shared__ Lin warp_maps[32];
     __shared__ float carry;
     __shared__ double red[32];
@@ -346,6 +346,7 @@ reverse_scan_kernel(const float* __restrict__ rewards, const MT* __restrict__ ma
             atomicAdd(&sums[1], d2);
             atomicAdd(&sums[2], dc);
         }
+        whiten_publish_status(sums, status);
     }
 }
 
@@ -354,7 +355,7 @@ template <int VEC, typename MT>
 __global__ void whiten_mask_apply_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
                                          const double* __restrict__ sums, float* __restrict__ out) {
     const double N = sums[2];
-    if (N == 0.0 || N == 1.0) return;  // status word: whiten_status_kernel
+    if (N == 0.0 || N == 1.0) return;  // status word: whiten_publish_status
     const double den = N + 1e-8;
     const double mean_d = sums[0] / den;
     double var_d = (sums[1] - 2.0 * mean_d * sums[0] + mean_d * mean_d * N) / den;
@@ -404,7 +405,7 @@ int vpg_outcome_advantage(int kind, const float* rewards, const void* mask, int 
     VPG_CUDA(cudaMemsetAsync(workspace, 0, static_cast<size_t>(2 * B + (kGStat + 2) * G) * sizeof(double), stream));
     VPG_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {rewards, advantages});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 32);
     const unsigned grid = static_cast<unsigned>(B * gx);
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
@@ -431,9 +432,9 @@ size_t vpg_reverse_scan_workspace_bytes(int64_t B, int64_t L) {
     return 4 * sizeof(double);
 }
 
-static inline unsigned scan_threads(int64_t L) {
+static inline unsigned scan_threads(int64_t B, int64_t L) {
     int64_t threads = round_up(ceil_div(L, kScanSeg), 32);
-    if (threads > 512) threads = 512;
+    if (threads > scan_block_threads(B)) threads = scan_block_threads(B);
     return static_cast<unsigned>(threads);
 }
 
@@ -451,10 +452,10 @@ int vpg_reinforce_plus_plus(const float* rewards, const void* mask, int mask_dty
     const bool vec = rows_vec_ok(n, mask, mask_dtype, {rewards, returns, advantages});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
-        reverse_scan_kernel<MT, 0><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
-            rewards, mk, nullptr, L, gamma, advantages, returns, sums, (L % kScanSeg == 0) && vec);
+        reverse_scan_kernel<MT, 0><<<static_cast<unsigned>(B), scan_threads(B, L), 0, stream>>>(
+            rewards, mk, nullptr, L, gamma, advantages, returns, sums, (L % kScanSeg == 0) && vec, status);
         count_launch();
-        VPG_CUDA(publish_whiten_status(sums, status, status_event, stream));
+        VPG_CUDA(record_whiten_status(status_event, stream));
         if (vec)
             whiten_mask_apply_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(returns, mk, n, sums, advantages);
         else
@@ -471,8 +472,8 @@ int vpg_remax(const float* rewards, const float* reward_baselines, const void* m
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int vec = (L % kScanSeg == 0) && rows_vec_ok(L, mask, mask_dtype, {rewards, advantages, returns});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
-        reverse_scan_kernel<MT, 1><<<static_cast<unsigned>(B), scan_threads(L), 0, stream>>>(
-            rewards, static_cast<const MT*>(mask), reward_baselines, L, 1.f, advantages, returns, nullptr, vec);
+        reverse_scan_kernel<MT, 1><<<static_cast<unsigned>(B), scan_threads(B, L), 0, stream>>>(
+            rewards, static_cast<const MT*>(mask), reward_baselines, L, 1.f, advantages, returns, nullptr, vec, nullptr);
     });
     VPG_LAUNCH_CHECK();
     return VPG_OK;
@@ -760,7 +761,7 @@ int vpg_kl_reward(const float* token_level_scores, const float* old_log_probs, c
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {token_level_scores, old_log_probs, ref_log_prob, token_level_rewards});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 32);
     const unsigned grid = static_cast<unsigned>(B * gx);
     double* ws = static_cast<double*>(workspace);
     VPG_DISPATCH_MASK(mask_dtype, MT, {
@@ -800,7 +801,7 @@ int vpg_data_metrics(const float* token_level_scores, const float* token_level_r
     VPG_CUDA(cudaMemcpyAsync(keys, init_keys, sizeof(init_keys), cudaMemcpyHostToDevice, stream));
     const bool vec = rows_vec_ok(L, response_mask, rmask_dtype,
                                  {token_level_scores, token_level_rewards, advantages, returns, values});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 16);
     VPG_DISPATCH_MASK(rmask_dtype, MT, {
         if (vec)
             data_metrics_kernel<4, MT><<<static_cast<unsigned>(B * gx), kThreads, 0, stream>>>(

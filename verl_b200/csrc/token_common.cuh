@@ -49,11 +49,14 @@ __device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pa
 }
 
 // Blocks per row.  The grid should be MANY waves of the resident blocks (4-8 per SM) whenever the problem allows it: with
-// ~2.5 waves (2048 rows, one block each) the last, partial wave costs 10-25 % of the sweep.  Target: `VPG_TOK_BLOCKS_PER_SM`
-// blocks per SM in total, never less than two iterations of work per block.  Default 8: more blocks cost more than the
-// partial last wave in every kernel that ends in per-block atomics (A/B at 8..128 per SM: profiles/r2_ab_token_grid.txt).
-static inline int blocks_per_row(int64_t B, int64_t L, int vec) {
-    static const int per_sm = env_int("VPG_TOK_BLOCKS_PER_SM", 8);
+// ~2.5 waves (2048 rows, one block each) the last, partial wave costs 10-25 % of the sweep — but every block ends in
+// barriers and atomics, so how finely a sweep may be cut depends on its epilogue.  `per_sm` is the kernel's own target of
+// blocks per SM in total (never less than two iterations of work per block), from the A/B at 8 / 16 / 32 per SM after the
+// epilogues were fused (profiles/r2_ab_token_grid.txt): 8 for the fused loss (seven block sums), 16 for the sweeps with
+// two or three sums, 32 for the ones that end in one atomic or none.  `VPG_TOK_BLOCKS_PER_SM` overrides all of them.
+static inline int blocks_per_row(int64_t B, int64_t L, int vec, int per_sm = 8) {
+    static const int forced = env_int("VPG_TOK_BLOCKS_PER_SM", 0);
+    if (forced > 0) per_sm = forced;
     const int64_t per_block = static_cast<int64_t>(kThreads) * vec * 2;
     int64_t need = ceil_div(L, per_block);
     int64_t want = ceil_div(static_cast<int64_t>(sm_count()) * per_sm, B > 0 ? B : 1);
@@ -91,6 +94,22 @@ __device__ __forceinline__ float min_nan(float a, float b) {
 }
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return min_nan(max_nan(x, lo), hi); }
 
+// Threads per block of the row-scan kernels (GAE, reverse scans): a block walks its row in chunks of threads * 8 tokens,
+// load -> compose -> barrier -> replay -> store, every chunk waiting for the carry of the one to its right.  The phases
+// of a block do not overlap each other, so what keeps HBM busy is the NUMBER of independent blocks on an SM, not their
+// size.  `VPG_SCAN_THREADS` (32..512, multiple of 32) overrides the choice below.
+static inline int scan_block_threads(int64_t rows) {
+    static const int forced = [] {
+        int v = env_int("VPG_SCAN_THREADS", 0);
+        v = (v / 32) * 32;
+        return v <= 0 ? 0 : (v > 512 ? 512 : v);
+    }();
+    if (forced) return forced;
+    // many rows: 256 threads, four blocks per SM (A/B at 2048 rows: GAE 0.73 -> 0.81, reverse scans 0.79 -> 0.85 of HBM
+    // peak); few rows (16 x 16384 at BASELINE configs[4]): the row is the critical path, the widest block is the fastest
+    return rows >= 2 * static_cast<int64_t>(sm_count()) ? 256 : 512;
+}
+
 static inline int flat_grid(int64_t n, int vec) {
     int64_t g = ceil_div(n, static_cast<int64_t>(kThreads) * vec * 4);
     const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
@@ -109,21 +128,26 @@ static inline bool rows_vec_ok(int64_t L, const void* mask, int mask_dtype, std:
 }
 
 
-// masked_whiten's error status (torch_functional.py:195-200: the reference raises when the mask sums to 0 or 1),
-// published by a one-thread kernel BETWEEN the statistics pass and the normalisation pass: `status` may be a pinned
-// (UVA-mapped) host word and `status_event` a cudaEvent_t recorded right behind it, so the host can learn the
-// status — and raise like the reference — while the normalisation pass is still running.
-static __global__ void whiten_status_kernel(const double* __restrict__ sums, int* status) {
-    const double N = sums[2];
-    *status = (N == 0.0) ? 1 : (N == 1.0) ? 2 : 0;
-    __threadfence_system();
+// masked_whiten's error status (torch_functional.py:195-200: the reference raises when the mask sums to 0 or 1).  The
+// kernel that produces the statistics publishes it from its LAST block (sums[3] is the arrival counter, zeroed with the
+// sums): `status` may be a pinned (UVA-mapped) host word and `status_event` a cudaEvent_t recorded right behind that
+// kernel, so the host learns the status — and raises like the reference — while the normalisation pass is still
+// running.  No launch of its own (the one-thread status kernel of round 1 cost 5.5 us between the two passes).
+__device__ __forceinline__ void whiten_publish_status(double* sums, int* status) {
+    // Only thread 0 wrote to `sums` (three atomics): it alone fences before it counts the block in.  A block-wide
+    // __threadfence here would hold every warp until its own output stores have drained (measured: -3 % on the scans).
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(reinterpret_cast<unsigned int*>(&sums[3]), 1u) == gridDim.x - 1) {
+            __threadfence();
+            const double N = __ldcg(&sums[2]);
+            *status = (N == 0.0) ? 1 : (N == 1.0) ? 2 : 0;
+            __threadfence_system();
+        }
+    }
 }
-static inline cudaError_t publish_whiten_status(const double* sums, int* status, void* status_event,
-                                                cudaStream_t stream) {
-    whiten_status_kernel<<<1, 1, 0, stream>>>(sums, status);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess && status_event) e = cudaEventRecord(static_cast<cudaEvent_t>(status_event), stream);
-    return e;
+static inline cudaError_t record_whiten_status(void* status_event, cudaStream_t stream) {
+    return status_event ? cudaEventRecord(static_cast<cudaEvent_t>(status_event), stream) : cudaSuccess;
 }
 
 // Warp-shuffle segmented reduction: sum of `v` over the lanes in `peers` (the lane set `__match_any_sync` returned for this

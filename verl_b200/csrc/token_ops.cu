@@ -10,6 +10,8 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
+#include <type_traits>
+
 #include "token_common.cuh"
 
 namespace vpg {
@@ -112,7 +114,8 @@ __global__ void kl_penalty_kernel(const float* __restrict__ lp, const float* __r
 // Fused PPO actor loss.  compute_policy_loss (core_algos.py:722-794) + agg_loss (:686-719) + kl_penalty (:1034-1069)
 // composed as in verl/workers/actor/dp_actor.py:422-469, forward and closed-form gradient.
 //
-// workspace (doubles): [0] two uint32 counters | [1] N = sum(mask) | [2..10) global sums G[8] |
+// workspace (doubles): [0] two uint32 counters | [1] N = sum(mask) | [2..8) global sums G[6] | [8] a mask value does not
+//                      fit the one-byte copy (coop kernel: is not 0 / 1) | [9] a mask value is neither 0 nor 1 |
 //                      [10, 10+B) row mask sums | [10+B, 10+4B) row sums of {pg, entropy, kl} * mask
 //   G: 0 pg 1 -log_ratio 2 clip 3 clip_lower 4 entropy 5 kl   (all weighted where(m,v,0)*m as masked_mean does)
 // =====================================================================================================
@@ -150,11 +153,14 @@ __global__ void mask_count_kernel(const MT* __restrict__ mask, long long B, long
     const int cx = blockIdx.x % gx;
     const long long base = b * L;
     float c = 0.f;
-    bool wide = false;
+    bool wide = false, odd = false;
     const long long stride = static_cast<long long>(gx) * blockDim.x * VEC;
     auto take = [&](const Pack<VEC>& m, long long t) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) c += m.v[j];
+        for (int j = 0; j < VEC; ++j) {
+            c += m.v[j];
+            odd |= !(m.v[j] == 0.f || m.v[j] == 1.f);
+        }
         if (cmask) {
             unsigned char q[VEC];
 #pragma unroll
@@ -191,6 +197,7 @@ __global__ void mask_count_kernel(const MT* __restrict__ mask, long long B, long
     }
     if (t < L) take(ldm<VEC, MT>(mask, base + t), t);
     if (cmask && __syncthreads_or(wide ? 1 : 0) && threadIdx.x == 0) ws[8] = 1.0;  // benign race: every writer stores 1
+    if (__syncthreads_or(odd ? 1 : 0) && threadIdx.x == 0) ws[9] = 1.0;            // a value that is neither 0 nor 1
     const double bc = block_sum<double>(static_cast<double>(c), red);
     if (threadIdx.x == 0) atomicAdd(&ws[kWsHeader + b], bc);
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
@@ -224,16 +231,154 @@ __device__ __forceinline__ double agg_finalize(int mode, const double* row_sum, 
     return s / static_cast<double>(B);
 }
 
-// kCount: forward only with token-mean aggregation — nothing needs the normaliser before the sweep, so the mask count is
-// taken in the same pass (no mask_count_kernel launch, the mask read once).
+// ---- the per-token body of the fused loss, shared by the row-wise kernel and the cooperative single-pass kernel ----
 // kSpec: 0 = every option read at run time; 1 / 2 = the two configurations the BASELINE recipes run (clip loss,
 // token-mean, 1: no KL term, 2: low_var_kl) with the options folded at compile time — the sweep is ISSUE-bound (ncu of the
 // generic body: ~150 instructions per token, sm throughput 66-72 % at 55 % of DRAM peak), so dead accumulators, option
-// tests and the select-on-isnan clamps are what the specialisation removes (~90 per token).
+// tests and the select-on-isnan clamps are what the specialisation removes (~105 per token).
+struct PpoOpts {
+    bool where_w, gpg, has_ent, has_kl, want_grad;
+    int kl_kind;
+    float ent_g;
+};
+template <int kSpec>
+__device__ __forceinline__ PpoOpts ppo_opts(const PpoParams& p, bool want_grad) {
+    PpoOpts o;
+    o.where_w = kSpec ? true : (p.agg_mode == VPG_AGG_TOKEN_MEAN);
+    o.gpg = kSpec ? false : (p.pg_kind == VPG_PG_GPG);
+    o.has_ent = p.entropy != nullptr;
+    o.has_kl = kSpec == 1 ? false : kSpec == 2 ? true : (p.ref_lp != nullptr && p.kl_kind >= 0);
+    o.kl_kind = kSpec == 2 ? static_cast<int>(VPG_KL_LOW_VAR) : p.kl_kind;
+    o.want_grad = want_grad;
+    o.ent_g = -p.entropy_coeff;
+    return o;
+}
+struct PpoAcc {
+    float a_pg = 0.f, a_lr = 0.f, a_clip = 0.f, a_low = 0.f, a_ent = 0.f, a_kl = 0.f;  // where-weighted (masked_mean)
+    float r_pg = 0.f, r_ent = 0.f, r_kl = 0.f;                                           // plain v*m (row sums)
+    float a_cnt = 0.f;                                                                   // sum of the mask (kCount)
+};
+
+// kBin: the caller knows that every mask value is 0 or 1 (flag from the mask pass), so `where(m, x, 0) * m` is the select
+// alone and the gradient weight is `coef` or 0 — bit-identical results, one multiply less per accumulator.
+template <int VEC, bool kCount, bool kBin>
+__device__ __forceinline__ void ppo_pack(const PpoParams& p, const PpoOpts& o, float coef, const Pack<VEC>& m,
+                                         const Pack<VEC>& old, const Pack<VEC>& lp, const Pack<VEC>& adv,
+                                         const Pack<VEC>& ent, const Pack<VEC>& ref, Pack<VEC>& dlp, Pack<VEC>& dent,
+                                         PpoAcc& a) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const float mj = m.v[j];
+        const bool on = mj != 0.f;
+        if (kCount) a.a_cnt += mj;
+        const float A = adv.v[j];
+        const float lr_raw = lp.v[j] - old.v[j];
+        const float lr = clampf(lr_raw, -20.f, 20.f);
+        const float ratio = expf(lr);
+        const float l1 = -A * ratio;
+        const float rc = clampf(ratio, p.ratio_lo, p.ratio_hi);
+        const float l2 = -A * rc;
+        const float c1 = max_nan(l1, l2);
+        const float l3 = -A * p.clip_c;
+        const float c2 = min_nan(l3, c1);
+        const float pg = o.gpg ? (-lp.v[j] * A) : ((A < 0.f) ? c2 : c1);
+        const bool clipped = !o.gpg && (l2 > l1);
+        const bool low = !o.gpg && (c1 > l3) && (A < 0.f);
+        auto wsum = [&](float& accu, bool sel, float x) {  // accu += where(m, x, 0) * m
+            if (kBin) accu += sel ? x : 0.f;
+            else accu += (sel ? x : 0.f) * mj;
+        };
+        wsum(a.a_pg, on, pg);
+        wsum(a.a_lr, on && !o.gpg, -lr);
+        wsum(a.a_clip, on && clipped, 1.f);
+        wsum(a.a_low, on && low, 1.f);
+        if (!o.where_w) a.r_pg += pg * mj;
+        float g = 0.f;
+        if (o.want_grad) {
+            // gradient of pg wrt log_prob (ties of maximum / min split 1/2, as torch autograd does); d l1 = l1
+            const bool in_lr = (lr_raw >= -20.f) && (lr_raw <= 20.f);
+            const float dl1 = in_lr ? l1 : 0.f;
+            const bool in_clip = (ratio >= p.ratio_lo) && (ratio <= p.ratio_hi);
+            const float dl2 = in_clip ? dl1 : 0.f;
+            const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
+            const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
+            g = o.gpg ? -A : ((A < 0.f) ? g_c2 : g_c1);
+        }
+        if (o.has_kl) {
+            float kv, kg;
+            kl_term(o.kl_kind, lp.v[j], ref.v[j], kv, kg);
+            wsum(a.a_kl, on, kv);
+            if (!o.where_w) a.r_kl += kv * mj;
+            g += p.kl_coef * kg;
+        }
+        const float cw = (kBin && o.where_w) ? (on ? coef : 0.f) : coef * (o.where_w ? (on ? mj : 0.f) : mj);
+        dlp.v[j] = cw * g;
+        if (o.has_ent) {
+            wsum(a.a_ent, on, ent.v[j]);
+            if (!o.where_w) a.r_ent += ent.v[j] * mj;
+            dent.v[j] = cw * o.ent_g;
+        }
+    }
+}
+
+// block sums + atomics of one block's accumulators: six global sums (+ the mask count) behind one barrier pair, the three
+// row sums of the seq-mean modes behind a second one
+template <bool kCount>
+__device__ __forceinline__ void ppo_block_reduce(const PpoParams& p, const PpoOpts& o, const PpoAcc& a, long long b,
+                                                 double* red_n /* 7 * 32 */) {
+    double tot[7] = {a.a_pg, a.a_lr, a.a_clip, a.a_low, a.a_ent, a.a_kl, a.a_cnt};
+    block_sum_n<7>(tot, red_n);
+    double rtot[3] = {a.r_pg, a.r_ent, a.r_kl};
+    if (!o.where_w) block_sum_n<3>(rtot, red_n);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) atomicAdd(&p.ws[2 + k], tot[k]);
+        if (kCount) atomicAdd(&p.ws[1], tot[6]);
+        if (!o.where_w) {  // row sums feed the seq-mean modes only
+            double* rows = p.ws + kWsHeader + p.B;
+            atomicAdd(&rows[b], rtot[0]);
+            atomicAdd(&rows[p.B + b], rtot[1]);
+            atomicAdd(&rows[2 * p.B + b], rtot[2]);
+        }
+    }
+}
+
+// run by every thread of the LAST block: aggregated losses -> metrics[8]
+__device__ __forceinline__ void ppo_finalize(const PpoParams& p, const PpoOpts& o, double n_total, double* red) {
+    double* ws = p.ws;
+    const double* rcnt = ws + kWsHeader;
+    const double* rows = ws + kWsHeader + p.B;
+    const double G0 = __ldcg(&ws[2]), G1 = __ldcg(&ws[3]), G2 = __ldcg(&ws[4]), G3 = __ldcg(&ws[5]);
+    const double G4 = __ldcg(&ws[6]), G5 = __ldcg(&ws[7]);
+    const double pg_loss = agg_finalize(p.agg_mode, rows, rcnt, G0, n_total, p.B, p.L, red);
+    const double ent_loss = o.has_ent ? agg_finalize(p.agg_mode, rows + p.B, rcnt, G4, n_total, p.B, p.L, red) : 0.0;
+    const double kl_loss = o.has_kl ? agg_finalize(p.agg_mode, rows + 2 * p.B, rcnt, G5, n_total, p.B, p.L, red) : 0.0;
+    if (threadIdx.x == 0) {
+        // fp32 composition as in dp_actor.py:445-469
+        const float pgf = static_cast<float>(pg_loss), entf = static_cast<float>(ent_loss);
+        const float klf = static_cast<float>(kl_loss);
+        float policy = pgf;
+        if (o.has_ent && p.entropy_coeff != 0.f) policy = policy - entf * p.entropy_coeff;
+        if (o.has_kl) policy = policy + klf * p.kl_coef;
+        const double den = n_total + 1e-8;
+        p.metrics[0] = policy * p.loss_scale;
+        p.metrics[1] = pgf;
+        p.metrics[2] = static_cast<float>(G2 / den);
+        p.metrics[3] = static_cast<float>(G1 / den);
+        p.metrics[4] = static_cast<float>(G3 / den);
+        p.metrics[5] = entf;
+        p.metrics[6] = klf;
+        p.metrics[7] = static_cast<float>(n_total);
+    }
+}
+
+// kCount: forward only with token-mean aggregation — nothing needs the normaliser before the sweep, so the mask count is
+// taken in the same pass (no mask_count_kernel launch, the mask read once).
 template <int VEC, typename MT, bool kCount, int kSpec>
 __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p, const MT* __restrict__ mask,
                                                                const unsigned char* __restrict__ cmask) {
     __shared__ double red[32];
+    __shared__ double red_n[7 * 32];
     const bool compact = !kCount && cmask != nullptr && p.ws[8] == 0.0;  // the one-byte copy holds every mask value exactly
     const long long b = blockIdx.x / p.gx;
     const int cx = blockIdx.x % p.gx;
@@ -242,125 +387,127 @@ __global__ void __launch_bounds__(kThreads, 4) ppo_loss_kernel(const PpoParams p
     double n_total = kCount ? 0.0 : ws[1];
     const double row_cnt = kCount ? 1.0 : ws[kWsHeader + b];
     const float coef = kCount ? 0.f : agg_coef(p.agg_mode, n_total, row_cnt, p.B, p.L) * p.loss_scale;
-    float a_cnt = 0.f;
-    const bool where_w = kSpec ? true : (p.agg_mode == VPG_AGG_TOKEN_MEAN);
-    const bool gpg = kSpec ? false : (p.pg_kind == VPG_PG_GPG);
-    const bool has_ent = p.entropy != nullptr;
-    const bool has_kl = kSpec == 1 ? false : kSpec == 2 ? true : (p.ref_lp != nullptr && p.kl_kind >= 0);
-    const int kl_kind = kSpec == 2 ? static_cast<int>(VPG_KL_LOW_VAR) : p.kl_kind;
-    const bool want_grad = !kCount && p.d_lp != nullptr;  // kCount: no gradient outputs, the gradient arithmetic is dead code
-    const float ent_g = -p.entropy_coeff;
-
-    float a_pg = 0.f, a_lr = 0.f, a_clip = 0.f, a_low = 0.f, a_ent = 0.f, a_kl = 0.f;  // where-weighted
-    float r_pg = 0.f, r_ent = 0.f, r_kl = 0.f;                                           // plain v*m (row sums)
+    // kCount: no gradient outputs, the gradient arithmetic is dead code
+    const PpoOpts o = ppo_opts<kSpec>(p, !kCount && p.d_lp != nullptr);
+    PpoAcc acc;
     const long long stride = static_cast<long long>(p.gx) * blockDim.x * VEC;
-    for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < p.L; t += stride) {
-        const long long i = base + t;
-        const Pack<VEC> m = compact ? ldm<VEC, unsigned char>(cmask, i) : ldm<VEC, MT>(mask, i);
-        const Pack<VEC> old = ldv<VEC>(p.old_lp, i);
-        const Pack<VEC> lp = ldv<VEC>(p.lp, i);
-        const Pack<VEC> adv = ldv<VEC>(p.adv, i);
-        Pack<VEC> ent, ref, dlp, dent;
-        if (has_ent) ent = ldv<VEC>(p.entropy, i);
-        if (has_kl) ref = ldv<VEC>(p.ref_lp, i);
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            const float mj = m.v[j];
-            const bool on = mj != 0.f;
-            if (kCount) a_cnt += mj;
-            const float A = adv.v[j];
-            const float lr_raw = lp.v[j] - old.v[j];
-            const float lr = clampf(lr_raw, -20.f, 20.f);
-            const float ratio = expf(lr);
-            const float l1 = -A * ratio;
-            const float rc = clampf(ratio, p.ratio_lo, p.ratio_hi);
-            const float l2 = -A * rc;
-            const float c1 = max_nan(l1, l2);
-            const float l3 = -A * p.clip_c;
-            const float c2 = min_nan(l3, c1);
-            const float pg = gpg ? (-lp.v[j] * A) : ((A < 0.f) ? c2 : c1);
-            const bool clipped = !gpg && (l2 > l1);
-            const bool low = !gpg && (c1 > l3) && (A < 0.f);
-            a_pg += (on ? pg : 0.f) * mj;
-            a_lr += ((on && !gpg) ? -lr : 0.f) * mj;
-            a_clip += ((on && clipped) ? 1.f : 0.f) * mj;
-            a_low += ((on && low) ? 1.f : 0.f) * mj;
-            if (!where_w) r_pg += pg * mj;
-            float g = 0.f;
-            if (want_grad) {
-                // gradient of pg wrt log_prob (ties of maximum / min split 1/2, as torch autograd does); d l1 = l1
-                const bool in_lr = (lr_raw >= -20.f) && (lr_raw <= 20.f);
-                const float dl1 = in_lr ? l1 : 0.f;
-                const bool in_clip = (ratio >= p.ratio_lo) && (ratio <= p.ratio_hi);
-                const float dl2 = in_clip ? dl1 : 0.f;
-                const float g_c1 = (l1 > l2) ? dl1 : ((l1 < l2) ? dl2 : 0.5f * (dl1 + dl2));
-                const float g_c2 = (c1 < l3) ? g_c1 : ((c1 == l3) ? 0.5f * g_c1 : 0.f);
-                g = gpg ? -A : ((A < 0.f) ? g_c2 : g_c1);
-            }
-            if (has_kl) {
-                float kv, kg;
-                kl_term(kl_kind, lp.v[j], ref.v[j], kv, kg);
-                a_kl += (on ? kv : 0.f) * mj;
-                if (!where_w) r_kl += kv * mj;
-                g += p.kl_coef * kg;
-            }
-            const float cw = coef * (where_w ? (on ? mj : 0.f) : mj);
-            dlp.v[j] = cw * g;
-            if (has_ent) {
-                a_ent += (on ? ent.v[j] : 0.f) * mj;
-                if (!where_w) r_ent += ent.v[j] * mj;
-                dent.v[j] = cw * ent_g;
-            }
+    auto sweep = [&](auto bin) {
+        constexpr bool kBin = decltype(bin)::value;
+        for (long long t = (static_cast<long long>(cx) * blockDim.x + threadIdx.x) * VEC; t < p.L; t += stride) {
+            const long long i = base + t;
+            const Pack<VEC> m = compact ? ldm<VEC, unsigned char>(cmask, i) : ldm<VEC, MT>(mask, i);
+            const Pack<VEC> old = ldv<VEC>(p.old_lp, i);
+            const Pack<VEC> lp = ldv<VEC>(p.lp, i);
+            const Pack<VEC> adv = ldv<VEC>(p.adv, i);
+            Pack<VEC> ent, ref, dlp, dent;
+            if (o.has_ent) ent = ldv<VEC>(p.entropy, i);
+            if (o.has_kl) ref = ldv<VEC>(p.ref_lp, i);
+            ppo_pack<VEC, kCount, kBin>(p, o, coef, m, old, lp, adv, ent, ref, dlp, dent, acc);
+            if (o.want_grad) stv<VEC>(p.d_lp, i, dlp);
+            if (!kCount && p.d_ent && o.has_ent) stv<VEC>(p.d_ent, i, dent);
         }
-        if (want_grad) stv<VEC>(p.d_lp, i, dlp);
-        if (!kCount && p.d_ent && has_ent) stv<VEC>(p.d_ent, i, dent);
-    }
-    // one barrier pair for the block sums of the sweep (six global sums + the mask count), a second one for the three row
-    // sums of the seq-mean modes
-    __shared__ double red_n[7 * 32];
-    double tot[7] = {a_pg, a_lr, a_clip, a_low, a_ent, a_kl, a_cnt};
-    block_sum_n<7>(tot, red_n);
-    double rtot[3] = {r_pg, r_ent, r_kl};
-    if (!where_w) block_sum_n<3>(rtot, red_n);
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) atomicAdd(&ws[2 + k], tot[k]);
-        if (kCount) atomicAdd(&ws[1], tot[6]);
-        if (!where_w) {  // row sums feed the seq-mean modes only
-            double* rows = ws + kWsHeader + p.B;
-            atomicAdd(&rows[b], rtot[0]);
-            atomicAdd(&rows[p.B + b], rtot[1]);
-            atomicAdd(&rows[2 * p.B + b], rtot[2]);
-        }
-    }
+    };
+    // the mask pass raises ws[9] when a mask value is neither 0 nor 1; the folded bodies then take the select-only sums
+    if (!kCount && kSpec != 0 && ws[9] == 0.0) sweep(std::true_type{});
+    else sweep(std::false_type{});
+    ppo_block_reduce<kCount>(p, o, acc, b, red_n);
     unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
     if (last_block_done(&counters[1], gridDim.x)) {
         if (kCount) n_total = __ldcg(&ws[1]);
-        const double* rcnt = ws + kWsHeader;
-        const double* rows = ws + kWsHeader + p.B;
-        const double G0 = __ldcg(&ws[2]), G1 = __ldcg(&ws[3]), G2 = __ldcg(&ws[4]), G3 = __ldcg(&ws[5]);
-        const double G4 = __ldcg(&ws[6]), G5 = __ldcg(&ws[7]);
-        const double pg_loss = agg_finalize(p.agg_mode, rows, rcnt, G0, n_total, p.B, p.L, red);
-        const double ent_loss = has_ent ? agg_finalize(p.agg_mode, rows + p.B, rcnt, G4, n_total, p.B, p.L, red) : 0.0;
-        const double kl_loss = has_kl ? agg_finalize(p.agg_mode, rows + 2 * p.B, rcnt, G5, n_total, p.B, p.L, red) : 0.0;
+        ppo_finalize(p, o, n_total, red);
+    }
+}
+
+// Token-mean loss WITH gradients in ONE launch and one read of the mask (cooperative launch, every block resident).  The
+// gradient of a token-mean loss needs sum(mask) before its first store, which is why the row-wise path runs a mask-only
+// pass first and re-reads a one-byte copy (38 bytes per token against the 36 of the inputs and outputs).  Here every
+// block owns a fixed set of 1024-token units of the flat [B*L] tokens: phase 1 streams their mask (four 128-bit loads in
+// flight), keeps one bit per token in shared memory and adds its count to ws[1]; after the grid barrier phase 2 streams
+// the float tensors once and takes the mask from shared memory.  Masks with values other than 0 / 1 (the reference allows
+// any weights) raise ws[8] in phase 1 and phase 2 re-reads them from global memory instead.
+constexpr int kCoopSliceUnit = kThreads * 4;         // tokens one block covers per step
+constexpr long long kCoopMaxSlice = 128 * 1024;      // tokens per block: 32 KB of shared memory (4 mask bits per byte)
+
+template <typename MT, int kSpec>
+__global__ void __launch_bounds__(kThreads, 4) ppo_loss_coop_kernel(const PpoParams p, const MT* __restrict__ mask,
+                                                                    long long n, long long iters) {
+    extern __shared__ unsigned char nib[];  // nib[it * kThreads + tid] = mask bits of the 4 tokens this thread owns in step it
+    __shared__ double red[32];
+    __shared__ double red_n[7 * 32];
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    double* ws = p.ws;
+    // step `it` of block b covers tokens [(it * gridDim.x + b) * kCoopSliceUnit, +kCoopSliceUnit): at any moment the grid
+    // streams ONE contiguous window of every tensor (contiguous per-block slices ran 25 % slower: 592 lock-step streams
+    // a fixed 224 KB apart)
+    const long long step = static_cast<long long>(gridDim.x) * kCoopSliceUnit;
+    const long long i0 = static_cast<long long>(blockIdx.x) * kCoopSliceUnit + static_cast<long long>(threadIdx.x) * 4;
+    // ---- phase 1: mask -> bits + count
+    {
+        float c = 0.f;
+        bool odd = false;
+        auto take = [&](const Pack<4>& m, long long it) {
+            unsigned int bits = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                c += m.v[j];
+                odd |= !(m.v[j] == 0.f || m.v[j] == 1.f);
+                bits |= (m.v[j] != 0.f ? 1u : 0u) << j;
+            }
+            nib[it * kThreads + threadIdx.x] = static_cast<unsigned char>(bits);
+        };
+        long long it = 0;
+        for (; it + 3 < iters && i0 + (it + 3) * step < n; it += 4) {
+            const long long i = i0 + it * step;
+            const Pack<4> m0 = ldm<4, MT>(mask, i), m1 = ldm<4, MT>(mask, i + step);
+            const Pack<4> m2 = ldm<4, MT>(mask, i + 2 * step), m3 = ldm<4, MT>(mask, i + 3 * step);
+            take(m0, it), take(m1, it + 1), take(m2, it + 2), take(m3, it + 3);
+        }
+        for (; it < iters && i0 + it * step < n; ++it) take(ldm<4, MT>(mask, i0 + it * step), it);
+        const int any_odd = __syncthreads_or(odd ? 1 : 0);
+        const double bc = block_sum<double>(static_cast<double>(c), red);
         if (threadIdx.x == 0) {
-            // fp32 composition as in dp_actor.py:445-469
-            const float pgf = static_cast<float>(pg_loss), entf = static_cast<float>(ent_loss);
-            const float klf = static_cast<float>(kl_loss);
-            float policy = pgf;
-            if (has_ent && p.entropy_coeff != 0.f) policy = policy - entf * p.entropy_coeff;
-            if (has_kl) policy = policy + klf * p.kl_coef;
-            const double den = n_total + 1e-8;
-            p.metrics[0] = policy * p.loss_scale;
-            p.metrics[1] = pgf;
-            p.metrics[2] = static_cast<float>(G2 / den);
-            p.metrics[3] = static_cast<float>(G1 / den);
-            p.metrics[4] = static_cast<float>(G3 / den);
-            p.metrics[5] = entf;
-            p.metrics[6] = klf;
-            p.metrics[7] = static_cast<float>(n_total);
+            atomicAdd(&ws[1], bc);
+            if (any_odd) ws[8] = 1.0;  // benign race: every writer stores 1
         }
     }
+    __threadfence();
+    grid.sync();
+    // ---- phase 2: the loss sweep
+    const double n_total = __ldcg(&ws[1]);
+    const bool binary = __ldcg(&ws[8]) == 0.0;
+    const float coef = agg_coef(VPG_AGG_TOKEN_MEAN, n_total, 1.0, p.B, p.L) * p.loss_scale;
+    const PpoOpts o = ppo_opts<kSpec>(p, p.d_lp != nullptr);
+    PpoAcc acc;
+    auto sweep = [&](auto bin) {
+        constexpr bool kBin = decltype(bin)::value;
+        for (long long it = 0; it < iters; ++it) {
+            const long long i = i0 + it * step;
+            if (i >= n) break;
+            Pack<4> m;
+            if (kBin) {
+                const unsigned int bits = nib[it * kThreads + threadIdx.x];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) m.v[j] = ((bits >> j) & 1u) ? 1.f : 0.f;
+            } else {
+                m = ldm<4, MT>(mask, i);
+            }
+            const Pack<4> old = ldv<4>(p.old_lp, i);
+            const Pack<4> lp = ldv<4>(p.lp, i);
+            const Pack<4> adv = ldv<4>(p.adv, i);
+            Pack<4> ent, ref, dlp, dent;
+            if (o.has_ent) ent = ldv<4>(p.entropy, i);
+            if (o.has_kl) ref = ldv<4>(p.ref_lp, i);
+            ppo_pack<4, false, kBin>(p, o, coef, m, old, lp, adv, ent, ref, dlp, dent, acc);
+            if (o.want_grad) stv<4>(p.d_lp, i, dlp);
+            if (p.d_ent && o.has_ent) stv<4>(p.d_ent, i, dent);
+        }
+    };
+    if (binary) sweep(std::true_type{});
+    else sweep(std::false_type{});
+    ppo_block_reduce<false>(p, o, acc, 0, red_n);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws);
+    if (last_block_done(&counters[1], gridDim.x)) ppo_finalize(p, o, n_total, red);
 }
 
 // agg_loss for an arbitrary loss matrix: forward sums + gradient d loss / d loss_mat
@@ -635,7 +782,7 @@ template <typename MT>
 __global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
                            const MT* __restrict__ mask, long long L, float gamma, float lam,
                            float* __restrict__ adv_out, float* __restrict__ ret_out, double* __restrict__ sums,
-                           int vec) {
+                           int vec, int* status) {
     __shared__ Affine warp_maps[32];
     __shared__ float carry[2];
     __shared__ double red[32];
@@ -750,12 +897,13 @@ __global__ void __launch_bounds__(512) gae_kernel(const float* __restrict__ rewa
         atomicAdd(&sums[1], d2);
         atomicAdd(&sums[2], dc);
     }
+    whiten_publish_status(sums, status);
 }
 
 // sums of v*m, v^2*m, m for masked_whiten
 template <int VEC, typename MT>
 __global__ void whiten_stats_kernel(const float* __restrict__ values, const MT* __restrict__ mask, long long n,
-                                    double* __restrict__ sums) {
+                                    double* __restrict__ sums, int* status) {
     __shared__ double red[32];
     float s1 = 0.f, s2 = 0.f, sc = 0.f;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * VEC;
@@ -778,6 +926,7 @@ __global__ void whiten_stats_kernel(const float* __restrict__ values, const MT* 
         atomicAdd(&sums[1], d2);
         atomicAdd(&sums[2], dc);
     }
+    whiten_publish_status(sums, status);
 }
 
 // masked_whiten (torch_functional.py:206-223): mean = S1/(N+1e-8); var = E[(x-mean)^2] * N/(N-1);
@@ -787,7 +936,7 @@ __global__ void whiten_apply_kernel(const float* values, long long n, const doub
                                     int shift_mean, float* out) {
     const double N = sums[2];
     if (N == 0.0 || N == 1.0) return;  // the reference raises ValueError (torch_functional.py:195-200; status word
-                                       // from whiten_status_kernel); outputs are left untouched
+                                       // from whiten_publish_status); outputs are left untouched
     const double den = N + 1e-8;
     const double mean_d = sums[0] / den;
     // sum((x-mean)^2 m) = S2 - 2 mean S1 + mean^2 N
@@ -886,6 +1035,48 @@ static bool spec_enabled() {
     return on != 0;
 }
 
+// VPG_TOK_COOP=0 keeps the token-mean losses with gradients on the two-launch path (mask count, then the sweep)
+static bool coop_enabled() {
+    static const int on = [] {
+        if (env_int("VPG_TOK_COOP", 1) == 0) return 0;
+        int dev = 0, ok = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev) != cudaSuccess) return 0;
+        return ok;
+    }();
+    return on != 0;
+}
+
+// Grid of the cooperative single-pass kernels: as many blocks as are resident at once (at most 4 per SM), every block
+// `iters` units of kCoopSliceUnit tokens (at most kCoopMaxSlice tokens: one mask bit per token has to fit in shared
+// memory).  Returns false when the problem does not fit (the caller takes the two-launch path).
+static bool coop_plan(const void* fn, int64_t n, long long* iters, unsigned* grid, size_t* smem) {
+    // Worth it while the launch it saves matters: at the BASELINE micro-batch sizes (20 k - 262 k tokens) the single launch
+    // is 25-35 % faster (C5: 35 -> 24 us).  On long sweeps it LOSES: every warp leaves the grid barrier at the same moment
+    // and the sweep is issue-bound, so load and arithmetic phases alternate in lock-step instead of overlapping (ncu at
+    // 2^25 tokens: 314 us at 47 % of DRAM peak against 53 + 161 us for the two launches).  Hence at most
+    // VPG_TOK_COOP_MAX_ITERS (default 4) units per block, i.e. up to ~2.4 M tokens on 148 SMs.
+    static const int max_iters = env_int("VPG_TOK_COOP_MAX_ITERS", 4);
+    int64_t blocks = static_cast<int64_t>(sm_count()) * 4;
+    const int64_t units = ceil_div(n, kCoopSliceUnit);
+    for (int pass = 0; pass < 2; ++pass) {
+        const int64_t g = units < blocks ? units : blocks;
+        const int64_t it = ceil_div(units, g);
+        if (it > max_iters || it * kCoopSliceUnit > kCoopMaxSlice) return false;
+        const size_t sm = static_cast<size_t>(it) * kThreads;
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, sm) != cudaSuccess || occ < 1) return false;
+        const int64_t resident = static_cast<int64_t>(occ) * sm_count();
+        const int64_t need = ceil_div(units, it);
+        if (need <= resident) {
+            *iters = it, *grid = static_cast<unsigned>(need), *smem = sm;
+            return true;
+        }
+        blocks = resident;  // fewer blocks fit than assumed: plan for that many
+    }
+    return false;
+}
+
 static size_t ppo_ws_header_bytes(int64_t B) {
     return round_up(static_cast<int64_t>(kWsHeader + 4 * (B > 0 ? B : 0)) * sizeof(double), 16);
 }
@@ -914,7 +1105,9 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
     VPG_CUDA(cudaMemsetAsync(workspace, 0, ppo_ws_header_bytes(B), stream));  // reduction slots only
     const bool vec = rows_vec_ok(L, mask, mask_dtype,
                                  {old_log_prob, log_prob, advantages, entropy, ref_log_prob, d_log_prob, d_entropy});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    // forward only + token-mean: one sweep, the mask count taken on the way
+    const bool one_pass = (agg_mode == VPG_AGG_TOKEN_MEAN) && !d_log_prob && !d_entropy;
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, one_pass ? 16 : 8);
     const unsigned grid = static_cast<unsigned>(B * gx);
     // 4- / 8-byte integer masks: the count pass leaves a one-byte copy for the loss pass
     unsigned char* cmask = (mask_dtype == VPG_MASK_I64 || mask_dtype == VPG_MASK_I32)
@@ -927,8 +1120,6 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
     p.loss_scale = loss_scale;
     p.metrics = metrics, p.d_lp = d_log_prob, p.d_ent = d_entropy;
     p.ws = static_cast<double*>(workspace);
-    // forward only + token-mean: one sweep, the mask count taken on the way
-    const bool one_pass = (agg_mode == VPG_AGG_TOKEN_MEAN) && !p.d_lp && !p.d_ent;
     // compile-time folded bodies for the recipes' configurations (vector path only)
     const bool kl_on = ref_log_prob != nullptr && kl_kind >= 0;
     int spec = 0;
@@ -940,6 +1131,27 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
         else if (V == 4 && spec == 2) ppo_loss_kernel<V, MT, COUNT, (V == 4 ? 2 : 0)><<<grid, kThreads, 0, stream>>>(p, mk, CM); \
         else ppo_loss_kernel<V, MT, COUNT, 0><<<grid, kThreads, 0, stream>>>(p, mk, CM);          \
     } while (0)
+    // token-mean with gradients: one cooperative launch that reads the mask once (see ppo_loss_coop_kernel)
+    bool coop_done = false;
+    if (spec != 0 && !one_pass && coop_enabled()) {
+        VPG_DISPATCH_MASK(mask_dtype, MT, {
+            const MT* mk = static_cast<const MT*>(mask);
+            const void* fn = spec == 1 ? reinterpret_cast<const void*>(ppo_loss_coop_kernel<MT, 1>)
+                                       : reinterpret_cast<const void*>(ppo_loss_coop_kernel<MT, 2>);
+            long long n = B * L, iters = 0;
+            unsigned cgrid = 0;
+            size_t smem = 0;
+            if (coop_plan(fn, n, &iters, &cgrid, &smem)) {
+                void* kargs[] = {&p, &mk, &n, &iters};
+                VPG_CUDA(cudaLaunchCooperativeKernel(fn, dim3(cgrid), dim3(kThreads), kargs, smem, stream));
+                coop_done = true;
+            }
+        });
+    }
+    if (coop_done) {
+        VPG_LAUNCH_CHECK();
+        return VPG_OK;
+    }
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         if (one_pass) {
@@ -972,7 +1184,7 @@ int vpg_agg_loss(const float* loss_mat, const void* mask, int mask_dtype, int64_
     VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
     double* ws = static_cast<double*>(workspace);
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {loss_mat, d_loss_mat});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 8);
     const unsigned grid = static_cast<unsigned>(B * gx);
     // one-byte mask copy for the second sweep when the caller's workspace has room for it (the ppo_loss size)
     unsigned char* cmask = ((mask_dtype == VPG_MASK_I64 || mask_dtype == VPG_MASK_I32) &&
@@ -1013,7 +1225,7 @@ int vpg_value_loss(const float* vpreds, const float* returns, const float* value
     VPG_CUDA(cudaMemsetAsync(workspace, 0, need, stream));
     double* ws = static_cast<double*>(workspace);
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {vpreds, returns, values, d_vpreds});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 16);
     const unsigned grid = static_cast<unsigned>(B * gx);
     // one-byte mask copy for the second sweep when the caller's workspace has room for it (the ppo_loss size)
     unsigned char* cmask = ((mask_dtype == VPG_MASK_I64 || mask_dtype == VPG_MASK_I32) &&
@@ -1057,7 +1269,7 @@ int vpg_grpo_advantage(const float* rewards, const void* mask, int mask_dtype, c
     float* adv_row = reinterpret_cast<float*>(gstat + 3 * G);
     VPG_CUDA(cudaMemsetAsync(workspace, 0, static_cast<size_t>(B + 3 * G) * sizeof(double), stream));
     const bool vec = rows_vec_ok(L, mask, mask_dtype, {rewards, advantages});
-    const int gx = blocks_per_row(B, L, vec ? 4 : 1);
+    const int gx = blocks_per_row(B, L, vec ? 4 : 1, 16);
     const unsigned grid = static_cast<unsigned>(B * gx);
     if (vec)
         row_score_kernel<4, float><<<grid, kThreads, 0, stream>>>(rewards, L, gx, scores);
@@ -1102,8 +1314,8 @@ size_t vpg_gae_workspace_bytes(int64_t B, int64_t L) {
 }
 
 static int whiten_apply(const float* values, int64_t n, const double* sums, int shift_mean, float* out,
-                        int32_t* status, void* status_event, cudaStream_t stream) {
-    VPG_CUDA(publish_whiten_status(sums, status, status_event, stream));
+                        void* status_event, cudaStream_t stream) {
+    VPG_CUDA(record_whiten_status(status_event, stream));  // right behind the kernel whose last block wrote the status
     if (n % 4 == 0 && aligned16(values) && aligned16(out))
         whiten_apply_kernel<4><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, n, sums, shift_mean, out);
     else
@@ -1123,14 +1335,14 @@ int vpg_gae(const float* rewards, const float* values, const void* mask, int mas
     double* sums = static_cast<double*>(workspace);
     VPG_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), stream));
     int64_t threads = round_up(ceil_div(L, kSeg), 32);
-    if (threads > 512) threads = 512;
+    if (threads > scan_block_threads(B)) threads = scan_block_threads(B);
     const int vec = (L % kSeg == 0) && rows_vec_ok(L, mask, mask_dtype, {rewards, values, advantages, returns});
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         gae_kernel<MT><<<static_cast<unsigned>(B), static_cast<unsigned>(threads), 0, stream>>>(
-            rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums, vec);
+            rewards, values, static_cast<const MT*>(mask), L, gamma, lam, advantages, returns, sums, vec, status);
     });
     VPG_LAUNCH_CHECK();
-    return whiten_apply(advantages, B * L, sums, 1, advantages, status, status_event, stream);
+    return whiten_apply(advantages, B * L, sums, 1, advantages, status_event, stream);
 }
 
 int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int64_t n, int shift_mean, float* out,
@@ -1145,12 +1357,12 @@ int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int
     VPG_DISPATCH_MASK(mask_dtype, MT, {
         const MT* mk = static_cast<const MT*>(mask);
         if (vec)
-            whiten_stats_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, mk, n, sums);
+            whiten_stats_kernel<4, MT><<<flat_grid(n, 4), kThreads, 0, stream>>>(values, mk, n, sums, status);
         else
-            whiten_stats_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, mk, n, sums);
+            whiten_stats_kernel<1, MT><<<flat_grid(n, 1), kThreads, 0, stream>>>(values, mk, n, sums, status);
     });
     VPG_LAUNCH_CHECK();
-    return whiten_apply(values, n, sums, shift_mean, out, status, status_event, stream);
+    return whiten_apply(values, n, sums, shift_mean, out, status_event, stream);
 }
 
 }  // extern "C"
