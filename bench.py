@@ -663,7 +663,7 @@ def run_ours(args, name, cfg):
     n_micro = len(micros)
     scale = 1.0 / n_micro
 
-    def compute(src, record):
+    def compute(src, record, window=None):
         """one micro-batch of the hot path through the public API -> metrics[8] (device)"""
         hidden = src["hidden"].detach().requires_grad_(True)
         marks = [ev() for _ in range(4)] if record else None
@@ -672,7 +672,7 @@ def run_ours(args, name, cfg):
         if kind == "actor":
             _loss, metrics, _lp, _ent = fused_actor_step(hidden, weight, src["ids"], src["attn"], src["old"], src["adv"],
                                                          src["rmask"], temperature=1.0, ref_log_prob=src["ref"],
-                                                         loss_scale=scale, **cfg["loss"])
+                                                         loss_scale=scale, window=window, **cfg["loss"])
             if record:
                 marks[3].record()
                 seg["_marks"].append((marks[0], None, None, marks[3]))
@@ -700,6 +700,14 @@ def run_ours(args, name, cfg):
 
     def step(e2e: bool, record: bool, last_step: bool = False):
         weight.grad = None
+        windows = [None] * n_micro
+        if kind == "actor" and not e2e:
+            # c3, inputs resident: the index plumbing of the whole mini-batch first (two host reads of token counts per
+            # micro-batch, inside the timed region), so that the eight lm-head passes then queue back to back — a host
+            # read between them leaves the GPU idle for as long as the host takes to enqueue the next GEMM (measured:
+            # 265 vs 318 ms per step on boxes with a slow host).  The e2e leg keeps the per-micro-batch order: a
+            # micro-batch's ids / mask arrive with its own H2D copy.
+            windows = [response_window(m["ids"], m["attn"], cfg["L"]) for m in micros]
         for mi in range(n_micro):
             if e2e:
                 slot = counter[0] & 1
@@ -713,7 +721,7 @@ def run_ours(args, name, cfg):
                     dist.all_gather_into_tensor(src["hidden"], src["hidden"][rank * rows:(rank + 1) * rows], group=group)
             else:
                 src = micros[mi]
-            metrics = compute(src, record)
+            metrics = compute(src, record, windows[mi])
             if e2e:
                 consumed[slot].record()
                 # the host reads EVERY micro-batch's loss / metrics, one behind the launches: micro-batch i's 32 bytes are

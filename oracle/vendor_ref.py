@@ -37,11 +37,16 @@ FILES = [
     "verl/utils/device.py",
     "verl/trainer/ppo/__init__.py",
     "verl/trainer/ppo/core_algos.py",
+    "verl/trainer/ppo/metric_utils.py",
+    "verl/utils/metric/__init__.py",
+    "verl/utils/metric/utils.py",
+    "verl/utils/import_utils.py",
     # the reference's own tests of the path
     "tests/utils/test_linear_cross_entropy.py",
     "tests/utils/test_linear_cross_entropy_tp.py",
     "tests/utils/test_torch_functional.py",
     "tests/trainer/ppo/test_core_algos_on_cpu.py",
+    "tests/trainer/ppo/test_metric_utils_on_cpu.py",
 ]
 
 

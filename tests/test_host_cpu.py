@@ -176,10 +176,12 @@ def test_compat_install_shadows_reference_paths():
         "from verl.utils.megatron.tensor_parallel import vocab_parallel_entropy;"
         "from verl.utils.experimental.torch_functional import FusedLinearForPPO;"
         "from verl.models.transformers.dense_common import forward_with_torch_backend, forward_with_triton_backend;"
+        "from verl.trainer.ppo.ray_trainer import compute_advantage, apply_kl_penalty;"
+        "from verl.trainer.ppo.metric_utils import compute_data_metrics;"
         "assert a is b and hasattr(ca, 'compute_policy_loss') and hasattr(F, 'masked_mean'); print('ok', len(r))"
     )
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "ok 10" in out.stdout, out.stderr
+    assert out.returncode == 0 and "ok 12" in out.stdout, out.stderr
 
 
 def test_d_hidden_allreduce_overlap_plan():

@@ -20,10 +20,10 @@ needs_snapshot = pytest.mark.skipif(not os.path.isfile(os.path.join(ROOT, "oracl
                                     reason="oracle/_ref snapshot missing (python -m oracle.vendor_ref)")
 
 
-def _run(args):
+def _run(args, plugin="vendored_install"):
     env = dict(os.environ, PYTHONPATH=os.path.join(ROOT, "tests") + os.pathsep + ROOT + os.pathsep +
                os.environ.get("PYTHONPATH", ""))
-    cmd = [sys.executable, "-m", "pytest", "-q", "-p", "vendored_install", "-p", "no:cacheprovider",
+    cmd = [sys.executable, "-m", "pytest", "-q", "-p", plugin, "-p", "no:cacheprovider",
            "--rootdir", REF_TESTS, "-c", os.devnull, *args]
     return subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env, cwd=REF_TESTS)
 
@@ -44,3 +44,28 @@ def test_reference_cpu_acceptance_tests_on_device():
               os.path.join(REF_TESTS, "utils", "test_torch_functional.py"), "-k", "not distributed"])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "13 passed" in r.stdout, r.stdout[-2000:]
+
+
+@needs_snapshot
+@pytest.mark.gpu
+def test_reference_acceptance_tests_with_importable_reference_patched():
+    """Deployment mode: the reference's own module objects are importable (loaded from the snapshot) and
+    compat.install() PATCHES the hot-path names into them.  The reference's core_algos tests (10), masked_mean cases (3)
+    and its compute_data_metrics tests (tests/trainer/ppo/test_metric_utils_on_cpu.py::TestComputeDataMetrics, 2 — a
+    MagicMock batch of host tensors) run unmodified on top."""
+    r = _run([os.path.join(REF_TESTS, "trainer", "ppo", "test_core_algos_on_cpu.py"),
+              os.path.join(REF_TESTS, "utils", "test_torch_functional.py"),
+              os.path.join(REF_TESTS, "trainer", "ppo", "test_metric_utils_on_cpu.py"),
+              "-k", "not distributed and (TestComputeDataMetrics or not metric_utils)"], plugin="vendored_install_patched")
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "15 passed" in r.stdout, r.stdout[-2000:]
+
+
+@needs_snapshot
+def test_patched_mode_plugin_patches_reference_modules():
+    """No device needed: with the reference's modules importable, install() reports 'patched' for them and replaces the
+    names (the plugin asserts it at import); the registry tests of the reference still pass on the patched module."""
+    r = _run([os.path.join(REF_TESTS, "trainer", "ppo", "test_core_algos_on_cpu.py"), "-k", "TestRegisterAdvEst"],
+             plugin="vendored_install_patched")
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "9 passed" in r.stdout, r.stdout[-2000:]

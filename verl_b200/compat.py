@@ -12,6 +12,10 @@
   verl.utils.experimental.torch_functional.{FusedLinearForPPO, FusedLinearForPPOFunction}   (the DEFAULT "torch"
       fused backend, verl/models/transformers/dense_common.py:88-121)
   verl.models.transformers.dense_common.{forward_with_torch_backend, forward_with_triton_backend, ...}
+  verl.trainer.ppo.metric_utils.compute_data_metrics and verl.trainer.ppo.ray_trainer.{apply_kl_penalty,
+      compute_advantage, compute_response_mask, compute_data_metrics}   (the driver-side call sites,
+      verl/trainer/ppo/ray_trainer.py:1283-1305; ray_trainer binds compute_data_metrics by name at import, so an
+      importable ray_trainer gets that name patched too)
   flash_attn.bert_padding.{unpad_input, pad_input, index_first_axis}   (only with patch_flash_attn=True)
 
 If the real ``verl`` package is importable its modules are patched attribute by attribute (everything outside the
@@ -32,6 +36,8 @@ from .utils.kernel import kernels as _k
 from .utils.kernel import linear_cross_entropy as _lce
 from .utils.experimental import torch_functional as _xtf
 from .models.transformers import dense_common as _dc
+from .trainer.ppo import metric_utils as _mu
+from .trainer.ppo import ray_trainer as _rt
 
 _TF_NAMES = [
     "logprobs_from_logits", "logprobs_from_logits_v2", "logprobs_from_logits_naive", "logprobs_from_logits_flash_attn",
@@ -110,12 +116,17 @@ def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
         "verl.utils.experimental.torch_functional": (_xtf, ["FusedLinearForPPOFunction", "FusedLinearForPPO"]),
         "verl.models.transformers.dense_common": (_dc, ["CausalLMOutputForPPO", "forward_base_model",
                                                         "forward_with_torch_backend", "forward_with_triton_backend"]),
+        # driver-side call sites (ray_trainer.py:1283-1305)
+        "verl.trainer.ppo.metric_utils": (_mu, ["compute_data_metrics"]),
+        "verl.trainer.ppo.ray_trainer": (_rt, ["apply_kl_penalty", "compute_response_mask", "compute_advantage"]),
     }
     for name, (src, names) in targets.items():
         real = _try_import(name)
         if real is not None and real is not src:
             for n in names:
                 setattr(real, n, getattr(src, n))
+            if name.endswith("ray_trainer"):  # `from verl.trainer.ppo.metric_utils import compute_data_metrics` at its top
+                real.compute_data_metrics = _mu.compute_data_metrics
             if name.endswith("core_algos"):
                 for key, fn in _ca.ADV_ESTIMATOR_REGISTRY.items():
                     real.ADV_ESTIMATOR_REGISTRY[key] = fn
