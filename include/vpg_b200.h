@@ -70,6 +70,9 @@ const char* vpg_version(void);
 const char* vpg_last_error(void);
 /* number of kernels this library has launched in the calling process (monotonic; for bench.py's gpu_launches) */
 int64_t vpg_launch_count(void);
+/* cudaStreamSynchronize(stream): the wait behind the host reads of token counts (unpad_input's nnz / max_seqlen — the
+ * reference syncs at the same points with nonzero() and .item(), flash_attn bert_padding / torch_functional.py:629-638) */
+int vpg_stream_synchronize(void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Fused lm-head -> per-token log-prob + entropy.

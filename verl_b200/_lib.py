@@ -21,6 +21,7 @@ SIGNATURES: dict[str, tuple] = {
     "vpg_version": (C.c_char_p, []),
     "vpg_last_error": (C.c_char_p, []),
     "vpg_launch_count": (c_int64, []),
+    "vpg_stream_synchronize": (c_int, [c_void_p]),
     "vpg_lce_num_splits": (c_int, [c_int64, c_int64, c_int64, c_int]),
     "vpg_lce_fwd_partials": (
         c_int,
@@ -264,8 +265,41 @@ def ptr(t: torch.Tensor | None):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device=None) -> int:
+    """cudaStream_t of torch's current stream on `device`.  At the BASELINE micro-batch sizes the token ops are host-bound
+    (12-45 us per call, `scripts/prof_host_overhead.py`), and `torch.cuda.current_stream(...)` alone costs 6 us of that
+    (device-index normalisation + a Stream object); the raw-stream query the compiled-graph runtime uses is ~0.3 us."""
+    if _raw_stream is not None:
+        idx = getattr(device, "index", device)
+        if idx is None:
+            idx = torch.cuda.current_device()
+        return _raw_stream(idx)
     return torch.cuda.current_stream(device).cuda_stream
+
+
+class on_device:
+    """``with on_device(dev):`` — `torch.cuda.device(dev)` that costs nothing when `dev` already is the current device
+    (the normal case: one process per GPU).  The library launches on the current device, so the guard is only needed when
+    a tensor lives elsewhere; entering torch's context manager unconditionally cost ~6 us per op call."""
+
+    __slots__ = ("_ctx",)
+
+    def __init__(self, device):
+        idx = getattr(device, "index", device)
+        self._ctx = None if (idx is None or idx == torch.cuda.current_device()) else torch.cuda.device(idx)
+
+    def __enter__(self):
+        if self._ctx is not None:
+            self._ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self._ctx is not None:
+            return self._ctx.__exit__(*exc)
+        return False
 
 
 def mask_arg(mask: torch.Tensor):

@@ -39,5 +39,9 @@ extern "C" {
 const char* vpg_version(void) { return "vpg_b200 0.1.0 (sm_100a)"; }
 const char* vpg_last_error(void) { return vpg::g_err; }
 int64_t vpg_launch_count(void) { return vpg::g_launches.load(std::memory_order_relaxed); }
+int vpg_stream_synchronize(void* stream) {
+    VPG_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    return VPG_OK;
+}
 
 }  // extern "C"

@@ -10,7 +10,9 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
 #include <type_traits>
+#include <vector>
 
 #include "token_common.cuh"
 
@@ -1047,6 +1049,29 @@ static bool coop_enabled() {
     return on != 0;
 }
 
+// Resident blocks per SM of a cooperative kernel, asked once per (kernel, KiB of dynamic shared memory) and device: the
+// call sits on the host path of every loss evaluation, which is host-bound at the BASELINE micro-batch sizes.
+static int coop_occupancy(const void* fn, size_t smem) {
+    struct Key {
+        const void* fn;
+        size_t kib;
+        int dev;
+        int occ;
+    };
+    static std::mutex mu;
+    static std::vector<Key> cache;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    const size_t kib = (smem + 1023) / 1024;
+    std::lock_guard<std::mutex> lk(mu);
+    for (const Key& k : cache)
+        if (k.fn == fn && k.kib == kib && k.dev == dev) return k.occ;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, kib * 1024) != cudaSuccess) occ = 0;
+    cache.push_back(Key{fn, kib, dev, occ});
+    return occ;
+}
+
 // Grid of the cooperative single-pass kernels: as many blocks as are resident at once (at most 4 per SM), every block
 // `iters` units of kCoopSliceUnit tokens (at most kCoopMaxSlice tokens: one mask bit per token has to fit in shared
 // memory).  Returns false when the problem does not fit (the caller takes the two-launch path).
@@ -1064,8 +1089,8 @@ static bool coop_plan(const void* fn, int64_t n, long long* iters, unsigned* gri
         const int64_t it = ceil_div(units, g);
         if (it > max_iters || it * kCoopSliceUnit > kCoopMaxSlice) return false;
         const size_t sm = static_cast<size_t>(it) * kThreads;
-        int occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, sm) != cudaSuccess || occ < 1) return false;
+        const int occ = coop_occupancy(fn, sm);
+        if (occ < 1) return false;
         const int64_t resident = static_cast<int64_t>(occ) * sm_count();
         const int64_t need = ceil_div(units, it);
         if (need <= resident) {

@@ -7,6 +7,7 @@ The reference-named Python API (verl_b200.utils.*, verl_b200.trainer.*) is built
 
 from __future__ import annotations
 
+import ctypes
 import math
 
 import threading
@@ -14,7 +15,7 @@ import threading
 import torch
 
 from . import _lib
-from ._lib import ADV_KINDS, AGG_MODES, KL_KINDS, PG_KINDS, check, mask_arg, ptr, stream_ptr
+from ._lib import ADV_KINDS, AGG_MODES, KL_KINDS, PG_KINDS, check, mask_arg, on_device, ptr, stream_ptr
 
 _F32 = torch.float32
 
@@ -55,7 +56,7 @@ def lce_forward_partials(hidden, weight, labels, temperature: float, label_offse
     V = weight.shape[0]
     S = num_splits or lce_num_splits(T, H, V)
     part = torch.empty((4, S, T), dtype=_F32, device=hidden.device)
-    with torch.cuda.device(hidden.device):
+    with on_device(hidden.device):
         check(_lib_().vpg_lce_fwd_partials_dt(operand_dtype(hidden, weight), ptr(hidden), ptr(weight), ptr(labels), T,
                                               H, V, float(temperature), int(label_offset), S, ptr(part),
                                               stream_ptr(hidden.device)))
@@ -128,7 +129,7 @@ def lce_forward_partials_push(hidden, weight, labels, temperature: float, label_
             raise ValueError("lce_forward_partials_push needs a multicast address or the peer addresses")
         arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
         dst, is_mc, n_push = gathered.data_ptr(), 0, len(ptrs)
-    with torch.cuda.device(hidden.device):
+    with on_device(hidden.device):
         check(_lib_().vpg_lce_fwd_partials_push(ptr(hidden), ptr(weight), ptr(labels), T, H, V, float(temperature),
                                                 int(label_offset), int(num_splits), dst, int(part_split0), int(P),
                                                 is_mc, arr, n_push, stream_ptr(hidden.device)))
@@ -158,7 +159,7 @@ def lce_backward_mcred(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature
     lib = _lib_()
     chunk_v, nbytes, ws = _bwd_workspace(T, H, V, hidden.device, chunk_v)
     d_weight = torch.empty_like(weight)
-    with torch.cuda.device(hidden.device):
+    with on_device(hidden.device):
         check(lib.vpg_lce_bwd_mcred(ptr(hidden), ptr(weight), ptr(labels), ptr(lse), ptr(eb), ptr(g_lp), ptr(g_ent),
                                     T, H, V, float(temperature), int(label_offset), int(chunk_v), None, ptr(d_weight),
                                     ptr(ws), nbytes, int(accum_multicast_ptr), stream_ptr(hidden.device)))
@@ -169,7 +170,7 @@ def cast_f32_bf16(src):
     _require_cuda(src)
     assert src.dtype == _F32 and src.is_contiguous()
     out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
-    with torch.cuda.device(src.device):
+    with on_device(src.device):
         check(_lib_().vpg_cast_f32_bf16(ptr(src), ptr(out), src.numel(), stream_ptr(src.device)))
     return out
 
@@ -179,7 +180,7 @@ def lce_finalize(partials, temperature: float):
     _require_cuda(partials)
     _, P, T = partials.shape
     out = torch.empty((4, T), dtype=_F32, device=partials.device)
-    with torch.cuda.device(partials.device):
+    with on_device(partials.device):
         check(_lib_().vpg_lce_finalize(ptr(partials), P, T, float(temperature), ptr(out[0]), ptr(out[1]), ptr(out[2]),
                                        ptr(out[3]), stream_ptr(partials.device)))
     return out[0], out[1], out[2], out[3]
@@ -236,7 +237,7 @@ def lce_backward(hidden, weight, labels, lse, eb, g_lp, g_ent, temperature: floa
         a.ar_world, a.ar_rank, a.ar_epoch = int(allreduce["world"]), int(allreduce["rank"]), int(allreduce["epoch"])
         a.ar_d_hidden_mc, a.ar_flags = int(allreduce["mc"]), ptr(allreduce["flags"])
         a.ar_peer_flags = ctypes.cast(arr, ctypes.POINTER(ctypes.c_void_p))
-    with torch.cuda.device(hidden.device):
+    with on_device(hidden.device):
         check(lib.vpg_lce_bwd_ex(ctypes.byref(a)))
     return d_hidden, d_weight
 
@@ -250,7 +251,7 @@ def gemm_bf16(A, B, a_kmajor=True, b_kmajor=True, out_dtype=torch.bfloat16, spli
     C = torch.empty((M, N), dtype=out_dtype, device=A.device)
     mode = 0 if out_dtype == torch.bfloat16 else 1
     lib = _lib_()
-    with torch.cuda.device(A.device):
+    with on_device(A.device):
         if split_k:
             nbytes = int(lib.vpg_gemm_splitk_workspace_bytes())
             ws = torch.empty(nbytes, dtype=torch.uint8, device=A.device)
@@ -276,7 +277,7 @@ def logits_stats(logits2d, labels=None, want_logprobs=True, want_entropy=True):
     ent = torch.empty(T, dtype=_F32, device=dev) if want_entropy else None
     lse = torch.empty(T, dtype=_F32, device=dev)
     ld = logits2d.stride(0) if T > 1 else V
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_logits_stats(logits2d.data_ptr(), int(logits2d.dtype == torch.bfloat16), T, V, ld,
                                        ptr(labels) if lp is not None else None, ptr(lp), ptr(ent), ptr(lse),
                                        stream_ptr(dev)))
@@ -293,7 +294,7 @@ def logits_partials(logits2d, labels=None, label_offset: int = 0):
     T, V = logits2d.shape
     part = torch.empty((4, 1, T), dtype=_F32, device=logits2d.device)
     ld = logits2d.stride(0) if T > 1 else V
-    with torch.cuda.device(logits2d.device):
+    with on_device(logits2d.device):
         check(_lib_().vpg_logits_partials(logits2d.data_ptr(), int(logits2d.dtype == torch.bfloat16), T, V, ld,
                                           ptr(labels), int(label_offset), ptr(part), stream_ptr(logits2d.device)))
     return part
@@ -306,7 +307,7 @@ def logits_stats_backward(logits2d, labels, lse, entropy, g_lp, g_ent):
     T, V = logits2d.shape
     assert logits2d.is_contiguous()
     d = torch.empty_like(logits2d)
-    with torch.cuda.device(logits2d.device):
+    with on_device(logits2d.device):
         check(_lib_().vpg_logits_stats_bwd(ptr(logits2d), int(logits2d.dtype == torch.bfloat16), T, V, V, ptr(labels),
                                            ptr(lse), ptr(entropy), ptr(g_lp), ptr(g_ent), ptr(d),
                                            stream_ptr(logits2d.device)))
@@ -336,7 +337,7 @@ def unpad_indices_launch(mask2d):
     slot = _StatusSlot.get(dev)  # the kernels write {nnz, max_seqlen} straight into pinned host memory (UVA)
     nbytes = int(lib.vpg_unpad_workspace_bytes(n))
     ws = _ws(nbytes, dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(lib.vpg_unpad_indices(ptr(m), mdt, B, S, ptr(indices_full), ptr(seqlens), ptr(cu), slot.pair_ptr, ptr(ws),
                                     ws.numel() * 8, stream_ptr(dev)))
     return indices_full, seqlens, cu, slot
@@ -356,8 +357,8 @@ def unpad_indices(mask2d):
         return (torch.empty(0, dtype=torch.int64, device=dev), torch.zeros(B, dtype=torch.int32, device=dev),
                 torch.zeros(B + 1, dtype=torch.int32, device=dev), 0)
     indices_full, seqlens, cu, slot = unpad_indices_launch(mask2d)
-    torch.cuda.current_stream(dev).synchronize()
-    nnz, max_seqlen = int(slot.pair[0]), int(slot.pair[1])
+    check(_lib_().vpg_stream_synchronize(stream_ptr(dev)))  # ctypes drops the GIL; no Stream object on the way
+    nnz, max_seqlen = slot.read_pair()
     indices = indices_full[:nnz]
     indices._vpg_ascending = True  # provenance mark: pad_input may then fill gaps in one pass (see scatter_rows)
     return indices, seqlens, cu, max_seqlen
@@ -374,7 +375,7 @@ def response_rows(indices, ids_rmpad, S: int, L: int):
     keep = torch.empty(max(T, 1), dtype=torch.uint8, device=dev)
     dst = torch.empty(max(T, 1), dtype=torch.int64, device=dev)
     labels = torch.empty(max(T, 1), dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_response_rows(ptr(indices.contiguous()), ptr(ids_rmpad.contiguous()), T, int(S), int(L),
                                         ptr(keep), ptr(dst), ptr(labels), stream_ptr(dev)))
     sel, _, _, _ = unpad_indices(keep[:T].view(1, T)) if T else (indices[:0], None, None, 0)
@@ -389,7 +390,7 @@ def gather_rows(src, indices):
     row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
     out = torch.empty((indices.numel(), *row_shape), dtype=src.dtype, device=src.device)
     if indices.numel() and row_bytes:
-        with torch.cuda.device(src.device):
+        with on_device(src.device):
             check(_lib_().vpg_gather_rows(ptr(src), ptr(indices.contiguous()), indices.numel(), row_bytes, ptr(out),
                                           stream_ptr(src.device)))
     return out
@@ -408,7 +409,7 @@ def scatter_rows(src, indices, n_out: int):
     row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
     out = torch.empty((n_out, *row_shape), dtype=src.dtype, device=src.device)
     if n_out and row_bytes:
-        with torch.cuda.device(src.device):
+        with on_device(src.device):
             check(_lib_().vpg_scatter_rows(ptr(src), ptr(indices.contiguous()), indices.numel(), row_bytes, ptr(out),
                                            n_out, fill, stream_ptr(src.device)))
     return out
@@ -426,7 +427,7 @@ def row_lengths(mask2d):
     B, S = mask2d.shape
     out = torch.empty(B, dtype=torch.int64, device=mask2d.device)
     if B:
-        with torch.cuda.device(mask2d.device):
+        with on_device(mask2d.device):
             check(_lib_().vpg_row_lengths(ptr(m), mdt, B, S, ptr(out), stream_ptr(mask2d.device)))
     return out
 
@@ -461,7 +462,7 @@ def packed_seq_layout(seqlens_i32, align: int):
     padded = torch.empty(B, dtype=torch.int32, device=dev)
     cu = torch.empty(B + 1, dtype=torch.int32, device=dev)
     totals = torch.empty(2, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_packed_seq_layout(ptr(seqlens_i32.contiguous()), B, int(align), ptr(padded), ptr(cu),
                                             ptr(totals), stream_ptr(dev)))
     total, mx = totals.tolist()
@@ -475,7 +476,7 @@ def packed_seq_map(cu_seqlens, cu_seqlens_padded, T: int, cp_size: int, cp_rank:
     gpos = torch.empty(T, dtype=torch.int64, device=dev)
     ldst = torch.empty(T, dtype=torch.int64, device=dev)
     if T:
-        with torch.cuda.device(dev):
+        with on_device(dev):
             check(_lib_().vpg_packed_seq_map(ptr(cu_seqlens), ptr(cu_seqlens_padded), cu_seqlens.numel() - 1, T,
                                              int(cp_size), int(cp_rank), ptr(gpos), ptr(ldst), stream_ptr(dev)))
     return gpos, ldst
@@ -490,7 +491,7 @@ def permute_rows(src, src_idx, dst_idx, n_out: int, zero_fill: bool = True):
     n = (src_idx if src_idx is not None else dst_idx if dst_idx is not None else src).shape[0]
     out = torch.empty((n_out, *row_shape), dtype=src.dtype, device=src.device)
     if n_out and row_bytes:
-        with torch.cuda.device(src.device):
+        with on_device(src.device):
             check(_lib_().vpg_permute_rows(ptr(src), ptr(src_idx), ptr(dst_idx), n, row_bytes, ptr(out), n_out,
                                            int(zero_fill), stream_ptr(src.device)))
     return out
@@ -503,7 +504,7 @@ def masked_sums(values, mask):
     v = _f32c(values)
     m, mdt = mask_arg(mask.contiguous())
     out = torch.empty(2, dtype=torch.float64, device=v.device)
-    with torch.cuda.device(v.device):
+    with on_device(v.device):
         check(_lib_().vpg_masked_sum(ptr(v), ptr(m), mdt, v.numel(), ptr(out), stream_ptr(v.device)))
     return out
 
@@ -517,7 +518,7 @@ def masked_row_sums(values, mask):
     rows = v.numel() // max(L, 1)
     s = torch.empty(rows, dtype=_F32, device=v.device)
     c = torch.empty(rows, dtype=_F32, device=v.device)
-    with torch.cuda.device(v.device):
+    with on_device(v.device):
         check(_lib_().vpg_masked_row_sum(ptr(v), ptr(m), mdt, rows, L, ptr(s), ptr(c), stream_ptr(v.device)))
     return s, c
 
@@ -529,7 +530,7 @@ def kl_penalty_fwd(logprob, ref_logprob, kind: str, want_grad: bool):
     a, b = _f32c(logprob), _f32c(ref_logprob)
     out = torch.empty_like(a)
     g = torch.empty_like(a) if want_grad else None
-    with torch.cuda.device(a.device):
+    with on_device(a.device):
         check(_lib_().vpg_kl_penalty(ptr(a), ptr(b), KL_KINDS[kind], a.numel(), ptr(out), ptr(g), stream_ptr(a.device)))
     return out, g
 
@@ -566,7 +567,7 @@ def ppo_loss(old_log_prob, log_prob, advantages, response_mask, *, cliprange_low
     d_lp = torch.empty_like(lp) if want_grad else None
     d_ent = torch.empty_like(lp) if (want_grad and ent is not None) else None
     ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(lib.vpg_ppo_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, ptr(ent), ptr(ref), B, L,
                                float(1 - cliprange_low), float(1 + cliprange_high), float(clip_ratio_c),
                                PG_KINDS[pg_kind], AGG_MODES[loss_agg_mode], float(entropy_coeff), float(kl_loss_coef),
@@ -589,7 +590,7 @@ def clip_cov_flags(old_log_prob, log_prob, advantages, response_mask, cliprange_
     dev = lp.device
     ws = _cov_ws(dev)
     flags = torch.empty(n, dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_clip_cov_flags(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(cliprange_low),
                                          float(cliprange_high), float(cov_lb), float(cov_ub), ptr(flags), ptr(ws),
                                          ws.numel() * 8, stream_ptr(dev)))
@@ -605,7 +606,7 @@ def clip_cov_loss(old_log_prob, log_prob, advantages, response_mask, cliprange_l
     pg = torch.empty(n, dtype=_F32, device=dev)
     dpg = torch.empty(n, dtype=_F32, device=dev)
     out3 = torch.empty(3, dtype=_F32, device=dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_clip_cov_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(cliprange_low),
                                         float(cliprange_high), ptr(zeroed), ptr(pg), ptr(dpg), ptr(out3), ptr(ws),
                                         ws.numel() * 8, stream_ptr(dev)))
@@ -623,7 +624,7 @@ def kl_cov_loss(old_log_prob, log_prob, advantages, response_mask, kl_cov_ratio:
     pg = torch.empty(n, dtype=_F32, device=dev)
     dpg = torch.empty(n, dtype=_F32, device=dev)
     out3 = torch.empty(3, dtype=_F32, device=dev)
-    with torch.cuda.device(dev):
+    with on_device(dev):
         check(_lib_().vpg_kl_cov_loss(ptr(old), ptr(lp), ptr(adv), ptr(m), mdt, n, float(kl_cov_ratio),
                                       float(ppo_kl_coef), ptr(pg), ptr(dpg), ptr(out3), ptr(ws), ws.numel() * 8,
                                       stream_ptr(dev)))
@@ -641,7 +642,7 @@ def agg_loss_fwd(loss_mat, loss_mask, loss_agg_mode: str, want_grad: bool):
     out = torch.empty(1, dtype=_F32, device=v.device)
     d = torch.empty_like(v) if want_grad else None
     ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), v.device)
-    with torch.cuda.device(v.device):
+    with on_device(v.device):
         check(lib.vpg_agg_loss(ptr(v), ptr(m), mdt, B, L, AGG_MODES[loss_agg_mode], ptr(out), ptr(d), ptr(ws),
                                ws.numel() * 8, stream_ptr(v.device)))
     return out[0], d
@@ -659,7 +660,7 @@ def value_loss(vpreds, returns, values, response_mask, cliprange_value: float, l
     out = torch.empty(2, dtype=_F32, device=vp.device)
     d = torch.empty_like(vp) if want_grad else None
     ws = _ws(int(lib.vpg_ppo_loss_workspace_bytes(B, L)), vp.device)
-    with torch.cuda.device(vp.device):
+    with on_device(vp.device):
         check(lib.vpg_value_loss(ptr(vp), ptr(rt), ptr(vo), ptr(m), mdt, B, L, float(cliprange_value),
                                  AGG_MODES[loss_agg_mode], ptr(out), ptr(d), ptr(ws), ws.numel() * 8,
                                  stream_ptr(vp.device)))
@@ -677,7 +678,7 @@ def outcome_advantage(kind: str, token_level_rewards, response_mask, group_ids, 
     adv = torch.empty_like(r)
     status = torch.empty(1, dtype=torch.int32, device=r.device)
     ws = _ws(int(lib.vpg_outcome_advantage_workspace_bytes(B, num_groups)), r.device)
-    with torch.cuda.device(r.device):
+    with on_device(r.device):
         check(lib.vpg_outcome_advantage(ADV_KINDS[kind], ptr(r), ptr(m), mdt, ptr(group_ids), B, L, int(num_groups),
                                         float(epsilon), int(bool(norm_by_std)), float(f_norm), ptr(adv), ptr(status),
                                         ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
@@ -698,7 +699,7 @@ def reinforce_plus_plus(token_level_rewards, response_mask, gamma: float):
     adv, ret = torch.empty_like(r), torch.empty_like(r)
     slot = _StatusSlot.get(r.device)
     ws = _ws(int(lib.vpg_reverse_scan_workspace_bytes(B, L)), r.device)
-    with torch.cuda.device(r.device):
+    with on_device(r.device):
         check(lib.vpg_reinforce_plus_plus(ptr(r), ptr(m), mdt, B, L, float(gamma), ptr(adv), ptr(ret), slot.word_ptr,
                                           ptr(ws), ws.numel() * 8, stream_ptr(r.device), slot.event_ptr))
     slot.wait_and_raise()
@@ -712,7 +713,7 @@ def remax(token_level_rewards, reward_baselines, response_mask):
     B, L = r.shape
     assert bsl.shape == (B,)
     adv, ret = torch.empty_like(r), torch.empty_like(r)
-    with torch.cuda.device(r.device):
+    with on_device(r.device):
         check(_lib_().vpg_remax(ptr(r), ptr(bsl), ptr(m), mdt, B, L, ptr(adv), ptr(ret), stream_ptr(r.device)))
     return adv, ret
 
@@ -729,7 +730,7 @@ def kl_reward(token_level_scores, old_log_probs, ref_log_prob, response_mask, ki
     out = torch.empty_like(sc)
     cur = torch.empty(1, dtype=_F32, device=sc.device)
     ws = _ws(int(lib.vpg_kl_reward_workspace_bytes(B)), sc.device)
-    with torch.cuda.device(sc.device):
+    with on_device(sc.device):
         check(lib.vpg_kl_reward(ptr(sc), ptr(lo), ptr(lr), ptr(m), mdt, KL_KINDS[kind], float(beta), B, L, ptr(out),
                                 ptr(cur), ptr(ws), ws.numel() * 8, stream_ptr(sc.device)))
     return out, cur
@@ -753,7 +754,7 @@ def data_metrics(token_level_scores, token_level_rewards, advantages, returns, v
     lib = _lib_()
     out = torch.empty(26, dtype=_F32, device=sc.device)
     ws = _ws(int(lib.vpg_data_metrics_workspace_bytes(B)), sc.device)
-    with torch.cuda.device(sc.device):
+    with on_device(sc.device):
         check(lib.vpg_data_metrics(ptr(sc), ptr(rw), ptr(adv), ptr(ret), ptr(val), ptr(rm), rdt, ptr(am), adt, B, L, S,
                                    ptr(out), ptr(ws), ws.numel() * 8, stream_ptr(sc.device)))
     return out
@@ -767,7 +768,7 @@ def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: in
     lib = _lib_()
     adv = torch.empty_like(r)
     ws = _ws(int(lib.vpg_grpo_workspace_bytes(B, num_groups)), r.device)
-    with torch.cuda.device(r.device):
+    with on_device(r.device):
         check(lib.vpg_grpo_advantage(ptr(r), ptr(m), mdt, ptr(group_ids), B, L, int(num_groups), float(epsilon),
                                      int(bool(norm_by_std)), ptr(adv), ptr(ws), ws.numel() * 8, stream_ptr(r.device)))
     return adv
@@ -775,9 +776,10 @@ def grpo_advantage(token_level_rewards, response_mask, group_ids, num_groups: in
 
 class _StatusSlot:
     """Pinned host status word + CUDA event, one per (thread, device).  The whitening entry points write the status
-    word from a one-thread kernel that runs BEFORE their normalisation pass and record the event right behind it, so
-    waiting for the event costs the statistics pass only: the ValueError of the reference (torch_functional.py:
-    195-200) is still raised synchronously, but the normalisation pass overlaps the host's wake-up."""
+    word from the last block of the kernel that produces the statistics, BEFORE their normalisation pass, and record the
+    event right behind that kernel, so waiting for the event costs the statistics pass only: the ValueError of the
+    reference (torch_functional.py:195-200) is still raised synchronously, but the normalisation pass overlaps the
+    host's wake-up."""
 
     _tls = threading.local()
 
@@ -786,8 +788,11 @@ class _StatusSlot:
         self.word_ptr = self.word.data_ptr()
         self.pair = torch.zeros(2, dtype=torch.int32).pin_memory()  # {nnz, max_seqlen} of unpad_indices
         self.pair_ptr = self.pair.data_ptr()
+        # plain ctypes views of the pinned words: reading `int(tensor[0])` costs 3-4 us per value on a host-bound path
+        self._word_c = ctypes.c_int32.from_address(self.word_ptr)
+        self._pair_c = (ctypes.c_int32 * 2).from_address(self.pair_ptr)
         self.event = torch.cuda.Event()
-        with torch.cuda.device(device):
+        with on_device(device):
             self.event.record()  # torch creates the cudaEvent_t lazily, at the first record
         self.event.synchronize()
         self.event_ptr = int(self.event.cuda_event)
@@ -802,9 +807,13 @@ class _StatusSlot:
             slots[idx] = cls(idx)
         return slots[idx]
 
+    def read_pair(self):
+        """{nnz, max_seqlen} as Python ints (valid once the stream has passed the unpad launch)."""
+        return int(self._pair_c[0]), int(self._pair_c[1])
+
     def wait_and_raise(self):
         self.event.synchronize()
-        _raise_whiten_code(int(self.word[0]))
+        _raise_whiten_code(int(self._word_c.value))
 
 
 def _raise_whiten_code(code: int):
@@ -823,7 +832,7 @@ def gae(token_level_rewards, values, response_mask, gamma: float, lam: float):
     adv, ret = torch.empty_like(r), torch.empty_like(r)
     slot = _StatusSlot.get(r.device)
     ws = _ws(int(lib.vpg_gae_workspace_bytes(B, L)), r.device)
-    with torch.cuda.device(r.device):
+    with on_device(r.device):
         check(lib.vpg_gae(ptr(r), ptr(v), ptr(m), mdt, B, L, float(gamma), float(lam), ptr(adv), ptr(ret),
                           slot.word_ptr, ptr(ws), ws.numel() * 8, stream_ptr(r.device), slot.event_ptr))
     slot.wait_and_raise()
@@ -837,7 +846,7 @@ def masked_whiten(values, mask, shift_mean=True):
     out = torch.empty_like(v)
     slot = _StatusSlot.get(v.device)
     ws = _ws(32, v.device)
-    with torch.cuda.device(v.device):
+    with on_device(v.device):
         check(_lib_().vpg_masked_whiten(ptr(v), ptr(m), mdt, v.numel(), int(bool(shift_mean)), ptr(out),
                                         slot.word_ptr, ptr(ws), ws.numel() * 8, stream_ptr(v.device), slot.event_ptr))
     slot.wait_and_raise()
