@@ -1168,8 +1168,12 @@ int vpg_ppo_loss(const float* old_log_prob, const float* log_prob, const float* 
             size_t smem = 0;
             if (coop_plan(fn, n, &iters, &cgrid, &smem)) {
                 void* kargs[] = {&p, &mk, &n, &iters};
-                VPG_CUDA(cudaLaunchCooperativeKernel(fn, dim3(cgrid), dim3(kThreads), kargs, smem, stream));
-                coop_done = true;
+                // a refused cooperative launch (fewer SMs than planned for: MPS share, green context) is not an error:
+                // the two-launch path below computes the same result
+                if (cudaLaunchCooperativeKernel(fn, dim3(cgrid), dim3(kThreads), kargs, smem, stream) == cudaSuccess)
+                    coop_done = true;
+                else
+                    (void)cudaGetLastError();
             }
         });
     }
