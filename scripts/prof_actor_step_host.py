@@ -9,7 +9,7 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-from verl_b200 import bert_padding, ops  # noqa: E402
+from verl_b200 import ops  # noqa: E402,F401  (loads the library)
 from verl_b200.trainer.ppo import core_algos  # noqa: E402
 from verl_b200.workers.actor import dp_actor  # noqa: E402
 

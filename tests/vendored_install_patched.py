@@ -5,7 +5,6 @@ modules are loaded from the oracle/_ref snapshot first (oracle.ref_import: the r
 modules stays the reference's.  The reference's test files then import ``verl.*`` as usual."""
 import os
 import sys
-import types
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
