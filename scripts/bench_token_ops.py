@@ -42,6 +42,38 @@ def timeit(fn, iters=10, warmup=3):
     return e0.elapsed_time(e1) / iters
 
 
+def timeit_graph(fn, iters=200):
+    """Replay latency of `fn` captured into a CUDA graph (None if the op cannot be captured: it reads a value back)."""
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            keep = fn()  # noqa: F841  (outputs live in the graph's pool)
+        for _ in range(5):
+            g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+    except Exception:  # noqa: BLE001
+        torch.cuda.synchronize()
+        return None
+
+
+# ops whose wrapper reads nothing back on the host (no ValueError semantics, no token counts): capturable
+GRAPHABLE = ("ppo_loss", "agg_loss", "masked_sum", "kl_penalty", "grpo_advantage", "remax", "value_loss", "kl_reward",
+             "gather_rows", "device time")
+
+
 def make(B, L, dev, seed=0):
     g = torch.Generator(device=dev).manual_seed(seed)
     lens = torch.randint(L // 4, L + 1, (B,), device=dev, generator=g)
@@ -112,6 +144,8 @@ def main():
     ap.add_argument("--tokens-log2", type=int, default=25)
     ap.add_argument("--only", default="", help="comma-separated substrings: run only the ops whose name contains one")
     ap.add_argument("--no-configs", action="store_true", help="skip the latencies at the BASELINE config sizes")
+    ap.add_argument("--graphs", action="store_true",
+                    help="config sizes: also the replay latency of every op that can be captured into a CUDA graph")
     args = ap.parse_args()
     only = [x for x in args.only.split(",") if x]
     dev = torch.device("cuda:0")
@@ -139,7 +173,11 @@ def main():
             if only and not any(o in name for o in only):
                 continue
             ms = timeit(fn, iters=50, warmup=5)
-            print(json.dumps({"config": cname, "op": name, "tokens": B * L, "us": round(ms * 1e3, 2)}), flush=True)
+            rec = {"config": cname, "op": name, "tokens": B * L, "us": round(ms * 1e3, 2)}
+            if args.graphs and any(g in name for g in GRAPHABLE):
+                gms = timeit_graph(fn)
+                rec["us_graph_replay"] = None if gms is None else round(gms * 1e3, 2)
+            print(json.dumps(rec), flush=True)
 
 
 if __name__ == "__main__":
