@@ -403,9 +403,9 @@ int vpg_data_metrics(const float* token_level_scores, const float* token_level_r
 /* compute_gae_advantage_return (core_algos.py:193-241): reverse recurrence per row with masked carry-through,
  * returns = adv + values, then masked_whiten (torch_functional.py:206-223) over the whole batch.
  * status[0] (i32) = 0 ok, 1 mask sum == 0, 2 mask sum == 1 (the reference raises ValueError there).  The word is
- * written by a one-thread kernel BETWEEN the recurrence / statistics pass and the normalisation pass; it may live in
- * device memory or in pinned host memory (UVA-mapped).  status_event (cudaEvent_t, may be NULL) is recorded right
- * behind that kernel, so a host that waits on it learns the status while the normalisation pass is still running.
+ * written by the last block of the recurrence / statistics kernel, i.e. BEFORE the normalisation pass starts; it may
+ * live in device memory or in pinned host memory (UVA-mapped).  status_event (cudaEvent_t, may be NULL) is recorded
+ * right behind that kernel, so a host that waits on it learns the status while the normalisation pass is still running.
  * workspace: vpg_gae_workspace_bytes(B, L). */
 size_t vpg_gae_workspace_bytes(int64_t B, int64_t L);
 int vpg_gae(const float* token_level_rewards, const float* values, const void* mask, int mask_dtype, int64_t B,

@@ -605,7 +605,7 @@ __global__ void data_metrics_kernel(const float* __restrict__ scores, const floa
         }
     }
     // epilogue: the eleven block sums share one barrier pair, the six max / min keys a second one; thread 0 issues every
-    // atomic (the per-block cost is what bounds how finely the sweep can be cut: profiles/r2_ab_token_grid.txt)
+    // atomic (the per-block cost is what bounds how finely the sweep can be cut: profiles/r2_ab_token_grid_after_epilogue_fusion.txt)
     __shared__ double red_n[11 * 32];
     __shared__ unsigned int red_k[6 * 32];
     double v[11] = {s1[0], s2[0], s1[1], s2[1], s1[2], s2[2], d1, d2, cnt, s_sc, s_rw};

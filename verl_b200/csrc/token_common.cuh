@@ -52,7 +52,7 @@ __device__ __forceinline__ void stv(float* __restrict__ p, long long i, const Pa
 // ~2.5 waves (2048 rows, one block each) the last, partial wave costs 10-25 % of the sweep — but every block ends in
 // barriers and atomics, so how finely a sweep may be cut depends on its epilogue.  `per_sm` is the kernel's own target of
 // blocks per SM in total (never less than two iterations of work per block), from the A/B at 8 / 16 / 32 per SM after the
-// epilogues were fused (profiles/r2_ab_token_grid.txt): 8 for the fused loss (seven block sums), 16 for the sweeps with
+// epilogues were fused (profiles/r2_ab_token_grid_after_epilogue_fusion.txt): 8 for the fused loss (seven block sums), 16 for the sweeps with
 // two or three sums, 32 for the ones that end in one atomic or none.  `VPG_TOK_BLOCKS_PER_SM` overrides all of them.
 static inline int blocks_per_row(int64_t B, int64_t L, int vec, int per_sm = 8) {
     static const int forced = env_int("VPG_TOK_BLOCKS_PER_SM", 0);
