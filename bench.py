@@ -933,7 +933,7 @@ def run_ours(args, name, cfg):
                        "bwd_chunking": ws["mode"],
                        "peak_allocated_bytes_in_timed_region": int(peak_mem),
                        "budget": f"{args.bwd_ws_mb} MiB (--bwd-ws-mb)" if args.bwd_ws_mb else
-                                 "library default: $VPG_BWD_WS_MB or 4096 MiB of dlogits (the [T,V] logits are never stored)"},
+                                 "library default: $VPG_BWD_WS_MB or 3072 MiB of dlogits (the [T,V] logits are never stored)"},
             "cpu_baseline": cpu,
         }
         if args.token_ops and world == 1:  # outside the timed region; a few seconds
@@ -979,7 +979,7 @@ def main():
     ap.add_argument("--token-ops", action=argparse.BooleanOptionalAction, default=True,
                     help="N=1: add the token-op HBM roofline table as `extra` (default on; --no-token-ops skips it)")
     ap.add_argument("--bwd-ws-mb", type=int, default=0,
-                    help="dlogits workspace budget of the backward in MiB (0 = library default, 4096)")
+                    help="dlogits workspace budget of the backward in MiB (0 = library default, 3072)")
     ap.add_argument("--tp-reduce", choices=["auto", "fused", "nccl", "multimem", "overlap"], default="auto",
                     help="N > 1: d_hidden all-reduce inside the d_weight GEMM kernel (fused; default when NVSwitch multicast "
                          "is available), after the GEMMs (nccl), under the d_weight GEMM on a second stream (overlap) or "

@@ -130,7 +130,7 @@ int vpg_lce_fwd_partials_push(const void* hidden_bf16, const void* weight_bf16, 
  * Workspace size: vpg_lce_bwd_workspace_bytes().  g_lp / g_ent may be NULL (treated as zeros).
  * d_hidden: bf16 [T,H]; d_weight: bf16 [V,H].  For vocab-parallel shards the caller all-reduces d_hidden. */
 size_t vpg_lce_bwd_workspace_bytes(int64_t T, int64_t H, int64_t V, int64_t chunk_v);
-int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V); /* budget: $VPG_BWD_WS_MB (default 4096) MiB */
+int64_t vpg_lce_bwd_default_chunk(int64_t T, int64_t H, int64_t V); /* budget: $VPG_BWD_WS_MB (default 3072) MiB */
 /* Largest chunk whose dlogits buffer fits `budget_bytes`, then the chunk count (up to +8) that wastes the fewest waves
  * of the persistent grid.  Fewer chunks = fewer launches and fp32 d_hidden round trips: one 20 GB chunk at configs[1]
  * is 2.5 % faster than seven 2.85 GB chunks. */
@@ -208,7 +208,7 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args);
 /* The chunking the backward will use for (chunk_v, chunk_t) as passed to vpg_lce_bwd_ex:
  * out4 = {mode (0 one block, 1 column chunks with an fp32 [T,H] d_hidden accumulator — the reference's _Split_Dlogits_N,
  * 2 row chunks with an fp32 [V,H] d_weight accumulator — its _Split_Dlogits_M), chunk width / height, number of chunks,
- * workspace bytes}.  With both 0 the dlogits block is bounded by $VPG_BWD_WS_MB (default 4096 MiB) and the orientation
+ * workspace bytes}.  With both 0 the dlogits block is bounded by $VPG_BWD_WS_MB (default 3072 MiB) and the orientation
  * with the smaller accumulator is taken (row chunks when T > V, e.g. a vocab shard of a long micro-batch). */
 int vpg_lce_bwd_plan(int64_t T, int64_t H, int64_t V, int64_t chunk_v, int64_t chunk_t, int64_t* out4);
 

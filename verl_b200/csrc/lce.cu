@@ -53,7 +53,7 @@ struct Tuning {
     int worker_perm = 0;     // VPG_WORKER_PERM=1: neighbour workers stream the same vocab split
     int cluster1 = 1;        // VPG_CLUSTER1=2: launch single-CTA tiles as clusters of two
     int reserve_pairs = -1;  // VPG_BWD_RESERVE_PAIRS: override of the caller's reserve_cta_pairs
-    int bwd_ws_mb = 4096;    // VPG_BWD_WS_MB: default dlogits workspace budget (MiB)
+    int bwd_ws_mb = 3072;    // VPG_BWD_WS_MB: default dlogits workspace budget (MiB)
     int splitk = 1;          // VPG_SPLITK=0 disables the split-K tail of the gradient GEMMs
     int wide = 3;            // VPG_GEMM_WIDE bit mask: 256x512 tiles of CTA pairs in d_weight / plain GEMMs (1), d_hidden (2)
     int ds_tma = 1;          // VPG_DS_TMA=0: dlogits by per-lane global stores instead of smem + TMA tensor stores
@@ -69,7 +69,7 @@ static const Tuning& tuning() {
         t.worker_perm = env_int("VPG_WORKER_PERM", 0);
         t.cluster1 = env_int("VPG_CLUSTER1", 1);
         t.reserve_pairs = env_int("VPG_BWD_RESERVE_PAIRS", -1);
-        t.bwd_ws_mb = env_int("VPG_BWD_WS_MB", 4096);
+        t.bwd_ws_mb = env_int("VPG_BWD_WS_MB", 3072);
         t.splitk = env_int("VPG_SPLITK", 1);
         t.ds_tma = env_int("VPG_DS_TMA", 1);
         t.wide = env_int("VPG_GEMM_WIDE", 3);

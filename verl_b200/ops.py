@@ -77,8 +77,9 @@ def backward_plan(T: int, H: int, V: int, chunk_v: int = 0, chunk_t: int = 0) ->
 
 def backward_chunk(T: int, H: int, V: int, device, chunk_v: int = 0) -> int:
     """Explicit column-chunk width to pass to the backward, or 0 = let the library plan.  An explicit ``chunk_v`` wins.
-    Otherwise the library bounds the 16-bit dlogits block by $VPG_BWD_WS_MB (default 4096 MiB — the order of the
-    reference's default 9 504-column split, kernels.py:1492-1501, at 64k tokens) and chunks along the vocabulary or along
+    Otherwise the library bounds the 16-bit dlogits block by $VPG_BWD_WS_MB (default 3072 MiB — what the
+    reference's own default backward peaks at for 64k tokens: 9 504-column dlogits splits, kernels.py:1492-1501, plus its
+    outputs = 3.1 GB) and chunks along the vocabulary or along
     the tokens, whichever needs the smaller fp32 accumulator.  Only under memory pressure (the planned workspace exceeds
     half of what is free right now) this falls back to narrower vocabulary chunks.  The whole-vocabulary single block
     (20 GB at BASELINE configs[1]) is opt-in: ``kernels.set_backward_chunk`` or the environment variable."""
