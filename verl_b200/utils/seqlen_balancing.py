@@ -16,7 +16,6 @@ the sequence axis and that has an "attention_mask" [B,S] entry (TensorDict is no
 
 from __future__ import annotations
 
-import copy
 from itertools import chain
 from typing import Any, Mapping
 
@@ -54,24 +53,20 @@ def get_seqlen_balanced_partitions(seqlen_list: list[int], k_partitions: int, eq
 
 
 def log_seqlen_unbalance(seqlen_list: list[int], partitions: list[list[int]], prefix):
-    """seqlen_balancing.py:194-239: imbalance statistics of a partitioning against the naive contiguous split."""
-    k_partition = len(partitions)
-    batch_size = len(seqlen_list) // k_partition
-    min_sum_seqlen = max_sum_seqlen = None
-    total_sum_seqlen = 0
-    for offset in range(0, len(seqlen_list), batch_size):
-        cur = sum(seqlen_list[offset:offset + batch_size])
-        min_sum_seqlen = cur if min_sum_seqlen is None else min(min_sum_seqlen, cur)
-        max_sum_seqlen = cur if max_sum_seqlen is None else max(max_sum_seqlen, cur)
-        total_sum_seqlen += cur
-    balanced = [sum(seqlen_list[i] for i in p) for p in partitions]
+    """seqlen_balancing.py:194-239: imbalance statistics of a partitioning against the naive contiguous split
+    (consecutive runs of len // k sequences)."""
+    k = len(partitions)
+    run = len(seqlen_list) // k
+    naive = [sum(seqlen_list[lo:lo + run]) for lo in range(0, len(seqlen_list), run)]
+    scheduled = [sum(seqlen_list[i] for i in part) for part in partitions]
+    lo, hi = min(naive), max(naive)
     return {
-        f"{prefix}/min": min_sum_seqlen,
-        f"{prefix}/max": max_sum_seqlen,
-        f"{prefix}/minmax_diff": max_sum_seqlen - min_sum_seqlen,
-        f"{prefix}/balanced_min": min(balanced),
-        f"{prefix}/balanced_max": max(balanced),
-        f"{prefix}/mean": total_sum_seqlen / len(partitions),
+        f"{prefix}/min": lo,
+        f"{prefix}/max": hi,
+        f"{prefix}/minmax_diff": hi - lo,
+        f"{prefix}/balanced_min": min(scheduled),
+        f"{prefix}/balanced_max": max(scheduled),
+        f"{prefix}/mean": sum(naive) / k,
     }
 
 
@@ -80,13 +75,31 @@ def ceildiv(a, b):
 
 
 def roundup_divisible(a, b):
-    return ((a + b - 1) // b) * b
+    return ceildiv(a, b) * b
 
 
 def _fields(batch) -> dict:
     if hasattr(batch, "items"):
         return {k: v for k, v in batch.items() if isinstance(v, torch.Tensor)}
     raise TypeError("batch must be a mapping of name -> tensor with an 'attention_mask' entry")
+
+
+def _micro_batch_count(lengths, max_token_len, device, dp_group, same_micro_num_in_dp, min_num_micro_batch,
+                       num_batches_divided_by) -> int:
+    """How many micro-batches the mini-batch is cut into (seqlen_balancing.py:281-296): enough for `max_token_len`
+    tokens each, never more than sequences, at least what a pipeline-parallel caller asks for, the maximum over the
+    data-parallel group (every rank must step the same number of times), rounded up to the caller's multiple."""
+    count = min(len(lengths), ceildiv(sum(lengths), max_token_len))
+    if min_num_micro_batch is not None:
+        count = max(count, min_num_micro_batch)
+    if same_micro_num_in_dp and dist.is_initialized():
+        agreed = torch.tensor([count], device=device)
+        dist.all_reduce(agreed, op=dist.ReduceOp.MAX, group=dp_group)
+        count = int(agreed.cpu().item())
+    if num_batches_divided_by is not None:
+        count = roundup_divisible(count, num_batches_divided_by)
+    assert count <= len(lengths)
+    return count
 
 
 def rearrange_micro_batches(
@@ -107,26 +120,17 @@ def rearrange_micro_batches(
     assert max_token_len >= max_seq_len, (
         f"max_token_len must be greater than the sequence length. Got {max_token_len=} and {max_seq_len=}"
     )
-    seq_len_effective = ops.row_lengths(attention_mask).tolist()
-    total_seqlen = sum(seq_len_effective)
-    num_micro_batches = min(len(seq_len_effective), ceildiv(total_seqlen, max_token_len))
-    if min_num_micro_batch is not None:
-        num_micro_batches = max(min_num_micro_batch, num_micro_batches)  # pipeline-parallel callers
-    if dist.is_initialized() and same_micro_num_in_dp:
-        n = torch.tensor([num_micro_batches], device=attention_mask.device)
-        dist.all_reduce(n, op=dist.ReduceOp.MAX, group=dp_group)
-        num_micro_batches = int(n.cpu().item())
-    if num_batches_divided_by is not None:
-        num_micro_batches = roundup_divisible(num_micro_batches, num_batches_divided_by)
-    assert num_micro_batches <= len(seq_len_effective)
-
-    micro_bsz_idx = get_seqlen_balanced_partitions(seq_len_effective, num_micro_batches, equal_size=False)
+    lengths = ops.row_lengths(attention_mask).tolist()
+    count = _micro_batch_count(lengths, max_token_len, attention_mask.device, dp_group, same_micro_num_in_dp,
+                               min_num_micro_batch, num_batches_divided_by)
+    micro_bsz_idx = get_seqlen_balanced_partitions(lengths, count, equal_size=False)
     if use_dynamic_bsz_balance:
-        # heaviest (sum of squared lengths ~ attention work) micro-batch first (:298-306)
-        micro_bsz_idx.sort(
-            key=lambda partition: (sum(seq_len_effective[i] ** 2 for i in partition), min(partition) if partition else 0),
-            reverse=True,
-        )
+        # heaviest micro-batch first, weight = sum of squared lengths ~ attention work (:298-306); ties by first index
+
+        def work(part):
+            return sum(lengths[i] * lengths[i] for i in part), (min(part) if part else 0)
+
+        micro_bsz_idx.sort(key=work, reverse=True)
     order = torch.tensor(list(chain.from_iterable(micro_bsz_idx)), dtype=torch.int64).to(
         attention_mask.device, non_blocking=True)
     sizes = [len(p) for p in micro_bsz_idx]
@@ -136,11 +140,11 @@ def rearrange_micro_batches(
 
 
 def get_reverse_idx(idx_map):
-    """seqlen_balancing.py:322-337: output[idx_map[i]] = i."""
-    reverse_idx_map = copy.deepcopy(idx_map)
-    for i, idx in enumerate(idx_map):
-        reverse_idx_map[idx] = i
-    return reverse_idx_map
+    """seqlen_balancing.py:322-337: the inverse permutation, out[idx_map[i]] = i (a new list)."""
+    out = list(idx_map)
+    for position, source in enumerate(idx_map):
+        out[source] = position
+    return out
 
 
 class MicroBatch:
