@@ -13,7 +13,7 @@ for f in sys.argv[1:]:
             mem = d.get("memory") or {}
             print(f"{f}: N={d['n_gpus']} {d['ms_per_step']:.2f} ms/step {d['value']:.0f} tok/s e2e {d['e2e']['ms_per_step']:.2f} ms "
                   f"reduce={d.get('tp_reduce')} parity={(d.get('parity') or {}).get('ok')} chunks={mem.get('bwd_chunks')} "
-                  f"({mem.get('bwd_chunking')})\n   kernels {rk}\n   segments {seg}\n   clocks {d.get('clocks')}\n   roofline frac {d['roofline']['frac']:.3f} "
+                  f"({mem.get('bwd_chunking')})\n   kernels {rk}\n   segments {seg}\n   clocks {d.get('clocks')}\n   roofline frac {d['roofline']['frac'] if d['roofline']['frac'] is None else round(d['roofline']['frac'], 3)} "
                   f"useful/burst {(d.get('roofline_step') or {}).get('useful_frac_of_burst')}")
     except Exception as e:  # noqa: BLE001
         print(f, "ERR", e)
