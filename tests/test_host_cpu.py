@@ -198,3 +198,27 @@ def test_d_hidden_allreduce_overlap_plan():
     pays, pairs = _overlap_plan(262144, 5120, 19008, 8, None, workers=w)                        # configs[4]
     assert pays and pairs == 8
     assert _overlap_plan(1024, 3584, 19008, 8, None, workers=4) == (False, 0)  # fewer pairs than the reserve
+
+
+def test_backward_plan_at_the_baseline_shapes():
+    """The backward's workspace plan under the default 3 GiB dlogits budget (host-only function): an 8-way vocab shard of
+    the BASELINE shapes stays ONE block (no fp32 accumulator pass), the single-GPU headline shape is cut along the
+    vocabulary, a vocab shard of a long micro-batch along the tokens (the smaller accumulator), and no plan exceeds the
+    budget by more than its one fp32 accumulator."""
+    from verl_b200 import ops
+
+    if os.environ.get("VPG_BWD_WS_MB"):
+        pytest.skip("VPG_BWD_WS_MB overrides the default budget")
+    budget = 3072 << 20
+    plans = {
+        "c2 n1": ((65536, 3584, 152064), "vocab", 7),
+        "c2 n8": ((65536, 3584, 19008), "single", 1),
+        "c4 n8": ((65536, 8192, 16032), "single", 1),
+        "c2 n4": ((65536, 3584, 38016), "token", 2),
+        "c5 n8": ((262144, 5120, 19008), "token", 4),
+    }
+    for name, ((T, H, V), mode, chunks) in plans.items():
+        p = ops.backward_plan(T, H, V)
+        assert p["mode"].startswith(mode) and p["chunks"] == chunks, (name, p)
+        acc = 0 if mode == "single" else 4 * H * (T if mode == "vocab" else V)
+        assert p["workspace_bytes"] <= budget + acc + (64 << 20), (name, p)
