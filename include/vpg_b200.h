@@ -359,6 +359,26 @@ int vpg_grpo_advantage(const float* token_level_rewards, const void* mask, int m
                        int64_t B, int64_t L, int64_t num_groups, float epsilon, int norm_by_std, float* advantages,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* vpg_grpo_advantage without a workspace argument.  No counterpart in the reference: it exists for hosts that cannot
+ * bring scratch memory to the call — a C / ctypes host without PyTorch's caching allocator (its only source of scratch
+ * would be cudaMalloc / cudaFree around the call, which stall every stream on the device, the colocated rollout engine's
+ * too), or a trainer whose GPU memory was handed wholesale to another pool so that an allocation in mid-step fails.
+ * Inputs and the `advantages` output are still the caller's; results are those of vpg_grpo_advantage.
+ *  - The scratch is a fixed array inside the library image (global memory, 576.25 KiB, 256-byte aligned).  Every GPU on
+ *    which the library gets loaded carries it until the process exits, whether or not this function is ever called.
+ *  - Limit: B <= VPG_GRPO_STATIC_MAX_ROWS (any L, any G <= B).  A larger B returns VPG_ERR_WORKSPACE and launches
+ *    nothing; use vpg_grpo_advantage for such batches.
+ *  - The first call on each device (made with that device current) looks the array's device address up through
+ *    cudaGetSymbolAddress and caches it.  Make that first call during start-up, before any stream capture is begun.
+ *  - The call itself allocates and frees nothing: a memset of the bytes it uses and three kernel launches on `stream`.
+ *  - One array per GPU, shared by all calls, holding whatever the last call left behind.  Each call clears the part it
+ *    needs first, so back-to-back calls on one stream are independent.  Calls that may overlap on the GPU (two streams,
+ *    two host threads) race on the array: order them yourself (events / one stream). */
+#define VPG_GRPO_STATIC_MAX_ROWS 16384
+int vpg_grpo_advantage_static(const float* token_level_rewards, const void* mask, int mask_dtype,
+                              const int32_t* group_ids, int64_t B, int64_t L, int64_t num_groups, float epsilon,
+                              int norm_by_std, float* advantages, void* stream);
+
 /* The other outcome-reward estimators with GRPO's skeleton (kind = VPG_ADV_*): RLOO, OPO, GPG,
  * REINFORCE++-baseline (followed by masked_whiten over the broadcast matrix, binary masks), GRPO-pass@k.
  * f_norm is GPG's normaliser.  status[0] (i32, device): 0 ok, 1 / 2 = mask sum 0 / 1 (REINFORCE++-baseline's

@@ -127,6 +127,10 @@ SIGNATURES: dict[str, tuple] = {
         [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p,
          c_size_t, c_void_p],
     ),
+    "vpg_grpo_advantage_static": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p],
+    ),
     "vpg_kl_reward_workspace_bytes": (c_size_t, [c_int64]),
     "vpg_kl_reward": (
         c_int,

@@ -1395,3 +1395,71 @@ int vpg_masked_whiten(const float* values, const void* mask, int mask_dtype, int
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// GRPO advantage for callers that cannot hand the library a scratch buffer (no counterpart in the reference).
+//
+// vpg_grpo_advantage needs (B + 3*G) doubles + B floats of scratch between its three launches, and every other entry
+// point of this library leaves it to the caller to bring that memory.  Two kinds of hosts cannot: a plain C / ctypes
+// host that runs without PyTorch's caching allocator, where the only way to get scratch is cudaMalloc / cudaFree around
+// the call, and both of those stall every stream of the device (the rollout engine that shares the GPU included); and a
+// trainer colocated with a rollout engine whose memory pool was sized to take all of HBM, where a cudaMalloc in the
+// middle of a step simply fails.  For them the scratch lives in the library image itself: one fixed array in device
+// global memory per GPU that loads the library, resident from module load until the process exits.
+//
+// The array is shared by every call on that GPU and keeps whatever the previous call left in it.  The part a call uses
+// is cleared on the stream at the start of the call (as vpg_grpo_advantage always does with its workspace), so calls
+// that follow one another on a stream are independent; two calls whose kernels can overlap on the GPU (different
+// streams, different host threads) would race on the array and must be ordered by the caller.
+// =====================================================================================================
+namespace vpg {
+
+constexpr int64_t kGrpoStaticMaxRows = VPG_GRPO_STATIC_MAX_ROWS;
+// worst case G == B: (B + 3B) doubles + B floats + 16 bytes, rounded up to the array's alignment (576.25 KiB)
+constexpr size_t kGrpoStaticBytes =
+    ((static_cast<size_t>(kGrpoStaticMaxRows) * (4 * sizeof(double) + sizeof(float)) + 16 + 255) / 256) * 256;
+
+static __device__ __align__(256) unsigned char g_grpo_static_scratch[kGrpoStaticBytes];
+
+// Device address of g_grpo_static_scratch on the CURRENT device.  In host code the array's name is only a handle for the
+// runtime's symbol table, not something a kernel can dereference, so the address is looked up once per device with
+// cudaGetSymbolAddress (which may also be the call that loads this module onto the device) and cached.
+static int grpo_static_scratch(void** out) {
+    static std::mutex mu;
+    static void* cache[64] = {nullptr};
+    int dev = -1;
+    VPG_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return set_error(VPG_ERR_UNSUPPORTED, "device ordinal %d outside the address cache (0..63)", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!cache[dev]) {
+        void* p = nullptr;
+        VPG_CUDA(cudaGetSymbolAddress(&p, g_grpo_static_scratch));
+        if (!p) return set_error(VPG_ERR_CUDA, "cudaGetSymbolAddress returned a null address on device %d", dev);
+        cache[dev] = p;
+    }
+    *out = cache[dev];
+    return VPG_OK;
+}
+
+}  // namespace vpg
+
+extern "C" {
+
+int vpg_grpo_advantage_static(const float* rewards, const void* mask, int mask_dtype, const int32_t* group_ids,
+                              int64_t B, int64_t L, int64_t G, float epsilon, int norm_by_std, float* advantages,
+                              void* stream) {
+    using namespace vpg;
+    if (B > kGrpoStaticMaxRows)
+        return set_error(VPG_ERR_WORKSPACE,
+                         "vpg_grpo_advantage_static: B=%lld rows exceed the built-in scratch (at most %lld rows); use "
+                         "vpg_grpo_advantage with a caller-provided workspace",
+                         (long long)B, (long long)kGrpoStaticMaxRows);
+    void* scratch = nullptr;
+    const int rc = grpo_static_scratch(&scratch);
+    if (rc != VPG_OK) return rc;
+    // same validation, clearing and launches as the workspace variant; G <= B <= max rows bounds the bytes it touches
+    return vpg_grpo_advantage(rewards, mask, mask_dtype, group_ids, B, L, G, epsilon, norm_by_std, advantages, scratch,
+                              kGrpoStaticBytes, stream);
+}
+
+}  // extern "C"
