@@ -222,3 +222,20 @@ def test_backward_plan_at_the_baseline_shapes():
         assert p["mode"].startswith(mode) and p["chunks"] == chunks, (name, p)
         acc = 0 if mode == "single" else 4 * H * (T if mode == "vocab" else V)
         assert p["workspace_bytes"] <= budget + acc + (64 << 20), (name, p)
+
+
+def test_ascending_mark_lapses_on_in_place_edits():
+    """the one-pass pad_input path is only taken while the index tensor is untouched since unpad_indices made it."""
+    from verl_b200 import ops
+
+    base = torch.arange(10)
+    idx = base[:6]
+    assert not ops.is_marked_ascending(idx)
+    ops.mark_ascending(idx)
+    assert ops.is_marked_ascending(idx)
+    assert not ops.is_marked_ascending(idx.clone())  # a different object carries no mark
+    for edit in (lambda t: t.add_(1), lambda t: t.__setitem__(0, 5), lambda t: t.copy_(torch.arange(6).flip(0)),
+                 lambda t: base.mul_(2)):  # the last one writes through the base the view shares its counter with
+        ops.mark_ascending(idx)
+        edit(idx)
+        assert not ops.is_marked_ascending(idx)

@@ -194,7 +194,7 @@ def test_pad_input_one_pass_gap_fill(row, dtype, dev):
         B, S = mask.shape
         md = mask.to(dev)
         idx, _, _, _ = ops.unpad_indices(md)
-        assert getattr(idx, "_vpg_ascending", False)
+        assert ops.is_marked_ascending(idx)
         n = idx.numel()
         vals = (torch.randn(n, row, generator=g) * 100).to(dtype).to(dev)
         fast = ops.scatter_rows(vals, idx, B * S)
@@ -205,3 +205,21 @@ def test_pad_input_one_pass_gap_fill(row, dtype, dev):
         assert torch.equal(fast, ref)
         out = bert_padding.pad_input(vals, idx, B, S)
         assert torch.equal(out.reshape(B * S, row), ref)
+
+
+def test_pad_input_after_in_place_edit_of_marked_indices(dev):
+    """A marked index tensor that is permuted in place afterwards must fall back to memset + scatter: the
+    one-pass gap-fill kernel assumes strictly ascending indices and would drop rows silently."""
+    from verl_b200 import ops
+
+    g = torch.Generator().manual_seed(3)
+    mask = (torch.rand(8, 257, generator=g) < 0.6).long().to(dev)
+    idx, _, _, _ = ops.unpad_indices(mask)
+    assert ops.is_marked_ascending(idx)
+    idx.copy_(idx.flip(0))  # still a valid scatter target list, no longer ascending
+    assert not ops.is_marked_ascending(idx)
+    vals = torch.randn(idx.numel(), 24, generator=g).to(dev)
+    out = ops.scatter_rows(vals, idx, mask.numel())
+    ref = torch.zeros(mask.numel(), 24, device=dev)
+    ref[idx] = vals
+    assert torch.equal(out, ref)

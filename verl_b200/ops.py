@@ -361,8 +361,18 @@ def unpad_indices(mask2d):
     check(_lib_().vpg_stream_synchronize(stream_ptr(dev)))  # ctypes drops the GIL; no Stream object on the way
     nnz, max_seqlen = slot.read_pair()
     indices = indices_full[:nnz]
-    indices._vpg_ascending = True  # provenance mark: pad_input may then fill gaps in one pass (see scatter_rows)
+    mark_ascending(indices)  # provenance mark: pad_input may then fill gaps in one pass (see scatter_rows)
     return indices, seqlens, cu, max_seqlen
+
+
+def mark_ascending(indices) -> None:
+    """Record that `indices` is strictly ascending and in range AS OF NOW (its autograd version counter is stored with
+    the mark; views share the counter with their base, so an in-place write through either one invalidates it)."""
+    indices._vpg_ascending = ("version", indices._version)
+
+
+def is_marked_ascending(indices) -> bool:
+    return getattr(indices, "_vpg_ascending", None) == ("version", indices._version)
 
 
 def response_rows(indices, ids_rmpad, S: int, L: int):
@@ -402,9 +412,11 @@ def scatter_rows(src, indices, n_out: int):
 
     Indices that come straight out of ``unpad_indices`` (strictly ascending by construction; the tensor object carries
     the mark ``_vpg_ascending``) take the ONE-pass kernel: every output row — scattered row or zero gap — is written
-    exactly once.  Any other index tensor (the API does not promise an order) takes memset + scatter."""
+    exactly once.  Any other index tensor (the API does not promise an order) takes memset + scatter — and so does a
+    marked tensor that was edited in place afterwards: the mark records the tensor's version counter and lapses when
+    the counter has moved (``indices.add_()``, ``indices[...] = ``, ``copy_``, an in-place sort)."""
     _require_cuda(src, indices)
-    fill = 2 if getattr(indices, "_vpg_ascending", False) else 1
+    fill = 2 if is_marked_ascending(indices) else 1
     src = src.contiguous()
     row_shape = src.shape[1:]
     row_bytes = src.element_size() * int(math.prod(row_shape)) if len(row_shape) else src.element_size()
