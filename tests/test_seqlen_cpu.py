@@ -128,6 +128,9 @@ def _ulysses_worker(rank, world, port_no, q):
         x = torch.full((2, 3), float(rank))
         y = U.gather_outputs_and_unpad(x, gather_dim=1, grad_scaler=False)
         assert y.shape == (2, 3 * world) and y[0].tolist() == [float(r) for r in range(world) for _ in range(3)]
+        # the plain axis-0 gather the reference also exports (verl/utils/ulysses.py:155-162)
+        z = U.all_gather_tensor(torch.full((2, 3), float(rank)))
+        assert z.shape == (2 * world, 3) and z[:, 0].tolist() == [float(r) for r in range(world) for _ in range(2)]
         q.put((rank, "ok"))
     except Exception as e:
         q.put((rank, f"{type(e).__name__}: {e}"))
@@ -162,3 +165,5 @@ def test_ulysses_without_group_is_identity():
     assert U.ulysses_pad(ids, None, sp_size=1) == (ids, None, 0)
     with pytest.raises(AssertionError):
         U.validate_ulysses_config(28, 8)
+    with pytest.raises(RuntimeError, match="gather_outputs_and_unpad"):
+        U.gather_outpus_and_unpad(x, 0)

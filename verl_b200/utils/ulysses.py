@@ -25,6 +25,7 @@ __all__ = [
     "set_ulysses_sequence_parallel_group", "get_ulysses_sequence_parallel_group",
     "get_ulysses_sequence_parallel_world_size", "get_ulysses_sequence_parallel_rank", "slice_input_tensor", "Gather",
     "gather_outputs_and_unpad", "ulysses_pad", "ulysses_pad_and_slice_inputs", "validate_ulysses_config",
+    "all_gather_tensor", "gather_outpus_and_unpad",
 ]
 
 _state = {"group": None}
@@ -72,6 +73,31 @@ def slice_input_tensor(x: torch.Tensor, dim: int, padding: bool = True, group=No
     return x.narrow(dim, rank * share, share).contiguous()
 
 
+def _stacked_all_gather(src: torch.Tensor, group, async_op: bool = False):
+    """ONE `all_gather_into_tensor` of a contiguous `src` into a fresh `[world, *src.shape]` buffer -> (buffer, work)."""
+    world = dist.get_world_size(group)
+    stacked = src.new_empty((world, *src.shape))
+    work = dist.all_gather_into_tensor(stacked.view(world * src.shape[0], *src.shape[1:]) if src.dim() else stacked, src,
+                                       group=group, async_op=async_op)
+    return stacked, work
+
+
+def all_gather_tensor(local_tensor: torch.Tensor, group=None, async_op: bool = False) -> torch.Tensor:
+    """Plain (non-differentiable) gather along axis 0: rank r's rows land at `[r*n, (r+1)*n)` of the result
+    (verl/utils/ulysses.py:155-162).  As there, ``async_op=True`` returns the buffer right away with the collective still
+    in flight on the backend's stream: the caller orders its own use of the result."""
+    g = _resolve(group)
+    src = local_tensor.contiguous()
+    stacked, _ = _stacked_all_gather(src, g, async_op)
+    return stacked.view(stacked.shape[0] * src.shape[0], *src.shape[1:]) if src.dim() else stacked
+
+
+def gather_outpus_and_unpad(*args, **kwargs):
+    """The misspelt name the reference keeps only to point callers at the right one (verl/utils/ulysses.py:237-240)."""
+    raise RuntimeError(
+        "please use verl.utils.ulysses.gather_outputs_and_unpad instead of verl.utils.ulysses.gather_outpus_and_unpad")
+
+
 class Gather(torch.autograd.Function):
     """Differentiable all-gather along `gather_dim` (verl/utils/ulysses.py:194-234).  Backward: this rank's slice of the
     incoming gradient, times the group size when ``grad_scaler`` (every sp rank holds a replica of the loss)."""
@@ -82,9 +108,7 @@ class Gather(torch.autograd.Function):
         ctx.meta = (dist.get_rank(group), world, gather_dim % max(local_tensor.dim(), 1), local_tensor.size(gather_dim),
                     bool(grad_scaler))
         src = local_tensor.contiguous()
-        stacked = src.new_empty((world, *src.shape))
-        dist.all_gather_into_tensor(stacked.view(world * src.shape[0], *src.shape[1:]) if src.dim() else stacked, src,
-                                    group=group)
+        stacked, _ = _stacked_all_gather(src, group)
         axis = ctx.meta[2]
         if src.dim() == 0:
             return stacked
