@@ -163,10 +163,15 @@ int vpg_lce_bwd_f32(const void* hidden_f32, const void* weight_f32, const void* 
  *      multicast-bound) bf16 [T,H] buffer and ar_d_hidden_mc the multicast address of the same buffer.  The backward
  *      computes d_hidden BEFORE its last d_weight GEMM; that GEMM's otherwise idle warp (one per CTA) then pulls the
  *      switch-reduced sum of this rank's 1/world slice (multimem.ld_reduce) and broadcasts it into every rank's buffer
- *      (multimem.st) while the tensor cores work on d_weight.  ar_flags: this rank's 17 uint32 flags (zeroed once at
+ *      (multimem.st) while the tensor cores work on d_weight.  ar_flags: this rank's 18 uint32 flags (zeroed once at
  *      allocation) in symmetric memory; ar_peer_flags[r]: rank r's flag array as mapped into this process (HOST array
- *      of ar_world device pointers, own rank included); ar_epoch: call counter, identical on all ranks, never 0.
- *      When the call's kernels have completed on a rank, its d_hidden holds the sum over all ranks.
+ *      of ar_world device pointers, own rank included); ar_epoch: call counter, identical on all ranks, in
+ *      [1, 2^31) (the top bit marks a poisoned flag).
+ *      When the call's kernels have completed on a rank and ar_flags[17] is still 0, its d_hidden holds the sum over
+ *      all ranks.  Every wait for a peer inside the kernel has a budget ($VPG_AR_TIMEOUT_MS, default 60000, 0 = none):
+ *      a rank that gives up on a peer (it never launched the matching call) skips its share of the reduction, stores
+ *      ar_epoch in ar_flags[17] and poisons its done flag so that late peers fail too instead of returning a partial
+ *      sum.  The caller reads ar_flags[17] after the call (non-zero = that call's d_hidden is not the sum).
  *  (b) d_hidden_ready_event (cudaEvent_t) — recorded as soon as d_hidden is complete; d_hidden is computed before the
  *      last d_weight GEMM, which runs on the fewest persistent workers that keep its number of scheduling rounds
  *      (at least reserve_cta_pairs CTA pairs stay free), so the caller's own all-reduce (NCCL on a second stream)

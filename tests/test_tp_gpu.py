@@ -70,3 +70,16 @@ def test_reference_own_kernel_test_passes_on_one_gpu():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "mode=ours: all cases passed" in r.stdout, r.stdout[-3000:]
     assert r.stdout.count("Verified forward & backward correctness.") == 5, r.stdout[-3000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_in_kernel_allreduce_gives_up_on_a_missing_peer():
+    """The fused d_hidden all-reduce waits for its peers inside the d_weight GEMM kernel.  A peer that never launches the
+    matching backward must cost the others a bounded wait and a RuntimeError, not a hung GPU; a peer that arrives late
+    must fail too rather than return a partial sum (scripts/tp_timeout_check.py)."""
+    env = dict(os.environ, VPG_AR_TIMEOUT_MS="1500")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29545", os.path.join(ROOT, "scripts", "tp_timeout_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT OK" in r.stdout and "MISMATCH" not in r.stdout

@@ -809,6 +809,9 @@ int vpg_lce_bwd_ex(const vpg_lce_bwd_args* args) {
                 p.ar_mc = a.ar_d_hidden_mc;
                 p.ar_nvec = T * H / 8;
                 p.ar_flags = a.ar_flags;
+                // budget of each wait for a peer inside the kernel (a peer that raised or diverged never sets its flag)
+                static const int ar_timeout_ms = env_int("VPG_AR_TIMEOUT_MS", 60000);
+                p.ar_timeout_ns = ar_timeout_ms > 0 ? static_cast<unsigned long long>(ar_timeout_ms) * 1000000ull : 0ull;
                 for (int i = 0; i < a.ar_world; ++i) {
                     VPG_CHECK_ARG(a.ar_peer_flags[i], "ar_peer_flags[%d] is null", i);
                     p.ar_peer_flags[i] = a.ar_peer_flags[i];

@@ -124,7 +124,9 @@ struct TcParams {
     unsigned int ar_epoch;    // call counter, identical on all ranks; flags carry it
     void* ar_mc;              // multicast address of the symmetric buffer
     long long ar_nvec;        // 16-byte vectors in the buffer
-    unsigned int* ar_flags;   // this rank's flags: [0, 8) ready[peer], [8, 16) done[peer], [16] local done counter
+    unsigned int* ar_flags;   // this rank's flags: [0, 8) ready[peer], [8, 16) done[peer], [16] local done counter,
+                              // [17] error word (epoch of the first call whose exchange timed out or was poisoned)
+    unsigned long long ar_timeout_ns;  // budget of each wait for a peer's flag; 0 = wait for ever
     unsigned int* ar_peer_flags[8];  // peer-mapped addresses of every rank's flag array
     int hint_a, hint_b;  // L2 eviction priority of the A / B operand loads: 0 normal, 1 evict-first, 2 evict-last
     int worker_perm;  // 0/1: identity; S > 1: group physical neighbours on residues mod S (see kernel)
@@ -556,21 +558,49 @@ __device__ __forceinline__ void multimem_st_bf16x8(void* mc_addr, const uint4& v
 //                 all peers are done, so kernel completion means the local buffer holds the complete sum (and no peer
 //                 still reads this rank's partials).
 // Flags carry the call's epoch (same on all ranks, collective call order), so they never need resetting.
+//
+// A peer that never launches this kernel (it raised, ran out of memory, or its call order / epoch diverged) must not
+// hang the others inside a kernel: every wait has a budget (`ar_timeout_ns`, host: $VPG_AR_TIMEOUT_MS).  A rank whose
+// wait runs out skips its share of the reduction, stores the epoch in its error word ar_flags[17] (the host checks it
+// after the call and raises) and publishes its done flag POISONED (epoch | kArPoison), so that a peer which arrives
+// later and would otherwise complete with this rank's slice missing fails as well instead of returning a wrong sum.
+constexpr unsigned int kArPoison = 0x80000000u;  // epochs are 31-bit and never 0 (peer.py)
+constexpr int kArErrorWord = 17;
+
+// one lane: spin until *flag carries `epoch` (true), or its poisoned form / the budget runs out (false)
+__device__ __forceinline__ bool ar_wait_flag(const unsigned int* flag, unsigned int epoch, unsigned long long budget_ns,
+                                             unsigned int sleep_ns) {
+    unsigned long long t0 = 0;
+    for (unsigned int spin = 0;; ++spin) {
+        const unsigned int v = ld_acquire_sys_u32(flag);
+        if (v == epoch) return true;
+        if (v == (epoch | kArPoison)) return false;
+        if (budget_ns) {
+            if (spin == 0) t0 = global_timer_ns();
+            else if ((spin & 63u) == 0 && global_timer_ns() - t0 > budget_ns) return false;
+        }
+        __nanosleep(sleep_ns);
+    }
+}
+
 __device__ __forceinline__ void allreduce_worker(const TcParams& p, int cta, int num_ctas, int lane) {
     const int world = p.ar_world;
     const unsigned int epoch = p.ar_epoch;
     if (cta == 0 && lane < world) st_release_sys_u32(p.ar_peer_flags[lane] + p.ar_rank, epoch);
-    if (lane < world) {
-        while (ld_acquire_sys_u32(p.ar_flags + lane) != epoch) __nanosleep(100);
+    bool ok = true;
+    if (lane < world) ok = ar_wait_flag(p.ar_flags + lane, epoch, p.ar_timeout_ns, 100);
+    ok = __all_sync(0xffffffffu, ok);
+    if (!ok) {  // a peer's partial sums never became ready: nothing this rank could reduce is trustworthy
+        if (lane == 0) st_release_sys_u32(p.ar_flags + kArErrorWord, epoch);
+        __syncwarp();
     }
-    __syncwarp();
     const long long per = (p.ar_nvec + world - 1) / world;
     const long long v0 = per * p.ar_rank;
     const long long v1 = min(p.ar_nvec, v0 + per);
     uint4* base = reinterpret_cast<uint4*>(p.ar_mc);
     constexpr int kInFlight = 8;
     const long long stride = static_cast<long long>(num_ctas) * 32 * kInFlight;
-    for (long long i = v0 + static_cast<long long>(cta) * 32 * kInFlight + lane; i < v1; i += stride) {
+    for (long long i = v0 + static_cast<long long>(cta) * 32 * kInFlight + lane; ok && i < v1; i += stride) {
         uint4 v[kInFlight];
 #pragma unroll
         for (int j = 0; j < kInFlight; ++j)
@@ -584,13 +614,16 @@ __device__ __forceinline__ void allreduce_worker(const TcParams& p, int cta, int
     unsigned int last = 0;
     if (lane == 0) last = (atomicAdd(p.ar_flags + 16, 1u) == static_cast<unsigned int>(num_ctas - 1)) ? 1u : 0u;
     last = __shfl_sync(0xffffffffu, last, 0);
-    if (last) {  // every warp of this rank has fenced its broadcasts
+    if (last) {  // every warp of this rank has fenced its broadcasts (or recorded why it skipped them)
         if (lane == 0) p.ar_flags[16] = 0;
         asm volatile("fence.acq_rel.sys;" ::: "memory");
-        if (lane < world) st_release_sys_u32(p.ar_peer_flags[lane] + 8 + p.ar_rank, epoch);
+        const bool failed = ld_acquire_sys_u32(p.ar_flags + kArErrorWord) == epoch;
+        if (lane < world) st_release_sys_u32(p.ar_peer_flags[lane] + 8 + p.ar_rank, failed ? (epoch | kArPoison) : epoch);
     }
     if (cta == 0 && lane < world) {
-        while (ld_acquire_sys_u32(p.ar_flags + 8 + lane) != epoch) __nanosleep(200);
+        // a peer that is late, or poisoned its flag, leaves this rank's buffer without that peer's slice of the sum
+        if (!ar_wait_flag(p.ar_flags + 8 + lane, epoch, p.ar_timeout_ns, 200))
+            st_release_sys_u32(p.ar_flags + kArErrorWord, epoch);
     }
     __syncwarp();
 }

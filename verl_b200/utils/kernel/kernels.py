@@ -77,6 +77,8 @@ class Config:
     # "multimem" (multimem.red from the d_hidden GEMM epilogue; each GPU's NVLink ingress is world x |d_hidden|:
     # ~3 ms slower than NCCL at 8 GPUs for configs[1], hence opt-in); "auto" = fused when NVSwitch multicast is there
     _tp_reduce_mode: str = os.environ.get("VPG_TP_REDUCE", "nccl")
+    # "fused" mode only: True returns the symmetric slot itself as d_hidden (no copy; valid until the backward after next)
+    _tp_alias_slot: bool = os.environ.get("VPG_TP_ALIAS_SLOT", "0") == "1"
 
 
 _config = Config()
@@ -102,7 +104,7 @@ def set_vocab_parallel_exchange(mode: str):
     _config._tp_exchange = mode
 
 
-def set_reduce_d_hidden(enabled: bool, mode: str = "nccl"):
+def set_reduce_d_hidden(enabled: bool, mode: str = "nccl", alias_slot: bool | None = None):
     """True: the backward returns d_hidden already summed over the vocab-parallel group (the reference leaves that
     all-reduce to its callers).  mode "nccl": one all-reduce after the GEMMs.  mode "multimem" (needs the "nvlink"
     exchange and NVSwitch multicast): the d_hidden GEMM's epilogue reduces into every rank's fp32 buffer through the
@@ -110,14 +112,19 @@ def set_reduce_d_hidden(enabled: bool, mode: str = "nccl"):
     spares the SMs it does not need for its number of scheduling rounds; the NCCL all-reduce runs on a second stream
     under that GEMM.  mode "fused" (needs the "nvlink" exchange, NVSwitch multicast and bf16 operands): d_hidden is written
     into a symmetric slot and all-reduced INSIDE the d_weight GEMM kernel by its idle warps (two-shot NVLS:
-    multimem.ld_reduce + multimem.st), no SM and no launch of its own; the returned d_hidden is a view of one of two
-    alternating symmetric slots (valid until the backward after next).  mode "auto": "fused" when available, else
+    multimem.ld_reduce + multimem.st), no SM and no launch of its own; the sum lands in one of two alternating symmetric
+    slots and is returned as a copy (T*H bf16, small next to the GEMMs) — ``alias_slot=True`` returns the slot itself,
+    valid only until the backward after next, for callers that consume d_hidden at once.  The kernel's waits for its
+    peers are bounded ($VPG_AR_TIMEOUT_MS); a failed exchange raises from the next backward or from
+    ``peer.workspace(group, device).check_allreduce()``.  mode "auto": "fused" when available, else
     "overlap" when `_overlap_plan` says the hidden all-reduce is worth the extra scheduling rounds of the d_weight GEMM,
     else "nccl"."""
     if mode not in ("nccl", "multimem", "overlap", "auto", "fused"):
         raise ValueError(f"Invalid d_hidden reduction mode: {mode}")
     _config._tp_reduce_d_hidden = bool(enabled)
     _config._tp_reduce_mode = mode
+    if alias_slot is not None:
+        _config._tp_alias_slot = bool(alias_slot)
 
 
 _overlap_streams: dict = {}
@@ -310,6 +317,11 @@ def efficient_entropy_backward(
         d_hidden, d_weight = ops.lce_backward(
             hidden, weight, labels, lse.contiguous(), entropy_b.contiguous(), g_lp, g_ent, temperature,
             label_offset=rank * weight.shape[0], chunk_v=_config._chunk_v, allreduce=ar)
+        px.commit_d_hidden_slot(ar)  # epoch / slot parity advance only once the launch went through
+        if not _config._tp_alias_slot:
+            # the slot is overwritten by the backward after next; autograd may adopt the returned tensor as hidden.grad
+            # without a copy, and torch.autograd.grad hands it to the caller: give them memory of their own
+            d_hidden = d_hidden.clone()
     elif fused_reduce:
         # fused GEMM + all-reduce: zero every rank's fp32 buffer, barrier, the d_hidden GEMM's epilogue reduces into all
         # of them through the switch (multimem.red), barrier, convert this rank's copy

@@ -19,10 +19,14 @@ Replaces the exchange of verl/utils/kernel/kernels.py:609-661.
 
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
 _workspaces: dict = {}
+_AR_ERROR_WORD = 17  # kArErrorWord in csrc/tc_gemm.cuh
+_AR_CHECK = os.environ.get("VPG_AR_CHECK", "0") == "1"  # one tiny all-reduce per backward: ranks agree on T, H, epoch
 
 
 class PeerWorkspace:
@@ -110,19 +114,64 @@ class PeerWorkspace:
 
     def d_hidden_slot(self, T: int, H: int) -> dict:
         """Arguments of the in-kernel all-reduce (ops.lce_backward(allreduce=...)): a bf16 [T,H] view of one of two
-        alternating symmetric slots (the caller's d_hidden of step i stays intact while step i+1 runs), its multicast
-        address, the flag words and the call's epoch.  Same call order on all ranks (it is a collective's argument)."""
-        self._dh_parity = getattr(self, "_dh_parity", 0) ^ 1
-        self._ar_epoch = getattr(self, "_ar_epoch", 0) + 1
+        alternating symmetric slots (the d_hidden of step i stays intact while step i+1 runs), its multicast address, the
+        flag words and the call's epoch.  Same call order on all ranks (it is a collective's argument).
+
+        Nothing is consumed yet: slot parity and epoch advance in ``commit_d_hidden_slot`` AFTER the launch went through,
+        so a rank whose launch raises stays in step with its own state (its peers then run into the kernel's wait budget
+        and fail too, see ``check_allreduce``)."""
+        self.check_allreduce(wait=False)  # a failed exchange of an earlier call surfaces here at the latest
+        parity = getattr(self, "_dh_parity", 0) ^ 1
+        epoch = ((getattr(self, "_ar_epoch", 0) + 1) & 0x7FFFFFFF) or 1
         numel = (T * H + 1) // 2  # fp32 elements holding T*H bf16
-        t, hdl, _ = self._buffer(f"dh{self._dh_parity}", numel)
+        t, hdl, _ = self._buffer(f"dh{parity}", numel)
         ft, fh, _ = self._buffer("ar_flags", 64, zero=True)
         mc = self._mc_ptr(hdl)
         if not mc:
             raise RuntimeError("the in-kernel all-reduce needs NVSwitch multicast (no multicast address for the slot)")
+        if _AR_CHECK:  # debug: agree on the call before anyone can start waiting inside a kernel
+            sig = torch.tensor([T, -T, H, -H, epoch, -epoch], dtype=torch.int64, device=self.device)
+            dist.all_reduce(sig, op=dist.ReduceOp.MAX, group=self.group)
+            a = sig.tolist()
+            if a[0] != -a[1] or a[2] != -a[3] or a[4] != -a[5]:
+                raise RuntimeError(f"in-kernel all-reduce: ranks disagree on the call (T {-a[1]}..{a[0]}, H {-a[3]}..{a[2]}, "
+                                   f"epoch {-a[5]}..{a[4]}); this rank has T={T} H={H} epoch={epoch}")
         return dict(out=t.view(torch.bfloat16)[:T * H].view(T, H), mc=mc, flags=ft.view(torch.int32),
                     peer_flags=[int(p) for p in fh.buffer_ptrs], world=self.world, rank=self.rank,
-                    epoch=self._ar_epoch & 0x7FFFFFFF or 1)
+                    epoch=epoch, parity=parity)
+
+    def commit_d_hidden_slot(self, ar: dict):
+        """The backward that took `ar` has been enqueued: advance slot parity and epoch, and queue a 4-byte copy of this
+        rank's error word (flags[17], written by the kernel when a wait for a peer ran out or met a poisoned flag) into
+        pinned memory behind it.  No synchronisation here; ``check_allreduce`` looks at the word once the copy is done."""
+        self._dh_parity, self._ar_epoch = ar["parity"], ar["epoch"]
+        if getattr(self, "_err_host", None) is None:
+            self._err_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._err_event = torch.cuda.Event()
+        self._err_host.copy_(ar["flags"][_AR_ERROR_WORD:_AR_ERROR_WORD + 1], non_blocking=True)
+        self._err_event.record(torch.cuda.current_stream(self.device))
+        self._err_pending = True
+
+    def check_allreduce(self, wait: bool = True):
+        """Raise if an in-kernel all-reduce on this rank gave up on a peer (it never launched the matching backward:
+        raised, ran out of memory, or diverged in call order; budget: $VPG_AR_TIMEOUT_MS, default 60 s per wait).
+        The returned d_hidden of that call is not the sum.  ``wait=False`` only looks if the kernel has finished;
+        ``wait=True`` blocks on it (call it where you would synchronise anyway, e.g. before the optimizer step).  After a
+        failure the group's epochs are out of step: ``peer.reset()`` on every rank before using the workspace again."""
+        if not getattr(self, "_err_pending", False):
+            return
+        if wait:
+            self._err_event.synchronize()
+        elif not self._err_event.query():
+            return
+        self._err_pending = False
+        bad = int(self._err_host[0])
+        if bad:
+            self._err_pending = True  # sticky: every later check raises as well
+            raise RuntimeError(
+                f"in-kernel d_hidden all-reduce failed on rank {self.rank} (call epoch {bad & 0x7FFFFFFF}): a peer did not "
+                "reach the matching backward within the wait budget, or gave up itself; the gradient of that call is "
+                "not the sum over the ranks")
 
     def d_hidden_accum(self, T: int, H: int):
         """-> (local fp32 view [T, H], multicast address | 0)"""
