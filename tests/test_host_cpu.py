@@ -239,3 +239,31 @@ def test_ascending_mark_lapses_on_in_place_edits():
         ops.mark_ascending(idx)
         edit(idx)
         assert not ops.is_marked_ascending(idx)
+
+
+def test_backward_chunk_under_memory_pressure(monkeypatch):
+    """the fallback counts torch's cached-but-unused memory as available, narrows the vocabulary chunks when
+    the planned workspace exceeds half of that, and raises a clear error when even 256-column chunks cannot fit because
+    the fp32 [T,H] accumulator does not shrink with the chunk width."""
+    from verl_b200 import ops
+
+    T, H, V = 65536, 3584, 152064
+    GiB = 2**30
+
+    def pretend(free, reserved=0, allocated=0):
+        monkeypatch.setattr(torch.cuda, "mem_get_info", lambda device=None: (free, 180 * GiB))
+        monkeypatch.setattr(torch.cuda, "memory_reserved", lambda device=None: reserved)
+        monkeypatch.setattr(torch.cuda, "memory_allocated", lambda device=None: allocated)
+
+    pretend(100 * GiB)
+    assert ops.backward_chunk(T, H, V, "cuda:0") == 0  # plenty: the library plans
+    assert ops.backward_chunk(T, H, V, "cuda:0", chunk_v=4096) == 4096  # an explicit width always wins
+    pretend(1 * GiB, reserved=120 * GiB, allocated=20 * GiB)
+    assert ops.backward_chunk(T, H, V, "cuda:0") == 0  # the cache counts as available
+    pretend(4 * GiB)
+    narrow = ops.backward_chunk(T, H, V, "cuda:0")
+    assert narrow >= 256 and narrow % 256 == 0
+    assert ops.backward_plan(T, H, V, narrow)["workspace_bytes"] <= 4 * GiB
+    pretend(GiB // 2)  # less than the 896 MiB accumulator alone
+    with pytest.raises(RuntimeError, match="accumulator"):
+        ops.backward_chunk(T, H, V, "cuda:0")

@@ -86,12 +86,21 @@ def backward_chunk(T: int, H: int, V: int, device, chunk_v: int = 0) -> int:
     if chunk_v and chunk_v > 0:
         return int(chunk_v)
     lib = _lib_()
+    # what this process can still get: free on the device + what torch's caching allocator holds but is not using
     free, _total = torch.cuda.mem_get_info(device)
-    if int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, 0)) <= free // 2:
+    avail = free + max(0, torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device))
+    if int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, 0)) <= avail // 2:
         return 0
     chunk = int(lib.vpg_lce_bwd_default_chunk(T, H, V))
-    while chunk > 256 and int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, chunk)) > free // 2:
+    while chunk > 256 and int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, chunk)) > avail // 2:
         chunk = max(256, (chunk // 2) // 256 * 256)
+    need = int(lib.vpg_lce_bwd_workspace_bytes(T, H, V, chunk))
+    if need > avail:
+        # narrower chunks only shrink the dlogits block; the fp32 [T,H] accumulator of column chunking stays
+        raise RuntimeError(
+            f"lm-head backward: even {chunk}-column dlogits chunks need a {need / 2**20:.0f} MiB workspace (of which "
+            f"{T * H * 4 / 2**20:.0f} MiB is the fp32 [T,H] d_hidden accumulator, which chunking cannot shrink) but only "
+            f"{avail / 2**20:.0f} MiB are available on {device}; split the micro-batch (fewer tokens per call)")
     return chunk
 
 
