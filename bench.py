@@ -941,9 +941,90 @@ def run_ours(args, name, cfg):
                 line["extra"] = {"token_ops": token_ops_table(torch, dev, peaks)}
             except Exception as e:  # the headline line must not depend on the side table
                 line["extra"] = {"token_ops_error": f"{type(e).__name__}: {e}"}
+    # ---- the other BASELINE configurations, each in a child process of every rank (outside every timed region)
+    extra_cfgs = run_extra_configs(args, name, world, rank) if args.extra_configs else None
+    parity_ok = True
+    if rank == 0:
+        if extra_cfgs is not None:
+            line.setdefault("extra", {})["configs"] = extra_cfgs
+        # compact verdict as the LAST key: it survives a tail of the line
+        probes = {name: parity}
+        probes.update({k: v.get("parity") for k, v in (extra_cfgs or {}).items()})
+        bad = [k for k, v in probes.items() if v is not None and not v.get("ok", False)]
+        bad += [k for k, v in (extra_cfgs or {}).items() if "error" in v]
+        parity_ok = not bad
+        line["verdict"] = {
+            "parity_ok": parity_ok, "failed": bad, "n_gpus": world,
+            "lp_max_abs": (parity or {}).get("lp_max_abs"), "dw_excess": (parity or {}).get("dw_excess_over_tol"),
+            "dh_excess": (parity or {}).get("dh_excess_over_tol"),
+            "configs": {name: round(ms_dev, 2), **{k: (round(v["ms_per_step"], 2) if "ms_per_step" in v else "error")
+                                                     for k, v in (extra_cfgs or {}).items()}},
+            "unit": "ms_per_step; parity_ok covers the fp32 probe of every configuration listed, at this N",
+        }
         print(json.dumps(line), flush=True)
     if world > 1:
+        flag = torch.tensor([1 if parity_ok else 0], device=dev)
+        dist.broadcast(flag, src=0)
+        parity_ok = bool(int(flag.item()))
         dist.destroy_process_group()
+    if not parity_ok:  # a green exit code means every parity probe of this run passed
+        sys.exit(3)
+
+
+EXTRA_CONFIGS = {1: ["c1", "c3", "c4"], 2: ["c4"], 4: ["c4"], 8: ["c4", "c5"]}  # c5 at N=1 is 1.2 s per step: N=8 only
+
+
+def run_extra_configs(args, name, world, rank):
+    """After the headline (c2) of a default run: the other BASELINE.json configurations at this N, 3 timed steps each, so
+    that a driver-run record carries them and their parity verdicts.  Every rank starts the same child
+    (`bench.py --config cX --gpus N`) with its own RANK / LOCAL_RANK and a fresh rendezvous port; rank 0's child prints
+    the JSON line, which is compacted here.  A child that fails is recorded as {"error": ...}: the headline stands."""
+    import subprocess
+
+    if name != "c2" or args.tokens or world not in EXTRA_CONFIGS:
+        return None
+    out = {}
+    base_port = int(os.environ.get("MASTER_PORT", "29500"))
+    for i, cname in enumerate(EXTRA_CONFIGS[world]):
+        env = dict(os.environ)
+        env.pop("TORCHELASTIC_USE_AGENT_STORE", None)  # the child group brings its own store on its own port
+        env["MASTER_PORT"] = str(base_port + 23 + 7 * i)
+        cmd = [sys.executable, os.path.abspath(__file__), "--config", cname, "--gpus", str(world), "--steps", "3",
+               "--warmup", "3", "--no-extra-configs", "--no-token-ops", "--tp-reduce", args.tp_reduce, "--tp-exchange",
+               args.tp_exchange, "--e2e-gather", args.e2e_gather]
+        cmd += ["--cpu-tokens", "20480"] if cname == "c1" else ["--no-cpu-baseline"]  # c1: the CPU side in full (§8d)
+        try:
+            r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=420)
+        except subprocess.TimeoutExpired:
+            out[cname] = {"error": "timeout after 420 s"}
+            continue
+        if rank != 0:
+            continue
+        rec = None
+        for ln in reversed(r.stdout.splitlines()):
+            if ln.startswith("{"):
+                try:
+                    rec = json.loads(ln)
+                    break
+                except ValueError:
+                    pass
+        if rec is None:  # rc 3 = the child's own parity probe failed: its line is still there and says so
+            out[cname] = {"error": f"rc={r.returncode}: " + (r.stderr.strip().splitlines() or ["no output"])[-1][:300]}
+            continue
+        par = rec.get("parity") or {}
+        step = rec.get("roofline_step") or {}
+        out[cname] = {
+            "workload": rec["config"].get("workload"), "ms_per_step": rec["ms_per_step"], "value": rec["value"],
+            "unit": rec["unit"], "steps": rec["steps"], "e2e_ms_per_step": rec["e2e"].get("ms_per_step"),
+            "e2e_value": rec["e2e"]["value"], "useful_frac_of_sustained": step.get("useful_frac_of_sustained"),
+            "fwd_frac_of_sustained": (rec.get("roofline") or {}).get("frac"),
+            "parity": {k: par.get(k) for k in ("ok", "lp_max_abs", "ent_max_abs", "loss_rel", "dh_excess_over_tol",
+                                               "dw_excess_over_tol") if k in par},
+            "clocks": rec.get("clocks"),
+        }
+        if rec.get("cpu_baseline"):
+            out[cname]["cpu_baseline"] = rec["cpu_baseline"]
+    return out if rank == 0 else {}
 
 
 def token_ops_table(torch, dev, peaks, log2_tokens: int = 25):
@@ -978,6 +1059,9 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the fp32 parity probe (outside the timed region)")
     ap.add_argument("--token-ops", action=argparse.BooleanOptionalAction, default=True,
                     help="N=1: add the token-op HBM roofline table as `extra` (default on; --no-token-ops skips it)")
+    ap.add_argument("--extra-configs", action=argparse.BooleanOptionalAction, default=True,
+                    help="default run (c2): afterwards run the other BASELINE configurations at this N for 3 steps each "
+                         "in child processes and attach them as extra.configs (N=1: c1 c3 c4; N=2/4: c4; N=8: c4 c5)")
     ap.add_argument("--bwd-ws-mb", type=int, default=0,
                     help="dlogits workspace budget of the backward in MiB (0 = library default, 3072)")
     ap.add_argument("--tp-reduce", choices=["auto", "fused", "nccl", "multimem", "overlap"], default="auto",
