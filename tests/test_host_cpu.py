@@ -267,3 +267,35 @@ def test_backward_chunk_under_memory_pressure(monkeypatch):
     pretend(GiB // 2)  # less than the 896 MiB accumulator alone
     with pytest.raises(RuntimeError, match="accumulator"):
         ops.backward_chunk(T, H, V, "cuda:0")
+
+
+def test_compat_install_rebinds_callers_that_imported_by_name():
+    """a caller that did `from verl.trainer.ppo.core_algos import agg_loss` before install() must not
+    keep the reference function.  Fake reference modules stand in for verl (separate process: install() edits
+    sys.modules)."""
+    import subprocess
+
+    code = '''
+import sys, types
+def mk(name, **attrs):
+    m = types.ModuleType(name); m.__dict__.update(attrs); sys.modules[name] = m
+    parent, _, leaf = name.rpartition(".")
+    if parent: setattr(sys.modules[parent], leaf, m)
+    return m
+for pkg in ("verl", "verl.trainer", "verl.trainer.ppo", "verl.workers", "verl.workers.actor"):
+    mk(pkg).__path__ = []
+def agg_loss(*a, **k): return "reference"
+def kl_penalty(*a, **k): return "reference"
+ca = mk("verl.trainer.ppo.core_algos", agg_loss=agg_loss, kl_penalty=kl_penalty, ADV_ESTIMATOR_REGISTRY={}, POLICY_LOSS_REGISTRY={})
+caller = mk("verl.workers.actor.dp_actor", agg_loss=agg_loss, kl_penalty=kl_penalty, unrelated=len)
+import verl_b200.compat as c
+from verl_b200.trainer.ppo import core_algos as ours
+r = c.install()
+assert r["verl.trainer.ppo.core_algos"] == "patched", r
+assert ca.agg_loss is ours.agg_loss and caller.agg_loss is ours.agg_loss and caller.kl_penalty is ours.kl_penalty
+assert caller.unrelated is len
+assert "verl.workers.actor.dp_actor.agg_loss" in r["rebound"], r
+print("ok")
+'''
+    out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stdout + out.stderr

@@ -73,6 +73,25 @@ def _namespace(name):
     return mod
 
 
+def _rebind_by_name_imports(replaced: dict) -> list:
+    """`from verl.trainer.ppo.core_algos import agg_loss, kl_penalty` executed BEFORE install() leaves the caller holding
+    the reference function (verl/workers/actor/dp_actor.py:29,36, megatron_actor.py:40, ray_trainer.py:47): patching the
+    defining module's attribute does not reach it.  Walk the already-imported `verl.*` modules and swap every module
+    global that still IS one of the replaced reference objects.  -> ["module.name", ...] of what was re-bound."""
+    if not replaced:
+        return []
+    rebound = []
+    for mod_name, mod in list(sys.modules.items()):
+        if mod is None or not (mod_name == "verl" or mod_name.startswith("verl.")):
+            continue
+        for attr, val in list(vars(mod).items()):
+            hit = replaced.get(id(val))
+            if hit is not None and hit[0] is val:
+                setattr(mod, attr, hit[1])
+                rebound.append(f"{mod_name}.{attr}")
+    return sorted(rebound)
+
+
 _EXTRA_TARGETS = {
     # §8(f).3 / (f).4 callers' plumbing: module -> (verl_b200 module, names)
     "verl.utils.seqlen_balancing": ("verl_b200.utils.seqlen_balancing", [
@@ -88,7 +107,9 @@ _EXTRA_TARGETS = {
 
 
 def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
-    """Route the reference's hot-path imports to verl_b200.  Returns {module name: 'patched' | 'shadowed'}.
+    """Route the reference's hot-path imports to verl_b200.  Returns {module name: 'patched' | 'shadowed'} (+ the key
+    'rebound': module globals of already-imported `verl.*` callers that held a reference function by name and were
+    swapped too, so calling install() after the workers were imported still takes effect).
 
     The §8(f).3/(f).4 plumbing modules (seqlen_balancing, ulysses, megatron.tensor_parallel, mcore.util) are shadowed
     when the reference module is not importable; an importable one is only patched with patch_extras=True (its
@@ -120,10 +141,14 @@ def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
         "verl.trainer.ppo.metric_utils": (_mu, ["compute_data_metrics"]),
         "verl.trainer.ppo.ray_trainer": (_rt, ["apply_kl_penalty", "compute_response_mask", "compute_advantage"]),
     }
+    replaced = {}  # id(reference object) -> (reference object, replacement): for callers that imported it BY NAME
     for name, (src, names) in targets.items():
         real = _try_import(name)
         if real is not None and real is not src:
             for n in names:
+                old = getattr(real, n, None)
+                if old is not None and old is not getattr(src, n) and callable(old):
+                    replaced[id(old)] = (old, getattr(src, n))
                 setattr(real, n, getattr(src, n))
             if name.endswith("ray_trainer"):  # `from verl.trainer.ppo.metric_utils import compute_data_metrics` at its top
                 real.compute_data_metrics = _mu.compute_data_metrics
@@ -138,6 +163,9 @@ def install(patch_flash_attn: bool = False, patch_extras: bool = False) -> dict:
             sys.modules[name] = src
             setattr(_namespace(parent), leaf, src)
             report[name] = "shadowed"
+    rebound = _rebind_by_name_imports(replaced)
+    if rebound:
+        report["rebound"] = rebound
     if patch_flash_attn:
         fa = _try_import("flash_attn.bert_padding")
         if fa is not None:
