@@ -161,7 +161,16 @@ def test_agg_loss_and_kl_penalty(dev):
         base = {"k1": "kl", "k2": "mse", "k3": "low_var_kl"}.get(kind, kind)
         lpg = lp.clone().requires_grad_(True)
         out = ca.kl_penalty(lpg, ref, kind)
-        close(out, T(g["kl_penalty|" + base], dev), rel=1e-6, abs_=5e-7)  # exp(k)-k-1 cancels to ~1 ulp of 1.0
+        # Which bar governs per-token kl_penalty: the 1e-5 RELATIVE bar of north_star is stated
+        # for "loss and advantages", i.e. for the aggregated scalars and O(1) per-token values.  A per-token
+        # low_var_kl is exp(k) - k - 1 with k near 0: both implementations cancel ~1.0 - 1.0 in fp32, so one element
+        # is only good to ~1 ulp of 1.0 (6e-8) in ABSOLUTE terms and its relative error is unbounded as kl -> 0 (the
+        # 1.37e-5 max_rel_err of profiles/r2_final2_driver_ops_e2e.jsonl is one such element of size ~4e-3).  The
+        # per-token bar is therefore absolute (5e-7 = a few ulp of 1.0) with a tight relative term for large values;
+        # the 1e-5 relative bar is applied where the reference consumes the values: the aggregated kl loss below.
+        close(out, T(g["kl_penalty|" + base], dev), rel=1e-6, abs_=5e-7)
+        want_agg = port.agg_loss(T(g["kl_penalty|" + base], "cpu"), T(g["mask"], "cpu"), "token-mean")
+        np.testing.assert_allclose(float(ca.agg_loss(out.detach(), mask, "token-mean")), float(want_agg), rtol=REL)
         out.sum().backward()
         lpc = T(g["lp"], "cpu").requires_grad_(True)
         port.kl_penalty(lpc, T(g["ref"], "cpu"), base).sum().backward()
