@@ -947,6 +947,8 @@ def run_ours(args, name, cfg):
     if rank == 0:
         if extra_cfgs is not None:
             line.setdefault("extra", {})["configs"] = extra_cfgs
+        if args.reference_gpu and world == 1 and name == "c2" and not args.tokens:
+            line.setdefault("extra", {})["reference_gpu"] = reference_gpu_leg(cfg)
         # compact verdict as the LAST key: it survives a tail of the line
         probes = {name: parity}
         probes.update({k: v.get("parity") for k, v in (extra_cfgs or {}).items()})
@@ -961,6 +963,11 @@ def run_ours(args, name, cfg):
                                                      for k, v in (extra_cfgs or {}).items()}},
             "unit": "ms_per_step; parity_ok covers the fp32 probe of every configuration listed, at this N",
         }
+        rg = (line.get("extra") or {}).get("reference_gpu") or {}
+        if "speedup_over_triton" in rg or "speedup_over_torch_fused" in rg:
+            line["verdict"]["x_reference_gpu_fwd_bwd"] = {
+                "triton": round((rg.get("speedup_over_triton") or {}).get("fwd_bwd", 0.0), 2) or None,
+                "torch_fused": round((rg.get("speedup_over_torch_fused") or {}).get("fwd_bwd", 0.0), 2) or None}
         print(json.dumps(line), flush=True)
     if world > 1:
         flag = torch.tensor([1 if parity_ok else 0], device=dev)
@@ -969,6 +976,37 @@ def run_ours(args, name, cfg):
         dist.destroy_process_group()
     if not parity_ok:  # a green exit code means every parity probe of this run passed
         sys.exit(3)
+
+
+def reference_gpu_leg(cfg, timeout_s: int = 420):
+    """The reference's own GPU implementations of the lm-head op on this B200, beside ours ("the reference GPU
+    comparator to beat"): its Triton kernels and its default cuBLAS-chunked `torch` backend, unmodified from the
+    oracle/_ref snapshot, timed by scripts/bench_ref_gpu.py in a child process with the protocol of the reference's own
+    test (tests/utils/test_linear_cross_entropy.py:289-348: forward and backward timed separately, peak memory).  A
+    comparator outside every timed region; a failure is recorded and leaves the headline alone."""
+    import subprocess
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "ref_gpu.json")
+        cmd = [sys.executable, os.path.join(ROOT, "scripts", "bench_ref_gpu.py"), "--tokens", str(cfg["T"]), "--hidden",
+               str(cfg["H"]), "--vocab", str(cfg["V"]), "--iters", "2", "--warmup", "1", "--out", out]
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+            rep = json.load(open(out))
+        except Exception as e:  # noqa: BLE001
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+    res = {"shape": rep.get("shape"), "protocol": "reference tests/utils/test_linear_cross_entropy.py:289-348, 2 iterations "
+           "after 1 warm-up, CUDA events, same inputs for all three; unmodified reference from oracle/_ref"}
+    for k, v in (rep.get("impls") or {}).items():
+        res[k] = {"fwd_ms": v.get("fwd_ms"), "bwd_ms": v.get("bwd_ms"), "fwd_bwd_ms": v.get("fwd_bwd_ms"),
+                  "peak_fwd_MB": v.get("peak_fwd_MB"), "peak_bwd_MB": v.get("peak_bwd_MB")}
+    for k in ("ours_vs_triton", "ours_vs_torch_fused", "speedup_over_triton", "speedup_over_torch_fused"):
+        if k in rep:
+            res[k] = rep[k]
+    if rep.get("errors"):
+        res["errors"] = rep["errors"]
+    return res
 
 
 EXTRA_CONFIGS = {1: ["c1", "c3", "c4"], 2: ["c4"], 4: ["c4"], 8: ["c4", "c5"]}  # c5 at N=1 is 1.2 s per step: N=8 only
@@ -990,7 +1028,7 @@ def run_extra_configs(args, name, world, rank):
         env.pop("TORCHELASTIC_USE_AGENT_STORE", None)  # the child group brings its own store on its own port
         env["MASTER_PORT"] = str(base_port + 23 + 7 * i)
         cmd = [sys.executable, os.path.abspath(__file__), "--config", cname, "--gpus", str(world), "--steps", "3",
-               "--warmup", "3", "--no-extra-configs", "--no-token-ops", "--tp-reduce", args.tp_reduce, "--tp-exchange",
+               "--warmup", "3", "--no-extra-configs", "--no-reference-gpu", "--no-token-ops", "--tp-reduce", args.tp_reduce, "--tp-exchange",
                args.tp_exchange, "--e2e-gather", args.e2e_gather]
         cmd += ["--cpu-tokens", "20480"] if cname == "c1" else ["--no-cpu-baseline"]  # c1: the CPU side in full (§8d)
         try:
@@ -1062,6 +1100,9 @@ def main():
     ap.add_argument("--extra-configs", action=argparse.BooleanOptionalAction, default=True,
                     help="default run (c2): afterwards run the other BASELINE configurations at this N for 3 steps each "
                          "in child processes and attach them as extra.configs (N=1: c1 c3 c4; N=2/4: c4; N=8: c4 c5)")
+    ap.add_argument("--reference-gpu", action=argparse.BooleanOptionalAction, default=True,
+                    help="default run (c2, N=1): time the reference's Triton op and its torch backend on this GPU in a "
+                         "child process and attach them as extra.reference_gpu")
     ap.add_argument("--bwd-ws-mb", type=int, default=0,
                     help="dlogits workspace budget of the backward in MiB (0 = library default, 3072)")
     ap.add_argument("--tp-reduce", choices=["auto", "fused", "nccl", "multimem", "overlap"], default="auto",

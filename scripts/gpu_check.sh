@@ -61,7 +61,7 @@ for stage in "$@"; do
         M=gpu__time_duration.sum,dram__bytes.sum.per_second,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,sm__throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread,launch__grid_size,launch__block_size,smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio,dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum
         timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
             --log-file $out/${T}_ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-parity \
-            --no-token-ops --no-extra-configs > $out/${T}_ncu_launches.log 2>&1; echo "ncu launch list rc=$?"
+            --no-token-ops --no-extra-configs --no-reference-gpu > $out/${T}_ncu_launches.log 2>&1; echo "ncu launch list rc=$?"
         timeout 900 ncu --set full --clock-control none --import-source on -k regex:tc_gemm -c 16 -o $out/${T}_lce_full -f \
             python scripts/prof_step.py > $out/${T}_ncu_full.log 2>&1; echo "ncu full rc=$?"
         python scripts/ncu_summary.py $out/${T}_lce_full.ncu-rep $out/${T}_ncu_full_tc_gemm_kernels.csv \
