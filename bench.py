@@ -906,8 +906,9 @@ def run_ours(args, name, cfg):
                 "frac": fwd_tf / peaks["sustained"] if fwd_tf else None,
                 "traffic": _traffic(T, H, v_local),
                 "traffic_unit": "bytes of DRAM read+write per launch (ncu --set full, profiles/roofline_traffic.json); "
-                                "algorithmic operand bytes = 2*(T*H + V*H) + 16*S*T; cache-aware I/O lower bound of the "
-                                "contraction through a 126 MB L2 = 2*T*V*H/sqrt(L2 elements)*2 B (18 GB at configs[1])",
+                                "algorithmic operand bytes = 2*(T*H + V*H) + 16*S*T; a token-slab-resident schedule through the "
+                                "126 MB L2 would need V*H*2*(T/T_slab) + T*H*2 = 5-9 GB at configs[1] (DESIGN.md 4.1): the "
+                                "excess is the A working set of a wave (136 MB) thrashing L2",
                 "peak_source": peaks["source"] + ", sustained bf16 figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": fwd_tf / peaks["burst"] if fwd_tf else None,
                 "algorithmic_flops_per_launch": flops_fwd / n_fwd, "launch_ms": fwd_kernel_ms / n_fwd if fwd_kernel_ms else None,
